@@ -1,0 +1,165 @@
+/*
+ * tcq4_b200.h -- C ABI of the B200-native TCQ4_K32 W4A4 MUL_MAT hot path.
+ *
+ * Drop-in boundary for skyne98/llama.cpp-rrs (all file:line under /root/reference):
+ * every entry point below replaces one piece of the fork's ggml-cuda plug-in surface for
+ * GGML_TYPE_TCQ4_K32 and nothing else.  Plain pointers and sizes only; all data pointers are
+ * DEVICE pointers unless the name says host.  No entry point allocates, synchronises or touches
+ * host state on the launch path, so every launch is CUDA-graph-capture safe
+ * (ggml/src/ggml-cuda/ggml-cuda.cu:3791-3799).
+ *
+ * There is no CPU fallback: on a machine without an sm_100 device every compute entry point
+ * returns TCQ4_ERR_NO_DEVICE.
+ */
+#ifndef TCQ4_B200_H
+#define TCQ4_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+#ifndef __cplusplus
+#include <stdbool.h>
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__CUDACC__) || defined(CUDART_VERSION) || defined(__DRIVER_TYPES_H__)
+/* cudaStream_t already known */
+#else
+typedef struct CUstream_st *cudaStream_t;
+#endif
+
+#define TCQ4_B200_API __attribute__((visibility("default")))
+
+/* ---- format constants (ggml/src/ggml-common.h:315-341, ggml/src/ggml.c:750-757) ------------- */
+#define TCQ4_B200_GGML_TYPE        42     /* GGML_TYPE_TCQ4_K32, ggml/include/ggml.h:432 */
+#define TCQ4_B200_TILE_K           256
+#define TCQ4_B200_TILE_CHANNELS    8
+#define TCQ4_B200_TILE_BYTES       1184
+#define TCQ4_B200_ACT_BLOCK_BYTES  160    /* block_rrs_int4_tc, ggml/src/ggml-cuda/tcq4_k32.cuh:51-56 */
+
+/* ---- status codes (the reference aborts via GGML_ASSERT, rrs.cu:256-259; the shim asserts ==0) */
+enum {
+    TCQ4_OK             = 0,
+    TCQ4_ERR_SHAPE      = 1,   /* K % 256 != 0, N % 8 != 0, or non-positive dims (rrs.cu:258-259) */
+    TCQ4_ERR_ARG        = 2,   /* null / misaligned pointer */
+    TCQ4_ERR_WORKSPACE  = 3,   /* workspace too small (and cannot grow: stream is capturing) */
+    TCQ4_ERR_CUDA       = 4,   /* a CUDA runtime call failed; see tcq4_b200_last_error() */
+    TCQ4_ERR_NO_DEVICE  = 5    /* no sm_100 device: there is no CPU fallback */
+};
+
+/* kernel selection, see tcq4_b200_select_kernel() */
+enum {
+    TCQ4_KERNEL_AUTO  = 0,
+    TCQ4_KERNEL_GEMV  = 1,     /* fused FWHT+quant+streaming dot, small M, HBM-bound          */
+    TCQ4_KERNEL_GEMM  = 2      /* activation kernel + tcgen05.mma kind::i8 GEMM, tensor-bound */
+};
+
+TCQ4_B200_API const char *tcq4_b200_version(void);
+TCQ4_B200_API const char *tcq4_b200_last_error(void);
+
+/* ggml_cuda_supports_rrs + the asserts of ggml_cuda_rrs_mul_mat (rrs.cu:237-239, 256-259) and the
+ * MUL_MAT case of ggml_backend_cuda_device_supports_op (ggml-cuda.cu:4457-4459).
+ * cc = compute capability * 10 (100 for sm_100).  Returns 1 if this library takes the op. */
+TCQ4_B200_API int tcq4_b200_supports(int64_t M, int64_t N, int64_t K, int cc);
+
+/* Which kernel ggml_cuda_rrs_mul_mat's dispatch (rrs.cu:317-343) would map to here. */
+TCQ4_B200_API int tcq4_b200_select_kernel(int64_t M, int64_t N, int64_t K);
+
+/* Scratch bytes tcq4_b200_mul_mat_ws needs for this shape (quantised activations, split-K partials).
+ * The reference's live path needs none (rrs.cu:321); its #else path takes it from ctx.pool()
+ * (rrs.cu:326-328) -- a ggml shim does the same with this size. */
+TCQ4_B200_API size_t tcq4_b200_workspace_size(int64_t M, int64_t N, int64_t K);
+
+/* THE hot path.  Replaces tcq4_rrs_fused_gemm_smallM (tcq4_k32.cuh:150-156, called from
+ * ggml_cuda_rrs_mul_mat, rrs.cu:321):  y[m*N+n] = sum_k W[n][k] * x[m*K+k] in W4A4 arithmetic.
+ *   w_tiles : [N/8][K/256] block_tcq4_tile, 16-byte aligned (ggml buffers are 128-byte aligned)
+ *   x       : F32 [M][K] contiguous;  y : F32 [M][N] contiguous
+ *   d_perm  : int32[K] device channel permutation or NULL (rrs.cu:266-270)
+ *   workspace: >= tcq4_b200_workspace_size(M,N,K) bytes, 256-byte aligned, must stay valid until
+ *             the launch completes; first use of a workspace must be preceded by
+ *             tcq4_b200_workspace_init (zeroes the split-K tickets).
+ * Asynchronous on `stream`. */
+TCQ4_B200_API int tcq4_b200_mul_mat_ws(const void *w_tiles, const float *x, float *y,
+                                       int64_t M, int64_t N, int64_t K, const int32_t *d_perm,
+                                       void *workspace, size_t workspace_bytes, int kernel,
+                                       cudaStream_t stream);
+TCQ4_B200_API int tcq4_b200_workspace_init(void *workspace, size_t workspace_bytes, cudaStream_t stream);
+
+/* Same, with scratch taken from a per-device arena owned by the library.  The arena grows with
+ * cudaMalloc only outside stream capture; call tcq4_b200_reserve at load time to pre-size it. */
+TCQ4_B200_API int tcq4_b200_mul_mat(const void *w_tiles, const float *x, float *y,
+                                    int64_t M, int64_t N, int64_t K, const int32_t *d_perm,
+                                    cudaStream_t stream);
+TCQ4_B200_API int tcq4_b200_reserve(int64_t max_M, int64_t max_N, int64_t max_K);
+
+/* End-to-end entry with HOST activations/outputs (weights stay resident on the device, as they do
+ * in a ggml CUDA buffer): H2D copy of x, MUL_MAT, D2H copy of y, all on `stream`, then a stream
+ * synchronise.  Mirrors ggml_backend_tensor_set + graph_compute + ggml_backend_tensor_get. */
+TCQ4_B200_API int tcq4_b200_mul_mat_host(const void *w_tiles_dev, const float *x_host, float *y_host,
+                                         int64_t M, int64_t N, int64_t K, const int32_t *d_perm,
+                                         cudaStream_t stream);
+
+/* Stand-alone activation stage.  Replaces tcq4_rrs_fwht_quantize_tc / tcq4_rrs_perm_fwht_quantize_tc
+ * (tcq4_k32.cuh:79-94, tcq4_k32.cu:181-277): perm gather -> FWHT-256 -> 1/16 -> max-scale ->
+ * int4 codes + per-group sums, written as block_rrs_int4_tc [M][K/256] (160 B each). */
+TCQ4_B200_API int tcq4_b200_fwht_quantize_tc(const float *x, void *y_blocks, const int32_t *d_perm,
+                                             int64_t K, int64_t M, cudaStream_t stream);
+
+/* Verification taps (not on the product path): run the chosen kernel and also dump the integer
+ * accumulators.  isum: int32 [M][N][K/256] = sum_g sc[n][kt][g]*dot_g (the TMEM accumulator of the
+ * GEMM, and the same quantity formed from the per-group dots in the GEMV).  Nullable. */
+TCQ4_B200_API int tcq4_b200_mul_mat_debug(const void *w_tiles, const float *x, float *y,
+                                          int64_t M, int64_t N, int64_t K, const int32_t *d_perm,
+                                          void *workspace, size_t workspace_bytes, int kernel,
+                                          int32_t *isum, cudaStream_t stream);
+
+/* ---- channel-permutation registry ------------------------------------------------------------
+ * The three symbols libllama resolves by name through ggml_backend_reg_get_proc_address
+ * (ggml/include/ggml-cuda.h:48-50, ggml-cuda.cu:4148-4158, 4876-4885; caller
+ * src/llama-model.cpp:7176-7197), same names and signatures.  Registration copies h_perm to the
+ * CURRENT device (rrs.cu:82-99); the registry is keyed by (device, name) and guarded by a mutex. */
+TCQ4_B200_API void ggml_backend_cuda_tcq4_register_perm(const char *tensor_name, const int32_t *h_perm, int K);
+TCQ4_B200_API void ggml_backend_cuda_tcq4_clear_perms(void);
+TCQ4_B200_API void ggml_backend_cuda_tcq4_set_reorder_enabled(bool enabled);
+/* ggml_cuda_rrs_get_perm / has_perm / get_reorder_enabled (rrs.cu:101-127): device pointer for the
+ * current device, or NULL when absent or reordering is disabled. */
+TCQ4_B200_API const int32_t *tcq4_b200_get_perm(const char *tensor_name);
+TCQ4_B200_API int  tcq4_b200_has_perm(const char *tensor_name);
+TCQ4_B200_API int  tcq4_b200_get_reorder_enabled(void);
+
+/* ---- N-sharding (no reference counterpart) ------------------------------------------
+ * Rows [n0,n1) of an [N][K] TCQ4 tensor are the contiguous byte range
+ * [n0*(K/256)*148, n1*(K/256)*148) (tiles are n-tile major, ggml-quants.c:1550-1573).
+ * Splits N over `world` ranks at multiples of `align` channels (align % 8 == 0). */
+TCQ4_B200_API int tcq4_b200_shard_range(int64_t N, int64_t K, int world, int rank, int64_t align,
+                                        int64_t *n0, int64_t *n1, size_t *byte_offset, size_t *byte_len);
+
+/* ---- host-side mirror of the ggml operator interface -------------------------------------------
+ * Minimal view of ggml_tensor (ggml/include/ggml.h:650-690): just the fields
+ * ggml_cuda_rrs_mul_mat reads (rrs.cu:247-270).  ne/nb follow ggml (ne[0] fastest). */
+typedef struct {
+    int         type;        /* ggml_type: 0 = F32, 42 = TCQ4_K32 */
+    int64_t     ne[4];
+    size_t      nb[4];
+    void       *data;        /* device pointer */
+    const char *name;        /* tensor name, perm lookup key (rrs.cu:268-270) */
+} tcq4_tensor_view;
+
+/* MUL_MAT case of ggml_backend_cuda_device_supports_op for a TCQ4 src0 (ggml-cuda.cu:4397-4459). */
+TCQ4_B200_API int tcq4_b200_ggml_supports_op(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1,
+                                             const tcq4_tensor_view *dst, int cc);
+/* ggml_cuda_rrs_mul_mat (rrs.cu:241-344): shape extraction, asserts (returned as status instead
+ * of abort), perm lookup by src0->name, launch on `stream` (= ctx.stream()). */
+TCQ4_B200_API int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1,
+                                         tcq4_tensor_view *dst, void *workspace, size_t workspace_bytes,
+                                         cudaStream_t stream);
+
+/* Launch statistics since load (kernels launched by this library), for bench.py's gpu_launches. */
+TCQ4_B200_API uint64_t tcq4_b200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TCQ4_B200_H */

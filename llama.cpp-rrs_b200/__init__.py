@@ -1,0 +1,134 @@
+"""tcq4_b200 -- host-side binding of the B200-native TCQ4_K32 W4A4 MUL_MAT path.
+
+The product is the C-ABI shared library ``libtcq4_b200.so`` (include/tcq4_b200.h) built from
+``csrc/``; this module is the thin Python mirror of the reference's operator interface for this
+path (``ggml_cuda_rrs_mul_mat`` and the ``ggml_backend_cuda_tcq4_*`` registry,
+/root/reference/ggml/src/ggml-cuda/rrs.cu:82-127, 241-344).  PyTorch is used for device memory,
+streams and torch.distributed plumbing only: no torch type crosses the C boundary.
+
+There is NO CPU fallback and nothing here touches ``oracle/``: if the CUDA library is missing the
+import fails loudly, and compute calls without an sm_100 device raise ``Tcq4Error``.
+
+The directory name ``llama.cpp-rrs_b200`` is not a Python identifier; load it with
+``__graft_entry__.load_package()`` (registers it as module ``tcq4_b200``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libtcq4_b200.so")
+
+TILE_BYTES = 1184
+TILE_K = 256
+TILE_CHANNELS = 8
+ACT_BLOCK_BYTES = 160
+GGML_TYPE_F32 = 0
+GGML_TYPE_TCQ4_K32 = 42
+
+KERNEL_AUTO, KERNEL_GEMV, KERNEL_GEMM = 0, 1, 2
+
+STATUS = {0: "OK", 1: "ERR_SHAPE", 2: "ERR_ARG", 3: "ERR_WORKSPACE", 4: "ERR_CUDA", 5: "ERR_NO_DEVICE"}
+
+# every symbol include/tcq4_b200.h declares (tests check the library exports all of them)
+EXPORTS = [
+    "tcq4_b200_version", "tcq4_b200_last_error", "tcq4_b200_supports", "tcq4_b200_select_kernel",
+    "tcq4_b200_workspace_size", "tcq4_b200_mul_mat_ws", "tcq4_b200_workspace_init", "tcq4_b200_mul_mat",
+    "tcq4_b200_reserve", "tcq4_b200_mul_mat_host", "tcq4_b200_fwht_quantize_tc", "tcq4_b200_mul_mat_debug",
+    "ggml_backend_cuda_tcq4_register_perm", "ggml_backend_cuda_tcq4_clear_perms",
+    "ggml_backend_cuda_tcq4_set_reorder_enabled", "tcq4_b200_get_perm", "tcq4_b200_has_perm",
+    "tcq4_b200_get_reorder_enabled", "tcq4_b200_shard_range", "tcq4_b200_ggml_supports_op",
+    "tcq4_b200_ggml_mul_mat", "tcq4_b200_launch_count",
+]
+
+
+class Tcq4Error(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"tcq4_b200: {STATUS.get(status, status)}: {msg}")
+        self.status = status
+
+
+class TensorView(C.Structure):
+    """tcq4_tensor_view (include/tcq4_b200.h): the ggml_tensor fields ggml_cuda_rrs_mul_mat reads."""
+    _fields_ = [("type", C.c_int), ("ne", C.c_int64 * 4), ("nb", C.c_size_t * 4), ("data", C.c_void_p),
+                ("name", C.c_char_p)]
+
+
+def _load() -> C.CDLL:
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a).  There is no CPU or PyTorch fallback for this path.")
+    lib = C.CDLL(LIB_PATH)
+    i64, vp, sz, ci = C.c_int64, C.c_void_p, C.c_size_t, C.c_int
+    lib.tcq4_b200_version.restype = C.c_char_p
+    lib.tcq4_b200_last_error.restype = C.c_char_p
+    lib.tcq4_b200_supports.argtypes = [i64, i64, i64, ci]
+    lib.tcq4_b200_select_kernel.argtypes = [i64, i64, i64]
+    lib.tcq4_b200_workspace_size.restype = sz
+    lib.tcq4_b200_workspace_size.argtypes = [i64, i64, i64]
+    lib.tcq4_b200_mul_mat_ws.argtypes = [vp, vp, vp, i64, i64, i64, vp, vp, sz, ci, vp]
+    lib.tcq4_b200_workspace_init.argtypes = [vp, sz, vp]
+    lib.tcq4_b200_mul_mat.argtypes = [vp, vp, vp, i64, i64, i64, vp, vp]
+    lib.tcq4_b200_reserve.argtypes = [i64, i64, i64]
+    lib.tcq4_b200_mul_mat_host.argtypes = [vp, vp, vp, i64, i64, i64, vp, vp]
+    lib.tcq4_b200_fwht_quantize_tc.argtypes = [vp, vp, vp, i64, i64, vp]
+    lib.tcq4_b200_mul_mat_debug.argtypes = [vp, vp, vp, i64, i64, i64, vp, vp, sz, ci, vp, vp]
+    lib.ggml_backend_cuda_tcq4_register_perm.restype = None
+    lib.ggml_backend_cuda_tcq4_register_perm.argtypes = [C.c_char_p, vp, ci]
+    lib.ggml_backend_cuda_tcq4_clear_perms.restype = None
+    lib.ggml_backend_cuda_tcq4_set_reorder_enabled.restype = None
+    lib.ggml_backend_cuda_tcq4_set_reorder_enabled.argtypes = [C.c_bool]
+    lib.tcq4_b200_get_perm.restype = vp
+    lib.tcq4_b200_get_perm.argtypes = [C.c_char_p]
+    lib.tcq4_b200_has_perm.argtypes = [C.c_char_p]
+    lib.tcq4_b200_shard_range.argtypes = [i64, i64, ci, ci, i64, C.POINTER(i64), C.POINTER(i64),
+                                          C.POINTER(sz), C.POINTER(sz)]
+    lib.tcq4_b200_ggml_supports_op.argtypes = [C.POINTER(TensorView)] * 3 + [ci]
+    lib.tcq4_b200_ggml_mul_mat.argtypes = [C.POINTER(TensorView)] * 3 + [vp, sz, vp]
+    lib.tcq4_b200_launch_count.restype = C.c_uint64
+    return lib
+
+
+LIB = _load()
+
+
+def _check(status: int):
+    if status != 0:
+        raise Tcq4Error(status, LIB.tcq4_b200_last_error().decode(errors="replace"))
+
+
+def version() -> str:
+    return LIB.tcq4_b200_version().decode()
+
+
+def launch_count() -> int:
+    return int(LIB.tcq4_b200_launch_count())
+
+
+def supports(M: int, N: int, K: int, cc: int = 100) -> bool:
+    return bool(LIB.tcq4_b200_supports(M, N, K, cc))
+
+
+def select_kernel(M: int, N: int, K: int) -> int:
+    return int(LIB.tcq4_b200_select_kernel(M, N, K))
+
+
+def workspace_size(M: int, N: int, K: int) -> int:
+    return int(LIB.tcq4_b200_workspace_size(M, N, K))
+
+
+def tile_bytes(N: int, K: int) -> int:
+    """ggml_nbytes of an [N][K] TCQ4_K32 tensor (ggml.c:750-757: N * K/256 * 148)."""
+    return (N // TILE_CHANNELS) * (K // TILE_K) * TILE_BYTES
+
+
+def shard_range(N: int, K: int, world: int, rank: int, align: int = 128):
+    n0, n1 = C.c_int64(), C.c_int64()
+    off, ln = C.c_size_t(), C.c_size_t()
+    _check(LIB.tcq4_b200_shard_range(N, K, world, rank, align, C.byref(n0), C.byref(n1), C.byref(off), C.byref(ln)))
+    return n0.value, n1.value, off.value, ln.value
+
+
+from ._device import *  # noqa: E402,F401,F403  (torch-facing half: memory, streams, distributed)

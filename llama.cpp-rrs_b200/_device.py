@@ -1,0 +1,241 @@
+"""Torch-facing half of the binding: device memory, streams, torch.distributed plumbing.
+
+Mirrors the reference operator interface for this path:
+  mul_mat / ggml_mul_mat      <- ggml_cuda_rrs_mul_mat            (rrs.cu:241-344)
+  fwht_quantize_tc            <- tcq4_rrs_(perm_)fwht_quantize_tc (tcq4_k32.cuh:79-94)
+  register_perm / clear_perms / set_reorder_enabled / get_perm    (rrs.cu:82-127)
+  ShardedWeight               <- N-sharded MUL_MAT + all-gather (no reference counterpart)
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
+               ACT_BLOCK_BYTES, TensorView, _check, shard_range, tile_bytes, workspace_size)
+
+__all__ = ["Workspace", "mul_mat", "mul_mat_debug", "mul_mat_host", "fwht_quantize_tc", "register_perm",
+           "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
+           "ggml_supports_op", "ShardedWeight", "random_tiles"]
+
+
+def _stream_ptr(stream=None) -> int:
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return int(s.cuda_stream)
+
+
+def _req_cuda(t: torch.Tensor, dtype, what: str):
+    if not t.is_cuda or t.dtype != dtype or not t.is_contiguous():
+        raise ValueError(f"{what} must be a contiguous CUDA tensor of dtype {dtype}")
+
+
+class Workspace:
+    """Caller-owned scratch arena for tcq4_b200_mul_mat_ws (the ggml shim would take it from ctx.pool())."""
+
+    def __init__(self, nbytes: int, device=None):
+        nbytes = max(int(nbytes), 256)
+        self.buf = torch.zeros(nbytes + 256, dtype=torch.uint8, device=device or "cuda")
+        off = (-self.buf.data_ptr()) % 256
+        self.ptr = self.buf.data_ptr() + off
+        self.nbytes = nbytes
+        # torch.zeros already cleared the split-K tickets; init again through the ABI for parity of use
+        _check(LIB.tcq4_b200_workspace_init(self.ptr, self.nbytes, _stream_ptr()))
+
+    @classmethod
+    def for_shape(cls, M: int, N: int, K: int, device=None) -> "Workspace":
+        return cls(workspace_size(M, N, K), device)
+
+
+def mul_mat(w_tiles: torch.Tensor, x: torch.Tensor, N: int, perm: torch.Tensor | None = None,
+            out: torch.Tensor | None = None, workspace: Workspace | None = None, kernel: int = KERNEL_AUTO,
+            stream=None) -> torch.Tensor:
+    """y[M][N] = W4A4(w_tiles [N][K], x [M][K]).  Asynchronous on the current stream."""
+    _req_cuda(w_tiles, torch.uint8, "w_tiles")
+    _req_cuda(x, torch.float32, "x")
+    M, K = x.shape
+    if w_tiles.numel() != tile_bytes(N, K):
+        raise ValueError(f"w_tiles has {w_tiles.numel()} bytes, expected {tile_bytes(N, K)} for N={N} K={K}")
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.float32, device=x.device)
+    _req_cuda(out, torch.float32, "out")
+    pp = 0
+    if perm is not None:
+        _req_cuda(perm, torch.int32, "perm")
+        pp = perm.data_ptr()
+    if workspace is None:
+        _check(LIB.tcq4_b200_mul_mat(w_tiles.data_ptr(), x.data_ptr(), out.data_ptr(), M, N, K, pp,
+                                     _stream_ptr(stream)))
+    else:
+        _check(LIB.tcq4_b200_mul_mat_ws(w_tiles.data_ptr(), x.data_ptr(), out.data_ptr(), M, N, K, pp,
+                                        workspace.ptr, workspace.nbytes, kernel, _stream_ptr(stream)))
+    return out
+
+
+def mul_mat_debug(w_tiles: torch.Tensor, x: torch.Tensor, N: int, perm: torch.Tensor | None = None,
+                  kernel: int = KERNEL_AUTO, workspace: Workspace | None = None):
+    """Verification tap: returns (y, isum int32 [M][N][K/256]) -- the integer accumulators."""
+    _req_cuda(w_tiles, torch.uint8, "w_tiles")
+    _req_cuda(x, torch.float32, "x")
+    M, K = x.shape
+    ws = workspace or Workspace.for_shape(M, N, K, x.device)
+    y = torch.empty((M, N), dtype=torch.float32, device=x.device)
+    isum = torch.zeros((M, N, K // TILE_K), dtype=torch.int32, device=x.device)
+    pp = perm.data_ptr() if perm is not None else 0
+    _check(LIB.tcq4_b200_mul_mat_debug(w_tiles.data_ptr(), x.data_ptr(), y.data_ptr(), M, N, K, pp, ws.ptr,
+                                       ws.nbytes, kernel, isum.data_ptr(), _stream_ptr()))
+    return y, isum
+
+
+def mul_mat_host(w_tiles: torch.Tensor, x_host: torch.Tensor, y_host: torch.Tensor, N: int,
+                 perm: torch.Tensor | None = None, stream=None) -> torch.Tensor:
+    """End-to-end call with HOST (pinned) x and y; weights resident on the device.  Synchronous."""
+    _req_cuda(w_tiles, torch.uint8, "w_tiles")
+    if x_host.is_cuda or y_host.is_cuda or x_host.dtype != torch.float32 or y_host.dtype != torch.float32:
+        raise ValueError("x_host / y_host must be float32 CPU tensors (pinned for full speed)")
+    M, K = x_host.shape
+    pp = perm.data_ptr() if perm is not None else 0
+    _check(LIB.tcq4_b200_mul_mat_host(w_tiles.data_ptr(), x_host.data_ptr(), y_host.data_ptr(), M, N, K, pp,
+                                      _stream_ptr(stream)))
+    return y_host
+
+
+def fwht_quantize_tc(x: torch.Tensor, perm: torch.Tensor | None = None, stream=None) -> torch.Tensor:
+    """Stand-alone activation stage -> block_rrs_int4_tc bytes [M][K/256][160]."""
+    _req_cuda(x, torch.float32, "x")
+    M, K = x.shape
+    out = torch.empty((M, K // TILE_K, ACT_BLOCK_BYTES), dtype=torch.uint8, device=x.device)
+    pp = perm.data_ptr() if perm is not None else 0
+    _check(LIB.tcq4_b200_fwht_quantize_tc(x.data_ptr(), out.data_ptr(), pp, K, M, _stream_ptr(stream)))
+    return out
+
+
+def reserve(max_M: int, max_N: int, max_K: int):
+    _check(LIB.tcq4_b200_reserve(max_M, max_N, max_K))
+
+
+# ---- channel-permutation registry (ggml_backend_cuda_tcq4_*, ggml-cuda.cu:4148-4158) ------------
+def register_perm(name: str, perm) -> None:
+    p = torch.as_tensor(perm, dtype=torch.int32).contiguous().cpu()
+    LIB.ggml_backend_cuda_tcq4_register_perm(name.encode(), p.data_ptr(), int(p.numel()))
+
+
+def clear_perms() -> None:
+    LIB.ggml_backend_cuda_tcq4_clear_perms()
+
+
+def set_reorder_enabled(enabled: bool) -> None:
+    LIB.ggml_backend_cuda_tcq4_set_reorder_enabled(bool(enabled))
+
+
+def get_perm_ptr(name: str) -> int:
+    return int(LIB.tcq4_b200_get_perm(name.encode()) or 0)
+
+
+def has_perm(name: str) -> bool:
+    return bool(LIB.tcq4_b200_has_perm(name.encode()))
+
+
+# ---- ggml operator mirror ---------------------------------------------------------------------
+def _view(t: torch.Tensor | None, gtype: int, ne, nb, name: bytes | None, data_ptr: int | None = None) -> TensorView:
+    v = TensorView()
+    v.type = gtype
+    for i in range(4):
+        v.ne[i] = ne[i] if i < len(ne) else 1
+        v.nb[i] = nb[i] if i < len(nb) else nb[-1]
+    v.data = data_ptr if data_ptr is not None else (t.data_ptr() if t is not None else 0)
+    v.name = name
+    return v
+
+
+def _views(w_tiles, x, y, N, name):
+    M, K = x.shape
+    row = (K // TILE_K) * 148
+    src0 = _view(w_tiles, GGML_TYPE_TCQ4_K32, [K, N, 1, 1], [148, row, row * N, row * N], name)
+    src1 = _view(x, GGML_TYPE_F32, [K, M, 1, 1], [4, 4 * K, 4 * K * M, 4 * K * M], b"src1")
+    dst = _view(y, GGML_TYPE_F32, [N, M, 1, 1], [4, 4 * N, 4 * N * M, 4 * N * M], b"dst")
+    return src0, src1, dst
+
+
+def ggml_supports_op(K: int, N: int, M: int, cc: int = 100) -> bool:
+    src0 = _view(None, GGML_TYPE_TCQ4_K32, [K, N, 1, 1], [148, (K // TILE_K) * 148] * 2, b"w", 0)
+    src1 = _view(None, GGML_TYPE_F32, [K, M, 1, 1], [4, 4 * K, 4 * K * M, 4 * K * M], b"x", 0)
+    dst = _view(None, GGML_TYPE_F32, [N, M, 1, 1], [4, 4 * N, 4 * N * M, 4 * N * M], b"y", 0)
+    return bool(LIB.tcq4_b200_ggml_supports_op(C.byref(src0), C.byref(src1), C.byref(dst), cc))
+
+
+def ggml_mul_mat(w_tiles: torch.Tensor, x: torch.Tensor, N: int, name: str = "", out: torch.Tensor | None = None,
+                 workspace: Workspace | None = None, stream=None) -> torch.Tensor:
+    """ggml_cuda_rrs_mul_mat(ctx, src0, src1, dst): perm is looked up by src0->name (rrs.cu:266-270)."""
+    M, K = x.shape
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.float32, device=x.device)
+    src0, src1, dst = _views(w_tiles, x, out, N, name.encode())
+    wp, wb = (workspace.ptr, workspace.nbytes) if workspace is not None else (0, 0)
+    _check(LIB.tcq4_b200_ggml_mul_mat(C.byref(src0), C.byref(src1), C.byref(dst), wp, wb, _stream_ptr(stream)))
+    return out
+
+
+# ---- synthetic tiles for throughput runs (weights synthesised directly as tiles) -----
+def random_tiles(N: int, K: int, seed: int = 0, device="cuda") -> torch.Tensor:
+    """Uniform random nibbles, sc in [1,127], S in fp16 U(1e-3,1e-2), Z = zc = 0."""
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    nt = (N // TILE_CHANNELS) * (K // TILE_K)
+    t = torch.zeros((nt, TILE_BYTES), dtype=torch.uint8, device=device)
+    t[:, :1024] = torch.randint(0, 256, (nt, 1024), dtype=torch.uint8, device=device, generator=g)
+    S = (torch.rand((nt, 8), device=device, generator=g) * 9e-3 + 1e-3).to(torch.float16)
+    t[:, 1024:1040] = S.view(torch.uint8).reshape(nt, 16)
+    sc = torch.randint(1, 128, (nt, 64), dtype=torch.int16, device=device, generator=g).to(torch.uint8)
+    t[:, 1056:1120] = sc
+    return t.reshape(-1)
+
+
+# ---- N-sharded MUL_MAT across the GPUs of one box ------------------------------------------------
+class ShardedWeight:
+    """Rows [n0,n1) of an [N][K] TCQ4 tensor on this rank (a contiguous byte range, no repacking).
+
+    forward(): local MUL_MAT on the replicated activations, then an all-gather of the fp32 column
+    blocks over NCCL/NVLink on the compute stream.  The gather lands in [world][M][N/world] and one
+    strided copy puts it into ggml's dst layout C[m*N + n]; for M == 1 the shard is already contiguous.
+    """
+
+    def __init__(self, N: int, K: int, world: int, rank: int, tiles_full: torch.Tensor | None = None,
+                 tiles_local: torch.Tensor | None = None, align: int = 128):
+        self.N, self.K, self.world, self.rank = N, K, world, rank
+        self.n0, self.n1, off, ln = shard_range(N, K, world, rank, align)
+        self.ranges = [shard_range(N, K, world, r, align)[:2] for r in range(world)]
+        self.even = all((b - a) == (self.ranges[0][1] - self.ranges[0][0]) for a, b in self.ranges)
+        if tiles_local is not None:
+            self.tiles = tiles_local
+        else:
+            self.tiles = tiles_full[off:off + ln].contiguous()
+        assert self.tiles.numel() == ln
+
+    @property
+    def n_local(self) -> int:
+        return self.n1 - self.n0
+
+    def local(self, x: torch.Tensor, perm=None, out=None, workspace=None) -> torch.Tensor:
+        if self.n_local == 0:
+            return torch.empty((x.shape[0], 0), dtype=torch.float32, device=x.device)
+        return mul_mat(self.tiles, x, self.n_local, perm, out=out, workspace=workspace)
+
+    def gather(self, yl: torch.Tensor) -> torch.Tensor:
+        """All-gather the per-rank column blocks [M][n_local] into ggml's dst layout [M][N]."""
+        import torch.distributed as dist
+        M = yl.shape[0]
+        if self.world == 1:
+            return yl
+        if self.even:
+            gathered = torch.empty((self.world, M, self.n_local), dtype=yl.dtype, device=yl.device)
+            dist.all_gather_into_tensor(gathered, yl.contiguous())
+            if M == 1:
+                return gathered.reshape(1, self.N)
+            return gathered.permute(1, 0, 2).reshape(M, self.N)
+        parts = [torch.empty((M, b - a), dtype=yl.dtype, device=yl.device) for a, b in self.ranges]
+        dist.all_gather(parts, yl.contiguous())
+        return torch.cat(parts, dim=1)
+
+    def forward(self, x: torch.Tensor, perm=None, workspace=None) -> torch.Tensor:
+        return self.gather(self.local(x, perm, workspace=workspace))

@@ -1,0 +1,89 @@
+// tcq4_act.cu -- K1: Rotated-Runtime-Smooth activation stage (perm gather -> FWHT-256 -> 1/16 ->
+// per-block max-scale -> int4 codes + group sums) as a warp-shuffle butterfly over coalesced
+// 128-bit loads.  One warp owns one 256-block: 8 floats per lane (two LDG.128), FWHT stages
+// h=1,2,4 in registers and h=8..128 by __shfl_xor_sync; no shared memory, no block barrier.
+//
+// Replaces tcq4_rrs_fused_activation_tc_kernel (/root/reference/ggml/src/ggml-cuda/tcq4_k32.cu:181-277,
+// one 256-thread CTA + 1 KB smem + ~14 __syncthreads per block).
+//
+// Two output formats:
+//   MODE_REF   : block_rrs_int4_tc [M][KT] (160 B), byte-compatible with the reference
+//   MODE_STAGE : s8 codes in the UMMA K-major layout the tcgen05 GEMM bulk-copies (tcq4_common.cuh)
+#include "tcq4_common.cuh"
+#include "tcq4_kernels.h"
+
+namespace tcq4 {
+
+constexpr int ACT_WARPS_PER_CTA = 8;
+
+enum { MODE_REF = 0, MODE_STAGE = 1 };
+
+template <int MODE>
+__global__ void __launch_bounds__(ACT_WARPS_PER_CTA * 32)
+tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ perm, int M, int K,
+                      ActBlockTC *__restrict__ out_ref, ActStage st) {
+    const int lane = threadIdx.x & 31;
+    const int KT = K / TILE_K;
+    const long long nblocks = (long long)M * KT;
+    const long long warp0 = (long long)blockIdx.x * ACT_WARPS_PER_CTA + (threadIdx.x >> 5);
+    const long long nwarps = (long long)gridDim.x * ACT_WARPS_PER_CTA;
+
+    for (long long b = warp0; b < nblocks; b += nwarps) {
+        const int m = (int)(b / KT);
+        const int kt = (int)(b - (long long)m * KT);
+        float v[8];
+        rrs_load_block(x + (size_t)m * K, perm, kt, lane, v);
+        const ActQuant a = rrs_quantize_block(v, lane);
+
+        if (MODE == MODE_REF) {
+            // qs[t] = q[2t] | q[2t+1] << 4  (tcq4_k32.cu:266-270): lane l owns bytes l*4 .. l*4+3
+            ActBlockTC *blk = out_ref + b;
+            uint32_t w = 0;
+#pragma unroll
+            for (int r = 0; r < 8; r++) w |= (uint32_t)(a.q[r] & 0xF) << (4 * r);
+            reinterpret_cast<uint32_t *>(blk->qs)[lane] = w;
+            if (lane == 0) blk->smooth_scale = a.max_abs;
+            if ((lane & 3) == 0) blk->sum_q[lane >> 2] = (int16_t)a.gsum;
+            if (lane < 3) reinterpret_cast<uint32_t *>(blk->pad)[lane] = 0u;
+        } else {
+            // s8 codes, sigma order {0,1,4,5,2,3,6,7}; lane pair (2j, 2j+1) forms 16-B K-chunk j
+            const uint32_t w0 = (uint32_t)(a.q[0] & 0xFF) | ((uint32_t)(a.q[1] & 0xFF) << 8) |
+                                ((uint32_t)(a.q[4] & 0xFF) << 16) | ((uint32_t)(a.q[5] & 0xFF) << 24);
+            const uint32_t w1 = (uint32_t)(a.q[2] & 0xFF) | ((uint32_t)(a.q[3] & 0xFF) << 8) |
+                                ((uint32_t)(a.q[6] & 0xFF) << 16) | ((uint32_t)(a.q[7] & 0xFF) << 24);
+            const int mb = m >> 7, r = m & 127;
+            int8_t *unit = st.codes + ((size_t)mb * KT + kt) * ACT_UNIT_BYTES;
+            uint2 *dst = reinterpret_cast<uint2 *>(unit + (lane >> 1) * ACT_LBO + r * 16 + (lane & 1) * 8);
+            *dst = make_uint2(w0, w1);
+            if (lane == 0) st.a7[b] = __fdiv_rn(a.max_abs, 7.0f);
+            if ((lane & 3) == 0) st.sumq[b * 8 + (lane >> 2)] = (int16_t)a.gsum;
+        }
+    }
+}
+
+static int act_grid(int64_t nblocks, int num_sms) {
+    const int64_t ctas = (nblocks + ACT_WARPS_PER_CTA - 1) / ACT_WARPS_PER_CTA;
+    const int64_t cap = (int64_t)num_sms * 8;     // 8 CTAs x 8 warps = full occupancy, then grid-stride
+    return (int)(ctas < cap ? ctas : cap);
+}
+
+cudaError_t launch_act_quant_ref(const float *x, const int32_t *perm, int64_t M, int64_t K, void *out_blocks,
+                                 int num_sms, cudaStream_t stream) {
+    const int64_t nblocks = M * (K / TILE_K);
+    if (nblocks == 0) return cudaSuccess;
+    ActStage none{nullptr, nullptr, nullptr};
+    tcq4_act_quant_kernel<MODE_REF><<<act_grid(nblocks, num_sms), ACT_WARPS_PER_CTA * 32, 0, stream>>>(
+        x, perm, (int)M, (int)K, reinterpret_cast<ActBlockTC *>(out_blocks), none);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_act_quant_stage(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st,
+                                   int num_sms, cudaStream_t stream) {
+    const int64_t nblocks = M * (K / TILE_K);
+    if (nblocks == 0) return cudaSuccess;
+    tcq4_act_quant_kernel<MODE_STAGE><<<act_grid(nblocks, num_sms), ACT_WARPS_PER_CTA * 32, 0, stream>>>(
+        x, perm, (int)M, (int)K, nullptr, st);
+    return cudaGetLastError();
+}
+
+}  // namespace tcq4

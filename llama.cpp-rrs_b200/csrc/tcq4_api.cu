@@ -1,0 +1,390 @@
+// tcq4_api.cu -- C-ABI layer (include/tcq4_b200.h): dispatch, workspace carving, per-device scratch
+// arena.  Host-side equivalent of ggml_cuda_rrs_mul_mat's launch logic
+// (/root/reference/ggml/src/ggml-cuda/rrs.cu:241-344).  The channel-permutation registry and the
+// ggml operator mirror live in tcq4_registry.cu.
+//
+// Nothing here allocates or synchronises on the launch path except the explicit convenience
+// entries (tcq4_b200_mul_mat's arena growth outside capture, tcq4_b200_mul_mat_host).
+#include "../../include/tcq4_b200.h"
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+#include "tcq4_kernels.h"
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+void set_err(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char *what) {
+    set_err("%s: %s", what, cudaGetErrorString(e));
+    return TCQ4_ERR_CUDA;
+}
+
+constexpr int MAX_DEV = 16;
+struct DevInfo {
+    bool   ready = false;
+    bool   ok = false;          // sm_100 device with attributes set
+    int    cc = 0;
+    int    num_sms = 0;
+    size_t smem_optin = 0;
+    // arena
+    void  *arena = nullptr;
+    size_t arena_bytes = 0;
+    // host staging for tcq4_b200_mul_mat_host
+    float *hx = nullptr, *hy = nullptr;
+    size_t hx_bytes = 0, hy_bytes = 0;
+};
+DevInfo g_dev[MAX_DEV];
+std::mutex g_dev_mu;
+
+// Resolve (and lazily initialise) the current device.  Returns nullptr + status on failure.
+DevInfo *current_device(int *status) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= MAX_DEV) {
+        (void)cudaGetLastError();
+        set_err("no CUDA device available (%s): this library has no CPU fallback",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device index out of range");
+        *status = TCQ4_ERR_NO_DEVICE;
+        return nullptr;
+    }
+    DevInfo &d = g_dev[dev];
+    if (!d.ready) {
+        std::lock_guard<std::mutex> lk(g_dev_mu);
+        if (!d.ready) {
+            int major = 0, minor = 0, sms = 0, optin = 0;
+            cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+            cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev);
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+            d.cc = major * 10 + minor;
+            d.num_sms = sms;
+            d.smem_optin = (size_t)optin;
+            d.ok = false;
+            if (major == 10) {
+                cudaError_t e1 = tcq4::gemv_init_attributes(d.smem_optin);
+                cudaError_t e2 = tcq4::gemm_init_attributes(d.smem_optin);
+                d.ok = (e1 == cudaSuccess && e2 == cudaSuccess);
+                if (!d.ok) set_err("kernel attribute setup failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+            } else {
+                set_err("device %d is sm_%d, this library is sm_100a only and has no fallback", dev, d.cc);
+            }
+            d.ready = true;
+        }
+    }
+    if (!d.ok) {
+        *status = (d.cc / 10 == 10) ? TCQ4_ERR_CUDA : TCQ4_ERR_NO_DEVICE;
+        return nullptr;
+    }
+    *status = TCQ4_OK;
+    return &d;
+}
+
+bool shape_ok(int64_t M, int64_t N, int64_t K) {
+    return M >= 1 && N >= 8 && K >= 256 && (K % TCQ4_B200_TILE_K) == 0 && (N % TCQ4_B200_TILE_CHANNELS) == 0 &&
+           M <= (1 << 24) && N <= (1 << 28) && K <= (1 << 24);
+}
+
+// Workspace layout (all sub-buffers 256-byte aligned):
+//   [0, tickets)           int[NT]         split-K tickets of the GEMV (must be zero between launches)
+//   [tickets, +partials)   float[...]      GEMV split-K partial sums
+//   [.., +codes/a7/sumq)   GEMM activation staging
+struct WsLayout {
+    size_t ticket_off = 0, ticket_bytes = 0;
+    size_t partial_off = 0, partial_bytes = 0;
+    size_t codes_off = 0, a7_off = 0, sumq_off = 0;
+    size_t total = 0;
+};
+
+// worst-case sizes that do not depend on the device, so tcq4_b200_workspace_size is callable anywhere
+WsLayout ws_layout(int64_t M, int64_t N, int64_t K) {
+    WsLayout L;
+    const int64_t NT = N / 8, KT = K / 256;
+    L.ticket_off = 0;
+    L.ticket_bytes = (size_t)tcq4::round_up(NT * 4, 256);
+    L.partial_off = L.ticket_off + L.ticket_bytes;
+    const int64_t Mg = M < tcq4::GEMV_MAX_M ? M : tcq4::GEMV_MAX_M;
+    // GEMV split-K: a row of KT tiles is cut into at most KT pieces whatever the grid is
+    const int64_t maxslots = KT;
+    L.partial_bytes = (size_t)tcq4::round_up(NT * maxslots * Mg * 8 * 4, 256);
+    L.codes_off = L.partial_off + L.partial_bytes;
+    const int64_t MB = (M + 127) / 128;
+    const size_t codes = (size_t)tcq4::round_up(MB * KT * (int64_t)tcq4::ACT_UNIT_BYTES, 256);
+    L.a7_off = L.codes_off + codes;
+    L.sumq_off = L.a7_off + (size_t)tcq4::round_up(M * KT * 4, 256);
+    L.total = L.sumq_off + (size_t)tcq4::round_up(M * KT * 16, 256);
+    return L;
+}
+
+int select_kernel(const DevInfo *d, int64_t M, int64_t N, int64_t K, tcq4::GemvPlan *gv) {
+    const int sms = d ? d->num_sms : 148;
+    const size_t optin = d ? d->smem_optin : (size_t)232448;
+    tcq4::GemvPlan tmp;
+    if (tcq4::gemv_plan(M, N, K, sms, optin, gv ? gv : &tmp)) return TCQ4_KERNEL_GEMV;
+    return TCQ4_KERNEL_GEMM;
+}
+
+int run_mul_mat(const void *w, const float *x, float *y, int64_t M, int64_t N, int64_t K, const int32_t *perm,
+                void *ws, size_t ws_bytes, int kernel, int32_t *dbg_isum, cudaStream_t stream) {
+    if (!shape_ok(M, N, K)) {
+        set_err("unsupported shape M=%lld N=%lld K=%lld (need K%%256==0, N%%8==0)", (long long)M, (long long)N,
+                (long long)K);
+        return TCQ4_ERR_SHAPE;
+    }
+    if (!w || !x || !y || ((uintptr_t)w & 15) || ((uintptr_t)x & 15) || ((uintptr_t)y & 15) ||
+        (perm && ((uintptr_t)perm & 15))) {
+        set_err("null or misaligned pointer (w/x/y/perm must be 16-byte aligned device pointers)");
+        return TCQ4_ERR_ARG;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    const WsLayout L = ws_layout(M, N, K);
+    if (!ws || ((uintptr_t)ws & 255) || ws_bytes < L.total) {
+        set_err("workspace too small or misaligned: need %zu bytes (256-aligned), got %zu", L.total, ws_bytes);
+        return TCQ4_ERR_WORKSPACE;
+    }
+    uint8_t *wsb = reinterpret_cast<uint8_t *>(ws);
+
+    tcq4::GemvPlan gv;
+    int k = kernel;
+    if (k == TCQ4_KERNEL_AUTO) k = select_kernel(d, M, N, K, &gv);
+    if (k == TCQ4_KERNEL_GEMV) {
+        if (!tcq4::gemv_plan(M, N, K, d->num_sms, d->smem_optin, &gv)) {
+            set_err("GEMV kernel does not take M=%lld K=%lld (M<=%d and M*K codes must fit shared memory)",
+                    (long long)M, (long long)K, tcq4::GEMV_MAX_M);
+            return TCQ4_ERR_SHAPE;
+        }
+        if (gv.partial_bytes > L.partial_bytes) {
+            set_err("internal: GEMV partial buffer bound too small");
+            return TCQ4_ERR_WORKSPACE;
+        }
+        cudaError_t e = tcq4::launch_gemv(w, x, perm, y, M, N, K, gv, reinterpret_cast<float *>(wsb + L.partial_off),
+                                          reinterpret_cast<int *>(wsb + L.ticket_off), dbg_isum, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "gemv launch");
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        return TCQ4_OK;
+    }
+    if (k != TCQ4_KERNEL_GEMM) {
+        set_err("unknown kernel selector %d", kernel);
+        return TCQ4_ERR_ARG;
+    }
+    tcq4::GemmPlan gm;
+    if (!tcq4::gemm_plan(M, N, K, d->num_sms, d->smem_optin, &gm)) {
+        set_err("GEMM kernel cannot be planned for this shape/device");
+        return TCQ4_ERR_SHAPE;
+    }
+    tcq4::ActStage st;
+    st.codes = reinterpret_cast<int8_t *>(wsb + L.codes_off);
+    st.a7 = reinterpret_cast<float *>(wsb + L.a7_off);
+    st.sumq = reinterpret_cast<int16_t *>(wsb + L.sumq_off);
+    cudaError_t e = tcq4::launch_act_quant_stage(x, perm, M, K, st, d->num_sms, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
+    e = tcq4::launch_gemm(w, st, y, M, N, K, gm, dbg_isum, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "gemm launch");
+    g_launches.fetch_add(2, std::memory_order_relaxed);
+    return TCQ4_OK;
+}
+
+}  // namespace
+
+// =================================================================================================
+// exported C ABI
+// =================================================================================================
+extern "C" {
+
+const char *tcq4_b200_version(void) { return "tcq4-b200 0.1 (sm_100a)"; }
+const char *tcq4_b200_last_error(void) { return g_err; }
+uint64_t tcq4_b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int tcq4_b200_supports(int64_t M, int64_t N, int64_t K, int cc) {
+    return (cc >= 100 && cc < 110 && shape_ok(M, N, K)) ? 1 : 0;
+}
+
+int tcq4_b200_select_kernel(int64_t M, int64_t N, int64_t K) {
+    if (!shape_ok(M, N, K)) return TCQ4_KERNEL_AUTO;
+    int dev = -1;
+    const DevInfo *d = nullptr;
+    if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < MAX_DEV && g_dev[dev].ready && g_dev[dev].ok)
+        d = &g_dev[dev];
+    else
+        (void)cudaGetLastError();
+    return select_kernel(d, M, N, K, nullptr);
+}
+
+size_t tcq4_b200_workspace_size(int64_t M, int64_t N, int64_t K) {
+    if (!shape_ok(M, N, K)) return 0;
+    return ws_layout(M, N, K).total;
+}
+
+int tcq4_b200_workspace_init(void *workspace, size_t workspace_bytes, cudaStream_t stream) {
+    if (!workspace || ((uintptr_t)workspace & 255)) {
+        set_err("workspace must be a 256-byte aligned device pointer");
+        return TCQ4_ERR_ARG;
+    }
+    int status;
+    if (!current_device(&status)) return status;
+    // only the ticket region has to be zero, but its size depends on N: clear everything once
+    cudaError_t e = cudaMemsetAsync(workspace, 0, workspace_bytes, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "workspace memset");
+    return TCQ4_OK;
+}
+
+int tcq4_b200_mul_mat_ws(const void *w_tiles, const float *x, float *y, int64_t M, int64_t N, int64_t K,
+                         const int32_t *d_perm, void *workspace, size_t workspace_bytes, int kernel,
+                         cudaStream_t stream) {
+    return run_mul_mat(w_tiles, x, y, M, N, K, d_perm, workspace, workspace_bytes, kernel, nullptr, stream);
+}
+
+int tcq4_b200_mul_mat_debug(const void *w_tiles, const float *x, float *y, int64_t M, int64_t N, int64_t K,
+                            const int32_t *d_perm, void *workspace, size_t workspace_bytes, int kernel,
+                            int32_t *isum, cudaStream_t stream) {
+    return run_mul_mat(w_tiles, x, y, M, N, K, d_perm, workspace, workspace_bytes, kernel, isum, stream);
+}
+
+// grow the per-device arena (never while the stream is capturing)
+static int arena_ensure(DevInfo *d, size_t need, cudaStream_t stream) {
+    if (d->arena_bytes >= need) return TCQ4_OK;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (stream != nullptr && cudaStreamIsCapturing(stream, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone) {
+        set_err("scratch arena too small (%zu < %zu) and the stream is capturing: call tcq4_b200_reserve first",
+                d->arena_bytes, need);
+        return TCQ4_ERR_WORKSPACE;
+    }
+    std::lock_guard<std::mutex> lk(g_dev_mu);
+    if (d->arena_bytes >= need) return TCQ4_OK;
+    cudaError_t e = cudaDeviceSynchronize();          // old arena may still be in use
+    if (e != cudaSuccess) return cuda_fail(e, "arena sync");
+    if (d->arena) cudaFree(d->arena);
+    d->arena = nullptr;
+    d->arena_bytes = 0;
+    const size_t bytes = (size_t)tcq4::round_up((int64_t)need, 1 << 20);
+    e = cudaMalloc(&d->arena, bytes);
+    if (e != cudaSuccess) return cuda_fail(e, "arena cudaMalloc");
+    e = cudaMemset(d->arena, 0, bytes);
+    if (e != cudaSuccess) return cuda_fail(e, "arena memset");
+    d->arena_bytes = bytes;
+    return TCQ4_OK;
+}
+
+int tcq4_b200_reserve(int64_t max_M, int64_t max_N, int64_t max_K) {
+    if (!shape_ok(max_M, max_N, max_K)) {
+        set_err("reserve: unsupported shape");
+        return TCQ4_ERR_SHAPE;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    size_t need = ws_layout(max_M, max_N, max_K).total;
+    // the GEMV partial region scales with min(M,4): make sure small-M calls of the same N,K fit too
+    const size_t need4 = ws_layout(max_M < 4 ? max_M : 4, max_N, max_K).total;
+    if (need4 > need) need = need4;
+    return arena_ensure(d, need, nullptr);
+}
+
+int tcq4_b200_mul_mat(const void *w_tiles, const float *x, float *y, int64_t M, int64_t N, int64_t K,
+                      const int32_t *d_perm, cudaStream_t stream) {
+    if (!shape_ok(M, N, K)) {
+        set_err("unsupported shape M=%lld N=%lld K=%lld", (long long)M, (long long)N, (long long)K);
+        return TCQ4_ERR_SHAPE;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    const size_t need = ws_layout(M, N, K).total;
+    status = arena_ensure(d, need, stream);
+    if (status != TCQ4_OK) return status;
+    return run_mul_mat(w_tiles, x, y, M, N, K, d_perm, d->arena, d->arena_bytes, TCQ4_KERNEL_AUTO, nullptr, stream);
+}
+
+int tcq4_b200_mul_mat_host(const void *w_tiles_dev, const float *x_host, float *y_host, int64_t M, int64_t N,
+                           int64_t K, const int32_t *d_perm, cudaStream_t stream) {
+    if (!shape_ok(M, N, K) || !x_host || !y_host) {
+        set_err("mul_mat_host: bad shape or null host pointer");
+        return TCQ4_ERR_SHAPE;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    const size_t xb = (size_t)M * K * 4, yb = (size_t)M * N * 4;
+    if (d->hx_bytes < xb) {
+        cudaDeviceSynchronize();
+        if (d->hx) cudaFree(d->hx);
+        d->hx = nullptr; d->hx_bytes = 0;
+        cudaError_t e = cudaMalloc(&d->hx, xb);
+        if (e != cudaSuccess) return cuda_fail(e, "x staging cudaMalloc");
+        d->hx_bytes = xb;
+    }
+    if (d->hy_bytes < yb) {
+        cudaDeviceSynchronize();
+        if (d->hy) cudaFree(d->hy);
+        d->hy = nullptr; d->hy_bytes = 0;
+        cudaError_t e = cudaMalloc(&d->hy, yb);
+        if (e != cudaSuccess) return cuda_fail(e, "y staging cudaMalloc");
+        d->hy_bytes = yb;
+    }
+    cudaError_t e = cudaMemcpyAsync(d->hx, x_host, xb, cudaMemcpyHostToDevice, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "H2D copy");
+    status = tcq4_b200_mul_mat(w_tiles_dev, d->hx, d->hy, M, N, K, d_perm, stream);
+    if (status != TCQ4_OK) return status;
+    e = cudaMemcpyAsync(y_host, d->hy, yb, cudaMemcpyDeviceToHost, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "D2H copy");
+    e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) return cuda_fail(e, "stream sync");
+    return TCQ4_OK;
+}
+
+int tcq4_b200_fwht_quantize_tc(const float *x, void *y_blocks, const int32_t *d_perm, int64_t K, int64_t M,
+                               cudaStream_t stream) {
+    if (M < 1 || K < 256 || (K % 256) != 0) {
+        set_err("fwht_quantize_tc: need M>=1 and K%%256==0");
+        return TCQ4_ERR_SHAPE;
+    }
+    if (!x || !y_blocks || ((uintptr_t)x & 15) || ((uintptr_t)y_blocks & 15) || (d_perm && ((uintptr_t)d_perm & 15))) {
+        set_err("fwht_quantize_tc: null or misaligned pointer");
+        return TCQ4_ERR_ARG;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    cudaError_t e = tcq4::launch_act_quant_ref(x, d_perm, M, K, y_blocks, d->num_sms, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return TCQ4_OK;
+}
+
+int tcq4_b200_shard_range(int64_t N, int64_t K, int world, int rank, int64_t align, int64_t *n0, int64_t *n1,
+                          size_t *byte_offset, size_t *byte_len) {
+    if (world < 1 || rank < 0 || rank >= world || align < 8 || (align % 8) != 0 || N < 8 || (N % 8) != 0 ||
+        K < 256 || (K % 256) != 0) {
+        set_err("shard_range: bad arguments");
+        return TCQ4_ERR_ARG;
+    }
+    const int64_t units = (N + align - 1) / align;          // last unit may be short
+    const int64_t base = units / world, rem = units % world;
+    const int64_t u0 = rank * base + (rank < rem ? rank : rem);
+    const int64_t u1 = u0 + base + (rank < rem ? 1 : 0);
+    int64_t a = u0 * align, b = u1 * align;
+    if (a > N) a = N;
+    if (b > N) b = N;
+    if (n0) *n0 = a;
+    if (n1) *n1 = b;
+    const size_t row_bytes = (size_t)(K / 256) * 148;       // ggml_row_size (ggml.c:750-757)
+    if (byte_offset) *byte_offset = (size_t)a * row_bytes;
+    if (byte_len) *byte_len = (size_t)(b - a) * row_bytes;
+    return TCQ4_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,46 @@
+// tcq4_kernels.h -- internal launch interface between the C-ABI layer (tcq4_api.cu) and the kernels.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "tcq4_common.cuh"
+
+namespace tcq4 {
+
+// ---- K1: activation stage (tcq4_act.cu) -------------------------------------------------------
+cudaError_t launch_act_quant_ref(const float *x, const int32_t *perm, int64_t M, int64_t K, void *out_blocks,
+                                 int num_sms, cudaStream_t stream);
+cudaError_t launch_act_quant_stage(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st,
+                                   int num_sms, cudaStream_t stream);
+
+// ---- K3: fused decode GEMV (tcq4_gemv.cu) -----------------------------------------------------
+constexpr int GEMV_MAX_M = 4;
+struct GemvPlan {
+    int     grid;            // CTAs (persistent, one per SM)
+    size_t  smem_bytes;
+    int     maxslots;        // split-K partial slots per n-tile row
+    size_t  partial_bytes;   // workspace: float [NT][maxslots][M][8]
+    size_t  ticket_bytes;    // workspace: int   [NT]
+};
+bool        gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, GemvPlan *plan);
+cudaError_t gemv_init_attributes(size_t smem_optin);
+cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm, float *y, int64_t M, int64_t N,
+                        int64_t K, const GemvPlan &plan, float *ws_partial, int *ws_ticket, int32_t *dbg_isum,
+                        cudaStream_t stream);
+
+// ---- K2: tcgen05 prefill GEMM (tcq4_gemm.cu) --------------------------------------------------
+struct GemmPlan {
+    dim3    grid;
+    size_t  smem_bytes;
+    size_t  stage_codes_bytes;   // workspace: ActStage.codes
+    size_t  stage_a7_bytes;
+    size_t  stage_sumq_bytes;
+};
+bool        gemm_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, GemmPlan *plan);
+cudaError_t gemm_init_attributes(size_t smem_optin);
+cudaError_t launch_gemm(const void *w_tiles, ActStage st, float *y, int64_t M, int64_t N, int64_t K,
+                        const GemmPlan &plan, int32_t *dbg_isum, cudaStream_t stream);
+
+}  // namespace tcq4

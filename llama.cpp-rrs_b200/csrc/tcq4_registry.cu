@@ -1,0 +1,134 @@
+// tcq4_registry.cu -- channel-permutation registry and the host-side mirror of the ggml operator
+// entry, i.e. the rest of the fork's plug-in surface for GGML_TYPE_TCQ4_K32:
+//   ggml_cuda_rrs_register_perm / get_perm / has_perm / clear_perms / set/get_reorder_enabled
+//       /root/reference/ggml/src/ggml-cuda/rrs.cu:82-127
+//   ggml_backend_cuda_tcq4_* wrappers resolved by name from libllama
+//       /root/reference/ggml/src/ggml-cuda/ggml-cuda.cu:4148-4158, 4876-4885
+//   ggml_cuda_rrs_mul_mat shape extraction and asserts
+//       /root/reference/ggml/src/ggml-cuda/rrs.cu:241-270
+//
+// Differences from the reference, on purpose: the registry is keyed by (device, name)
+// and mutex-guarded, CUDA errors are checked, and lookups on the launch path take a shared lock and
+// do not allocate (the reference builds a std::string and hashes it per call, rrs.cu:104-106).
+#include "../../include/tcq4_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <shared_mutex>
+#include <string>
+#include <utility>
+
+namespace {
+
+struct PermEntry {
+    int32_t *d_perm = nullptr;
+    int      K = 0;
+};
+struct KeyLess {
+    using is_transparent = void;
+    using Key = std::pair<int, std::string>;
+    using View = std::pair<int, const char *>;
+    bool operator()(const Key &a, const Key &b) const { return a < b; }
+    bool operator()(const Key &a, const View &b) const {
+        return a.first != b.first ? a.first < b.first : std::strcmp(a.second.c_str(), b.second) < 0;
+    }
+    bool operator()(const View &a, const Key &b) const {
+        return a.first != b.first ? a.first < b.first : std::strcmp(a.second, b.second.c_str()) < 0;
+    }
+};
+std::map<std::pair<int, std::string>, PermEntry, KeyLess> g_perms;
+std::shared_mutex g_perm_mu;
+std::atomic<bool> g_reorder_enabled{true};      // rrs.cu:83
+
+int current_dev() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return -1;
+    }
+    return dev;
+}
+
+bool is_contiguous_2d(const tcq4_tensor_view *t, size_t elem_row_bytes) {
+    return t->nb[1] == elem_row_bytes && t->ne[2] == 1 && t->ne[3] == 1;
+}
+
+}  // namespace
+
+extern "C" {
+
+void ggml_backend_cuda_tcq4_register_perm(const char *tensor_name, const int32_t *h_perm, int K) {
+    if (!tensor_name || !h_perm || K <= 0) return;
+    const int dev = current_dev();
+    if (dev < 0) return;                                   // no device: nothing to register on
+    int32_t *d_perm = nullptr;
+    if (cudaMalloc(&d_perm, (size_t)K * sizeof(int32_t)) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return;
+    }
+    if (cudaMemcpy(d_perm, h_perm, (size_t)K * sizeof(int32_t), cudaMemcpyHostToDevice) != cudaSuccess) {
+        (void)cudaGetLastError();
+        cudaFree(d_perm);
+        return;
+    }
+    std::unique_lock<std::shared_mutex> lk(g_perm_mu);
+    PermEntry &e = g_perms[std::make_pair(dev, std::string(tensor_name))];
+    if (e.d_perm) cudaFree(e.d_perm);                      // rrs.cu:88-90: replace an existing entry
+    e.d_perm = d_perm;
+    e.K = K;
+}
+
+void ggml_backend_cuda_tcq4_clear_perms(void) {
+    std::unique_lock<std::shared_mutex> lk(g_perm_mu);
+    for (auto &kv : g_perms)
+        if (kv.second.d_perm) cudaFree(kv.second.d_perm);
+    g_perms.clear();
+}
+
+void ggml_backend_cuda_tcq4_set_reorder_enabled(bool enabled) { g_reorder_enabled.store(enabled); }
+int tcq4_b200_get_reorder_enabled(void) { return g_reorder_enabled.load() ? 1 : 0; }
+
+const int32_t *tcq4_b200_get_perm(const char *tensor_name) {
+    if (!tensor_name || tensor_name[0] == '\0' || !g_reorder_enabled.load()) return nullptr;   // rrs.cu:102,268
+    const int dev = current_dev();
+    if (dev < 0) return nullptr;
+    std::shared_lock<std::shared_mutex> lk(g_perm_mu);
+    auto it = g_perms.find(std::make_pair(dev, tensor_name));
+    return it == g_perms.end() ? nullptr : it->second.d_perm;
+}
+
+int tcq4_b200_has_perm(const char *tensor_name) { return tcq4_b200_get_perm(tensor_name) != nullptr ? 1 : 0; }
+
+int tcq4_b200_ggml_supports_op(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1, const tcq4_tensor_view *dst,
+                               int cc) {
+    if (!src0 || !src1 || !dst) return 0;
+    if (src0->type != TCQ4_B200_GGML_TYPE || src1->type != 0 || dst->type != 0) return 0;
+    if (src0->ne[0] != src1->ne[0]) return 0;                                   // rrs.cu:256
+    if (dst->ne[0] != src0->ne[1] || dst->ne[1] != src1->ne[1]) return 0;
+    return tcq4_b200_supports(src1->ne[1], src0->ne[1], src0->ne[0], cc);
+}
+
+int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1, tcq4_tensor_view *dst,
+                           void *workspace, size_t workspace_bytes, cudaStream_t stream) {
+    if (!src0 || !src1 || !dst) return TCQ4_ERR_ARG;
+    const int64_t K = src0->ne[0], N = src0->ne[1];          // rrs.cu:247-254
+    const int64_t M = src1->ne[1];
+    if (src0->type != TCQ4_B200_GGML_TYPE || src1->type != 0 || dst->type != 0) return TCQ4_ERR_ARG;
+    if (src0->ne[0] != src1->ne[0]) return TCQ4_ERR_SHAPE;   // GGML_ASSERT(ne00 == ne10)
+    if (dst->ne[0] != N || dst->ne[1] != M) return TCQ4_ERR_SHAPE;
+    // the reference silently ignores ne[2], ne[3] and strides (rrs.cu:247-254); assert instead
+    if (src0->ne[2] != 1 || src0->ne[3] != 1) return TCQ4_ERR_SHAPE;
+    if (!is_contiguous_2d(src1, (size_t)K * 4) || !is_contiguous_2d(dst, (size_t)N * 4)) return TCQ4_ERR_SHAPE;
+    if (src0->nb[1] != (size_t)(K / 256) * 148) return TCQ4_ERR_SHAPE;          // ggml_row_size, ggml.c:750-757
+    const int32_t *d_perm = src0->name ? tcq4_b200_get_perm(src0->name) : nullptr;   // rrs.cu:266-270
+    if (workspace)
+        return tcq4_b200_mul_mat_ws(src0->data, (const float *)src1->data, (float *)dst->data, M, N, K, d_perm,
+                                    workspace, workspace_bytes, TCQ4_KERNEL_AUTO, stream);
+    return tcq4_b200_mul_mat(src0->data, (const float *)src1->data, (float *)dst->data, M, N, K, d_perm, stream);
+}
+
+}  // extern "C"

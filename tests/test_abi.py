@@ -1,0 +1,97 @@
+"""The C-ABI library: loads, exports every symbol include/tcq4_b200.h declares, host logic works and
+compute entry points fail LOUDLY without a GPU (no CPU fallback).  No compute calls here."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    src = open(os.path.join(ROOT, "include", "tcq4_b200.h")).read()
+    return sorted(set(re.findall(r"^TCQ4_B200_API[^;(]*?\b(\w+)\s*\(", src, flags=re.M)))
+
+
+def test_exports_match_header(t4):
+    syms = _declared_symbols()
+    assert len(syms) >= 20
+    assert sorted(t4.EXPORTS) == syms
+    lib = C.CDLL(t4.LIB_PATH)
+    for s in syms:
+        assert hasattr(lib, s), s
+
+
+def test_supports_and_select(t4):
+    assert t4.supports(1, 9728, 2560) and t4.supports(512, 9728, 2560)
+    assert not t4.supports(1, 9728, 2500)           # K % 256 (rrs.cu:258)
+    assert not t4.supports(1, 9732, 2560)           # N % 8   (rrs.cu:259)
+    assert not t4.supports(1, 9728, 2560, cc=86)    # sm_100a only
+    assert not t4.supports(0, 8, 256)
+    assert t4.select_kernel(1, 9728, 2560) == t4.KERNEL_GEMV
+    assert t4.select_kernel(4, 2560, 9728) == t4.KERNEL_GEMV
+    assert t4.select_kernel(5, 9728, 2560) == t4.KERNEL_GEMM
+    assert t4.select_kernel(512, 9728, 2560) == t4.KERNEL_GEMM
+    assert t4.select_kernel(4, 1024, 65536) == t4.KERNEL_GEMM      # codes do not fit shared memory
+
+
+def test_ggml_supports_op(t4):
+    assert t4.ggml_supports_op(2560, 9728, 512)
+    assert not t4.ggml_supports_op(2560 + 32, 9728, 512)
+
+
+def test_workspace_size_monotone(t4):
+    a = t4.workspace_size(1, 9728, 2560)
+    b = t4.workspace_size(512, 9728, 2560)
+    assert 0 < a < b and b % 256 == 0
+    assert t4.workspace_size(1, 9728, 2500) == 0
+    assert t4.tile_bytes(9728, 2560) == 14397440
+
+
+def test_shard_range_covers_and_aligns(t4):
+    for N, K, world in [(9728, 2560, 8), (25600, 5120, 4), (28672, 8192, 8), (1024, 2560, 8), (8, 256, 2)]:
+        prev = 0
+        total = 0
+        for r in range(world):
+            n0, n1, off, ln = t4.shard_range(N, K, world, r, 128)
+            assert n0 == prev and n0 % 8 == 0 and (n1 % 128 == 0 or n1 == N)
+            assert off == n0 * (K // 256) * 148 and ln == (n1 - n0) * (K // 256) * 148
+            prev = n1
+            total += ln
+        assert prev == N and total == t4.tile_bytes(N, K)
+    with pytest.raises(t4.Tcq4Error):
+        t4.shard_range(9728, 2560, 0, 0)
+
+
+def test_registry_without_device_is_safe(t4):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the gpu tests")
+    t4.register_perm("blk.0.attn_q.weight", list(range(256)))
+    assert not t4.has_perm("blk.0.attn_q.weight")
+    t4.clear_perms()
+
+
+def test_no_cpu_fallback(t4):
+    """Without an sm_100 device compute calls return TCQ4_ERR_NO_DEVICE; nothing is computed on the CPU."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    buf = (C.c_char * 4096)()
+    addr = (C.addressof(buf) + 255) & ~255
+    st = t4.LIB.tcq4_b200_mul_mat_ws(addr, addr, addr, 1, 8, 256, None, addr, 1 << 20, 0, None)
+    assert st == 5, t4.LIB.tcq4_b200_last_error()
+    assert b"no CPU fallback" in t4.LIB.tcq4_b200_last_error() or b"no fallback" in t4.LIB.tcq4_b200_last_error()
+    st = t4.LIB.tcq4_b200_fwht_quantize_tc(addr, addr, None, 256, 1, None)
+    assert st == 5
+
+
+def test_product_never_imports_oracle():
+    """The product path must not route through the oracle (oracle/tcq4_oracle.h rules)."""
+    pkg = os.path.join(ROOT, "llama.cpp-rrs_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                txt = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "pyoracle" not in txt and "liboracle" not in txt and "tcq4_oracle" not in txt, f
