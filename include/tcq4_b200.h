@@ -156,6 +156,13 @@ TCQ4_B200_API int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq
                                          tcq4_tensor_view *dst, void *workspace, size_t workspace_bytes,
                                          cudaStream_t stream);
 
+/* Tensor-pipe peak of this device for one tcgen05.mma flavour: a bare single-thread issue loop on
+ * every SM (kind: 0 = i8, 1 = bf16 (kind::f16), 2 = e4m3 (kind::f8f6f4); M = 128; N in {64..256};
+ * swizzle: 0 = none (the GEMM's operand layout), 1 = 128B).  MEASURED_PEAKS.json has no INT8 figure,
+ * so this is the measured denominator for the GEMM's tensor roofline.  Synchronous. */
+TCQ4_B200_API int tcq4_b200_measure_umma(int kind, int N, int swizzle, int iters, double *tops_out,
+                                         double *cycles_per_mma_out);
+
 /* Launch statistics since load (kernels launched by this library), for bench.py's gpu_launches. */
 TCQ4_B200_API uint64_t tcq4_b200_launch_count(void);
 

@@ -39,7 +39,7 @@ EXPORTS = [
     "ggml_backend_cuda_tcq4_register_perm", "ggml_backend_cuda_tcq4_clear_perms",
     "ggml_backend_cuda_tcq4_set_reorder_enabled", "tcq4_b200_get_perm", "tcq4_b200_has_perm",
     "tcq4_b200_get_reorder_enabled", "tcq4_b200_shard_range", "tcq4_b200_ggml_supports_op",
-    "tcq4_b200_ggml_mul_mat", "tcq4_b200_launch_count",
+    "tcq4_b200_ggml_mul_mat", "tcq4_b200_launch_count", "tcq4_b200_measure_umma",
 ]
 
 
@@ -88,6 +88,7 @@ def _load() -> C.CDLL:
     lib.tcq4_b200_ggml_supports_op.argtypes = [C.POINTER(TensorView)] * 3 + [ci]
     lib.tcq4_b200_ggml_mul_mat.argtypes = [C.POINTER(TensorView)] * 3 + [vp, sz, vp]
     lib.tcq4_b200_launch_count.restype = C.c_uint64
+    lib.tcq4_b200_measure_umma.argtypes = [ci, ci, ci, ci, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     return lib
 
 
@@ -105,6 +106,13 @@ def version() -> str:
 
 def launch_count() -> int:
     return int(LIB.tcq4_b200_launch_count())
+
+
+def measure_umma(kind: int, N: int = 256, swizzle: int = 0, iters: int = 2000):
+    """(TOPS, cycles per MMA) of a bare tcgen05.mma loop: kind 0 = i8, 1 = bf16, 2 = fp8."""
+    tops, cyc = C.c_double(), C.c_double()
+    _check(LIB.tcq4_b200_measure_umma(kind, N, swizzle, iters, C.byref(tops), C.byref(cyc)))
+    return tops.value, cyc.value
 
 
 def supports(M: int, N: int, K: int, cc: int = 100) -> bool:

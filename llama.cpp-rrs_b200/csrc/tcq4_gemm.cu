@@ -8,24 +8,25 @@
 // Exact integer formulation.  kind::i8 has K = 32 per instruction = one scale group, and
 // the weight scale S*sc[n][g]/127 changes every group.  Instead of draining TMEM every 32-deep step,
 // the int8 scale code is folded into the weight: p = sc*q in [-1016, 1016] is split exactly as
-// p = 16*hi + lo, hi in [-64, 63] (s8), lo in [0, 15]; two MMAs per group accumulate
-//     D_hi += A * hi            (s8 x s8)
-//     D_lo += A * (16*lo)       (s8 x u8)
-// over the whole 256-block, so  256*D_hi + D_lo = 16 * sum_g sc_g * dot_g  exactly in int32, and the
-// fp32 epilogue runs once per 256-block with  a7[m][kt] * S[n][kt] / 127.
+// p = 16*hi + lo, hi in [-64, 63], lo in [0, 15] (both s8).  The B operand of ONE MMA per group is
+// 256 rows: 128 channels' hi bytes followed by the same channels' lo bytes (a tcgen05.mma takes
+// ~128 cycles whatever N <= 256 is -- measured, tests/gpu_umma_peak.py -- so N = 256 is the only
+// full-rate shape for cta_group::1).  TMEM columns [0,128) accumulate D_hi = A*hi and [128,256)
+// D_lo = A*lo over the whole 256-block, so  16*D_hi + D_lo = sum_g sc_g * dot_g  exactly in int32,
+// and the fp32 epilogue runs once per 256-block with  a7[m][kt] * S[n][kt] / 127.
 //
 // Weight unpack (CUDA cores, per 8-nibble word): nibble pairs are pulled into 16-bit fields,
 // biased to unsigned (u = q + 8), and ONE integer multiply-add per pair forms
 //     field = 16*sc*u + (32768 - 128*sc) = 16*p + 32768
-// whose byte 0 is 16*lo and byte 1 is hi + 128; two PRMTs gather the hi bytes and two the lo bytes
-// (plus one XOR to remove the +128).  The resulting K byte order inside an 8-slice is
+// whose byte 0 is 16*lo and byte 1 is hi + 128; two PRMTs gather the hi bytes (one XOR removes the
+// +128) and two the lo bytes (one shift removes the x16).  The resulting K byte order inside an 8-slice is
 // {0,1,4,5,2,3,6,7}; the activation kernel writes its s8 codes in the same order.
 //
-// CTA = 128 tokens x 128 channels, 14 warps:
-//   warp 0      bulk-copy producer: per k-tile one 32 KB activation unit + 16 raw 1184-B weight tiles
-//   warp 1      TMEM allocator + single-thread MMA issuer
-//   warps 2-5   weight unpack (raw tiles -> K-major no-swizzle UMMA operand, hi and lo)
-//   warps 6-13  epilogue: tcgen05.ld, combine hi/lo, scale, fp32 accumulate in registers, store
+// CTA = 128 tokens x 128 channels, 18 warps:
+//   warp 0       bulk-copy producer: per k-tile one 32 KB activation unit + 16 raw 1184-B weight tiles
+//   warp 1       TMEM allocator + single-thread MMA issuer (8 MMAs 128x256x32 per k-tile)
+//   warps 2-9    weight unpack (raw tiles -> K-major no-swizzle UMMA operand, hi rows then lo rows)
+//   warps 10-17  epilogue: tcgen05.ld, combine hi/lo, scale, fp32 accumulate in registers, store
 // TMEM: 2 accumulator stages x (128 hi + 128 lo) columns, so MMA(kt+1) overlaps epilogue(kt).
 #include "tcq4_common.cuh"
 #include "tcq4_kernels.h"
@@ -35,13 +36,16 @@ namespace tcq4 {
 constexpr int GM_BM = 128;                  // tokens per CTA
 constexpr int GM_BN = 128;                  // channels per CTA
 constexpr int GM_NTL = GM_BN / TILE_CH;     // 16 n-tiles per CTA
-constexpr int GM_THREADS = 14 * 32;
-constexpr int GM_UNPACK_WARP0 = 2, GM_UNPACK_WARPS = 4;
-constexpr int GM_EPI_WARP0 = 6, GM_EPI_WARPS = 8;
+constexpr int GM_UNPACK_WARP0 = 2, GM_UNPACK_WARPS = 8;
+constexpr int GM_EPI_WARP0 = GM_UNPACK_WARP0 + GM_UNPACK_WARPS, GM_EPI_WARPS = 8;
+constexpr int GM_THREADS = (GM_EPI_WARP0 + GM_EPI_WARPS) * 32;
+constexpr int GM_SN_WARPS = 4;              // unpack warps 0-3 also publish S[] for the epilogue
 
 constexpr int GM_A_BYTES = ACT_UNIT_BYTES;                 // 32768 per stage
 constexpr int GM_RAW_BYTES = GM_NTL * TILE_BYTES;          // 18944 per stage
-constexpr int GM_BHALF_BYTES = 2 * 4 * 2 * 2048;           // {hi,lo} x 4 groups x 2 K-chunks x 2 KB
+constexpr int GM_B_LBO = 2 * GM_NTL * 128;                 // 4096: K-chunk stride (32 row-groups x 128 B)
+constexpr int GM_BGROUP_BYTES = 2 * GM_B_LBO;              // 8192: one 32-group = 2 K-chunks
+constexpr int GM_BHALF_BYTES = 4 * GM_BGROUP_BYTES;        // 32768: 4 groups
 constexpr int GM_SN_RING = 4;
 
 struct GemmSmem {
@@ -50,7 +54,7 @@ struct GemmSmem {
     static constexpr int off_b = off_raw + 2 * GM_RAW_BYTES;           // 103424, 128-aligned
     static constexpr int off_sn = off_b + 2 * GM_BHALF_BYTES;
     static constexpr int off_zflag = off_sn + GM_SN_RING * GM_BN * 4;
-    static constexpr int off_bar = off_zflag + GM_SN_RING * GM_UNPACK_WARPS * 4;
+    static constexpr int off_bar = off_zflag + GM_SN_RING * GM_SN_WARPS * 4;
     static constexpr int n_bar = 12 + GM_SN_RING;
     static constexpr int off_tmem = off_bar + n_bar * 8;
     static constexpr int total = off_tmem + 16;
@@ -72,6 +76,32 @@ __device__ __noinline__ float zero_point_term(const uint8_t *__restrict__ w, con
         zs += ((float)sumq[((size_t)m * KT + kt) * 8 + g] * a7) * bz;
     }
     return zs;
+}
+
+// Unpack one 16-byte chunk (channel c of group g: 32 nibbles) into 32 hi bytes + 32 lo bytes.
+//   out_hi / out_lo point at this channel's 16-byte row in K-chunk 0; K-chunk 1 is GM_B_LBO further.
+__device__ __forceinline__ void unpack_chunk(const uint4 wq, int sc, uint8_t *out_hi, uint8_t *out_lo) {
+    const uint32_t mul = (uint32_t)(16 * sc);
+    const uint32_t bias = (uint32_t)(32768 - 128 * sc) * 0x00010001u;
+    const uint32_t wv[4] = {wq.x, wq.y, wq.z, wq.w};
+    uint32_t hi[8], lo[8];
+#pragma unroll
+    for (int s = 0; s < 4; s++) {
+        uint32_t P[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t up = ((wv[s] >> (4 * i)) & 0x000F000Fu) ^ 0x00080008u;    // u = q + 8 in two fields
+            P[i] = up * mul + bias;                                                  // 16*sc*q + 32768
+        }
+        hi[s * 2 + 0] = __byte_perm(P[0], P[1], 0x7351) ^ 0x80808080u;               // elements 0,1,4,5
+        hi[s * 2 + 1] = __byte_perm(P[2], P[3], 0x7351) ^ 0x80808080u;               // elements 2,3,6,7
+        lo[s * 2 + 0] = __byte_perm(P[0], P[1], 0x6240) >> 4;
+        lo[s * 2 + 1] = __byte_perm(P[2], P[3], 0x6240) >> 4;
+    }
+    *reinterpret_cast<uint4 *>(out_hi) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4 *>(out_hi + GM_B_LBO) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+    *reinterpret_cast<uint4 *>(out_lo) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    *reinterpret_cast<uint4 *>(out_lo + GM_B_LBO) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
 }
 
 template <bool DEBUG>
@@ -104,7 +134,7 @@ tcq4_gemm_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict__
             mbar_init(&accfull[i], 1);
             mbar_init(&accempty[i], GM_EPI_WARPS);
         }
-        for (int i = 0; i < GM_SN_RING; i++) mbar_init(&snfull[i], GM_UNPACK_WARPS);
+        for (int i = 0; i < GM_SN_RING; i++) mbar_init(&snfull[i], GM_SN_WARPS);
         fence_mbar_init();
     }
     if (warp == 1) {
@@ -133,14 +163,13 @@ tcq4_gemm_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict__
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
-            constexpr uint32_t idesc_hi = umma_idesc_i8(GM_BM, GM_BN, 1, 1);
-            constexpr uint32_t idesc_lo = umma_idesc_i8(GM_BM, GM_BN, 1, 0);
+            constexpr uint32_t idesc = umma_idesc_i8(GM_BM, 2 * GM_BN, 1, 1);     // 128 x 256 x 32, s8 x s8
             const uint32_t a_base = smem_u32(sA), b_base = smem_u32(sB);
             for (int kt = 0; kt < KT; kt++) {
                 const int s = kt & 1, u = kt >> 1, as = kt & 1;
                 mbar_wait(&full[s], (uint32_t)(u & 1));
                 if (u > 0) mbar_wait(&accempty[as], (uint32_t)((u - 1) & 1));
-                const uint32_t d_hi = tmem + as * 256, d_lo = d_hi + GM_BN;
+                const uint32_t d = tmem + as * 256;
                 for (int h = 0; h < 2; h++) {
                     mbar_wait(&bfull[h], (uint32_t)(kt & 1));
                     tc_fence_after();
@@ -149,10 +178,9 @@ tcq4_gemm_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict__
                         const int g = h * 4 + gl;
                         const uint64_t a_desc =
                             umma_desc_kmajor_noswz(a_base + s * GM_A_BYTES + (2 * g) * ACT_LBO, ACT_LBO, ACT_SBO);
-                        const uint32_t bh = b_base + h * GM_BHALF_BYTES + ((0 * 4 + gl) * 2) * 2048;
-                        const uint32_t bl = b_base + h * GM_BHALF_BYTES + ((1 * 4 + gl) * 2) * 2048;
-                        umma_i8(d_hi, a_desc, umma_desc_kmajor_noswz(bh, 2048, 128), idesc_hi, g > 0 ? 1u : 0u);
-                        umma_i8(d_lo, a_desc, umma_desc_kmajor_noswz(bl, 2048, 128), idesc_lo, g > 0 ? 1u : 0u);
+                        const uint64_t b_desc =
+                            umma_desc_kmajor_noswz(b_base + h * GM_BHALF_BYTES + gl * GM_BGROUP_BYTES, GM_B_LBO, 128);
+                        umma_i8(d, a_desc, b_desc, idesc, g > 0 ? 1u : 0u);
                     }
                     umma_commit(&bfree[h]);
                 }
@@ -162,13 +190,13 @@ tcq4_gemm_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict__
         }
     } else if (warp < GM_EPI_WARP0) {
         // ===================== weight unpack =====================
-        const int ut = threadIdx.x - GM_UNPACK_WARP0 * 32;          // 0..127
+        const int uw = warp - GM_UNPACK_WARP0;
+        const int ut = threadIdx.x - GM_UNPACK_WARP0 * 32;          // 0..255
         for (int kt = 0; kt < KT; kt++) {
             const int s = kt & 1, u = kt >> 1;
             mbar_wait(&full[s], (uint32_t)(u & 1));
             const uint8_t *raw = sRaw + s * GM_RAW_BYTES;
-            // per-channel super-scale for the epilogue + zero-point presence flag
-            {
+            if (uw < GM_SN_WARPS) {     // per-channel super-scale for the epilogue + zero-point presence flag
                 const int j = ut >> 3, c = ut & 7;
                 float sv = 0.0f;
                 int zf = 0;
@@ -184,7 +212,7 @@ tcq4_gemm_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict__
                 const int anyz = __any_sync(0xffffffffu, zf);
                 __syncwarp();
                 if (lane == 0) {
-                    sZflag[ring * GM_UNPACK_WARPS + (warp - GM_UNPACK_WARP0)] = anyz;
+                    sZflag[ring * GM_SN_WARPS + uw] = anyz;
                     mbar_arrive(&snfull[ring]);      // release: epilogue(kt) acquires before reading
                 }
             }
@@ -192,37 +220,16 @@ tcq4_gemm_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict__
                 if (kt > 0) mbar_wait(&bfree[h], (uint32_t)((kt - 1) & 1));
                 uint8_t *bh = sB + h * GM_BHALF_BYTES;
 #pragma unroll
-                for (int it = 0; it < 4; it++) {
-                    const int qid = it * 128 + ut;                  // (gl, j, c)
+                for (int it = 0; it < 2; it++) {
+                    const int qid = it * 256 + ut;                  // (gl, j, c)
                     const int c = qid & 7, j = (qid >> 3) & 15, gl = qid >> 7;
                     if (j < ntl) {
                         const uint8_t *tp = raw + j * TILE_BYTES;
                         const int g = h * 4 + gl;
                         const uint4 wq = *reinterpret_cast<const uint4 *>(tp + g * 128 + c * 16);
                         const int sc = *reinterpret_cast<const int8_t *>(tp + TILE_OFF_SC + c * 8 + g);
-                        const uint32_t mul = (uint32_t)(16 * sc);
-                        const uint32_t bias = (uint32_t)(32768 - 128 * sc) * 0x00010001u;
-                        const uint32_t wv[4] = {wq.x, wq.y, wq.z, wq.w};
-                        uint32_t hi[8], lo[8];
-#pragma unroll
-                        for (int sidx = 0; sidx < 4; sidx++) {
-                            uint32_t P[4];
-#pragma unroll
-                            for (int i = 0; i < 4; i++) {
-                                const uint32_t up = ((wv[sidx] >> (4 * i)) & 0x000F000Fu) ^ 0x00080008u;
-                                P[i] = up * mul + bias;
-                            }
-                            hi[sidx * 2 + 0] = __byte_perm(P[0], P[1], 0x7351) ^ 0x80808080u;
-                            hi[sidx * 2 + 1] = __byte_perm(P[2], P[3], 0x7351) ^ 0x80808080u;
-                            lo[sidx * 2 + 0] = __byte_perm(P[0], P[1], 0x6240);
-                            lo[sidx * 2 + 1] = __byte_perm(P[2], P[3], 0x6240);
-                        }
-                        uint8_t *dh = bh + ((0 * 4 + gl) * 2) * 2048 + j * 128 + c * 16;
-                        uint8_t *dl = bh + ((1 * 4 + gl) * 2) * 2048 + j * 128 + c * 16;
-                        *reinterpret_cast<uint4 *>(dh) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                        *reinterpret_cast<uint4 *>(dh + 2048) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-                        *reinterpret_cast<uint4 *>(dl) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-                        *reinterpret_cast<uint4 *>(dl + 2048) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+                        uint8_t *row = bh + gl * GM_BGROUP_BYTES + j * 128 + c * 16;
+                        unpack_chunk(wq, sc, row, row + GM_NTL * 128);      // lo rows follow the 128 hi rows
                     }
                 }
                 fence_proxy_async_smem();
@@ -247,9 +254,8 @@ tcq4_gemm_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict__
 
         for (int kt = 0; kt < KT; kt++) {
             const int as = kt & 1, u = kt >> 1;
-            // row factor: a7 / 16 (weights carried x16) / 127
             const float a7 = mvalid ? st.a7[(size_t)m * KT + kt] : 0.0f;
-            const float rm = a7 * (1.0f / (16.0f * 127.0f));
+            const float rm = a7 * (1.0f / 127.0f);          // row factor a7/127; column factor S[n]
             const int ring = kt & (GM_SN_RING - 1);
             mbar_wait(&snfull[ring], (uint32_t)((kt / GM_SN_RING) & 1));
             mbar_wait(&accfull[as], (uint32_t)(u & 1));
@@ -258,29 +264,31 @@ tcq4_gemm_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict__
             const uint32_t t_hi = tmem + ((uint32_t)(quarter * 32) << 16) + as * 256 + colhalf * 64;
             const uint32_t t_lo = t_hi + GM_BN;
 #pragma unroll
-            for (int ch = 0; ch < 4; ch++) {
-                uint32_t rh[16], rl[16];
-                tmem_ld_32x16(t_hi + ch * 16, rh);
-                tmem_ld_32x16(t_lo + ch * 16, rl);
+            for (int ch = 0; ch < 8; ch++) {
+                uint32_t rh[8], rl[8];
+                tmem_ld_32x8(t_hi + ch * 8, rh);
+                tmem_ld_32x8(t_lo + ch * 8, rl);
                 tmem_ld_wait();
-                if (ch == 3) {               // all TMEM reads of this stage are done: hand it back
+                if (ch == 7) {               // all TMEM reads of this stage are done: hand it back
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&accempty[as]);
                 }
+                const float4 s0 = *reinterpret_cast<const float4 *>(sn + ch * 8);
+                const float4 s1 = *reinterpret_cast<const float4 *>(sn + ch * 8 + 4);
+                const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
 #pragma unroll
-                for (int i = 0; i < 16; i++) {
-                    const int i16 = ((int)rh[i] << 8) + (int)rl[i];          // = 16 * sum_g sc*dot
-                    const float f = (float)i16 * rm;
-                    acc[ch * 16 + i] = __fmaf_rn(f, sn[ch * 16 + i], acc[ch * 16 + i]);
+                for (int i = 0; i < 8; i++) {
+                    const int isum = ((int)rh[i] << 4) + (int)rl[i];         // = sum_g sc*dot, exact
+                    const float f = (float)isum * rm;
+                    acc[ch * 8 + i] = __fmaf_rn(f, sv[i], acc[ch * 8 + i]);
                     if (DEBUG) {
-                        const int n = n_base + ch * 16 + i;
-                        if (dbg_isum && mvalid && n < N) dbg_isum[((size_t)m * N + n) * KT + kt] = i16 >> 4;
+                        const int n = n_base + ch * 8 + i;
+                        if (dbg_isum && mvalid && n < N) dbg_isum[((size_t)m * N + n) * KT + kt] = isum;
                     }
                 }
             }
-            // zero-point term (Z != 0 never produced by the reference quantiser; kept for format parity)
-            const int *zfl = sZflag + ring * GM_UNPACK_WARPS;
+            const int *zfl = sZflag + ring * GM_SN_WARPS;
             if ((zfl[0] | zfl[1] | zfl[2] | zfl[3]) && mvalid) {
 #pragma unroll
                 for (int i = 0; i < 64; i++) {

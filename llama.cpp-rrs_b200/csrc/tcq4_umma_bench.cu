@@ -1,0 +1,130 @@
+// tcq4_umma_bench.cu -- bare tcgen05.mma issue loop: measures the tensor-pipe peak of this box for
+// kind::i8 / kind::f16 / kind::f8f6f4 at a given N and shared-memory layout.  MEASURED_PEAKS.json
+// has no INT8 entry, so this is the denominator the GEMM's tensor roofline is
+// quoted against, and the experiment that decides the operand layout.  Operand contents are
+// irrelevant (zeroed smem); only issue/fetch/execute timing is measured.
+#include "../../include/tcq4_b200.h"
+#include "tcq4_common.cuh"
+
+namespace tcq4 {
+
+enum { UB_I8 = 0, UB_BF16 = 1, UB_FP8 = 2 };
+
+template <int KIND>
+__device__ __forceinline__ void ub_mma(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+    if (KIND == UB_I8) {
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(a), "l"(b), "r"(idesc),
+                     "r"(acc) : "memory");
+    } else if (KIND == UB_BF16) {
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(a), "l"(b), "r"(idesc),
+                     "r"(acc) : "memory");
+    } else {
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(a), "l"(b),
+                     "r"(idesc), "r"(acc) : "memory");
+    }
+}
+
+// swizzle: 0 = none (LBO 2048 / SBO 128, the layout of tcq4_gemm.cu), 1 = SWIZZLE_128B (SBO 1024)
+template <int KIND>
+__global__ void __launch_bounds__(128, 1)
+umma_bench_kernel(int N, int swizzle, int iters, int kslices, long long *cycles_out) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < (64 * 1024) / 4; i += blockDim.x) reinterpret_cast<uint32_t *>(smem)[i] = 0;
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        fence_mbar_init();
+    }
+    if (warp == 0) {
+        tmem_alloc(&tmem_slot, 512);
+        tmem_relinquish();
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_slot;
+    if (threadIdx.x == 0) {
+        uint32_t idesc;
+        if (KIND == UB_I8) idesc = umma_idesc_i8(128, N, 1, 1);
+        else if (KIND == UB_BF16) idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | (8u << 24);
+        else idesc = (1u << 4) | ((uint32_t)(N >> 3) << 17) | (8u << 24);
+        const uint32_t a_base = smem_u32(smem), b_base = a_base + 32 * 1024;
+        const long long t0 = clock64();
+        for (int it = 0; it < iters; it++) {
+            for (int ks = 0; ks < kslices; ks++) {
+                uint64_t ad, bd;
+                if (swizzle == 0) {
+                    ad = umma_desc_kmajor_noswz(a_base + ks * 4096, 2048, 128);
+                    bd = umma_desc_kmajor_noswz(b_base + ks * (N * 32), N * 16, 128);
+                } else {
+                    // 128B swizzle, K-major: rows 128 B apart, 8-row groups 1024 B apart, k-slice = +32 B
+                    ad = ((uint64_t)(((a_base + ks * 32) >> 4) & 0x3FFF)) | ((uint64_t)1 << 16) |
+                         ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+                    bd = ((uint64_t)(((b_base + ks * 32) >> 4) & 0x3FFF)) | ((uint64_t)1 << 16) |
+                         ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+                }
+                ub_mma<KIND>(tmem + (it & 1) * 256, ad, bd, idesc, 1u);
+            }
+        }
+        umma_commit(&bar);
+        mbar_wait(&bar, 0);
+        const long long t1 = clock64();
+        cycles_out[blockIdx.x] = t1 - t0;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+}  // namespace tcq4
+
+extern "C" TCQ4_B200_API int tcq4_b200_measure_umma(int kind, int N, int swizzle, int iters, double *tops_out,
+                                                    double *cycles_per_mma_out) {
+    using namespace tcq4;
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return TCQ4_ERR_NO_DEVICE;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int kslices = 4;
+    const size_t smem = 64 * 1024 + 1024;
+    long long *d_cycles = nullptr;
+    if (cudaMalloc(&d_cycles, sizeof(long long) * sms) != cudaSuccess) return TCQ4_ERR_CUDA;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    float ms = 0.f;
+    cudaError_t err = cudaSuccess;
+    for (int rep = 0; rep < 2; rep++) {     // first rep warms up
+        cudaEventRecord(e0);
+        if (kind == UB_I8) {
+            cudaFuncSetAttribute(umma_bench_kernel<UB_I8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            umma_bench_kernel<UB_I8><<<sms, 128, smem>>>(N, swizzle, iters, kslices, d_cycles);
+        } else if (kind == UB_BF16) {
+            cudaFuncSetAttribute(umma_bench_kernel<UB_BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            umma_bench_kernel<UB_BF16><<<sms, 128, smem>>>(N, swizzle, iters, kslices, d_cycles);
+        } else {
+            cudaFuncSetAttribute(umma_bench_kernel<UB_FP8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            umma_bench_kernel<UB_FP8><<<sms, 128, smem>>>(N, swizzle, iters, kslices, d_cycles);
+        }
+        cudaEventRecord(e1);
+        err = cudaEventSynchronize(e1);
+        if (err != cudaSuccess) break;
+        cudaEventElapsedTime(&ms, e0, e1);
+    }
+    long long h_cycles = 0;
+    cudaMemcpy(&h_cycles, d_cycles, sizeof(long long), cudaMemcpyDeviceToHost);
+    cudaFree(d_cycles);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (err != cudaSuccess) return TCQ4_ERR_CUDA;
+    const double kelems = (kind == UB_BF16) ? 16.0 : 32.0;
+    const double ops = 2.0 * 128.0 * N * kelems * (double)iters * kslices * sms;
+    if (tops_out) *tops_out = ops / (ms * 1e-3) / 1e12;
+    if (cycles_per_mma_out) *cycles_per_mma_out = (double)h_cycles / ((double)iters * kslices);
+    return TCQ4_OK;
+}

@@ -1,0 +1,314 @@
+"""GPU parity tests (B200): the CUDA path, called through the C ABI, against the CPU oracle.
+
+Bar (BASELINE.json north_star): activation int4 codes, max_abs, group sums and the int32 accumulators
+bit-exact; fp32 outputs within NMSE <= 1e-3 of the oracle (asserted much tighter: <= 1e-9, only the
+fp32 association differs).  Nothing here reads /root/reference."""
+import numpy as np
+import pytest
+
+from conftest import block_perm, make_acts, make_weights, nmse
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+FP32_NMSE_SPEC = 1e-3      # tolerance stated by north_star
+FP32_NMSE_TIGHT = 1e-9     # what we actually hold
+
+
+def _dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _unpack_ref_blocks(blocks: np.ndarray):
+    """block_rrs_int4_tc bytes [M][KT][160] -> codes int8 [M][K], max_abs f32 [M][KT], sum_q int16 [M][KT][8]."""
+    M, KT, _ = blocks.shape
+    qs = blocks[:, :, :128]
+    lo = (qs & 0xF).astype(np.int8)
+    hi = (qs >> 4).astype(np.int8)
+    lo = np.where(lo >= 8, lo - 16, lo).astype(np.int8)
+    hi = np.where(hi >= 8, hi - 16, hi).astype(np.int8)
+    codes = np.stack([lo, hi], axis=-1).reshape(M, KT * 256)
+    mx = np.ascontiguousarray(blocks[:, :, 128:132]).view(np.float32).reshape(M, KT)
+    sq = np.ascontiguousarray(blocks[:, :, 132:148]).view(np.int16).reshape(M, KT, 8)
+    return codes, mx, sq
+
+
+# ------------------------------------------------------------------------------------------------
+# K1: activation stage
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,K,use_perm", [(1, 256, False), (3, 2560, False), (7, 1024, True), (130, 512, True),
+                                          (512, 2560, False)])
+def test_act_quant_bit_exact(t4, orc, M, K, use_perm):
+    rng = np.random.default_rng(100 + M + K)
+    x = make_acts(rng, M, K)
+    perm = block_perm(rng, K) if use_perm else None
+    blocks = t4.fwht_quantize_tc(_dev(x), _dev(perm) if use_perm else None).cpu().numpy()
+    codes, mx, sq = _unpack_ref_blocks(blocks)
+    rc, rmx, rsq = orc.quantize_act(x, perm)
+    assert np.array_equal(codes, rc)
+    assert np.array_equal(mx.view(np.uint32), rmx.view(np.uint32))
+    assert np.array_equal(sq, rsq)
+    # and byte-for-byte against the oracle's block_rrs_int4_tc writer
+    ob = orc.quantize_act_blocks(x, perm).reshape(M, K // 256, 160)
+    assert np.array_equal(blocks[:, :, :148], ob[:, :, :148])
+
+
+def test_act_quant_edge_cases(t4, orc):
+    K = 1024
+    x = np.zeros((8, K), dtype=np.float32)
+    x[1, :256] = 1e-12
+    x[2, 7] = 1000.0
+    x[3, :] = np.linspace(-3, 3, K, dtype=np.float32)
+    x[4, 300] = np.inf
+    x[5, 10] = np.nan
+    x[6, :] = 1e30
+    x[7, :] = -7.0
+    rc, rmx, rsq = orc.quantize_act(x)
+    codes, mx, sq = _unpack_ref_blocks(t4.fwht_quantize_tc(_dev(x)).cpu().numpy())
+    assert np.array_equal(codes, rc)
+    assert np.array_equal(sq, rsq)
+    assert np.array_equal(mx, rmx, equal_nan=True)                       # NaN payload bits may differ
+
+
+def test_act_quant_arbitrary_perm(t4, orc):
+    """The reference kernel accepts any index vector (act_row[perm[k]], tcq4_k32.cu:774-775)."""
+    rng = np.random.default_rng(5)
+    K = 768
+    x = make_acts(rng, 4, K)
+    perm = rng.permutation(K).astype(np.int32)
+    codes, _, _ = _unpack_ref_blocks(t4.fwht_quantize_tc(_dev(x), _dev(perm)).cpu().numpy())
+    assert np.array_equal(codes, orc.quantize_act(x, perm)[0])
+
+
+# ------------------------------------------------------------------------------------------------
+# K3: fused decode GEMV
+# ------------------------------------------------------------------------------------------------
+GEMV_SHAPES = [(1, 8, 256), (1, 64, 512), (2, 256, 1024), (3, 136, 768), (4, 1024, 2560), (1, 2560, 9728),
+               (4, 9728, 2560)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMV_SHAPES)
+@pytest.mark.parametrize("use_perm", [False, True])
+def test_gemv_vs_oracle(t4, orc, M, N, K, use_perm):
+    rng = np.random.default_rng(200 + M + N + K)
+    W = make_weights(rng, N, K)
+    x = make_acts(rng, M, K)
+    perm = block_perm(rng, K) if use_perm else None
+    tiles = orc.quantize_tiles(orc.apply_perm_weights(W, perm) if use_perm else W)
+    ref = orc.mul_mat(tiles, x, N, perm, want_isum=True)
+    y, isum = t4.mul_mat_debug(_dev(tiles), _dev(x), N, _dev(perm) if use_perm else None, kernel=t4.KERNEL_GEMV)
+    torch.cuda.synchronize()
+    assert np.array_equal(isum.cpu().numpy(), ref["isum"])             # int32 accumulators bit-exact
+    e = nmse(y.cpu().numpy(), ref["C"])
+    assert e <= FP32_NMSE_TIGHT <= FP32_NMSE_SPEC, e
+
+
+def test_gemv_whole_row_is_bit_identical(t4, orc):
+    """When one warp owns a whole output row the fp32 result is bit-identical to the oracle
+    (same 4,2,1 tree over groups, sequential over k-tiles, no FMA contraction)."""
+    rng = np.random.default_rng(7)
+    M, N, K = 2, 16384, 256          # KT = 1: every row is whole
+    tiles = orc.quantize_tiles(make_weights(rng, N, K))
+    x = make_acts(rng, M, K)
+    y = t4.mul_mat(_dev(tiles), _dev(x), N, workspace=t4.Workspace.for_shape(M, N, K), kernel=t4.KERNEL_GEMV)
+    ref = orc.mul_mat(tiles, x, N)["C"]
+    assert np.array_equal(y.cpu().numpy().view(np.uint32), ref.view(np.uint32))
+
+
+def test_gemv_zero_points(t4, orc):
+    """Tiles with non-zero Z/zc: the format carries them even though the quantiser writes 0."""
+    rng = np.random.default_rng(8)
+    M, N, K = 2, 64, 512
+    t = orc.quantize_tiles(make_weights(rng, N, K)).reshape(-1, 1184).copy()
+    t[:, 1040:1056] = np.frombuffer(rng.uniform(-0.01, 0.01, (t.shape[0], 8)).astype(np.float16).tobytes(),
+                                    dtype=np.uint8).reshape(t.shape[0], 16)
+    t[:, 1120:1184] = rng.integers(-127, 128, (t.shape[0], 64)).astype(np.int8).view(np.uint8)
+    t = t.reshape(-1)
+    x = make_acts(rng, M, K)
+    ref = orc.mul_mat(t, x, N)["C"]
+    y = t4.mul_mat(_dev(t), _dev(x), N, workspace=t4.Workspace.for_shape(M, N, K), kernel=t4.KERNEL_GEMV)
+    assert nmse(y.cpu().numpy(), ref) <= FP32_NMSE_TIGHT
+
+
+def test_gemv_repeatable_and_tickets_self_clean(t4, orc):
+    rng = np.random.default_rng(9)
+    M, N, K = 1, 1024, 2560
+    tiles = _dev(orc.quantize_tiles(make_weights(rng, N, K)))
+    x = _dev(make_acts(rng, M, K))
+    ws = t4.Workspace.for_shape(M, N, K)
+    y0 = t4.mul_mat(tiles, x, N, workspace=ws, kernel=t4.KERNEL_GEMV).clone()
+    for _ in range(5):
+        y = t4.mul_mat(tiles, x, N, workspace=ws, kernel=t4.KERNEL_GEMV)
+        assert torch.equal(y, y0)                                        # deterministic split-K
+
+
+# ------------------------------------------------------------------------------------------------
+# K2: tcgen05 GEMM
+# ------------------------------------------------------------------------------------------------
+GEMM_SHAPES = [(5, 128, 256), (128, 128, 256), (130, 256, 512), (64, 8, 256), (33, 136, 768), (257, 1024, 1024),
+               (512, 9728, 2560)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_vs_oracle(t4, orc, M, N, K):
+    rng = np.random.default_rng(300 + M + N + K)
+    W = make_weights(rng, N, K)
+    x = make_acts(rng, M, K)
+    tiles = orc.quantize_tiles(W)
+    big = M * N * K > 2e9
+    Mo = 24 if big else M                      # oracle on a row subset at the full size
+    rows = np.sort(rng.choice(M, Mo, replace=False)) if big else np.arange(M)
+    ref = orc.mul_mat(tiles, x[rows], N, want_isum=True)
+    y, isum = t4.mul_mat_debug(_dev(tiles), _dev(x), N, kernel=t4.KERNEL_GEMM)
+    torch.cuda.synchronize()
+    assert np.array_equal(isum.cpu().numpy()[rows], ref["isum"])        # TMEM accumulators bit-exact
+    e = nmse(y.cpu().numpy()[rows], ref["C"])
+    assert e <= FP32_NMSE_TIGHT <= FP32_NMSE_SPEC, e
+
+
+def test_gemm_with_perm_and_negative_scale_codes(t4, orc):
+    """perm path + sc < 0 (int8 allows it; the quantiser never writes it) exercise the unpack bias math."""
+    rng = np.random.default_rng(11)
+    M, N, K = 40, 128, 512
+    perm = block_perm(rng, K)
+    t = orc.quantize_tiles(orc.apply_perm_weights(make_weights(rng, N, K), perm)).reshape(-1, 1184).copy()
+    sc = t[:, 1056:1120].view(np.int8)
+    sc[:, ::3] = -sc[:, ::3]
+    sc[:, 5] = -127
+    t = t.reshape(-1)
+    x = make_acts(rng, M, K)
+    ref = orc.mul_mat(t, x, N, perm, want_isum=True)
+    y, isum = t4.mul_mat_debug(_dev(t), _dev(x), N, _dev(perm), kernel=t4.KERNEL_GEMM)
+    assert np.array_equal(isum.cpu().numpy(), ref["isum"])
+    assert nmse(y.cpu().numpy(), ref["C"]) <= FP32_NMSE_TIGHT
+
+
+def test_gemm_zero_points(t4, orc):
+    rng = np.random.default_rng(12)
+    M, N, K = 20, 128, 512
+    t = orc.quantize_tiles(make_weights(rng, N, K)).reshape(-1, 1184).copy()
+    t[:, 1040:1056] = np.frombuffer(rng.uniform(-0.01, 0.01, (t.shape[0], 8)).astype(np.float16).tobytes(),
+                                    dtype=np.uint8).reshape(t.shape[0], 16)
+    t[:, 1120:1184] = rng.integers(-127, 128, (t.shape[0], 64)).astype(np.int8).view(np.uint8)
+    t = t.reshape(-1)
+    x = make_acts(rng, M, K)
+    ref = orc.mul_mat(t, x, N)["C"]
+    y = t4.mul_mat(_dev(t), _dev(x), N, workspace=t4.Workspace.for_shape(M, N, K), kernel=t4.KERNEL_GEMM)
+    assert nmse(y.cpu().numpy(), ref) <= 1e-8
+
+
+def test_gemm_equals_gemv_on_small_m(t4, orc):
+    """Both kernels form the same int32 accumulators; fp32 differs only by association."""
+    rng = np.random.default_rng(13)
+    M, N, K = 3, 512, 1024
+    tiles = _dev(orc.quantize_tiles(make_weights(rng, N, K)))
+    x = _dev(make_acts(rng, M, K))
+    y1, i1 = t4.mul_mat_debug(tiles, x, N, kernel=t4.KERNEL_GEMV)
+    y2, i2 = t4.mul_mat_debug(tiles, x, N, kernel=t4.KERNEL_GEMM)
+    assert torch.equal(i1, i2)
+    assert nmse(y2.cpu().numpy(), y1.cpu().numpy()) <= FP32_NMSE_TIGHT
+
+
+# ------------------------------------------------------------------------------------------------
+# size-independent properties at BASELINE.json's full sizes (synthetic tiles, no oracle run)
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,N,K", [(1, 9728, 2560), (512, 9728, 2560), (64, 14336, 4096)])
+def test_full_size_properties(t4, M, N, K):
+    tiles = t4.random_tiles(N, K, seed=3)
+    g = torch.Generator(device="cuda")
+    g.manual_seed(4)
+    x = torch.randn((M, K), device="cuda", generator=g)
+    ws = t4.Workspace.for_shape(M, N, K)
+    y = t4.mul_mat(tiles, x, N, workspace=ws).clone()
+    assert torch.isfinite(y).all()
+    # (1) power-of-two scaling of x scales y exactly (codes unchanged, a7 scales exactly)
+    y4 = t4.mul_mat(tiles, x * 4.0, N, workspace=ws)
+    assert torch.equal(y4, y * 4.0)
+    # (2) rows are independent: a row computed alone through the GEMV has the same integer
+    #     accumulators, so fp32 agrees to association error
+    r = M // 2
+    y1 = t4.mul_mat(tiles, x[r:r + 1].contiguous(), N, workspace=ws, kernel=t4.KERNEL_GEMV)
+    assert nmse(y1.cpu().numpy(), y[r:r + 1].cpu().numpy()) <= FP32_NMSE_TIGHT
+    # (3) N-sharding: concatenated shard outputs are bit-identical to the full output
+    parts = []
+    for rank in range(4):
+        sw = t4.ShardedWeight(N, K, 4, rank, tiles_full=tiles)
+        parts.append(sw.local(x, workspace=ws).clone())
+    ycat = torch.cat(parts, dim=1)
+    if t4.select_kernel(M, N, K) == t4.KERNEL_GEMM:
+        assert torch.equal(ycat, y)
+    else:
+        assert nmse(ycat.cpu().numpy(), y.cpu().numpy()) <= FP32_NMSE_TIGHT
+
+
+# ------------------------------------------------------------------------------------------------
+# boundary: registry, ggml mirror, host entry, capture safety
+# ------------------------------------------------------------------------------------------------
+def test_registry_and_ggml_mirror(t4, orc):
+    rng = np.random.default_rng(14)
+    M, N, K = 2, 64, 512
+    perm = block_perm(rng, K)
+    tiles = orc.quantize_tiles(orc.apply_perm_weights(make_weights(rng, N, K), perm))
+    x = make_acts(rng, M, K)
+    t4.clear_perms()
+    t4.set_reorder_enabled(True)
+    name = "blk.0.ffn_up.weight"
+    assert not t4.has_perm(name)
+    t4.register_perm(name, perm)
+    assert t4.has_perm(name) and t4.get_perm_ptr(name) != 0
+    y = t4.ggml_mul_mat(_dev(tiles), _dev(x), N, name=name)
+    assert nmse(y.cpu().numpy(), orc.mul_mat(tiles, x, N, perm)["C"]) <= FP32_NMSE_TIGHT
+    t4.set_reorder_enabled(False)                       # rrs.cu:102: lookups return nullptr when disabled
+    assert not t4.has_perm(name)
+    y2 = t4.ggml_mul_mat(_dev(tiles), _dev(x), N, name=name)
+    assert nmse(y2.cpu().numpy(), orc.mul_mat(tiles, x, N, None)["C"]) <= FP32_NMSE_TIGHT
+    t4.set_reorder_enabled(True)
+    t4.register_perm(name, np.arange(K, dtype=np.int32))   # re-registration replaces (rrs.cu:88-90)
+    y3 = t4.ggml_mul_mat(_dev(tiles), _dev(x), N, name=name)
+    assert torch.equal(y3, y2)
+    t4.clear_perms()
+    assert not t4.has_perm(name)
+
+
+def test_error_behaviour(t4):
+    x = torch.zeros((1, 300), device="cuda")
+    w = torch.zeros(1184, dtype=torch.uint8, device="cuda")
+    with pytest.raises((t4.Tcq4Error, ValueError)):
+        t4.mul_mat(w, x, 8)
+    with pytest.raises(t4.Tcq4Error) as ei:
+        t4.mul_mat(w, torch.zeros((1, 256), device="cuda"), 8, workspace=t4.Workspace(256))
+    assert ei.value.status == 3
+
+
+def test_host_entry_matches_device_entry(t4, orc):
+    rng = np.random.default_rng(15)
+    for M in (1, 37):
+        N, K = 256, 512
+        tiles = _dev(orc.quantize_tiles(make_weights(rng, N, K)))
+        xh = torch.from_numpy(make_acts(rng, M, K)).pin_memory()
+        yh = torch.empty((M, N), dtype=torch.float32).pin_memory()
+        t4.mul_mat_host(tiles, xh, yh, N)
+        yd = t4.mul_mat(tiles, xh.cuda(), N)
+        assert torch.equal(yh, yd.cpu())
+
+
+def test_cuda_graph_capture(t4, orc):
+    """Launches are capture-safe: no allocation / sync on the path (ggml-cuda.cu:3791-3799)."""
+    rng = np.random.default_rng(16)
+    N, K = 512, 1024
+    tiles = _dev(orc.quantize_tiles(make_weights(rng, N, K)))
+    for M in (1, 48):
+        x = _dev(make_acts(rng, M, K))
+        ws = t4.Workspace.for_shape(M, N, K)
+        out = torch.empty((M, N), device="cuda")
+        eager = t4.mul_mat(tiles, x, N, workspace=ws).clone()
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(s):
+            with torch.cuda.graph(g, stream=s):
+                t4.mul_mat(tiles, x, N, out=out, workspace=ws)
+        for _ in range(3):
+            g.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(out, eager)
