@@ -1,0 +1,423 @@
+#!/usr/bin/env python
+"""bench.py -- TCQ4_K32 W4A4 MUL_MAT on B200: Qwen3-4B's 252 linear matmuls (BASELINE.json configs[1]).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            own arm (CUDA, through the C ABI)
+  python bench.py --impl reference [--steps K] [--warmup W]      the reference's CPU path (oracle/_ref)
+  torchrun ... bench.py --gpus N ...                             N-sharded (column-parallel) + NCCL all-gather
+
+A step = one 512-token prefill pass over the 36 x 7 TCQ4_K32 matmuls of Qwen3-4B (q,k,v,o,gate,up,down),
+synthetic tiles, 252 distinct weight buffers (2.1 GB >> 126 MB L2, so every weight byte comes from HBM).
+`value` = prefill tokens/s of that matmul chain (linear layers only -- all this path covers); the same
+JSON line also carries the batch-1 decode pass (`decode`), the per-kernel roofline legs, the end-to-end
+number through the host-buffer C-ABI call, and the CPU baseline.  Nothing here reads /root/reference.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# Qwen3-4B (hidden 2560, ffn 9728, 32 q heads x 128, 8 kv heads x 128, 36 layers): (name, N, K)
+QWEN3_4B_LAYER = [("attn_q", 4096, 2560), ("attn_k", 1024, 2560), ("attn_v", 1024, 2560), ("attn_output", 2560, 4096),
+                  ("ffn_gate", 9728, 2560), ("ffn_up", 9728, 2560), ("ffn_down", 2560, 9728)]
+QWEN3_4B_LAYERS = 36
+PREFILL_M = 512
+METRIC = "qwen3_4b_tcq4_k32_mul_mat_prefill512_tokens_per_s"
+UNIT = "tok/s"
+TILE_BYTES = 1184
+
+
+def alg_bytes(M, N, K):
+    """N*K*1184/2048 weight bytes + fp32 activations in + fp32 outputs out."""
+    return N * K * TILE_BYTES // 2048 + 4 * M * K + 4 * M * N
+
+
+def layer_ops(M):
+    return sum(2 * M * N * K for _, N, K in QWEN3_4B_LAYER)
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"hbm_gbs": float(d["hbm_gbs"]), "bf16_tflops": float(d["bf16_tflops"]),
+                "bf16_tflops_sustained": float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+# --------------------------------------------------------------------------------------------------
+# clocks sampling (B200_PROFILING.md recipe)
+# --------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.path = f"/tmp/tcq4_clocks_{os.getpid()}.csv"
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                c = [x.strip() for x in line.split(",")]
+                if len(c) < 9:
+                    continue
+                try:
+                    sm.append(float(c[1]))
+                    mx.append(float(c[2]))
+                except ValueError:
+                    continue
+                for i, nme in enumerate(names):
+                    if c[5 + i].lower().startswith("active"):
+                        reasons.add(nme)
+            os.unlink(self.path)
+        except Exception:  # noqa: BLE001
+            pass
+        if sm:
+            busy = [v for v in sm if v > 0.5 * max(sm)] or sm
+            out.update(sm_mhz=statistics.median(busy), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU side: the reference's own CPU code (oracle/_ref), used ONLY as the reported baseline
+# --------------------------------------------------------------------------------------------------
+def cpu_random_tiles(N, K, seed):
+    """Same distribution as the device generator: random nibbles, sc in [1,127], S ~ U(1e-3,1e-2) fp16, Z = zc = 0."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    nt = (N // 8) * (K // 256)
+    t = np.zeros((nt, TILE_BYTES), dtype=np.uint8)
+    t[:, :1024] = rng.integers(0, 256, (nt, 1024), dtype=np.uint8)
+    t[:, 1024:1040] = (rng.random((nt, 8)) * 9e-3 + 1e-3).astype(np.float16).view(np.uint8).reshape(nt, 16)
+    t[:, 1056:1120] = rng.integers(1, 128, (nt, 64), dtype=np.uint8)
+    return t.reshape(-1)
+
+
+class CpuLayer:
+    """One Qwen3-4B layer's 7 matmuls on the host cores: dequantize_row_tcq4_tile -> F32, ggml_fwht_impl
+    on the activations, ggml CPU backend F32 MUL_MAT.  A bounded sample of the workload:
+    tokens/s = M / (36 * t_layer)."""
+
+    def __init__(self, M):
+        import numpy as np
+        from oracle import pyoracle
+        self.np = np
+        self.rb = pyoracle.RefBaseline()
+        self.M = M
+        self.tiles = [cpu_random_tiles(N, K, 1000 + i) for i, (_, N, K) in enumerate(QWEN3_4B_LAYER)]
+        rng = np.random.default_rng(5)
+        self.x = {K: rng.standard_normal((M, K)).astype(np.float32) for K in {k for _, _, k in QWEN3_4B_LAYER}}
+
+    def run(self):
+        parts = {"dequant_s": 0.0, "fwht_s": 0.0, "matmul_s": 0.0}
+        t0 = time.perf_counter()
+        for (_, N, K), tl in zip(QWEN3_4B_LAYER, self.tiles):
+            _, t = self.rb.mul_mat(tl, self.x[K], N)
+            for k in parts:
+                parts[k] += t[k]
+        return time.perf_counter() - t0, parts
+
+
+def cpu_baseline_leg(M=PREFILL_M, reps=2):
+    layer = CpuLayer(M)
+    layer.run()                                  # warm-up: thread pool, page faults
+    best, parts = None, None
+    for _ in range(reps):
+        t, p = layer.run()
+        if best is None or t < best:
+            best, parts = t, p
+    return {"value": M / (best * QWEN3_4B_LAYERS), "unit": UNIT, "cores": layer.rb.threads, "kind": layer.rb.kind,
+            "sample": f"1 of {QWEN3_4B_LAYERS} layers (7 matmuls, M={M}), best of {reps}, scaled x{QWEN3_4B_LAYERS}",
+            "layer_s": best, "parts_s": {k: round(v, 4) for k, v in parts.items()}}
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's CPU implementation of the path (there is no CPU TCQ4 MUL_MAT in
+    the fork, README.md:54; north_star defines the CPU baseline as quantiser output -> dequant -> F32 MUL_MAT)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    layer = CpuLayer(PREFILL_M)
+    for _ in range(max(1, min(args.warmup, 2))):
+        layer.run()
+    ts = []
+    for _ in range(args.steps):
+        t, _ = layer.run()
+        ts.append(t)
+    t_step = sum(ts) / len(ts) * QWEN3_4B_LAYERS           # a step = all 36 layers; each timed step is a 1-layer sample
+    val = PREFILL_M / t_step
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t_step * 1e3, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "Qwen3-4B TCQ4_K32 252 linear matmuls, 512-token prefill (BASELINE.json configs[1])",
+                       "M": PREFILL_M, "layers": QWEN3_4B_LAYERS, "matmuls_per_layer": len(QWEN3_4B_LAYER)},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": layer.rb.threads, "kind": layer.rb.kind,
+                             "sample": f"each step = 1 of {QWEN3_4B_LAYERS} layers (7 matmuls, M={PREFILL_M}) scaled x{QWEN3_4B_LAYERS}"},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------
+# own arm
+# --------------------------------------------------------------------------------------------------
+class Chain:
+    """The 252 matmuls of Qwen3-4B, N-sharded over `world` ranks (shard = contiguous tile byte range)."""
+
+    def __init__(self, t4, torch, M, world, rank, weights=None):
+        self.t4, self.torch, self.M, self.world, self.rank = t4, torch, M, world, rank
+        self.ops = []                                  # (sharded weight, K, N)
+        if weights is None:
+            weights = []
+            for layer in range(QWEN3_4B_LAYERS):
+                for j, (_, N, K) in enumerate(QWEN3_4B_LAYER):
+                    n0, n1, _, _ = t4.shard_range(N, K, world, rank, 64)
+                    tl = t4.random_tiles(n1 - n0, K, seed=(layer * 16 + j) * 64 + rank)
+                    weights.append(t4.ShardedWeight(N, K, world, rank, tiles_local=tl, align=64))
+        self.weights = weights
+        g = torch.Generator(device="cuda")
+        g.manual_seed(17)
+        Ks = sorted({K for _, _, K in QWEN3_4B_LAYER})
+        Ns = sorted({N for _, N, _ in QWEN3_4B_LAYER})
+        self.x = {K: torch.randn((M, K), device="cuda", generator=g) for K in Ks}
+        self.y_local = {N: torch.empty((M, t4.shard_range(N, 256, world, rank, 64)[1] - t4.shard_range(N, 256, world, rank, 64)[0]),
+                                       device="cuda") for N in Ns}
+        wsz = max(t4.workspace_size(M, w.n_local, w.K) for w in weights)
+        self.ws = t4.Workspace(wsz)
+        self.graph = None
+        self.launches_per_step = None
+
+    def weight_bytes(self):
+        return sum(w.tiles.numel() for w in self.weights)
+
+    def step_eager(self):
+        last = None
+        for w in self.weights:
+            yl = w.local(self.x[w.K], out=self.y_local[w.N], workspace=self.ws)
+            last = w.gather(yl) if self.world > 1 else yl
+        return last
+
+    def capture(self):
+        torch = self.torch
+        c0 = self.t4.launch_count()
+        self.step_eager()
+        self.launches_per_step = self.t4.launch_count() - c0
+        torch.cuda.synchronize()
+        try:
+            g = torch.cuda.CUDAGraph()
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                with torch.cuda.graph(g, stream=s):
+                    self.step_eager()
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+            self.graph = g
+        except Exception as e:  # noqa: BLE001  (NCCL capture can be refused; eager is still correct)
+            print(f"[bench] CUDA graph capture failed ({type(e).__name__}: {e}); running eager", file=sys.stderr)
+            self.graph = None
+            torch.cuda.synchronize()
+
+    def step(self):
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self.step_eager()
+
+
+def timed_steps(torch, dist, chain, steps, warmup, world):
+    """W untimed steps, then exactly K steps between barrier + synchronize, CUDA events, max over ranks."""
+    for _ in range(warmup):
+        chain.step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        chain.step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        dist.barrier()
+    return ms / steps
+
+
+def kernel_leg(t4, torch, chain, steps, kernel, M):
+    """Per-launch CUDA events around the main kernel over an eager pass of the same steps (roofline leg)."""
+    n_launch = len(chain.weights) * steps
+    t4.profile_begin(n_launch)
+    for _ in range(steps):
+        for w in chain.weights:
+            w.local(chain.x[w.K], out=chain.y_local[w.N], workspace=chain.ws)
+    main_ms, pre_ms, n = t4.profile_end(kernel)
+    return main_ms, pre_ms, n
+
+
+def e2e_leg(t4, torch, chain, steps, M):
+    """Same chain through the host-buffer C-ABI entry (tcq4_b200_mul_mat_host): per matmul an H2D copy of x
+    from pinned memory, the MUL_MAT, a D2H copy of y into pinned memory, stream sync."""
+    xh = {K: v.cpu().pin_memory() for K, v in chain.x.items()}
+    yh = {N: torch.empty((M, v.shape[1]), dtype=torch.float32).pin_memory() for N, v in chain.y_local.items()}
+    h2d = sum(4 * M * w.K for w in chain.weights)
+    d2h = sum(4 * M * w.n_local for w in chain.weights)
+
+    def one():
+        for w in chain.weights:
+            t4.mul_mat_host(w.tiles, xh[w.K], yh[w.N], w.n_local)
+    one()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    torch.cuda.synchronize()
+    return (time.perf_counter() - t0) / steps, h2d, d2h
+
+
+def run_own_arm(args):
+    import torch
+    import __graft_entry__ as graft
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- this path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    t4 = graft.load_package()
+    peaks = load_peaks()
+    M = PREFILL_M
+
+    # ---- prefill chain (the headline step) -------------------------------------------------------------
+    pre = Chain(t4, torch, M, world, rank)
+    pre.capture()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms_step = timed_steps(torch, dist, pre, args.steps, args.warmup, world)
+    # ---- decode chain (batch 1) over the same weights, timed in the same clock-sampled window --------------
+    dec = Chain(t4, torch, 1, world, rank, weights=pre.weights)
+    dec.capture()
+    dec_steps = max(args.steps, 20)
+    ms_dec = timed_steps(torch, dist, dec, dec_steps, max(args.warmup, 3), world)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- per-kernel roofline legs (N-shard-local kernels; events on the launching stream) ----------------
+    gm_ms, act_ms, gm_n = kernel_leg(t4, torch, pre, args.steps, t4.KERNEL_GEMM, M)
+    gv_ms, _, gv_n = kernel_leg(t4, torch, dec, min(dec_steps, 10), t4.KERNEL_GEMV, 1)
+    ops_local = sum(2 * M * w.n_local * w.K for w in pre.weights)                 # per step, this rank
+    bytes_local_dec = sum(alg_bytes(1, w.n_local, w.K) for w in dec.weights)
+    i8_peak = 2.0 * peaks["bf16_tflops"]          # dense int8 = 2 x dense bf16 on the same tensor pipe
+    try:
+        umma_i8, _ = t4.measure_umma(0, 256, 0, 4000)    # bare tcgen05.mma kind::i8 128x256x32 issue loop, all SMs
+    except Exception:  # noqa: BLE001
+        umma_i8 = None
+    gm_tops = ops_local * (gm_n / max(1, len(pre.weights))) / (gm_ms * 1e-3) / 1e12 if gm_n else 0.0
+    gv_gbs = bytes_local_dec * (gv_n / max(1, len(dec.weights))) / (gv_ms * 1e-3) / 1e9 if gv_n else 0.0
+
+    # ---- end to end through the host-buffer C-ABI call ---------------------------------------------------
+    e2e_s, h2d, d2h = e2e_leg(t4, torch, pre, max(1, min(args.steps, 2)), M)
+    if world > 1:
+        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+
+    if rank == 0:
+        total_ops = QWEN3_4B_LAYERS * layer_ops(M)
+        total_dec_bytes = QWEN3_4B_LAYERS * sum(alg_bytes(1, N, K) for _, N, K in QWEN3_4B_LAYER)
+        line = {
+            "metric": METRIC, "value": M / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "s8", "data": "synthetic",
+            "config": {"workload": "Qwen3-4B TCQ4_K32 252 linear matmuls, 512-token prefill (BASELINE.json configs[1])",
+                       "M": M, "layers": QWEN3_4B_LAYERS, "matmuls_per_layer": len(QWEN3_4B_LAYER),
+                       "weight_bytes_per_gpu": pre.weight_bytes(), "parallelism": f"N-shard x{world} + fp32 all-gather",
+                       "l2": "252 distinct weight buffers (2.1 GB total) >> 126 MB L2; activations stay L2-resident",
+                       "cuda_graph": pre.graph is not None},
+            "tops": total_ops / (ms_step * 1e-3) / 1e12,
+            "decode": {"value": 1.0 / (ms_dec * 1e-3), "unit": UNIT, "ms_per_step": ms_dec, "steps": dec_steps,
+                       "gbs": total_dec_bytes / (ms_dec * 1e-3) / 1e9, "frac_hbm": total_dec_bytes / (ms_dec * 1e-3) / 1e9
+                       / (peaks["hbm_gbs"] * world), "cuda_graph": dec.graph is not None},
+            "roofline": {"bound": "tensor", "kernel": "tcq4_gemm_kernel (tcgen05.mma kind::i8)", "achieved": gm_tops,
+                         "peak": i8_peak, "unit": "TOP/s", "frac": gm_tops / i8_peak, "traffic": None,
+                         "peak_source": f"2 x bf16_tflops of MEASURED_PEAKS.json ({peaks['source']}, burst)",
+                         "peak_umma_i8_measured": umma_i8, "frac_of_umma_i8": (gm_tops / umma_i8) if umma_i8 else None,
+                         "ops": "useful 2*M*N*K per launch; the tensor pipe executes 2x that (exact hi/lo split)",
+                         "launches": gm_n, "avg_launch_us": gm_ms * 1e3 / max(1, gm_n),
+                         "act_kernel_avg_us": act_ms * 1e3 / max(1, gm_n),
+                         "timed": "per-launch CUDA events, eager pass of the same steps after the timed region"},
+            "roofline_decode": {"bound": "hbm", "kernel": "tcq4_gemv_kernel", "achieved": gv_gbs, "peak": peaks["hbm_gbs"],
+                                "unit": "GB/s", "frac": gv_gbs / peaks["hbm_gbs"], "traffic": None, "launches": gv_n,
+                                "avg_launch_us": gv_ms * 1e3 / max(1, gv_n), "peak_source": f"hbm_gbs ({peaks['source']})"},
+            "e2e": {"value": M / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_s * 1e3, "api": "tcq4_b200_mul_mat_host per matmul (pinned host x and y)"},
+            "gpu_launches": int(pre.launches_per_step * args.steps),
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                line["cpu_baseline"] = cpu_baseline_leg()
+            except Exception as e:  # noqa: BLE001
+                line["cpu_baseline"] = {"error": f"{type(e).__name__}: {e}"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_own_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -163,6 +163,15 @@ TCQ4_B200_API int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq
 TCQ4_B200_API int tcq4_b200_measure_umma(int kind, int N, int swizzle, int iters, double *tops_out,
                                          double *cycles_per_mma_out);
 
+/* Per-launch timing tap for the roofline leg of bench.py (no reference counterpart; the fork's
+ * ggml_cuda_rrs_benchmark, rrs.cu:350-419, times with CUDA events the same way): between begin and
+ * end every tcq4_b200_mul_mat* call records CUDA events on its stream around the activation kernel and
+ * around the main kernel.  end() synchronises the device and returns, for launches whose main kernel
+ * was `kernel` (TCQ4_KERNEL_AUTO = all), the summed main-kernel and activation-kernel milliseconds.
+ * Not thread-safe, not usable under stream capture. */
+TCQ4_B200_API int tcq4_b200_profile_begin(int max_launches);
+TCQ4_B200_API int tcq4_b200_profile_end(int kernel, double *main_ms_sum, double *pre_ms_sum, int *launches);
+
 /* Launch statistics since load (kernels launched by this library), for bench.py's gpu_launches. */
 TCQ4_B200_API uint64_t tcq4_b200_launch_count(void);
 

@@ -40,6 +40,7 @@ EXPORTS = [
     "ggml_backend_cuda_tcq4_set_reorder_enabled", "tcq4_b200_get_perm", "tcq4_b200_has_perm",
     "tcq4_b200_get_reorder_enabled", "tcq4_b200_shard_range", "tcq4_b200_ggml_supports_op",
     "tcq4_b200_ggml_mul_mat", "tcq4_b200_launch_count", "tcq4_b200_measure_umma",
+    "tcq4_b200_profile_begin", "tcq4_b200_profile_end",
 ]
 
 
@@ -89,6 +90,8 @@ def _load() -> C.CDLL:
     lib.tcq4_b200_ggml_mul_mat.argtypes = [C.POINTER(TensorView)] * 3 + [vp, sz, vp]
     lib.tcq4_b200_launch_count.restype = C.c_uint64
     lib.tcq4_b200_measure_umma.argtypes = [ci, ci, ci, ci, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.tcq4_b200_profile_begin.argtypes = [ci]
+    lib.tcq4_b200_profile_end.argtypes = [ci, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(ci)]
     return lib
 
 
@@ -113,6 +116,17 @@ def measure_umma(kind: int, N: int = 256, swizzle: int = 0, iters: int = 2000):
     tops, cyc = C.c_double(), C.c_double()
     _check(LIB.tcq4_b200_measure_umma(kind, N, swizzle, iters, C.byref(tops), C.byref(cyc)))
     return tops.value, cyc.value
+
+
+def profile_begin(max_launches: int) -> None:
+    _check(LIB.tcq4_b200_profile_begin(max_launches))
+
+
+def profile_end(kernel: int = KERNEL_AUTO):
+    """(main-kernel ms summed, activation-kernel ms summed, launches) since profile_begin."""
+    a, b, n = C.c_double(), C.c_double(), C.c_int()
+    _check(LIB.tcq4_b200_profile_end(kernel, C.byref(a), C.byref(b), C.byref(n)))
+    return a.value, b.value, n.value
 
 
 def supports(M: int, N: int, K: int, cc: int = 100) -> bool:

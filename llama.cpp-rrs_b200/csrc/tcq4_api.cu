@@ -32,6 +32,17 @@ int cuda_fail(cudaError_t e, const char *what) {
     return TCQ4_ERR_CUDA;
 }
 
+// ---- per-launch timing tap (bench.py's roofline leg): CUDA events around every launch of the main
+// kernel (GEMV or GEMM) and around the activation kernel, on the launching stream.  Diagnostic only:
+// single-threaded use, never active during stream capture.
+struct ProfState {
+    bool   on = false;
+    int    cap = 0, n = 0;
+    cudaEvent_t *ev = nullptr;      // 3 per launch: before act, before main, after main
+    int   *kind = nullptr;          // TCQ4_KERNEL_GEMV / TCQ4_KERNEL_GEMM
+};
+ProfState g_prof;
+
 constexpr int MAX_DEV = 16;
 struct DevInfo {
     bool   ready = false;
@@ -171,9 +182,18 @@ int run_mul_mat(const void *w, const float *x, float *y, int64_t M, int64_t N, i
             set_err("internal: GEMV partial buffer bound too small");
             return TCQ4_ERR_WORKSPACE;
         }
+        const bool prof = g_prof.on && g_prof.n < g_prof.cap;
+        if (prof) {
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
+        }
         cudaError_t e = tcq4::launch_gemv(w, x, perm, y, M, N, K, gv, reinterpret_cast<float *>(wsb + L.partial_off),
                                           reinterpret_cast<int *>(wsb + L.ticket_off), dbg_isum, stream);
         if (e != cudaSuccess) return cuda_fail(e, "gemv launch");
+        if (prof) {
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
+            g_prof.kind[g_prof.n++] = TCQ4_KERNEL_GEMV;
+        }
         g_launches.fetch_add(1, std::memory_order_relaxed);
         return TCQ4_OK;
     }
@@ -190,10 +210,17 @@ int run_mul_mat(const void *w, const float *x, float *y, int64_t M, int64_t N, i
     st.codes = reinterpret_cast<int8_t *>(wsb + L.codes_off);
     st.a7 = reinterpret_cast<float *>(wsb + L.a7_off);
     st.sumq = reinterpret_cast<int16_t *>(wsb + L.sumq_off);
+    const bool prof = g_prof.on && g_prof.n < g_prof.cap;
+    if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
     cudaError_t e = tcq4::launch_act_quant_stage(x, perm, M, K, st, d->num_sms, stream);
     if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
+    if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
     e = tcq4::launch_gemm(w, st, y, M, N, K, gm, dbg_isum, stream);
     if (e != cudaSuccess) return cuda_fail(e, "gemm launch");
+    if (prof) {
+        cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
+        g_prof.kind[g_prof.n++] = TCQ4_KERNEL_GEMM;
+    }
     g_launches.fetch_add(2, std::memory_order_relaxed);
     return TCQ4_OK;
 }
@@ -362,6 +389,51 @@ int tcq4_b200_fwht_quantize_tc(const float *x, void *y_blocks, const int32_t *d_
     cudaError_t e = tcq4::launch_act_quant_ref(x, d_perm, M, K, y_blocks, d->num_sms, stream);
     if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
     g_launches.fetch_add(1, std::memory_order_relaxed);
+    return TCQ4_OK;
+}
+
+int tcq4_b200_profile_begin(int max_launches) {
+    if (max_launches < 1 || max_launches > (1 << 20)) {
+        set_err("profile_begin: max_launches out of range");
+        return TCQ4_ERR_ARG;
+    }
+    int status;
+    if (!current_device(&status)) return status;
+    if (g_prof.cap < max_launches) {
+        for (int i = 0; i < 3 * g_prof.cap; i++) cudaEventDestroy(g_prof.ev[i]);
+        delete[] g_prof.ev;
+        delete[] g_prof.kind;
+        g_prof.ev = new cudaEvent_t[3 * (size_t)max_launches];
+        g_prof.kind = new int[max_launches];
+        for (int i = 0; i < 3 * max_launches; i++) {
+            cudaError_t e = cudaEventCreate(&g_prof.ev[i]);
+            if (e != cudaSuccess) return cuda_fail(e, "profile event create");
+        }
+        g_prof.cap = max_launches;
+    }
+    g_prof.n = 0;
+    g_prof.on = true;
+    return TCQ4_OK;
+}
+
+int tcq4_b200_profile_end(int kernel, double *main_ms_sum, double *pre_ms_sum, int *launches) {
+    g_prof.on = false;
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) return cuda_fail(e, "profile sync");
+    double a = 0.0, b = 0.0;
+    int n = 0;
+    for (int i = 0; i < g_prof.n; i++) {
+        if (kernel != TCQ4_KERNEL_AUTO && g_prof.kind[i] != kernel) continue;
+        float pre = 0.0f, mn = 0.0f;
+        cudaEventElapsedTime(&pre, g_prof.ev[3 * i + 0], g_prof.ev[3 * i + 1]);
+        cudaEventElapsedTime(&mn, g_prof.ev[3 * i + 1], g_prof.ev[3 * i + 2]);
+        a += mn;
+        b += pre;
+        n++;
+    }
+    if (main_ms_sum) *main_ms_sum = a;
+    if (pre_ms_sum) *pre_ms_sum = b;
+    if (launches) *launches = n;
     return TCQ4_OK;
 }
 

@@ -261,6 +261,8 @@ tcq4_gemm_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict__
             mbar_wait(&accfull[as], (uint32_t)(u & 1));
             tc_fence_after();
             const float *sn = sSn + ring * GM_BN + colhalf * 64;
+            const int *zfl = sZflag + ring * GM_SN_WARPS;
+            const int anyz = zfl[0] | zfl[1] | zfl[2] | zfl[3];
             const uint32_t t_hi = tmem + ((uint32_t)(quarter * 32) << 16) + as * 256 + colhalf * 64;
             const uint32_t t_lo = t_hi + GM_BN;
 #pragma unroll
@@ -268,14 +270,16 @@ tcq4_gemm_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict__
                 uint32_t rh[8], rl[8];
                 tmem_ld_32x8(t_hi + ch * 8, rh);
                 tmem_ld_32x8(t_lo + ch * 8, rl);
+                // S[] of this k-tile is read BEFORE the stage is handed back: accempty(kt) is what lets
+                // MMA(kt+2) -> empty -> TMA(kt+4) -> the unpack warps overwrite ring slot (kt+4)&3 == kt&3.
+                const float4 s0 = *reinterpret_cast<const float4 *>(sn + ch * 8);
+                const float4 s1 = *reinterpret_cast<const float4 *>(sn + ch * 8 + 4);
                 tmem_ld_wait();
-                if (ch == 7) {               // all TMEM reads of this stage are done: hand it back
+                if (ch == 7) {               // all TMEM and ring reads of this stage are done: hand it back
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&accempty[as]);
                 }
-                const float4 s0 = *reinterpret_cast<const float4 *>(sn + ch * 8);
-                const float4 s1 = *reinterpret_cast<const float4 *>(sn + ch * 8 + 4);
                 const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
 #pragma unroll
                 for (int i = 0; i < 8; i++) {
@@ -288,8 +292,7 @@ tcq4_gemm_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict__
                     }
                 }
             }
-            const int *zfl = sZflag + ring * GM_SN_WARPS;
-            if ((zfl[0] | zfl[1] | zfl[2] | zfl[3]) && mvalid) {
+            if (anyz && mvalid) {
 #pragma unroll
                 for (int i = 0; i < 64; i++) {
                     const int n = n_base + i;

@@ -261,3 +261,86 @@ class RefCPU:
         y[:] = x
         self.lib.ggml_fwht_impl(_ptr(y, _f32p), n)
         return y.copy()
+
+
+class RefBaseline:
+    """bench.py's CPU baseline: the reference's CPU-side TCQ4 path timed step by step --
+    dequantize_row_tcq4_tile -> F32 Hadamard-domain weights, ggml_fwht_impl on (permuted) activations,
+    ggml CPU backend F32 MUL_MAT -- all from oracle/_ref (the reference's own code).  Falls back to
+    the scalar port (Oracle.mul_mat_f32) when oracle/_ref is absent; `kind` says which."""
+
+    def __init__(self, threads: int | None = None):
+        self.threads = int(threads or len(os.sched_getaffinity(0)))
+        self.kind = "port"
+        self.ref = None
+        self.drv = None
+        so = os.path.join(HERE, "_ref", "libref_baseline.so")
+        try:
+            build_ref()
+            self.ref = RefCPU()
+            self.drv = C.CDLL(so)
+            self.drv.refbase_mul_mat_f32.argtypes = [_f32p, _f32p, _f32p, C.c_int64, C.c_int64, C.c_int64, C.c_int]
+            self.kind = "reference"
+        except Exception:  # noqa: BLE001
+            self.orc = Oracle()
+
+    # -- step (2): tiles -> F32 [N][K], threaded over tile ranges (ctypes releases the GIL) ----------
+    def dequant(self, tiles: np.ndarray, N: int, K: int) -> np.ndarray:
+        from concurrent.futures import ThreadPoolExecutor
+        tiles = np.ascontiguousarray(tiles, dtype=np.uint8)
+        nt = tiles.size // TILE_BYTES
+        flat = np.empty(nt * 2048, dtype=np.float32)
+        nchunk = min(self.threads, max(1, nt // 64))
+        bounds = np.linspace(0, nt, nchunk + 1).astype(np.int64)
+
+        def work(i):
+            a, b = int(bounds[i]), int(bounds[i + 1])
+            if b > a:
+                self.ref.lib.dequantize_row_tcq4_tile(tiles.ctypes.data + a * TILE_BYTES,
+                                                      _ptr(flat[a * 2048:b * 2048], _f32p), (b - a) * 256)
+        with ThreadPoolExecutor(self.threads) as ex:
+            list(ex.map(work, range(nchunk)))
+        y = flat.reshape(N // 8, K // 256, 8, 256)
+        return np.ascontiguousarray(y.transpose(0, 2, 1, 3)).reshape(N, K)
+
+    # -- step (3): x -> FWHT256(perm(x)) on 64-byte aligned rows --------------------------------------
+    def rotate(self, x: np.ndarray, perm: np.ndarray | None = None) -> np.ndarray:
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        if perm is not None:
+            x = np.ascontiguousarray(x[:, perm])
+        M, K = x.shape
+        buf = np.zeros(M * K + 16, dtype=np.float32)
+        off = (-buf.ctypes.data // 4) % 16
+        y = buf[off:off + M * K]
+        y[:] = x.reshape(-1)
+        base = y.ctypes.data
+        for b in range(M * K // 256):
+            self.ref.lib.ggml_fwht_impl(C.cast(base + b * 1024, _f32p), 256)
+        return y.reshape(M, K)
+
+    # -- step (4): ggml CPU backend F32 MUL_MAT -------------------------------------------------------
+    def matmul(self, Wf: np.ndarray, xr: np.ndarray) -> np.ndarray:
+        N, K = Wf.shape
+        M = xr.shape[0]
+        y = np.empty((M, N), dtype=np.float32)
+        rc = self.drv.refbase_mul_mat_f32(_ptr(Wf, _f32p), _ptr(np.ascontiguousarray(xr), _f32p), _ptr(y, _f32p),
+                                          M, N, K, self.threads)
+        assert rc == 0, rc
+        return y
+
+    def mul_mat(self, tiles: np.ndarray, x: np.ndarray, N: int, perm: np.ndarray | None = None):
+        """Full per-call CPU path; returns (y, {'dequant_s','fwht_s','matmul_s'})."""
+        import time
+        K = x.shape[1]
+        if self.kind != "reference":
+            t0 = time.perf_counter()
+            y = self.orc.mul_mat_f32(tiles, x, N, perm)
+            return y, {"dequant_s": 0.0, "fwht_s": 0.0, "matmul_s": time.perf_counter() - t0}
+        t0 = time.perf_counter()
+        Wf = self.dequant(tiles, N, K)
+        t1 = time.perf_counter()
+        xr = self.rotate(x, perm)
+        t2 = time.perf_counter()
+        y = self.matmul(Wf, xr)
+        t3 = time.perf_counter()
+        return y, {"dequant_s": t1 - t0, "fwht_s": t2 - t1, "matmul_s": t3 - t2}
