@@ -334,12 +334,14 @@ def run_own_arm(args):
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    torch.cuda.profiler.start()     # cudaProfilerStart: `ncu --profile-from-start off` sees only the timed regions
     ms_step = timed_steps(torch, dist, pre, args.steps, args.warmup, world)
     # ---- decode chain (batch 1) over the same weights, timed in the same clock-sampled window --------------
     dec = Chain(t4, torch, 1, world, rank, weights=pre.weights)
     dec.capture()
     dec_steps = max(args.steps, 20)
     ms_dec = timed_steps(torch, dist, dec, dec_steps, max(args.warmup, 3), world)
+    torch.cuda.profiler.stop()
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- per-kernel roofline legs (N-shard-local kernels; events on the launching stream) ----------------
