@@ -172,6 +172,14 @@ TCQ4_B200_API int tcq4_b200_measure_umma(int kind, int N, int swizzle, int iters
 TCQ4_B200_API int tcq4_b200_profile_begin(int max_launches);
 TCQ4_B200_API int tcq4_b200_profile_end(int kernel, double *main_ms_sum, double *pre_ms_sum, int *launches);
 
+/* Diagnostic: SM-wide cost (cycles per warp-instruction, 16 resident warps) of the warp-level instructions the
+ * decode kernel is built from.  kind: 0 = mma.sync.m16n8k32.s8 (legacy IMMA), 1 = dp4a, 2 = shfl, 3 = redux.add */
+TCQ4_B200_API int tcq4_b200_measure_pipe(int kind, int iters, double *cycles_per_warp_instr_per_sm);
+
+/* Diagnostic: per-CTA phase timestamps (ns) of the last GEMV launched through tcq4_b200_mul_mat_debug:
+ * out[cta][8] = {start, prefetch issued, dependency resolved, activation stage done, stream done, end}. */
+TCQ4_B200_API int tcq4_b200_debug_gemv_phases(unsigned long long *out, size_t bytes);
+
 /* Launch statistics since load (kernels launched by this library), for bench.py's gpu_launches. */
 TCQ4_B200_API uint64_t tcq4_b200_launch_count(void);
 

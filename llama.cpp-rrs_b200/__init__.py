@@ -40,7 +40,8 @@ EXPORTS = [
     "ggml_backend_cuda_tcq4_set_reorder_enabled", "tcq4_b200_get_perm", "tcq4_b200_has_perm",
     "tcq4_b200_get_reorder_enabled", "tcq4_b200_shard_range", "tcq4_b200_ggml_supports_op",
     "tcq4_b200_ggml_mul_mat", "tcq4_b200_launch_count", "tcq4_b200_measure_umma",
-    "tcq4_b200_profile_begin", "tcq4_b200_profile_end",
+    "tcq4_b200_profile_begin", "tcq4_b200_profile_end", "tcq4_b200_debug_gemv_phases",
+    "tcq4_b200_measure_pipe",
 ]
 
 
@@ -90,6 +91,8 @@ def _load() -> C.CDLL:
     lib.tcq4_b200_ggml_mul_mat.argtypes = [C.POINTER(TensorView)] * 3 + [vp, sz, vp]
     lib.tcq4_b200_launch_count.restype = C.c_uint64
     lib.tcq4_b200_measure_umma.argtypes = [ci, ci, ci, ci, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.tcq4_b200_debug_gemv_phases.argtypes = [vp, sz]
+    lib.tcq4_b200_measure_pipe.argtypes = [ci, ci, C.POINTER(C.c_double)]
     lib.tcq4_b200_profile_begin.argtypes = [ci]
     lib.tcq4_b200_profile_end.argtypes = [ci, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(ci)]
     return lib

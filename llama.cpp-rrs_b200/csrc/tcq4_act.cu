@@ -28,35 +28,41 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
     const long long warp0 = (long long)blockIdx.x * ACT_WARPS_PER_CTA + (threadIdx.x >> 5);
     const long long nwarps = (long long)gridDim.x * ACT_WARPS_PER_CTA;
 
+    __shared__ __align__(16) float scratch_all[ACT_WARPS_PER_CTA * 256];
+    float *scratch = scratch_all + (threadIdx.x >> 5) * 256;
+
     for (long long b = warp0; b < nblocks; b += nwarps) {
         const int m = (int)(b / KT);
         const int kt = (int)(b - (long long)m * KT);
         float v[8];
         rrs_load_block(x + (size_t)m * K, perm, kt, lane, v);
-        const ActQuant a = rrs_quantize_block(v, lane);
+        const ActQuantT a = rrs_quantize_block_t<true>(v, lane, scratch);
+        const uint2 e = rrs_codes_layout_a(a, lane, scratch);        // byte r = code of element lane*8 + r
+        int gs = 0;                                                  // lane g < 8 keeps the sum of group g
+#pragma unroll
+        for (int g = 0; g < 8; g++) gs = (lane == g) ? a.gsum[g] : gs;
 
         if (MODE == MODE_REF) {
             // qs[t] = q[2t] | q[2t+1] << 4  (tcq4_k32.cu:266-270): lane l owns bytes l*4 .. l*4+3
             ActBlockTC *blk = out_ref + b;
-            uint32_t w = 0;
-#pragma unroll
-            for (int r = 0; r < 8; r++) w |= (uint32_t)(a.q[r] & 0xF) << (4 * r);
+            const uint32_t lo = e.x & 0x0F0F0F0Fu, hi = e.y & 0x0F0F0F0Fu;       // nibbles of elements 0-3 / 4-7
+            const uint32_t p0 = lo | (lo >> 4);                                  // bytes 0,2: e0|e1<<4, e2|e3<<4
+            const uint32_t p1 = hi | (hi >> 4);
+            const uint32_t w = (p0 & 0xFFu) | ((p0 >> 8) & 0xFF00u) | ((p1 & 0xFFu) << 16) | ((p1 << 8) & 0xFF000000u);
             reinterpret_cast<uint32_t *>(blk->qs)[lane] = w;
             if (lane == 0) blk->smooth_scale = a.max_abs;
-            if ((lane & 3) == 0) blk->sum_q[lane >> 2] = (int16_t)a.gsum;
+            if (lane < 8) blk->sum_q[lane] = (int16_t)gs;
             if (lane < 3) reinterpret_cast<uint32_t *>(blk->pad)[lane] = 0u;
         } else {
             // s8 codes, sigma order {0,1,4,5,2,3,6,7}; lane pair (2j, 2j+1) forms 16-B K-chunk j
-            const uint32_t w0 = (uint32_t)(a.q[0] & 0xFF) | ((uint32_t)(a.q[1] & 0xFF) << 8) |
-                                ((uint32_t)(a.q[4] & 0xFF) << 16) | ((uint32_t)(a.q[5] & 0xFF) << 24);
-            const uint32_t w1 = (uint32_t)(a.q[2] & 0xFF) | ((uint32_t)(a.q[3] & 0xFF) << 8) |
-                                ((uint32_t)(a.q[6] & 0xFF) << 16) | ((uint32_t)(a.q[7] & 0xFF) << 24);
+            const uint32_t w0 = __byte_perm(e.x, e.y, 0x5410);       // e0 e1 e4 e5
+            const uint32_t w1 = __byte_perm(e.x, e.y, 0x7632);       // e2 e3 e6 e7
             const int mb = m >> 7, r = m & 127;
             int8_t *unit = st.codes + ((size_t)mb * KT + kt) * ACT_UNIT_BYTES;
             uint2 *dst = reinterpret_cast<uint2 *>(unit + (lane >> 1) * ACT_LBO + r * 16 + (lane & 1) * 8);
             *dst = make_uint2(w0, w1);
             if (lane == 0) st.a7[b] = __fdiv_rn(a.max_abs, 7.0f);
-            if ((lane & 3) == 0) st.sumq[b * 8 + (lane >> 2)] = (int16_t)a.gsum;
+            if (lane < 8) st.sumq[b * 8 + lane] = (int16_t)gs;
         }
     }
 }

@@ -126,10 +126,11 @@ WsLayout ws_layout(int64_t M, int64_t N, int64_t K) {
     L.ticket_off = 0;
     L.ticket_bytes = (size_t)tcq4::round_up(NT * 4, 256);
     L.partial_off = L.ticket_off + L.ticket_bytes;
-    const int64_t Mg = M < tcq4::GEMV_MAX_M ? M : tcq4::GEMV_MAX_M;
-    // GEMV split-K: a row of KT tiles is cut into at most KT pieces whatever the grid is
+    // GEMV split-K: a row of KT tiles is cut into at most KT CTA pieces whatever the grid is; a slot holds
+    // 8 or 16 activation rows x 8 channels
     const int64_t maxslots = KT;
-    L.partial_bytes = (size_t)tcq4::round_up(NT * maxslots * Mg * 8 * 4, 256);
+    const int64_t slot_rows = (M <= 8) ? 8 : 16;
+    L.partial_bytes = (size_t)tcq4::round_up(NT * maxslots * slot_rows * 8 * 4, 256);   // kept for every M: size is monotone in M
     L.codes_off = L.partial_off + L.partial_bytes;
     const int64_t MB = (M + 127) / 128;
     const size_t codes = (size_t)tcq4::round_up(MB * KT * (int64_t)tcq4::ACT_UNIT_BYTES, 256);
@@ -315,9 +316,11 @@ int tcq4_b200_reserve(int64_t max_M, int64_t max_N, int64_t max_K) {
     DevInfo *d = current_device(&status);
     if (!d) return status;
     size_t need = ws_layout(max_M, max_N, max_K).total;
-    // the GEMV partial region scales with min(M,4): make sure small-M calls of the same N,K fit too
-    const size_t need4 = ws_layout(max_M < 4 ? max_M : 4, max_N, max_K).total;
-    if (need4 > need) need = need4;
+    // the GEMV partial region exists only for M <= GEMV_MAX_M: make sure small-M calls of the same N,K fit too
+    for (int64_t m : {(int64_t)8, (int64_t)16}) {
+        const size_t n2 = ws_layout(max_M < m ? max_M : m, max_N, max_K).total;
+        if (n2 > need) need = n2;
+    }
     return arena_ensure(d, need, nullptr);
 }
 
@@ -390,6 +393,12 @@ int tcq4_b200_fwht_quantize_tc(const float *x, void *y_blocks, const int32_t *d_
     if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return TCQ4_OK;
+}
+
+int tcq4_b200_debug_gemv_phases(unsigned long long *out, size_t bytes) {
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = tcq4::gemv_read_prof(out, bytes);
+    return e == cudaSuccess ? TCQ4_OK : cuda_fail(e, "gemv phase read");
 }
 
 int tcq4_b200_profile_begin(int max_launches) {

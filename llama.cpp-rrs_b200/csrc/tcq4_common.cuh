@@ -287,6 +287,94 @@ __device__ __forceinline__ ActQuant rrs_quantize_block(float (&v)[8], int lane) 
     return out;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Same arithmetic, fewer warp shuffles (SHFL issues at one warp-instruction per clock per SM --
+// measured, tests/gpu_pipe_peak.py -- and the 40 shuffles of the version above are what bounds it).
+// The block enters in layout A (lane l holds i = l*8 + r): stages h = 1,2,4 in registers, h = 8,16 by
+// shuffle (lane bits 0,1).  It is then transposed through a 1 KB per-warp shared-memory scratch into
+// layout B (lane l holds i = r*32 + l, i.e. ONE element of each 32-group r), where h = 32,64,128 are
+// again in registers.  Same (j, j+h) pairs, same operand order, same stage order -> bit-identical.
+// Group sums are one REDUX each.  Output: codes in layout B.
+// ---------------------------------------------------------------------------------------------
+struct ActQuantT {
+    int   q[8];      // q[g] = code of element g*32 + lane
+    float max_abs;   // after the < 1e-10 -> 1.0 rule
+    int   gsum[8];   // sum of the 32 codes of group g (all lanes)
+};
+
+template <bool WANT_GSUM>
+__device__ __forceinline__ ActQuantT rrs_quantize_block_t(float (&v)[8], int lane, float *scratch /* 256 floats, this warp's */) {
+#pragma unroll
+    for (int h = 1; h < 8; h <<= 1) {
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+            if ((r & h) == 0) {
+                const float a = v[r], b = v[r + h];
+                v[r]     = a + b;
+                v[r + h] = a - b;
+            }
+        }
+    }
+#pragma unroll
+    for (int d = 1; d < 4; d <<= 1) {                      // h = 8, 16
+        const float sgn = (lane & d) ? -1.0f : 1.0f;       // upper lane: lower - upper = o + (-v)
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+            const float o = __shfl_xor_sync(0xffffffffu, v[r], d);
+            v[r] = __fmaf_rn(v[r], sgn, o);                // exact: v * (+-1) + o rounds once, like the add
+        }
+    }
+    __syncwarp();
+    *reinterpret_cast<float4 *>(scratch + lane * 8)     = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4 *>(scratch + lane * 8 + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < 8; r++) v[r] = scratch[r * 32 + lane];
+#pragma unroll
+    for (int h = 1; h < 8; h <<= 1) {                      // h = 32, 64, 128 on the register index
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+            if ((r & h) == 0) {
+                const float a = v[r], b = v[r + h];
+                v[r]     = a + b;
+                v[r + h] = a - b;
+            }
+        }
+    }
+    float mx = 0.0f;
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        v[r] = v[r] * (1.0f / 16.0f);
+        const float a = fabsf(v[r]);
+        mx = (r == 0) ? a : fmaxf(mx, a);
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+    if (mx < 1e-10f) mx = 1.0f;
+    const float inv = __fdiv_rn(7.0f, mx);
+    ActQuantT out;
+    out.max_abs = mx;
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        const float scaled = v[r] * inv;
+        const int q = (int)fmaxf(-7.0f, fminf(7.0f, rintf(scaled)));
+        out.q[r] = q;
+        out.gsum[r] = WANT_GSUM ? __reduce_add_sync(0xffffffffu, q) : 0;
+    }
+    return out;
+}
+
+// codes of layout B -> layout A through the same scratch: returns the s8 codes of elements lane*8 .. lane*8+7
+// (byte r of the 64-bit result = element lane*8 + r)
+__device__ __forceinline__ uint2 rrs_codes_layout_a(const ActQuantT &a, int lane, float *scratch) {
+    uint8_t *sb = reinterpret_cast<uint8_t *>(scratch);
+    __syncwarp();
+#pragma unroll
+    for (int g = 0; g < 8; g++) sb[g * 32 + lane] = (uint8_t)a.q[g];
+    __syncwarp();
+    return *reinterpret_cast<const uint2 *>(sb + lane * 8);
+}
+
 // load the 8 elements of lane `lane` of block kt of row x_row (optionally through perm)
 __device__ __forceinline__ void rrs_load_block(const float *__restrict__ x_row, const int32_t *__restrict__ perm,
                                                int kt, int lane, float (&v)[8]) {
@@ -301,6 +389,24 @@ __device__ __forceinline__ void rrs_load_block(const float *__restrict__ x_row, 
         const int4 p1 = __ldg(reinterpret_cast<const int4 *>(perm + base) + 1);
         v[0] = __ldg(x_row + p0.x); v[1] = __ldg(x_row + p0.y); v[2] = __ldg(x_row + p0.z); v[3] = __ldg(x_row + p0.w);
         v[4] = __ldg(x_row + p1.x); v[5] = __ldg(x_row + p1.y); v[6] = __ldg(x_row + p1.z); v[7] = __ldg(x_row + p1.w);
+    }
+}
+
+// same, but x through ld.global.cg (L2 only): used by kernels launched with programmatic stream
+// serialization, whose CTAs may be resident (with a warm L1) before the producer of x has finished
+__device__ __forceinline__ void rrs_load_block_cg(const float *__restrict__ x_row, const int32_t *__restrict__ perm,
+                                                  int kt, int lane, float (&v)[8]) {
+    const int base = kt * TILE_K + lane * 8;
+    if (perm == nullptr) {
+        const float4 a = __ldcg(reinterpret_cast<const float4 *>(x_row + base));
+        const float4 b = __ldcg(reinterpret_cast<const float4 *>(x_row + base) + 1);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+        v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
+        const int4 p0 = __ldg(reinterpret_cast<const int4 *>(perm + base));
+        const int4 p1 = __ldg(reinterpret_cast<const int4 *>(perm + base) + 1);
+        v[0] = __ldcg(x_row + p0.x); v[1] = __ldcg(x_row + p0.y); v[2] = __ldcg(x_row + p0.z); v[3] = __ldcg(x_row + p0.w);
+        v[4] = __ldcg(x_row + p1.x); v[5] = __ldcg(x_row + p1.y); v[6] = __ldcg(x_row + p1.z); v[7] = __ldcg(x_row + p1.w);
     }
 }
 

@@ -1,78 +1,176 @@
-// tcq4_gemv.cu -- K3: fused decode GEMV/GEMM for M <= 4 (bandwidth-bound).
+// tcq4_gemv.cu -- K3: fused decode GEMV / small-batch GEMM for M <= 16 (HBM-bandwidth bound).
 //
-// One persistent CTA per SM.  The flattened tile list [N/8][K/256] is exactly memory order
-// (/root/reference/ggml/src/ggml-quants.c:1550-1573), so it is cut into W = grid*8 contiguous byte
-// ranges, one per warp; each warp streams its range through a private ring of 1-D bulk async copies
-// (cp.async.bulk -> UBLKCP, 1184 B per tile, GV_DEPTH tiles in flight) and never synchronises with
-// another warp inside the loop.  While the first tiles are in flight the CTA runs the activation
-// stage (FWHT-256 + quantise, tcq4_common.cuh) for all M rows into shared memory -- 148x redundant
-// instead of the reference's ceil(N/32)*M x (tcq4_k32.cu:768-831), and off the critical path.
+// Replaces tcq4_rrs_fused_gemm_smallM_kernel (/root/reference/ggml/src/ggml-cuda/tcq4_k32.cu:733-889,
+// grid (ceil(N/32), M), every block redoing the activation stage and re-reading the weights per m)
+// and tcq4_rrs_fused_gemv_kernel (:296-459).
 //
-// Per tile a lane owns two 16-byte chunks = (group g, channel c) and (g+4, c): 32 nibbles each,
-// expanded to s8*16 with two logic ops per word ((w<<4)&0xF0F0F0F0, w&0xF0F0F0F0) and fed to dp4a
-// against the s8 codes (stored de-interleaved even/odd per 8-slice to match).  The fp32 epilogue
-// reproduces tcq4_k32.cu:841-883 operation for operation, including the 4,2,1 xor tree over
-// groups, so whenever one warp owns a whole output row the result is bit-identical to the oracle.
-//
-// Rows cut by a warp boundary are finished deterministically: every contributing warp writes its
-// partial to a workspace slot and takes a ticket; the last one sums the slots in k order.
+// Shape of the kernel
+//  * Persistent, one CTA of 16 warps per SM.  The flattened tile list [N/8][K/256] is exactly memory
+//    order (ggml-quants.c:1550-1573); it is cut into contiguous row ranges per cluster and each of those
+//    into 32 contiguous warp ranges.  A warp streams its range through a private ring of 1-D bulk async
+//    copies (cp.async.bulk -> UBLKCP, 1184 B per tile) and never synchronises with another warp
+//    inside the loop.
+//  * Programmatic dependent launch: barrier init and the first ring fill touch only the (constant)
+//    weights, so they run BEFORE griddepcontrol.wait, and launch_dependents is signalled right after
+//    them -- the next MUL_MAT of the stream starts prefetching its weights into the shared memory of the
+//    same SMs while this one is still computing.  x is read (ld.global.cg) only after the wait.
+//  * The block's int4 x int4 dots run on the legacy warp-level tensor path: the tile format is already
+//    the m16n8k32 B-fragment order (ggml-common.h:315-341), so lane L's 32-bit word of a group IS its B
+//    fragment; two logic ops turn it into two s8x4 registers carrying 16*q, and one
+//    mma.sync.m16n8k32.s8.s8 per 32-group multiplies 8 channels by up to 16 activation rows at once.
+//    M <= 8 and M <= 16 therefore cost the same weight traffic and nearly the same instructions as M = 1.
+//  * Per-group scale codes enter in the integer domain: the eight per-group dots of a channel fit s16,
+//    so four PRMT + four IDP.2A form isum = sum_g sc_g * dot_g exactly (the same int32 the tcgen05 GEMM
+//    accumulates in TMEM), and the fp32 step per (row, channel, k-tile) is the GEMM's:
+//    acc = fma(float(isum) * (a7/127), S, acc).
+//  * CTAs run as clusters of two (one TPC).  A cluster owns whole output rows (n-tiles), so no row is ever
+//    cut by a cluster boundary and the kernel needs no global atomics, tickets or fences at its tail; the
+//    cluster's tiles are split evenly over its 32 warps, and rows cut by a warp boundary are combined
+//    deterministically (k order) in CTA 0's shared memory -- CTA 1 stores its partials there through DSMEM --
+//    after one cluster barrier.
+#include <cstdlib>
+
 #include "tcq4_common.cuh"
 #include "tcq4_kernels.h"
 
 namespace tcq4 {
 
-constexpr int GV_WARPS = 8;
-constexpr int GV_DEPTH = 8;
+constexpr int GV_WARPS = 16;
+constexpr int GV_DEPTH = 4;
 constexpr int GV_THREADS = GV_WARPS * 32;
+constexpr int GV_CLUSTER = 2;
+constexpr int GV_WORKERS = GV_WARPS * GV_CLUSTER;     // warps of a cluster
+constexpr int GV_ENTRIES = GV_WORKERS * 2;            // partial-row slots (a warp cuts at most two rows)
 
-struct GvSplit {
-    long long T, W, base, rem;
-    __host__ __device__ long long start(long long gw) const { return gw * base + (gw < rem ? gw : rem); }
-    __host__ __device__ long long count(long long gw) const { return base + (gw < rem ? 1 : 0); }
-    __host__ __device__ long long owner(long long t) const {
-        const long long cut = rem * (base + 1);
-        if (t < cut) return t / (base + 1);
-        return rem + (t - cut) / base;     // base >= 1 here: t >= cut can only happen when base > 0
+struct GvSplit {    // even split of T items over W workers, contiguous
+    int base, rem;
+    __host__ __device__ GvSplit(int T, int W) : base(T / W), rem(T % W) {}
+    __host__ __device__ int start(int w) const { return w * base + (w < rem ? w : rem); }
+    __host__ __device__ int count(int w) const { return base + (w < rem ? 1 : 0); }
+};
+
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// address of `p` (this CTA's shared memory) in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t dsmem_addr(const void *p, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void dsmem_st_f2(uint32_t addr, float a, float b) {
+    asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
+}
+__device__ __forceinline__ void dsmem_st_f(uint32_t addr, float a) {
+    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(a) : "memory");
+}
+__device__ __forceinline__ void dsmem_st_i(uint32_t addr, int v) {
+    asm volatile("st.shared::cluster.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+// D(16x8, s32) = A(16x32, s8, row) * B(32x8, s8, col); rows 8..15 of A are a1/a3
+__device__ __forceinline__ void mma_s8(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                       uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+        : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0));
+}
+
+// shared-memory carve-up (bytes), shared by the kernel and the planner
+struct GvSmem {
+    int off_ring, off_full, off_afrag, off_rm, off_sumq, off_part, off_prow, off_scratch, total;
+    __host__ __device__ static int al(int o) { return (o + 15) & ~15; }
+    __host__ __device__ GvSmem(int M, int KT) {
+        int o = 0;
+        off_ring = o;    o = al(o + GV_WARPS * GV_DEPTH * TILE_BYTES);   // 75776
+        off_full = o;    o = al(o + GV_WARPS * GV_DEPTH * 8);
+        off_afrag = o;   o = al(o + M * KT * 256);                       // [KT][8 groups][M][4 k-quarters] uint2 = M*K bytes
+        off_rm = o;      o = al(o + 2 * M * KT * 4);                     // [KT][M] a7/127, then [KT][M] a7
+        off_sumq = o;    o = al(o + M * KT * 8 * 4);                     // [M][KT][8] group sums (zero-point path)
+        off_part = o;    o = al(o + GV_ENTRIES * M * 32);                // [entry][M rows][8 ch] fp32 (used in CTA 0)
+        off_prow = o;    o = al(o + GV_ENTRIES * 4);                     // [entry] n-tile or -1
+        off_scratch = o; o = al(o + GV_WARPS * 1024);                    // FWHT transposition scratch, 1 KB per warp
+        total = o;
     }
 };
 
-template <int MR, bool DEBUG>
-__global__ void __launch_bounds__(GV_THREADS, 1)
+// phase timestamps (ns, %globaltimer) of the DEBUG instantiation: [cta][0..5] = start, prefetch issued,
+// dependency resolved, activation stage done, stream loop done, end
+__device__ unsigned long long g_gv_prof[160][8];
+__device__ unsigned long long g_gv_iter[GV_WARPS][8][3];     // CTA 0: per warp, per tile: wait begin / data ready / done
+__device__ __forceinline__ unsigned long long gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define GV_ITER(i, k) do { if (DEBUG && blockIdx.x == 0 && lane == 0 && (i) < 8) g_gv_iter[warp][i][k] = gtime(); } while (0)
+#define GV_STAMP(i) do { if (DEBUG && threadIdx.x == 0 && blockIdx.x < 160) g_gv_prof[blockIdx.x][i] = gtime(); } while (0)
+
+// Zero-point term of one (row, channel, k-tile) (tcq4_k32.cu:850,872-873).  Cold: the fork's quantiser always
+// writes Z = 0 (ggml-quants.c:1603).
+__device__ __noinline__ float gv_zero_point(unsigned short zh, uint2 zcv, const int *sumq8, float a7) {
+    const float Z = __half2float(__ushort_as_half(zh));
+    const uint32_t zc[2] = {zcv.x, zcv.y};
+    float zs = 0.0f;
+    for (int g = 0; g < 8; g++) {
+        const float sq = (float)sumq8[g] * a7;
+        const int cg = (int)(int8_t)(zc[g >> 2] >> (8 * (g & 3)));
+        zs += sq * __fdiv_rn(Z * (float)cg, 127.0f);
+    }
+    return zs;
+}
+
+template <int MB, bool DEBUG>
+__global__ void __launch_bounds__(GV_THREADS, MB == 1 ? 2 : 1)
 tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, const int32_t *__restrict__ perm,
-                 float *__restrict__ y, int N, int K, float *__restrict__ ws_partial, int *__restrict__ ws_ticket,
-                 int maxslots, int32_t *__restrict__ dbg_isum) {
+                 float *__restrict__ y, int M, int N, int K, int32_t *__restrict__ dbg_isum) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int KT = K / TILE_K;
     const int NT = N / TILE_CH;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = lane & 3, r = lane >> 2;          // mma fragment coordinates: k-quarter / row (token) or column pair
 
-    // smem carve-up
-    uint8_t *ring = smem;                                                  // [GV_WARPS][GV_DEPTH][1184]
-    uint64_t *full = reinterpret_cast<uint64_t *>(ring + GV_WARPS * GV_DEPTH * TILE_BYTES);
-    uint32_t *codes = reinterpret_cast<uint32_t *>(full + GV_WARPS * GV_DEPTH);   // [MR][K] bytes
-    float *a7s = reinterpret_cast<float *>(reinterpret_cast<uint8_t *>(codes) + (size_t)MR * K);   // [MR][KT]
-    int *sumq = reinterpret_cast<int *>(a7s + MR * KT);                    // [MR][KT][8]
+    const GvSmem L(M, KT);
+    uint8_t *ring = smem + L.off_ring;
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem + L.off_full);
+    uint2 *afrag = reinterpret_cast<uint2 *>(smem + L.off_afrag);      // [KT][8][M][4]
+    float *rms = reinterpret_cast<float *>(smem + L.off_rm);           // [KT][M]   a7 / 127
+    float *a7s = rms + M * KT;                                         // [KT][M]   max_abs / 7
+    int *sumq = reinterpret_cast<int *>(smem + L.off_sumq);            // [M][KT][8]
+    float *part = reinterpret_cast<float *>(smem + L.off_part);        // [entry][M][8]   (CTA 0's copy is the live one)
+    int *prow = reinterpret_cast<int *>(smem + L.off_prow);            // [entry] n-tile or -1
 
-    GvSplit sp;
-    sp.T = (long long)NT * KT;
-    sp.W = (long long)gridDim.x * GV_WARPS;
-    sp.base = sp.T / sp.W;
-    sp.rem = sp.T % sp.W;
-    const long long gw = (long long)blockIdx.x * GV_WARPS + warp;
-    const long long t0 = sp.start(gw);
-    const int cnt = (int)sp.count(gw);
+    // ---- work split: whole rows per cluster, tiles evenly over the cluster's 32 warps ------------------
+    const int crank = (int)cluster_ctarank();
+    const int cid = blockIdx.x / GV_CLUSTER, ncl = gridDim.x / GV_CLUSTER;
+    const GvSplit rs(NT, ncl);
+    const int R0 = rs.start(cid), nR = rs.count(cid);
+    const int wid = crank * GV_WARPS + warp;
+    const GvSplit wsp(nR * KT, GV_WORKERS);
+    const int lt0 = wsp.start(wid), cnt = wsp.count(wid);
 
-    if (threadIdx.x == 0) {
-        for (int i = 0; i < GV_WARPS * GV_DEPTH; i++) mbar_init(&full[i], 1);
-        fence_mbar_init();
-    }
-    __syncthreads();
+    GV_STAMP(0);
+    if (threadIdx.x < GV_ENTRIES) prow[threadIdx.x] = -1;
 
+    // ---- weight prefetch: constant data, legal before the programmatic dependency resolves -----------
+    // Each warp owns its ring and its barriers: lane 0 initialises them and issues the first copies without
+    // any CTA-wide barrier (the other lanes first touch them after the __syncthreads below).
     uint8_t *myring = ring + warp * GV_DEPTH * TILE_BYTES;
     uint64_t *myfull = full + warp * GV_DEPTH;
-    const uint8_t *wsrc = w + (size_t)t0 * TILE_BYTES;
+    const uint8_t *wsrc = w + ((size_t)R0 * KT + lt0) * TILE_BYTES;
     uint64_t pol = 0;
     if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < GV_DEPTH; i++) mbar_init(&myfull[i], 1);
+        fence_mbar_init();
         pol = l2_policy_evict_first();
         const int pre = cnt < GV_DEPTH ? cnt : GV_DEPTH;
         for (int i = 0; i < pre; i++) {
@@ -80,225 +178,272 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
             bulk_g2s_stream(myring + i * TILE_BYTES, wsrc + (size_t)i * TILE_BYTES, TILE_BYTES, &myfull[i], pol);
         }
     }
+    __syncwarp();
+    // first half of a cluster barrier: "my prow[] is initialised" (the peer waits before its first remote store)
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    GV_STAMP(1);
+    pdl_launch_dependents();     // the next MUL_MAT may start its own prefetch on this SM
+    pdl_wait();                  // x belongs to the previous kernel until here
+    GV_STAMP(2);
 
-    // activation stage for all MR rows (weights are already in flight)
-    for (int b = warp; b < MR * KT; b += GV_WARPS) {
+    // ---- activation stage for all M rows -----------------------------------------------------------------
+    // (latency-bound here -- at most a few 256-blocks per warp -- so the all-shuffle butterfly, whose dependent
+    //  chain is shorter than the shared-memory transposition of K1, is the faster one)
+    for (int b = warp; b < M * KT; b += GV_WARPS) {
         const int m = b / KT, kt = b - m * KT;
         float v[8];
-        rrs_load_block(x + (size_t)m * K, perm, kt, lane, v);
-        const ActQuant a = rrs_quantize_block(v, lane);
+        rrs_load_block_cg(x + (size_t)m * K, perm, kt, lane, v);
+        const ActQuant a = rrs_quantize_block(v, lane);                // lane = (group r, k-quarter q), elements lane*8..+7
         const uint32_t ev = (uint32_t)(a.q[0] & 0xFF) | ((uint32_t)(a.q[2] & 0xFF) << 8) |
                             ((uint32_t)(a.q[4] & 0xFF) << 16) | ((uint32_t)(a.q[6] & 0xFF) << 24);
         const uint32_t od = (uint32_t)(a.q[1] & 0xFF) | ((uint32_t)(a.q[3] & 0xFF) << 8) |
                             ((uint32_t)(a.q[5] & 0xFF) << 16) | ((uint32_t)(a.q[7] & 0xFF) << 24);
-        reinterpret_cast<uint2 *>(codes)[((size_t)m * K + kt * TILE_K) / 8 + lane] = make_uint2(ev, od);
-        if (lane == 0) a7s[b] = __fdiv_rn(a.max_abs, 7.0f);
-        if ((lane & 3) == 0) sumq[b * 8 + (lane >> 2)] = a.gsum;
+        afrag[((kt * 8 + r) * M + m) * 4 + q] = make_uint2(ev, od);
+        if (lane == 0) {
+            const float a7 = __fdiv_rn(a.max_abs, 7.0f);
+            a7s[kt * M + m] = a7;
+            rms[kt * M + m] = a7 * (1.0f / 127.0f);
+        }
+        if (q == 0) sumq[(m * KT + kt) * 8 + r] = a.gsum;
     }
     __syncthreads();
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    GV_STAMP(3);
 
-    const int c = lane & 7;
-    const int g0 = lane >> 3, g1 = g0 + 4;
-    float acc[MR];
+    // Fragment roles (mma.m16n8k32, PTX ISA "Matrix Fragments for mma.m16n8k32"): A (16 x 32, row) = the tile's
+    // 8 channels in rows 0..7 -- lane (c = lane/4, s = lane%4) holds a0 = word (c, s) even nibbles, a2 = odd nibbles,
+    // rows 8..15 (a1, a3) are zero; B (32 x 8, col) = up to 8 activation rows -- lane (n = lane/4, s) holds the codes
+    // of token n, slice s (b0 = even positions, b1 = odd).  D: lane (c, s) gets tokens 2s, 2s+1 of channel c.
+    // Lanes whose token does not exist read the last valid row instead (their D columns are never used).
+    const int c = r;                                          // channel of this lane's D fragment
+    const int tk0 = 2 * q, tk1 = 2 * q + 1;                   // tokens of this lane's D fragment (block mb adds 8)
+    const int brow0 = min(r, M - 1), brow1 = min(r + 8, M - 1);
+    float acc[MB][2];
 #pragma unroll
-    for (int m = 0; m < MR; m++) acc[m] = 0.0f;
+    for (int i = 0; i < MB; i++) acc[i][0] = acc[i][1] = 0.0f;
+    int nseg = 0;
+    int nt = R0 + lt0 / KT, kt = lt0 % KT;
+    bool from_row_start = (kt == 0);
+    const uint32_t part0 = dsmem_addr(part, 0), prow0 = dsmem_addr(prow, 0);    // CTA 0's copies
+    const uint32_t ring_u32 = smem_u32(myring), full_u32 = smem_u32(myfull);
+    const uint2 *af0 = afrag + brow0 * 4 + q;                  // + ((kt*8 + g) * M) * 4
+    const uint2 *af1 = afrag + brow1 * 4 + q;
+    const int af_g = M * 4;                                    // uint2 stride between groups
 
     for (int i = 0; i < cnt; i++) {
-        const long long t = t0 + i;
-        const int nt = (int)(t / KT);
-        const int kt = (int)(t - (long long)nt * KT);
         const int slot = i % GV_DEPTH;
+        GV_ITER(i, 0);
         mbar_wait(&myfull[slot], (uint32_t)((i / GV_DEPTH) & 1));
+        GV_ITER(i, 1);
 
         const uint8_t *tp = myring + slot * TILE_BYTES;
-        const uint4 wa = *reinterpret_cast<const uint4 *>(tp + lane * 16);
-        const uint4 wb = *reinterpret_cast<const uint4 *>(tp + 512 + lane * 16);
-        const float S = __half2float(*reinterpret_cast<const __half *>(tp + TILE_OFF_S + 2 * c));
-        const float Z = __half2float(*reinterpret_cast<const __half *>(tp + TILE_OFF_Z + 2 * c));
-        const int sc0 = *reinterpret_cast<const int8_t *>(tp + TILE_OFF_SC + c * 8 + g0);
-        const int sc1 = *reinterpret_cast<const int8_t *>(tp + TILE_OFF_SC + c * 8 + g1);
-        const int zc0 = *reinterpret_cast<const int8_t *>(tp + TILE_OFF_ZC + c * 8 + g0);
-        const int zc1 = *reinterpret_cast<const int8_t *>(tp + TILE_OFF_ZC + c * 8 + g1);
+        uint32_t wv[8];
+#pragma unroll
+        for (int g = 0; g < 8; g++) wv[g] = reinterpret_cast<const uint32_t *>(tp)[g * 32 + lane];
+        const uint2 scv = *reinterpret_cast<const uint2 *>(tp + TILE_OFF_SC + 8 * c);      // sc[c][0..7]
+        const unsigned short sh = *reinterpret_cast<const unsigned short *>(tp + TILE_OFF_S + 2 * c);
+        const unsigned short zh = *reinterpret_cast<const unsigned short *>(tp + TILE_OFF_Z + 2 * c);
+        const bool anyz = __any_sync(0xffffffffu, (zh & 0x7FFFu) != 0u);
+        uint2 zcv = make_uint2(0, 0);
+        if (anyz) zcv = *reinterpret_cast<const uint2 *>(tp + TILE_OFF_ZC + 8 * c);
         __syncwarp();
-        if (lane == 0 && i + GV_DEPTH < cnt) {     // refill the slot just drained
-            mbar_arrive_expect_tx(&myfull[slot], TILE_BYTES);
-            bulk_g2s_stream(myring + slot * TILE_BYTES, wsrc + (size_t)(i + GV_DEPTH) * TILE_BYTES, TILE_BYTES,
-                            &myfull[slot], pol);
-        }
-
-        // b_scale = S*sc/127, b_zero = Z*zc/127   (tcq4_k32.cu:849-850), IEEE divide
-        const float bs0 = __fdiv_rn(S * (float)sc0, 127.0f);
-        const float bs1 = __fdiv_rn(S * (float)sc1, 127.0f);
-        const float zp0 = Z * (float)zc0, zp1 = Z * (float)zc1;
-        const float bz0 = (zp0 == 0.0f) ? zp0 : __fdiv_rn(zp0, 127.0f);
-        const float bz1 = (zp1 == 0.0f) ? zp1 : __fdiv_rn(zp1, 127.0f);
-
-        const uint32_t wv0[4] = {wa.x, wa.y, wa.z, wa.w};
-        const uint32_t wv1[4] = {wb.x, wb.y, wb.z, wb.w};
-        uint32_t lo0[4], hi0[4], lo1[4], hi1[4];
-#pragma unroll
-        for (int s = 0; s < 4; s++) {
-            lo0[s] = (wv0[s] << 4) & 0xF0F0F0F0u;
-            hi0[s] = wv0[s] & 0xF0F0F0F0u;
-            lo1[s] = (wv1[s] << 4) & 0xF0F0F0F0u;
-            hi1[s] = wv1[s] & 0xF0F0F0F0u;
-        }
-
-#pragma unroll
-        for (int m = 0; m < MR; m++) {
-            const uint4 *ap0 = reinterpret_cast<const uint4 *>(reinterpret_cast<const uint8_t *>(codes) +
-                                                               (size_t)m * K + kt * TILE_K + g0 * 32);
-            const uint4 *ap1 = ap0 + 8;     // +128 bytes = 4 groups
-            const uint4 A0 = ap0[0], A1 = ap0[1], B0 = ap1[0], B1 = ap1[1];
-            int d0 = 0, d1 = 0;
-            d0 = __dp4a((int)lo0[0], (int)A0.x, d0); d0 = __dp4a((int)hi0[0], (int)A0.y, d0);
-            d0 = __dp4a((int)lo0[1], (int)A0.z, d0); d0 = __dp4a((int)hi0[1], (int)A0.w, d0);
-            d0 = __dp4a((int)lo0[2], (int)A1.x, d0); d0 = __dp4a((int)hi0[2], (int)A1.y, d0);
-            d0 = __dp4a((int)lo0[3], (int)A1.z, d0); d0 = __dp4a((int)hi0[3], (int)A1.w, d0);
-            d1 = __dp4a((int)lo1[0], (int)B0.x, d1); d1 = __dp4a((int)hi1[0], (int)B0.y, d1);
-            d1 = __dp4a((int)lo1[1], (int)B0.z, d1); d1 = __dp4a((int)hi1[1], (int)B0.w, d1);
-            d1 = __dp4a((int)lo1[2], (int)B1.x, d1); d1 = __dp4a((int)hi1[2], (int)B1.y, d1);
-            d1 = __dp4a((int)lo1[3], (int)B1.z, d1); d1 = __dp4a((int)hi1[3], (int)B1.w, d1);
-            d0 >>= 4;   // weights were carried as 16*q
-            d1 >>= 4;
-
-            const float a7 = a7s[m * KT + kt];
-            const float sq0 = (float)sumq[(m * KT + kt) * 8 + g0];
-            const float sq1 = (float)sumq[(m * KT + kt) * 8 + g1];
-            // contrib = (float)dot*a7*b_scale + (float)sum_a*a7*b_zero   (tcq4_k32.cu:872-873)
-            const float c0 = ((float)d0 * a7) * bs0 + (sq0 * a7) * bz0;
-            const float c1 = ((float)d1 * a7) * bs1 + (sq1 * a7) * bz1;
-            float v = c0 + c1;                                   // xor 4 : g <-> g+4
-            v += __shfl_xor_sync(0xffffffffu, v, 16);            // xor 2
-            v += __shfl_xor_sync(0xffffffffu, v, 8);             // xor 1
-            acc[m] += v;                                         // tcq4_k32.cu:881-883
-
-            if (DEBUG) {
-                int is = sc0 * d0 + sc1 * d1;
-                is += __shfl_xor_sync(0xffffffffu, is, 16);
-                is += __shfl_xor_sync(0xffffffffu, is, 8);
-                if (lane < 8 && dbg_isum) dbg_isum[((size_t)m * N + nt * 8 + c) * KT + kt] = is;
+        if (i + GV_DEPTH < cnt) {                  // refill the slot just drained (warp-uniform operands, one issuer)
+            if (elect_one()) {
+                const uint32_t bar = full_u32 + slot * 8, dst = ring_u32 + slot * TILE_BYTES;
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(TILE_BYTES) : "memory");
+                asm volatile(
+                    "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
+                        "r"(dst), "l"(wsrc + (size_t)(i + GV_DEPTH) * TILE_BYTES), "r"(TILE_BYTES), "r"(bar), "l"(pol)
+                    : "memory");
             }
         }
+
+        // one mma per 32-group (per 8 activation rows); group pairs are folded straight into
+        // isum = sum_g sc_g * dot_g (exact): the two 16*dot values (each fits s16) are packed by one PRMT and hit
+        // two scale bytes with one IDP.2A
+        int is[MB][2];
+#pragma unroll
+        for (int mb = 0; mb < MB; mb++) is[mb][0] = is[mb][1] = 0;
+        const int afk = kt * 8 * af_g;
+#pragma unroll
+        for (int gp = 0; gp < 4; gp++) {
+            int dd[MB][2][4];
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const int g = gp * 2 + h;
+                const uint32_t a0 = (wv[g] << 4) & 0xF0F0F0F0u;      // nibbles 0,2,4,6 of the word as 16*q (s8)
+                const uint32_t a2 = wv[g] & 0xF0F0F0F0u;             // nibbles 1,3,5,7
+                const uint2 b = af0[afk + g * af_g];
+                mma_s8(dd[0][h], a0, 0u, a2, 0u, b.x, b.y);
+                if (MB > 1) {
+                    const uint2 b2 = af1[afk + g * af_g];
+                    mma_s8(dd[MB - 1][h], a0, 0u, a2, 0u, b2.x, b2.y);
+                }
+            }
+            const uint32_t scw = gp < 2 ? scv.x : scv.y;
+#pragma unroll
+            for (int mb = 0; mb < MB; mb++) {
+#pragma unroll
+                for (int j = 0; j < 2; j++) {
+                    const int p = (int)__byte_perm((uint32_t)dd[mb][0][j], (uint32_t)dd[mb][1][j], 0x5410);
+                    is[mb][j] = (gp & 1) ? __dp2a_hi(p, (int)scw, is[mb][j]) : __dp2a_lo(p, (int)scw, is[mb][j]);
+                }
+            }
+        }
+        const float S = __half2float(__ushort_as_half(sh));
+#pragma unroll
+        for (int mb = 0; mb < MB; mb++) {
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                const int m = 8 * mb + tk0 + j;
+                const bool valid = m < M;
+                const int isv = is[mb][j] >> 4;                      // weights were carried as 16*q: exact
+                const float rm = valid ? rms[kt * M + m] : 0.0f;
+                acc[mb][j] = __fmaf_rn((float)isv * rm, S, acc[mb][j]);
+                if (anyz && valid) acc[mb][j] += gv_zero_point(zh, zcv, sumq + (m * KT + kt) * 8, a7s[kt * M + m]);
+                if (DEBUG && dbg_isum && valid) dbg_isum[((size_t)m * N + nt * 8 + c) * KT + kt] = isv;
+            }
+        }
+        GV_ITER(i, 2);
 
         // end of this warp's share of row nt?
-        if (kt == KT - 1 || i == cnt - 1) {
-            const long long row_first = (long long)nt * KT;
-            const bool whole = (row_first >= t0) && (row_first + KT <= t0 + cnt);
-            if (whole) {
-                if (lane < 8) {
+        const bool row_end = (kt == KT - 1);
+        if (row_end || i == cnt - 1) {
+            if (row_end && from_row_start) {            // the whole row was this warp's
 #pragma unroll
-                    for (int m = 0; m < MR; m++) y[(size_t)m * N + nt * 8 + c] = acc[m];
-                }
-            } else {
-                const long long first_owner = sp.owner(row_first);
-                const int nslots = (int)(sp.owner(row_first + KT - 1) - first_owner) + 1;
-                const int myslot = (int)(gw - first_owner);
-                float *prow = ws_partial + (size_t)nt * maxslots * (MR * 8);
-                if (lane < 8) {
+                for (int mb = 0; mb < MB; mb++)
 #pragma unroll
-                    for (int m = 0; m < MR; m++) __stcg(prow + ((size_t)myslot * MR + m) * 8 + c, acc[m]);
-                }
-                __threadfence();
-                __syncwarp();
-                int last = 0;
-                if (lane == 0) last = (atomicAdd(&ws_ticket[nt], 1) == nslots - 1);
-                last = __shfl_sync(0xffffffffu, last, 0);
-                if (last) {
-                    __threadfence();
-                    if (lane < 8) {
+                    for (int j = 0; j < 2; j++)
+                        if (8 * mb + tk0 + j < M) y[(size_t)(8 * mb + tk0 + j) * N + nt * 8 + c] = acc[mb][j];
+            } else {                                    // a cut row: park the partial in CTA 0's shared memory
+                const int e = wid * 2 + nseg;
 #pragma unroll
-                        for (int m = 0; m < MR; m++) {
-                            float s = 0.0f;
-                            for (int sl = 0; sl < nslots; sl++) s += __ldcg(prow + ((size_t)sl * MR + m) * 8 + c);
-                            y[(size_t)m * N + nt * 8 + c] = s;
-                        }
-                    }
-                    if (lane == 0) ws_ticket[nt] = 0;     // self-cleaning for the next launch
-                }
+                for (int mb = 0; mb < MB; mb++)
+#pragma unroll
+                    for (int j = 0; j < 2; j++)
+                        if (8 * mb + tk0 + j < M)
+                            dsmem_st_f(part0 + (uint32_t)(((e * M + 8 * mb + tk0 + j) * 8 + c) * 4), acc[mb][j]);
+                if (lane == 0) dsmem_st_i(prow0 + (uint32_t)(e * 4), nt);
+                nseg++;
             }
 #pragma unroll
-            for (int m = 0; m < MR; m++) acc[m] = 0.0f;
+            for (int mb = 0; mb < MB; mb++) acc[mb][0] = acc[mb][1] = 0.0f;
+        }
+        if (row_end) {
+            kt = 0;
+            nt++;
+            from_row_start = true;
+        } else {
+            kt++;
         }
     }
+    (void)tk1;
+    GV_STAMP(4);
+    cluster_sync_all();          // all partials (local and remote) have landed in CTA 0
+
+    // ---- CTA 0 combines the cut rows in k order (entry order = worker order = tile order) ----------------
+    if (crank == 0) {
+        for (int sidx = 0; sidx < GV_ENTRIES / GV_WARPS; sidx++) {
+            const int e = warp * (GV_ENTRIES / GV_WARPS) + sidx;
+            const int row = prow[e];
+            if (row < 0) continue;
+            int prev = -1;
+            for (int j = e - 1; j >= 0; j--) {
+                const int pr = prow[j];
+                if (pr >= 0) { prev = pr; break; }
+            }
+            if (prev == row) continue;                         // an earlier entry owns this row's run
+            // lane -> (token m = lane / 8 (+4 per pass), channel lane % 8): coalesced 32-byte row pieces of y
+            for (int m = lane >> 3; m < M; m += 4) {
+                float sum = 0.0f;
+                for (int j = e; j < GV_ENTRIES; j++) {
+                    const int pr = prow[j];
+                    if (pr < 0) continue;
+                    if (pr != row) break;
+                    sum += part[(size_t)(j * M + m) * 8 + (lane & 7)];
+                }
+                y[(size_t)m * N + row * 8 + (lane & 7)] = sum;
+            }
+        }
+    }
+    GV_STAMP(5);
 }
 
-static size_t gemv_smem_bytes(int64_t M, int64_t K) {
-    const int64_t KT = K / TILE_K;
-    size_t s = (size_t)GV_WARPS * GV_DEPTH * TILE_BYTES;
-    s += (size_t)GV_WARPS * GV_DEPTH * sizeof(uint64_t);
-    s += (size_t)M * K;                 // codes
-    s += (size_t)M * KT * sizeof(float);
-    s += (size_t)M * KT * 8 * sizeof(int);
-    return s;
-}
+static int gemv_mb(int64_t M) { return M <= 8 ? 1 : 2; }
 
 bool gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, GemvPlan *plan) {
     if (M < 1 || M > GEMV_MAX_M) return false;
-    const size_t smem = gemv_smem_bytes(M, K);
-    if (smem > smem_optin) return false;
     const int64_t NT = N / TILE_CH, KT = K / TILE_K;
-    const int64_t T = NT * KT;
-    int grid = num_sms;
-    const int64_t need = (T + GV_WARPS - 1) / GV_WARPS;
-    if (need < grid) grid = (int)(need < 1 ? 1 : need);
-    plan->grid = grid;
-    plan->smem_bytes = smem;
-    const int64_t W = (int64_t)grid * GV_WARPS;
-    const int64_t base = T / W;
-    // a row of KT tiles can be cut into at most ceil(KT/base)+1 pieces (base >= 1), or KT pieces (base == 0)
-    int64_t maxslots = base >= 1 ? (KT + base - 1) / base + 1 : KT;
-    if (maxslots > KT) maxslots = KT;
-    if (maxslots < 1) maxslots = 1;
-    plan->maxslots = (int)maxslots;
-    plan->partial_bytes = (size_t)round_up((int64_t)NT * maxslots * M * 8 * sizeof(float), 256);
-    plan->ticket_bytes = (size_t)round_up(NT * (int64_t)sizeof(int), 256);
+    if (NT * KT >= (int64_t)1 << 30) return false;                 // 32-bit tile arithmetic in the kernel
+    const GvSmem L((int)M, (int)KT);
+    if ((size_t)L.total > smem_optin) return false;
+    int64_t clusters = num_sms / GV_CLUSTER;
+    if (NT < clusters) clusters = NT;                              // a cluster owns whole rows
+    if (clusters < 1) clusters = 1;
+    plan->grid = (int)(clusters * GV_CLUSTER);
+    plan->smem_bytes = (size_t)L.total;
+    plan->maxslots = 0;
+    plan->partial_bytes = 0;                                       // no global scratch: rows never leave a cluster
+    plan->ticket_bytes = 0;
     return true;
 }
 
-template <int MR>
-static cudaError_t launch_gemv_mr(const void *w, const float *x, const int32_t *perm, float *y, int64_t N, int64_t K,
-                                  const GemvPlan &plan, float *ws_partial, int *ws_ticket, int32_t *dbg,
-                                  cudaStream_t stream) {
-    if (dbg) {
-        auto kern = tcq4_gemv_kernel<MR, true>;
-        kern<<<plan.grid, GV_THREADS, plan.smem_bytes, stream>>>((const uint8_t *)w, x, perm, y, (int)N, (int)K,
-                                                                 ws_partial, ws_ticket, plan.maxslots, dbg);
-    } else {
-        auto kern = tcq4_gemv_kernel<MR, false>;
-        kern<<<plan.grid, GV_THREADS, plan.smem_bytes, stream>>>((const uint8_t *)w, x, perm, y, (int)N, (int)K,
-                                                                 ws_partial, ws_ticket, plan.maxslots, nullptr);
-    }
-    return cudaGetLastError();
+template <int MB, bool DEBUG>
+static cudaError_t launch_gemv_t(const void *w, const float *x, const int32_t *perm, float *y, int64_t M, int64_t N,
+                                 int64_t K, const GemvPlan &plan, int32_t *dbg, cudaStream_t stream) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)plan.grid);
+    cfg.blockDim = dim3(GV_THREADS);
+    cfg.dynamicSmemBytes = plan.smem_bytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = GV_CLUSTER;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    static const bool no_pdl = getenv("TCQ4_NO_PDL") != nullptr;     // diagnostic switch (tests/gpu_diag_gemv.py)
+    cfg.numAttrs = no_pdl ? 1 : 2;
+    return cudaLaunchKernelEx(&cfg, tcq4_gemv_kernel<MB, DEBUG>, (const uint8_t *)w, x, perm, y, (int)M, (int)N, (int)K, dbg);
 }
 
-template <int MR>
-static cudaError_t gemv_attr_mr(size_t smem_optin) {
-    cudaError_t e = cudaFuncSetAttribute(tcq4_gemv_kernel<MR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+template <int MB>
+static cudaError_t gemv_attr_mb(size_t smem_optin) {
+    cudaError_t e = cudaFuncSetAttribute(tcq4_gemv_kernel<MB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)smem_optin);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(tcq4_gemv_kernel<MR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    return cudaFuncSetAttribute(tcq4_gemv_kernel<MB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)smem_optin);
 }
 
 cudaError_t gemv_init_attributes(size_t smem_optin) {
-    cudaError_t e;
-    if ((e = gemv_attr_mr<1>(smem_optin)) != cudaSuccess) return e;
-    if ((e = gemv_attr_mr<2>(smem_optin)) != cudaSuccess) return e;
-    if ((e = gemv_attr_mr<3>(smem_optin)) != cudaSuccess) return e;
-    return gemv_attr_mr<4>(smem_optin);
+    cudaError_t e = gemv_attr_mb<1>(smem_optin);
+    if (e != cudaSuccess) return e;
+    return gemv_attr_mb<2>(smem_optin);
 }
 
 cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm, float *y, int64_t M, int64_t N,
                         int64_t K, const GemvPlan &plan, float *ws_partial, int *ws_ticket, int32_t *dbg_isum,
                         cudaStream_t stream) {
-    switch (M) {
-        case 1: return launch_gemv_mr<1>(w_tiles, x, perm, y, N, K, plan, ws_partial, ws_ticket, dbg_isum, stream);
-        case 2: return launch_gemv_mr<2>(w_tiles, x, perm, y, N, K, plan, ws_partial, ws_ticket, dbg_isum, stream);
-        case 3: return launch_gemv_mr<3>(w_tiles, x, perm, y, N, K, plan, ws_partial, ws_ticket, dbg_isum, stream);
-        case 4: return launch_gemv_mr<4>(w_tiles, x, perm, y, N, K, plan, ws_partial, ws_ticket, dbg_isum, stream);
-        default: return cudaErrorInvalidValue;
+    (void)ws_partial;
+    (void)ws_ticket;
+    if (M < 1 || M > GEMV_MAX_M) return cudaErrorInvalidValue;
+    if (gemv_mb(M) == 1) {
+        if (dbg_isum) return launch_gemv_t<1, true>(w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
+        return launch_gemv_t<1, false>(w_tiles, x, perm, y, M, N, K, plan, nullptr, stream);
     }
+    if (dbg_isum) return launch_gemv_t<2, true>(w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
+    return launch_gemv_t<2, false>(w_tiles, x, perm, y, M, N, K, plan, nullptr, stream);
+}
+
+cudaError_t gemv_read_prof(unsigned long long *host_out, size_t bytes) {
+    const size_t a = sizeof(g_gv_prof), b = sizeof(g_gv_iter);
+    cudaError_t e = cudaMemcpyFromSymbol(host_out, g_gv_prof, bytes < a ? bytes : a);
+    if (e == cudaSuccess && bytes >= a + b)
+        e = cudaMemcpyFromSymbol(reinterpret_cast<uint8_t *>(host_out) + a, g_gv_iter, b);
+    return e;
 }
 
 }  // namespace tcq4

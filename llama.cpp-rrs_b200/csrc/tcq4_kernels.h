@@ -16,12 +16,12 @@ cudaError_t launch_act_quant_stage(const float *x, const int32_t *perm, int64_t 
                                    int num_sms, cudaStream_t stream);
 
 // ---- K3: fused decode GEMV (tcq4_gemv.cu) -----------------------------------------------------
-constexpr int GEMV_MAX_M = 4;
+constexpr int GEMV_MAX_M = 16;
 struct GemvPlan {
     int     grid;            // CTAs (persistent, one per SM)
     size_t  smem_bytes;
     int     maxslots;        // split-K partial slots per n-tile row
-    size_t  partial_bytes;   // workspace: float [NT][maxslots][M][8]
+    size_t  partial_bytes;   // workspace: float [NT][maxslots][8 or 16 rows][8]
     size_t  ticket_bytes;    // workspace: int   [NT]
 };
 bool        gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, GemvPlan *plan);
@@ -29,6 +29,8 @@ cudaError_t gemv_init_attributes(size_t smem_optin);
 cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm, float *y, int64_t M, int64_t N,
                         int64_t K, const GemvPlan &plan, float *ws_partial, int *ws_ticket, int32_t *dbg_isum,
                         cudaStream_t stream);
+
+cudaError_t gemv_read_prof(unsigned long long *host_out, size_t bytes);   // DEBUG-instantiation phase stamps
 
 // ---- K2: tcgen05 prefill GEMM (tcq4_gemm.cu) --------------------------------------------------
 struct GemmPlan {

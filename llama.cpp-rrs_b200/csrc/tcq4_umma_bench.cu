@@ -128,3 +128,68 @@ extern "C" TCQ4_B200_API int tcq4_b200_measure_umma(int kind, int N, int swizzle
     if (cycles_per_mma_out) *cycles_per_mma_out = (double)h_cycles / ((double)iters * kslices);
     return TCQ4_OK;
 }
+
+// ---- warp-level pipe microbenchmark: cycles per warp-instruction per SM for the instructions the decode
+// kernel could be built on (legacy IMMA int8, IDP.4A, SHFL, REDUX).  16 warps per SM, `unroll` independent
+// chains per warp.  kind: 0 = mma.sync.m16n8k32.s8, 1 = dp4a, 2 = shfl.xor, 3 = redux.add
+namespace tcq4 {
+template <int KIND>
+__global__ void __launch_bounds__(512, 1) pipe_bench_kernel(int iters, long long *cycles_out, int *sink) {
+    int acc[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = threadIdx.x + i + j;
+    uint32_t a = threadIdx.x * 2654435761u, b = a ^ 0x9E3779B9u;
+    __syncthreads();
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            if (KIND == 0) {
+                asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                             : "+r"(acc[i][0]), "+r"(acc[i][1]), "+r"(acc[i][2]), "+r"(acc[i][3])
+                             : "r"(a), "r"(b), "r"(a), "r"(b), "r"(a), "r"(b));
+            } else if (KIND == 1) {
+                acc[i][0] = __dp4a((int)a, (int)b, acc[i][0]);
+            } else if (KIND == 2) {
+                acc[i][0] = __shfl_xor_sync(0xffffffffu, acc[i][0], 1 + (i & 15));
+            } else {
+                acc[i][0] += __reduce_add_sync(0xffffffffu, acc[i][0]);
+            }
+        }
+    }
+    __syncthreads();
+    const long long t1 = clock64();
+    int s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += acc[i][0] + acc[i][1] + acc[i][2] + acc[i][3];
+    if (s == 0x7fffffff) *sink = s;
+    if (threadIdx.x == 0) cycles_out[blockIdx.x] = t1 - t0;
+}
+}  // namespace tcq4
+
+extern "C" TCQ4_B200_API int tcq4_b200_measure_pipe(int kind, int iters, double *cycles_per_warp_instr_per_sm) {
+    using namespace tcq4;
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return TCQ4_ERR_NO_DEVICE;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    long long *d_cycles = nullptr;
+    int *d_sink = nullptr;
+    if (cudaMalloc(&d_cycles, sizeof(long long) * sms) != cudaSuccess) return TCQ4_ERR_CUDA;
+    cudaMalloc(&d_sink, sizeof(int));
+    for (int rep = 0; rep < 2; rep++) {
+        if (kind == 0) pipe_bench_kernel<0><<<sms, 512>>>(iters, d_cycles, d_sink);
+        else if (kind == 1) pipe_bench_kernel<1><<<sms, 512>>>(iters, d_cycles, d_sink);
+        else if (kind == 2) pipe_bench_kernel<2><<<sms, 512>>>(iters, d_cycles, d_sink);
+        else pipe_bench_kernel<3><<<sms, 512>>>(iters, d_cycles, d_sink);
+    }
+    cudaError_t err = cudaDeviceSynchronize();
+    long long h = 0;
+    cudaMemcpy(&h, d_cycles, sizeof(long long), cudaMemcpyDeviceToHost);
+    cudaFree(d_cycles);
+    cudaFree(d_sink);
+    if (err != cudaSuccess) return TCQ4_ERR_CUDA;
+    if (cycles_per_warp_instr_per_sm) *cycles_per_warp_instr_per_sm = (double)h / ((double)iters * 8 * 16);
+    return TCQ4_OK;
+}

@@ -1,0 +1,36 @@
+"""GPU diagnostic (not a pytest file): time a chain of back-to-back GEMV launches, eager and as a CUDA graph.
+   TCQ4_NO_PDL=1 python tests/gpu_chain.py   disables programmatic dependent launch for comparison."""
+import os, sys
+import torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import __graft_entry__ as graft
+t4 = graft.load_package()
+
+def run(M, N, K, nbuf=24):
+    bufs = [t4.random_tiles(N, K, seed=i) for i in range(nbuf)]
+    x = torch.randn((M, K), device="cuda")
+    ws = t4.Workspace.for_shape(M, N, K)
+    outs = [torch.empty((M, N), device="cuda") for _ in range(2)]
+    def chain():
+        for i in range(nbuf):
+            t4.mul_mat(bufs[i], x, N, out=outs[i & 1], workspace=ws)
+    def timeit(fn, reps):
+        for _ in range(3): fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps): fn()
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) * 1e3 / (reps * nbuf)
+    us_e = timeit(chain, 10)
+    g = torch.cuda.CUDAGraph(); s = torch.cuda.Stream(); s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        with torch.cuda.graph(g, stream=s):
+            chain()
+    us_g = timeit(g.replay, 10)
+    wb = bufs[0].numel()
+    print(f"M={M} N={N} K={K} pdl={'off' if os.environ.get('TCQ4_NO_PDL') else 'on'}: eager {us_e:.2f} us/launch, graph {us_g:.2f} us/launch "
+          f"-> {wb / us_g / 1e3:.0f} GB/s", flush=True)
+
+for shp in [(1, 9728, 2560), (1, 2560, 9728), (1, 4096, 2560), (1, 1024, 2560), (8, 9728, 2560)]:
+    run(*shp)

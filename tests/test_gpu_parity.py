@@ -84,7 +84,7 @@ def test_act_quant_arbitrary_perm(t4, orc):
 # K3: fused decode GEMV
 # ------------------------------------------------------------------------------------------------
 GEMV_SHAPES = [(1, 8, 256), (1, 64, 512), (2, 256, 1024), (3, 136, 768), (4, 1024, 2560), (1, 2560, 9728),
-               (4, 9728, 2560)]
+               (4, 9728, 2560), (8, 1024, 2560), (9, 264, 512), (16, 4096, 2560), (13, 2560, 4096), (7, 16384, 256)]
 
 
 @pytest.mark.parametrize("M,N,K", GEMV_SHAPES)
@@ -103,22 +103,27 @@ def test_gemv_vs_oracle(t4, orc, M, N, K, use_perm):
     assert e <= FP32_NMSE_TIGHT <= FP32_NMSE_SPEC, e
 
 
-def test_gemv_whole_row_is_bit_identical(t4, orc):
-    """When one warp owns a whole output row the fp32 result is bit-identical to the oracle
-    (same 4,2,1 tree over groups, sequential over k-tiles, no FMA contraction)."""
+def test_gemv_whole_rows_match_the_gemm_bitwise(t4, orc):
+    """KT = 1: every output row is whole inside one warp, and the GEMV's fp32 step per (row, channel, k-tile)
+    is the GEMM's (fma(float(isum) * (a7/127), S, acc)), so the two kernels agree bit for bit; against the oracle
+    (which divides by 127 per group, tcq4_k32.cu:849) only the last ulp differs."""
     rng = np.random.default_rng(7)
-    M, N, K = 2, 16384, 256          # KT = 1: every row is whole
+    M, N, K = 2, 16384, 256
     tiles = orc.quantize_tiles(make_weights(rng, N, K))
     x = make_acts(rng, M, K)
-    y = t4.mul_mat(_dev(tiles), _dev(x), N, workspace=t4.Workspace.for_shape(M, N, K), kernel=t4.KERNEL_GEMV)
+    ws = t4.Workspace.for_shape(M, N, K)
+    y = t4.mul_mat(_dev(tiles), _dev(x), N, workspace=ws, kernel=t4.KERNEL_GEMV).clone()
+    y2 = t4.mul_mat(_dev(tiles), _dev(x), N, workspace=ws, kernel=t4.KERNEL_GEMM)
+    assert torch.equal(y, y2)
     ref = orc.mul_mat(tiles, x, N)["C"]
-    assert np.array_equal(y.cpu().numpy().view(np.uint32), ref.view(np.uint32))
+    assert nmse(y.cpu().numpy(), ref) <= 1e-12
 
 
-def test_gemv_zero_points(t4, orc):
+@pytest.mark.parametrize("M", [2, 11])
+def test_gemv_zero_points(t4, orc, M):
     """Tiles with non-zero Z/zc: the format carries them even though the quantiser writes 0."""
     rng = np.random.default_rng(8)
-    M, N, K = 2, 64, 512
+    N, K = 64, 512
     t = orc.quantize_tiles(make_weights(rng, N, K)).reshape(-1, 1184).copy()
     t[:, 1040:1056] = np.frombuffer(rng.uniform(-0.01, 0.01, (t.shape[0], 8)).astype(np.float16).tobytes(),
                                     dtype=np.uint8).reshape(t.shape[0], 16)
@@ -128,6 +133,48 @@ def test_gemv_zero_points(t4, orc):
     ref = orc.mul_mat(t, x, N)["C"]
     y = t4.mul_mat(_dev(t), _dev(x), N, workspace=t4.Workspace.for_shape(M, N, K), kernel=t4.KERNEL_GEMV)
     assert nmse(y.cpu().numpy(), ref) <= FP32_NMSE_TIGHT
+
+
+def test_gemv_back_to_back_launches_overlap_safely(t4, orc):
+    """The GEMV is launched with programmatic stream serialization: a launch prefetches its weights while the
+    previous one is still running and only then waits for it.  A dependent chain y1 = W1 x, y2 = W2 y1', ...
+    (each input produced by the previous launch, one shared workspace) must equal the same chain run with a
+    device synchronise between launches, eagerly and as one CUDA graph."""
+    rng = np.random.default_rng(21)
+    dims = [2560, 1024, 2560, 512, 1024, 2560]
+    M = 3
+    Ws = [_dev(orc.quantize_tiles(make_weights(rng, dims[i + 1], dims[i]))) for i in range(len(dims) - 1)]
+    x0 = _dev(make_acts(rng, M, dims[0]))
+    ws = t4.Workspace.for_shape(M, max(dims), max(dims))
+    bufs = [torch.empty((M, d), device="cuda") for d in dims[1:]]
+
+    def chain(sync):
+        cur = x0
+        for W, out, n in zip(Ws, bufs, dims[1:]):
+            t4.mul_mat(W, cur, n, out=out, workspace=ws, kernel=t4.KERNEL_GEMV)
+            if sync:
+                torch.cuda.synchronize()
+            cur = out
+        return [b.clone() for b in bufs]
+
+    want = chain(True)
+    for _ in range(3):
+        got = chain(False)
+        torch.cuda.synchronize()
+        for a, b in zip(got, want):
+            assert torch.equal(a, b)
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        with torch.cuda.graph(g, stream=s):
+            chain(False)
+    for b in bufs:
+        b.zero_()
+    g.replay()
+    torch.cuda.synchronize()
+    for a, b in zip(bufs, want):
+        assert torch.equal(a, b)
 
 
 def test_gemv_repeatable_and_tickets_self_clean(t4, orc):
