@@ -345,7 +345,7 @@ def run_own_arm(args):
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- per-kernel roofline legs (N-shard-local kernels; events on the launching stream) ----------------
-    gm_ms, act_ms, gm_n = kernel_leg(t4, torch, pre, args.steps, t4.KERNEL_GEMM, M)
+    gm_ms, act_ms, gm_n = kernel_leg(t4, torch, pre, args.steps, t4.KERNEL_AUTO, M)
     gv_ms, _, gv_n = kernel_leg(t4, torch, dec, min(dec_steps, 10), t4.KERNEL_GEMV, 1)
     ops_local = sum(2 * M * w.n_local * w.K for w in pre.weights)                 # per step, this rank
     bytes_local_dec = sum(alg_bytes(1, w.n_local, w.K) for w in dec.weights)
@@ -380,7 +380,7 @@ def run_own_arm(args):
             "decode": {"value": 1.0 / (ms_dec * 1e-3), "unit": UNIT, "ms_per_step": ms_dec, "steps": dec_steps,
                        "gbs": total_dec_bytes / (ms_dec * 1e-3) / 1e9, "frac_hbm": total_dec_bytes / (ms_dec * 1e-3) / 1e9
                        / (peaks["hbm_gbs"] * world), "cuda_graph": dec.graph is not None},
-            "roofline": {"bound": "tensor", "kernel": "tcq4_gemm_kernel (tcgen05.mma kind::i8)", "achieved": gm_tops,
+            "roofline": {"bound": "tensor", "kernel": "tcq4_gemm2_kernel (tcgen05.mma.cta_group::2 kind::i8)", "achieved": gm_tops,
                          "peak": i8_peak, "unit": "TOP/s", "frac": gm_tops / i8_peak, "traffic": None,
                          "peak_source": f"2 x bf16_tflops of MEASURED_PEAKS.json ({peaks['source']}, burst)",
                          "peak_umma_i8_measured": umma_i8, "frac_of_umma_i8": (gm_tops / umma_i8) if umma_i8 else None,

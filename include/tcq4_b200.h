@@ -53,7 +53,8 @@ enum {
 enum {
     TCQ4_KERNEL_AUTO  = 0,
     TCQ4_KERNEL_GEMV  = 1,     /* fused FWHT+quant+streaming dot, small M, HBM-bound          */
-    TCQ4_KERNEL_GEMM  = 2      /* activation kernel + tcgen05.mma kind::i8 GEMM, tensor-bound */
+    TCQ4_KERNEL_GEMM  = 2,     /* activation kernel + tcgen05.mma kind::i8 GEMM, one CTA per 128 tokens   */
+    TCQ4_KERNEL_GEMM2 = 3      /* same on CTA pairs (cta_group::2, 256 tokens per pair): M > 128          */
 };
 
 TCQ4_B200_API const char *tcq4_b200_version(void);
@@ -171,6 +172,9 @@ TCQ4_B200_API int tcq4_b200_measure_umma(int kind, int N, int swizzle, int iters
  * Not thread-safe, not usable under stream capture. */
 TCQ4_B200_API int tcq4_b200_profile_begin(int max_launches);
 TCQ4_B200_API int tcq4_b200_profile_end(int kernel, double *main_ms_sum, double *pre_ms_sum, int *launches);
+
+/* Same for a CTA pair: tcgen05.mma.cta_group::2.kind::i8, M = 256, N in {64..256}, no-swizzle K-major. */
+TCQ4_B200_API int tcq4_b200_measure_umma2(int N, int iters, double *tops_out, double *cycles_per_mma_out);
 
 /* Diagnostic: SM-wide cost (cycles per warp-instruction, 16 resident warps) of the warp-level instructions the
  * decode kernel is built from.  kind: 0 = mma.sync.m16n8k32.s8 (legacy IMMA), 1 = dp4a, 2 = shfl, 3 = redux.add */

@@ -27,7 +27,7 @@ ACT_BLOCK_BYTES = 160
 GGML_TYPE_F32 = 0
 GGML_TYPE_TCQ4_K32 = 42
 
-KERNEL_AUTO, KERNEL_GEMV, KERNEL_GEMM = 0, 1, 2
+KERNEL_AUTO, KERNEL_GEMV, KERNEL_GEMM, KERNEL_GEMM2 = 0, 1, 2, 3
 
 STATUS = {0: "OK", 1: "ERR_SHAPE", 2: "ERR_ARG", 3: "ERR_WORKSPACE", 4: "ERR_CUDA", 5: "ERR_NO_DEVICE"}
 
@@ -41,7 +41,7 @@ EXPORTS = [
     "tcq4_b200_get_reorder_enabled", "tcq4_b200_shard_range", "tcq4_b200_ggml_supports_op",
     "tcq4_b200_ggml_mul_mat", "tcq4_b200_launch_count", "tcq4_b200_measure_umma",
     "tcq4_b200_profile_begin", "tcq4_b200_profile_end", "tcq4_b200_debug_gemv_phases",
-    "tcq4_b200_measure_pipe",
+    "tcq4_b200_measure_pipe", "tcq4_b200_measure_umma2",
 ]
 
 
@@ -92,6 +92,7 @@ def _load() -> C.CDLL:
     lib.tcq4_b200_launch_count.restype = C.c_uint64
     lib.tcq4_b200_measure_umma.argtypes = [ci, ci, ci, ci, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.tcq4_b200_debug_gemv_phases.argtypes = [vp, sz]
+    lib.tcq4_b200_measure_umma2.argtypes = [ci, ci, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.tcq4_b200_measure_pipe.argtypes = [ci, ci, C.POINTER(C.c_double)]
     lib.tcq4_b200_profile_begin.argtypes = [ci]
     lib.tcq4_b200_profile_end.argtypes = [ci, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(ci)]

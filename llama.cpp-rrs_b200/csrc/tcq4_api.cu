@@ -87,6 +87,7 @@ DevInfo *current_device(int *status) {
             if (major == 10) {
                 cudaError_t e1 = tcq4::gemv_init_attributes(d.smem_optin);
                 cudaError_t e2 = tcq4::gemm_init_attributes(d.smem_optin);
+                if (e2 == cudaSuccess) e2 = tcq4::gemm2_init_attributes(d.smem_optin);
                 d.ok = (e1 == cudaSuccess && e2 == cudaSuccess);
                 if (!d.ok) set_err("kernel attribute setup failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
             } else {
@@ -132,7 +133,7 @@ WsLayout ws_layout(int64_t M, int64_t N, int64_t K) {
     const int64_t slot_rows = (M <= 8) ? 8 : 16;
     L.partial_bytes = (size_t)tcq4::round_up(NT * maxslots * slot_rows * 8 * 4, 256);   // kept for every M: size is monotone in M
     L.codes_off = L.partial_off + L.partial_bytes;
-    const int64_t MB = (M + 127) / 128;
+    const int64_t MB = ((M + 255) / 256) * 2;       // whole CTA pairs: the pair kernel bulk-copies both units
     const size_t codes = (size_t)tcq4::round_up(MB * KT * (int64_t)tcq4::ACT_UNIT_BYTES, 256);
     L.a7_off = L.codes_off + codes;
     L.sumq_off = L.a7_off + (size_t)tcq4::round_up(M * KT * 4, 256);
@@ -145,7 +146,7 @@ int select_kernel(const DevInfo *d, int64_t M, int64_t N, int64_t K, tcq4::GemvP
     const size_t optin = d ? d->smem_optin : (size_t)232448;
     tcq4::GemvPlan tmp;
     if (tcq4::gemv_plan(M, N, K, sms, optin, gv ? gv : &tmp)) return TCQ4_KERNEL_GEMV;
-    return TCQ4_KERNEL_GEMM;
+    return M > 128 ? TCQ4_KERNEL_GEMM2 : TCQ4_KERNEL_GEMM;
 }
 
 int run_mul_mat(const void *w, const float *x, float *y, int64_t M, int64_t N, int64_t K, const int32_t *perm,
@@ -198,7 +199,7 @@ int run_mul_mat(const void *w, const float *x, float *y, int64_t M, int64_t N, i
         g_launches.fetch_add(1, std::memory_order_relaxed);
         return TCQ4_OK;
     }
-    if (k != TCQ4_KERNEL_GEMM) {
+    if (k != TCQ4_KERNEL_GEMM && k != TCQ4_KERNEL_GEMM2) {
         set_err("unknown kernel selector %d", kernel);
         return TCQ4_ERR_ARG;
     }
@@ -216,11 +217,20 @@ int run_mul_mat(const void *w, const float *x, float *y, int64_t M, int64_t N, i
     cudaError_t e = tcq4::launch_act_quant_stage(x, perm, M, K, st, d->num_sms, stream);
     if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
     if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
-    e = tcq4::launch_gemm(w, st, y, M, N, K, gm, dbg_isum, stream);
+    if (k == TCQ4_KERNEL_GEMM2) {
+        tcq4::Gemm2Plan g2;
+        if (!tcq4::gemm2_plan(M, N, K, d->num_sms, d->smem_optin, &g2)) {
+            set_err("pair GEMM kernel cannot be planned for this shape/device");
+            return TCQ4_ERR_SHAPE;
+        }
+        e = tcq4::launch_gemm2(w, st, y, M, N, K, g2, dbg_isum, stream);
+    } else {
+        e = tcq4::launch_gemm(w, st, y, M, N, K, gm, dbg_isum, stream);
+    }
     if (e != cudaSuccess) return cuda_fail(e, "gemm launch");
     if (prof) {
         cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
-        g_prof.kind[g_prof.n++] = TCQ4_KERNEL_GEMM;
+        g_prof.kind[g_prof.n++] = k;
     }
     g_launches.fetch_add(2, std::memory_order_relaxed);
     return TCQ4_OK;

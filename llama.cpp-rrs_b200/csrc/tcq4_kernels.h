@@ -45,4 +45,15 @@ cudaError_t gemm_init_attributes(size_t smem_optin);
 cudaError_t launch_gemm(const void *w_tiles, ActStage st, float *y, int64_t M, int64_t N, int64_t K,
                         const GemmPlan &plan, int32_t *dbg_isum, cudaStream_t stream);
 
+// ---- K2 on CTA pairs, M > 128 (tcq4_gemm2.cu) --------------------------------------------------
+struct Gemm2Plan {
+    dim3    grid;            // (2 * ceil(M/256), ceil(NT / (2*ntl))), clusters of 2 along x
+    size_t  smem_bytes;
+    int     ntl;             // n-tiles (8 channels) unpacked per CTA per pair-tile
+};
+bool        gemm2_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, Gemm2Plan *plan);
+cudaError_t gemm2_init_attributes(size_t smem_optin);
+cudaError_t launch_gemm2(const void *w_tiles, ActStage st, float *y, int64_t M, int64_t N, int64_t K,
+                         const Gemm2Plan &plan, int32_t *dbg_isum, cudaStream_t stream);
+
 }  // namespace tcq4

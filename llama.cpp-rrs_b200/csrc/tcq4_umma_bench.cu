@@ -129,6 +129,92 @@ extern "C" TCQ4_B200_API int tcq4_b200_measure_umma(int kind, int N, int swizzle
     return TCQ4_OK;
 }
 
+// ---- cta_group::2 variant: a CTA pair issues M = 256 MMAs (each CTA holds 128 rows of A and N/2 rows of B) ----
+namespace tcq4 {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1)
+umma2_bench_kernel(int N, int iters, int kslices, long long *cycles_out) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int warp = threadIdx.x >> 5;
+    uint32_t crank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
+    for (int i = threadIdx.x; i < (64 * 1024) / 4; i += blockDim.x) reinterpret_cast<uint32_t *>(smem)[i] = 0;
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        fence_mbar_init();
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    tc_fence_after();
+    const uint32_t tmem = tmem_slot;
+    if (crank == 0 && threadIdx.x == 0) {
+        const uint32_t idesc = umma_idesc_i8(256, N, 1, 1);
+        const uint32_t a_base = smem_u32(smem), b_base = a_base + 32 * 1024;
+        const int nh = N / 2;     // B rows held by each CTA
+        const long long t0 = clock64();
+        for (int it = 0; it < iters; it++) {
+            for (int ks = 0; ks < kslices; ks++) {
+                const uint64_t ad = umma_desc_kmajor_noswz(a_base + ks * 4096, 2048, 128);
+                const uint64_t bd = umma_desc_kmajor_noswz(b_base + ks * (nh * 32), nh * 16, 128);
+                const uint32_t d = tmem + (it & 1) * 256;
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                             "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(ad), "l"(bd),
+                             "r"(idesc), "r"(1u) : "memory");
+            }
+        }
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::
+                         "r"(smem_u32(&bar)), "h"((uint16_t)1) : "memory");
+        mbar_wait(&bar, 0);
+        const long long t1 = clock64();
+        cycles_out[blockIdx.x / 2] = t1 - t0;
+    }
+    tc_fence_before();
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+}
+}  // namespace tcq4
+
+extern "C" TCQ4_B200_API int tcq4_b200_measure_umma2(int N, int iters, double *tops_out, double *cycles_per_mma_out) {
+    using namespace tcq4;
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return TCQ4_ERR_NO_DEVICE;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    sms &= ~1;
+    const int kslices = 4;
+    const size_t smem = 64 * 1024 + 1024;
+    long long *d_cycles = nullptr;
+    if (cudaMalloc(&d_cycles, sizeof(long long) * sms) != cudaSuccess) return TCQ4_ERR_CUDA;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    float ms = 0.f;
+    cudaError_t err = cudaFuncSetAttribute(umma2_bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    for (int rep = 0; rep < 2 && err == cudaSuccess; rep++) {
+        cudaEventRecord(e0);
+        umma2_bench_kernel<<<sms, 128, smem>>>(N, iters, kslices, d_cycles);
+        cudaEventRecord(e1);
+        err = cudaEventSynchronize(e1);
+        if (err != cudaSuccess) break;
+        cudaEventElapsedTime(&ms, e0, e1);
+    }
+    long long h_cycles = 0;
+    cudaMemcpy(&h_cycles, d_cycles, sizeof(long long), cudaMemcpyDeviceToHost);
+    cudaFree(d_cycles);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (err != cudaSuccess) return TCQ4_ERR_CUDA;
+    const double ops = 2.0 * 256.0 * N * 32.0 * (double)iters * kslices * (sms / 2);
+    if (tops_out) *tops_out = ops / (ms * 1e-3) / 1e12;
+    if (cycles_per_mma_out) *cycles_per_mma_out = (double)h_cycles / ((double)iters * kslices);
+    return TCQ4_OK;
+}
+
 // ---- warp-level pipe microbenchmark: cycles per warp-instruction per SM for the instructions the decode
 // kernel could be built on (legacy IMMA int8, IDP.4A, SHFL, REDUX).  16 warps per SM, `unroll` independent
 // chains per warp.  kind: 0 = mma.sync.m16n8k32.s8, 1 = dp4a, 2 = shfl.xor, 3 = redux.add

@@ -33,7 +33,8 @@ def test_supports_and_select(t4):
     assert t4.select_kernel(4, 2560, 9728) == t4.KERNEL_GEMV
     assert t4.select_kernel(16, 9728, 2560) == t4.KERNEL_GEMV
     assert t4.select_kernel(17, 9728, 2560) == t4.KERNEL_GEMM
-    assert t4.select_kernel(512, 9728, 2560) == t4.KERNEL_GEMM
+    assert t4.select_kernel(128, 9728, 2560) == t4.KERNEL_GEMM
+    assert t4.select_kernel(512, 9728, 2560) == t4.KERNEL_GEMM2
     assert t4.select_kernel(4, 1024, 65536) == t4.KERNEL_GEMM      # codes do not fit shared memory
 
 

@@ -213,6 +213,50 @@ def test_gemm_vs_oracle(t4, orc, M, N, K):
     assert e <= FP32_NMSE_TIGHT <= FP32_NMSE_SPEC, e
 
 
+GEMM2_SHAPES = [(129, 256, 512), (256, 128, 256), (300, 1024, 1024), (257, 264, 768), (130, 8, 256), (640, 2560, 1024),
+                (512, 9728, 2560)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM2_SHAPES)
+def test_gemm2_pairs_vs_oracle(t4, orc, M, N, K):
+    """The CTA-pair kernel (cta_group::2): TMEM accumulators bit-exact, fp32 as tight as the single-CTA kernel."""
+    rng = np.random.default_rng(400 + M + N + K)
+    W = make_weights(rng, N, K)
+    x = make_acts(rng, M, K)
+    tiles = orc.quantize_tiles(W)
+    big = M * N * K > 2e9
+    Mo = 24 if big else M
+    rows = np.sort(rng.choice(M, Mo, replace=False)) if big else np.arange(M)
+    ref = orc.mul_mat(tiles, x[rows], N, want_isum=True)
+    y, isum = t4.mul_mat_debug(_dev(tiles), _dev(x), N, kernel=t4.KERNEL_GEMM2)
+    torch.cuda.synchronize()
+    assert np.array_equal(isum.cpu().numpy()[rows], ref["isum"])
+    e = nmse(y.cpu().numpy()[rows], ref["C"])
+    assert e <= FP32_NMSE_TIGHT <= FP32_NMSE_SPEC, e
+    # and the non-debug instantiation agrees bit for bit with the single-CTA kernel
+    ws = t4.Workspace.for_shape(M, N, K)
+    y2 = t4.mul_mat(_dev(tiles), _dev(x), N, workspace=ws, kernel=t4.KERNEL_GEMM2).clone()
+    y1 = t4.mul_mat(_dev(tiles), _dev(x), N, workspace=ws, kernel=t4.KERNEL_GEMM)
+    assert torch.equal(y1, y2)
+
+
+def test_gemm2_zero_points_and_perm(t4, orc):
+    rng = np.random.default_rng(15)
+    M, N, K = 200, 136, 512
+    perm = block_perm(rng, K)
+    t = orc.quantize_tiles(orc.apply_perm_weights(make_weights(rng, N, K), perm)).reshape(-1, 1184).copy()
+    t[:, 1040:1056] = np.frombuffer(rng.uniform(-0.01, 0.01, (t.shape[0], 8)).astype(np.float16).tobytes(),
+                                    dtype=np.uint8).reshape(t.shape[0], 16)
+    t[:, 1120:1184] = rng.integers(-127, 128, (t.shape[0], 64)).astype(np.int8).view(np.uint8)
+    sc = t[:, 1056:1120].view(np.int8)
+    sc[:, ::5] = -sc[:, ::5]
+    t = t.reshape(-1)
+    x = make_acts(rng, M, K)
+    ref = orc.mul_mat(t, x, N, perm)["C"]
+    y = t4.mul_mat(_dev(t), _dev(x), N, _dev(perm), workspace=t4.Workspace.for_shape(M, N, K), kernel=t4.KERNEL_GEMM2)
+    assert nmse(y.cpu().numpy(), ref) <= 1e-8
+
+
 def test_gemm_with_perm_and_negative_scale_codes(t4, orc):
     """perm path + sc < 0 (int8 allows it; the quantiser never writes it) exercise the unpack bias math."""
     rng = np.random.default_rng(11)
