@@ -177,12 +177,19 @@ TCQ4_B200_API int tcq4_b200_profile_end(int kernel, double *main_ms_sum, double 
 TCQ4_B200_API int tcq4_b200_measure_umma2(int N, int iters, double *tops_out, double *cycles_per_mma_out);
 
 /* Diagnostic: SM-wide cost (cycles per warp-instruction, 16 resident warps) of the warp-level instructions the
- * decode kernel is built from.  kind: 0 = mma.sync.m16n8k32.s8 (legacy IMMA), 1 = dp4a, 2 = shfl, 3 = redux.add */
+ * decode kernel is built from.  kind: 0 = mma.sync.m16n8k32.s8 (legacy IMMA), 1 = dp4a, 2 = shfl, 3 = redux.add,
+ * 4 = cvt.rn.f32.s32 (I2FP), 5 = mad.lo.s32 (IMAD) */
 TCQ4_B200_API int tcq4_b200_measure_pipe(int kind, int iters, double *cycles_per_warp_instr_per_sm);
+/* TMEM read bandwidth: `warps` warps per SM loop tcgen05.ld.32x32b.x{cols} (cols = 8, 16 or 32) over their lane
+ * quarter; returns bytes per clock per SM.  Bounds the prefill epilogue ("TMEM read rate"). */
+TCQ4_B200_API int tcq4_b200_measure_tmem_ld(int cols, int warps, int iters, double* bytes_per_clk_per_sm);
 
 /* Diagnostic: per-CTA phase timestamps (ns) of the last GEMV launched through tcq4_b200_mul_mat_debug:
  * out[cta][8] = {start, prefetch issued, dependency resolved, activation stage done, stream done, end}. */
 TCQ4_B200_API int tcq4_b200_debug_gemv_phases(unsigned long long *out, size_t bytes);
+/* Diagnostics: SM-clock stamps [cta 2][role 6][k-tile 16][event 8] of one cluster of the pair GEMM, recorded when
+ * the environment has TCQ4_G2_PROF set (a separate instantiation; the product kernel carries no stamps). */
+TCQ4_B200_API int tcq4_b200_debug_gemm2_timeline(long long *out, size_t bytes);
 
 /* Launch statistics since load (kernels launched by this library), for bench.py's gpu_launches. */
 TCQ4_B200_API uint64_t tcq4_b200_launch_count(void);

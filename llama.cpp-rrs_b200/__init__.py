@@ -40,8 +40,9 @@ EXPORTS = [
     "ggml_backend_cuda_tcq4_set_reorder_enabled", "tcq4_b200_get_perm", "tcq4_b200_has_perm",
     "tcq4_b200_get_reorder_enabled", "tcq4_b200_shard_range", "tcq4_b200_ggml_supports_op",
     "tcq4_b200_ggml_mul_mat", "tcq4_b200_launch_count", "tcq4_b200_measure_umma",
-    "tcq4_b200_profile_begin", "tcq4_b200_profile_end", "tcq4_b200_debug_gemv_phases",
-    "tcq4_b200_measure_pipe", "tcq4_b200_measure_umma2",
+    "tcq4_b200_profile_begin", "tcq4_b200_profile_end", "tcq4_b200_debug_gemv_phases", "tcq4_b200_debug_gemm2_timeline",
+    "tcq4_b200_measure_pipe",
+    "tcq4_b200_measure_tmem_ld", "tcq4_b200_measure_umma2",
 ]
 
 
@@ -92,8 +93,10 @@ def _load() -> C.CDLL:
     lib.tcq4_b200_launch_count.restype = C.c_uint64
     lib.tcq4_b200_measure_umma.argtypes = [ci, ci, ci, ci, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.tcq4_b200_debug_gemv_phases.argtypes = [vp, sz]
+    lib.tcq4_b200_debug_gemm2_timeline.argtypes = [vp, sz]
     lib.tcq4_b200_measure_umma2.argtypes = [ci, ci, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.tcq4_b200_measure_pipe.argtypes = [ci, ci, C.POINTER(C.c_double)]
+    lib.tcq4_b200_measure_tmem_ld.argtypes = [ci, ci, ci, C.POINTER(C.c_double)]
     lib.tcq4_b200_profile_begin.argtypes = [ci]
     lib.tcq4_b200_profile_end.argtypes = [ci, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(ci)]
     return lib

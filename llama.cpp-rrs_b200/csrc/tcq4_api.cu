@@ -405,6 +405,12 @@ int tcq4_b200_fwht_quantize_tc(const float *x, void *y_blocks, const int32_t *d_
     return TCQ4_OK;
 }
 
+int tcq4_b200_debug_gemm2_timeline(long long *out, size_t bytes) {
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = tcq4::gemm2_read_prof(out, bytes);
+    return e == cudaSuccess ? TCQ4_OK : TCQ4_ERR_CUDA;
+}
+
 int tcq4_b200_debug_gemv_phases(unsigned long long *out, size_t bytes) {
     cudaError_t e = cudaDeviceSynchronize();
     if (e == cudaSuccess) e = tcq4::gemv_read_prof(out, bytes);

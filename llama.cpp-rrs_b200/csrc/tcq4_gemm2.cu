@@ -3,20 +3,30 @@
 // Same exact integer formulation as tcq4_gemm.cu (p = sc*q = 16*hi + lo folded into the weight operand, one
 // 256-wide accumulation per 256-block, fp32 epilogue once per 256-block), re-tiled so that the CUDA-core work
 // per tensor-core cycle halves:
-//   * a cluster of two CTAs (one TPC) owns 256 tokens x (16*ntl) channels; each CTA stages its own 128 token
-//     rows of s8 activation codes and unpacks only ITS half of the channels (ntl n-tiles = 8*ntl channels ->
-//     16*ntl operand rows: hi rows then lo rows).  One M = 256, N = 32*ntl, K = 32 MMA per 32-group, issued by
+//   * a cluster of two CTAs (one TPC) owns 256 tokens x (16*NTL) channels; each CTA stages its own 128 token
+//     rows of s8 activation codes and unpacks only ITS half of the channels (NTL n-tiles = 8*NTL channels ->
+//     16*NTL operand rows: hi rows then lo rows).  One M = 256, N = 32*NTL, K = 32 MMA per 32-group, issued by
 //     the leader CTA, reads A and B from both CTAs' shared memory and writes 128 lanes x N columns of TMEM in
 //     each.  Weight unpack per SM is half of the single-CTA kernel's for the same MMA time.
-//   * ntl (1..8) is chosen by the planner so that the number of pair-tiles is a multiple of the 74 SM pairs
-//     as nearly as possible (M = 512, N = 9728: ntl = 6 -> 204 tiles = 2.76 waves instead of 152 = 2.05).
-//   * epilogue: hi/lo combine is one IMAD, the fp32 steps are packed f32x2 (FMUL2 / FFMA2).
-// Cross-CTA signalling: the unpack warps of both CTAs arrive (release.cluster) on the LEADER's bfull barriers,
+//   * NTL (2..8) is a template parameter chosen by the planner (waves of pair-tiles x work per tile); the
+//     kernel is bound by issue slots of the unpack + epilogue warps (ncu: profiles/), so every loop over
+//     n-tiles is unrolled at compile time and nothing in the inner loops depends on a kernel argument.
+//   * epilogue per output and 256-block: one IMAD (16*hi + lo), one I2F, and the two fp32 steps packed as
+//     f32x2 (FMUL2 / FFMA2), in the reference's operation order.
+// Pipeline: 3 stages of {activation unit 32 KB + NTL raw tiles + the peer tiles' 160 metadata bytes} filled by
+// one bulk-copy thread, 4 half-k-tile stages of unpacked B, 2 TMEM accumulator stages.
+// Cross-CTA signalling: the unpack warps of both CTAs arrive on the LEADER's bfull barriers (which also tells
+// the leader that the peer's activation unit has landed, because those warps waited for the peer's stage),
 // the epilogue warps of both CTAs on the leader's accempty barriers; the leader's tcgen05.commit multicasts
-// to both CTAs' bfree / empty / accfull barriers; per-channel super-scales S travel through DSMEM.
+// to both CTAs' bfree / empty / accfull barriers.  No data crosses CTAs through generic loads/stores: each CTA
+// bulk-copies the 160 metadata bytes of the peer's tiles for its own epilogue's per-channel super-scales.
 //
 // Replaces tcq4_rrs_gemm_imma_kernel (/root/reference/ggml/src/ggml-cuda/tcq4_k32.cu:1217-1412) and, for these M,
 // the live scalar kernel tcq4_rrs_fused_gemm_smallM (tcq4_k32.cu:733-889).
+#include <cuda.h>      // CUtensorMap (types only; the encoder is fetched through cudaGetDriverEntryPoint)
+
+#include <cstdlib>
+
 #include "tcq4_common.cuh"
 #include "tcq4_kernels.h"
 
@@ -24,29 +34,33 @@ namespace tcq4 {
 
 constexpr int G2_BM = 128;                  // tokens per CTA (256 per pair)
 constexpr int G2_MAXNTL = 8;                // n-tiles per CTA (8 channels each)
+constexpr int G2_MINNTL = 2;
 constexpr int G2_UNPACK_WARP0 = 2, G2_UNPACK_WARPS = 8;
 constexpr int G2_EPI_WARP0 = G2_UNPACK_WARP0 + G2_UNPACK_WARPS, G2_EPI_WARPS = 8;
-constexpr int G2_THREADS = (G2_EPI_WARP0 + G2_EPI_WARPS) * 32;
+constexpr int G2_THREADS = (G2_EPI_WARP0 + G2_EPI_WARPS) * 32;             // 18 warps
 
-constexpr int G2_A_BYTES = ACT_UNIT_BYTES;                   // 32768 per stage
-constexpr int G2_RAW_BYTES = G2_MAXNTL * TILE_BYTES;         // 9472 per stage
-constexpr int G2_BH_BYTES = 16384;                           // one half k-tile (4 groups) of B at ntl = 8
+constexpr int G2_A_BYTES = ACT_UNIT_BYTES;                                  // 32768
+constexpr int G2_RAW_BYTES = G2_MAXNTL * TILE_BYTES;                        // 9472: own tiles
+constexpr int G2_META_BYTES = 2 * G2_MAXNTL * 160;                          // 2560: S, Z, sc, zc of the pair's 2*NTL tiles
+constexpr int G2_STAGE_BYTES = G2_A_BYTES + G2_RAW_BYTES + G2_META_BYTES;   // 44800
+constexpr int G2_STAGES = 3;
+constexpr int G2_BH_BYTES = 16384;                                          // one half k-tile (4 groups) of B at NTL = 8
 constexpr int G2_BH_STAGES = 4;
-constexpr int G2_SN_RING = 4;
+constexpr int G2_SN_RING = 8;
 
 struct Gemm2Smem {
-    static constexpr int off_a = 0;
-    static constexpr int off_raw = off_a + 2 * G2_A_BYTES;                 // 65536
-    static constexpr int off_b = off_raw + 2 * G2_RAW_BYTES;               // 84480
-    static constexpr int off_sn = off_b + G2_BH_STAGES * G2_BH_BYTES;      // 150016
+    static constexpr int off_stage = 0;                                     // [stage]{A | raw | meta}
+    static constexpr int off_b = off_stage + G2_STAGES * G2_STAGE_BYTES;    // 134400
+    static constexpr int off_sn = off_b + G2_BH_STAGES * G2_BH_BYTES;       // 199936
     static constexpr int off_zflag = off_sn + G2_SN_RING * 128 * 4;
     static constexpr int off_bar = off_zflag + G2_SN_RING * 4 * 4;
-    static constexpr int n_bar = 2 + 2 + G2_BH_STAGES + G2_BH_STAGES + 2 + 2 + G2_SN_RING;
+    static constexpr int n_bar = 2 * G2_STAGES + 2 * G2_BH_STAGES + 2 + 2 + G2_SN_RING;
     static constexpr int off_tmem = off_bar + n_bar * 8;
     static constexpr int total = off_tmem + 16;
 };
-static_assert(Gemm2Smem::off_b % 128 == 0, "B operand must be 128-byte aligned");
+static_assert(G2_STAGE_BYTES % 128 == 0 && Gemm2Smem::off_b % 128 == 0, "operands must be 128-byte aligned");
 static_assert(Gemm2Smem::off_bar % 8 == 0, "barriers must be 8-byte aligned");
+static_assert(Gemm2Smem::total <= 227 * 1024, "shared memory budget");
 
 // ---- cluster-scope helpers --------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t g2_ctarank() {
@@ -59,23 +73,16 @@ __device__ __forceinline__ uint32_t g2_mapa(uint32_t local_addr, uint32_t rank) 
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
     return r;
 }
-// arrive on a barrier anywhere in the cluster (address from g2_mapa), releasing this thread's prior writes
+// Arrive on a barrier anywhere in the cluster (address from g2_mapa).  Default semantics (release at CTA scope),
+// exactly what CUTLASS's ClusterBarrier::arrive(cta_id) emits for its 2-SM pipelines: the data this signal covers
+// is shared memory of the ARRIVING CTA read by the tensor core's async proxy (ordered by fence.proxy.async before
+// the arrive) or TMEM (ordered by tcgen05.fence), never another CTA's generic loads -- a cluster-scope release
+// would cost MEMBAR.ALL.GPU per arrive and CCTL.IVALL per wait (seen in SASS, and measured: -30 %).
 __device__ __forceinline__ void g2_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // wait on a LOCAL barrier whose arrivals may come from the peer CTA
-__device__ __forceinline__ void g2_wait_cluster(uint64_t *bar, uint32_t parity) {
-    uint32_t ok;
-    do {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(ok)
-            : "r"(smem_u32(bar)), "r"(parity)
-            : "memory");
-    } while (!ok);
-}
+__device__ __forceinline__ void g2_wait_cluster(uint64_t *bar, uint32_t parity) { mbar_wait(bar, parity); }
 __device__ __forceinline__ void g2_cluster_sync() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
@@ -136,23 +143,26 @@ __device__ __noinline__ float g2_zero_point_term(const uint8_t *__restrict__ w, 
 
 // Unpack one 16-byte chunk (channel c of group g: 32 nibbles) into 32 hi bytes + 32 lo bytes (see tcq4_gemm.cu).
 //   out_hi / out_lo point at this channel's 16-byte row in K-chunk 0; K-chunk 1 is `lbo` bytes further.
+// Two nibbles per IMAD in 16-bit fields: field = 16*sc*(q + 8) + (32768 - 128*sc) = 16*p + 32768, whose high byte
+// is (hi + 128) and whose low byte is 16*lo.  Odd nibbles stay where they are (value 16*u) and take the
+// multiplier sc instead of 16*sc, so one shift serves four fields.
 __device__ __forceinline__ void g2_unpack_chunk(const uint4 wq, int sc, uint8_t *out_hi, uint8_t *out_lo, int lbo) {
-    const uint32_t mul = (uint32_t)(16 * sc);
+    const uint32_t mul16 = (uint32_t)(16 * sc), mul1 = (uint32_t)sc;
     const uint32_t bias = (uint32_t)(32768 - 128 * sc) * 0x00010001u;
     const uint32_t wv[4] = {wq.x, wq.y, wq.z, wq.w};
     uint32_t hi[8], lo[8];
 #pragma unroll
     for (int s = 0; s < 4; s++) {
-        uint32_t P[4];
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const uint32_t up = ((wv[s] >> (4 * i)) & 0x000F000Fu) ^ 0x00080008u;    // u = q + 8 in two fields
-            P[i] = up * mul + bias;                                                  // 16*sc*q + 32768
-        }
-        hi[s * 2 + 0] = __byte_perm(P[0], P[1], 0x7351) ^ 0x80808080u;               // elements 0,1,4,5
-        hi[s * 2 + 1] = __byte_perm(P[2], P[3], 0x7351) ^ 0x80808080u;               // elements 2,3,6,7
-        lo[s * 2 + 0] = __byte_perm(P[0], P[1], 0x6240) >> 4;
-        lo[s * 2 + 1] = __byte_perm(P[2], P[3], 0x6240) >> 4;
+        const uint32_t x = wv[s] ^ 0x88888888u;                                      // u = q + 8 in every nibble
+        const uint32_t x8 = x >> 8;
+        const uint32_t P0 = (x & 0x000F000Fu) * mul16 + bias;                        // elements 0, 4
+        const uint32_t P1 = (x & 0x00F000F0u) * mul1 + bias;                         // elements 1, 5
+        const uint32_t P2 = (x8 & 0x000F000Fu) * mul16 + bias;                       // elements 2, 6
+        const uint32_t P3 = (x8 & 0x00F000F0u) * mul1 + bias;                        // elements 3, 7
+        hi[s * 2 + 0] = __byte_perm(P0, P1, 0x7351) ^ 0x80808080u;                   // elements 0,1,4,5
+        hi[s * 2 + 1] = __byte_perm(P2, P3, 0x7351) ^ 0x80808080u;                   // elements 2,3,6,7
+        lo[s * 2 + 0] = __byte_perm(P0, P1, 0x6240) >> 4;
+        lo[s * 2 + 1] = __byte_perm(P2, P3, 0x6240) >> 4;
     }
     *reinterpret_cast<uint4 *>(out_hi) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
     *reinterpret_cast<uint4 *>(out_hi + lbo) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
@@ -160,44 +170,101 @@ __device__ __forceinline__ void g2_unpack_chunk(const uint4 wq, int sc, uint8_t 
     *reinterpret_cast<uint4 *>(out_lo + lbo) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
 }
 
-template <bool DEBUG>
+__device__ __forceinline__ int g2_mad16(uint32_t hi, uint32_t lo) {      // 16*hi + lo as ONE integer multiply-add
+    int r;
+    asm("mad.lo.s32 %0, %1, 16, %2;" : "=r"(r) : "r"(hi), "r"(lo));
+    return r;
+}
+
+// Timeline stamps (PROF instantiation only; diagnostics): [cta 2][role 6][k-tile 16][event 8] SM clocks of one cluster
+constexpr int G2_PROF_KT = 16;
+__device__ long long g_g2_prof[2 * 6 * G2_PROF_KT * 8];
+constexpr int G2_PROF_CTAS = 4096;
+__device__ long long g_g2_cta[G2_PROF_CTAS * 6];      // per CTA: smid, entry, set up, main loop done, stored, exit (ns)
+__device__ __forceinline__ long long g2_globaltimer() {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define G2_CTA_STAMP(ev)                                                                           \
+    do {                                                                                           \
+        if (PROF && cta_id < G2_PROF_CTAS) g_g2_cta[cta_id * 6 + (ev)] = g2_globaltimer();         \
+    } while (0)
+#define G2_STAMP(role, kt, ev)                                                                     \
+    do {                                                                                           \
+        if (PROF && prof_on && (kt) < G2_PROF_KT)                                                  \
+            g_g2_prof[(((int)rank * 6 + (role)) * G2_PROF_KT + (kt)) * 8 + (ev)] = clock64();      \
+    } while (0)
+
+// 2-D tiled bulk tensor copy global -> shared, completing on an mbarrier (coordinates: {inner, outer} in elements)
+__device__ __forceinline__ void g2_tma_2d(void *dst_smem, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void g2_tma_2d_hint(void *dst_smem, const CUtensorMap *map, int c0, int c1, uint64_t *bar,
+                                               uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], "
+        "[%2], %5;" ::"r"(smem_u32(dst_smem)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
+        : "memory");
+}
+
+template <int NTL, bool DEBUG, bool PROF = false>
 __global__ void __launch_bounds__(G2_THREADS, 1)
-tcq4_gemm2_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict__ y, int M, int N, int K, int ntl,
+tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_constant__ CUtensorMap tm_meta,
+                  const uint8_t *__restrict__ w, ActStage st, float *__restrict__ y, int M, int N, int K,
                   int32_t *__restrict__ dbg_isum) {
     extern __shared__ __align__(128) uint8_t smem[];
+    constexpr int LBO = 256 * NTL;                               // K-chunk stride of B: (16*NTL rows) * 16 B
+    constexpr int BGROUP = 2 * LBO;                              // one 32-group = 2 K-chunks
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int KT = K / TILE_K, NT = N / TILE_CH;
     const uint32_t rank = g2_ctarank();
     const int mb = blockIdx.x;                                   // 128-row block of this CTA (pair = blocks 2p, 2p+1)
-    const int nt_pair = blockIdx.y * (2 * ntl);                  // first n-tile of the pair
-    const int nt0 = nt_pair + (int)rank * ntl;                   // first n-tile this CTA unpacks
-    const int ntl_r = max(0, min(ntl, NT - nt0));                // n-tiles actually present
-    const int lbo = 256 * ntl;                                   // K-chunk stride of B: (16*ntl rows) * 16 B
-    const int bgroup = 2 * lbo;                                  // one 32-group = 2 K-chunks
+    const int nt_pair = blockIdx.y * (2 * NTL);                  // first n-tile of the pair
+    const int nt0 = nt_pair + (int)rank * NTL;                   // first n-tile this CTA unpacks
+    const int ntl_r = max(0, min(NTL, NT - nt0));                // n-tiles actually present
+    const bool prof_on = PROF && blockIdx.y == gridDim.y / 2 && blockIdx.x < 2;
+    const int cta_id = (int)(blockIdx.y * gridDim.x + blockIdx.x);
+    if (PROF && threadIdx.x == G2_EPI_WARP0 * 32) {
+        uint32_t smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        if (cta_id < G2_PROF_CTAS) g_g2_cta[cta_id * 6] = smid;
+        G2_CTA_STAMP(1);
+    }
 
-    uint8_t *sA = smem + Gemm2Smem::off_a;
-    uint8_t *sRaw = smem + Gemm2Smem::off_raw;
+    uint8_t *sStage = smem + Gemm2Smem::off_stage;
     uint8_t *sB = smem + Gemm2Smem::off_b;
     float *sSn = reinterpret_cast<float *>(smem + Gemm2Smem::off_sn);          // [ring][2 halves][64]
     int *sZflag = reinterpret_cast<int *>(smem + Gemm2Smem::off_zflag);        // [ring][2 halves][2 warps]
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + Gemm2Smem::off_bar);
-    uint64_t *full = bars + 0, *empty = bars + 2, *bfull = bars + 4, *bfree = bars + 4 + G2_BH_STAGES,
-             *accfull = bars + 4 + 2 * G2_BH_STAGES, *accempty = accfull + 2, *snfull = accempty + 2;
+    uint64_t *full = bars, *empty = full + G2_STAGES, *bfull = empty + G2_STAGES, *bfree = bfull + G2_BH_STAGES,
+             *accfull = bfree + G2_BH_STAGES, *accempty = accfull + 2, *snfull = accempty + 2;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + Gemm2Smem::off_tmem);
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 2; i++) {
+        for (int i = 0; i < G2_STAGES; i++) {
             mbar_init(&full[i], 1);
             mbar_init(&empty[i], 1 + G2_UNPACK_WARPS);           // leader's commit (multicast) + local unpack warps
-            mbar_init(&accfull[i], 1);                           // leader's commit (multicast)
-            mbar_init(&accempty[i], 2 * G2_EPI_WARPS);           // epilogue warps of both CTAs (used in the leader)
         }
         for (int i = 0; i < G2_BH_STAGES; i++) {
             mbar_init(&bfull[i], 2 * G2_UNPACK_WARPS);           // unpack warps of both CTAs (used in the leader)
             mbar_init(&bfree[i], 1);                             // leader's commit (multicast)
         }
-        for (int i = 0; i < G2_SN_RING; i++) mbar_init(&snfull[i], 4);     // 2 publishing warps per CTA
+        for (int i = 0; i < 2; i++) {
+            mbar_init(&accfull[i], 1);                           // leader's commit (multicast)
+            mbar_init(&accempty[i], 2 * G2_EPI_WARPS);           // epilogue warps of both CTAs (used in the leader)
+        }
+        for (int i = 0; i < G2_SN_RING; i++) mbar_init(&snfull[i], 4);     // 4 local publishing warps
         fence_mbar_init();
+    }
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_tiles) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_meta) : "memory");
     }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512)
@@ -208,109 +275,134 @@ tcq4_gemm2_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict_
     g2_cluster_sync();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
+    if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(2);
 
     if (warp == 0) {
-        // ===================== producer (each CTA loads its own activation rows and its own weight tiles) =====
+        // ===================== producer: three copies per k-tile =====================
+        //   the CTA's activation unit (32 KB, contiguous), its NTL raw tiles and the 160 metadata bytes of all 2*NTL
+        //   tiles of the pair.  The tensor is viewed as a 2-D array of 8-byte words [n-tile][KT*148]; one tiled
+        //   copy with a box of {148 or 20 words, NTL or 2*NTL rows} replaces one bulk copy per tile (17 copies per
+        //   k-tile issued by one thread cost ~2200 cycles of uniform-datapath work and were THE bottleneck of the
+        //   first version of this kernel).  Rows beyond the tensor are zero-filled and counted in the byte total.
         if (lane == 0) {
+            constexpr uint32_t total_tx = (uint32_t)(G2_A_BYTES + NTL * TILE_BYTES + 2 * NTL * 160);
             const uint64_t pol_w = l2_policy_evict_first();
+            const uint8_t *a_src = reinterpret_cast<const uint8_t *>(st.codes) + (size_t)mb * KT * ACT_UNIT_BYTES;
+            int s = 0, u = 0;
             for (int kt = 0; kt < KT; kt++) {
-                const int s = kt & 1, u = kt >> 1;
                 if (u > 0) mbar_wait(&empty[s], (uint32_t)((u - 1) & 1));
-                mbar_arrive_expect_tx(&full[s], (uint32_t)(G2_A_BYTES + ntl_r * TILE_BYTES));
-                bulk_g2s(sA + s * G2_A_BYTES, st.codes + ((size_t)mb * KT + kt) * ACT_UNIT_BYTES, G2_A_BYTES, &full[s]);
-                for (int j = 0; j < ntl_r; j++)
-                    bulk_g2s_stream(sRaw + s * G2_RAW_BYTES + j * TILE_BYTES,
-                                    w + ((size_t)(nt0 + j) * KT + kt) * TILE_BYTES, TILE_BYTES, &full[s], pol_w);
+                G2_STAMP(0, kt, 0);
+                uint8_t *stg = sStage + s * G2_STAGE_BYTES;
+                mbar_arrive_expect_tx(&full[s], total_tx);
+                bulk_g2s(stg, a_src, G2_A_BYTES, &full[s]);
+                g2_tma_2d_hint(stg + G2_A_BYTES, &tm_tiles, kt * (TILE_BYTES / 8), nt0, &full[s], pol_w);
+                g2_tma_2d(stg + G2_A_BYTES + G2_RAW_BYTES, &tm_meta, kt * (TILE_BYTES / 8) + TILE_NIB / 8, nt_pair, &full[s]);
+                a_src += ACT_UNIT_BYTES;
+                G2_STAMP(0, kt, 1);
+                if (++s == G2_STAGES) { s = 0; u++; }
             }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (leader CTA only) =====================
         if (rank == 0 && lane == 0) {
-            const uint32_t idesc = umma_idesc_i8(2 * G2_BM, 32 * ntl, 1, 1);      // 256 x (32*ntl) x 32, s8 x s8
-            const uint32_t a_base = smem_u32(sA), b_base = smem_u32(sB);
+            constexpr uint32_t idesc = umma_idesc_i8(2 * G2_BM, 32 * NTL, 1, 1);      // 256 x (32*NTL) x 32, s8 x s8
+            const uint32_t stage_base = smem_u32(sStage), b_base = smem_u32(sB);
+            int s = 0;
             for (int kt = 0; kt < KT; kt++) {
-                const int s = kt & 1, u = kt >> 1, as = kt & 1;
-                if (u > 0) g2_wait_cluster(&accempty[as], (uint32_t)((u - 1) & 1));
+                const int as = kt & 1, u2 = kt >> 1;
+                G2_STAMP(1, kt, 0);
+                if (u2 > 0) mbar_wait(&accempty[as], (uint32_t)((u2 - 1) & 1));
+                G2_STAMP(1, kt, 1);
                 tc_fence_after();
                 const uint32_t d = tmem + as * 256;
+#pragma unroll
                 for (int h = 0; h < 2; h++) {
                     const int hq = 2 * kt + h, hs = hq & (G2_BH_STAGES - 1), v = hq / G2_BH_STAGES;
-                    g2_wait_cluster(&bfull[hs], (uint32_t)(v & 1));
+                    mbar_wait(&bfull[hs], (uint32_t)(v & 1));      // also: both CTAs' stage s has landed
+                    G2_STAMP(1, kt, 2 + h);
                     tc_fence_after();
 #pragma unroll
                     for (int gl = 0; gl < 4; gl++) {
                         const int g = h * 4 + gl;
                         const uint64_t a_desc =
-                            umma_desc_kmajor_noswz(a_base + s * G2_A_BYTES + (2 * g) * ACT_LBO, ACT_LBO, ACT_SBO);
+                            umma_desc_kmajor_noswz(stage_base + s * G2_STAGE_BYTES + (2 * g) * ACT_LBO, ACT_LBO, ACT_SBO);
                         const uint64_t b_desc =
-                            umma_desc_kmajor_noswz(b_base + hs * G2_BH_BYTES + gl * bgroup, (uint32_t)lbo, 128);
+                            umma_desc_kmajor_noswz(b_base + hs * G2_BH_BYTES + gl * BGROUP, (uint32_t)LBO, 128);
                         umma_i8_2cta(d, a_desc, b_desc, idesc, g > 0 ? 1u : 0u);
                     }
                     umma_commit_2cta(&bfree[hs]);
                 }
                 umma_commit_2cta(&empty[s]);
                 umma_commit_2cta(&accfull[as]);
+                G2_STAMP(1, kt, 4);
+                if (++s == G2_STAGES) s = 0;
             }
         }
     } else if (warp < G2_EPI_WARP0) {
-        // ===================== weight unpack (this CTA's ntl n-tiles) =====================
+        // ===================== weight unpack (this CTA's NTL n-tiles) =====================
         const int uw = warp - G2_UNPACK_WARP0;
         const int ut = threadIdx.x - G2_UNPACK_WARP0 * 32;          // 0..255
-        // chunk of this thread inside a half k-tile: (gl, j, c) with 8*ntl chunks per group
-        const int per_group = 8 * ntl;
-        const int gl_t = ut / per_group, rem_t = ut - gl_t * per_group;
+        // chunk of this thread inside a half k-tile: (gl, j, c) with 8*NTL chunks per group
+        constexpr int PER_GROUP = 8 * NTL;
+        const int gl_t = ut / PER_GROUP, rem_t = ut - gl_t * PER_GROUP;
         const int j_t = rem_t >> 3, c_t = rem_t & 7;
         const bool has_chunk = (gl_t < 4) && (j_t < ntl_r);
+        const bool warp_has_chunk = (uw * 32) < 4 * PER_GROUP;      // warp-uniform: any lane of this warp may have one
         const uint32_t bfull_leader = g2_mapa(smem_u32(bfull), 0);
-        const uint32_t peer = rank ^ 1u;
-        const uint32_t sn_peer = g2_mapa(smem_u32(sSn), peer), zf_peer = g2_mapa(smem_u32(sZflag), peer),
-                       snfull_peer = g2_mapa(smem_u32(snfull), peer);
+        const int tile_off = G2_A_BYTES + j_t * TILE_BYTES;
+        const int b_off = gl_t * BGROUP + j_t * 128 + c_t * 16;
+        // publishing role of warps 0..3: super-scale of channel (half, j, c) of the pair's 16*NTL channels
+        const int p_half = ut >> 6, p_j = (ut & 63) >> 3, p_c = ut & 7;
+        const bool p_valid = p_j < NTL;                             // absent tiles were zero-filled by the copy
+        const int p_off = G2_A_BYTES + G2_RAW_BYTES + (p_half * NTL + p_j) * 160;
+        int s = 0, u = 0;
         for (int kt = 0; kt < KT; kt++) {
-            const int s = kt & 1, u = kt >> 1;
+            const int prole = (lane == 0 && (uw == 0 || uw == 7)) ? (uw == 0 ? 2 : 3) : -1;
+            if (prole >= 0) G2_STAMP(prole, kt, 0);
             mbar_wait(&full[s], (uint32_t)(u & 1));
-            const uint8_t *raw = sRaw + s * G2_RAW_BYTES;
-            if (uw < 2) {     // per-channel super-scale for both CTAs' epilogues + zero-point presence flag
-                const int j = ut >> 3, c = ut & 7;
+            if (prole >= 0) G2_STAMP(prole, kt, 1);
+            const uint8_t *stg = sStage + s * G2_STAGE_BYTES;
+            if (uw < 4) {     // per-channel super-scale of all 16*NTL channels + zero-point presence flag
                 float sv = 0.0f;
                 int zf = 0;
-                if (j < ntl_r) {
-                    const uint8_t *tp = raw + j * TILE_BYTES;
-                    sv = __half2float(*reinterpret_cast<const __half *>(tp + TILE_OFF_S + 2 * c));
-                    const float zv = __half2float(*reinterpret_cast<const __half *>(tp + TILE_OFF_Z + 2 * c));
-                    const uint2 zc = *reinterpret_cast<const uint2 *>(tp + TILE_OFF_ZC + c * 8);
+                if (p_valid) {
+                    const uint8_t *md = stg + p_off;
+                    sv = __half2float(*reinterpret_cast<const __half *>(md + 2 * p_c));
+                    const float zv = __half2float(*reinterpret_cast<const __half *>(md + 16 + 2 * p_c));
+                    const uint2 zc = *reinterpret_cast<const uint2 *>(md + 96 + p_c * 8);
                     zf = (zv != 0.0f) && ((zc.x | zc.y) != 0u);
                 }
                 const int ring = kt & (G2_SN_RING - 1);
-                const int idx = (ring * 2 + (int)rank) * 64 + ut;
-                sSn[idx] = sv;
-                g2_st_remote_f32(sn_peer + (uint32_t)idx * 4, sv);
+                sSn[ring * 128 + ut] = sv;
                 const int anyz = __any_sync(0xffffffffu, zf);
                 __syncwarp();
                 if (lane == 0) {
-                    const int zi = (ring * 2 + (int)rank) * 2 + uw;
-                    sZflag[zi] = anyz;
-                    g2_st_remote_b32(zf_peer + (uint32_t)zi * 4, anyz);
-                    g2_arrive_cluster(g2_mapa(smem_u32(&snfull[ring]), rank));     // local, cluster-scope release
-                    g2_arrive_cluster(snfull_peer + (uint32_t)ring * 8);
+                    sZflag[ring * 4 + uw] = anyz;
+                    mbar_arrive(&snfull[ring]);      // release: epilogue(kt) acquires before reading
                 }
             }
+#pragma unroll
             for (int h = 0; h < 2; h++) {
-                const int hq = 2 * kt + h, hs = hq & (G2_BH_STAGES - 1), v = hq / G2_BH_STAGES;
+                const int hs = 2 * (kt & 1) + h, v = kt >> 1;
                 if (v > 0) mbar_wait(&bfree[hs], (uint32_t)((v - 1) & 1));
-                if (has_chunk) {
-                    const uint8_t *tp = raw + j_t * TILE_BYTES;
-                    const int g = h * 4 + gl_t;
-                    const uint4 wq = *reinterpret_cast<const uint4 *>(tp + g * 128 + c_t * 16);
-                    const int sc = *reinterpret_cast<const int8_t *>(tp + TILE_OFF_SC + c_t * 8 + g);
-                    uint8_t *row = sB + hs * G2_BH_BYTES + gl_t * bgroup + j_t * 128 + c_t * 16;
-                    g2_unpack_chunk(wq, sc, row, row + ntl * 128, lbo);      // lo rows follow the 8*ntl hi rows
+                if (prole >= 0) G2_STAMP(prole, kt, 2 + 2 * h);
+                if (warp_has_chunk) {
+                    if (has_chunk) {
+                        const uint8_t *tp = stg + tile_off;
+                        const int g = h * 4 + gl_t;
+                        const uint4 wq = *reinterpret_cast<const uint4 *>(tp + g * 128 + c_t * 16);
+                        const int sc = *reinterpret_cast<const int8_t *>(tp + TILE_OFF_SC + c_t * 8 + g);
+                        uint8_t *row = sB + hs * G2_BH_BYTES + b_off;
+                        g2_unpack_chunk(wq, sc, row, row + NTL * 128, LBO);      // lo rows follow the 8*NTL hi rows
+                    }
+                    fence_proxy_async_smem();
                 }
-                fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) g2_arrive_cluster(bfull_leader + (uint32_t)hs * 8);
+                if (prole >= 0) G2_STAMP(prole, kt, 3 + 2 * h);
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[s]);
+            if (lane == 0) mbar_arrive(&empty[s]);      // after the __syncwarp above: every lane has read its raw bytes
+            if (++s == G2_STAGES) { s = 0; u++; }
         }
     } else {
         // ===================== epilogue =====================
@@ -320,77 +412,83 @@ tcq4_gemm2_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict_
         const int row = quarter * 32 + lane;
         const int m = mb * G2_BM + row;
         const bool mvalid = m < M;
-        const int n_base = (nt_pair + colhalf * ntl) * TILE_CH;
+        const int n_base = (nt_pair + colhalf * NTL) * TILE_CH;
         const uint32_t accempty_leader = g2_mapa(smem_u32(accempty), 0);
-        uint64_t acc2[32];                                  // 64 fp32 accumulators as f32x2 pairs
+        const uint32_t t_base = tmem + ((uint32_t)(quarter * 32) << 16) + colhalf * (16 * NTL);
+        const float *a7p = st.a7 + (size_t)(mvalid ? m : 0) * KT;
+        uint64_t acc2[4 * NTL];                             // 8*NTL fp32 accumulators as f32x2 pairs
 #pragma unroll
-        for (int i = 0; i < 32; i++) acc2[i] = 0ull;
+        for (int i = 0; i < 4 * NTL; i++) acc2[i] = 0ull;
 
+        float a7 = mvalid ? a7p[0] : 0.0f;
         for (int kt = 0; kt < KT; kt++) {
-            const int as = kt & 1, u = kt >> 1;
-            const float a7 = mvalid ? st.a7[(size_t)m * KT + kt] : 0.0f;
+            const int as = kt & 1, u2 = kt >> 1;
             const float rm = a7 * (1.0f / 127.0f);          // row factor a7/127; column factor S[n]
+            const float a7_cur = a7;
+            if (kt + 1 < KT && mvalid) a7 = a7p[kt + 1];    // next block's scale: its latency hides under this block
             const uint64_t rm2 = g2_pack(rm, rm);
             const int ring = kt & (G2_SN_RING - 1);
-            g2_wait_cluster(&snfull[ring], (uint32_t)((kt / G2_SN_RING) & 1));
-            mbar_wait(&accfull[as], (uint32_t)(u & 1));
+            const int erole = (lane == 0 && (ew == 0 || ew == 7)) ? (ew == 0 ? 4 : 5) : -1;
+            if (erole >= 0) G2_STAMP(erole, kt, 0);
+            mbar_wait(&snfull[ring], (uint32_t)((kt / G2_SN_RING) & 1));
+            mbar_wait(&accfull[as], (uint32_t)(u2 & 1));
+            if (erole >= 0) G2_STAMP(erole, kt, 1);
             tc_fence_after();
-            const float *sn = sSn + (ring * 2 + colhalf) * 64;
-            const int *zfl = sZflag + (ring * 2 + colhalf) * 2;
-            const int anyz = zfl[0] | zfl[1];
-            const uint32_t t_hi = tmem + ((uint32_t)(quarter * 32) << 16) + as * 256 + colhalf * (16 * ntl);
-            const uint32_t t_lo = t_hi + 8 * ntl;
+            const float *sn = sSn + ring * 128 + colhalf * 64;
+            const int anyz = sZflag[ring * 4 + colhalf * 2] | sZflag[ring * 4 + colhalf * 2 + 1];
+            const uint32_t t_hi = t_base + as * 256;
 #pragma unroll
-            for (int ch = 0; ch < G2_MAXNTL; ch++) {
-                if (ch < ntl) {
-                    uint32_t rh[8], rl[8];
-                    tmem_ld_32x8(t_hi + ch * 8, rh);
-                    tmem_ld_32x8(t_lo + ch * 8, rl);
-                    // S[] of this k-tile is read BEFORE the stage is handed back (ring slot reuse, see tcq4_gemm.cu)
-                    const ulonglong2 s01 = *reinterpret_cast<const ulonglong2 *>(sn + ch * 8);
-                    const ulonglong2 s23 = *reinterpret_cast<const ulonglong2 *>(sn + ch * 8 + 4);
-                    tmem_ld_wait();
-                    if (ch == ntl - 1) {         // all TMEM and ring reads of this stage are done: hand it back
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) g2_arrive_cluster(accempty_leader + (uint32_t)as * 8);
-                    }
-                    const uint64_t sv2[4] = {s01.x, s01.y, s23.x, s23.y};
+            for (int ch = 0; ch < NTL; ch++) {
+                uint32_t rh[8], rl[8];
+                tmem_ld_32x8(t_hi + ch * 8, rh);
+                tmem_ld_32x8(t_hi + 8 * NTL + ch * 8, rl);
+                // S[] of this k-tile is read BEFORE the stage is handed back (ring slot reuse, see tcq4_gemm.cu)
+                const ulonglong2 s01 = *reinterpret_cast<const ulonglong2 *>(sn + ch * 8);
+                const ulonglong2 s23 = *reinterpret_cast<const ulonglong2 *>(sn + ch * 8 + 4);
+                tmem_ld_wait();
+                if (ch == NTL - 1) {             // all TMEM reads of this stage are done: hand it back
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) g2_arrive_cluster(accempty_leader + (uint32_t)as * 8);
+                    if (erole >= 0) G2_STAMP(erole, kt, 2);
+                }
+                const uint64_t sv2[4] = {s01.x, s01.y, s23.x, s23.y};
 #pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const int is0 = (int)rh[2 * i] * 16 + (int)rl[2 * i];             // = sum_g sc*dot, exact
-                        const int is1 = (int)rh[2 * i + 1] * 16 + (int)rl[2 * i + 1];
-                        const uint64_t f2 = g2_mul2(g2_pack((float)is0, (float)is1), rm2);
-                        acc2[ch * 4 + i] = g2_fma2(f2, sv2[i], acc2[ch * 4 + i]);
-                        if (DEBUG) {
-                            const int n = n_base + ch * 8 + 2 * i;
-                            if (dbg_isum && mvalid && n < N) {
-                                dbg_isum[((size_t)m * N + n) * KT + kt] = is0;
-                                dbg_isum[((size_t)m * N + n + 1) * KT + kt] = is1;
-                            }
+                for (int i = 0; i < 4; i++) {
+                    const int is0 = g2_mad16(rh[2 * i], rl[2 * i]);             // = sum_g sc*dot, exact
+                    const int is1 = g2_mad16(rh[2 * i + 1], rl[2 * i + 1]);
+                    const uint64_t f2 = g2_mul2(g2_pack((float)is0, (float)is1), rm2);
+                    acc2[ch * 4 + i] = g2_fma2(f2, sv2[i], acc2[ch * 4 + i]);
+                    if (DEBUG) {
+                        const int n = n_base + ch * 8 + 2 * i;
+                        if (dbg_isum && mvalid && n < N) {
+                            dbg_isum[((size_t)m * N + n) * KT + kt] = is0;
+                            dbg_isum[((size_t)m * N + n + 1) * KT + kt] = is1;
                         }
                     }
                 }
             }
+            if (erole >= 0) G2_STAMP(erole, kt, 3);
             if (anyz && mvalid) {
 #pragma unroll
-                for (int i = 0; i < 32; i++) {
+                for (int i = 0; i < 4 * NTL; i++) {
                     const int n = n_base + 2 * i;
-                    if (2 * i < 8 * ntl && n < N) {
+                    if (n < N) {
                         float a, b;
                         g2_unpack(acc2[i], a, b);
-                        a += g2_zero_point_term(w, st.sumq, m, n, kt, KT, a7);
-                        b += g2_zero_point_term(w, st.sumq, m, n + 1, kt, KT, a7);
+                        a += g2_zero_point_term(w, st.sumq, m, n, kt, KT, a7_cur);
+                        b += g2_zero_point_term(w, st.sumq, m, n + 1, kt, KT, a7_cur);
                         acc2[i] = g2_pack(a, b);
                     }
                 }
             }
         }
+        if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(3);
         if (mvalid) {
             float *yrow = y + (size_t)m * N + n_base;
 #pragma unroll
-            for (int i = 0; i < 32; i += 2) {
-                if (2 * i < 8 * ntl && n_base + 2 * i + 3 < N) {
+            for (int i = 0; i < 4 * NTL; i += 2) {
+                if (n_base + 2 * i < N) {       // N % 8 == 0: a chunk of 8 channels is entirely inside or outside
                     float a, b, c, d;
                     g2_unpack(acc2[i], a, b);
                     g2_unpack(acc2[i + 1], c, d);
@@ -400,13 +498,16 @@ tcq4_gemm2_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict_
         }
     }
 
+    if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(4);
     tc_fence_before();
     g2_cluster_sync();
+    if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(5);
     if (warp == 1)
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
 }
 
 bool gemm2_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, Gemm2Plan *plan) {
+    (void)K;
     if (M < 1 || (size_t)Gemm2Smem::total > smem_optin || num_sms < 2) return false;
     const int64_t NT = N / TILE_CH;
     const int64_t MB2 = (M + 2 * G2_BM - 1) / (2 * G2_BM);
@@ -414,7 +515,7 @@ bool gemm2_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin,
     // n-tiles per CTA: minimise (waves of pair-tiles) x (work per tile + a fixed fill/drain share)
     int best = G2_MAXNTL;
     int64_t best_cost = -1;
-    for (int ntl = G2_MAXNTL; ntl >= 2; ntl--) {
+    for (int ntl = G2_MAXNTL; ntl >= G2_MINNTL; ntl--) {
         const int64_t tiles = MB2 * ((NT + 2 * ntl - 1) / (2 * ntl));
         const int64_t waves = (tiles + pairs - 1) / pairs;
         const int64_t cost = waves * (ntl + 1);
@@ -427,6 +528,54 @@ bool gemm2_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin,
     plan->grid = dim3((unsigned)(2 * MB2), (unsigned)((NT + 2 * best - 1) / (2 * best)), 1);
     plan->smem_bytes = Gemm2Smem::total;
     return true;
+}
+
+// ---- tensor maps: the TCQ4 tensor as [NT rows][KT*148 eight-byte words], boxes of whole tiles / of their metadata
+typedef CUresult (*G2EncodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static G2EncodeTiled g2_encoder() {
+    static G2EncodeTiled fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (G2EncodeTiled)p;
+    }();
+    return fn;
+}
+static bool g2_make_map(CUtensorMap *map, const void *w, int64_t NT, int64_t KT, uint32_t box_words, uint32_t box_rows) {
+    G2EncodeTiled enc = g2_encoder();
+    if (!enc) return false;
+    const cuuint64_t gdim[2] = {(cuuint64_t)KT * (TILE_BYTES / 8), (cuuint64_t)NT};
+    const cuuint64_t gstride[1] = {(cuuint64_t)KT * TILE_BYTES};
+    const cuuint32_t box[2] = {box_words, box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    return enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, const_cast<void *>(w), gdim, gstride, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int NTL>
+static cudaError_t launch_gemm2_t(cudaLaunchConfig_t *cfg, const void *w_tiles, ActStage st, float *y, int64_t M, int64_t N,
+                                  int64_t K, int32_t *dbg_isum) {
+    CUtensorMap tm_tiles, tm_meta;
+    if (!g2_make_map(&tm_tiles, w_tiles, N / TILE_CH, K / TILE_K, TILE_BYTES / 8, NTL) ||
+        !g2_make_map(&tm_meta, w_tiles, N / TILE_CH, K / TILE_K, 160 / 8, 2 * NTL))
+        return cudaErrorInvalidValue;      // unaligned tensor base or no driver entry point
+    static const bool prof = getenv("TCQ4_G2_PROF") != nullptr;     // diagnostics: timeline stamps of one cluster
+    if (prof && !dbg_isum) {
+        cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             Gemm2Smem::total);
+        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, true>, tm_tiles, tm_meta, (const uint8_t *)w_tiles, st, y,
+                                  (int)M, (int)N, (int)K, (int32_t *)nullptr);
+    }
+    if (dbg_isum)
+        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, true>, tm_tiles, tm_meta, (const uint8_t *)w_tiles, st, y,
+                                  (int)M, (int)N, (int)K, dbg_isum);
+    return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false>, tm_tiles, tm_meta, (const uint8_t *)w_tiles, st, y, (int)M,
+                              (int)N, (int)K, (int32_t *)nullptr);
 }
 
 cudaError_t launch_gemm2(const void *w_tiles, ActStage st, float *y, int64_t M, int64_t N, int64_t K,
@@ -443,19 +592,53 @@ cudaError_t launch_gemm2(const void *w_tiles, ActStage st, float *y, int64_t M, 
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    if (dbg_isum)
-        return cudaLaunchKernelEx(&cfg, tcq4_gemm2_kernel<true>, (const uint8_t *)w_tiles, st, y, (int)M, (int)N, (int)K,
-                                  plan.ntl, dbg_isum);
-    return cudaLaunchKernelEx(&cfg, tcq4_gemm2_kernel<false>, (const uint8_t *)w_tiles, st, y, (int)M, (int)N, (int)K,
-                              plan.ntl, (int32_t *)nullptr);
+    static const int force_ntl = getenv("TCQ4_G2_NTL") ? atoi(getenv("TCQ4_G2_NTL")) : 0;     // experiments only
+    int ntl = plan.ntl;
+    if (force_ntl >= G2_MINNTL && force_ntl <= G2_MAXNTL) {
+        ntl = force_ntl;
+        cfg.gridDim.y = (unsigned)((N / TILE_CH + 2 * ntl - 1) / (2 * ntl));
+    }
+    switch (ntl) {
+        case 2: return launch_gemm2_t<2>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
+        case 3: return launch_gemm2_t<3>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
+        case 4: return launch_gemm2_t<4>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
+        case 5: return launch_gemm2_t<5>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
+        case 6: return launch_gemm2_t<6>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
+        case 7: return launch_gemm2_t<7>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
+        case 8: return launch_gemm2_t<8>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+cudaError_t gemm2_read_prof(long long *host_out, size_t bytes) {
+    // first the one-cluster timeline, then (if the caller's buffer is larger) the per-CTA stamps
+    const size_t n1 = bytes < sizeof(g_g2_prof) ? bytes : sizeof(g_g2_prof);
+    cudaError_t e = cudaMemcpyFromSymbol(host_out, g_g2_prof, n1);
+    if (e != cudaSuccess || bytes <= sizeof(g_g2_prof)) return e;
+    size_t n2 = bytes - sizeof(g_g2_prof);
+    if (n2 > sizeof(g_g2_cta)) n2 = sizeof(g_g2_cta);
+    return cudaMemcpyFromSymbol(reinterpret_cast<char *>(host_out) + sizeof(g_g2_prof), g_g2_cta, n2);
+}
+
+template <int NTL>
+static cudaError_t gemm2_set_smem() {
+    cudaError_t e = cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         Gemm2Smem::total);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                Gemm2Smem::total);
 }
 
 cudaError_t gemm2_init_attributes(size_t smem_optin) {
     (void)smem_optin;
-    cudaError_t e = cudaFuncSetAttribute(tcq4_gemm2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         Gemm2Smem::total);
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(tcq4_gemm2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm2Smem::total);
+    cudaError_t e;
+    if ((e = gemm2_set_smem<2>()) != cudaSuccess) return e;
+    if ((e = gemm2_set_smem<3>()) != cudaSuccess) return e;
+    if ((e = gemm2_set_smem<4>()) != cudaSuccess) return e;
+    if ((e = gemm2_set_smem<5>()) != cudaSuccess) return e;
+    if ((e = gemm2_set_smem<6>()) != cudaSuccess) return e;
+    if ((e = gemm2_set_smem<7>()) != cudaSuccess) return e;
+    return gemm2_set_smem<8>();
 }
 
 }  // namespace tcq4

@@ -30,6 +30,7 @@ cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm
                         int64_t K, const GemvPlan &plan, float *ws_partial, int *ws_ticket, int32_t *dbg_isum,
                         cudaStream_t stream);
 
+cudaError_t gemm2_read_prof(long long *host_out, size_t bytes);            // PROF-instantiation timeline stamps
 cudaError_t gemv_read_prof(unsigned long long *host_out, size_t bytes);   // DEBUG-instantiation phase stamps
 
 // ---- K2: tcgen05 prefill GEMM (tcq4_gemm.cu) --------------------------------------------------

@@ -217,7 +217,7 @@ extern "C" TCQ4_B200_API int tcq4_b200_measure_umma2(int N, int iters, double *t
 
 // ---- warp-level pipe microbenchmark: cycles per warp-instruction per SM for the instructions the decode
 // kernel could be built on (legacy IMMA int8, IDP.4A, SHFL, REDUX).  16 warps per SM, `unroll` independent
-// chains per warp.  kind: 0 = mma.sync.m16n8k32.s8, 1 = dp4a, 2 = shfl.xor, 3 = redux.add
+// chains per warp.  kind: 0 = mma.sync.m16n8k32.s8, 1 = dp4a, 2 = shfl.xor, 3 = redux.add, 4 = cvt.rn.f32.s32, 5 = mad.lo.s32
 namespace tcq4 {
 template <int KIND>
 __global__ void __launch_bounds__(512, 1) pipe_bench_kernel(int iters, long long *cycles_out, int *sink) {
@@ -240,6 +240,10 @@ __global__ void __launch_bounds__(512, 1) pipe_bench_kernel(int iters, long long
                 acc[i][0] = __dp4a((int)a, (int)b, acc[i][0]);
             } else if (KIND == 2) {
                 acc[i][0] = __shfl_xor_sync(0xffffffffu, acc[i][0], 1 + (i & 15));
+            } else if (KIND == 4) {
+                acc[i][0] = __float_as_int((float)acc[i][0]);          // I2FP.F32.S32
+            } else if (KIND == 5) {
+                acc[i][0] = acc[i][0] * 16 + (int)a;                   // IMAD
             } else {
                 acc[i][0] += __reduce_add_sync(0xffffffffu, acc[i][0]);
             }
@@ -268,6 +272,8 @@ extern "C" TCQ4_B200_API int tcq4_b200_measure_pipe(int kind, int iters, double 
         if (kind == 0) pipe_bench_kernel<0><<<sms, 512>>>(iters, d_cycles, d_sink);
         else if (kind == 1) pipe_bench_kernel<1><<<sms, 512>>>(iters, d_cycles, d_sink);
         else if (kind == 2) pipe_bench_kernel<2><<<sms, 512>>>(iters, d_cycles, d_sink);
+        else if (kind == 4) pipe_bench_kernel<4><<<sms, 512>>>(iters, d_cycles, d_sink);
+        else if (kind == 5) pipe_bench_kernel<5><<<sms, 512>>>(iters, d_cycles, d_sink);
         else pipe_bench_kernel<3><<<sms, 512>>>(iters, d_cycles, d_sink);
     }
     cudaError_t err = cudaDeviceSynchronize();
@@ -277,5 +283,85 @@ extern "C" TCQ4_B200_API int tcq4_b200_measure_pipe(int kind, int iters, double 
     cudaFree(d_sink);
     if (err != cudaSuccess) return TCQ4_ERR_CUDA;
     if (cycles_per_warp_instr_per_sm) *cycles_per_warp_instr_per_sm = (double)h / ((double)iters * 8 * 16);
+    return TCQ4_OK;
+}
+
+// ---- TMEM read bandwidth: `warps` warps per SM each loop tcgen05.ld.32x32b.x{8,16,32} over their own lane
+// quarter.  The prefill epilogue reads every accumulator once per 256-block, so this rate (not the MMA rate)
+// bounds it when the accumulator tile is wide.
+namespace tcq4 {
+template <int COLS>
+__global__ void __launch_bounds__(1024, 1) tmem_ld_bench_kernel(int iters, long long *cycles_out, int *sink) {
+    __shared__ uint32_t slot;
+    const int warp = threadIdx.x >> 5;
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&slot)), "r"(512)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t base = slot + ((uint32_t)((warp & 3) * 32) << 16);
+    uint32_t x = 0;
+    __syncthreads();
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint32_t col = (uint32_t)(((warp >> 2) * 4 + j) * COLS) & 511u;
+            if (COLS == 8) {
+                uint32_t r[8];
+                tmem_ld_32x8(base + col, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 8; i++) x ^= r[i];
+            } else if (COLS == 16) {
+                uint32_t r[16];
+                tmem_ld_32x16(base + col, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 16; i++) x ^= r[i];
+            } else {
+                uint32_t r[32];
+                tmem_ld_32x32(base + col, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; i++) x ^= r[i];
+            }
+        }
+    }
+    __syncthreads();
+    const long long t1 = clock64();
+    if (x == 0x12345678u) *sink = (int)x;
+    if (threadIdx.x == 0) cycles_out[blockIdx.x] = t1 - t0;
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(slot), "r"(512) : "memory");
+}
+}  // namespace tcq4
+
+extern "C" TCQ4_B200_API int tcq4_b200_measure_tmem_ld(int cols, int warps, int iters, double *bytes_per_clk_per_sm) {
+    using namespace tcq4;
+    if ((cols != 8 && cols != 16 && cols != 32) || warps < 1 || warps > 32 || iters < 1) return TCQ4_ERR_ARG;
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return TCQ4_ERR_NO_DEVICE;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    long long *d_cycles = nullptr;
+    int *d_sink = nullptr;
+    if (cudaMalloc(&d_cycles, sizeof(long long) * sms) != cudaSuccess) return TCQ4_ERR_CUDA;
+    cudaMalloc(&d_sink, sizeof(int));
+    for (int rep = 0; rep < 2; rep++) {
+        if (cols == 8) tmem_ld_bench_kernel<8><<<sms, warps * 32>>>(iters, d_cycles, d_sink);
+        else if (cols == 16) tmem_ld_bench_kernel<16><<<sms, warps * 32>>>(iters, d_cycles, d_sink);
+        else tmem_ld_bench_kernel<32><<<sms, warps * 32>>>(iters, d_cycles, d_sink);
+    }
+    cudaError_t err = cudaDeviceSynchronize();
+    long long h = 0;
+    cudaMemcpy(&h, d_cycles, sizeof(long long), cudaMemcpyDeviceToHost);
+    cudaFree(d_cycles);
+    cudaFree(d_sink);
+    if (err != cudaSuccess) return TCQ4_ERR_CUDA;
+    if (bytes_per_clk_per_sm) *bytes_per_clk_per_sm = (double)iters * 4 * warps * 32.0 * cols * 4.0 / (double)h;
     return TCQ4_OK;
 }
