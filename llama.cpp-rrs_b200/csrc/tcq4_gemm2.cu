@@ -26,6 +26,7 @@
 #include <cuda.h>      // CUtensorMap (types only; the encoder is fetched through cudaGetDriverEntryPoint)
 
 #include <cstdlib>
+#include <type_traits>
 
 #include "tcq4_common.cuh"
 #include "tcq4_kernels.h"
@@ -52,13 +53,15 @@ struct Gemm2Smem {
     static constexpr int off_stage = 0;                                     // [stage]{A | raw | meta}
     static constexpr int off_b = off_stage + G2_STAGES * G2_STAGE_BYTES;    // 134400
     static constexpr int off_sn = off_b + G2_BH_STAGES * G2_BH_BYTES;       // 199936
-    static constexpr int off_zflag = off_sn + G2_SN_RING * 128 * 4;
+    static constexpr int off_out = off_sn + G2_SN_RING * 128 * 4;           // [8 epilogue warps][2 boxes][32 rows x 32 B]
+    static constexpr int off_zflag = off_out + G2_EPI_WARPS * 2048;
     static constexpr int off_bar = off_zflag + G2_SN_RING * 4 * 4;
     static constexpr int n_bar = 2 * G2_STAGES + 2 * G2_BH_STAGES + 2 + 2 + G2_SN_RING;
     static constexpr int off_tmem = off_bar + n_bar * 8;
     static constexpr int total = off_tmem + 16;
 };
-static_assert(G2_STAGE_BYTES % 128 == 0 && Gemm2Smem::off_b % 128 == 0, "operands must be 128-byte aligned");
+static_assert(G2_STAGE_BYTES % 128 == 0 && Gemm2Smem::off_b % 128 == 0 && Gemm2Smem::off_out % 128 == 0,
+              "operands and store boxes must be 128-byte aligned");
 static_assert(Gemm2Smem::off_bar % 8 == 0, "barriers must be 8-byte aligned");
 static_assert(Gemm2Smem::total <= 227 * 1024, "shared memory budget");
 
@@ -81,8 +84,17 @@ __device__ __forceinline__ uint32_t g2_mapa(uint32_t local_addr, uint32_t rank) 
 __device__ __forceinline__ void g2_arrive_cluster(uint32_t cluster_addr) {
     asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
-// wait on a LOCAL barrier whose arrivals may come from the peer CTA
-__device__ __forceinline__ void g2_wait_cluster(uint64_t *bar, uint32_t parity) { mbar_wait(bar, parity); }
+// Wait with a suspend-time hint: the thread sleeps in hardware until the phase completes or the hint (ns) expires,
+// instead of re-issuing try_wait every few dozen cycles (polling was ~20 % of all issued instructions).
+__device__ __forceinline__ void g2_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "G2_WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+        "@!p bra G2_WAIT_%=;\n\t}" ::"r"(smem_u32(bar)),
+        "r"(parity), "r"(20000u)
+        : "memory");
+}
 __device__ __forceinline__ void g2_cluster_sync() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
@@ -177,8 +189,8 @@ __device__ __forceinline__ int g2_mad16(uint32_t hi, uint32_t lo) {      // 16*h
 }
 
 // Timeline stamps (PROF instantiation only; diagnostics): [cta 2][role 6][k-tile 16][event 8] SM clocks of one cluster
-constexpr int G2_PROF_KT = 16;
-__device__ long long g_g2_prof[2 * 6 * G2_PROF_KT * 8];
+constexpr int G2_PROF_KT = 32;
+__device__ long long g_g2_prof[2 * 6 * G2_PROF_KT * 8];      // [cta 2][role 6][global k-tile 32][event 8]
 constexpr int G2_PROF_CTAS = 4096;
 __device__ long long g_g2_cta[G2_PROF_CTAS * 6];      // per CTA: smid, entry, set up, main loop done, stored, exit (ns)
 __device__ __forceinline__ long long g2_globaltimer() {
@@ -213,23 +225,37 @@ __device__ __forceinline__ void g2_tma_2d_hint(void *dst_smem, const CUtensorMap
         : "memory");
 }
 
+__device__ __forceinline__ void g2_tma_store_2d(const CUtensorMap *map, const void *src_smem, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map),
+                 "r"(smem_u32(src_smem)), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void g2_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N_PENDING>
+__device__ __forceinline__ void g2_store_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N_PENDING) : "memory");
+}
+
+// PERSISTENT: one cluster per SM pair walks the (row-pair, column-block) tiles t = cluster, cluster + C, ...
+// (row-pairs fastest, so that clusters running at the same time share weight tiles in L2).  Every ring and both
+// TMEM accumulator stages keep running across tile boundaries (all roles count k-tiles globally), so the
+// producer / unpack / MMA warps are already inside the next tile while the epilogue warps finish and store the
+// previous one; there is no per-tile launch, TMEM allocation, cluster barrier or drain (those cost ~40 % of the
+// non-persistent version: profiles/).
 template <int NTL, bool DEBUG, bool PROF = false>
 __global__ void __launch_bounds__(G2_THREADS, 1)
 tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_constant__ CUtensorMap tm_meta,
-                  const uint8_t *__restrict__ w, ActStage st, float *__restrict__ y, int M, int N, int K,
-                  int32_t *__restrict__ dbg_isum) {
+                  const __grid_constant__ CUtensorMap tm_y, const uint8_t *__restrict__ w, ActStage st, int M, int N, int K,
+                  int MB2, int num_tiles, int32_t *__restrict__ dbg_isum) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int LBO = 256 * NTL;                               // K-chunk stride of B: (16*NTL rows) * 16 B
     constexpr int BGROUP = 2 * LBO;                              // one 32-group = 2 K-chunks
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int KT = K / TILE_K, NT = N / TILE_CH;
     const uint32_t rank = g2_ctarank();
-    const int mb = blockIdx.x;                                   // 128-row block of this CTA (pair = blocks 2p, 2p+1)
-    const int nt_pair = blockIdx.y * (2 * NTL);                  // first n-tile of the pair
-    const int nt0 = nt_pair + (int)rank * NTL;                   // first n-tile this CTA unpacks
-    const int ntl_r = max(0, min(NTL, NT - nt0));                // n-tiles actually present
-    const bool prof_on = PROF && blockIdx.y == gridDim.y / 2 && blockIdx.x < 2;
-    const int cta_id = (int)(blockIdx.y * gridDim.x + blockIdx.x);
+    const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+    const bool prof_on = PROF && cluster_id == num_clusters / 2;
+    const int cta_id = (int)blockIdx.x;
     if (PROF && threadIdx.x == G2_EPI_WARP0 * 32) {
         uint32_t smid;
         asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
@@ -241,6 +267,7 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
     uint8_t *sB = smem + Gemm2Smem::off_b;
     float *sSn = reinterpret_cast<float *>(smem + Gemm2Smem::off_sn);          // [ring][2 halves][64]
     int *sZflag = reinterpret_cast<int *>(smem + Gemm2Smem::off_zflag);        // [ring][2 halves][2 warps]
+    uint8_t *sOut = smem + Gemm2Smem::off_out;                                 // [epilogue warp][2][32 rows x 32 B]
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + Gemm2Smem::off_bar);
     uint64_t *full = bars, *empty = full + G2_STAGES, *bfull = empty + G2_STAGES, *bfree = bfull + G2_BH_STAGES,
              *accfull = bfree + G2_BH_STAGES, *accempty = accfull + 2, *snfull = accempty + 2;
@@ -265,6 +292,7 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_tiles) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_meta) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_y) : "memory");
     }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512)
@@ -287,19 +315,23 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         if (lane == 0) {
             constexpr uint32_t total_tx = (uint32_t)(G2_A_BYTES + NTL * TILE_BYTES + 2 * NTL * 160);
             const uint64_t pol_w = l2_policy_evict_first();
-            const uint8_t *a_src = reinterpret_cast<const uint8_t *>(st.codes) + (size_t)mb * KT * ACT_UNIT_BYTES;
-            int s = 0, u = 0;
-            for (int kt = 0; kt < KT; kt++) {
-                if (u > 0) mbar_wait(&empty[s], (uint32_t)((u - 1) & 1));
-                G2_STAMP(0, kt, 0);
-                uint8_t *stg = sStage + s * G2_STAGE_BYTES;
-                mbar_arrive_expect_tx(&full[s], total_tx);
-                bulk_g2s(stg, a_src, G2_A_BYTES, &full[s]);
-                g2_tma_2d_hint(stg + G2_A_BYTES, &tm_tiles, kt * (TILE_BYTES / 8), nt0, &full[s], pol_w);
-                g2_tma_2d(stg + G2_A_BYTES + G2_RAW_BYTES, &tm_meta, kt * (TILE_BYTES / 8) + TILE_NIB / 8, nt_pair, &full[s]);
-                a_src += ACT_UNIT_BYTES;
-                G2_STAMP(0, kt, 1);
-                if (++s == G2_STAGES) { s = 0; u++; }
+            int s = 0, u = 0, gk = 0;
+            for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+                const int mb = 2 * (t % MB2) + (int)rank, nt_pair = (t / MB2) * (2 * NTL), nt0 = nt_pair + (int)rank * NTL;
+                const uint8_t *a_src = reinterpret_cast<const uint8_t *>(st.codes) + (size_t)mb * KT * ACT_UNIT_BYTES;
+                for (int kt = 0; kt < KT; kt++, gk++) {
+                    if (u > 0) g2_wait(&empty[s], (uint32_t)((u - 1) & 1));
+                    G2_STAMP(0, gk, 0);
+                    uint8_t *stg = sStage + s * G2_STAGE_BYTES;
+                    mbar_arrive_expect_tx(&full[s], total_tx);
+                    bulk_g2s(stg, a_src, G2_A_BYTES, &full[s]);
+                    g2_tma_2d_hint(stg + G2_A_BYTES, &tm_tiles, kt * (TILE_BYTES / 8), nt0, &full[s], pol_w);
+                    g2_tma_2d(stg + G2_A_BYTES + G2_RAW_BYTES, &tm_meta, kt * (TILE_BYTES / 8) + TILE_NIB / 8, nt_pair,
+                              &full[s]);
+                    a_src += ACT_UNIT_BYTES;
+                    G2_STAMP(0, gk, 1);
+                    if (++s == G2_STAGES) { s = 0; u++; }
+                }
             }
         }
     } else if (warp == 1) {
@@ -307,19 +339,22 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         if (rank == 0 && lane == 0) {
             constexpr uint32_t idesc = umma_idesc_i8(2 * G2_BM, 32 * NTL, 1, 1);      // 256 x (32*NTL) x 32, s8 x s8
             const uint32_t stage_base = smem_u32(sStage), b_base = smem_u32(sB);
+            int my_tiles = 0;
+            for (int t = cluster_id; t < num_tiles; t += num_clusters) my_tiles++;
+            const int total_k = my_tiles * KT;
             int s = 0;
-            for (int kt = 0; kt < KT; kt++) {
-                const int as = kt & 1, u2 = kt >> 1;
-                G2_STAMP(1, kt, 0);
-                if (u2 > 0) mbar_wait(&accempty[as], (uint32_t)((u2 - 1) & 1));
-                G2_STAMP(1, kt, 1);
+            for (int gk = 0; gk < total_k; gk++) {
+                const int as = gk & 1, u2 = gk >> 1;
+                G2_STAMP(1, gk, 0);
+                if (u2 > 0) g2_wait(&accempty[as], (uint32_t)((u2 - 1) & 1));
+                G2_STAMP(1, gk, 1);
                 tc_fence_after();
                 const uint32_t d = tmem + as * 256;
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
-                    const int hq = 2 * kt + h, hs = hq & (G2_BH_STAGES - 1), v = hq / G2_BH_STAGES;
-                    mbar_wait(&bfull[hs], (uint32_t)(v & 1));      // also: both CTAs' stage s has landed
-                    G2_STAMP(1, kt, 2 + h);
+                    const int hs = 2 * (gk & 1) + h, v = gk >> 1;
+                    g2_wait(&bfull[hs], (uint32_t)(v & 1));      // also: both CTAs' stage s has landed
+                    G2_STAMP(1, gk, 2 + h);
                     tc_fence_after();
 #pragma unroll
                     for (int gl = 0; gl < 4; gl++) {
@@ -334,7 +369,7 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
                 }
                 umma_commit_2cta(&empty[s]);
                 umma_commit_2cta(&accfull[as]);
-                G2_STAMP(1, kt, 4);
+                G2_STAMP(1, gk, 4);
                 if (++s == G2_STAGES) s = 0;
             }
         }
@@ -346,7 +381,6 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         constexpr int PER_GROUP = 8 * NTL;
         const int gl_t = ut / PER_GROUP, rem_t = ut - gl_t * PER_GROUP;
         const int j_t = rem_t >> 3, c_t = rem_t & 7;
-        const bool has_chunk = (gl_t < 4) && (j_t < ntl_r);
         const bool warp_has_chunk = (uw * 32) < 4 * PER_GROUP;      // warp-uniform: any lane of this warp may have one
         const uint32_t bfull_leader = g2_mapa(smem_u32(bfull), 0);
         const int tile_off = G2_A_BYTES + j_t * TILE_BYTES;
@@ -355,54 +389,58 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         const int p_half = ut >> 6, p_j = (ut & 63) >> 3, p_c = ut & 7;
         const bool p_valid = p_j < NTL;                             // absent tiles were zero-filled by the copy
         const int p_off = G2_A_BYTES + G2_RAW_BYTES + (p_half * NTL + p_j) * 160;
-        int s = 0, u = 0;
-        for (int kt = 0; kt < KT; kt++) {
-            const int prole = (lane == 0 && (uw == 0 || uw == 7)) ? (uw == 0 ? 2 : 3) : -1;
-            if (prole >= 0) G2_STAMP(prole, kt, 0);
-            mbar_wait(&full[s], (uint32_t)(u & 1));
-            if (prole >= 0) G2_STAMP(prole, kt, 1);
-            const uint8_t *stg = sStage + s * G2_STAGE_BYTES;
-            if (uw < 4) {     // per-channel super-scale of all 16*NTL channels + zero-point presence flag
-                float sv = 0.0f;
-                int zf = 0;
-                if (p_valid) {
-                    const uint8_t *md = stg + p_off;
-                    sv = __half2float(*reinterpret_cast<const __half *>(md + 2 * p_c));
-                    const float zv = __half2float(*reinterpret_cast<const __half *>(md + 16 + 2 * p_c));
-                    const uint2 zc = *reinterpret_cast<const uint2 *>(md + 96 + p_c * 8);
-                    zf = (zv != 0.0f) && ((zc.x | zc.y) != 0u);
-                }
-                const int ring = kt & (G2_SN_RING - 1);
-                sSn[ring * 128 + ut] = sv;
-                const int anyz = __any_sync(0xffffffffu, zf);
-                __syncwarp();
-                if (lane == 0) {
-                    sZflag[ring * 4 + uw] = anyz;
-                    mbar_arrive(&snfull[ring]);      // release: epilogue(kt) acquires before reading
-                }
-            }
-#pragma unroll
-            for (int h = 0; h < 2; h++) {
-                const int hs = 2 * (kt & 1) + h, v = kt >> 1;
-                if (v > 0) mbar_wait(&bfree[hs], (uint32_t)((v - 1) & 1));
-                if (prole >= 0) G2_STAMP(prole, kt, 2 + 2 * h);
-                if (warp_has_chunk) {
-                    if (has_chunk) {
-                        const uint8_t *tp = stg + tile_off;
-                        const int g = h * 4 + gl_t;
-                        const uint4 wq = *reinterpret_cast<const uint4 *>(tp + g * 128 + c_t * 16);
-                        const int sc = *reinterpret_cast<const int8_t *>(tp + TILE_OFF_SC + c_t * 8 + g);
-                        uint8_t *row = sB + hs * G2_BH_BYTES + b_off;
-                        g2_unpack_chunk(wq, sc, row, row + NTL * 128, LBO);      // lo rows follow the 8*NTL hi rows
+        int s = 0, u = 0, gk = 0;
+        for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+            const int nt0 = (t / MB2) * (2 * NTL) + (int)rank * NTL;
+            const bool has_chunk = (gl_t < 4) && (j_t < NT - nt0);  // n-tiles beyond the tensor: nothing to unpack
+            for (int kt = 0; kt < KT; kt++, gk++) {
+                const int prole = (lane == 0 && (uw == 0 || uw == 7)) ? (uw == 0 ? 2 : 3) : -1;
+                if (prole >= 0) G2_STAMP(prole, gk, 0);
+                g2_wait(&full[s], (uint32_t)(u & 1));
+                if (prole >= 0) G2_STAMP(prole, gk, 1);
+                const uint8_t *stg = sStage + s * G2_STAGE_BYTES;
+                if (uw < 4) {     // per-channel super-scale of all 16*NTL channels + zero-point presence flag
+                    float sv = 0.0f;
+                    int zf = 0;
+                    if (p_valid) {
+                        const uint8_t *md = stg + p_off;
+                        sv = __half2float(*reinterpret_cast<const __half *>(md + 2 * p_c));
+                        const float zv = __half2float(*reinterpret_cast<const __half *>(md + 16 + 2 * p_c));
+                        const uint2 zc = *reinterpret_cast<const uint2 *>(md + 96 + p_c * 8);
+                        zf = (zv != 0.0f) && ((zc.x | zc.y) != 0u);
                     }
-                    fence_proxy_async_smem();
+                    const int ring = gk & (G2_SN_RING - 1);
+                    sSn[ring * 128 + ut] = sv;
+                    const int anyz = __any_sync(0xffffffffu, zf);
+                    __syncwarp();
+                    if (lane == 0) {
+                        sZflag[ring * 4 + uw] = anyz;
+                        mbar_arrive(&snfull[ring]);      // release: epilogue(gk) acquires before reading
+                    }
                 }
-                __syncwarp();
-                if (lane == 0) g2_arrive_cluster(bfull_leader + (uint32_t)hs * 8);
-                if (prole >= 0) G2_STAMP(prole, kt, 3 + 2 * h);
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int hs = 2 * (gk & 1) + h, v = gk >> 1;
+                    if (v > 0) g2_wait(&bfree[hs], (uint32_t)((v - 1) & 1));
+                    if (prole >= 0) G2_STAMP(prole, gk, 2 + 2 * h);
+                    if (warp_has_chunk) {
+                        if (has_chunk) {
+                            const uint8_t *tp = stg + tile_off;
+                            const int g = h * 4 + gl_t;
+                            const uint4 wq = *reinterpret_cast<const uint4 *>(tp + g * 128 + c_t * 16);
+                            const int sc = *reinterpret_cast<const int8_t *>(tp + TILE_OFF_SC + c_t * 8 + g);
+                            uint8_t *row = sB + hs * G2_BH_BYTES + b_off;
+                            g2_unpack_chunk(wq, sc, row, row + NTL * 128, LBO);      // lo rows follow the 8*NTL hi rows
+                        }
+                        fence_proxy_async_smem();
+                    }
+                    __syncwarp();
+                    if (lane == 0) g2_arrive_cluster(bfull_leader + (uint32_t)hs * 8);
+                    if (prole >= 0) G2_STAMP(prole, gk, 3 + 2 * h);
+                }
+                if (lane == 0) mbar_arrive(&empty[s]);      // after the __syncwarp above: every lane has read its raw bytes
+                if (++s == G2_STAGES) { s = 0; u++; }
             }
-            if (lane == 0) mbar_arrive(&empty[s]);      // after the __syncwarp above: every lane has read its raw bytes
-            if (++s == G2_STAGES) { s = 0; u++; }
         }
     } else {
         // ===================== epilogue =====================
@@ -410,95 +448,120 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
         const int colhalf = ew >> 2;                        // 0: channels unpacked by CTA 0, 1: by CTA 1
         const int row = quarter * 32 + lane;
-        const int m = mb * G2_BM + row;
-        const bool mvalid = m < M;
-        const int n_base = (nt_pair + colhalf * NTL) * TILE_CH;
         const uint32_t accempty_leader = g2_mapa(smem_u32(accempty), 0);
         const uint32_t t_base = tmem + ((uint32_t)(quarter * 32) << 16) + colhalf * (16 * NTL);
-        const float *a7p = st.a7 + (size_t)(mvalid ? m : 0) * KT;
+        uint8_t *obuf = sOut + ew * 2048;                   // two 32 x 32 B boxes per warp
         uint64_t acc2[4 * NTL];                             // 8*NTL fp32 accumulators as f32x2 pairs
+        int gk = 0;
+        int mb = 2 * (cluster_id % MB2) + (int)rank;
+        float a7 = 0.0f;
+        if (cluster_id < num_tiles && mb * G2_BM + row < M) a7 = st.a7[(size_t)(mb * G2_BM + row) * KT];
+        for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+            const int m = mb * G2_BM + row;
+            const bool mvalid = m < M;
+            const int n_base = ((t / MB2) * (2 * NTL) + colhalf * NTL) * TILE_CH;
+            const float *a7p = st.a7 + (size_t)(mvalid ? m : 0) * KT;
+            // first scale of the NEXT tile of this cluster (fetched during the last k-tile of this one)
+            const int t_next = t + num_clusters;
+            const int mb_next = 2 * (t_next % MB2) + (int)rank;
+            const int m_next = mb_next * G2_BM + row;
+            const float *a7_next = (t_next < num_tiles && m_next < M) ? st.a7 + (size_t)m_next * KT : nullptr;
 #pragma unroll
-        for (int i = 0; i < 4 * NTL; i++) acc2[i] = 0ull;
-
-        float a7 = mvalid ? a7p[0] : 0.0f;
-        for (int kt = 0; kt < KT; kt++) {
-            const int as = kt & 1, u2 = kt >> 1;
-            const float rm = a7 * (1.0f / 127.0f);          // row factor a7/127; column factor S[n]
-            const float a7_cur = a7;
-            if (kt + 1 < KT && mvalid) a7 = a7p[kt + 1];    // next block's scale: its latency hides under this block
-            const uint64_t rm2 = g2_pack(rm, rm);
-            const int ring = kt & (G2_SN_RING - 1);
-            const int erole = (lane == 0 && (ew == 0 || ew == 7)) ? (ew == 0 ? 4 : 5) : -1;
-            if (erole >= 0) G2_STAMP(erole, kt, 0);
-            mbar_wait(&snfull[ring], (uint32_t)((kt / G2_SN_RING) & 1));
-            mbar_wait(&accfull[as], (uint32_t)(u2 & 1));
-            if (erole >= 0) G2_STAMP(erole, kt, 1);
-            tc_fence_after();
-            const float *sn = sSn + ring * 128 + colhalf * 64;
-            const int anyz = sZflag[ring * 4 + colhalf * 2] | sZflag[ring * 4 + colhalf * 2 + 1];
-            const uint32_t t_hi = t_base + as * 256;
-#pragma unroll
-            for (int ch = 0; ch < NTL; ch++) {
-                uint32_t rh[8], rl[8];
-                tmem_ld_32x8(t_hi + ch * 8, rh);
-                tmem_ld_32x8(t_hi + 8 * NTL + ch * 8, rl);
-                // S[] of this k-tile is read BEFORE the stage is handed back (ring slot reuse, see tcq4_gemm.cu)
-                const ulonglong2 s01 = *reinterpret_cast<const ulonglong2 *>(sn + ch * 8);
-                const ulonglong2 s23 = *reinterpret_cast<const ulonglong2 *>(sn + ch * 8 + 4);
-                tmem_ld_wait();
-                if (ch == NTL - 1) {             // all TMEM reads of this stage are done: hand it back
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) g2_arrive_cluster(accempty_leader + (uint32_t)as * 8);
-                    if (erole >= 0) G2_STAMP(erole, kt, 2);
+            for (int i = 0; i < 4 * NTL; i++) acc2[i] = 0ull;
+            for (int kt = 0; kt < KT; kt++, gk++) {
+                const int as = gk & 1, u2 = gk >> 1;
+                const float rm = a7 * (1.0f / 127.0f);          // row factor a7/127; column factor S[n]
+                const float a7_cur = a7;
+                if (kt + 1 < KT) {
+                    if (mvalid) a7 = a7p[kt + 1];               // next block's scale: its latency hides under this block
+                } else {
+                    a7 = a7_next ? a7_next[0] : 0.0f;
                 }
-                const uint64_t sv2[4] = {s01.x, s01.y, s23.x, s23.y};
+                const uint64_t rm2 = g2_pack(rm, rm);
+                const int ring = gk & (G2_SN_RING - 1);
+                const int erole = (lane == 0 && (ew == 0 || ew == 7)) ? (ew == 0 ? 4 : 5) : -1;
+                if (erole >= 0) G2_STAMP(erole, gk, 0);
+                g2_wait(&snfull[ring], (uint32_t)((gk / G2_SN_RING) & 1));
+                g2_wait(&accfull[as], (uint32_t)(u2 & 1));
+                if (erole >= 0) G2_STAMP(erole, gk, 1);
+                tc_fence_after();
+                const float *sn = sSn + ring * 128 + colhalf * 64;
+                const int anyz = sZflag[ring * 4 + colhalf * 2] | sZflag[ring * 4 + colhalf * 2 + 1];
+                const uint32_t t_hi = t_base + as * 256;
 #pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const int is0 = g2_mad16(rh[2 * i], rl[2 * i]);             // = sum_g sc*dot, exact
-                    const int is1 = g2_mad16(rh[2 * i + 1], rl[2 * i + 1]);
-                    const uint64_t f2 = g2_mul2(g2_pack((float)is0, (float)is1), rm2);
-                    acc2[ch * 4 + i] = g2_fma2(f2, sv2[i], acc2[ch * 4 + i]);
-                    if (DEBUG) {
-                        const int n = n_base + ch * 8 + 2 * i;
-                        if (dbg_isum && mvalid && n < N) {
-                            dbg_isum[((size_t)m * N + n) * KT + kt] = is0;
-                            dbg_isum[((size_t)m * N + n + 1) * KT + kt] = is1;
+                for (int ch = 0; ch < NTL; ch++) {
+                    uint32_t rh[8], rl[8];
+                    tmem_ld_32x8(t_hi + ch * 8, rh);
+                    tmem_ld_32x8(t_hi + 8 * NTL + ch * 8, rl);
+                    // S[] of this k-tile is read BEFORE the stage is handed back (ring slot reuse, see tcq4_gemm.cu)
+                    const ulonglong2 s01 = *reinterpret_cast<const ulonglong2 *>(sn + ch * 8);
+                    const ulonglong2 s23 = *reinterpret_cast<const ulonglong2 *>(sn + ch * 8 + 4);
+                    tmem_ld_wait();
+                    if (ch == NTL - 1) {             // all TMEM reads of this stage are done: hand it back
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) g2_arrive_cluster(accempty_leader + (uint32_t)as * 8);
+                        if (erole >= 0) G2_STAMP(erole, gk, 2);
+                    }
+                    const uint64_t sv2[4] = {s01.x, s01.y, s23.x, s23.y};
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const int is0 = g2_mad16(rh[2 * i], rl[2 * i]);             // = sum_g sc*dot, exact
+                        const int is1 = g2_mad16(rh[2 * i + 1], rl[2 * i + 1]);
+                        const uint64_t f2 = g2_mul2(g2_pack((float)is0, (float)is1), rm2);
+                        acc2[ch * 4 + i] = g2_fma2(f2, sv2[i], acc2[ch * 4 + i]);
+                        if (DEBUG) {
+                            const int n = n_base + ch * 8 + 2 * i;
+                            if (dbg_isum && mvalid && n < N) {
+                                dbg_isum[((size_t)m * N + n) * KT + kt] = is0;
+                                dbg_isum[((size_t)m * N + n + 1) * KT + kt] = is1;
+                            }
+                        }
+                    }
+                }
+                if (erole >= 0) G2_STAMP(erole, gk, 3);
+                if (anyz && mvalid) {
+#pragma unroll
+                    for (int i = 0; i < 4 * NTL; i++) {
+                        const int n = n_base + 2 * i;
+                        if (n < N) {
+                            float a, b;
+                            g2_unpack(acc2[i], a, b);
+                            a += g2_zero_point_term(w, st.sumq, m, n, kt, KT, a7_cur);
+                            b += g2_zero_point_term(w, st.sumq, m, n + 1, kt, KT, a7_cur);
+                            acc2[i] = g2_pack(a, b);
                         }
                     }
                 }
             }
-            if (erole >= 0) G2_STAMP(erole, kt, 3);
-            if (anyz && mvalid) {
+            // ---- the tile's 32 rows x 8*NTL channels of this warp: one 32 x 32 B box per 8 channels through shared
+            //      memory and a tiled bulk store (rows >= M and channels >= N are clipped by the copy engine)
+            if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(3);
+            if (lane == 0) g2_store_wait_read<0>();         // both boxes are free again (stores of the previous tile)
+            __syncwarp();
+            const int row0 = mb * G2_BM + quarter * 32;
 #pragma unroll
-                for (int i = 0; i < 4 * NTL; i++) {
-                    const int n = n_base + 2 * i;
-                    if (n < N) {
-                        float a, b;
-                        g2_unpack(acc2[i], a, b);
-                        a += g2_zero_point_term(w, st.sumq, m, n, kt, KT, a7_cur);
-                        b += g2_zero_point_term(w, st.sumq, m, n + 1, kt, KT, a7_cur);
-                        acc2[i] = g2_pack(a, b);
-                    }
+            for (int ch = 0; ch < NTL; ch++) {
+                uint8_t *box = obuf + (ch & 1) * 1024;
+                if (ch >= 2) {
+                    if (lane == 0) g2_store_wait_read<1>(); // the store issued two chunks ago has read this box
+                    __syncwarp();
+                }
+                *reinterpret_cast<ulonglong2 *>(box + lane * 32) = make_ulonglong2(acc2[ch * 4 + 0], acc2[ch * 4 + 1]);
+                *reinterpret_cast<ulonglong2 *>(box + lane * 32 + 16) = make_ulonglong2(acc2[ch * 4 + 2], acc2[ch * 4 + 3]);
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    if (n_base + ch * 8 < N && row0 < M) g2_tma_store_2d(&tm_y, box, n_base + ch * 8, row0);
+                    g2_store_commit();
                 }
             }
+            if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(4);
+            mb = mb_next;
         }
-        if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(3);
-        if (mvalid) {
-            float *yrow = y + (size_t)m * N + n_base;
-#pragma unroll
-            for (int i = 0; i < 4 * NTL; i += 2) {
-                if (n_base + 2 * i < N) {       // N % 8 == 0: a chunk of 8 channels is entirely inside or outside
-                    float a, b, c, d;
-                    g2_unpack(acc2[i], a, b);
-                    g2_unpack(acc2[i + 1], c, d);
-                    *reinterpret_cast<float4 *>(yrow + 2 * i) = make_float4(a, b, c, d);
-                }
-            }
-        }
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");     // all stores complete before exit
     }
 
-    if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(4);
     tc_fence_before();
     g2_cluster_sync();
     if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(5);
@@ -506,26 +569,31 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
 }
 
+static int64_t g2_tiles(int64_t M, int64_t N, int ntl) {
+    const int64_t NT = N / TILE_CH, MB2 = (M + 2 * G2_BM - 1) / (2 * G2_BM);
+    return MB2 * ((NT + 2 * ntl - 1) / (2 * ntl));
+}
+
 bool gemm2_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, Gemm2Plan *plan) {
     (void)K;
     if (M < 1 || (size_t)Gemm2Smem::total > smem_optin || num_sms < 2) return false;
-    const int64_t NT = N / TILE_CH;
-    const int64_t MB2 = (M + 2 * G2_BM - 1) / (2 * G2_BM);
     const int64_t pairs = num_sms / 2;
-    // n-tiles per CTA: minimise (waves of pair-tiles) x (work per tile + a fixed fill/drain share)
+    // n-tiles per CTA: the persistent clusters each walk ceil(tiles / pairs) tiles of ntl n-tiles per CTA; a small
+    // per-tile term stands for the output store and for the narrower MMA's lower rate
     int best = G2_MAXNTL;
     int64_t best_cost = -1;
     for (int ntl = G2_MAXNTL; ntl >= G2_MINNTL; ntl--) {
-        const int64_t tiles = MB2 * ((NT + 2 * ntl - 1) / (2 * ntl));
-        const int64_t waves = (tiles + pairs - 1) / pairs;
-        const int64_t cost = waves * (ntl + 1);
+        const int64_t tiles = g2_tiles(M, N, ntl);
+        const int64_t rounds = (tiles + pairs - 1) / pairs;
+        const int64_t cost = rounds * (4 * ntl + 1);
         if (best_cost < 0 || cost < best_cost) {
             best_cost = cost;
             best = ntl;
         }
     }
     plan->ntl = best;
-    plan->grid = dim3((unsigned)(2 * MB2), (unsigned)((NT + 2 * best - 1) / (2 * best)), 1);
+    const int64_t tiles = g2_tiles(M, N, best);
+    plan->grid = dim3((unsigned)(2 * (tiles < pairs ? tiles : pairs)), 1, 1);
     plan->smem_bytes = Gemm2Smem::total;
     return true;
 }
@@ -557,25 +625,39 @@ static bool g2_make_map(CUtensorMap *map, const void *w, int64_t NT, int64_t KT,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// the fp32 output [M][N] with boxes of 32 rows x 8 channels
+static bool g2_make_y_map(CUtensorMap *map, float *y, int64_t M, int64_t N) {
+    G2EncodeTiled enc = g2_encoder();
+    if (!enc) return false;
+    const cuuint64_t gdim[2] = {(cuuint64_t)N, (cuuint64_t)M};
+    const cuuint64_t gstride[1] = {(cuuint64_t)N * sizeof(float)};
+    const cuuint32_t box[2] = {8, 32};
+    const cuuint32_t estr[2] = {1, 1};
+    return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, y, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <int NTL>
 static cudaError_t launch_gemm2_t(cudaLaunchConfig_t *cfg, const void *w_tiles, ActStage st, float *y, int64_t M, int64_t N,
                                   int64_t K, int32_t *dbg_isum) {
-    CUtensorMap tm_tiles, tm_meta;
+    CUtensorMap tm_tiles, tm_meta, tm_y;
     if (!g2_make_map(&tm_tiles, w_tiles, N / TILE_CH, K / TILE_K, TILE_BYTES / 8, NTL) ||
-        !g2_make_map(&tm_meta, w_tiles, N / TILE_CH, K / TILE_K, 160 / 8, 2 * NTL))
+        !g2_make_map(&tm_meta, w_tiles, N / TILE_CH, K / TILE_K, 160 / 8, 2 * NTL) || !g2_make_y_map(&tm_y, y, M, N))
         return cudaErrorInvalidValue;      // unaligned tensor base or no driver entry point
+    const int MB2 = (int)((M + 2 * G2_BM - 1) / (2 * G2_BM));
+    const int num_tiles = (int)g2_tiles(M, N, NTL);
     static const bool prof = getenv("TCQ4_G2_PROF") != nullptr;     // diagnostics: timeline stamps of one cluster
     if (prof && !dbg_isum) {
         cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              Gemm2Smem::total);
-        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, true>, tm_tiles, tm_meta, (const uint8_t *)w_tiles, st, y,
-                                  (int)M, (int)N, (int)K, (int32_t *)nullptr);
+        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, true>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles,
+                                  st, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
     }
     if (dbg_isum)
-        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, true>, tm_tiles, tm_meta, (const uint8_t *)w_tiles, st, y,
-                                  (int)M, (int)N, (int)K, dbg_isum);
-    return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false>, tm_tiles, tm_meta, (const uint8_t *)w_tiles, st, y, (int)M,
-                              (int)N, (int)K, (int32_t *)nullptr);
+        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, true>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st,
+                                  (int)M, (int)N, (int)K, MB2, num_tiles, dbg_isum);
+    return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st,
+                              (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
 }
 
 cudaError_t launch_gemm2(const void *w_tiles, ActStage st, float *y, int64_t M, int64_t N, int64_t K,
@@ -596,7 +678,11 @@ cudaError_t launch_gemm2(const void *w_tiles, ActStage st, float *y, int64_t M, 
     int ntl = plan.ntl;
     if (force_ntl >= G2_MINNTL && force_ntl <= G2_MAXNTL) {
         ntl = force_ntl;
-        cfg.gridDim.y = (unsigned)((N / TILE_CH + 2 * ntl - 1) / (2 * ntl));
+        int dev = 0, sms = 2;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        const int64_t tiles = g2_tiles(M, N, ntl), cap = sms / 2;
+        cfg.gridDim.x = (unsigned)(2 * (tiles < cap ? tiles : cap));
     }
     switch (ntl) {
         case 2: return launch_gemm2_t<2>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);

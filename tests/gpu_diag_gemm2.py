@@ -19,17 +19,17 @@ out = torch.empty((M, N), device="cuda")
 for _ in range(3):
     t4.mul_mat(tiles, x, N, out=out, workspace=ws, kernel=t4.KERNEL_GEMM2)
 torch.cuda.synchronize()
-raw = np.zeros(2 * 6 * 16 * 8 + 4096 * 6, dtype=np.int64)
+raw = np.zeros(2 * 6 * 32 * 8 + 4096 * 6, dtype=np.int64)
 rc = t4.LIB.tcq4_b200_debug_gemm2_timeline(raw.ctypes.data, raw.nbytes)
-buf = raw[:2 * 6 * 16 * 8].reshape(2, 6, 16, 8)
-cta = raw[2 * 6 * 16 * 8:].reshape(4096, 6)
+buf = raw[:2 * 6 * 32 * 8].reshape(2, 6, 32, 8)
+cta = raw[2 * 6 * 32 * 8:].reshape(4096, 6)
 cta = cta[cta[:, 1] > 0]
 if len(cta):
     t_first = cta[:, 1].min()
     d = cta[:, 1:] - t_first
     print(f"{len(cta)} CTAs; kernel span {int(d[:, 4].max())} ns")
     ph = np.diff(cta[:, 1:], axis=1)
-    for i, nm in enumerate(["setup", "main loop", "store y", "final sync"]):
+    for i, nm in enumerate(["setup", "to last tile's loop end", "store y", "final sync"]):
         print(f"   {nm:10s} median {int(np.median(ph[:, i])):6d} ns   p90 {int(np.percentile(ph[:, i], 90)):6d}   max {int(ph[:, i].max()):6d}")
     gaps = []
     for sm in np.unique(cta[:, 0]):
@@ -40,7 +40,7 @@ if len(cta):
         print(f"   gap between a CTA's exit and the next CTA's entry on the same SM: median {int(np.median(gaps))} ns, p90 {int(np.percentile(gaps, 90))}, max {int(max(gaps))}")
         per_sm = [int((cta[:, 0] == sm).sum()) for sm in np.unique(cta[:, 0])]
         print(f"   CTAs per SM: min {min(per_sm)} max {max(per_sm)}")
-KT = min(K // 256, 16)
+KT = min(3 * (K // 256), 32)
 names = {0: ("producer", ["empty_ok", "issued"]),
          1: ("mma", ["top", "accempty_ok", "bfull0_ok", "bfull1_ok", "committed"]),
          2: ("unpack w0", ["top", "full_ok", "bfree0_ok", "done0", "bfree1_ok", "done1"]),
