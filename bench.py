@@ -194,8 +194,9 @@ def run_reference_arm(args):
 class Chain:
     """The 252 matmuls of Qwen3-4B, N-sharded over `world` ranks (shard = contiguous tile byte range)."""
 
-    def __init__(self, t4, torch, M, world, rank, weights=None):
+    def __init__(self, t4, torch, M, world, rank, weights=None, gather=True):
         self.t4, self.torch, self.M, self.world, self.rank = t4, torch, M, world, rank
+        self.gather = gather                           # False: the sharded MUL_MATs alone (SURVEY 8e reports both)
         self.ops = []                                  # (sharded weight, K, N)
         if weights is None:
             weights = []
@@ -224,7 +225,7 @@ class Chain:
         last = None
         for w in self.weights:
             yl = w.local(self.x[w.K], out=self.y_local[w.N], workspace=self.ws)
-            last = w.gather(yl) if self.world > 1 else yl
+            last = w.gather(yl) if (self.world > 1 and self.gather) else yl
         return last
 
     def capture(self):
@@ -290,8 +291,9 @@ def kernel_leg(t4, torch, chain, steps, kernel, M):
 
 
 def e2e_leg(t4, torch, chain, steps, M):
-    """Same chain through the host-buffer C-ABI entry (tcq4_b200_mul_mat_host): per matmul an H2D copy of x
-    from pinned memory, the MUL_MAT, a D2H copy of y into pinned memory, stream sync."""
+    """Same chain through the host-buffer C-ABI entry (tcq4_b200_mul_mat_host_async + tcq4_b200_host_sync): per
+    matmul an H2D copy of x from pinned memory, the MUL_MAT, a D2H copy of y into pinned memory; the library
+    overlaps the copies of neighbouring calls with the kernels; one sync per step."""
     xh = {K: v.cpu().pin_memory() for K, v in chain.x.items()}
     yh = {N: torch.empty((M, v.shape[1]), dtype=torch.float32).pin_memory() for N, v in chain.y_local.items()}
     h2d = sum(4 * M * w.K for w in chain.weights)
@@ -299,7 +301,8 @@ def e2e_leg(t4, torch, chain, steps, M):
 
     def one():
         for w in chain.weights:
-            t4.mul_mat_host(w.tiles, xh[w.K], yh[w.N], w.n_local)
+            t4.mul_mat_host_async(w.tiles, xh[w.K], yh[w.N], w.n_local)
+        t4.host_sync()              # every y of the step is in host memory here
     one()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -323,6 +326,8 @@ def run_own_arm(args):
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"          # keep NCCL's version banner off stdout: one JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     t4 = graft.load_package()
     peaks = load_peaks()
@@ -343,6 +348,15 @@ def run_own_arm(args):
     ms_dec = timed_steps(torch, dist, dec, dec_steps, max(args.warmup, 3), world)
     torch.cuda.profiler.stop()
     clocks = sampler.stop() if rank == 0 else None
+    # ---- N > 1: the same chains without the fp32 all-gather (the sharded MUL_MATs alone; SURVEY 8e asks for both) ----
+    ms_step_ng = ms_dec_ng = None
+    if world > 1:
+        pre_ng = Chain(t4, torch, M, world, rank, weights=pre.weights, gather=False)
+        pre_ng.capture()
+        ms_step_ng = timed_steps(torch, dist, pre_ng, args.steps, args.warmup, world)
+        dec_ng = Chain(t4, torch, 1, world, rank, weights=pre.weights, gather=False)
+        dec_ng.capture()
+        ms_dec_ng = timed_steps(torch, dist, dec_ng, dec_steps, max(args.warmup, 3), world)
 
     # ---- per-kernel roofline legs (N-shard-local kernels; events on the launching stream) ----------------
     gm_ms, act_ms, gm_n = kernel_leg(t4, torch, pre, args.steps, t4.KERNEL_AUTO, M)
@@ -392,10 +406,16 @@ def run_own_arm(args):
                                 "unit": "GB/s", "frac": gv_gbs / peaks["hbm_gbs"], "traffic": None, "launches": gv_n,
                                 "avg_launch_us": gv_ms * 1e3 / max(1, gv_n), "peak_source": f"hbm_gbs ({peaks['source']})"},
             "e2e": {"value": M / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": e2e_s * 1e3, "api": "tcq4_b200_mul_mat_host per matmul (pinned host x and y)"},
+                    "ms_per_step": e2e_s * 1e3, "api": "tcq4_b200_mul_mat_host_async per matmul (pinned host x and y, copies inside the timed region) + tcq4_b200_host_sync per step"},
             "gpu_launches": int(pre.launches_per_step * args.steps),
             "clocks": clocks,
         }
+        if world > 1:
+            line["sharded_mul_mat_only"] = {
+                "note": "same chains without the fp32 all-gather of the N-sharded outputs (max over ranks)",
+                "value": M / (ms_step_ng * 1e-3), "unit": UNIT, "ms_per_step": ms_step_ng,
+                "tops": total_ops / (ms_step_ng * 1e-3) / 1e12,
+                "decode": {"value": 1.0 / (ms_dec_ng * 1e-3), "unit": UNIT, "ms_per_step": ms_dec_ng}}
         if world == 1 and not args.no_cpu_baseline:
             try:
                 line["cpu_baseline"] = cpu_baseline_leg()
@@ -403,8 +423,13 @@ def run_own_arm(args):
                 line["cpu_baseline"] = {"error": f"{type(e).__name__}: {e}"}
         print(json.dumps(line), flush=True)
     if world > 1:
+        # Captured graphs hold NCCL kernels; tearing the communicator down under them can block for minutes.
+        # Everything is measured and printed: synchronise, meet once more, and leave without the teardown.
+        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():

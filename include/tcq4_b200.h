@@ -102,6 +102,15 @@ TCQ4_B200_API int tcq4_b200_mul_mat_host(const void *w_tiles_dev, const float *x
                                          int64_t M, int64_t N, int64_t K, const int32_t *d_perm,
                                          cudaStream_t stream);
 
+/* Pipelined form of the same: returns once the work is queued.  Consecutive calls overlap the host->device copy
+ * of the next matmul, the kernels of the current one and the device->host copy of the previous one (three
+ * library-owned streams, double-buffered device staging), so both PCIe directions and the SMs are busy at once.
+ * x_host must stay unchanged and y_host must not be read until tcq4_b200_host_sync() returns TCQ4_OK.
+ * Pinned host memory is needed for the copies to be asynchronous.  Not capturable (it owns its streams). */
+TCQ4_B200_API int tcq4_b200_mul_mat_host_async(const void *w_tiles_dev, const float *x_host, float *y_host, int64_t M,
+                                               int64_t N, int64_t K, const int32_t *d_perm);
+TCQ4_B200_API int tcq4_b200_host_sync(void);
+
 /* Stand-alone activation stage.  Replaces tcq4_rrs_fwht_quantize_tc / tcq4_rrs_perm_fwht_quantize_tc
  * (tcq4_k32.cuh:79-94, tcq4_k32.cu:181-277): perm gather -> FWHT-256 -> 1/16 -> max-scale ->
  * int4 codes + per-group sums, written as block_rrs_int4_tc [M][K/256] (160 B each). */

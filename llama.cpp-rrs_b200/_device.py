@@ -15,7 +15,7 @@ import torch
 from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
                ACT_BLOCK_BYTES, TensorView, _check, shard_range, tile_bytes, workspace_size)
 
-__all__ = ["Workspace", "mul_mat", "mul_mat_debug", "mul_mat_host", "fwht_quantize_tc", "register_perm",
+__all__ = ["Workspace", "mul_mat", "mul_mat_debug", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
            "ggml_supports_op", "ShardedWeight", "random_tiles"]
 
@@ -98,6 +98,21 @@ def mul_mat_host(w_tiles: torch.Tensor, x_host: torch.Tensor, y_host: torch.Tens
     _check(LIB.tcq4_b200_mul_mat_host(w_tiles.data_ptr(), x_host.data_ptr(), y_host.data_ptr(), M, N, K, pp,
                                       _stream_ptr(stream)))
     return y_host
+
+
+def mul_mat_host_async(w_tiles: torch.Tensor, x_host: torch.Tensor, y_host: torch.Tensor, N: int,
+                       perm: torch.Tensor | None = None) -> None:
+    """Queue one host-buffer MUL_MAT on the library's copy/compute pipeline; y_host is valid after host_sync()."""
+    _req_cuda(w_tiles, torch.uint8, "w_tiles")
+    if x_host.is_cuda or y_host.is_cuda or x_host.dtype != torch.float32 or y_host.dtype != torch.float32:
+        raise ValueError("x_host / y_host must be float32 CPU tensors (pinned for asynchronous copies)")
+    M, K = x_host.shape
+    pp = perm.data_ptr() if perm is not None else 0
+    _check(LIB.tcq4_b200_mul_mat_host_async(w_tiles.data_ptr(), x_host.data_ptr(), y_host.data_ptr(), M, N, K, pp))
+
+
+def host_sync() -> None:
+    _check(LIB.tcq4_b200_host_sync())
 
 
 def fwht_quantize_tc(x: torch.Tensor, perm: torch.Tensor | None = None, stream=None) -> torch.Tensor:

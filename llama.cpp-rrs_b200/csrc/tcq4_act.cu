@@ -9,6 +9,8 @@
 // Two output formats:
 //   MODE_REF   : block_rrs_int4_tc [M][KT] (160 B), byte-compatible with the reference
 //   MODE_STAGE : s8 codes in the UMMA K-major layout the tcgen05 GEMM bulk-copies (tcq4_common.cuh)
+#include <cstdlib>
+
 #include "tcq4_common.cuh"
 #include "tcq4_kernels.h"
 
@@ -30,6 +32,9 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
 
     __shared__ __align__(16) float scratch_all[ACT_WARPS_PER_CTA * 256];
     float *scratch = scratch_all + (threadIdx.x >> 5) * 256;
+
+    pdl_launch_dependents();     // the GEMM behind this kernel may set itself up (it waits before reading the codes)
+    pdl_wait();                  // x and the staging arena belong to the previous kernel until here
 
     for (long long b = warp0; b < nblocks; b += nwarps) {
         const int m = (int)(b / KT);
@@ -73,23 +78,37 @@ static int act_grid(int64_t nblocks, int num_sms) {
     return (int)(ctas < cap ? ctas : cap);
 }
 
+template <typename Kern>
+static cudaError_t launch_act(Kern kern, int grid, cudaStream_t stream, const float *x, const int32_t *perm, int M, int K,
+                              ActBlockTC *out_ref, ActStage st) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(ACT_WARPS_PER_CTA * 32);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    static const bool no_pdl = getenv("TCQ4_NO_PDL") != nullptr;
+    cfg.numAttrs = no_pdl ? 0 : 1;
+    return cudaLaunchKernelEx(&cfg, kern, x, perm, M, K, out_ref, st);
+}
+
 cudaError_t launch_act_quant_ref(const float *x, const int32_t *perm, int64_t M, int64_t K, void *out_blocks,
                                  int num_sms, cudaStream_t stream) {
     const int64_t nblocks = M * (K / TILE_K);
     if (nblocks == 0) return cudaSuccess;
     ActStage none{nullptr, nullptr, nullptr};
-    tcq4_act_quant_kernel<MODE_REF><<<act_grid(nblocks, num_sms), ACT_WARPS_PER_CTA * 32, 0, stream>>>(
-        x, perm, (int)M, (int)K, reinterpret_cast<ActBlockTC *>(out_blocks), none);
-    return cudaGetLastError();
+    return launch_act(tcq4_act_quant_kernel<MODE_REF>, act_grid(nblocks, num_sms), stream, x, perm, (int)M, (int)K,
+                      reinterpret_cast<ActBlockTC *>(out_blocks), none);
 }
 
 cudaError_t launch_act_quant_stage(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st,
                                    int num_sms, cudaStream_t stream) {
     const int64_t nblocks = M * (K / TILE_K);
     if (nblocks == 0) return cudaSuccess;
-    tcq4_act_quant_kernel<MODE_STAGE><<<act_grid(nblocks, num_sms), ACT_WARPS_PER_CTA * 32, 0, stream>>>(
-        x, perm, (int)M, (int)K, nullptr, st);
-    return cudaGetLastError();
+    return launch_act(tcq4_act_quant_kernel<MODE_STAGE>, act_grid(nblocks, num_sms), stream, x, perm, (int)M, (int)K,
+                      (ActBlockTC *)nullptr, st);
 }
 
 }  // namespace tcq4

@@ -146,7 +146,11 @@ int select_kernel(const DevInfo *d, int64_t M, int64_t N, int64_t K, tcq4::GemvP
     const size_t optin = d ? d->smem_optin : (size_t)232448;
     tcq4::GemvPlan tmp;
     if (tcq4::gemv_plan(M, N, K, sms, optin, gv ? gv : &tmp)) return TCQ4_KERNEL_GEMV;
-    return M > 128 ? TCQ4_KERNEL_GEMM2 : TCQ4_KERNEL_GEMM;
+    // 17 <= M <= 128: the single-CTA GEMM (128-row tiles, every SM busy) only wins on wide, shallow matrices;
+    // elsewhere the persistent pair GEMM is up to 2x faster even with its second row block empty (measured:
+    // profiles/, "M <= 128")
+    if (M <= 128 && N >= 8192 && K <= 4096) return TCQ4_KERNEL_GEMM;
+    return TCQ4_KERNEL_GEMM2;
 }
 
 int run_mul_mat(const void *w, const float *x, float *y, int64_t M, int64_t N, int64_t K, const int32_t *perm,
@@ -383,6 +387,98 @@ int tcq4_b200_mul_mat_host(const void *w_tiles_dev, const float *x_host, float *
     if (e != cudaSuccess) return cuda_fail(e, "D2H copy");
     e = cudaStreamSynchronize(stream);
     if (e != cudaSuccess) return cuda_fail(e, "stream sync");
+    return TCQ4_OK;
+}
+
+// ---- pipelined host-buffer path ---------------------------------------------------------------------------------
+// A caller with HOST activations (the end-to-end leg of bench.py; a CPU-resident ggml graph handing single
+// MUL_MATs to this device) queues matmuls back to back: the H2D copy of call i+1, the kernels of call i and the D2H
+// copy of call i-1 run on three library-owned streams over double-buffered staging, so PCIe moves in both
+// directions while the SMs compute.  Results are valid after tcq4_b200_host_sync().
+namespace {
+struct HostPipe {
+    bool ready = false;
+    cudaStream_t s_in = nullptr, s_cmp = nullptr, s_out = nullptr;
+    cudaEvent_t in_done[2] = {nullptr, nullptr}, cmp_done[2] = {nullptr, nullptr}, out_done[2] = {nullptr, nullptr};
+    float *hx[2] = {nullptr, nullptr}, *hy[2] = {nullptr, nullptr};
+    size_t hx_bytes[2] = {0, 0}, hy_bytes[2] = {0, 0};
+    uint64_t n = 0;
+};
+HostPipe g_pipe[MAX_DEV];
+
+cudaError_t pipe_init(HostPipe &p) {
+    if (p.ready) return cudaSuccess;
+    cudaError_t e;
+    if ((e = cudaStreamCreateWithFlags(&p.s_in, cudaStreamNonBlocking)) != cudaSuccess) return e;
+    if ((e = cudaStreamCreateWithFlags(&p.s_cmp, cudaStreamNonBlocking)) != cudaSuccess) return e;
+    if ((e = cudaStreamCreateWithFlags(&p.s_out, cudaStreamNonBlocking)) != cudaSuccess) return e;
+    for (int i = 0; i < 2; i++) {
+        if ((e = cudaEventCreateWithFlags(&p.in_done[i], cudaEventDisableTiming)) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&p.cmp_done[i], cudaEventDisableTiming)) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&p.out_done[i], cudaEventDisableTiming)) != cudaSuccess) return e;
+    }
+    p.ready = true;
+    return cudaSuccess;
+}
+cudaError_t pipe_grow(HostPipe &p, float **buf, size_t *have, size_t need) {
+    if (*have >= need) return cudaSuccess;
+    cudaError_t e = cudaDeviceSynchronize();      // rare: only when a larger shape than any before arrives
+    if (e != cudaSuccess) return e;
+    if (*buf) cudaFree(*buf);
+    *buf = nullptr;
+    *have = 0;
+    e = cudaMalloc(buf, need);
+    if (e == cudaSuccess) *have = need;
+    (void)p;
+    return e;
+}
+}  // namespace
+
+int tcq4_b200_mul_mat_host_async(const void *w_tiles_dev, const float *x_host, float *y_host, int64_t M, int64_t N,
+                                 int64_t K, const int32_t *d_perm) {
+    if (!shape_ok(M, N, K) || !x_host || !y_host) {
+        set_err("mul_mat_host_async: bad shape or null host pointer");
+        return TCQ4_ERR_SHAPE;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    HostPipe &p = g_pipe[dev];
+    cudaError_t e = pipe_init(p);
+    if (e != cudaSuccess) return cuda_fail(e, "host pipeline setup");
+    const size_t xb = (size_t)M * K * 4, yb = (size_t)M * N * 4;
+    const int slot = (int)(p.n & 1);
+    if ((e = pipe_grow(p, &p.hx[slot], &p.hx_bytes[slot], xb)) != cudaSuccess) return cuda_fail(e, "x staging cudaMalloc");
+    if ((e = pipe_grow(p, &p.hy[slot], &p.hy_bytes[slot], yb)) != cudaSuccess) return cuda_fail(e, "y staging cudaMalloc");
+    if (p.n >= 2) {
+        cudaStreamWaitEvent(p.s_in, p.cmp_done[slot], 0);      // the kernels of call n-2 have read this x slot
+        cudaStreamWaitEvent(p.s_cmp, p.out_done[slot], 0);     // the D2H copy of call n-2 has drained this y slot
+    }
+    if ((e = cudaMemcpyAsync(p.hx[slot], x_host, xb, cudaMemcpyHostToDevice, p.s_in)) != cudaSuccess)
+        return cuda_fail(e, "H2D copy");
+    cudaEventRecord(p.in_done[slot], p.s_in);
+    cudaStreamWaitEvent(p.s_cmp, p.in_done[slot], 0);
+    status = tcq4_b200_mul_mat(w_tiles_dev, p.hx[slot], p.hy[slot], M, N, K, d_perm, p.s_cmp);
+    if (status != TCQ4_OK) return status;
+    cudaEventRecord(p.cmp_done[slot], p.s_cmp);
+    cudaStreamWaitEvent(p.s_out, p.cmp_done[slot], 0);
+    if ((e = cudaMemcpyAsync(y_host, p.hy[slot], yb, cudaMemcpyDeviceToHost, p.s_out)) != cudaSuccess)
+        return cuda_fail(e, "D2H copy");
+    cudaEventRecord(p.out_done[slot], p.s_out);
+    p.n++;
+    return TCQ4_OK;
+}
+
+int tcq4_b200_host_sync(void) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEV) return TCQ4_ERR_NO_DEVICE;
+    HostPipe &p = g_pipe[dev];
+    if (!p.ready) return TCQ4_OK;
+    cudaError_t e = cudaStreamSynchronize(p.s_out);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(p.s_cmp);
+    if (e != cudaSuccess) return cuda_fail(e, "host pipeline sync");
     return TCQ4_OK;
 }
 

@@ -304,6 +304,8 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(2);
+    pdl_launch_dependents();     // the next kernel of the stream may set itself up behind this one
+    pdl_wait();                  // codes / scales (activation kernel) and y belong to earlier kernels until here
 
     if (warp == 0) {
         // ===================== producer: three copies per k-tile =====================
@@ -667,13 +669,16 @@ cudaError_t launch_gemm2(const void *w_tiles, ActStage st, float *y, int64_t M, 
     cfg.blockDim = dim3(G2_THREADS);
     cfg.dynamicSmemBytes = plan.smem_bytes;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    static const bool no_pdl = getenv("TCQ4_NO_PDL") != nullptr;
+    cfg.numAttrs = no_pdl ? 1 : 2;
     static const int force_ntl = getenv("TCQ4_G2_NTL") ? atoi(getenv("TCQ4_G2_NTL")) : 0;     // experiments only
     int ntl = plan.ntl;
     if (force_ntl >= G2_MINNTL && force_ntl <= G2_MAXNTL) {

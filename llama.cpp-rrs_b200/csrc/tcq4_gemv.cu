@@ -49,8 +49,6 @@ struct GvSplit {    // even split of T items over W workers, contiguous
     __host__ __device__ int count(int w) const { return base + (w < rem ? 1 : 0); }
 };
 
-__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));

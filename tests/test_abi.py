@@ -35,6 +35,8 @@ def test_supports_and_select(t4):
     assert t4.select_kernel(17, 9728, 2560) == t4.KERNEL_GEMM
     assert t4.select_kernel(128, 9728, 2560) == t4.KERNEL_GEMM
     assert t4.select_kernel(512, 9728, 2560) == t4.KERNEL_GEMM2
+    assert t4.select_kernel(64, 2560, 9728) == t4.KERNEL_GEMM2      # deep or narrow matrices: the pair GEMM
+    assert t4.select_kernel(64, 1024, 2560) == t4.KERNEL_GEMM2
     assert t4.select_kernel(4, 1024, 65536) == t4.KERNEL_GEMM      # codes do not fit shared memory
 
 

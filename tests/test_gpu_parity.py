@@ -383,6 +383,25 @@ def test_host_entry_matches_device_entry(t4, orc):
         assert torch.equal(yh, yd.cpu())
 
 
+def test_pipelined_host_entry_matches_device_entry(t4, orc):
+    """Queued host-buffer matmuls (copies and kernels of different calls overlap) give the device entry's bits,
+    including when slots are reused with different shapes."""
+    rng = np.random.default_rng(151)
+    cases = []
+    for i, (M, N, K) in enumerate([(3, 256, 512), (150, 512, 256), (1, 1024, 512), (300, 256, 1024), (17, 512, 512),
+                                   (260, 1024, 256)]):
+        tiles = _dev(orc.quantize_tiles(make_weights(rng, N, K)))
+        xh = torch.from_numpy(make_acts(rng, M, K)).pin_memory()
+        yh = torch.full((M, N), float("nan"), dtype=torch.float32).pin_memory()
+        cases.append((tiles, xh, yh, N))
+    for rep in range(2):
+        for tiles, xh, yh, N in cases:
+            t4.mul_mat_host_async(tiles, xh, yh, N)
+        t4.host_sync()
+        for tiles, xh, yh, N in cases:
+            assert torch.equal(yh, t4.mul_mat(tiles, xh.cuda(), N).cpu())
+
+
 def test_cuda_graph_capture(t4, orc):
     """Launches are capture-safe: no allocation / sync on the path (ggml-cuda.cu:3791-3799)."""
     rng = np.random.default_rng(16)
