@@ -63,14 +63,13 @@ __device__ __forceinline__ uint32_t dsmem_addr(const void *p, uint32_t rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(rank));
     return r;
 }
-__device__ __forceinline__ void dsmem_st_f2(uint32_t addr, float a, float b) {
-    asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
-}
-__device__ __forceinline__ void dsmem_st_f(uint32_t addr, float a) {
-    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(a) : "memory");
-}
-__device__ __forceinline__ void dsmem_st_i(uint32_t addr, int v) {
-    asm volatile("st.shared::cluster.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+// Asynchronous 4-byte store into a CTA of the cluster that also counts its bytes on an mbarrier of that CTA: the
+// receiver learns "all partials have landed" from the barrier's transaction count -- no cluster barrier, no fence
+// (barrier.cluster.arrive.release costs MEMBAR.ALL.GPU, ~1 us on the critical path of every decode launch).
+__device__ __forceinline__ void dsmem_st_async(uint32_t addr, uint32_t v, uint32_t bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(addr), "r"(v),
+                 "r"(bar)
+                 : "memory");
 }
 
 // D(16x8, s32) = A(16x32, s8, row) * B(32x8, s8, col); rows 8..15 of A are a1/a3
@@ -84,7 +83,7 @@ __device__ __forceinline__ void mma_s8(int (&d)[4], uint32_t a0, uint32_t a1, ui
 
 // shared-memory carve-up (bytes), shared by the kernel and the planner
 struct GvSmem {
-    int off_ring, off_full, off_afrag, off_rm, off_sumq, off_part, off_prow, off_scratch, total;
+    int off_ring, off_full, off_afrag, off_rm, off_sumq, off_part, off_prow, off_cbar, off_scratch, total;
     __host__ __device__ static int al(int o) { return (o + 15) & ~15; }
     __host__ __device__ GvSmem(int M, int KT) {
         int o = 0;
@@ -95,6 +94,7 @@ struct GvSmem {
         off_sumq = o;    o = al(o + M * KT * 8 * 4);                     // [M][KT][8] group sums (zero-point path)
         off_part = o;    o = al(o + GV_ENTRIES * M * 32);                // [entry][M rows][8 ch] fp32 (used in CTA 0)
         off_prow = o;    o = al(o + GV_ENTRIES * 4);                     // [entry] n-tile or -1
+        off_cbar = o;    o = al(o + 8);                                  // (CTA 0) "all partial rows have landed"
         off_scratch = o; o = al(o + GV_WARPS * 1024);                    // FWHT transposition scratch, 1 KB per warp
         total = o;
     }
@@ -145,6 +145,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     int *sumq = reinterpret_cast<int *>(smem + L.off_sumq);            // [M][KT][8]
     float *part = reinterpret_cast<float *>(smem + L.off_part);        // [entry][M][8]   (CTA 0's copy is the live one)
     int *prow = reinterpret_cast<int *>(smem + L.off_prow);            // [entry] n-tile or -1
+    uint64_t *cbar = reinterpret_cast<uint64_t *>(smem + L.off_cbar);
 
     // ---- work split: whole rows per cluster, tiles evenly over the cluster's 32 warps ------------------
     const int crank = (int)cluster_ctarank();
@@ -156,7 +157,13 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     const int lt0 = wsp.start(wid), cnt = wsp.count(wid);
 
     GV_STAMP(0);
-    if (threadIdx.x < GV_ENTRIES) prow[threadIdx.x] = -1;
+    // CTA 0 collects the cut rows of the whole cluster: every warp of the cluster sends both of its entry slots
+    // (used or not), so the byte total is fixed and the barrier can be armed before anything else happens
+    if (crank == 0 && threadIdx.x == 0) {
+        mbar_init(cbar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_arrive_expect_tx(cbar, (uint32_t)(GV_ENTRIES * (M * 32 + 4)));
+    }
 
     // ---- weight prefetch: constant data, legal before the programmatic dependency resolves -----------
     // Each warp owns its ring and its barriers: lane 0 initialises them and issues the first copies without
@@ -177,8 +184,9 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
         }
     }
     __syncwarp();
-    // first half of a cluster barrier: "my prow[] is initialised" (the peer waits before its first remote store)
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    // first half of a cluster barrier: "CTA 0 is running and its collection barrier is initialised" (execution
+    // ordering only -- the init was published by fence.mbarrier_init -- so the relaxed form, which has no fence)
+    asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
     GV_STAMP(1);
     pdl_launch_dependents();     // the next MUL_MAT may start its own prefetch on this SM
     pdl_wait();                  // x belongs to the previous kernel until here
@@ -222,7 +230,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     int nseg = 0;
     int nt = R0 + lt0 / KT, kt = lt0 % KT;
     bool from_row_start = (kt == 0);
-    const uint32_t part0 = dsmem_addr(part, 0), prow0 = dsmem_addr(prow, 0);    // CTA 0's copies
+    const uint32_t part0 = dsmem_addr(part, 0), prow0 = dsmem_addr(prow, 0), cbar0 = dsmem_addr(cbar, 0);    // CTA 0's copies
     const uint32_t ring_u32 = smem_u32(myring), full_u32 = smem_u32(myfull);
     const uint2 *af0 = afrag + brow0 * 4 + q;                  // + ((kt*8 + g) * M) * 4
     const uint2 *af1 = afrag + brow1 * 4 + q;
@@ -320,8 +328,9 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
 #pragma unroll
                     for (int j = 0; j < 2; j++)
                         if (8 * mb + tk0 + j < M)
-                            dsmem_st_f(part0 + (uint32_t)(((e * M + 8 * mb + tk0 + j) * 8 + c) * 4), acc[mb][j]);
-                if (lane == 0) dsmem_st_i(prow0 + (uint32_t)(e * 4), nt);
+                            dsmem_st_async(part0 + (uint32_t)(((e * M + 8 * mb + tk0 + j) * 8 + c) * 4),
+                                           __float_as_uint(acc[mb][j]), cbar0);
+                if (lane == 0) dsmem_st_async(prow0 + (uint32_t)(e * 4), (uint32_t)nt, cbar0);
                 nseg++;
             }
 #pragma unroll
@@ -336,8 +345,19 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
         }
     }
     (void)tk1;
+    // unused entry slots are sent too (row = -1, zeros): the byte total CTA 0 waits for is fixed
+    for (; nseg < 2; nseg++) {
+        const int e = wid * 2 + nseg;
+#pragma unroll
+        for (int mb = 0; mb < MB; mb++)
+#pragma unroll
+            for (int j = 0; j < 2; j++)
+                if (8 * mb + tk0 + j < M) dsmem_st_async(part0 + (uint32_t)(((e * M + 8 * mb + tk0 + j) * 8 + c) * 4), 0u, cbar0);
+        if (lane == 0) dsmem_st_async(prow0 + (uint32_t)(e * 4), 0xFFFFFFFFu, cbar0);
+    }
     GV_STAMP(4);
-    cluster_sync_all();          // all partials (local and remote) have landed in CTA 0
+    if (crank != 0) return;      // nothing reads this CTA's shared memory: CTA 1 is done
+    mbar_wait(cbar, 0u);         // all partials (local and remote) have landed in CTA 0
 
     // ---- CTA 0 combines the cut rows in k order (entry order = worker order = tile order) ----------------
     if (crank == 0) {
