@@ -243,14 +243,20 @@ class ShardedWeight:
         if self.world == 1:
             return yl
         if self.even:
-            gathered = torch.empty((self.world, M, self.n_local), dtype=yl.dtype, device=yl.device)
-            dist.all_gather_into_tensor(gathered, yl.contiguous())
+            flat = torch.empty((self.world * M, self.n_local), dtype=yl.dtype, device=yl.device)
+            dist.all_gather_into_tensor(flat, yl.contiguous())      # rank-major concatenation (NCCL and gloo agree)
             if M == 1:
-                return gathered.reshape(1, self.N)
-            return gathered.permute(1, 0, 2).reshape(M, self.N)
-        parts = [torch.empty((M, b - a), dtype=yl.dtype, device=yl.device) for a, b in self.ranges]
-        dist.all_gather(parts, yl.contiguous())
-        return torch.cat(parts, dim=1)
+                return flat.reshape(1, self.N)
+            return flat.view(self.world, M, self.n_local).permute(1, 0, 2).reshape(M, self.N)
+        # uneven shards (N not a multiple of world * align): pad every block to the widest one, one collective
+        n_max = max(b - a for a, b in self.ranges)
+        mine = torch.zeros((M, n_max), dtype=yl.dtype, device=yl.device)
+        if self.n_local:
+            mine[:, :self.n_local] = yl
+        flat = torch.empty((self.world * M, n_max), dtype=yl.dtype, device=yl.device)
+        dist.all_gather_into_tensor(flat, mine)
+        blocks = flat.view(self.world, M, n_max)
+        return torch.cat([blocks[r, :, :b - a] for r, (a, b) in enumerate(self.ranges)], dim=1)
 
     def forward(self, x: torch.Tensor, perm=None, workspace=None) -> torch.Tensor:
         return self.gather(self.local(x, perm, workspace=workspace))

@@ -44,7 +44,14 @@ constexpr int G2_A_BYTES = ACT_UNIT_BYTES;                                  // 3
 constexpr int G2_RAW_BYTES = G2_MAXNTL * TILE_BYTES;                        // 9472: own tiles
 constexpr int G2_META_BYTES = 2 * G2_MAXNTL * 160;                          // 2560: S, Z, sc, zc of the pair's 2*NTL tiles
 constexpr int G2_STAGE_BYTES = G2_A_BYTES + G2_RAW_BYTES + G2_META_BYTES;   // 44800
-constexpr int G2_STAGES = 3;
+#ifndef TCQ4_G2_STAGES
+#define TCQ4_G2_STAGES 3
+#endif
+#ifndef TCQ4_G2_OUT_BOXES
+#define TCQ4_G2_OUT_BOXES 2      /* 2 load stages + 6 boxes was measured: 10 % slower (the load ring is the wrong place to save) */
+#endif
+constexpr int G2_STAGES = TCQ4_G2_STAGES;
+constexpr int G2_OUT_BOXES = TCQ4_G2_OUT_BOXES;                             // 32 x 32 B store boxes per epilogue warp
 constexpr int G2_BH_BYTES = 16384;                                          // one half k-tile (4 groups) of B at NTL = 8
 constexpr int G2_BH_STAGES = 4;
 constexpr int G2_SN_RING = 8;
@@ -53,8 +60,8 @@ struct Gemm2Smem {
     static constexpr int off_stage = 0;                                     // [stage]{A | raw | meta}
     static constexpr int off_b = off_stage + G2_STAGES * G2_STAGE_BYTES;    // 134400
     static constexpr int off_sn = off_b + G2_BH_STAGES * G2_BH_BYTES;       // 199936
-    static constexpr int off_out = off_sn + G2_SN_RING * 128 * 4;           // [8 epilogue warps][2 boxes][32 rows x 32 B]
-    static constexpr int off_zflag = off_out + G2_EPI_WARPS * 2048;
+    static constexpr int off_out = off_sn + G2_SN_RING * 128 * 4;           // [8 epilogue warps][boxes][32 rows x 32 B]
+    static constexpr int off_zflag = off_out + G2_EPI_WARPS * G2_OUT_BOXES * 1024;
     static constexpr int off_bar = off_zflag + G2_SN_RING * 4 * 4;
     static constexpr int n_bar = 2 * G2_STAGES + 2 * G2_BH_STAGES + 2 + 2 + G2_SN_RING;
     static constexpr int off_tmem = off_bar + n_bar * 8;
@@ -452,7 +459,7 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         const int row = quarter * 32 + lane;
         const uint32_t accempty_leader = g2_mapa(smem_u32(accempty), 0);
         const uint32_t t_base = tmem + ((uint32_t)(quarter * 32) << 16) + colhalf * (16 * NTL);
-        uint8_t *obuf = sOut + ew * 2048;                   // two 32 x 32 B boxes per warp
+        uint8_t *obuf = sOut + ew * (G2_OUT_BOXES * 1024);  // this warp's 32 x 32 B store boxes
         uint64_t acc2[4 * NTL];                             // 8*NTL fp32 accumulators as f32x2 pairs
         int gk = 0;
         int mb = 2 * (cluster_id % MB2) + (int)rank;
@@ -539,14 +546,14 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
             // ---- the tile's 32 rows x 8*NTL channels of this warp: one 32 x 32 B box per 8 channels through shared
             //      memory and a tiled bulk store (rows >= M and channels >= N are clipped by the copy engine)
             if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(3);
-            if (lane == 0) g2_store_wait_read<0>();         // both boxes are free again (stores of the previous tile)
+            if (lane == 0) g2_store_wait_read<0>();         // the boxes are free again (stores of the previous tile)
             __syncwarp();
             const int row0 = mb * G2_BM + quarter * 32;
 #pragma unroll
             for (int ch = 0; ch < NTL; ch++) {
-                uint8_t *box = obuf + (ch & 1) * 1024;
-                if (ch >= 2) {
-                    if (lane == 0) g2_store_wait_read<1>(); // the store issued two chunks ago has read this box
+                uint8_t *box = obuf + (ch % G2_OUT_BOXES) * 1024;
+                if (ch >= G2_OUT_BOXES) {
+                    if (lane == 0) g2_store_wait_read<G2_OUT_BOXES - 1>();     // the store that used this box has read it
                     __syncwarp();
                 }
                 *reinterpret_cast<ulonglong2 *>(box + lane * 32) = make_ulonglong2(acc2[ch * 4 + 0], acc2[ch * 4 + 1]);
