@@ -36,9 +36,9 @@ namespace tcq4 {
 constexpr int G2_BM = 128;                  // tokens per CTA (256 per pair)
 constexpr int G2_MAXNTL = 8;                // n-tiles per CTA (8 channels each)
 constexpr int G2_MINNTL = 2;
-constexpr int G2_UNPACK_WARP0 = 2, G2_UNPACK_WARPS = 8;
+constexpr int G2_UNPACK_WARP0 = 4, G2_UNPACK_WARPS = 8;     // warps 0..3: producer, MMA issuer, two idle (warpgroup-aligned roles)
 constexpr int G2_EPI_WARP0 = G2_UNPACK_WARP0 + G2_UNPACK_WARPS, G2_EPI_WARPS = 8;
-constexpr int G2_THREADS = (G2_EPI_WARP0 + G2_EPI_WARPS) * 32;             // 18 warps
+constexpr int G2_THREADS = (G2_EPI_WARP0 + G2_EPI_WARPS) * 32;             // 20 warps = 5 warpgroups
 
 constexpr int G2_A_BYTES = ACT_UNIT_BYTES;                                  // 32768
 constexpr int G2_RAW_BYTES = G2_MAXNTL * TILE_BYTES;                        // 9472: own tiles
@@ -310,11 +310,16 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
     g2_cluster_sync();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
+    // Register re-balance between the warpgroups (the kernel launches with 96 per thread): the epilogue keeps 64
+    // fp32 accumulators and wants two TMEM chunks in flight, everybody else needs few.
+    // (setmaxnreg is the first instruction of each warpgroup's role branch below)
     if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(2);
     pdl_launch_dependents();     // the next kernel of the stream may set itself up behind this one
     pdl_wait();                  // codes / scales (activation kernel) and y belong to earlier kernels until here
 
-    if (warp == 0) {
+    if (warp < G2_UNPACK_WARP0) {
+      asm volatile("setmaxnreg.dec.sync.aligned.u32 56;" ::: "memory");
+      if (warp == 0) {
         // ===================== producer: three copies per k-tile =====================
         //   the CTA's activation unit (32 KB, contiguous), its NTL raw tiles and the 160 metadata bytes of all 2*NTL
         //   tiles of the pair.  The tensor is viewed as a 2-D array of 8-byte words [n-tile][KT*148]; one tiled
@@ -343,7 +348,7 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
                 }
             }
         }
-    } else if (warp == 1) {
+      } else if (warp == 1) {
         // ===================== MMA issuer (leader CTA only) =====================
         if (rank == 0 && lane == 0) {
             constexpr uint32_t idesc = umma_idesc_i8(2 * G2_BM, 32 * NTL, 1, 1);      // 256 x (32*NTL) x 32, s8 x s8
@@ -382,7 +387,9 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
                 if (++s == G2_STAGES) s = 0;
             }
         }
+      }
     } else if (warp < G2_EPI_WARP0) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;" ::: "memory");
         // ===================== weight unpack (this CTA's NTL n-tiles) =====================
         const int uw = warp - G2_UNPACK_WARP0;
         const int ut = threadIdx.x - G2_UNPACK_WARP0 * 32;          // 0..255
@@ -453,6 +460,7 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         }
     } else {
         // ===================== epilogue =====================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 152;" ::: "memory");
         const int ew = warp - G2_EPI_WARP0;                 // 0..7
         const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
         const int colhalf = ew >> 2;                        // 0: channels unpacked by CTA 0, 1: by CTA 1
@@ -497,16 +505,20 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
                 const float *sn = sSn + ring * 128 + colhalf * 64;
                 const int anyz = sZflag[ring * 4 + colhalf * 2] | sZflag[ring * 4 + colhalf * 2 + 1];
                 const uint32_t t_hi = t_base + as * 256;
+                // two chunks of TMEM loads in flight: chunk ch+1 is requested before the math of chunk ch
+                uint32_t rh[2][8], rl[2][8];
+                tmem_ld_32x8(t_hi, rh[0]);
+                tmem_ld_32x8(t_hi + 8 * NTL, rl[0]);
 #pragma unroll
                 for (int ch = 0; ch < NTL; ch++) {
-                    uint32_t rh[8], rl[8];
-                    tmem_ld_32x8(t_hi + ch * 8, rh);
-                    tmem_ld_32x8(t_hi + 8 * NTL + ch * 8, rl);
                     // S[] of this k-tile is read BEFORE the stage is handed back (ring slot reuse, see tcq4_gemm.cu)
                     const ulonglong2 s01 = *reinterpret_cast<const ulonglong2 *>(sn + ch * 8);
                     const ulonglong2 s23 = *reinterpret_cast<const ulonglong2 *>(sn + ch * 8 + 4);
-                    tmem_ld_wait();
-                    if (ch == NTL - 1) {             // all TMEM reads of this stage are done: hand it back
+                    tmem_ld_wait();                  // chunk ch has landed
+                    if (ch + 1 < NTL) {
+                        tmem_ld_32x8(t_hi + (ch + 1) * 8, rh[(ch + 1) & 1]);
+                        tmem_ld_32x8(t_hi + 8 * NTL + (ch + 1) * 8, rl[(ch + 1) & 1]);
+                    } else {                         // all TMEM reads of this stage are done: hand it back
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0) g2_arrive_cluster(accempty_leader + (uint32_t)as * 8);
@@ -515,8 +527,8 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
                     const uint64_t sv2[4] = {s01.x, s01.y, s23.x, s23.y};
 #pragma unroll
                     for (int i = 0; i < 4; i++) {
-                        const int is0 = g2_mad16(rh[2 * i], rl[2 * i]);             // = sum_g sc*dot, exact
-                        const int is1 = g2_mad16(rh[2 * i + 1], rl[2 * i + 1]);
+                        const int is0 = g2_mad16(rh[ch & 1][2 * i], rl[ch & 1][2 * i]);             // = sum_g sc*dot, exact
+                        const int is1 = g2_mad16(rh[ch & 1][2 * i + 1], rl[ch & 1][2 * i + 1]);
                         const uint64_t f2 = g2_mul2(g2_pack((float)is0, (float)is1), rm2);
                         acc2[ch * 4 + i] = g2_fma2(f2, sv2[i], acc2[ch * 4 + i]);
                         if (DEBUG) {
