@@ -70,7 +70,7 @@ class ClockSampler:
         try:
             self.f = open(self.path, "w")
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.index), "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+                                          "-i", str(self.index), "-lms", "20"], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:  # noqa: BLE001
             self.proc = None
 
@@ -215,6 +215,13 @@ class Chain:
                                        device="cuda") for N in Ns}
         wsz = max(t4.workspace_size(M, w.n_local, w.K) for w in weights)
         self.ws = t4.Workspace(wsz)
+        # N > 1 with the gather: every matmul keeps its own column block until its all-gather (second stream) has
+        # read it, so the gather of matmul i overlaps the kernels of matmul i+1
+        self.y_each = None
+        self.comm = None
+        if world > 1 and gather:
+            self.y_each = [torch.empty((M, w.n_local), device="cuda") for w in weights]
+            self.comm = torch.cuda.Stream()
         self.graph = None
         self.launches_per_step = None
 
@@ -222,10 +229,21 @@ class Chain:
         return sum(w.tiles.numel() for w in self.weights)
 
     def step_eager(self):
+        torch = self.torch
         last = None
-        for w in self.weights:
-            yl = w.local(self.x[w.K], out=self.y_local[w.N], workspace=self.ws)
-            last = w.gather(yl) if (self.world > 1 and self.gather) else yl
+        if self.comm is None:
+            for w in self.weights:
+                last = w.local(self.x[w.K], out=self.y_local[w.N], workspace=self.ws)
+            return last
+        main = torch.cuda.current_stream()
+        for i, w in enumerate(self.weights):
+            yl = w.local(self.x[w.K], out=self.y_each[i], workspace=self.ws)
+            ev = torch.cuda.Event()
+            ev.record(main)
+            self.comm.wait_event(ev)
+            with torch.cuda.stream(self.comm):
+                last = w.gather(yl)                      # NCCL all-gather + re-layout into C[m*N + n]
+        main.wait_stream(self.comm)                      # every output of the step is gathered before the step ends
         return last
 
     def capture(self):
@@ -312,6 +330,11 @@ def e2e_leg(t4, torch, chain, steps, M):
     return (time.perf_counter() - t0) / steps, h2d, d2h
 
 
+# per-launch DRAM traffic of the headline shapes from the committed ncu captures (profiles/)
+PREFILL_TRAFFIC_BYTES = 15789568
+DECODE_TRAFFIC_BYTES = 14439680
+
+
 def run_own_arm(args):
     import torch
     import __graft_entry__ as graft
@@ -387,7 +410,7 @@ def run_own_arm(args):
             "vs_baseline": None, "dtype": "s8", "data": "synthetic",
             "config": {"workload": "Qwen3-4B TCQ4_K32 252 linear matmuls, 512-token prefill (BASELINE.json configs[1])",
                        "M": M, "layers": QWEN3_4B_LAYERS, "matmuls_per_layer": len(QWEN3_4B_LAYER),
-                       "weight_bytes_per_gpu": pre.weight_bytes(), "parallelism": f"N-shard x{world} + fp32 all-gather",
+                       "weight_bytes_per_gpu": pre.weight_bytes(), "parallelism": (f"N-shard x{world} + fp32 all-gather of every output on a second stream (overlaps the next matmul; all gathers complete inside the step)" if world > 1 else "single GPU"),
                        "l2": "252 distinct weight buffers (2.1 GB total) >> 126 MB L2; activations stay L2-resident",
                        "cuda_graph": pre.graph is not None},
             "tops": total_ops / (ms_step * 1e-3) / 1e12,
@@ -395,7 +418,10 @@ def run_own_arm(args):
                        "gbs": total_dec_bytes / (ms_dec * 1e-3) / 1e9, "frac_hbm": total_dec_bytes / (ms_dec * 1e-3) / 1e9
                        / (peaks["hbm_gbs"] * world), "cuda_graph": dec.graph is not None},
             "roofline": {"bound": "tensor", "kernel": "tcq4_gemm2_kernel (tcgen05.mma.cta_group::2 kind::i8)", "achieved": gm_tops,
-                         "peak": i8_peak, "unit": "TOP/s", "frac": gm_tops / i8_peak, "traffic": None,
+                         "peak": i8_peak, "unit": "TOP/s", "frac": gm_tops / i8_peak, "traffic": PREFILL_TRAFFIC_BYTES,
+                         "traffic_note": "dram__bytes_read+write of the M=512,N=9728,K=2560 launch from one ncu --set full capture "
+                                         "(profiles/prof_gemm2_r01_summary.csv): the weights; x codes and y stay in the 126 MB L2; "
+                                         "algorithmic bytes of that launch incl. x and y are 39.6 MB",
                          "peak_source": f"2 x bf16_tflops of MEASURED_PEAKS.json ({peaks['source']}, burst)",
                          "peak_umma_i8_measured": umma_i8, "frac_of_umma_i8": (gm_tops / umma_i8) if umma_i8 else None,
                          "ops": "useful 2*M*N*K per launch; the tensor pipe executes 2x that (exact hi/lo split)",
@@ -403,7 +429,9 @@ def run_own_arm(args):
                          "act_kernel_avg_us": act_ms * 1e3 / max(1, gm_n),
                          "timed": "per-launch CUDA events, eager pass of the same steps after the timed region"},
             "roofline_decode": {"bound": "hbm", "kernel": "tcq4_gemv_kernel", "achieved": gv_gbs, "peak": peaks["hbm_gbs"],
-                                "unit": "GB/s", "frac": gv_gbs / peaks["hbm_gbs"], "traffic": None, "launches": gv_n,
+                                "unit": "GB/s", "frac": gv_gbs / peaks["hbm_gbs"], "traffic": DECODE_TRAFFIC_BYTES,
+                                "traffic_note": "dram__bytes_read+write of the M=1,N=9728,K=2560 launch (profiles/prof_gemv_r01b_summary.csv); "
+                                                "algorithmic 14.45 MB", "launches": gv_n,
                                 "avg_launch_us": gv_ms * 1e3 / max(1, gv_n), "peak_source": f"hbm_gbs ({peaks['source']})"},
             "e2e": {"value": M / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_s * 1e3, "api": "tcq4_b200_mul_mat_host_async per matmul (pinned host x and y, copies inside the timed region) + tcq4_b200_host_sync per step"},

@@ -98,6 +98,15 @@ TCQ4_B200_API int tcq4_b200_reserve(int64_t max_M, int64_t max_N, int64_t max_K)
 /* End-to-end entry with HOST activations/outputs (weights stay resident on the device, as they do
  * in a ggml CUDA buffer): H2D copy of x, MUL_MAT, D2H copy of y, all on `stream`, then a stream
  * synchronise.  Mirrors ggml_backend_tensor_set + graph_compute + ggml_backend_tensor_get. */
+/* N-sharded MUL_MAT with the all-gather fused into the epilogue (no counterpart in the fork, whose TCQ4 path is
+ * single-GPU: ggml-cuda.cu:2195-2200).  Computes the N output columns of this GPU's weight shard and stores them at
+ * column col0 of EVERY destination: y_peers[i] is the base of a row-major fp32 [M][ldc] matrix, normally the same
+ * symmetric buffer on each GPU of the node, peer-mapped into this process.  ldc % 4 == 0, col0 % 4 == 0, n_peers <= 8.
+ * The caller places one cross-GPU barrier between these stores and the consumers of C. */
+TCQ4_B200_API int tcq4_b200_mul_mat_peers(const void *w_tiles, const float *x, float *const *y_peers, int n_peers,
+                                          int64_t ldc, int64_t col0, int64_t M, int64_t N, int64_t K,
+                                          const int32_t *d_perm, cudaStream_t stream);
+
 TCQ4_B200_API int tcq4_b200_mul_mat_host(const void *w_tiles_dev, const float *x_host, float *y_host,
                                          int64_t M, int64_t N, int64_t K, const int32_t *d_perm,
                                          cudaStream_t stream);

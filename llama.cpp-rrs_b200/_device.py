@@ -15,7 +15,7 @@ import torch
 from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
                ACT_BLOCK_BYTES, TensorView, _check, shard_range, tile_bytes, workspace_size)
 
-__all__ = ["Workspace", "mul_mat", "mul_mat_debug", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
+__all__ = ["Workspace", "mul_mat", "mul_mat_debug", "mul_mat_peers", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
            "ggml_supports_op", "ShardedWeight", "random_tiles"]
 
@@ -85,6 +85,20 @@ def mul_mat_debug(w_tiles: torch.Tensor, x: torch.Tensor, N: int, perm: torch.Te
     _check(LIB.tcq4_b200_mul_mat_debug(w_tiles.data_ptr(), x.data_ptr(), y.data_ptr(), M, N, K, pp, ws.ptr,
                                        ws.nbytes, kernel, isum.data_ptr(), _stream_ptr()))
     return y, isum
+
+
+def mul_mat_peers(w_tiles: torch.Tensor, x: torch.Tensor, peer_ptrs, ldc: int, col0: int, N: int,
+                  perm: torch.Tensor | None = None, stream=None) -> None:
+    """N-sharded MUL_MAT whose epilogue stores its N columns at column col0 of every [M][ldc] fp32 matrix in
+    `peer_ptrs` (device pointers, normally one peer-mapped symmetric buffer per GPU): the all-gather fused away."""
+    import ctypes as _C
+    _req_cuda(w_tiles, torch.uint8, "w_tiles")
+    _req_cuda(x, torch.float32, "x")
+    M, K = x.shape
+    arr = (_C.c_void_p * len(peer_ptrs))(*[int(p) for p in peer_ptrs])
+    pp = perm.data_ptr() if perm is not None else 0
+    _check(LIB.tcq4_b200_mul_mat_peers(w_tiles.data_ptr(), x.data_ptr(), arr, len(peer_ptrs), ldc, col0, M, N, K, pp,
+                                       _stream_ptr(stream)))
 
 
 def mul_mat_host(w_tiles: torch.Tensor, x_host: torch.Tensor, y_host: torch.Tensor, N: int,

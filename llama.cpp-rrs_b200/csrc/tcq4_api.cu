@@ -153,8 +153,18 @@ int select_kernel(const DevInfo *d, int64_t M, int64_t N, int64_t K, tcq4::GemvP
     return TCQ4_KERNEL_GEMM2;
 }
 
-int run_mul_mat(const void *w, const float *x, float *y, int64_t M, int64_t N, int64_t K, const int32_t *perm,
+tcq4::YOut single_out(float *y, int64_t N) {
+    tcq4::YOut o;
+    for (int i = 0; i < tcq4::MAX_PEERS; i++) o.p[i] = y;
+    o.n = 1;
+    o.ldc = N;
+    return o;
+}
+
+int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t N, int64_t K, const int32_t *perm,
                 void *ws, size_t ws_bytes, int kernel, int32_t *dbg_isum, cudaStream_t stream) {
+    float *y = yo.p[0];
+    const bool plain = (yo.n == 1 && yo.ldc == N);     // ggml's dst; otherwise strided and/or several destinations
     if (!shape_ok(M, N, K)) {
         set_err("unsupported shape M=%lld N=%lld K=%lld (need K%%256==0, N%%8==0)", (long long)M, (long long)N,
                 (long long)K);
@@ -165,6 +175,15 @@ int run_mul_mat(const void *w, const float *x, float *y, int64_t M, int64_t N, i
         set_err("null or misaligned pointer (w/x/y/perm must be 16-byte aligned device pointers)");
         return TCQ4_ERR_ARG;
     }
+    if (yo.n < 1 || yo.n > tcq4::MAX_PEERS || yo.ldc < N || (yo.ldc & 3)) {
+        set_err("bad output spec: 1..%d destinations, ldc >= N and a multiple of 4", tcq4::MAX_PEERS);
+        return TCQ4_ERR_ARG;
+    }
+    for (int i = 0; i < yo.n; i++)
+        if (!yo.p[i] || ((uintptr_t)yo.p[i] & 15)) {
+            set_err("null or misaligned destination %d", i);
+            return TCQ4_ERR_ARG;
+        }
     int status;
     DevInfo *d = current_device(&status);
     if (!d) return status;
@@ -178,6 +197,7 @@ int run_mul_mat(const void *w, const float *x, float *y, int64_t M, int64_t N, i
     tcq4::GemvPlan gv;
     int k = kernel;
     if (k == TCQ4_KERNEL_AUTO) k = select_kernel(d, M, N, K, &gv);
+    if (k == TCQ4_KERNEL_GEMM && !plain) k = TCQ4_KERNEL_GEMM2;      // only the pair GEMM and the GEMV write strided / to peers
     if (k == TCQ4_KERNEL_GEMV) {
         if (!tcq4::gemv_plan(M, N, K, d->num_sms, d->smem_optin, &gv)) {
             set_err("GEMV kernel does not take M=%lld K=%lld (M<=%d and M*K codes must fit shared memory)",
@@ -193,7 +213,7 @@ int run_mul_mat(const void *w, const float *x, float *y, int64_t M, int64_t N, i
             cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
             cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
         }
-        cudaError_t e = tcq4::launch_gemv(w, x, perm, y, M, N, K, gv, reinterpret_cast<float *>(wsb + L.partial_off),
+        cudaError_t e = tcq4::launch_gemv(w, x, perm, yo, M, N, K, gv, reinterpret_cast<float *>(wsb + L.partial_off),
                                           reinterpret_cast<int *>(wsb + L.ticket_off), dbg_isum, stream);
         if (e != cudaSuccess) return cuda_fail(e, "gemv launch");
         if (prof) {
@@ -227,7 +247,7 @@ int run_mul_mat(const void *w, const float *x, float *y, int64_t M, int64_t N, i
             set_err("pair GEMM kernel cannot be planned for this shape/device");
             return TCQ4_ERR_SHAPE;
         }
-        e = tcq4::launch_gemm2(w, st, y, M, N, K, g2, dbg_isum, stream);
+        e = tcq4::launch_gemm2(w, st, yo, M, N, K, g2, dbg_isum, stream);
     } else {
         e = tcq4::launch_gemm(w, st, y, M, N, K, gm, dbg_isum, stream);
     }
@@ -287,13 +307,13 @@ int tcq4_b200_workspace_init(void *workspace, size_t workspace_bytes, cudaStream
 int tcq4_b200_mul_mat_ws(const void *w_tiles, const float *x, float *y, int64_t M, int64_t N, int64_t K,
                          const int32_t *d_perm, void *workspace, size_t workspace_bytes, int kernel,
                          cudaStream_t stream) {
-    return run_mul_mat(w_tiles, x, y, M, N, K, d_perm, workspace, workspace_bytes, kernel, nullptr, stream);
+    return run_mul_mat(w_tiles, x, single_out(y, N), M, N, K, d_perm, workspace, workspace_bytes, kernel, nullptr, stream);
 }
 
 int tcq4_b200_mul_mat_debug(const void *w_tiles, const float *x, float *y, int64_t M, int64_t N, int64_t K,
                             const int32_t *d_perm, void *workspace, size_t workspace_bytes, int kernel,
                             int32_t *isum, cudaStream_t stream) {
-    return run_mul_mat(w_tiles, x, y, M, N, K, d_perm, workspace, workspace_bytes, kernel, isum, stream);
+    return run_mul_mat(w_tiles, x, single_out(y, N), M, N, K, d_perm, workspace, workspace_bytes, kernel, isum, stream);
 }
 
 // grow the per-device arena (never while the stream is capturing)
@@ -350,7 +370,31 @@ int tcq4_b200_mul_mat(const void *w_tiles, const float *x, float *y, int64_t M, 
     const size_t need = ws_layout(M, N, K).total;
     status = arena_ensure(d, need, stream);
     if (status != TCQ4_OK) return status;
-    return run_mul_mat(w_tiles, x, y, M, N, K, d_perm, d->arena, d->arena_bytes, TCQ4_KERNEL_AUTO, nullptr, stream);
+    return run_mul_mat(w_tiles, x, single_out(y, N), M, N, K, d_perm, d->arena, d->arena_bytes, TCQ4_KERNEL_AUTO, nullptr,
+                       stream);
+}
+
+// N-sharded MUL_MAT with the all-gather fused away: the N columns this GPU owns are written, by the kernel's own
+// epilogue, at column col0 of EVERY destination matrix (row-major [M][ldc] fp32).  With peer-mapped pointers (one per
+// GPU of the node) every GPU ends up with the full C without a collective on the path; the caller orders consumers
+// behind all producers (one cross-GPU barrier per step or per matmul).  n_peers = 1 is a strided single-GPU store.
+int tcq4_b200_mul_mat_peers(const void *w_tiles, const float *x, float *const *y_peers, int n_peers, int64_t ldc,
+                            int64_t col0, int64_t M, int64_t N, int64_t K, const int32_t *d_perm, cudaStream_t stream) {
+    if (!shape_ok(M, N, K) || !y_peers || n_peers < 1 || n_peers > tcq4::MAX_PEERS || col0 < 0 || (col0 & 3) ||
+        col0 + N > ldc) {
+        set_err("mul_mat_peers: bad shape, destination count (1..%d) or column window", tcq4::MAX_PEERS);
+        return TCQ4_ERR_SHAPE;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    status = arena_ensure(d, ws_layout(M, N, K).total, stream);
+    if (status != TCQ4_OK) return status;
+    tcq4::YOut o;
+    for (int i = 0; i < tcq4::MAX_PEERS; i++) o.p[i] = y_peers[i < n_peers ? i : 0] ? y_peers[i < n_peers ? i : 0] + col0 : nullptr;
+    o.n = n_peers;
+    o.ldc = ldc;
+    return run_mul_mat(w_tiles, x, o, M, N, K, d_perm, d->arena, d->arena_bytes, TCQ4_KERNEL_AUTO, nullptr, stream);
 }
 
 int tcq4_b200_mul_mat_host(const void *w_tiles_dev, const float *x_host, float *y_host, int64_t M, int64_t N,

@@ -126,6 +126,16 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
+// Where a kernel writes its [M][N] result: `n` row-major fp32 matrices with leading dimension ldc, each pointer already
+// offset to this call's first column.  n = 1, ldc = N is ggml's dst; n = G with peer-mapped pointers is the N-sharded
+// MUL_MAT whose epilogue stores its column block straight into every GPU's full C (the all-gather fused away).
+constexpr int MAX_PEERS = 8;
+struct YOut {
+    float    *p[MAX_PEERS];
+    int       n;
+    long long ldc;
+};
+
 // Programmatic dependent launch: a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start
 // once every CTA of its predecessor has executed launch_dependents (or exited); it must not touch memory the
 // predecessor reads or writes before griddepcontrol.wait, which returns when the predecessor has completed and

@@ -249,10 +249,15 @@ __device__ __forceinline__ void g2_store_wait_read() {
 // producer / unpack / MMA warps are already inside the next tile while the epilogue warps finish and store the
 // previous one; there is no per-tile launch, TMEM allocation, cluster barrier or drain (those cost ~40 % of the
 // non-persistent version: profiles/).
+struct G2YMaps {       // one store map per destination matrix (this GPU's C, or every GPU's C when N-sharded)
+    CUtensorMap m[MAX_PEERS];
+    int n;
+};
+
 template <int NTL, bool DEBUG, bool PROF = false>
 __global__ void __launch_bounds__(G2_THREADS, 1)
 tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_constant__ CUtensorMap tm_meta,
-                  const __grid_constant__ CUtensorMap tm_y, const uint8_t *__restrict__ w, ActStage st, int M, int N, int K,
+                  const __grid_constant__ G2YMaps tm_y, const uint8_t *__restrict__ w, ActStage st, int M, int N, int K,
                   int MB2, int num_tiles, int32_t *__restrict__ dbg_isum) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int LBO = 256 * NTL;                               // K-chunk stride of B: (16*NTL rows) * 16 B
@@ -299,7 +304,7 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_tiles) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_meta) : "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_y) : "memory");
+        for (int pi = 0; pi < tm_y.n; pi++) asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_y.m[pi]) : "memory");
     }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512)
@@ -573,7 +578,8 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
                 fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) {
-                    if (n_base + ch * 8 < N && row0 < M) g2_tma_store_2d(&tm_y, box, n_base + ch * 8, row0);
+                    if (n_base + ch * 8 < N && row0 < M)
+                        for (int pi = 0; pi < tm_y.n; pi++) g2_tma_store_2d(&tm_y.m[pi], box, n_base + ch * 8, row0);
                     g2_store_commit();
                 }
             }
@@ -647,11 +653,11 @@ static bool g2_make_map(CUtensorMap *map, const void *w, int64_t NT, int64_t KT,
 }
 
 // the fp32 output [M][N] with boxes of 32 rows x 8 channels
-static bool g2_make_y_map(CUtensorMap *map, float *y, int64_t M, int64_t N) {
+static bool g2_make_y_map(CUtensorMap *map, float *y, int64_t M, int64_t N, int64_t ldc) {
     G2EncodeTiled enc = g2_encoder();
     if (!enc) return false;
     const cuuint64_t gdim[2] = {(cuuint64_t)N, (cuuint64_t)M};
-    const cuuint64_t gstride[1] = {(cuuint64_t)N * sizeof(float)};
+    const cuuint64_t gstride[1] = {(cuuint64_t)ldc * sizeof(float)};
     const cuuint32_t box[2] = {8, 32};
     const cuuint32_t estr[2] = {1, 1};
     return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, y, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -659,12 +665,17 @@ static bool g2_make_y_map(CUtensorMap *map, float *y, int64_t M, int64_t N) {
 }
 
 template <int NTL>
-static cudaError_t launch_gemm2_t(cudaLaunchConfig_t *cfg, const void *w_tiles, ActStage st, float *y, int64_t M, int64_t N,
+static cudaError_t launch_gemm2_t(cudaLaunchConfig_t *cfg, const void *w_tiles, ActStage st, YOut y, int64_t M, int64_t N,
                                   int64_t K, int32_t *dbg_isum) {
-    CUtensorMap tm_tiles, tm_meta, tm_y;
+    CUtensorMap tm_tiles, tm_meta;
+    G2YMaps tm_y;
     if (!g2_make_map(&tm_tiles, w_tiles, N / TILE_CH, K / TILE_K, TILE_BYTES / 8, NTL) ||
-        !g2_make_map(&tm_meta, w_tiles, N / TILE_CH, K / TILE_K, 160 / 8, 2 * NTL) || !g2_make_y_map(&tm_y, y, M, N))
+        !g2_make_map(&tm_meta, w_tiles, N / TILE_CH, K / TILE_K, 160 / 8, 2 * NTL))
         return cudaErrorInvalidValue;      // unaligned tensor base or no driver entry point
+    if (y.n < 1 || y.n > MAX_PEERS) return cudaErrorInvalidValue;
+    tm_y.n = y.n;
+    for (int pi = 0; pi < MAX_PEERS; pi++)
+        if (!g2_make_y_map(&tm_y.m[pi], y.p[pi < y.n ? pi : 0], M, N, y.ldc)) return cudaErrorInvalidValue;
     const int MB2 = (int)((M + 2 * G2_BM - 1) / (2 * G2_BM));
     const int num_tiles = (int)g2_tiles(M, N, NTL);
     static const bool prof = getenv("TCQ4_G2_PROF") != nullptr;     // diagnostics: timeline stamps of one cluster
@@ -681,7 +692,7 @@ static cudaError_t launch_gemm2_t(cudaLaunchConfig_t *cfg, const void *w_tiles, 
                               (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
 }
 
-cudaError_t launch_gemm2(const void *w_tiles, ActStage st, float *y, int64_t M, int64_t N, int64_t K,
+cudaError_t launch_gemm2(const void *w_tiles, ActStage st, YOut y, int64_t M, int64_t N, int64_t K,
                          const Gemm2Plan &plan, int32_t *dbg_isum, cudaStream_t stream) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = plan.grid;

@@ -129,7 +129,7 @@ __device__ __noinline__ float gv_zero_point(unsigned short zh, uint2 zcv, const 
 template <int MB, bool DEBUG>
 __global__ void __launch_bounds__(GV_THREADS, MB == 1 ? 2 : 1)
 tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, const int32_t *__restrict__ perm,
-                 float *__restrict__ y, int M, int N, int K, int32_t *__restrict__ dbg_isum) {
+                 const YOut out, int M, int N, int K, int32_t *__restrict__ dbg_isum) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int KT = K / TILE_K;
     const int NT = N / TILE_CH;
@@ -320,7 +320,9 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                 for (int mb = 0; mb < MB; mb++)
 #pragma unroll
                     for (int j = 0; j < 2; j++)
-                        if (8 * mb + tk0 + j < M) y[(size_t)(8 * mb + tk0 + j) * N + nt * 8 + c] = acc[mb][j];
+                        if (8 * mb + tk0 + j < M)
+                            for (int pi = 0; pi < out.n; pi++)
+                                out.p[pi][(size_t)(8 * mb + tk0 + j) * out.ldc + nt * 8 + c] = acc[mb][j];
             } else {                                    // a cut row: park the partial in CTA 0's shared memory
                 const int e = wid * 2 + nseg;
 #pragma unroll
@@ -380,7 +382,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                     if (pr != row) break;
                     sum += part[(size_t)(j * M + m) * 8 + (lane & 7)];
                 }
-                y[(size_t)m * N + row * 8 + (lane & 7)] = sum;
+                for (int pi = 0; pi < out.n; pi++) out.p[pi][(size_t)m * out.ldc + row * 8 + (lane & 7)] = sum;
             }
         }
     }
@@ -407,7 +409,7 @@ bool gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, 
 }
 
 template <int MB, bool DEBUG>
-static cudaError_t launch_gemv_t(const void *w, const float *x, const int32_t *perm, float *y, int64_t M, int64_t N,
+static cudaError_t launch_gemv_t(const void *w, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
                                  int64_t K, const GemvPlan &plan, int32_t *dbg, cudaStream_t stream) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)plan.grid);
@@ -442,7 +444,7 @@ cudaError_t gemv_init_attributes(size_t smem_optin) {
     return gemv_attr_mb<2>(smem_optin);
 }
 
-cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm, float *y, int64_t M, int64_t N,
+cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
                         int64_t K, const GemvPlan &plan, float *ws_partial, int *ws_ticket, int32_t *dbg_isum,
                         cudaStream_t stream) {
     (void)ws_partial;

@@ -26,7 +26,7 @@ struct GemvPlan {
 };
 bool        gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, GemvPlan *plan);
 cudaError_t gemv_init_attributes(size_t smem_optin);
-cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm, float *y, int64_t M, int64_t N,
+cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
                         int64_t K, const GemvPlan &plan, float *ws_partial, int *ws_ticket, int32_t *dbg_isum,
                         cudaStream_t stream);
 
@@ -54,7 +54,7 @@ struct Gemm2Plan {
 };
 bool        gemm2_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, Gemm2Plan *plan);
 cudaError_t gemm2_init_attributes(size_t smem_optin);
-cudaError_t launch_gemm2(const void *w_tiles, ActStage st, float *y, int64_t M, int64_t N, int64_t K,
+cudaError_t launch_gemm2(const void *w_tiles, ActStage st, YOut y, int64_t M, int64_t N, int64_t K,
                          const Gemm2Plan &plan, int32_t *dbg_isum, cudaStream_t stream);
 
 }  // namespace tcq4

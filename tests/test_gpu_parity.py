@@ -402,6 +402,24 @@ def test_pipelined_host_entry_matches_device_entry(t4, orc):
             assert torch.equal(yh, t4.mul_mat(tiles, xh.cuda(), N).cpu())
 
 
+@pytest.mark.parametrize("M", [1, 3, 16, 64, 300])
+def test_peer_destinations_strided_window(t4, orc, M):
+    """tcq4_b200_mul_mat_peers: the shard's columns land at column col0 of EVERY destination matrix (here two
+    buffers on the same GPU stand in for two GPUs' symmetric buffers), nothing else is touched, bits equal the
+    plain entry's.  Covers the GEMV (M <= 16) and the pair GEMM (which also takes over 17 <= M <= 128)."""
+    rng = np.random.default_rng(300 + M)
+    N, K, ldc, col0 = 256, 512, 1024, 512
+    tiles = _dev(orc.quantize_tiles(make_weights(rng, N, K)))
+    x = _dev(make_acts(rng, M, K))
+    want = t4.mul_mat(tiles, x, N)
+    dst = [torch.full((M, ldc), -7.0, device="cuda") for _ in range(2)]
+    t4.mul_mat_peers(tiles, x, [d.data_ptr() for d in dst], ldc, col0, N)
+    torch.cuda.synchronize()
+    for d in dst:
+        assert torch.equal(d[:, col0:col0 + N], want)
+        assert bool((d[:, :col0] == -7.0).all()) and bool((d[:, col0 + N:] == -7.0).all())
+
+
 def test_cuda_graph_capture(t4, orc):
     """Launches are capture-safe: no allocation / sync on the path (ggml-cuda.cu:3791-3799)."""
     rng = np.random.default_rng(16)
