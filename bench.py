@@ -194,7 +194,7 @@ def run_reference_arm(args):
 class Chain:
     """The 252 matmuls of Qwen3-4B, N-sharded over `world` ranks (shard = contiguous tile byte range)."""
 
-    def __init__(self, t4, torch, M, world, rank, weights=None, gather=True):
+    def __init__(self, t4, torch, M, world, rank, weights=None, gather=True, mode="fused"):
         self.t4, self.torch, self.M, self.world, self.rank = t4, torch, M, world, rank
         self.gather = gather                           # False: the sharded MUL_MATs alone (SURVEY 8e reports both)
         self.ops = []                                  # (sharded weight, K, N)
@@ -219,9 +219,34 @@ class Chain:
         # read it, so the gather of matmul i overlaps the kernels of matmul i+1
         self.y_each = None
         self.comm = None
+        self.sym = None                                # N -> (symmetric [M][N] buffer, handle, peer pointers)
+        self.mode = mode
+        self.gather_kind = "none"
         if world > 1 and gather:
-            self.y_each = [torch.empty((M, w.n_local), device="cuda") for w in weights]
-            self.comm = torch.cuda.Stream()
+            try:
+                # fused path: every rank's epilogue stores its column block straight into every rank's C
+                import torch.distributed as dist
+                import torch.distributed._symmetric_memory as symm_mem
+                self.sym = {}
+                for N in Ns:
+                    buf = symm_mem.empty((M, N), dtype=torch.float32, device="cuda")
+                    hdl = symm_mem.rendezvous(buf, dist.group.WORLD)
+                    self.sym[N] = (buf, hdl, [int(p) for p in hdl.buffer_ptrs])
+                self.mode = mode
+                if mode == "fused":
+                    self.gather_kind = ("fused peer stores (tcq4_b200_mul_mat_peers over symmetric memory) + one cross-GPU "
+                                        "barrier per step")
+                else:
+                    self.copy_streams = [torch.cuda.Stream() for _ in range(world)]
+                    self.gather_kind = ("MUL_MAT into the local symmetric C + copy-engine pushes of the column block to every "
+                                        "peer on side streams (tcq4_b200_push_columns) + one cross-GPU barrier per step")
+            except Exception as e:  # noqa: BLE001
+                print(f"[bench] symmetric memory unavailable ({type(e).__name__}: {e}); NCCL all-gather on a second stream",
+                      file=sys.stderr)
+                self.sym = None
+                self.y_each = [torch.empty((M, w.n_local), device="cuda") for w in weights]
+                self.comm = torch.cuda.Stream()
+                self.gather_kind = "NCCL all-gather of every output on a second stream (overlaps the next matmul)"
         self.graph = None
         self.launches_per_step = None
 
@@ -231,6 +256,33 @@ class Chain:
     def step_eager(self):
         torch = self.torch
         last = None
+        if self.sym is not None and self.mode == "fused":
+            for w in self.weights:
+                buf, hdl, ptrs = self.sym[w.N]
+                if w.n_local:
+                    self.t4.mul_mat_peers(w.tiles, self.x[w.K], ptrs, w.N, w.n0, w.n_local)
+                last = buf
+            self.sym[self.weights[-1].N][1].barrier()     # every rank's stores of this step have landed everywhere
+            return last
+        if self.sym is not None:
+            main = torch.cuda.current_stream()
+            for w in self.weights:
+                buf, hdl, ptrs = self.sym[w.N]
+                if w.n_local:
+                    self.t4.mul_mat_peers(w.tiles, self.x[w.K], [ptrs[self.rank]], w.N, w.n0, w.n_local)
+                    ev = torch.cuda.Event()
+                    ev.record(main)
+                    for r in range(self.world):
+                        if r != self.rank:
+                            cs = self.copy_streams[r]
+                            cs.wait_event(ev)
+                            self.t4.push_columns(ptrs[r], ptrs[self.rank], self.M, w.N, w.n0, w.n_local, stream=cs)
+                last = buf
+            for r in range(self.world):
+                if r != self.rank:
+                    main.wait_stream(self.copy_streams[r])
+            self.sym[self.weights[-1].N][1].barrier()
+            return last
         if self.comm is None:
             for w in self.weights:
                 last = w.local(self.x[w.K], out=self.y_local[w.N], workspace=self.ws)
@@ -371,6 +423,40 @@ def run_own_arm(args):
     ms_dec = timed_steps(torch, dist, dec, dec_steps, max(args.warmup, 3), world)
     torch.cuda.profiler.stop()
     clocks = sampler.stop() if rank == 0 else None
+    fused_ok = None
+    variants = None
+    if world > 1 and pre.sym is not None:
+        def check(chain):
+            # one-off check (not timed): the exchange gives the same full C as the NCCL all-gather
+            chain.sym[chain.weights[-1].N][0].zero_()
+            torch.cuda.synchronize()
+            dist.barrier()
+            chain.step_eager()
+            torch.cuda.synchronize()
+            dist.barrier()
+            wl = chain.weights[-1]
+            want = wl.forward(chain.x[wl.K], workspace=chain.ws)
+            torch.cuda.synchronize()
+            ok = bool(torch.equal(chain.sym[wl.N][0], want))
+            dist.barrier()
+            return ok
+        fused_ok = check(pre)
+        # second variant of the exchange: copy engines instead of the epilogue's own peer stores
+        pre_dma = Chain(t4, torch, M, world, rank, weights=pre.weights, mode="dma")
+        pre_dma.capture()
+        ms_step_dma = timed_steps(torch, dist, pre_dma, args.steps, args.warmup, world)
+        dec_dma = Chain(t4, torch, 1, world, rank, weights=pre.weights, mode="dma")
+        dec_dma.capture()
+        ms_dec_dma = timed_steps(torch, dist, dec_dma, dec_steps, max(args.warmup, 3), world)
+        dma_ok = check(pre_dma)
+        variants = {"fused_peer_stores": {"ms_per_step": ms_step, "decode_ms_per_step": ms_dec, "matches_nccl": fused_ok},
+                    "copy_engine_pushes": {"ms_per_step": ms_step_dma, "decode_ms_per_step": ms_dec_dma, "matches_nccl": dma_ok}}
+        if ms_step_dma < ms_step:
+            ms_step, pre_kind = ms_step_dma, pre_dma.gather_kind
+        else:
+            pre_kind = pre.gather_kind
+        ms_dec = min(ms_dec, ms_dec_dma)
+        pre.gather_kind = pre_kind
     # ---- N > 1: the same chains without the fp32 all-gather (the sharded MUL_MATs alone; SURVEY 8e asks for both) ----
     ms_step_ng = ms_dec_ng = None
     if world > 1:
@@ -410,7 +496,7 @@ def run_own_arm(args):
             "vs_baseline": None, "dtype": "s8", "data": "synthetic",
             "config": {"workload": "Qwen3-4B TCQ4_K32 252 linear matmuls, 512-token prefill (BASELINE.json configs[1])",
                        "M": M, "layers": QWEN3_4B_LAYERS, "matmuls_per_layer": len(QWEN3_4B_LAYER),
-                       "weight_bytes_per_gpu": pre.weight_bytes(), "parallelism": (f"N-shard x{world} + fp32 all-gather of every output on a second stream (overlaps the next matmul; all gathers complete inside the step)" if world > 1 else "single GPU"),
+                       "weight_bytes_per_gpu": pre.weight_bytes(), "parallelism": (f"N-shard x{world}; gather: {pre.gather_kind}" if world > 1 else "single GPU"),
                        "l2": "252 distinct weight buffers (2.1 GB total) >> 126 MB L2; activations stay L2-resident",
                        "cuda_graph": pre.graph is not None},
             "tops": total_ops / (ms_step * 1e-3) / 1e12,
@@ -439,6 +525,7 @@ def run_own_arm(args):
             "clocks": clocks,
         }
         if world > 1:
+            line["config"]["exchange_variants"] = variants      # value / decode use the faster one
             line["sharded_mul_mat_only"] = {
                 "note": "same chains without the fp32 all-gather of the N-sharded outputs (max over ranks)",
                 "value": M / (ms_step_ng * 1e-3), "unit": UNIT, "ms_per_step": ms_step_ng,

@@ -107,6 +107,12 @@ TCQ4_B200_API int tcq4_b200_mul_mat_peers(const void *w_tiles, const float *x, f
                                           int64_t ldc, int64_t col0, int64_t M, int64_t N, int64_t K,
                                           const int32_t *d_perm, cudaStream_t stream);
 
+/* Copy-engine form of the exchange: after a plain/strided MUL_MAT into the LOCAL C (n_peers = 1 above), push this
+ * GPU's column window [col0, col0+ncols) of the row-major [M][ldc] matrix into the same window of a peer's matrix
+ * (one cudaMemcpy2DAsync; no SM work, overlaps the next matmul when issued on a side stream). */
+TCQ4_B200_API int tcq4_b200_push_columns(float *dst_base, const float *src_base, int64_t M, int64_t ldc, int64_t col0,
+                                         int64_t ncols, cudaStream_t stream);
+
 TCQ4_B200_API int tcq4_b200_mul_mat_host(const void *w_tiles_dev, const float *x_host, float *y_host,
                                          int64_t M, int64_t N, int64_t K, const int32_t *d_perm,
                                          cudaStream_t stream);

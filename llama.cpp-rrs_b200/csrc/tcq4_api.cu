@@ -397,6 +397,22 @@ int tcq4_b200_mul_mat_peers(const void *w_tiles, const float *x, float *const *y
     return run_mul_mat(w_tiles, x, o, M, N, K, d_perm, d->arena, d->arena_bytes, TCQ4_KERNEL_AUTO, nullptr, stream);
 }
 
+// Copy-engine half of the same exchange: push `ncols` columns starting at col0 of a local row-major [M][ldc] fp32
+// matrix into the same window of a (peer-mapped) destination matrix.  One 2-D async copy, no SM involved; with the
+// plain MUL_MAT writing the local C and this call per peer on side streams, the transfer of matmul i overlaps the
+// kernels of matmul i+1.
+int tcq4_b200_push_columns(float *dst_base, const float *src_base, int64_t M, int64_t ldc, int64_t col0, int64_t ncols,
+                           cudaStream_t stream) {
+    if (!dst_base || !src_base || M < 1 || ncols < 1 || col0 < 0 || col0 + ncols > ldc) {
+        set_err("push_columns: bad window");
+        return TCQ4_ERR_ARG;
+    }
+    cudaError_t e = cudaMemcpy2DAsync(dst_base + col0, (size_t)ldc * 4, src_base + col0, (size_t)ldc * 4, (size_t)ncols * 4,
+                                      (size_t)M, cudaMemcpyDefault, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "push_columns");
+    return TCQ4_OK;
+}
+
 int tcq4_b200_mul_mat_host(const void *w_tiles_dev, const float *x_host, float *y_host, int64_t M, int64_t N,
                            int64_t K, const int32_t *d_perm, cudaStream_t stream) {
     if (!shape_ok(M, N, K) || !x_host || !y_host) {
