@@ -107,6 +107,12 @@ TCQ4_B200_API int tcq4_b200_mul_mat_peers(const void *w_tiles, const float *x, f
                                           int64_t ldc, int64_t col0, int64_t M, int64_t N, int64_t K,
                                           const int32_t *d_perm, cudaStream_t stream);
 
+/* The same exchange through the NVSwitch: y_multicast is the multicast (NVLS) address of the symmetric C; each store
+ * of the epilogue is a multimem.st replicated by the switch into every GPU's copy (outbound traffic 1x). */
+TCQ4_B200_API int tcq4_b200_mul_mat_multicast(const void *w_tiles, const float *x, float *y_multicast, int64_t ldc,
+                                              int64_t col0, int64_t M, int64_t N, int64_t K, const int32_t *d_perm,
+                                              cudaStream_t stream);
+
 /* Copy-engine form of the exchange: after a plain/strided MUL_MAT into the LOCAL C (n_peers = 1 above), push this
  * GPU's column window [col0, col0+ncols) of the row-major [M][ldc] matrix into the same window of a peer's matrix
  * (one cudaMemcpy2DAsync; no SM work, overlaps the next matmul when issued on a side stream). */

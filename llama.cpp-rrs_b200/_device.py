@@ -15,7 +15,7 @@ import torch
 from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
                ACT_BLOCK_BYTES, TensorView, _check, shard_range, tile_bytes, workspace_size)
 
-__all__ = ["Workspace", "mul_mat", "mul_mat_debug", "mul_mat_peers", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
+__all__ = ["Workspace", "mul_mat", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
            "ggml_supports_op", "ShardedWeight", "random_tiles"]
 
@@ -99,6 +99,18 @@ def mul_mat_peers(w_tiles: torch.Tensor, x: torch.Tensor, peer_ptrs, ldc: int, c
     pp = perm.data_ptr() if perm is not None else 0
     _check(LIB.tcq4_b200_mul_mat_peers(w_tiles.data_ptr(), x.data_ptr(), arr, len(peer_ptrs), ldc, col0, M, N, K, pp,
                                        _stream_ptr(stream)))
+
+
+def mul_mat_multicast(w_tiles: torch.Tensor, x: torch.Tensor, mc_ptr: int, ldc: int, col0: int, N: int,
+                      perm: torch.Tensor | None = None, stream=None) -> None:
+    """N-sharded MUL_MAT storing through the multicast (NVLS) address of the symmetric C: one multimem.st per element
+    group, replicated by the switch into every GPU's copy."""
+    _req_cuda(w_tiles, torch.uint8, "w_tiles")
+    _req_cuda(x, torch.float32, "x")
+    M, K = x.shape
+    pp = perm.data_ptr() if perm is not None else 0
+    _check(LIB.tcq4_b200_mul_mat_multicast(w_tiles.data_ptr(), x.data_ptr(), int(mc_ptr), ldc, col0, M, N, K, pp,
+                                           _stream_ptr(stream)))
 
 
 def push_columns(dst_ptr: int, src_ptr: int, M: int, ldc: int, col0: int, ncols: int, stream=None) -> None:

@@ -158,13 +158,14 @@ tcq4::YOut single_out(float *y, int64_t N) {
     for (int i = 0; i < tcq4::MAX_PEERS; i++) o.p[i] = y;
     o.n = 1;
     o.ldc = N;
+    o.mc = nullptr;
     return o;
 }
 
 int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t N, int64_t K, const int32_t *perm,
                 void *ws, size_t ws_bytes, int kernel, int32_t *dbg_isum, cudaStream_t stream) {
     float *y = yo.p[0];
-    const bool plain = (yo.n == 1 && yo.ldc == N);     // ggml's dst; otherwise strided and/or several destinations
+    const bool plain = (yo.n == 1 && yo.ldc == N && !yo.mc);     // ggml's dst; otherwise strided / several destinations
     if (!shape_ok(M, N, K)) {
         set_err("unsupported shape M=%lld N=%lld K=%lld (need K%%256==0, N%%8==0)", (long long)M, (long long)N,
                 (long long)K);
@@ -394,6 +395,26 @@ int tcq4_b200_mul_mat_peers(const void *w_tiles, const float *x, float *const *y
     for (int i = 0; i < tcq4::MAX_PEERS; i++) o.p[i] = y_peers[i < n_peers ? i : 0] ? y_peers[i < n_peers ? i : 0] + col0 : nullptr;
     o.n = n_peers;
     o.ldc = ldc;
+    o.mc = nullptr;
+    return run_mul_mat(w_tiles, x, o, M, N, K, d_perm, d->arena, d->arena_bytes, TCQ4_KERNEL_AUTO, nullptr, stream);
+}
+
+// Same exchange through the switch: y_multicast is the multicast (NVLS) address of the symmetric [M][ldc] C; every
+// store of the epilogue is a multimem.st that the NVSwitch replicates into all GPUs' copies, this GPU's included.
+int tcq4_b200_mul_mat_multicast(const void *w_tiles, const float *x, float *y_multicast, int64_t ldc, int64_t col0,
+                                int64_t M, int64_t N, int64_t K, const int32_t *d_perm, cudaStream_t stream) {
+    if (!shape_ok(M, N, K) || !y_multicast || col0 < 0 || (col0 & 3) || col0 + N > ldc) {
+        set_err("mul_mat_multicast: bad shape or column window");
+        return TCQ4_ERR_SHAPE;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    status = arena_ensure(d, ws_layout(M, N, K).total, stream);
+    if (status != TCQ4_OK) return status;
+    tcq4::YOut o = single_out(y_multicast + col0, N);
+    o.ldc = ldc;
+    o.mc = y_multicast + col0;
     return run_mul_mat(w_tiles, x, o, M, N, K, d_perm, d->arena, d->arena_bytes, TCQ4_KERNEL_AUTO, nullptr, stream);
 }
 

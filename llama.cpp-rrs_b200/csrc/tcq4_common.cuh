@@ -134,7 +134,15 @@ struct YOut {
     float    *p[MAX_PEERS];
     int       n;
     long long ldc;
-};
+    float    *mc;          // non-null: ONE multicast (NVLS) address of the symmetric C instead of p[]: every store is
+};                         // replicated to all GPUs by the switch (multimem.st), so the outbound traffic is 1x, not (G-1)x
+__device__ __forceinline__ void multimem_st_f32(float *addr, float v) {
+    asm volatile("multimem.st.weak.global.f32 [%0], %1;" ::"l"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_st_v4(float *addr, float4 v) {
+    asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
 
 // Programmatic dependent launch: a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start
 // once every CTA of its predecessor has executed launch_dependents (or exited); it must not touch memory the

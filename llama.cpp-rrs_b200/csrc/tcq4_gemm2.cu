@@ -252,6 +252,8 @@ __device__ __forceinline__ void g2_store_wait_read() {
 struct G2YMaps {       // one store map per destination matrix (this GPU's C, or every GPU's C when N-sharded)
     CUtensorMap m[MAX_PEERS];
     int n;
+    float *mc;             // non-null: multicast address of C (already offset to this call's first column)
+    long long mc_ldc;
 };
 
 template <int NTL, bool DEBUG, bool PROF = false>
@@ -568,6 +570,23 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
             const int row0 = mb * G2_BM + quarter * 32;
 #pragma unroll
             for (int ch = 0; ch < NTL; ch++) {
+                if (tm_y.mc) {
+                    // NVLS form: the box is read back 16 rows x 32 B per instruction and stored ONCE to the multicast
+                    // address; the switch replicates it into every GPU's C (this one included)
+                    uint8_t *box0 = obuf;
+                    __syncwarp();
+                    *reinterpret_cast<ulonglong2 *>(box0 + lane * 32) = make_ulonglong2(acc2[ch * 4 + 0], acc2[ch * 4 + 1]);
+                    *reinterpret_cast<ulonglong2 *>(box0 + lane * 32 + 16) = make_ulonglong2(acc2[ch * 4 + 2], acc2[ch * 4 + 3]);
+                    __syncwarp();
+                    const float4 v0 = *reinterpret_cast<const float4 *>(box0 + lane * 16);            // rows 0..15
+                    const float4 v1 = *reinterpret_cast<const float4 *>(box0 + 512 + lane * 16);      // rows 16..31
+                    if (n_base + ch * 8 < N) {
+                        float *dst = tm_y.mc + (size_t)(row0 + (lane >> 1)) * tm_y.mc_ldc + n_base + ch * 8 + (lane & 1) * 4;
+                        if (row0 + (lane >> 1) < M) multimem_st_v4(dst, v0);
+                        if (row0 + 16 + (lane >> 1) < M) multimem_st_v4(dst + (size_t)16 * tm_y.mc_ldc, v1);
+                    }
+                    continue;
+                }
                 uint8_t *box = obuf + (ch % G2_OUT_BOXES) * 1024;
                 if (ch >= G2_OUT_BOXES) {
                     if (lane == 0) g2_store_wait_read<G2_OUT_BOXES - 1>();     // the store that used this box has read it
@@ -674,6 +693,8 @@ static cudaError_t launch_gemm2_t(cudaLaunchConfig_t *cfg, const void *w_tiles, 
         return cudaErrorInvalidValue;      // unaligned tensor base or no driver entry point
     if (y.n < 1 || y.n > MAX_PEERS) return cudaErrorInvalidValue;
     tm_y.n = y.n;
+    tm_y.mc = y.mc;
+    tm_y.mc_ldc = y.ldc;
     for (int pi = 0; pi < MAX_PEERS; pi++)
         if (!g2_make_y_map(&tm_y.m[pi], y.p[pi < y.n ? pi : 0], M, N, y.ldc)) return cudaErrorInvalidValue;
     const int MB2 = (int)((M + 2 * G2_BM - 1) / (2 * G2_BM));

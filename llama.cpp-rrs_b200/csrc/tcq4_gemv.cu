@@ -320,9 +320,12 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                 for (int mb = 0; mb < MB; mb++)
 #pragma unroll
                     for (int j = 0; j < 2; j++)
-                        if (8 * mb + tk0 + j < M)
-                            for (int pi = 0; pi < out.n; pi++)
-                                out.p[pi][(size_t)(8 * mb + tk0 + j) * out.ldc + nt * 8 + c] = acc[mb][j];
+                        if (8 * mb + tk0 + j < M) {
+                            if (out.mc) multimem_st_f32(out.mc + (size_t)(8 * mb + tk0 + j) * out.ldc + nt * 8 + c, acc[mb][j]);
+                            else
+                                for (int pi = 0; pi < out.n; pi++)
+                                    out.p[pi][(size_t)(8 * mb + tk0 + j) * out.ldc + nt * 8 + c] = acc[mb][j];
+                        }
             } else {                                    // a cut row: park the partial in CTA 0's shared memory
                 const int e = wid * 2 + nseg;
 #pragma unroll
@@ -382,7 +385,9 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                     if (pr != row) break;
                     sum += part[(size_t)(j * M + m) * 8 + (lane & 7)];
                 }
-                for (int pi = 0; pi < out.n; pi++) out.p[pi][(size_t)m * out.ldc + row * 8 + (lane & 7)] = sum;
+                if (out.mc) multimem_st_f32(out.mc + (size_t)m * out.ldc + row * 8 + (lane & 7), sum);
+                else
+                    for (int pi = 0; pi < out.n; pi++) out.p[pi][(size_t)m * out.ldc + row * 8 + (lane & 7)] = sum;
             }
         }
     }
