@@ -571,19 +571,37 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
 #pragma unroll
             for (int ch = 0; ch < NTL; ch++) {
                 if (tm_y.mc) {
-                    // NVLS form: the box is read back 16 rows x 32 B per instruction and stored ONCE to the multicast
-                    // address; the switch replicates it into every GPU's C (this one included)
-                    uint8_t *box0 = obuf;
-                    __syncwarp();
-                    *reinterpret_cast<ulonglong2 *>(box0 + lane * 32) = make_ulonglong2(acc2[ch * 4 + 0], acc2[ch * 4 + 1]);
-                    *reinterpret_cast<ulonglong2 *>(box0 + lane * 32 + 16) = make_ulonglong2(acc2[ch * 4 + 2], acc2[ch * 4 + 3]);
-                    __syncwarp();
-                    const float4 v0 = *reinterpret_cast<const float4 *>(box0 + lane * 16);            // rows 0..15
-                    const float4 v1 = *reinterpret_cast<const float4 *>(box0 + 512 + lane * 16);      // rows 16..31
-                    if (n_base + ch * 8 < N) {
-                        float *dst = tm_y.mc + (size_t)(row0 + (lane >> 1)) * tm_y.mc_ldc + n_base + ch * 8 + (lane & 1) * 4;
-                        if (row0 + (lane >> 1) < M) multimem_st_v4(dst, v0);
-                        if (row0 + 16 + (lane >> 1) < M) multimem_st_v4(dst + (size_t)16 * tm_y.mc_ldc, v1);
+                    // NVLS form: chunks go through the two boxes in PAIRS and are read back 8 rows x 64 B per instruction,
+                    // then stored ONCE to the multicast address; the switch replicates every store into all GPUs' C
+                    // (this one included).  Wider row segments matter: 32-byte multicast writes reach ~140 GB/s per GPU.
+                    uint8_t *bx = obuf + (ch & 1) * 1024;
+                    if ((ch & 1) == 0) __syncwarp();             // the previous pair has been read back
+                    *reinterpret_cast<ulonglong2 *>(bx + lane * 32) = make_ulonglong2(acc2[ch * 4 + 0], acc2[ch * 4 + 1]);
+                    *reinterpret_cast<ulonglong2 *>(bx + lane * 32 + 16) = make_ulonglong2(acc2[ch * 4 + 2], acc2[ch * 4 + 3]);
+                    if ((ch & 1) == 1) {                         // both chunks of the pair are in the boxes
+                        __syncwarp();
+                        const int cpair = ch - 1;
+                        if (n_base + cpair * 8 < N) {            // N % 8 == 0 but not % 16: the second chunk may be outside
+                            const int q4 = lane & 3, rr = lane >> 2;
+                            const uint8_t *src = obuf + (q4 >> 1) * 1024 + (q4 & 1) * 16;
+                            const bool in2 = (q4 < 2) || (n_base + ch * 8 < N);
+#pragma unroll
+                            for (int k = 0; k < 4; k++) {
+                                const int r = rr + 8 * k;
+                                const float4 v = *reinterpret_cast<const float4 *>(src + r * 32);
+                                if (in2 && row0 + r < M)
+                                    multimem_st_v4(tm_y.mc + (size_t)(row0 + r) * tm_y.mc_ldc + n_base + cpair * 8 + q4 * 4, v);
+                            }
+                        }
+                    } else if (ch == NTL - 1) {                  // odd NTL: the last chunk alone, 16 rows x 32 B per instruction
+                        __syncwarp();
+                        const float4 v0 = *reinterpret_cast<const float4 *>(bx + lane * 16);            // rows 0..15
+                        const float4 v1 = *reinterpret_cast<const float4 *>(bx + 512 + lane * 16);      // rows 16..31
+                        if (n_base + ch * 8 < N) {
+                            float *dst = tm_y.mc + (size_t)(row0 + (lane >> 1)) * tm_y.mc_ldc + n_base + ch * 8 + (lane & 1) * 4;
+                            if (row0 + (lane >> 1) < M) multimem_st_v4(dst, v0);
+                            if (row0 + 16 + (lane >> 1) < M) multimem_st_v4(dst + (size_t)16 * tm_y.mc_ldc, v1);
+                        }
                     }
                     continue;
                 }
