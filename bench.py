@@ -185,7 +185,7 @@ def run_reference_arm(args):
                              "sample": f"each step = 1 of {QWEN3_4B_LAYERS} layers (7 matmuls, M={PREFILL_M}) scaled x{QWEN3_4B_LAYERS}"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------------------
@@ -565,7 +565,7 @@ def run_own_arm(args):
                 line["cpu_baseline"] = cpu_baseline_leg()
             except Exception as e:  # noqa: BLE001
                 line["cpu_baseline"] = {"error": f"{type(e).__name__}: {e}"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         # Captured graphs hold NCCL kernels; tearing the communicator down under them can block for minutes.
         # Everything is measured and printed: synchronise, meet once more, and leave without the teardown.
@@ -576,7 +576,23 @@ def run_own_arm(args):
         os._exit(0)
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict):
+    """The ONE JSON line of the contract, on the process's original stdout."""
+    out = _REAL_STDOUT if _REAL_STDOUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    # Everything else any library prints to fd 1 (NCCL's version banner, for one) goes to stderr: stdout carries
+    # exactly one JSON line.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
