@@ -256,7 +256,10 @@ struct G2YMaps {       // one store map per destination matrix (this GPU's C, or
     long long mc_ldc;
 };
 
-template <int NTL, bool DEBUG, bool PROF = false>
+// OUTM: 0 = one destination (ggml's dst; the code path of the single-GPU product), 1 = several peer-mapped
+// destinations (one tiled store per GPU), 2 = one NVSwitch multicast destination (multimem.st).  A template parameter:
+// carrying the choice at run time cost the plain path 8-10 % (measured).
+template <int NTL, bool DEBUG, bool PROF = false, int OUTM = 0>
 __global__ void __launch_bounds__(G2_THREADS, 1)
 tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_constant__ CUtensorMap tm_meta,
                   const __grid_constant__ G2YMaps tm_y, const uint8_t *__restrict__ w, ActStage st, int M, int N, int K,
@@ -306,7 +309,9 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_tiles) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_meta) : "memory");
-        for (int pi = 0; pi < tm_y.n; pi++) asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_y.m[pi]) : "memory");
+        if (OUTM != 2)
+            for (int pi = 0; pi < (OUTM == 1 ? tm_y.n : 1); pi++)
+                asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_y.m[pi]) : "memory");
     }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512)
@@ -570,7 +575,7 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
             const int row0 = mb * G2_BM + quarter * 32;
 #pragma unroll
             for (int ch = 0; ch < NTL; ch++) {
-                if (tm_y.mc) {
+                if (OUTM == 2) {
                     // NVLS form: chunks go through the two boxes in PAIRS and are read back 8 rows x 64 B per instruction,
                     // then stored ONCE to the multicast address; the switch replicates every store into all GPUs' C
                     // (this one included).  Wider row segments matter: 32-byte multicast writes reach ~140 GB/s per GPU.
@@ -615,8 +620,13 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
                 fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) {
-                    if (n_base + ch * 8 < N && row0 < M)
-                        for (int pi = 0; pi < tm_y.n; pi++) g2_tma_store_2d(&tm_y.m[pi], box, n_base + ch * 8, row0);
+                    if (n_base + ch * 8 < N && row0 < M) {
+                        if (OUTM == 1) {
+                            for (int pi = 0; pi < tm_y.n; pi++) g2_tma_store_2d(&tm_y.m[pi], box, n_base + ch * 8, row0);
+                        } else {
+                            g2_tma_store_2d(&tm_y.m[0], box, n_base + ch * 8, row0);
+                        }
+                    }
                     g2_store_commit();
                 }
             }
@@ -717,6 +727,12 @@ static cudaError_t launch_gemm2_t(cudaLaunchConfig_t *cfg, const void *w_tiles, 
         if (!g2_make_y_map(&tm_y.m[pi], y.p[pi < y.n ? pi : 0], M, N, y.ldc)) return cudaErrorInvalidValue;
     const int MB2 = (int)((M + 2 * G2_BM - 1) / (2 * G2_BM));
     const int num_tiles = (int)g2_tiles(M, N, NTL);
+    if (y.mc)
+        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, false, 2>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles,
+                                  st, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
+    if (y.n > 1)
+        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, false, 1>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles,
+                                  st, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
     static const bool prof = getenv("TCQ4_G2_PROF") != nullptr;     // diagnostics: timeline stamps of one cluster
     if (prof && !dbg_isum) {
         cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -746,8 +762,8 @@ cudaError_t launch_gemm2(const void *w_tiles, ActStage st, YOut y, int64_t M, in
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    static const bool no_pdl = getenv("TCQ4_NO_PDL") != nullptr;
-    cfg.numAttrs = no_pdl ? 1 : 2;
+    static const bool pdl = getenv("TCQ4_PDL") != nullptr;      // opt-in, see tcq4_gemv.cu (no measurable gain here)
+    cfg.numAttrs = pdl ? 2 : 1;
     static const int force_ntl = getenv("TCQ4_G2_NTL") ? atoi(getenv("TCQ4_G2_NTL")) : 0;     // experiments only
     int ntl = plan.ntl;
     if (force_ntl >= G2_MINNTL && force_ntl <= G2_MAXNTL) {
@@ -785,7 +801,12 @@ static cudaError_t gemm2_set_smem() {
     cudaError_t e = cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Gemm2Smem::total);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    e = cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm2Smem::total);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, false, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             Gemm2Smem::total);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, false, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 Gemm2Smem::total);
 }
 

@@ -1,5 +1,5 @@
 """GPU diagnostic (not a pytest file): time a chain of back-to-back GEMV launches, eager and as a CUDA graph.
-   TCQ4_NO_PDL=1 python tests/gpu_chain.py   disables programmatic dependent launch for comparison."""
+   TCQ4_PDL=1 python tests/gpu_chain.py   enables programmatic dependent launch (off by default) for comparison."""
 import os, sys
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -29,7 +29,7 @@ def run(M, N, K, nbuf=24):
             chain()
     us_g = timeit(g.replay, 10)
     wb = bufs[0].numel()
-    print(f"M={M} N={N} K={K} pdl={'off' if os.environ.get('TCQ4_NO_PDL') else 'on'}: eager {us_e:.2f} us/launch, graph {us_g:.2f} us/launch "
+    print(f"M={M} N={N} K={K} pdl={'on' if os.environ.get('TCQ4_PDL') else 'off'}: eager {us_e:.2f} us/launch, graph {us_g:.2f} us/launch "
           f"-> {wb / us_g / 1e3:.0f} GB/s", flush=True)
 
 for shp in [(1, 9728, 2560), (1, 2560, 9728), (1, 4096, 2560), (1, 1024, 2560), (8, 9728, 2560)]:
