@@ -61,9 +61,9 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
             if (lane < 8) blk->sum_q[lane] = (int16_t)gs;
             if (lane < 3) reinterpret_cast<uint32_t *>(blk->pad)[lane] = 0u;
         } else {
-            // s8 codes, sigma order {0,1,4,5,2,3,6,7}; lane pair (2j, 2j+1) forms 16-B K-chunk j
-            const uint32_t w0 = __byte_perm(e.x, e.y, 0x5410);       // e0 e1 e4 e5
-            const uint32_t w1 = __byte_perm(e.x, e.y, 0x7632);       // e2 e3 e6 e7
+            // s8 codes, sigma order {0,2,4,6,1,3,5,7}; lane pair (2j, 2j+1) forms 16-B K-chunk j
+            const uint32_t w0 = __byte_perm(e.x, e.y, 0x6420);       // e0 e2 e4 e6
+            const uint32_t w1 = __byte_perm(e.x, e.y, 0x7531);       // e1 e3 e5 e7
             const int mb = m >> 7, r = m & 127;
             int8_t *unit = st.codes + ((size_t)mb * KT + kt) * ACT_UNIT_BYTES;
             uint2 *dst = reinterpret_cast<uint2 *>(unit + (lane >> 1) * ACT_LBO + r * 16 + (lane & 1) * 8);

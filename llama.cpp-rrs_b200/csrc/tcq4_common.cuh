@@ -45,7 +45,7 @@ static_assert(sizeof(ActBlockTC) == 160, "block_rrs_int4_tc must be 160 bytes");
 // no-swizzle K-major UMMA layout:  [16 K-chunks of 16 B][16 row-groups][8 rows][16 B].
 //   LBO (K-direction core-matrix stride) = 2048 B, SBO (row-group stride) = 128 B.
 // Inside a 32-group the K byte order is sigma-permuted per 8-slice: byte r of slice s holds element
-// s*8 + SIGMA[r], SIGMA = {0,1,4,5,2,3,6,7} -- the order the weight unpack produces for free.
+// s*8 + SIGMA[r], SIGMA = {0,2,4,6,1,3,5,7} -- the order the weight unpack (unpack_chunk_split) produces for free.
 constexpr int ACT_UNIT_BYTES = 128 * 256;
 constexpr int ACT_LBO        = 2048;
 constexpr int ACT_SBO        = 128;
@@ -57,6 +57,41 @@ struct ActStage {           // pointers into the caller's workspace
 };
 
 __host__ __device__ inline int64_t round_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
+
+#ifdef __CUDACC__
+// ---- weight unpack for the tcgen05 GEMMs: one 16-byte chunk (channel c of group g: 32 int4 nibbles) ->
+//      32 "hi" bytes + 32 "lo" bytes of the s8 B operand, with the group's int8 sub-scale folded in EXACTLY:
+//          sc = 16*sh + sl  (sh = sc >> 4 arithmetic in [-8, 7], sl = sc & 15),   q in [-8, 7]
+//          p  = sc*q = 16*(sh*q) + (sl*q),    sh*q in [-56, 64],  sl*q in [-120, 105]   -> both fit s8
+//      so  16 * (A . hi) + (A . lo) = sum_k a_k * sc * q_k  in int32, the same identity the epilogue always used.
+//      Splitting the SCALE (not the product) keeps every field inside one byte, so a register of four nibble bytes
+//      is multiplied at once: with u = q + 8 in [0, 15],  byte = s*u + (128 - 8*s) = s*q + 128 in [8, 233] -- no carry
+//      between bytes for any s in [-8, 15] -- and one XOR 0x80 per byte turns it into the two's-complement s8.
+//      Per 8-nibble word: 1 shift, 2 mask ops, 4 multiply-adds, 4 XORs (the product-split version needed 17 with
+//      four byte permutes).  Even nibbles land in one register and odd ones in the next: K byte order inside an
+//      8-slice is {0,2,4,6,1,3,5,7}, which the activation kernel mirrors in its s8 codes.
+//      out_hi / out_lo point at this channel's 16-byte row in K-chunk 0; K-chunk 1 is lbo bytes further.
+__device__ __forceinline__ void unpack_chunk_split(const uint4 wq, int sc, uint8_t *out_hi, uint8_t *out_lo, int lbo) {
+    const uint32_t sh = (uint32_t)(sc >> 4), sl = (uint32_t)(sc & 15);
+    const uint32_t ch = 0x80808080u - sh * 0x08080808u;        // 128 - 8*sh in every byte
+    const uint32_t cl = 0x80808080u - sl * 0x08080808u;
+    const uint32_t wv[4] = {wq.x, wq.y, wq.z, wq.w};
+    uint32_t hi[8], lo[8];
+#pragma unroll
+    for (int s = 0; s < 4; s++) {
+        const uint32_t e = (wv[s] ^ 0x08080808u) & 0x0F0F0F0Fu;            // u of elements 0, 2, 4, 6
+        const uint32_t o = ((wv[s] >> 4) ^ 0x08080808u) & 0x0F0F0F0Fu;     // u of elements 1, 3, 5, 7
+        hi[s * 2 + 0] = (e * sh + ch) ^ 0x80808080u;
+        hi[s * 2 + 1] = (o * sh + ch) ^ 0x80808080u;
+        lo[s * 2 + 0] = (e * sl + cl) ^ 0x80808080u;
+        lo[s * 2 + 1] = (o * sl + cl) ^ 0x80808080u;
+    }
+    *reinterpret_cast<uint4 *>(out_hi) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4 *>(out_hi + lbo) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+    *reinterpret_cast<uint4 *>(out_lo) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    *reinterpret_cast<uint4 *>(out_lo + lbo) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+}
+#endif
 
 // ---------------------------------------------------------------------------------------------
 // PTX wrappers (sm_100a)

@@ -15,12 +15,9 @@
 // D_lo = A*lo over the whole 256-block, so  16*D_hi + D_lo = sum_g sc_g * dot_g  exactly in int32,
 // and the fp32 epilogue runs once per 256-block with  a7[m][kt] * S[n][kt] / 127.
 //
-// Weight unpack (CUDA cores, per 8-nibble word): nibble pairs are pulled into 16-bit fields,
-// biased to unsigned (u = q + 8), and ONE integer multiply-add per pair forms
-//     field = 16*sc*u + (32768 - 128*sc) = 16*p + 32768
-// whose byte 0 is 16*lo and byte 1 is hi + 128; two PRMTs gather the hi bytes (one XOR removes the
-// +128) and two the lo bytes (one shift removes the x16).  The resulting K byte order inside an 8-slice is
-// {0,1,4,5,2,3,6,7}; the activation kernel writes its s8 codes in the same order.
+// Weight unpack (CUDA cores): unpack_chunk_split in tcq4_common.cuh -- the group scale is split as sc = 16*sh + sl
+// and folded into the nibbles four bytes at a time ("hi" rows = sh*q, "lo" rows = sl*q, both s8).  The resulting
+// K byte order inside an 8-slice is {0,2,4,6,1,3,5,7}; the activation kernel writes its s8 codes in the same order.
 //
 // CTA = 128 tokens x 128 channels, 18 warps:
 //   warp 0       bulk-copy producer: per k-tile one 32 KB activation unit + 16 raw 1184-B weight tiles
@@ -76,32 +73,6 @@ __device__ __noinline__ float zero_point_term(const uint8_t *__restrict__ w, con
         zs += ((float)sumq[((size_t)m * KT + kt) * 8 + g] * a7) * bz;
     }
     return zs;
-}
-
-// Unpack one 16-byte chunk (channel c of group g: 32 nibbles) into 32 hi bytes + 32 lo bytes.
-//   out_hi / out_lo point at this channel's 16-byte row in K-chunk 0; K-chunk 1 is GM_B_LBO further.
-__device__ __forceinline__ void unpack_chunk(const uint4 wq, int sc, uint8_t *out_hi, uint8_t *out_lo) {
-    const uint32_t mul = (uint32_t)(16 * sc);
-    const uint32_t bias = (uint32_t)(32768 - 128 * sc) * 0x00010001u;
-    const uint32_t wv[4] = {wq.x, wq.y, wq.z, wq.w};
-    uint32_t hi[8], lo[8];
-#pragma unroll
-    for (int s = 0; s < 4; s++) {
-        uint32_t P[4];
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const uint32_t up = ((wv[s] >> (4 * i)) & 0x000F000Fu) ^ 0x00080008u;    // u = q + 8 in two fields
-            P[i] = up * mul + bias;                                                  // 16*sc*q + 32768
-        }
-        hi[s * 2 + 0] = __byte_perm(P[0], P[1], 0x7351) ^ 0x80808080u;               // elements 0,1,4,5
-        hi[s * 2 + 1] = __byte_perm(P[2], P[3], 0x7351) ^ 0x80808080u;               // elements 2,3,6,7
-        lo[s * 2 + 0] = __byte_perm(P[0], P[1], 0x6240) >> 4;
-        lo[s * 2 + 1] = __byte_perm(P[2], P[3], 0x6240) >> 4;
-    }
-    *reinterpret_cast<uint4 *>(out_hi) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-    *reinterpret_cast<uint4 *>(out_hi + GM_B_LBO) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-    *reinterpret_cast<uint4 *>(out_lo) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-    *reinterpret_cast<uint4 *>(out_lo + GM_B_LBO) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
 }
 
 template <bool DEBUG>
@@ -229,7 +200,7 @@ tcq4_gemm_kernel(const uint8_t *__restrict__ w, ActStage st, float *__restrict__
                         const uint4 wq = *reinterpret_cast<const uint4 *>(tp + g * 128 + c * 16);
                         const int sc = *reinterpret_cast<const int8_t *>(tp + TILE_OFF_SC + c * 8 + g);
                         uint8_t *row = bh + gl * GM_BGROUP_BYTES + j * 128 + c * 16;
-                        unpack_chunk(wq, sc, row, row + GM_NTL * 128);      // lo rows follow the 128 hi rows
+                        unpack_chunk_split(wq, sc, row, row + GM_NTL * 128, GM_B_LBO);      // lo rows follow the 128 hi rows
                     }
                 }
                 fence_proxy_async_smem();

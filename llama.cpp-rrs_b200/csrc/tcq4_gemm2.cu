@@ -1,6 +1,6 @@
 // tcq4_gemm2.cu -- K2 for M > 128: W4A4 prefill GEMM on CTA PAIRS (tcgen05.mma.cta_group::2 kind::i8).
 //
-// Same exact integer formulation as tcq4_gemm.cu (p = sc*q = 16*hi + lo folded into the weight operand, one
+// Same exact integer formulation as tcq4_gemm.cu (p = sc*q = 16*(sh*q) + sl*q folded into the weight operand, one
 // 256-wide accumulation per 256-block, fp32 epilogue once per 256-block), re-tiled so that the CUDA-core work
 // per tensor-core cycle halves:
 //   * a cluster of two CTAs (one TPC) owns 256 tokens x (16*NTL) channels; each CTA stages its own 128 token
@@ -121,6 +121,18 @@ __device__ __forceinline__ void umma_i8_2cta(uint32_t d_tmem, uint64_t a_desc, u
         "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// same, the two 64-bit shared-memory descriptors given as {low, high} 32-bit halves
+__device__ __forceinline__ void umma_i8_2cta_parts(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                                   uint32_t b_hi, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "mov.b64 da, {%1, %2};\n\t"
+        "mov.b64 db, {%3, %4};\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::i8 [%0], da, db, %5, p;\n\t}" ::"r"(d_tmem),
+        "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // arrive on the barrier at this shared-memory offset in BOTH CTAs when all prior MMAs of this thread completed
 __device__ __forceinline__ void umma_commit_2cta(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::
@@ -158,35 +170,6 @@ __device__ __noinline__ float g2_zero_point_term(const uint8_t *__restrict__ w, 
         zs += ((float)sumq[((size_t)m * KT + kt) * 8 + g] * a7) * bz;
     }
     return zs;
-}
-
-// Unpack one 16-byte chunk (channel c of group g: 32 nibbles) into 32 hi bytes + 32 lo bytes (see tcq4_gemm.cu).
-//   out_hi / out_lo point at this channel's 16-byte row in K-chunk 0; K-chunk 1 is `lbo` bytes further.
-// Two nibbles per IMAD in 16-bit fields: field = 16*sc*(q + 8) + (32768 - 128*sc) = 16*p + 32768, whose high byte
-// is (hi + 128) and whose low byte is 16*lo.  Odd nibbles stay where they are (value 16*u) and take the
-// multiplier sc instead of 16*sc, so one shift serves four fields.
-__device__ __forceinline__ void g2_unpack_chunk(const uint4 wq, int sc, uint8_t *out_hi, uint8_t *out_lo, int lbo) {
-    const uint32_t mul16 = (uint32_t)(16 * sc), mul1 = (uint32_t)sc;
-    const uint32_t bias = (uint32_t)(32768 - 128 * sc) * 0x00010001u;
-    const uint32_t wv[4] = {wq.x, wq.y, wq.z, wq.w};
-    uint32_t hi[8], lo[8];
-#pragma unroll
-    for (int s = 0; s < 4; s++) {
-        const uint32_t x = wv[s] ^ 0x88888888u;                                      // u = q + 8 in every nibble
-        const uint32_t x8 = x >> 8;
-        const uint32_t P0 = (x & 0x000F000Fu) * mul16 + bias;                        // elements 0, 4
-        const uint32_t P1 = (x & 0x00F000F0u) * mul1 + bias;                         // elements 1, 5
-        const uint32_t P2 = (x8 & 0x000F000Fu) * mul16 + bias;                       // elements 2, 6
-        const uint32_t P3 = (x8 & 0x00F000F0u) * mul1 + bias;                        // elements 3, 7
-        hi[s * 2 + 0] = __byte_perm(P0, P1, 0x7351) ^ 0x80808080u;                   // elements 0,1,4,5
-        hi[s * 2 + 1] = __byte_perm(P2, P3, 0x7351) ^ 0x80808080u;                   // elements 2,3,6,7
-        lo[s * 2 + 0] = __byte_perm(P0, P1, 0x6240) >> 4;
-        lo[s * 2 + 1] = __byte_perm(P2, P3, 0x6240) >> 4;
-    }
-    *reinterpret_cast<uint4 *>(out_hi) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-    *reinterpret_cast<uint4 *>(out_hi + lbo) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-    *reinterpret_cast<uint4 *>(out_lo) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-    *reinterpret_cast<uint4 *>(out_lo + lbo) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
 }
 
 __device__ __forceinline__ int g2_mad16(uint32_t hi, uint32_t lo) {      // 16*hi + lo as ONE integer multiply-add
@@ -362,40 +345,51 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         }
       } else if (warp == 1) {
         // ===================== MMA issuer (leader CTA only) =====================
-        if (rank == 0 && lane == 0) {
+        // The whole warp walks the loop converged and ONE elected lane issues (elect.sync, which lets ptxas keep the
+        // operands in uniform registers without a per-instruction election loop); the descriptors are a constant high
+        // word plus a low word that advances by compile-time constants.  This loop IS the kernel's critical path: the
+        // first version (one lane under `lane == 0`, descriptors rebuilt from addresses, ~200 instructions per k-tile
+        // at ~10 cycles each in a loaded SM) issued a k-tile's eight MMAs slower than the tensor pipe executes them.
+        if (rank == 0) {
             constexpr uint32_t idesc = umma_idesc_i8(2 * G2_BM, 32 * NTL, 1, 1);      // 256 x (32*NTL) x 32, s8 x s8
-            const uint32_t stage_base = smem_u32(sStage), b_base = smem_u32(sB);
+            constexpr uint32_t a_hi = (uint32_t)(ACT_SBO >> 4) | (1u << 14);          // bits 32..: SBO, version bit 46
+            constexpr uint32_t b_hi = (uint32_t)(128 >> 4) | (1u << 14);
+            const uint32_t a_lo0 = (smem_u32(sStage) >> 4) | ((uint32_t)(ACT_LBO >> 4) << 16);
+            const uint32_t b_lo0 = (smem_u32(sB) >> 4) | ((uint32_t)(LBO >> 4) << 16);
             int my_tiles = 0;
             for (int t = cluster_id; t < num_tiles; t += num_clusters) my_tiles++;
             const int total_k = my_tiles * KT;
             int s = 0;
             for (int gk = 0; gk < total_k; gk++) {
                 const int as = gk & 1, u2 = gk >> 1;
-                G2_STAMP(1, gk, 0);
+                if (lane == 0) G2_STAMP(1, gk, 0);
                 if (u2 > 0) g2_wait(&accempty[as], (uint32_t)((u2 - 1) & 1));
-                G2_STAMP(1, gk, 1);
-                tc_fence_after();
+                if (lane == 0) G2_STAMP(1, gk, 1);
                 const uint32_t d = tmem + as * 256;
+                const uint32_t a_lo = a_lo0 + (uint32_t)s * (G2_STAGE_BYTES >> 4);
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
                     const int hs = 2 * (gk & 1) + h, v = gk >> 1;
                     g2_wait(&bfull[hs], (uint32_t)(v & 1));      // also: both CTAs' stage s has landed
-                    G2_STAMP(1, gk, 2 + h);
+                    if (lane == 0) G2_STAMP(1, gk, 2 + h);
                     tc_fence_after();
+                    if (elect_one()) {
+                        const uint32_t b_lo = b_lo0 + (uint32_t)hs * (G2_BH_BYTES >> 4);
 #pragma unroll
-                    for (int gl = 0; gl < 4; gl++) {
-                        const int g = h * 4 + gl;
-                        const uint64_t a_desc =
-                            umma_desc_kmajor_noswz(stage_base + s * G2_STAGE_BYTES + (2 * g) * ACT_LBO, ACT_LBO, ACT_SBO);
-                        const uint64_t b_desc =
-                            umma_desc_kmajor_noswz(b_base + hs * G2_BH_BYTES + gl * BGROUP, (uint32_t)LBO, 128);
-                        umma_i8_2cta(d, a_desc, b_desc, idesc, g > 0 ? 1u : 0u);
+                        for (int gl = 0; gl < 4; gl++) {
+                            const int g = h * 4 + gl;
+                            umma_i8_2cta_parts(d, a_lo + (uint32_t)g * ((2 * ACT_LBO) >> 4), a_hi,
+                                               b_lo + (uint32_t)gl * (BGROUP >> 4), b_hi, idesc, g > 0 ? 1u : 0u);
+                        }
+                        umma_commit_2cta(&bfree[hs]);
+                        if (h == 1) {
+                            umma_commit_2cta(&empty[s]);
+                            umma_commit_2cta(&accfull[as]);
+                        }
                     }
-                    umma_commit_2cta(&bfree[hs]);
+                    __syncwarp();
                 }
-                umma_commit_2cta(&empty[s]);
-                umma_commit_2cta(&accfull[as]);
-                G2_STAMP(1, gk, 4);
+                if (lane == 0) G2_STAMP(1, gk, 4);
                 if (++s == G2_STAGES) s = 0;
             }
         }
@@ -458,7 +452,7 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
                             const uint4 wq = *reinterpret_cast<const uint4 *>(tp + g * 128 + c_t * 16);
                             const int sc = *reinterpret_cast<const int8_t *>(tp + TILE_OFF_SC + c_t * 8 + g);
                             uint8_t *row = sB + hs * G2_BH_BYTES + b_off;
-                            g2_unpack_chunk(wq, sc, row, row + NTL * 128, LBO);      // lo rows follow the 8*NTL hi rows
+                            unpack_chunk_split(wq, sc, row, row + NTL * 128, LBO);      // lo rows follow the 8*NTL hi rows
                         }
                         fence_proxy_async_smem();
                     }
