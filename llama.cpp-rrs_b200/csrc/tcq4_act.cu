@@ -95,6 +95,13 @@ static cudaError_t launch_act(Kern kern, int grid, cudaStream_t stream, const fl
     // kernels' own prologues had been shortened); TCQ4_PDL=1 turns it on for experiments -- then x must be read
     // with ld.global.cg (rrs_load_block_cg).
     cfg.numAttrs = 0;
+    // same L1/shared split as the GEMM that follows (no SM reconfiguration between the two launches)
+    static bool carve_ref = false, carve_stage = false;
+    bool &done = (out_ref != nullptr) ? carve_ref : carve_stage;
+    if (!done) {
+        cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+        done = true;
+    }
     return cudaLaunchKernelEx(&cfg, kern, x, perm, M, K, out_ref, st);
 }
 

@@ -35,12 +35,9 @@
 
 namespace tcq4 {
 
-constexpr int GV_WARPS = 16;
-constexpr int GV_DEPTH = 4;
-constexpr int GV_THREADS = GV_WARPS * 32;
+// Warps per CTA and ring depth are launch parameters (GemvPlan); the planner uses 16 warps x 4 tiles.
 constexpr int GV_CLUSTER = 2;
-constexpr int GV_WORKERS = GV_WARPS * GV_CLUSTER;     // warps of a cluster
-constexpr int GV_ENTRIES = GV_WORKERS * 2;            // partial-row slots (a warp cuts at most two rows)
+// a cluster has 2*NW workers (warps) and 4*NW partial-row slots (a warp cuts at most two rows)
 
 struct GvSplit {    // even split of T items over W workers, contiguous
     int base, rem;
@@ -83,33 +80,36 @@ __device__ __forceinline__ void mma_s8(int (&d)[4], uint32_t a0, uint32_t a1, ui
 
 // shared-memory carve-up (bytes), shared by the kernel and the planner
 struct GvSmem {
-    int off_ring, off_full, off_afrag, off_rm, off_sumq, off_part, off_prow, off_cbar, off_scratch, total;
+    int off_ring, off_full, off_afrag, off_rm, off_sumq, off_part, off_prow, off_cbar, total;
     __host__ __device__ static int al(int o) { return (o + 15) & ~15; }
-    __host__ __device__ GvSmem(int M, int KT) {
+    __host__ __device__ GvSmem(int M, int KT, int NW, int depth) {
+        const int entries = NW * GV_CLUSTER * 2;
         int o = 0;
-        off_ring = o;    o = al(o + GV_WARPS * GV_DEPTH * TILE_BYTES);   // 75776
-        off_full = o;    o = al(o + GV_WARPS * GV_DEPTH * 8);
+        off_ring = o;    o = al(o + NW * depth * TILE_BYTES);            // 75776 (16 x 4) or 113664 (32 x 3)
+        off_full = o;    o = al(o + NW * depth * 8);
         off_afrag = o;   o = al(o + M * KT * 256);                       // [KT][8 groups][M][4 k-quarters] uint2 = M*K bytes
         off_rm = o;      o = al(o + 2 * M * KT * 4);                     // [KT][M] a7/127, then [KT][M] a7
         off_sumq = o;    o = al(o + M * KT * 8 * 4);                     // [M][KT][8] group sums (zero-point path)
-        off_part = o;    o = al(o + GV_ENTRIES * M * 32);                // [entry][M rows][8 ch] fp32 (used in CTA 0)
-        off_prow = o;    o = al(o + GV_ENTRIES * 4);                     // [entry] n-tile or -1
+        off_part = o;    o = al(o + entries * M * 32);                   // [entry][M rows][8 ch] fp32 (used in CTA 0)
+        off_prow = o;    o = al(o + entries * 4);                        // [entry] n-tile or -1
         off_cbar = o;    o = al(o + 8);                                  // (CTA 0) "all partial rows have landed"
-        off_scratch = o; o = al(o + GV_WARPS * 1024);                    // FWHT transposition scratch, 1 KB per warp
         total = o;
     }
 };
 
 // phase timestamps (ns, %globaltimer) of the DEBUG instantiation: [cta][0..5] = start, prefetch issued,
 // dependency resolved, activation stage done, stream loop done, end
-__device__ unsigned long long g_gv_prof[160][8];
-__device__ unsigned long long g_gv_iter[GV_WARPS][8][3];     // CTA 0: per warp, per tile: wait begin / data ready / done
+__device__ unsigned long long g_gv_prof[160][16];
+__device__ unsigned long long g_gv_iter[16][8][3];     // CTA 0: per warp, per tile: wait begin / data ready / done
 __device__ __forceinline__ unsigned long long gtime() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
-#define GV_ITER(i, k) do { if (DEBUG && blockIdx.x == 0 && lane == 0 && (i) < 8) g_gv_iter[warp][i][k] = gtime(); } while (0)
+#define GV_ITER(i, k) do { if (DEBUG && blockIdx.x == 0 && lane == 0 && warp < 16 && (i) < 8) g_gv_iter[warp][i][k] = gtime(); } while (0)
+// stamp taken only once `dep` (a float) is available
+#define GV_STAMP_DEP(i, dep) do { if (DEBUG && threadIdx.x == 0 && blockIdx.x < 160) { unsigned long long t_; \
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_) : "f"(dep)); g_gv_prof[blockIdx.x][i] = t_; } } while (0)
 #define GV_STAMP(i) do { if (DEBUG && threadIdx.x == 0 && blockIdx.x < 160) g_gv_prof[blockIdx.x][i] = gtime(); } while (0)
 
 // Zero-point term of one (row, channel, k-tile) (tcq4_k32.cu:850,872-873).  Cold: the fork's quantiser always
@@ -126,17 +126,21 @@ __device__ __noinline__ float gv_zero_point(unsigned short zh, uint2 zcv, const 
     return zs;
 }
 
-template <int MB, bool DEBUG>
-__global__ void __launch_bounds__(GV_THREADS, MB == 1 ? 2 : 1)
+// MT > 0 selects the dp4a inner loop for exactly MT <= 4 tokens (see "dp4a path" below); MT = 0 the IMMA loop for
+// up to 8 * MB tokens.
+template <int MB, int MT, bool DEBUG>
+__global__ void __launch_bounds__(512, (MT == 1 && !DEBUG) ? 2 : 1)
 tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, const int32_t *__restrict__ perm,
-                 const YOut out, int M, int N, int K, int32_t *__restrict__ dbg_isum) {
+                 const YOut out, int M, int N, int K, int depth, int32_t *__restrict__ dbg_isum) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int KT = K / TILE_K;
     const int NT = N / TILE_CH;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = lane & 3, r = lane >> 2;          // mma fragment coordinates: k-quarter / row (token) or column pair
 
-    const GvSmem L(M, KT);
+    const int NW = (int)(blockDim.x >> 5);          // warps of this CTA
+    const int workers = NW * GV_CLUSTER, entries = workers * 2;
+    const GvSmem L(M, KT, NW, depth);
     uint8_t *ring = smem + L.off_ring;
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + L.off_full);
     uint2 *afrag = reinterpret_cast<uint2 *>(smem + L.off_afrag);      // [KT][8][M][4]
@@ -152,8 +156,8 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     const int cid = blockIdx.x / GV_CLUSTER, ncl = gridDim.x / GV_CLUSTER;
     const GvSplit rs(NT, ncl);
     const int R0 = rs.start(cid), nR = rs.count(cid);
-    const int wid = crank * GV_WARPS + warp;
-    const GvSplit wsp(nR * KT, GV_WORKERS);
+    const int wid = crank * NW + warp;
+    const GvSplit wsp(nR * KT, workers);
     const int lt0 = wsp.start(wid), cnt = wsp.count(wid);
 
     GV_STAMP(0);
@@ -162,22 +166,21 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     if (crank == 0 && threadIdx.x == 0) {
         mbar_init(cbar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        mbar_arrive_expect_tx(cbar, (uint32_t)(GV_ENTRIES * (M * 32 + 4)));
+        mbar_arrive_expect_tx(cbar, (uint32_t)(entries * (M * 32 + 4)));
     }
 
     // ---- weight prefetch: constant data, legal before the programmatic dependency resolves -----------
     // Each warp owns its ring and its barriers: lane 0 initialises them and issues the first copies without
     // any CTA-wide barrier (the other lanes first touch them after the __syncthreads below).
-    uint8_t *myring = ring + warp * GV_DEPTH * TILE_BYTES;
-    uint64_t *myfull = full + warp * GV_DEPTH;
+    uint8_t *myring = ring + warp * depth * TILE_BYTES;
+    uint64_t *myfull = full + warp * depth;
     const uint8_t *wsrc = w + ((size_t)R0 * KT + lt0) * TILE_BYTES;
     uint64_t pol = 0;
     if (lane == 0) {
-#pragma unroll
-        for (int i = 0; i < GV_DEPTH; i++) mbar_init(&myfull[i], 1);
+        for (int i = 0; i < depth; i++) mbar_init(&myfull[i], 1);
         fence_mbar_init();
         pol = l2_policy_evict_first();
-        const int pre = cnt < GV_DEPTH ? cnt : GV_DEPTH;
+        const int pre = cnt < depth ? cnt : depth;
         for (int i = 0; i < pre; i++) {
             mbar_arrive_expect_tx(&myfull[i], TILE_BYTES);
             bulk_g2s_stream(myring + i * TILE_BYTES, wsrc + (size_t)i * TILE_BYTES, TILE_BYTES, &myfull[i], pol);
@@ -188,29 +191,45 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     // ordering only -- the init was published by fence.mbarrier_init -- so the relaxed form, which has no fence)
     asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
     GV_STAMP(1);
-    pdl_launch_dependents();     // the next MUL_MAT may start its own prefetch on this SM
+    pdl_launch_dependents();     // the next MUL_MAT may start its own prefetch on this SM (signalling later -- after
+                                 // the activation stage or after the loop -- measured 3-20 % slower)
     pdl_wait();                  // x belongs to the previous kernel until here
     GV_STAMP(2);
 
     // ---- activation stage for all M rows -----------------------------------------------------------------
     // (latency-bound here -- at most a few 256-blocks per warp -- so the all-shuffle butterfly, whose dependent
     //  chain is shorter than the shared-memory transposition of K1, is the faster one)
-    for (int b = warp; b < M * KT; b += GV_WARPS) {
+    // The loads of the next block are issued before the butterfly of the current one: a warp with several blocks
+    // (K = 9728: 38 blocks per row) pays the L2 round trip once, not once per block.
+    float vn[8];
+    if (warp < M * KT) rrs_load_block_cg(x + (size_t)(warp / KT) * K, perm, warp % KT, lane, vn);
+    for (int b = warp; b < M * KT; b += NW) {
         const int m = b / KT, kt = b - m * KT;
         float v[8];
-        rrs_load_block_cg(x + (size_t)m * K, perm, kt, lane, v);
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = vn[i];
+        if (b + NW < M * KT) rrs_load_block_cg(x + (size_t)((b + NW) / KT) * K, perm, (b + NW) % KT, lane, vn);
+        if (b == warp) GV_STAMP_DEP(8, v[0] + v[7]);
         const ActQuant a = rrs_quantize_block(v, lane);                // lane = (group r, k-quarter q), elements lane*8..+7
+        if (b == warp) GV_STAMP_DEP(9, a.max_abs + (float)(a.q[7] + a.gsum));
         const uint32_t ev = (uint32_t)(a.q[0] & 0xFF) | ((uint32_t)(a.q[2] & 0xFF) << 8) |
                             ((uint32_t)(a.q[4] & 0xFF) << 16) | ((uint32_t)(a.q[6] & 0xFF) << 24);
         const uint32_t od = (uint32_t)(a.q[1] & 0xFF) | ((uint32_t)(a.q[3] & 0xFF) << 8) |
                             ((uint32_t)(a.q[5] & 0xFF) << 16) | ((uint32_t)(a.q[7] & 0xFF) << 24);
-        afrag[((kt * 8 + r) * M + m) * 4 + q] = make_uint2(ev, od);
+        if (MT > 0) {       // dp4a path: per (k-tile, group, token) 32 bytes = {ev of slices 0..3, od of slices 0..3}
+            uint32_t *ad = reinterpret_cast<uint32_t *>(afrag) + ((kt * 8 + r) * M + m) * 8;
+            ad[q] = ev;
+            ad[4 + q] = od;
+        } else {
+            afrag[((kt * 8 + r) * M + m) * 4 + q] = make_uint2(ev, od);
+        }
         if (lane == 0) {
             const float a7 = __fdiv_rn(a.max_abs, 7.0f);
             a7s[kt * M + m] = a7;
             rms[kt * M + m] = a7 * (1.0f / 127.0f);
         }
         if (q == 0) sumq[(m * KT + kt) * 8 + r] = a.gsum;
+        if (b == warp) GV_STAMP(6);
     }
     __syncthreads();
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -236,10 +255,133 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     const uint2 *af1 = afrag + brow1 * 4 + q;
     const int af_g = M * 4;                                    // uint2 stride between groups
 
+    if constexpr (MT > 0) {
+    // ---- dp4a path (M = MT <= 4) ---------------------------------------------------------------------------
+    // With one to four tokens the m16n8k32 shape is mostly padding and the loop is bound by instruction issue, so the
+    // lanes are re-mapped for wide loads instead: lane l = (gq = l / 8, cc = l % 8) reads words 4l .. 4l+3 of the tile's
+    // first and second half with two LDS.128 = ALL 32 nibbles of channel cc in groups gq and gq + 4.  Per word: three
+    // logic ops (even / odd nibbles as 16*q in s8 lanes) and two DP4A per token against the token's codes (LDS.128,
+    // broadcast within a group).  The two group dots (16*dot fits s16) meet their scale codes in one IDP.2A; two
+    // shuffles add the four group pairs: isum = sum_g sc_g * dot_g, the same int32 as the IMMA path and the GEMMs.
+    const int cc = lane & 7, gq = lane >> 3;
+    const uint32_t scsel = (uint32_t)gq | ((uint32_t)(4 + gq) << 4);      // PRMT: byte 0 = sc[gq], byte 1 = sc[gq + 4]
+    const uint4 *afq = reinterpret_cast<const uint4 *>(afrag);           // [(kt*8 + g) * M + m][2] = {ev[4]}, {od[4]}
+    float accd[MT];
+#pragma unroll
+    for (int m = 0; m < MT; m++) accd[m] = 0.0f;
+    int slot = 0;
+    uint32_t phase = 0;
     for (int i = 0; i < cnt; i++) {
-        const int slot = i % GV_DEPTH;
         GV_ITER(i, 0);
-        mbar_wait(&myfull[slot], (uint32_t)((i / GV_DEPTH) & 1));
+        mbar_wait(&myfull[slot], phase);
+        GV_ITER(i, 1);
+        const uint8_t *tp = myring + slot * TILE_BYTES;
+        const uint4 w0 = *reinterpret_cast<const uint4 *>(tp + lane * 16);
+        const uint4 w1 = *reinterpret_cast<const uint4 *>(tp + 512 + lane * 16);
+        const uint2 scv = *reinterpret_cast<const uint2 *>(tp + TILE_OFF_SC + 8 * cc);
+        const unsigned short sh = *reinterpret_cast<const unsigned short *>(tp + TILE_OFF_S + 2 * cc);
+        const unsigned short zh = *reinterpret_cast<const unsigned short *>(tp + TILE_OFF_Z + 2 * cc);
+        const bool anyz = __any_sync(0xffffffffu, (zh & 0x7FFFu) != 0u);
+        uint2 zcv = make_uint2(0, 0);
+        if (anyz) zcv = *reinterpret_cast<const uint2 *>(tp + TILE_OFF_ZC + 8 * cc);
+        __syncwarp();
+        if (i + depth < cnt) {
+            if (elect_one()) {
+                const uint32_t bar = full_u32 + slot * 8, dst = ring_u32 + slot * TILE_BYTES;
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(TILE_BYTES) : "memory");
+                asm volatile(
+                    "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
+                        "r"(dst), "l"(wsrc + (size_t)(i + depth) * TILE_BYTES), "r"(TILE_BYTES), "r"(bar), "l"(pol)
+                    : "memory");
+            }
+        }
+        const uint32_t ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+        uint32_t ae[8], ao[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            ae[j] = (ww[j] << 4) & 0xF0F0F0F0u;
+            ao[j] = ww[j] & 0xF0F0F0F0u;
+        }
+        const int scp = (int)__byte_perm(scv.x, scv.y, scsel);
+        const float S = __half2float(__ushort_as_half(sh));
+#pragma unroll
+        for (int m = 0; m < MT; m++) {
+            const uint4 *a0p = afq + ((kt * 8 + gq) * MT + m) * 2;
+            const uint4 *a1p = afq + ((kt * 8 + gq + 4) * MT + m) * 2;
+            const uint4 e0 = a0p[0], o0 = a0p[1], e1 = a1p[0], o1 = a1p[1];
+            int d0 = __dp4a((int)ae[0], (int)e0.x, 0);
+            d0 = __dp4a((int)ao[0], (int)o0.x, d0);
+            d0 = __dp4a((int)ae[1], (int)e0.y, d0);
+            d0 = __dp4a((int)ao[1], (int)o0.y, d0);
+            d0 = __dp4a((int)ae[2], (int)e0.z, d0);
+            d0 = __dp4a((int)ao[2], (int)o0.z, d0);
+            d0 = __dp4a((int)ae[3], (int)e0.w, d0);
+            d0 = __dp4a((int)ao[3], (int)o0.w, d0);
+            int d1 = __dp4a((int)ae[4], (int)e1.x, 0);
+            d1 = __dp4a((int)ao[4], (int)o1.x, d1);
+            d1 = __dp4a((int)ae[5], (int)e1.y, d1);
+            d1 = __dp4a((int)ao[5], (int)o1.y, d1);
+            d1 = __dp4a((int)ae[6], (int)e1.z, d1);
+            d1 = __dp4a((int)ao[6], (int)o1.z, d1);
+            d1 = __dp4a((int)ae[7], (int)e1.w, d1);
+            d1 = __dp4a((int)ao[7], (int)o1.w, d1);
+            int is = __dp2a_lo((int)__byte_perm((uint32_t)d0, (uint32_t)d1, 0x5410), scp, 0);
+            is += __shfl_xor_sync(0xffffffffu, is, 8);
+            is += __shfl_xor_sync(0xffffffffu, is, 16);
+            const int isv = is >> 4;                                 // weights were carried as 16*q: exact
+            accd[m] = __fmaf_rn((float)isv * rms[kt * MT + m], S, accd[m]);
+            if (anyz) accd[m] += gv_zero_point(zh, zcv, sumq + (m * KT + kt) * 8, a7s[kt * MT + m]);
+            if (DEBUG && dbg_isum && lane < 8) dbg_isum[((size_t)m * N + nt * 8 + cc) * KT + kt] = isv;
+        }
+        GV_ITER(i, 2);
+        if (++slot == depth) { slot = 0; phase ^= 1u; }
+
+        const bool row_end = (kt == KT - 1);
+        if (row_end || i == cnt - 1) {
+            if (row_end && from_row_start) {            // the whole row was this warp's: lanes 0..7 hold its 8 channels
+                if (lane < 8) {
+#pragma unroll
+                    for (int m = 0; m < MT; m++) {
+                        if (out.mc) multimem_st_f32(out.mc + (size_t)m * out.ldc + nt * 8 + cc, accd[m]);
+                        else
+                            for (int pi = 0; pi < out.n; pi++) out.p[pi][(size_t)m * out.ldc + nt * 8 + cc] = accd[m];
+                    }
+                }
+            } else {                                    // a cut row: park the partial in CTA 0's shared memory
+                const int e = wid * 2 + nseg;
+                if (lane < 8) {
+#pragma unroll
+                    for (int m = 0; m < MT; m++)
+                        dsmem_st_async(part0 + (uint32_t)(((e * MT + m) * 8 + cc) * 4), __float_as_uint(accd[m]), cbar0);
+                }
+                if (lane == 0) dsmem_st_async(prow0 + (uint32_t)(e * 4), (uint32_t)nt, cbar0);
+                nseg++;
+            }
+#pragma unroll
+            for (int m = 0; m < MT; m++) accd[m] = 0.0f;
+        }
+        if (row_end) {
+            kt = 0;
+            nt++;
+            from_row_start = true;
+        } else {
+            kt++;
+        }
+    }
+    for (; nseg < 2; nseg++) {                          // unused entry slots are sent too: fixed byte total
+        const int e = wid * 2 + nseg;
+        if (lane < 8) {
+#pragma unroll
+            for (int m = 0; m < MT; m++) dsmem_st_async(part0 + (uint32_t)(((e * MT + m) * 8 + cc) * 4), 0u, cbar0);
+        }
+        if (lane == 0) dsmem_st_async(prow0 + (uint32_t)(e * 4), 0xFFFFFFFFu, cbar0);
+    }
+    } else {
+    int slot = 0;
+    uint32_t phase = 0;
+    for (int i = 0; i < cnt; i++) {
+        GV_ITER(i, 0);
+        mbar_wait(&myfull[slot], phase);
         GV_ITER(i, 1);
 
         const uint8_t *tp = myring + slot * TILE_BYTES;
@@ -253,13 +395,13 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
         uint2 zcv = make_uint2(0, 0);
         if (anyz) zcv = *reinterpret_cast<const uint2 *>(tp + TILE_OFF_ZC + 8 * c);
         __syncwarp();
-        if (i + GV_DEPTH < cnt) {                  // refill the slot just drained (warp-uniform operands, one issuer)
+        if (i + depth < cnt) {                  // refill the slot just drained (warp-uniform operands, one issuer)
             if (elect_one()) {
                 const uint32_t bar = full_u32 + slot * 8, dst = ring_u32 + slot * TILE_BYTES;
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(TILE_BYTES) : "memory");
                 asm volatile(
                     "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
-                        "r"(dst), "l"(wsrc + (size_t)(i + GV_DEPTH) * TILE_BYTES), "r"(TILE_BYTES), "r"(bar), "l"(pol)
+                        "r"(dst), "l"(wsrc + (size_t)(i + depth) * TILE_BYTES), "r"(TILE_BYTES), "r"(bar), "l"(pol)
                     : "memory");
             }
         }
@@ -311,6 +453,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
             }
         }
         GV_ITER(i, 2);
+        if (++slot == depth) { slot = 0; phase ^= 1u; }
 
         // end of this warp's share of row nt?
         const bool row_end = (kt == KT - 1);
@@ -360,14 +503,16 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                 if (8 * mb + tk0 + j < M) dsmem_st_async(part0 + (uint32_t)(((e * M + 8 * mb + tk0 + j) * 8 + c) * 4), 0u, cbar0);
         if (lane == 0) dsmem_st_async(prow0 + (uint32_t)(e * 4), 0xFFFFFFFFu, cbar0);
     }
+    }   // IMMA path
     GV_STAMP(4);
     if (crank != 0) return;      // nothing reads this CTA's shared memory: CTA 1 is done
     mbar_wait(cbar, 0u);         // all partials (local and remote) have landed in CTA 0
+    GV_STAMP(7);
 
     // ---- CTA 0 combines the cut rows in k order (entry order = worker order = tile order) ----------------
     if (crank == 0) {
-        for (int sidx = 0; sidx < GV_ENTRIES / GV_WARPS; sidx++) {
-            const int e = warp * (GV_ENTRIES / GV_WARPS) + sidx;
+        for (int sidx = 0; sidx < 4; sidx++) {                  // entries / NW = 4 slots per warp
+            const int e = warp * 4 + sidx;
             const int row = prow[e];
             if (row < 0) continue;
             int prev = -1;
@@ -376,10 +521,47 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                 if (pr >= 0) { prev = pr; break; }
             }
             if (prev == row) continue;                         // an earlier entry owns this row's run
+            if (M <= 2) {
+                // One or two tokens leave 3/4 of the lanes idle in the loop below and a run of ten or more entries
+                // (N=1024, K=2560: every warp holds one tile) costs ~60 cycles per entry.  Here the lanes look at 32
+                // entries at once (two ballots give the run), lane quarter jj sums every 4th member and two shuffles
+                // add the quarters: a fixed association, so the result stays deterministic.
+                const int jj = lane >> 3, c8 = lane & 7;
+                float s2[2] = {0.0f, 0.0f};
+                int nth = 0;
+                for (int base = e;; base += 32) {
+                    const int idx = base + lane;
+                    const int pr = idx < entries ? prow[idx] : 0x7fffffff;      // past the end: ends the run
+                    const unsigned stopm = __ballot_sync(0xffffffffu, pr >= 0 && pr != row);
+                    const int lim = stopm ? __ffs((int)stopm) - 1 : 32;
+                    unsigned same = __ballot_sync(0xffffffffu, pr == row) & (lim == 32 ? 0xffffffffu : ((1u << lim) - 1u));
+                    while (same) {
+                        const int i = __ffs((int)same) - 1;
+                        same &= same - 1u;
+                        if ((nth & 3) == jj) {
+                            s2[0] += part[(size_t)((base + i) * M) * 8 + c8];
+                            if (M == 2) s2[1] += part[(size_t)((base + i) * M + 1) * 8 + c8];
+                        }
+                        nth++;
+                    }
+                    if (lim < 32) break;
+                }
+                for (int m = 0; m < M; m++) {
+                    float v = s2[m];
+                    v += __shfl_xor_sync(0xffffffffu, v, 8);
+                    v += __shfl_xor_sync(0xffffffffu, v, 16);
+                    if (jj == 0) {
+                        if (out.mc) multimem_st_f32(out.mc + (size_t)m * out.ldc + row * 8 + c8, v);
+                        else
+                            for (int pi = 0; pi < out.n; pi++) out.p[pi][(size_t)m * out.ldc + row * 8 + c8] = v;
+                    }
+                }
+                continue;
+            }
             // lane -> (token m = lane / 8 (+4 per pass), channel lane % 8): coalesced 32-byte row pieces of y
             for (int m = lane >> 3; m < M; m += 4) {
                 float sum = 0.0f;
-                for (int j = e; j < GV_ENTRIES; j++) {
+                for (int j = e; j < entries; j++) {
                     const int pr = prow[j];
                     if (pr < 0) continue;
                     if (pr != row) break;
@@ -400,8 +582,26 @@ bool gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, 
     if (M < 1 || M > GEMV_MAX_M) return false;
     const int64_t NT = N / TILE_CH, KT = K / TILE_K;
     if (NT * KT >= (int64_t)1 << 30) return false;                 // 32-bit tile arithmetic in the kernel
-    const GvSmem L((int)M, (int)KT);
+    // 16 warps.  (32 warps x 3 tiles -- every tile of the decode shapes requested by the prologue -- measured 20 %
+    // SLOWER, 12.1 vs 10.0 us at N=9728, K=2560: the loop is bound by instruction issue, not by latency.)
+    // Ring depth = the most tiles any warp will see, at most 3.  Deeper rings measured slower once launches overlap
+    // (N=9728, K=2560, M=1, graph of 24 launches: 7.0 us per launch with 2 or 3 slots, 7.4 with 4, 7.8 with 5): the
+    // prefetch burst of the next launch shares the SM's return path with the refills of the running one, and
+    // two resident CTAs must share the 228 KB.
+    const int nw = 16;
+    int64_t clusters_ = num_sms / GV_CLUSTER;
+    if (NT < clusters_) clusters_ = NT;
+    if (clusters_ < 1) clusters_ = 1;
+    const int64_t rows_max = (NT + clusters_ - 1) / clusters_;
+    const int64_t per_warp = (rows_max * KT + nw * GV_CLUSTER - 1) / (nw * GV_CLUSTER);
+    int depth = per_warp < 2 ? 2 : (per_warp > 3 ? 3 : (int)per_warp);
+    static const char *denv = getenv("TCQ4_GV_DEPTH");
+    if (denv && atoi(denv) >= 2 && atoi(denv) <= 8) depth = atoi(denv);
+    while (depth > 2 && (size_t)GvSmem((int)M, (int)KT, nw, depth).total > smem_optin) depth--;
+    const GvSmem L((int)M, (int)KT, nw, depth);
     if ((size_t)L.total > smem_optin) return false;
+    plan->warps = nw;
+    plan->depth = depth;
     int64_t clusters = num_sms / GV_CLUSTER;
     if (NT < clusters) clusters = NT;                              // a cluster owns whole rows
     if (clusters < 1) clusters = 1;
@@ -413,12 +613,12 @@ bool gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, 
     return true;
 }
 
-template <int MB, bool DEBUG>
+template <int MB, int MT, bool DEBUG>
 static cudaError_t launch_gemv_t(const void *w, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
                                  int64_t K, const GemvPlan &plan, int32_t *dbg, cudaStream_t stream) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)plan.grid);
-    cfg.blockDim = dim3(GV_THREADS);
+    cfg.blockDim = dim3((unsigned)plan.warps * 32);
     cfg.dynamicSmemBytes = plan.smem_bytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr[2];
@@ -429,26 +629,46 @@ static cudaError_t launch_gemv_t(const void *w, const float *x, const int32_t *p
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    // programmatic dependent launch: opt-in (TCQ4_PDL=1).  It paid while the kernel's prologue cost 1.25 us; with
-    // the fence-free prologue the decode chain is 8 % FASTER without it (2.33 vs 2.53 ms per 252 launches).
-    static const bool pdl = getenv("TCQ4_PDL") != nullptr;
+    // Programmatic dependent launch (TCQ4_NO_PDL=1 turns it off).  It pays when this launch and the next one fit one SM
+    // together (M = 1: 64 registers, ring of <= 5 tiles): the next MUL_MAT's barrier setup and weight prefetch run under
+    // this one's loop.  N=9728, K=2560, M=1, 24 launches in a graph: 8.5 us per launch without, 7.0 us with.
+    static const bool pdl = getenv("TCQ4_NO_PDL") == nullptr;
     cfg.numAttrs = pdl ? 2 : 1;
-    return cudaLaunchKernelEx(&cfg, tcq4_gemv_kernel<MB, DEBUG>, (const uint8_t *)w, x, perm, y, (int)M, (int)N, (int)K, dbg);
+    return cudaLaunchKernelEx(&cfg, tcq4_gemv_kernel<MB, MT, DEBUG>, (const uint8_t *)w, x, perm, y, (int)M, (int)N, (int)K,
+                              plan.depth, dbg);
 }
 
-template <int MB>
-static cudaError_t gemv_attr_mb(size_t smem_optin) {
-    cudaError_t e = cudaFuncSetAttribute(tcq4_gemv_kernel<MB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+template <int MB, int MT>
+static cudaError_t gemv_attr_one(size_t smem_optin) {
+    cudaError_t e = cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)smem_optin);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(tcq4_gemv_kernel<MB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)smem_optin);
+    e = cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_optin);
+    if (e != cudaSuccess) return e;
+    // One shared-memory carve-out for every launch: matmuls of different K ask for different amounts of shared memory,
+    // and an SM cannot host the next launch (programmatic dependent launch) while its L1/shared split must change.
+    e = cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                             (int)cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, false>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                (int)cudaSharedmemCarveoutMaxShared);
 }
 
 cudaError_t gemv_init_attributes(size_t smem_optin) {
-    cudaError_t e = gemv_attr_mb<1>(smem_optin);
-    if (e != cudaSuccess) return e;
-    return gemv_attr_mb<2>(smem_optin);
+    cudaError_t e = gemv_attr_one<1, 0>(smem_optin);
+    if (e == cudaSuccess) e = gemv_attr_one<2, 0>(smem_optin);
+    if (e == cudaSuccess) e = gemv_attr_one<1, 1>(smem_optin);
+    if (e == cudaSuccess) e = gemv_attr_one<1, 2>(smem_optin);
+    if (e == cudaSuccess) e = gemv_attr_one<1, 3>(smem_optin);
+    if (e == cudaSuccess) e = gemv_attr_one<1, 4>(smem_optin);
+    return e;
+}
+
+template <int MB, int MT>
+static cudaError_t launch_gemv_d(bool debug, const void *w, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
+                                 int64_t K, const GemvPlan &plan, int32_t *dbg, cudaStream_t stream) {
+    if (debug) return launch_gemv_t<MB, MT, true>(w, x, perm, y, M, N, K, plan, dbg, stream);
+    return launch_gemv_t<MB, MT, false>(w, x, perm, y, M, N, K, plan, nullptr, stream);
 }
 
 cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
@@ -457,12 +677,20 @@ cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm
     (void)ws_partial;
     (void)ws_ticket;
     if (M < 1 || M > GEMV_MAX_M) return cudaErrorInvalidValue;
-    if (gemv_mb(M) == 1) {
-        if (dbg_isum) return launch_gemv_t<1, true>(w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
-        return launch_gemv_t<1, false>(w_tiles, x, perm, y, M, N, K, plan, nullptr, stream);
+    static const bool prof = getenv("TCQ4_GV_PROF") != nullptr;      // phase stamps without the isum dump
+    static const bool nodp = getenv("TCQ4_GV_NODP") != nullptr;      // diagnostics: IMMA loop for every M
+    const bool dbg = dbg_isum != nullptr || prof;
+    if (!nodp) {
+        switch (M) {
+            case 1: return launch_gemv_d<1, 1>(dbg, w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
+            case 2: return launch_gemv_d<1, 2>(dbg, w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
+            case 3: return launch_gemv_d<1, 3>(dbg, w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
+            case 4: return launch_gemv_d<1, 4>(dbg, w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
+            default: break;
+        }
     }
-    if (dbg_isum) return launch_gemv_t<2, true>(w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
-    return launch_gemv_t<2, false>(w_tiles, x, perm, y, M, N, K, plan, nullptr, stream);
+    if (gemv_mb(M) == 1) return launch_gemv_d<1, 0>(dbg, w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
+    return launch_gemv_d<2, 0>(dbg, w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
 }
 
 cudaError_t gemv_read_prof(unsigned long long *host_out, size_t bytes) {

@@ -19,6 +19,8 @@ cudaError_t launch_act_quant_stage(const float *x, const int32_t *perm, int64_t 
 constexpr int GEMV_MAX_M = 16;
 struct GemvPlan {
     int     grid;            // CTAs (persistent, one per SM)
+    int     warps;           // warps per CTA (16 or 32)
+    int     depth;           // tiles in flight per warp (ring slots)
     size_t  smem_bytes;
     int     maxslots;        // split-K partial slots per n-tile row
     size_t  partial_bytes;   // workspace: float [NT][maxslots][8 or 16 rows][8]

@@ -1,12 +1,12 @@
 """GPU diagnostic (not a pytest file): time a chain of back-to-back GEMV launches, eager and as a CUDA graph.
-   TCQ4_PDL=1 python tests/gpu_chain.py   enables programmatic dependent launch (off by default) for comparison."""
+   TCQ4_NO_PDL=1 python tests/gpu_chain.py   disables programmatic dependent launch (on by default) for comparison."""
 import os, sys
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import __graft_entry__ as graft
 t4 = graft.load_package()
 
-def run(M, N, K, nbuf=24):
+def run(M, N, K, nbuf=int(os.environ.get('NBUF', '24'))):
     bufs = [t4.random_tiles(N, K, seed=i) for i in range(nbuf)]
     x = torch.randn((M, K), device="cuda")
     ws = t4.Workspace.for_shape(M, N, K)
@@ -29,8 +29,36 @@ def run(M, N, K, nbuf=24):
             chain()
     us_g = timeit(g.replay, 10)
     wb = bufs[0].numel()
-    print(f"M={M} N={N} K={K} pdl={'on' if os.environ.get('TCQ4_PDL') else 'off'}: eager {us_e:.2f} us/launch, graph {us_g:.2f} us/launch "
+    print(f"M={M} N={N} K={K} pdl={'off' if os.environ.get('TCQ4_NO_PDL') else 'on'}: eager {us_e:.2f} us/launch, graph {us_g:.2f} us/launch "
           f"-> {wb / us_g / 1e3:.0f} GB/s", flush=True)
 
-for shp in [(1, 9728, 2560), (1, 2560, 9728), (1, 4096, 2560), (1, 1024, 2560), (8, 9728, 2560)]:
-    run(*shp)
+def layer_chain(M, layers=int(os.environ.get('LAYERS', '36'))):
+    """the bench's decode chain: 7 matmuls per layer, distinct weights per layer, inputs independent of outputs"""
+    shapes = [(4096, 2560), (1024, 2560), (1024, 2560), (2560, 4096), (9728, 2560), (9728, 2560), (2560, 9728)]
+    W = [[t4.random_tiles(n, k, seed=l * 8 + j) for j, (n, k) in enumerate(shapes)] for l in range(layers)]
+    x = {k: torch.randn((M, k), device="cuda") for k in (2560, 4096, 9728)}
+    y = {n: torch.empty((M, n), device="cuda") for n in (4096, 1024, 2560, 9728)}
+    ws = t4.Workspace.for_shape(M, 9728, 9728)
+    def chain():
+        for l in range(layers):
+            for j, (n, k) in enumerate(shapes):
+                t4.mul_mat(W[l][j], x[k], n, out=y[n], workspace=ws)
+    for _ in range(2): chain()
+    g = torch.cuda.CUDAGraph(); s = torch.cuda.Stream(); s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        with torch.cuda.graph(g, stream=s):
+            chain()
+    for _ in range(3): g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10): g.replay()
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 10
+    print(f"layer chain M={M} layers={layers}: {ms:.3f} ms/step, {ms * 1e3 / (layers * 7):.2f} us/launch", flush=True)
+
+if os.environ.get("LAYER_CHAIN"):
+    layer_chain(1)
+else:
+    for shp in [(1, 9728, 2560), (1, 2560, 9728), (1, 4096, 2560), (1, 1024, 2560), (8, 9728, 2560)]:
+        run(*shp)
