@@ -138,6 +138,36 @@ TCQ4_B200_API int tcq4_b200_host_sync(void);
 TCQ4_B200_API int tcq4_b200_fwht_quantize_tc(const float *x, void *y_blocks, const int32_t *d_perm,
                                              int64_t K, int64_t M, cudaStream_t stream);
 
+/* ---- quantiser side and GET_ROWS (the producer of the format and the only other op that reads it) ------
+ * Device weight quantiser, byte-identical to quantize_tcq4_tile (ggml/src/ggml-quants.c:1528-1639; reached through
+ * ggml_quantize_chunk, ggml.c:7681) on the same F32 input: per 8 rows and 256 columns FWHT-256, per-group absmax/7
+ * scales, fp16 super-scale, int8 sub-scale codes, int4 codes in mma.m16n8k32 B-fragment order, Z = zc = 0.
+ *   w      : F32 [nrow][K] row-major (device), 16-byte aligned;  K % 256 == 0
+ *   tiles  : out, [ceil(nrow/8)][K/256] block_tcq4_tile = tcq4_b200_quantize_size(nrow, K) bytes; rows past nrow are
+ *            quantised as zeros, as the reference pads its last group (ggml-quants.c:1565-1568)
+ *   d_perm : int32[K] device permutation or NULL: quantises W'[n][j] = W[n][perm[j]], i.e. apply_channel_perm_to_weights
+ *            (src/llama-quant.cpp:26-40) fused into the load.
+ * Asynchronous on `stream`, capture-safe. */
+TCQ4_B200_API size_t tcq4_b200_quantize_size(int64_t nrow, int64_t K);
+TCQ4_B200_API int tcq4_b200_quantize_tiles(const float *w, void *tiles, int64_t nrow, int64_t K, const int32_t *d_perm,
+                                           cudaStream_t stream);
+
+/* derive_tcq4_perms_from_imatrix for one tensor (tools/quantize/quantize.cpp:127-165): inside every 256-block the channel
+ * indices sorted by imatrix value, descending.  HOST arrays.  std::sort leaves the order of equal values unspecified in
+ * the reference; here ties keep ascending index.  A trailing partial block (K % 256 != 0) is sorted on its own, as there. */
+TCQ4_B200_API int tcq4_b200_perm_from_imatrix(const float *imatrix_host, int64_t K, int32_t *perm_host);
+
+/* GET_ROWS for a TCQ4 src0 (ggml_cuda_op_get_rows -> get_rows_cuda, ggml/src/ggml-cuda/getrows.cu:348-380: tile
+ * dequantisation k_get_rows_tcq4_tile :96-171 followed by the FWHT-256 that returns the rows to the weight domain; CPU
+ * counterpart ggml/src/ggml-cpu/ops.cpp:4800-4824), one fused pass:
+ *   dst[i][:] = FWHT256( dequant(row rows[i] of the tensor) ),   dst row stride dst_stride floats (>= K, % 4 == 0).
+ *   rows: int32[n_idx] device.  An index outside [0, nrows_src) gives a zero row and, when err_flag (device int) is
+ *   non-NULL, sets *err_flag = 1 (the reference reads out of bounds).  Channel permutations are NOT undone, as in the fork.
+ * Asynchronous on `stream`, capture-safe. */
+TCQ4_B200_API int tcq4_b200_get_rows(const void *w_tiles, const int32_t *rows, float *dst, int64_t n_idx,
+                                     int64_t nrows_src, int64_t K, int64_t dst_stride, int *err_flag,
+                                     cudaStream_t stream);
+
 /* Verification taps (not on the product path): run the chosen kernel and also dump the integer
  * accumulators.  isum: int32 [M][N][K/256] = sum_g sc[n][kt][g]*dot_g (the TMEM accumulator of the
  * GEMM, and the same quantity formed from the per-group dots in the GEMV).  Nullable. */

@@ -43,6 +43,7 @@ EXPORTS = [
     "tcq4_b200_profile_begin", "tcq4_b200_profile_end", "tcq4_b200_debug_gemv_phases", "tcq4_b200_debug_gemm2_timeline",
     "tcq4_b200_measure_pipe",
     "tcq4_b200_measure_tmem_ld", "tcq4_b200_measure_umma2",
+    "tcq4_b200_quantize_size", "tcq4_b200_quantize_tiles", "tcq4_b200_perm_from_imatrix", "tcq4_b200_get_rows",
 ]
 
 
@@ -103,6 +104,11 @@ def _load() -> C.CDLL:
     lib.tcq4_b200_measure_pipe.argtypes = [ci, ci, C.POINTER(C.c_double)]
     lib.tcq4_b200_measure_tmem_ld.argtypes = [ci, ci, ci, C.POINTER(C.c_double)]
     lib.tcq4_b200_profile_begin.argtypes = [ci]
+    lib.tcq4_b200_quantize_size.restype = sz
+    lib.tcq4_b200_quantize_size.argtypes = [i64, i64]
+    lib.tcq4_b200_quantize_tiles.argtypes = [vp, vp, i64, i64, vp, vp]
+    lib.tcq4_b200_perm_from_imatrix.argtypes = [vp, i64, vp]
+    lib.tcq4_b200_get_rows.argtypes = [vp, vp, vp, i64, i64, i64, i64, vp, vp]
     lib.tcq4_b200_profile_end.argtypes = [ci, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(ci)]
     return lib
 
@@ -156,6 +162,20 @@ def workspace_size(M: int, N: int, K: int) -> int:
 def tile_bytes(N: int, K: int) -> int:
     """ggml_nbytes of an [N][K] TCQ4_K32 tensor (ggml.c:750-757: N * K/256 * 148)."""
     return (N // TILE_CHANNELS) * (K // TILE_K) * TILE_BYTES
+
+
+def quantize_size(nrow: int, K: int) -> int:
+    """bytes of the tile tensor tcq4_b200_quantize_tiles writes: ceil(nrow/8) * K/256 * 1184."""
+    return int(LIB.tcq4_b200_quantize_size(nrow, K))
+
+
+def perm_from_imatrix(imatrix):
+    """derive_tcq4_perms_from_imatrix for one tensor (tools/quantize/quantize.cpp:127-165); numpy in, numpy int32 out."""
+    import numpy as np
+    im = np.ascontiguousarray(imatrix, dtype=np.float32)
+    out = np.empty(im.shape[0], dtype=np.int32)
+    _check(LIB.tcq4_b200_perm_from_imatrix(im.ctypes.data, im.shape[0], out.ctypes.data))
+    return out
 
 
 def shard_range(N: int, K: int, world: int, rank: int, align: int = 128):

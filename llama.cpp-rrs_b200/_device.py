@@ -13,11 +13,11 @@ import ctypes as C
 import torch
 
 from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
-               ACT_BLOCK_BYTES, TensorView, _check, shard_range, tile_bytes, workspace_size)
+               ACT_BLOCK_BYTES, TensorView, _check, quantize_size, shard_range, tile_bytes, workspace_size)
 
 __all__ = ["Workspace", "mul_mat", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
-           "ggml_supports_op", "ShardedWeight", "random_tiles"]
+           "ggml_supports_op", "ShardedWeight", "random_tiles", "quantize_tiles", "get_rows"]
 
 
 def _stream_ptr(stream=None) -> int:
@@ -154,6 +154,31 @@ def fwht_quantize_tc(x: torch.Tensor, perm: torch.Tensor | None = None, stream=N
     out = torch.empty((M, K // TILE_K, ACT_BLOCK_BYTES), dtype=torch.uint8, device=x.device)
     pp = perm.data_ptr() if perm is not None else 0
     _check(LIB.tcq4_b200_fwht_quantize_tc(x.data_ptr(), out.data_ptr(), pp, K, M, _stream_ptr(stream)))
+    return out
+
+
+def quantize_tiles(w: torch.Tensor, perm: torch.Tensor | None = None, stream=None) -> torch.Tensor:
+    """Device weight quantiser (quantize_tcq4_tile, ggml-quants.c:1528-1639): F32 [nrow][K] -> uint8 tile bytes
+    [ceil(nrow/8) * K/256 * 1184]; perm (int32[K], device) quantises W[:, perm] (llama-quant.cpp:26-40)."""
+    _req_cuda(w, torch.float32, "w")
+    nrow, K = w.shape
+    out = torch.empty(quantize_size(nrow, K), dtype=torch.uint8, device=w.device)
+    pp = perm.data_ptr() if perm is not None else 0
+    _check(LIB.tcq4_b200_quantize_tiles(w.data_ptr(), out.data_ptr(), nrow, K, pp, _stream_ptr(stream)))
+    return out
+
+
+def get_rows(w_tiles: torch.Tensor, rows: torch.Tensor, nrows_src: int, K: int, out: torch.Tensor | None = None,
+             err_flag: torch.Tensor | None = None, stream=None) -> torch.Tensor:
+    """GET_ROWS of a TCQ4 tensor (getrows.cu:96-171 + 348-380): out[i] = FWHT256(dequant(row rows[i])), F32 [n][K]."""
+    _req_cuda(w_tiles, torch.uint8, "w_tiles")
+    _req_cuda(rows, torch.int32, "rows")
+    n = rows.numel()
+    if out is None:
+        out = torch.empty((n, K), dtype=torch.float32, device=w_tiles.device)
+    ef = err_flag.data_ptr() if err_flag is not None else 0
+    _check(LIB.tcq4_b200_get_rows(w_tiles.data_ptr(), rows.data_ptr(), out.data_ptr(), n, nrows_src, K, out.stride(0), ef,
+                                  _stream_ptr(stream)))
     return out
 
 

@@ -40,9 +40,9 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
         const int m = (int)(b / KT);
         const int kt = (int)(b - (long long)m * KT);
         float v[8];
-        // __ldg is safe only because this kernel is NOT launched early (see launch_act): with programmatic stream
-        // serialization a stale L1 line of x could survive from an overlapping predecessor
-        rrs_load_block(x + (size_t)m * K, perm, kt, lane, v);
+        // ld.global.cg: every element is read once, and under programmatic stream serialization a stale L1 line of x
+        // could survive from an overlapping predecessor
+        rrs_load_block_cg(x + (size_t)m * K, perm, kt, lane, v);
         const ActQuantT a = rrs_quantize_block_t<true>(v, lane, scratch);
         const uint2 e = rrs_codes_layout_a(a, lane, scratch);        // byte r = code of element lane*8 + r
         int gs = 0;                                                  // lane g < 8 keeps the sum of group g
@@ -94,7 +94,8 @@ static cudaError_t launch_act(Kern kern, int grid, cudaStream_t stream, const fl
     // Dependent launch is OFF by default (measured round 1: no gain for prefill, -8 % for the decode chain once the
     // kernels' own prologues had been shortened); TCQ4_PDL=1 turns it on for experiments -- then x must be read
     // with ld.global.cg (rrs_load_block_cg).
-    cfg.numAttrs = 0;
+    static const bool pdl = getenv("TCQ4_PDL") != nullptr;
+    cfg.numAttrs = pdl ? 1 : 0;
     // same L1/shared split as the GEMM that follows (no SM reconfiguration between the two launches)
     static bool carve_ref = false, carve_stage = false;
     bool &done = (out_ref != nullptr) ? carve_ref : carve_stage;

@@ -7,6 +7,7 @@
 // entries (tcq4_b200_mul_mat's arena growth outside capture, tcq4_b200_mul_mat_host).
 #include "../../include/tcq4_b200.h"
 
+#include <algorithm>
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
@@ -579,6 +580,64 @@ int tcq4_b200_fwht_quantize_tc(const float *x, void *y_blocks, const int32_t *d_
     cudaError_t e = tcq4::launch_act_quant_ref(x, d_perm, M, K, y_blocks, d->num_sms, stream);
     if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
     g_launches.fetch_add(1, std::memory_order_relaxed);
+    return TCQ4_OK;
+}
+
+size_t tcq4_b200_quantize_size(int64_t nrow, int64_t K) {
+    if (nrow < 0 || K < 0 || (K % 256) != 0) return 0;
+    return (size_t)((nrow + 7) / 8) * (size_t)(K / 256) * TCQ4_B200_TILE_BYTES;
+}
+
+int tcq4_b200_quantize_tiles(const float *w, void *tiles, int64_t nrow, int64_t K, const int32_t *d_perm,
+                             cudaStream_t stream) {
+    if (nrow < 1 || K < 256 || (K % 256) != 0 || K > (int64_t)1 << 30) {
+        set_err("quantize_tiles: need nrow >= 1 and K %% 256 == 0 (got nrow=%lld K=%lld)", (long long)nrow, (long long)K);
+        return TCQ4_ERR_SHAPE;
+    }
+    if (!w || !tiles || ((uintptr_t)w & 15) || ((uintptr_t)tiles & 15) || (d_perm && ((uintptr_t)d_perm & 15))) {
+        set_err("quantize_tiles: null or misaligned pointer (16-byte alignment)");
+        return TCQ4_ERR_ARG;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    cudaError_t e = tcq4::launch_quantize_tiles(w, d_perm, tiles, nrow, K, d->num_sms, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "quantiser launch");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return TCQ4_OK;
+}
+
+int tcq4_b200_get_rows(const void *w_tiles, const int32_t *rows, float *dst, int64_t n_idx, int64_t nrows_src, int64_t K,
+                       int64_t dst_stride, int *err_flag, cudaStream_t stream) {
+    if (n_idx < 0 || nrows_src < 1 || K < 256 || (K % 256) != 0 || K > (int64_t)1 << 30 || dst_stride < K || (dst_stride & 3)) {
+        set_err("get_rows: need K %% 256 == 0, nrows_src >= 1, dst_stride >= K and a multiple of 4");
+        return TCQ4_ERR_SHAPE;
+    }
+    if (n_idx == 0) return TCQ4_OK;
+    if (!w_tiles || !rows || !dst || ((uintptr_t)w_tiles & 15) || ((uintptr_t)dst & 15) || ((uintptr_t)rows & 3)) {
+        set_err("get_rows: null or misaligned pointer");
+        return TCQ4_ERR_ARG;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    cudaError_t e = tcq4::launch_get_rows(w_tiles, rows, dst, n_idx, nrows_src, K, dst_stride, err_flag, d->num_sms, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "get_rows launch");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return TCQ4_OK;
+}
+
+int tcq4_b200_perm_from_imatrix(const float *imatrix_host, int64_t K, int32_t *perm_host) {
+    if (!imatrix_host || !perm_host || K < 1 || K > (int64_t)1 << 30) {
+        set_err("perm_from_imatrix: null pointer or bad K");
+        return TCQ4_ERR_ARG;
+    }
+    for (int64_t i = 0; i < K; i++) perm_host[i] = (int32_t)i;
+    for (int64_t b0 = 0; b0 < K; b0 += 256) {
+        const int64_t b1 = b0 + 256 < K ? b0 + 256 : K;
+        std::stable_sort(perm_host + b0, perm_host + b1,
+                         [imatrix_host](int32_t a, int32_t b) { return imatrix_host[a] > imatrix_host[b]; });
+    }
     return TCQ4_OK;
 }
 

@@ -32,6 +32,12 @@ cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm
                         int64_t K, const GemvPlan &plan, float *ws_partial, int *ws_ticket, int32_t *dbg_isum,
                         cudaStream_t stream);
 
+// ---- K4 / K5: device weight quantiser and GET_ROWS (tcq4_quant.cu) ------------------------------
+cudaError_t launch_quantize_tiles(const float *w, const int32_t *perm, void *tiles, int64_t nrow, int64_t K, int num_sms,
+                                  cudaStream_t stream);
+cudaError_t launch_get_rows(const void *tiles, const int32_t *rows, float *dst, int64_t n_idx, int64_t nrows_src,
+                            int64_t K, int64_t dst_stride, int *err_flag, int num_sms, cudaStream_t stream);
+
 cudaError_t gemm2_read_prof(long long *host_out, size_t bytes);            // PROF-instantiation timeline stamps
 cudaError_t gemv_read_prof(unsigned long long *host_out, size_t bytes);   // DEBUG-instantiation phase stamps
 

@@ -64,6 +64,7 @@ class Oracle:
         L.orc_quantize_tiles.restype = C.c_size_t
         L.orc_quantize_tiles.argtypes = [_f32p, C.c_void_p, C.c_int64, C.c_int64]
         L.orc_dequant_tiles.argtypes = [C.c_void_p, _f32p, C.c_int64]
+        L.orc_get_rows.argtypes = [C.c_void_p, _i32p, C.c_int64, C.c_int64, _f32p]
         L.orc_apply_perm_weights.argtypes = [_f32p, _f32p, C.c_int64, C.c_int64, _i32p]
         L.orc_perm_from_imatrix.argtypes = [_f32p, C.c_int64, _i32p]
         L.orc_quantize_act_row.argtypes = [_f32p, _i32p, C.c_int64, _i8p, _f32p, _i16p]
@@ -123,6 +124,14 @@ class Oracle:
         """Tile bytes -> Hadamard-domain weight matrix [N][K] float32."""
         y = self.dequant_tiles(tiles).reshape(N // 8, K // 256, 8, 256)
         return np.ascontiguousarray(y.transpose(0, 2, 1, 3)).reshape(N, K)
+
+    def get_rows(self, tiles: np.ndarray, rows: np.ndarray, K: int) -> np.ndarray:
+        """GET_ROWS: [len(rows)][K] float32 = FWHT256(dequant(selected rows))."""
+        tiles = np.ascontiguousarray(tiles, dtype=np.uint8)
+        rows = np.ascontiguousarray(rows, dtype=np.int32)
+        out = np.zeros((rows.size, K), dtype=np.float32)
+        self.lib.orc_get_rows(tiles.ctypes.data, _ptr(rows, _i32p), rows.size, K, _ptr(out, _f32p))
+        return out
 
     def apply_perm_weights(self, W: np.ndarray, perm: np.ndarray) -> np.ndarray:
         W = np.ascontiguousarray(W, dtype=np.float32)

@@ -204,6 +204,35 @@ void orc_dequant_tiles(const void *tiles, float *y, int64_t k) {
     }
 }
 
+/* ------------------------------------------------------------------------------------------
+ * GET_ROWS of a TCQ4 tensor -- ggml/src/ggml-cuda/getrows.cu:96-171 (row i01 = channel i01 % 8 of
+ * n-tile i01 / 8; scale = S*sc/127, zero = Z*zc/127, value = scale*q + zero) followed by the
+ * FWHT in 256-element chunks that takes the row back to the weight domain (getrows.cu:372-378;
+ * CPU: ggml/src/ggml-cpu/ops.cpp:4800-4824, ggml_fwht_impl with step 256).
+ * ---------------------------------------------------------------------------------------- */
+void orc_get_rows(const void *tiles, const int32_t *rows, int64_t n_idx, int64_t K, float *dst) {
+    const orc_tile *tp = (const orc_tile *)tiles;
+    const int64_t KT = K / ORC_TILE_K;
+    for (int64_t i = 0; i < n_idx; i++) {
+        const int64_t r = rows[i];
+        const int c = (int)(r % 8);
+        float *out = dst + i * K;
+        for (int64_t kt = 0; kt < KT; kt++) {
+            const orc_tile *t = &tp[(r / 8) * KT + kt];
+            const float S = orc_fp16_to_fp32(t->S[c]);
+            const float Z = orc_fp16_to_fp32(t->Z[c]);
+            for (int g = 0; g < 8; g++) {
+                const float scale = S * (float)t->sc[c][g] / 127.0f;
+                const float zero  = Z * (float)t->zc[c][g] / 127.0f;
+                int8_t gw[8][32];
+                orc_unpack_group(t->tiles[g], gw);
+                for (int j = 0; j < 32; j++) out[kt * 256 + g * 32 + j] = scale * (float)gw[c][j] + zero;
+            }
+            orc_fwht(out + kt * 256, 256);
+        }
+    }
+}
+
 /* src/llama-quant.cpp:26-40 */
 void orc_apply_perm_weights(const float *src, float *dst, int64_t nrows, int64_t ncols, const int32_t *perm) {
     for (int64_t r = 0; r < nrows; r++)

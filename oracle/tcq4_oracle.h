@@ -65,6 +65,10 @@ size_t orc_quantize_tiles(const float *src, void *dst, int64_t nrow, int64_t n_p
 /* ggml/src/ggml-quants.c:1425-1463 dequantize_row_tcq4_tile: y[t*2048 + c*256 + k], k elems total = ntiles*256 */
 void orc_dequant_tiles(const void *tiles, float *y, int64_t k);
 
+/* ggml/src/ggml-cuda/getrows.cu:96-171 + 372-378 (CPU: ggml-cpu/ops.cpp:4800-4824): dst[i][K] =
+ * FWHT256(dequant(row rows[i])) */
+void orc_get_rows(const void *tiles, const int32_t *rows, int64_t n_idx, int64_t K, float *dst);
+
 /* src/llama-quant.cpp:26-40 apply_channel_perm_to_weights: dst[r][c] = src[r][perm[c]] */
 void orc_apply_perm_weights(const float *src, float *dst, int64_t nrows, int64_t ncols, const int32_t *perm);
 
