@@ -217,6 +217,11 @@ TCQ4_B200_API int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq
                                          tcq4_tensor_view *dst, void *workspace, size_t workspace_bytes,
                                          cudaStream_t stream);
 
+/* ggml_cuda_op_get_rows for a TCQ4 src0 (ggml/src/ggml-cuda/getrows.cu:397-430, 348-380): src1 is GGML_TYPE_I32 (26)
+ * [ne10, ne11, ne12] with contiguous dim 0, dst F32 [K, ne10, ne11, ne12]; admitted by supports_op at ggml-cuda.cu:4478-4480. */
+TCQ4_B200_API int tcq4_b200_ggml_get_rows(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1,
+                                          tcq4_tensor_view *dst, int *err_flag, cudaStream_t stream);
+
 /* Tensor-pipe peak of this device for one tcgen05.mma flavour: a bare single-thread issue loop on
  * every SM (kind: 0 = i8, 1 = bf16 (kind::f16), 2 = e4m3 (kind::f8f6f4); M = 128; N in {64..256};
  * swizzle: 0 = none (the GEMM's operand layout), 1 = 128B).  MEASURED_PEAKS.json has no INT8 figure,

@@ -43,7 +43,7 @@ EXPORTS = [
     "tcq4_b200_profile_begin", "tcq4_b200_profile_end", "tcq4_b200_debug_gemv_phases", "tcq4_b200_debug_gemm2_timeline",
     "tcq4_b200_measure_pipe",
     "tcq4_b200_measure_tmem_ld", "tcq4_b200_measure_umma2",
-    "tcq4_b200_quantize_size", "tcq4_b200_quantize_tiles", "tcq4_b200_perm_from_imatrix", "tcq4_b200_get_rows",
+    "tcq4_b200_quantize_size", "tcq4_b200_quantize_tiles", "tcq4_b200_perm_from_imatrix", "tcq4_b200_get_rows", "tcq4_b200_ggml_get_rows",
 ]
 
 
@@ -108,6 +108,7 @@ def _load() -> C.CDLL:
     lib.tcq4_b200_quantize_size.argtypes = [i64, i64]
     lib.tcq4_b200_quantize_tiles.argtypes = [vp, vp, i64, i64, vp, vp]
     lib.tcq4_b200_perm_from_imatrix.argtypes = [vp, i64, vp]
+    lib.tcq4_b200_ggml_get_rows.argtypes = [C.POINTER(TensorView)] * 3 + [vp, vp]
     lib.tcq4_b200_get_rows.argtypes = [vp, vp, vp, i64, i64, i64, i64, vp, vp]
     lib.tcq4_b200_profile_end.argtypes = [ci, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(ci)]
     return lib

@@ -17,7 +17,7 @@ from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, 
 
 __all__ = ["Workspace", "mul_mat", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
-           "ggml_supports_op", "ShardedWeight", "random_tiles", "quantize_tiles", "get_rows"]
+           "ggml_supports_op", "ShardedWeight", "random_tiles", "quantize_tiles", "get_rows", "ggml_get_rows"]
 
 
 def _stream_ptr(stream=None) -> int:
@@ -234,6 +234,24 @@ def ggml_supports_op(K: int, N: int, M: int, cc: int = 100) -> bool:
     src1 = _view(None, GGML_TYPE_F32, [K, M, 1, 1], [4, 4 * K, 4 * K * M, 4 * K * M], b"x", 0)
     dst = _view(None, GGML_TYPE_F32, [N, M, 1, 1], [4, 4 * N, 4 * N * M, 4 * N * M], b"y", 0)
     return bool(LIB.tcq4_b200_ggml_supports_op(C.byref(src0), C.byref(src1), C.byref(dst), cc))
+
+
+def ggml_get_rows(w_tiles: torch.Tensor, idx: torch.Tensor, nrows: int, K: int, err_flag: torch.Tensor | None = None,
+                  stream=None) -> torch.Tensor:
+    """ggml_cuda_op_get_rows for a TCQ4 src0: idx int32 [ne12][ne11][ne10] (torch order), w_tiles holds one tile tensor
+    per (i12, i11) slice back to back; returns F32 [ne12][ne11][ne10][K]."""
+    _req_cuda(idx, torch.int32, "idx")
+    while idx.dim() < 3:
+        idx = idx.unsqueeze(0)
+    ne12, ne11, ne10 = idx.shape
+    row = (K // TILE_K) * 148
+    out = torch.empty((ne12, ne11, ne10, K), dtype=torch.float32, device=w_tiles.device)
+    src0 = _view(w_tiles, GGML_TYPE_TCQ4_K32, [K, nrows, ne11, ne12], [148, row, row * nrows, row * nrows * ne11], b"emb")
+    src1 = _view(idx, 26, [ne10, ne11, ne12, 1], [4, 4 * ne10, 4 * ne10 * ne11, 4 * ne10 * ne11 * ne12], b"idx")
+    dst = _view(out, GGML_TYPE_F32, [K, ne10, ne11, ne12], [4, 4 * K, 4 * K * ne10, 4 * K * ne10 * ne11], b"dst")
+    ef = err_flag.data_ptr() if err_flag is not None else 0
+    _check(LIB.tcq4_b200_ggml_get_rows(C.byref(src0), C.byref(src1), C.byref(dst), ef, _stream_ptr(stream)))
+    return out
 
 
 def ggml_mul_mat(w_tiles: torch.Tensor, x: torch.Tensor, N: int, name: str = "", out: torch.Tensor | None = None,

@@ -131,4 +131,28 @@ int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq4_tensor_view 
     return tcq4_b200_mul_mat(src0->data, (const float *)src1->data, (float *)dst->data, M, N, K, d_perm, stream);
 }
 
+// ggml_cuda_op_get_rows for a TCQ4 src0 (ggml/src/ggml-cuda/getrows.cu:397-430 -> get_rows_cuda :348-380):
+//   src0 [K, nrows, ne02, ne03] tiles, src1 I32 [ne10, ne11, ne12], dst F32 [K, ne10, ne11, ne12];
+//   slice (i11, i12) of the indices selects rows of slice (i11, i12) of src0 (k_get_rows_tcq4_tile :126).
+// One launch per (i11, i12) slice; the usual embedding lookup has one.
+int tcq4_b200_ggml_get_rows(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1, tcq4_tensor_view *dst,
+                            int *err_flag, cudaStream_t stream) {
+    if (!src0 || !src1 || !dst) return TCQ4_ERR_ARG;
+    if (src0->type != TCQ4_B200_GGML_TYPE || src1->type != 26 /* GGML_TYPE_I32 */ || dst->type != 0) return TCQ4_ERR_ARG;
+    const int64_t K = src0->ne[0], nrows = src0->ne[1];
+    const int64_t ne10 = src1->ne[0], ne11 = src1->ne[1], ne12 = src1->ne[2];
+    if (dst->ne[0] != K || dst->ne[1] != ne10 || dst->ne[2] != ne11 || dst->ne[3] != ne12) return TCQ4_ERR_SHAPE;
+    if (src1->nb[0] != 4 || dst->nb[0] != 4 || (dst->nb[1] & 15)) return TCQ4_ERR_SHAPE;
+    if (src0->nb[1] != (size_t)(K / 256) * 148) return TCQ4_ERR_SHAPE;
+    for (int64_t i12 = 0; i12 < ne12; i12++)
+        for (int64_t i11 = 0; i11 < ne11; i11++) {
+            const char *w = (const char *)src0->data + i11 * src0->nb[2] + i12 * src0->nb[3];
+            const int32_t *idx = (const int32_t *)((const char *)src1->data + i11 * src1->nb[1] + i12 * src1->nb[2]);
+            float *out = (float *)((char *)dst->data + i11 * dst->nb[2] + i12 * dst->nb[3]);
+            const int st = tcq4_b200_get_rows(w, idx, out, ne10, nrows, K, (int64_t)(dst->nb[1] / 4), err_flag, stream);
+            if (st != TCQ4_OK) return st;
+        }
+    return TCQ4_OK;
+}
+
 }  // extern "C"

@@ -211,3 +211,17 @@ def test_get_rows_of_device_quantised_embedding_roundtrip(t4):
     # idempotence of the format: re-quantising the dequantised rows gives rows within one int4 step everywhere
     again = t4.get_rows(t4.quantize_tiles(back), rows, N, K)
     assert float(((again - back) ** 2).sum() / (back ** 2).sum()) < 2e-2
+
+
+@pytest.mark.gpu
+def test_ggml_get_rows_mirror_batched(t4, orc):
+    """ggml_cuda_op_get_rows shape handling: index slice (i11, i12) reads tile-tensor slice (i11, i12) (getrows.cu:126)"""
+    rng = np.random.default_rng(31)
+    N, K, ne10, ne11, ne12 = 16, 512, 5, 2, 3
+    slices = [orc.quantize_tiles(make_weights(rng, N, K)) for _ in range(ne11 * ne12)]
+    idx = rng.integers(0, N, size=(ne12, ne11, ne10)).astype(np.int32)
+    got = t4.ggml_get_rows(_dev(np.concatenate(slices)), _dev(idx), N, K).cpu().numpy()
+    for i12 in range(ne12):
+        for i11 in range(ne11):
+            want = orc.get_rows(slices[i12 * ne11 + i11], idx[i12, i11], K)
+            assert np.array_equal(got[i12, i11].view(np.uint32), want.view(np.uint32))
