@@ -215,7 +215,9 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
             cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
             cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
         }
-        cudaError_t e = tcq4::launch_gemv(w, x, perm, yo, M, N, K, gv, reinterpret_cast<float *>(wsb + L.partial_off),
+        // the region once used for split-K partials now receives the pre-pass output when it is large enough
+        float *blob = gv.blob_bytes <= L.partial_bytes ? reinterpret_cast<float *>(wsb + L.partial_off) : nullptr;
+        cudaError_t e = tcq4::launch_gemv(w, x, perm, yo, M, N, K, gv, blob,
                                           reinterpret_cast<int *>(wsb + L.ticket_off), dbg_isum, stream);
         if (e != cudaSuccess) return cuda_fail(e, "gemv launch");
         if (prof) {

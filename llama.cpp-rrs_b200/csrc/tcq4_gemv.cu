@@ -126,12 +126,62 @@ __device__ __noinline__ float gv_zero_point(unsigned short zh, uint2 zcv, const 
     return zs;
 }
 
-// MT > 0 selects the dp4a inner loop for exactly MT <= 4 tokens (see "dp4a path" below); MT = 0 the IMMA loop for
+// One activation block (row m, k-tile kt) quantised by one warp and stored in the layout the inner loops read; `base` is
+// the start of the activation area (shared memory inside the GEMV, or the global blob of the pre-pass kernel -- the
+// two have the same layout, GvSmem offsets relative to off_afrag).  DP selects the dp4a arrangement of the codes.
+__device__ __forceinline__ void gv_store_act_block(const ActQuant &a, uint8_t *base, int rm_off, int sumq_off, int M, int KT,
+                                                   int m, int kt, int lane, bool DP) {
+    const int q = lane & 3, r = lane >> 2;
+    const uint32_t ev = (uint32_t)(a.q[0] & 0xFF) | ((uint32_t)(a.q[2] & 0xFF) << 8) |
+                        ((uint32_t)(a.q[4] & 0xFF) << 16) | ((uint32_t)(a.q[6] & 0xFF) << 24);
+    const uint32_t od = (uint32_t)(a.q[1] & 0xFF) | ((uint32_t)(a.q[3] & 0xFF) << 8) |
+                        ((uint32_t)(a.q[5] & 0xFF) << 16) | ((uint32_t)(a.q[7] & 0xFF) << 24);
+    if (DP) {           // dp4a path: per (k-tile, group, token) 32 bytes = {ev of slices 0..3, od of slices 0..3}
+        uint32_t *ad = reinterpret_cast<uint32_t *>(base) + ((kt * 8 + r) * M + m) * 8;
+        ad[q] = ev;
+        ad[4 + q] = od;
+    } else {            // IMMA path: [k-tile][group][token][k-quarter] {ev, od}
+        reinterpret_cast<uint2 *>(base)[((kt * 8 + r) * M + m) * 4 + q] = make_uint2(ev, od);
+    }
+    float *rms = reinterpret_cast<float *>(base + rm_off);
+    if (lane == 0) {
+        const float a7 = __fdiv_rn(a.max_abs, 7.0f);
+        rms[M * KT + kt * M + m] = a7;                       // a7s = rms + M*KT
+        rms[kt * M + m] = a7 * (1.0f / 127.0f);
+    }
+    if (q == 0) reinterpret_cast<int *>(base + sumq_off)[(m * KT + kt) * 8 + r] = a.gsum;
+}
+
+// Pre-pass for M * K/256 > GV_PREPASS_BLOCKS: inside the GEMV every CTA repeats the activation stage for all rows
+// (M = 8, K = 14336: 448 blocks on 16 warps = 28 rounds, 20 us); here the blocks are spread over the whole GPU once and
+// the GEMV copies the finished codes and scales (M*K + 40*M*K/256 bytes, L2-resident) into its shared memory.
+constexpr int GV_PREPASS_BLOCKS = 32;
+constexpr int GVP_WARPS = 4;
+
+__global__ void __launch_bounds__(GVP_WARPS * 32)
+tcq4_gemv_prepass_kernel(const float *__restrict__ x, const int32_t *__restrict__ perm, uint8_t *__restrict__ blob, int M,
+                         int K, int rm_off, int sumq_off, int dp) {
+    const int lane = threadIdx.x & 31;
+    const int KT = K / TILE_K;
+    const int b = blockIdx.x * GVP_WARPS + (threadIdx.x >> 5);
+    pdl_launch_dependents();     // the GEMV behind this kernel sets itself up and prefetches its weights meanwhile
+    pdl_wait();                  // x, and the blob the previous GEMV may still be reading, belong to earlier kernels
+    if (b >= M * KT) return;
+    const int m = b / KT, kt = b - m * KT;
+    float v[8];
+    rrs_load_block_cg(x + (size_t)m * K, perm, kt, lane, v);
+    const ActQuant a = rrs_quantize_block(v, lane);
+    gv_store_act_block(a, blob, rm_off, sumq_off, M, KT, m, kt, lane, dp != 0);
+}
+
+// MT > 0 selects the dp4a inner loop for exactly MT <= 3 tokens (at 4 the IMMA loop is faster: 14.9 vs 17.7 us at
+// N=14336, K=4096) (see "dp4a path" below); MT = 0 the IMMA loop for
 // up to 8 * MB tokens.
 template <int MB, int MT, bool DEBUG>
 __global__ void __launch_bounds__(512, (MT == 1 && !DEBUG) ? 2 : 1)
 tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, const int32_t *__restrict__ perm,
-                 const YOut out, int M, int N, int K, int depth, int32_t *__restrict__ dbg_isum) {
+                 const YOut out, int M, int N, int K, int depth, const uint8_t *__restrict__ pre_blob,
+                 int32_t *__restrict__ dbg_isum) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int KT = K / TILE_K;
     const int NT = N / TILE_CH;
@@ -201,35 +251,28 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     //  chain is shorter than the shared-memory transposition of K1, is the faster one)
     // The loads of the next block are issued before the butterfly of the current one: a warp with several blocks
     // (K = 9728: 38 blocks per row) pays the L2 round trip once, not once per block.
-    float vn[8];
-    if (warp < M * KT) rrs_load_block_cg(x + (size_t)(warp / KT) * K, perm, warp % KT, lane, vn);
-    for (int b = warp; b < M * KT; b += NW) {
-        const int m = b / KT, kt = b - m * KT;
-        float v[8];
+    if (pre_blob != nullptr) {
+        // the pre-pass kernel has done the work: copy codes, scales and group sums (one contiguous area, same layout)
+        const int n16 = (L.off_part - L.off_afrag) >> 4;
+        const uint4 *src = reinterpret_cast<const uint4 *>(pre_blob);
+        uint4 *dst = reinterpret_cast<uint4 *>(smem + L.off_afrag);
+        for (int i = threadIdx.x; i < n16; i += blockDim.x) dst[i] = __ldcg(src + i);
+    } else {
+        float vn[8];
+        if (warp < M * KT) rrs_load_block_cg(x + (size_t)(warp / KT) * K, perm, warp % KT, lane, vn);
+        for (int b = warp; b < M * KT; b += NW) {
+            const int m = b / KT, kt = b - m * KT;
+            float v[8];
 #pragma unroll
-        for (int i = 0; i < 8; i++) v[i] = vn[i];
-        if (b + NW < M * KT) rrs_load_block_cg(x + (size_t)((b + NW) / KT) * K, perm, (b + NW) % KT, lane, vn);
-        if (b == warp) GV_STAMP_DEP(8, v[0] + v[7]);
-        const ActQuant a = rrs_quantize_block(v, lane);                // lane = (group r, k-quarter q), elements lane*8..+7
-        if (b == warp) GV_STAMP_DEP(9, a.max_abs + (float)(a.q[7] + a.gsum));
-        const uint32_t ev = (uint32_t)(a.q[0] & 0xFF) | ((uint32_t)(a.q[2] & 0xFF) << 8) |
-                            ((uint32_t)(a.q[4] & 0xFF) << 16) | ((uint32_t)(a.q[6] & 0xFF) << 24);
-        const uint32_t od = (uint32_t)(a.q[1] & 0xFF) | ((uint32_t)(a.q[3] & 0xFF) << 8) |
-                            ((uint32_t)(a.q[5] & 0xFF) << 16) | ((uint32_t)(a.q[7] & 0xFF) << 24);
-        if (MT > 0) {       // dp4a path: per (k-tile, group, token) 32 bytes = {ev of slices 0..3, od of slices 0..3}
-            uint32_t *ad = reinterpret_cast<uint32_t *>(afrag) + ((kt * 8 + r) * M + m) * 8;
-            ad[q] = ev;
-            ad[4 + q] = od;
-        } else {
-            afrag[((kt * 8 + r) * M + m) * 4 + q] = make_uint2(ev, od);
+            for (int i = 0; i < 8; i++) v[i] = vn[i];
+            if (b + NW < M * KT) rrs_load_block_cg(x + (size_t)((b + NW) / KT) * K, perm, (b + NW) % KT, lane, vn);
+            if (b == warp) GV_STAMP_DEP(8, v[0] + v[7]);
+            const ActQuant a = rrs_quantize_block(v, lane);            // lane = (group r, k-quarter q), elements lane*8..+7
+            if (b == warp) GV_STAMP_DEP(9, a.max_abs + (float)(a.q[7] + a.gsum));
+            gv_store_act_block(a, smem + L.off_afrag, L.off_rm - L.off_afrag, L.off_sumq - L.off_afrag, M, KT, m, kt, lane,
+                               MT > 0);
+            if (b == warp) GV_STAMP(6);
         }
-        if (lane == 0) {
-            const float a7 = __fdiv_rn(a.max_abs, 7.0f);
-            a7s[kt * M + m] = a7;
-            rms[kt * M + m] = a7 * (1.0f / 127.0f);
-        }
-        if (q == 0) sumq[(m * KT + kt) * 8 + r] = a.gsum;
-        if (b == warp) GV_STAMP(6);
     }
     __syncthreads();
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -256,8 +299,8 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     const int af_g = M * 4;                                    // uint2 stride between groups
 
     if constexpr (MT > 0) {
-    // ---- dp4a path (M = MT <= 4) ---------------------------------------------------------------------------
-    // With one to four tokens the m16n8k32 shape is mostly padding and the loop is bound by instruction issue, so the
+    // ---- dp4a path (M = MT <= 3) ---------------------------------------------------------------------------
+    // With one to three tokens the m16n8k32 shape is mostly padding and the loop is bound by instruction issue, so the
     // lanes are re-mapped for wide loads instead: lane l = (gq = l / 8, cc = l % 8) reads words 4l .. 4l+3 of the tile's
     // first and second half with two LDS.128 = ALL 32 nibbles of channel cc in groups gq and gq + 4.  Per word: three
     // logic ops (even / odd nibbles as 16*q in s8 lanes) and two DP4A per token against the token's codes (LDS.128,
@@ -602,6 +645,11 @@ bool gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, 
     if ((size_t)L.total > smem_optin) return false;
     plan->warps = nw;
     plan->depth = depth;
+    static const bool nopre = getenv("TCQ4_GV_NOPRE") != nullptr;
+    // M = 1 keeps the stage inside the kernel: consecutive M = 1 launches share an SM (dependent launch), and a kernel
+    // between them costs more than the 2-4 rounds it saves (K = 14336: 14.1 us inside, 15.6 us with the pre-pass)
+    plan->prepass = !nopre && M >= 2 && M * KT > GV_PREPASS_BLOCKS;
+    plan->blob_bytes = (size_t)(L.off_part - L.off_afrag);
     int64_t clusters = num_sms / GV_CLUSTER;
     if (NT < clusters) clusters = NT;                              // a cluster owns whole rows
     if (clusters < 1) clusters = 1;
@@ -615,7 +663,8 @@ bool gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, 
 
 template <int MB, int MT, bool DEBUG>
 static cudaError_t launch_gemv_t(const void *w, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
-                                 int64_t K, const GemvPlan &plan, int32_t *dbg, cudaStream_t stream) {
+                                 int64_t K, const GemvPlan &plan, const uint8_t *pre_blob, int32_t *dbg,
+                                 cudaStream_t stream) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)plan.grid);
     cfg.blockDim = dim3((unsigned)plan.warps * 32);
@@ -635,7 +684,7 @@ static cudaError_t launch_gemv_t(const void *w, const float *x, const int32_t *p
     static const bool pdl = getenv("TCQ4_NO_PDL") == nullptr;
     cfg.numAttrs = pdl ? 2 : 1;
     return cudaLaunchKernelEx(&cfg, tcq4_gemv_kernel<MB, MT, DEBUG>, (const uint8_t *)w, x, perm, y, (int)M, (int)N, (int)K,
-                              plan.depth, dbg);
+                              plan.depth, pre_blob, dbg);
 }
 
 template <int MB, int MT>
@@ -655,26 +704,48 @@ static cudaError_t gemv_attr_one(size_t smem_optin) {
 }
 
 cudaError_t gemv_init_attributes(size_t smem_optin) {
-    cudaError_t e = gemv_attr_one<1, 0>(smem_optin);
+    cudaError_t e = cudaFuncSetAttribute(tcq4_gemv_prepass_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                         (int)cudaSharedmemCarveoutMaxShared);      // same split as the GEMV behind it
+    if (e != cudaSuccess) return e;
+    e = gemv_attr_one<1, 0>(smem_optin);
     if (e == cudaSuccess) e = gemv_attr_one<2, 0>(smem_optin);
     if (e == cudaSuccess) e = gemv_attr_one<1, 1>(smem_optin);
     if (e == cudaSuccess) e = gemv_attr_one<1, 2>(smem_optin);
     if (e == cudaSuccess) e = gemv_attr_one<1, 3>(smem_optin);
-    if (e == cudaSuccess) e = gemv_attr_one<1, 4>(smem_optin);
     return e;
 }
 
 template <int MB, int MT>
 static cudaError_t launch_gemv_d(bool debug, const void *w, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
-                                 int64_t K, const GemvPlan &plan, int32_t *dbg, cudaStream_t stream) {
-    if (debug) return launch_gemv_t<MB, MT, true>(w, x, perm, y, M, N, K, plan, dbg, stream);
-    return launch_gemv_t<MB, MT, false>(w, x, perm, y, M, N, K, plan, nullptr, stream);
+                                 int64_t K, const GemvPlan &plan, uint8_t *blob, int32_t *dbg, cudaStream_t stream) {
+    const uint8_t *pre = nullptr;
+    if (plan.prepass && blob != nullptr) {
+        // activation stage once for the whole GPU (see tcq4_gemv_prepass_kernel), in the GEMV's own layout
+        const GvSmem L((int)M, (int)(K / TILE_K), plan.warps, plan.depth);
+        cudaLaunchConfig_t cfg = {};
+        const int nblk = (int)(M * (K / TILE_K));
+        cfg.gridDim = dim3((unsigned)((nblk + GVP_WARPS - 1) / GVP_WARPS));
+        cfg.blockDim = dim3(GVP_WARPS * 32);
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        static const bool pdl = getenv("TCQ4_NO_PDL") == nullptr;
+        cfg.numAttrs = pdl ? 1 : 0;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, tcq4_gemv_prepass_kernel, x, perm, blob, (int)M, (int)K,
+                                           L.off_rm - L.off_afrag, L.off_sumq - L.off_afrag, MT > 0 ? 1 : 0);
+        if (e != cudaSuccess) return e;
+        pre = blob;
+    }
+    if (debug) return launch_gemv_t<MB, MT, true>(w, x, perm, y, M, N, K, plan, pre, dbg, stream);
+    return launch_gemv_t<MB, MT, false>(w, x, perm, y, M, N, K, plan, pre, nullptr, stream);
 }
 
 cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
                         int64_t K, const GemvPlan &plan, float *ws_partial, int *ws_ticket, int32_t *dbg_isum,
                         cudaStream_t stream) {
-    (void)ws_partial;
+    uint8_t *blob = reinterpret_cast<uint8_t *>(ws_partial);      // pre-pass output (plan.blob_bytes), may be null
     (void)ws_ticket;
     if (M < 1 || M > GEMV_MAX_M) return cudaErrorInvalidValue;
     static const bool prof = getenv("TCQ4_GV_PROF") != nullptr;      // phase stamps without the isum dump
@@ -682,15 +753,14 @@ cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm
     const bool dbg = dbg_isum != nullptr || prof;
     if (!nodp) {
         switch (M) {
-            case 1: return launch_gemv_d<1, 1>(dbg, w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
-            case 2: return launch_gemv_d<1, 2>(dbg, w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
-            case 3: return launch_gemv_d<1, 3>(dbg, w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
-            case 4: return launch_gemv_d<1, 4>(dbg, w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
+            case 1: return launch_gemv_d<1, 1>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream);
+            case 2: return launch_gemv_d<1, 2>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream);
+            case 3: return launch_gemv_d<1, 3>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream);
             default: break;
         }
     }
-    if (gemv_mb(M) == 1) return launch_gemv_d<1, 0>(dbg, w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
-    return launch_gemv_d<2, 0>(dbg, w_tiles, x, perm, y, M, N, K, plan, dbg_isum, stream);
+    if (gemv_mb(M) == 1) return launch_gemv_d<1, 0>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream);
+    return launch_gemv_d<2, 0>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream);
 }
 
 cudaError_t gemv_read_prof(unsigned long long *host_out, size_t bytes) {

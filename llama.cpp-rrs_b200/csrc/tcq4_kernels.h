@@ -21,6 +21,8 @@ struct GemvPlan {
     int     grid;            // CTAs (persistent, one per SM)
     int     warps;           // warps per CTA (16 or 32)
     int     depth;           // tiles in flight per warp (ring slots)
+    bool    prepass;         // activation stage in its own launch (M * K/256 large), result in the workspace blob
+    size_t  blob_bytes;      // workspace bytes of that result
     size_t  smem_bytes;
     int     maxslots;        // split-K partial slots per n-tile row
     size_t  partial_bytes;   // workspace: float [NT][maxslots][8 or 16 rows][8]
@@ -29,7 +31,7 @@ struct GemvPlan {
 bool        gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, GemvPlan *plan);
 cudaError_t gemv_init_attributes(size_t smem_optin);
 cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
-                        int64_t K, const GemvPlan &plan, float *ws_partial, int *ws_ticket, int32_t *dbg_isum,
+                        int64_t K, const GemvPlan &plan, float *ws_blob, int *ws_ticket, int32_t *dbg_isum,
                         cudaStream_t stream);
 
 // ---- K4 / K5: device weight quantiser and GET_ROWS (tcq4_quant.cu) ------------------------------

@@ -58,7 +58,16 @@ def layer_chain(M, layers=int(os.environ.get('LAYERS', '36'))):
     print(f"layer chain M={M} layers={layers}: {ms:.3f} ms/step, {ms * 1e3 / (layers * 7):.2f} us/launch", flush=True)
 
 if os.environ.get("LAYER_CHAIN"):
-    layer_chain(1)
+    layer_chain(int(os.environ.get("CHAIN_M", "1")))
+elif os.environ.get("SWEEP"):
+    # BASELINE configs[2]: Llama-3-8B gate/up and down projections, decode batch 1..64
+    for n, k in [(14336, 4096), (4096, 14336)]:
+        for m in (1, 2, 3, 4, 5, 8, 12, 16, 17, 24, 32, 48, 64):
+            run(m, n, k, nbuf=8)
+elif os.environ.get("CHAIN_M"):
+    m = int(os.environ["CHAIN_M"])
+    for n, k in [(4096, 2560), (1024, 2560), (2560, 4096), (9728, 2560), (2560, 9728)]:
+        run(m, n, k, nbuf=12)
 else:
     for shp in [(1, 9728, 2560), (1, 2560, 9728), (1, 4096, 2560), (1, 1024, 2560), (8, 9728, 2560)]:
         run(*shp)
