@@ -11,6 +11,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -242,8 +243,16 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
     st.sumq = reinterpret_cast<int16_t *>(wsb + L.sumq_off);
     const bool prof = g_prof.on && g_prof.n < g_prof.cap;
     if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
-    cudaError_t e = tcq4::launch_act_quant_stage(x, perm, M, K, st, d->num_sms, stream);
-    if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
+    // TCQ4_G2_FUSE=1: the pair GEMM runs the activation stage itself on its idle warps (no separate launch).  Opt-in:
+    // measured SLOWER (Qwen3-4B prefill chain 7.93 vs 7.04 ms; +7 us per MUL_MAT at K=2560, +15 us at K=9728) -- with 16
+    // warps per SM the butterfly is a latency chain of ~1.8 us per round, the stand-alone kernel hides it with 64.
+    static const bool want_fuse = getenv("TCQ4_G2_FUSE") != nullptr;
+    const bool fuse = (k == TCQ4_KERNEL_GEMM2) && want_fuse && L.ticket_bytes >= 8;
+    cudaError_t e = cudaSuccess;
+    if (!fuse) {
+        e = tcq4::launch_act_quant_stage(x, perm, M, K, st, d->num_sms, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
+    }
     if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
     if (k == TCQ4_KERNEL_GEMM2) {
         tcq4::Gemm2Plan g2;
@@ -251,7 +260,8 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
             set_err("pair GEMM kernel cannot be planned for this shape/device");
             return TCQ4_ERR_SHAPE;
         }
-        e = tcq4::launch_gemm2(w, st, yo, M, N, K, g2, dbg_isum, stream);
+        e = tcq4::launch_gemm2(w, st, yo, M, N, K, g2, dbg_isum, stream, fuse ? x : nullptr, perm,
+                               reinterpret_cast<int *>(wsb + L.ticket_off));
     } else {
         e = tcq4::launch_gemm(w, st, y, M, N, K, gm, dbg_isum, stream);
     }

@@ -226,6 +226,63 @@ __device__ __forceinline__ void g2_store_wait_read() {
     asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N_PENDING) : "memory");
 }
 
+// ---- activation stage inside the GEMM (FUSED mode, opt-in: TCQ4_G2_FUSE=1; measured slower, see tcq4_api.cu) --------
+// The stand-alone activation kernel costs a launch, a one-wave latency chain and a drain in front of EVERY MUL_MAT
+// (~4 of the 27 us of an average Qwen3-4B prefill matmul).  In fused mode the GEMM's own unpack and epilogue warps --
+// idle until the first weight tiles have landed and the first accumulator is complete -- quantise the M * K/256 blocks
+// (spread over all CTAs of the grid) into the same staging layout, then a grid-wide counter releases the producer's
+// activation copies and the epilogue's scale reads.  All CTAs of the grid are co-resident (persistent, one per SM), so
+// the barrier cannot deadlock; the last CTA to leave resets the counters (cnt[0] = warps done, cnt[1] = CTAs gone).
+struct G2Fuse {
+    const float   *x;        // null: the staging area was filled by tcq4_act_quant_kernel before this launch
+    const int32_t *perm;
+    int           *cnt;      // two zeroed ints in the workspace
+};
+__device__ __forceinline__ int g2_ld_acquire(const int *p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void g2_fused_act(const G2Fuse &fz, const ActStage &st, int M, int K, int wi, int nw, int lane,
+                                             int *sm_cnt) {
+    const int KT = K / TILE_K;
+    const int nblocks = M * KT;
+    float vn[8];
+    if (wi < nblocks) rrs_load_block_cg(fz.x + (size_t)(wi / KT) * K, fz.perm, wi % KT, lane, vn);
+    for (int b = wi; b < nblocks; b += nw) {
+        const int m = b / KT, kt = b - m * KT;
+        float v[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = vn[i];
+        if (b + nw < nblocks) rrs_load_block_cg(fz.x + (size_t)((b + nw) / KT) * K, fz.perm, (b + nw) % KT, lane, vn);
+        const ActQuant a = rrs_quantize_block(v, lane);               // lane holds elements lane*8 .. lane*8+7
+        // s8 codes, sigma order {0,2,4,6,1,3,5,7}; lane pair (2j, 2j+1) forms 16-B K-chunk j (as tcq4_act.cu MODE_STAGE)
+        const uint32_t w0 = (uint32_t)(a.q[0] & 0xFF) | ((uint32_t)(a.q[2] & 0xFF) << 8) |
+                            ((uint32_t)(a.q[4] & 0xFF) << 16) | ((uint32_t)(a.q[6] & 0xFF) << 24);
+        const uint32_t w1 = (uint32_t)(a.q[1] & 0xFF) | ((uint32_t)(a.q[3] & 0xFF) << 8) |
+                            ((uint32_t)(a.q[5] & 0xFF) << 16) | ((uint32_t)(a.q[7] & 0xFF) << 24);
+        int8_t *unit = st.codes + ((size_t)(m >> 7) * KT + kt) * ACT_UNIT_BYTES;
+        *reinterpret_cast<uint2 *>(unit + (lane >> 1) * ACT_LBO + (m & 127) * 16 + (lane & 1) * 8) = make_uint2(w0, w1);
+        if (lane == 0) st.a7[b] = __fdiv_rn(a.max_abs, 7.0f);
+        if ((lane & 3) == 0) st.sumq[b * 8 + (lane >> 2)] = (int16_t)a.gsum;
+    }
+    // publish: every lane's stores are fenced (generic and async proxy: the codes are read by bulk copies of OTHER SMs)
+    __threadfence();
+    asm volatile("fence.proxy.async;" ::: "memory");
+    __syncwarp();
+    // one global atomic per CTA (2 368 warps on one address cost ~10 us): the CTA's 16th warp reports for all of them
+    if (lane == 0 && atomicAdd_block(sm_cnt, 1) == G2_UNPACK_WARPS + G2_EPI_WARPS - 1) {
+        __threadfence();
+        atomicAdd(fz.cnt, 1);
+    }
+}
+// producer lane: wait until every CTA has reported, then open the CTA-local gate for the epilogue warps
+__device__ __forceinline__ void g2_fused_wait(const G2Fuse &fz, int target, volatile int *sm_go) {
+    while (g2_ld_acquire(fz.cnt) < target) __nanosleep(32);
+    asm volatile("fence.proxy.async;" ::: "memory");
+    *sm_go = 1;
+}
+
 // PERSISTENT: one cluster per SM pair walks the (row-pair, column-block) tiles t = cluster, cluster + C, ...
 // (row-pairs fastest, so that clusters running at the same time share weight tiles in L2).  Every ring and both
 // TMEM accumulator stages keep running across tile boundaries (all roles count k-tiles globally), so the
@@ -245,8 +302,8 @@ struct G2YMaps {       // one store map per destination matrix (this GPU's C, or
 template <int NTL, bool DEBUG, bool PROF = false, int OUTM = 0>
 __global__ void __launch_bounds__(G2_THREADS, 1)
 tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_constant__ CUtensorMap tm_meta,
-                  const __grid_constant__ G2YMaps tm_y, const uint8_t *__restrict__ w, ActStage st, int M, int N, int K,
-                  int MB2, int num_tiles, int32_t *__restrict__ dbg_isum) {
+                  const __grid_constant__ G2YMaps tm_y, const uint8_t *__restrict__ w, ActStage st, const G2Fuse fz, int M, int N,
+                  int K, int MB2, int num_tiles, int32_t *__restrict__ dbg_isum) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int LBO = 256 * NTL;                               // K-chunk stride of B: (16*NTL rows) * 16 B
     constexpr int BGROUP = 2 * LBO;                              // one 32-group = 2 K-chunks
@@ -287,6 +344,8 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
             mbar_init(&accempty[i], 2 * G2_EPI_WARPS);           // epilogue warps of both CTAs (used in the leader)
         }
         for (int i = 0; i < G2_SN_RING; i++) mbar_init(&snfull[i], 4);     // 4 local publishing warps
+        tmem_slot[1] = 0;        // fused activation stage: warps of this CTA that have reported / gate for the epilogue
+        tmem_slot[2] = 0;
         fence_mbar_init();
     }
     if (warp == 0 && lane == 0) {
@@ -311,6 +370,10 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
     if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(2);
     pdl_launch_dependents();     // the next kernel of the stream may set itself up behind this one
     pdl_wait();                  // codes / scales (activation kernel) and y belong to earlier kernels until here
+    const int fused_nw = (G2_UNPACK_WARPS + G2_EPI_WARPS) * (int)gridDim.x;     // warps that share the activation stage
+    const int fused_target = (int)gridDim.x;                                    // one report per CTA
+    int *sm_cnt = reinterpret_cast<int *>(tmem_slot) + 1;                       // zeroed with the barriers above
+    volatile int *sm_go = reinterpret_cast<volatile int *>(tmem_slot) + 2;
 
     if (warp < G2_UNPACK_WARP0) {
       asm volatile("setmaxnreg.dec.sync.aligned.u32 56;" ::: "memory");
@@ -333,10 +396,12 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
                     G2_STAMP(0, gk, 0);
                     uint8_t *stg = sStage + s * G2_STAGE_BYTES;
                     mbar_arrive_expect_tx(&full[s], total_tx);
-                    bulk_g2s(stg, a_src, G2_A_BYTES, &full[s]);
                     g2_tma_2d_hint(stg + G2_A_BYTES, &tm_tiles, kt * (TILE_BYTES / 8), nt0, &full[s], pol_w);
                     g2_tma_2d(stg + G2_A_BYTES + G2_RAW_BYTES, &tm_meta, kt * (TILE_BYTES / 8) + TILE_NIB / 8, nt_pair,
                               &full[s]);
+                    // fused mode: the weights are already on their way; the codes exist once every warp has reported
+                    if (gk == 0 && fz.x != nullptr) g2_fused_wait(fz, fused_target, sm_go);
+                    bulk_g2s(stg, a_src, G2_A_BYTES, &full[s]);
                     a_src += ACT_UNIT_BYTES;
                     G2_STAMP(0, gk, 1);
                     if (++s == G2_STAGES) { s = 0; u++; }
@@ -398,6 +463,8 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         asm volatile("setmaxnreg.dec.sync.aligned.u32 56;" ::: "memory");
         // ===================== weight unpack (this CTA's NTL n-tiles) =====================
         const int uw = warp - G2_UNPACK_WARP0;
+        if (fz.x != nullptr)
+            g2_fused_act(fz, st, M, K, (int)blockIdx.x * (G2_UNPACK_WARPS + G2_EPI_WARPS) + uw, fused_nw, lane, sm_cnt);
         const int ut = threadIdx.x - G2_UNPACK_WARP0 * 32;          // 0..255
         // chunk of this thread inside a half k-tile: (gl, j, c) with 8*NTL chunks per group
         constexpr int PER_GROUP = 8 * NTL;
@@ -478,7 +545,16 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         int gk = 0;
         int mb = 2 * (cluster_id % MB2) + (int)rank;
         float a7 = 0.0f;
-        if (cluster_id < num_tiles && mb * G2_BM + row < M) a7 = st.a7[(size_t)(mb * G2_BM + row) * KT];
+        if (fz.x != nullptr) {
+            g2_fused_act(fz, st, M, K, (int)blockIdx.x * (G2_UNPACK_WARPS + G2_EPI_WARPS) + G2_UNPACK_WARPS + ew, fused_nw, lane,
+                         sm_cnt);
+            if (lane == 0) {                                    // the scales below come from other CTAs' warps
+                while (*sm_go == 0) __nanosleep(32);
+                (void)g2_ld_acquire(fz.cnt);
+            }
+            __syncwarp();
+        }
+        if (cluster_id < num_tiles && mb * G2_BM + row < M) a7 = __ldcg(st.a7 + (size_t)(mb * G2_BM + row) * KT);
         for (int t = cluster_id; t < num_tiles; t += num_clusters) {
             const int m = mb * G2_BM + row;
             const bool mvalid = m < M;
@@ -632,6 +708,13 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
 
     tc_fence_before();
     g2_cluster_sync();
+    if (fz.x != nullptr && threadIdx.x == 0) {               // last CTA out re-arms the counters for the next launch
+        if (atomicAdd(fz.cnt + 1, 1) == (int)gridDim.x - 1) {
+            fz.cnt[0] = 0;
+            fz.cnt[1] = 0;
+            __threadfence();
+        }
+    }
     if (threadIdx.x == G2_EPI_WARP0 * 32) G2_CTA_STAMP(5);
     if (warp == 1)
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
@@ -706,8 +789,8 @@ static bool g2_make_y_map(CUtensorMap *map, float *y, int64_t M, int64_t N, int6
 }
 
 template <int NTL>
-static cudaError_t launch_gemm2_t(cudaLaunchConfig_t *cfg, const void *w_tiles, ActStage st, YOut y, int64_t M, int64_t N,
-                                  int64_t K, int32_t *dbg_isum) {
+static cudaError_t launch_gemm2_t(cudaLaunchConfig_t *cfg, const void *w_tiles, ActStage st, G2Fuse fz, YOut y, int64_t M,
+                                  int64_t N, int64_t K, int32_t *dbg_isum) {
     CUtensorMap tm_tiles, tm_meta;
     G2YMaps tm_y;
     if (!g2_make_map(&tm_tiles, w_tiles, N / TILE_CH, K / TILE_K, TILE_BYTES / 8, NTL) ||
@@ -722,27 +805,26 @@ static cudaError_t launch_gemm2_t(cudaLaunchConfig_t *cfg, const void *w_tiles, 
     const int MB2 = (int)((M + 2 * G2_BM - 1) / (2 * G2_BM));
     const int num_tiles = (int)g2_tiles(M, N, NTL);
     if (y.mc)
-        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, false, 2>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles,
-                                  st, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
+        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, false, 2>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st, fz, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
     if (y.n > 1)
-        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, false, 1>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles,
-                                  st, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
+        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, false, 1>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st, fz, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
     static const bool prof = getenv("TCQ4_G2_PROF") != nullptr;     // diagnostics: timeline stamps of one cluster
     if (prof && !dbg_isum) {
         cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              Gemm2Smem::total);
-        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, true>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles,
-                                  st, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
+        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, true>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st, fz, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
     }
     if (dbg_isum)
-        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, true>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st,
+        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, true>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st, fz,
                                   (int)M, (int)N, (int)K, MB2, num_tiles, dbg_isum);
-    return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st,
+    return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st, fz,
                               (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
 }
 
 cudaError_t launch_gemm2(const void *w_tiles, ActStage st, YOut y, int64_t M, int64_t N, int64_t K,
-                         const Gemm2Plan &plan, int32_t *dbg_isum, cudaStream_t stream) {
+                         const Gemm2Plan &plan, int32_t *dbg_isum, cudaStream_t stream, const float *fuse_x,
+                         const int32_t *fuse_perm, int *fuse_cnt) {
+    const G2Fuse fz{fuse_x, fuse_perm, fuse_cnt};
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = plan.grid;
     cfg.blockDim = dim3(G2_THREADS);
@@ -769,13 +851,13 @@ cudaError_t launch_gemm2(const void *w_tiles, ActStage st, YOut y, int64_t M, in
         cfg.gridDim.x = (unsigned)(2 * (tiles < cap ? tiles : cap));
     }
     switch (ntl) {
-        case 2: return launch_gemm2_t<2>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
-        case 3: return launch_gemm2_t<3>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
-        case 4: return launch_gemm2_t<4>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
-        case 5: return launch_gemm2_t<5>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
-        case 6: return launch_gemm2_t<6>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
-        case 7: return launch_gemm2_t<7>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
-        case 8: return launch_gemm2_t<8>(&cfg, w_tiles, st, y, M, N, K, dbg_isum);
+        case 2: return launch_gemm2_t<2>(&cfg, w_tiles, st, fz, y, M, N, K, dbg_isum);
+        case 3: return launch_gemm2_t<3>(&cfg, w_tiles, st, fz, y, M, N, K, dbg_isum);
+        case 4: return launch_gemm2_t<4>(&cfg, w_tiles, st, fz, y, M, N, K, dbg_isum);
+        case 5: return launch_gemm2_t<5>(&cfg, w_tiles, st, fz, y, M, N, K, dbg_isum);
+        case 6: return launch_gemm2_t<6>(&cfg, w_tiles, st, fz, y, M, N, K, dbg_isum);
+        case 7: return launch_gemm2_t<7>(&cfg, w_tiles, st, fz, y, M, N, K, dbg_isum);
+        case 8: return launch_gemm2_t<8>(&cfg, w_tiles, st, fz, y, M, N, K, dbg_isum);
         default: return cudaErrorInvalidValue;
     }
 }

@@ -64,7 +64,9 @@ struct Gemm2Plan {
 };
 bool        gemm2_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, Gemm2Plan *plan);
 cudaError_t gemm2_init_attributes(size_t smem_optin);
+// fuse_x != null: the kernel's own warps run the activation stage (x, perm) into `st` first; fuse_cnt = two zeroed ints
 cudaError_t launch_gemm2(const void *w_tiles, ActStage st, YOut y, int64_t M, int64_t N, int64_t K,
-                         const Gemm2Plan &plan, int32_t *dbg_isum, cudaStream_t stream);
+                         const Gemm2Plan &plan, int32_t *dbg_isum, cudaStream_t stream, const float *fuse_x = nullptr,
+                         const int32_t *fuse_perm = nullptr, int *fuse_cnt = nullptr);
 
 }  // namespace tcq4

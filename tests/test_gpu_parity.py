@@ -3,6 +3,7 @@
 Bar (BASELINE.json north_star): activation int4 codes, max_abs, group sums and the int32 accumulators
 bit-exact; fp32 outputs within NMSE <= 1e-3 of the oracle (asserted much tighter: <= 1e-9, only the
 fp32 association differs).  Nothing here reads /root/reference."""
+import os
 import numpy as np
 import pytest
 
@@ -440,3 +441,36 @@ def test_cuda_graph_capture(t4, orc):
             g.replay()
         torch.cuda.synchronize()
         assert torch.equal(out, eager)
+
+
+@pytest.mark.gpu
+def test_gemm2_fused_activation_stage_in_a_child_process():
+    """TCQ4_G2_FUSE=1 (read once at load, hence the child): the pair GEMM quantises the activations on its own warps behind
+    a grid-wide counter; accumulators must stay bit-exact and the counters must re-arm themselves launch after launch."""
+    import subprocess
+    import sys
+    code = r'''
+import numpy as np, torch, sys, os
+sys.path.insert(0, os.getcwd()); sys.path.insert(0, os.path.join(os.getcwd(), "tests"))
+import __graft_entry__ as graft
+from conftest import make_acts, make_weights, block_perm
+t4 = graft.load_package(); orc = graft.load_oracle().Oracle()
+rng = np.random.default_rng(11)
+for (M, N, K, use_perm) in [(300, 256, 1024, False), (129, 136, 512, True), (512, 1024, 2560, False)]:
+    tiles = orc.quantize_tiles(make_weights(rng, N, K)); x = make_acts(rng, M, K)
+    perm = block_perm(rng, K) if use_perm else None
+    ref = orc.mul_mat(tiles, x, N, perm=perm, want_isum=True)
+    ws = t4.Workspace.for_shape(M, N, K)
+    td, xd = torch.from_numpy(tiles).cuda(), torch.from_numpy(x).cuda()
+    pd = torch.from_numpy(perm).cuda() if use_perm else None
+    for rep in range(3):
+        y, isum = t4.mul_mat_debug(td, xd, N, perm=pd, kernel=t4.KERNEL_GEMM2, workspace=ws)
+        torch.cuda.synchronize()
+        assert np.array_equal(isum.cpu().numpy(), ref["isum"]), (M, N, K, rep)
+        yy = y.cpu().numpy(); assert ((yy - ref["C"]) ** 2).sum() / (ref["C"] ** 2).sum() < 1e-9
+print("FUSED_OK")
+'''
+    env = dict(os.environ, TCQ4_G2_FUSE="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=240)
+    assert "FUSED_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
