@@ -222,6 +222,36 @@ TCQ4_B200_API int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq
 TCQ4_B200_API int tcq4_b200_ggml_get_rows(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1,
                                           tcq4_tensor_view *dst, int *err_flag, cudaStream_t stream);
 
+/* ---- GGUF files with TCQ4 tensors and permutations (host side) ------------------------------------------
+ * The loader's scan for "tcq4.reorder.enabled" / "tcq4.<tensor>.perm" and the registration flow
+ * (src/llama-model.cpp:7129-7205), the verbatim upload of tensor bytes (ggml-cuda.cu:627-633), and the writer side of
+ * llama_model_quantize for these keys (src/llama-quant.cpp:840-854).  GGUF v2/v3 (ggml/src/gguf.cpp), little-endian. */
+typedef struct tcq4_gguf tcq4_gguf;
+TCQ4_B200_API int     tcq4_b200_gguf_open(const char *path, tcq4_gguf **out);
+TCQ4_B200_API void    tcq4_b200_gguf_close(tcq4_gguf *g);
+TCQ4_B200_API int     tcq4_b200_gguf_reorder_enabled(const tcq4_gguf *g);             /* -1: key absent, else 0 / 1 */
+TCQ4_B200_API int64_t tcq4_b200_gguf_n_tensors(const tcq4_gguf *g);
+TCQ4_B200_API int64_t tcq4_b200_gguf_n_perms(const tcq4_gguf *g);
+/* type = ggml_type (42 = TCQ4_K32); ne as ggml (ne[0] = K fastest); file_offset absolute; nbytes exact for F32, F16 and
+ * TCQ4_K32 (ne[1] * K/256 * 148), else the extent up to the next tensor.  Returned strings live until close. */
+TCQ4_B200_API int     tcq4_b200_gguf_tensor_info(const tcq4_gguf *g, int64_t i, const char **name, int *type, int64_t ne[4],
+                                                 uint64_t *file_offset, uint64_t *nbytes);
+TCQ4_B200_API int     tcq4_b200_gguf_perm(const tcq4_gguf *g, int64_t i, const char **tensor_name, const int32_t **perm,
+                                          int64_t *K);
+/* set_reorder_enabled + register_perm for every permutation of the file on the CURRENT device (call once per device: the
+ * fork registers with the first GPU backend only, llama-model.cpp:7200) */
+TCQ4_B200_API int     tcq4_b200_gguf_register_perms(const tcq4_gguf *g);
+TCQ4_B200_API int     tcq4_b200_gguf_read_tensor(const tcq4_gguf *g, int64_t i, void *dst_host, size_t dst_bytes);
+/* tensor bytes -> device memory through pinned staging, synchronous on return */
+TCQ4_B200_API int     tcq4_b200_gguf_load_tensor(const tcq4_gguf *g, int64_t i, void *dst_device, size_t dst_bytes,
+                                                 cudaStream_t stream);
+/* Writer: 2-D tensors of type F32 (0), F16 (1) or TCQ4_K32 (42) from host memory, "tcq4.<tensor>.perm" int32 arrays and
+ * "tcq4.reorder.enabled" (reorder_enabled < 0: key omitted), general.alignment = 32. */
+TCQ4_B200_API int     tcq4_b200_gguf_write(const char *path, int n_tensors, const char *const *names, const int *types,
+                                           const int64_t *ne0, const int64_t *ne1, const void *const *data_host, int n_perms,
+                                           const char *const *perm_tensors, const int32_t *const *perms,
+                                           const int64_t *perm_K, int reorder_enabled);
+
 /* Tensor-pipe peak of this device for one tcgen05.mma flavour: a bare single-thread issue loop on
  * every SM (kind: 0 = i8, 1 = bf16 (kind::f16), 2 = e4m3 (kind::f8f6f4); M = 128; N in {64..256};
  * swizzle: 0 = none (the GEMM's operand layout), 1 = 128B).  MEASURED_PEAKS.json has no INT8 figure,

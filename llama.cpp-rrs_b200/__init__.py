@@ -44,6 +44,9 @@ EXPORTS = [
     "tcq4_b200_measure_pipe",
     "tcq4_b200_measure_tmem_ld", "tcq4_b200_measure_umma2",
     "tcq4_b200_quantize_size", "tcq4_b200_quantize_tiles", "tcq4_b200_perm_from_imatrix", "tcq4_b200_get_rows", "tcq4_b200_ggml_get_rows",
+    "tcq4_b200_gguf_open", "tcq4_b200_gguf_close", "tcq4_b200_gguf_reorder_enabled", "tcq4_b200_gguf_n_tensors",
+    "tcq4_b200_gguf_n_perms", "tcq4_b200_gguf_tensor_info", "tcq4_b200_gguf_perm", "tcq4_b200_gguf_register_perms",
+    "tcq4_b200_gguf_read_tensor", "tcq4_b200_gguf_load_tensor", "tcq4_b200_gguf_write",
 ]
 
 
@@ -104,6 +107,22 @@ def _load() -> C.CDLL:
     lib.tcq4_b200_measure_pipe.argtypes = [ci, ci, C.POINTER(C.c_double)]
     lib.tcq4_b200_measure_tmem_ld.argtypes = [ci, ci, ci, C.POINTER(C.c_double)]
     lib.tcq4_b200_profile_begin.argtypes = [ci]
+    lib.tcq4_b200_gguf_open.argtypes = [C.c_char_p, C.POINTER(vp)]
+    lib.tcq4_b200_gguf_close.argtypes = [vp]
+    lib.tcq4_b200_gguf_close.restype = None
+    lib.tcq4_b200_gguf_reorder_enabled.argtypes = [vp]
+    lib.tcq4_b200_gguf_n_tensors.argtypes = [vp]
+    lib.tcq4_b200_gguf_n_tensors.restype = i64
+    lib.tcq4_b200_gguf_n_perms.argtypes = [vp]
+    lib.tcq4_b200_gguf_n_perms.restype = i64
+    lib.tcq4_b200_gguf_tensor_info.argtypes = [vp, i64, C.POINTER(C.c_char_p), C.POINTER(ci), C.POINTER(i64 * 4),
+                                               C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    lib.tcq4_b200_gguf_perm.argtypes = [vp, i64, C.POINTER(C.c_char_p), C.POINTER(vp), C.POINTER(i64)]
+    lib.tcq4_b200_gguf_register_perms.argtypes = [vp]
+    lib.tcq4_b200_gguf_read_tensor.argtypes = [vp, i64, vp, sz]
+    lib.tcq4_b200_gguf_load_tensor.argtypes = [vp, i64, vp, sz, vp]
+    lib.tcq4_b200_gguf_write.argtypes = [C.c_char_p, ci, C.POINTER(C.c_char_p), C.POINTER(ci), C.POINTER(i64), C.POINTER(i64),
+                                         C.POINTER(vp), ci, C.POINTER(C.c_char_p), C.POINTER(vp), C.POINTER(i64), ci]
     lib.tcq4_b200_quantize_size.restype = sz
     lib.tcq4_b200_quantize_size.argtypes = [i64, i64]
     lib.tcq4_b200_quantize_tiles.argtypes = [vp, vp, i64, i64, vp, vp]
@@ -177,6 +196,80 @@ def perm_from_imatrix(imatrix):
     out = np.empty(im.shape[0], dtype=np.int32)
     _check(LIB.tcq4_b200_perm_from_imatrix(im.ctypes.data, im.shape[0], out.ctypes.data))
     return out
+
+
+class GgufFile:
+    """GGUF file with TCQ4 tensors and permutations (tcq4_b200_gguf_*): host-side mirror of the loader's TCQ4 handling
+    (src/llama-model.cpp:7129-7205).  Works without a GPU except register_perms() and load()."""
+
+    def __init__(self, path: str):
+        self._h = None
+        h = C.c_void_p()
+        _check_plain(LIB.tcq4_b200_gguf_open(path.encode(), C.byref(h)), f"cannot parse {path}")
+        self._h = h
+        self.tensors = []                      # (name, ggml type, ne tuple, file offset, nbytes)
+        for i in range(LIB.tcq4_b200_gguf_n_tensors(h)):
+            name, typ, ne = C.c_char_p(), C.c_int(), (C.c_int64 * 4)()
+            off, nb = C.c_uint64(), C.c_uint64()
+            LIB.tcq4_b200_gguf_tensor_info(h, i, C.byref(name), C.byref(typ), C.byref(ne), C.byref(off), C.byref(nb))
+            self.tensors.append((name.value.decode(), typ.value, tuple(ne), off.value, nb.value))
+        self.perms = {}                        # tensor name -> numpy int32[K]
+        import numpy as np
+        for i in range(LIB.tcq4_b200_gguf_n_perms(h)):
+            name, ptr, K = C.c_char_p(), C.c_void_p(), C.c_int64()
+            LIB.tcq4_b200_gguf_perm(h, i, C.byref(name), C.byref(ptr), C.byref(K))
+            self.perms[name.value.decode()] = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_int32)), (K.value,)).copy()
+        r = LIB.tcq4_b200_gguf_reorder_enabled(h)
+        self.reorder_enabled = None if r < 0 else bool(r)
+
+    def read(self, i: int):
+        import numpy as np
+        out = np.empty(self.tensors[i][4], dtype=np.uint8)
+        _check_plain(LIB.tcq4_b200_gguf_read_tensor(self._h, i, out.ctypes.data, out.size), "read_tensor")
+        return out
+
+    def load(self, i: int, stream_ptr: int = 0):
+        """tensor bytes -> a new CUDA uint8 tensor (device bytes == file bytes)"""
+        import torch
+        out = torch.empty(self.tensors[i][4], dtype=torch.uint8, device="cuda")
+        _check_plain(LIB.tcq4_b200_gguf_load_tensor(self._h, i, out.data_ptr(), out.numel(), stream_ptr), "load_tensor")
+        return out
+
+    def register_perms(self):
+        _check_plain(LIB.tcq4_b200_gguf_register_perms(self._h), "register_perms")
+
+    def close(self):
+        if self._h:
+            LIB.tcq4_b200_gguf_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+
+def _check_plain(status: int, what: str):
+    if status != 0:
+        raise Tcq4Error(status, what)
+
+
+def gguf_write(path: str, tensors, perms=None, reorder_enabled=None) -> None:
+    """tensors: list of (name, ggml type (0 F32, 1 F16, 42 TCQ4_K32), ne0, ne1, numpy bytes); perms: {tensor name: int32[K]}."""
+    import numpy as np
+    perms = perms or {}
+    n = len(tensors)
+    names = (C.c_char_p * n)(*[t[0].encode() for t in tensors])
+    types = (C.c_int * n)(*[t[1] for t in tensors])
+    ne0 = (C.c_int64 * n)(*[t[2] for t in tensors])
+    ne1 = (C.c_int64 * n)(*[t[3] for t in tensors])
+    keep = [np.ascontiguousarray(t[4]) for t in tensors]
+    data = (C.c_void_p * n)(*[a.ctypes.data for a in keep])
+    m = len(perms)
+    pk = [np.ascontiguousarray(v, dtype=np.int32) for v in perms.values()]
+    pn = (C.c_char_p * m)(*[k.encode() for k in perms])
+    pp = (C.c_void_p * m)(*[a.ctypes.data for a in pk])
+    pK = (C.c_int64 * m)(*[a.size for a in pk])
+    flag = -1 if reorder_enabled is None else int(bool(reorder_enabled))
+    _check_plain(LIB.tcq4_b200_gguf_write(path.encode(), n, names, types, ne0, ne1, data, m, pn, pp, pK, flag), "gguf_write")
 
 
 def shard_range(N: int, K: int, world: int, rank: int, align: int = 128):

@@ -236,6 +236,104 @@ class RefCPU:
         L.ggml_type_name.restype = C.c_char_p
         L.ggml_type_name.argtypes = [C.c_int]
 
+    # ---- the reference's own GGUF reader / writer (ggml/src/gguf.cpp), to pin the product's tcq4_b200_gguf_* ----------
+    class _GgufInit(C.Structure):
+        _fields_ = [("no_alloc", C.c_bool), ("ctx", C.c_void_p)]
+
+    class _GgmlInit(C.Structure):
+        _fields_ = [("mem_size", C.c_size_t), ("mem_buffer", C.c_void_p), ("no_alloc", C.c_bool)]
+
+    def _gguf_sigs(self):
+        L = self.lib
+        if getattr(self, "_gguf_ready", False):
+            return L
+        vp, i64, sz = C.c_void_p, C.c_int64, C.c_size_t
+        L.gguf_init_from_file.restype = vp
+        L.gguf_init_from_file.argtypes = [C.c_char_p, self._GgufInit]
+        L.gguf_init_empty.restype = vp
+        L.gguf_free.argtypes = [vp]
+        for f, rt in (("gguf_get_n_tensors", i64), ("gguf_get_n_kv", i64), ("gguf_get_data_offset", sz)):
+            getattr(L, f).restype = rt
+            getattr(L, f).argtypes = [vp]
+        for f, rt in (("gguf_get_tensor_name", C.c_char_p), ("gguf_get_tensor_type", C.c_int), ("gguf_get_tensor_offset", sz),
+                      ("gguf_get_tensor_size", sz), ("gguf_get_key", C.c_char_p), ("gguf_get_kv_type", C.c_int),
+                      ("gguf_get_arr_type", C.c_int), ("gguf_get_arr_n", sz), ("gguf_get_arr_data", vp),
+                      ("gguf_get_val_bool", C.c_bool)):
+            getattr(L, f).restype = rt
+            getattr(L, f).argtypes = [vp, i64]
+        L.gguf_find_key.restype = i64
+        L.gguf_find_key.argtypes = [vp, C.c_char_p]
+        L.gguf_set_val_bool.argtypes = [vp, C.c_char_p, C.c_bool]
+        L.gguf_set_arr_data.argtypes = [vp, C.c_char_p, C.c_int, vp, sz]
+        L.gguf_add_tensor.argtypes = [vp, vp]
+        L.gguf_write_to_file.restype = C.c_bool
+        L.gguf_write_to_file.argtypes = [vp, C.c_char_p, C.c_bool]
+        L.ggml_init.restype = vp
+        L.ggml_init.argtypes = [self._GgmlInit]
+        L.ggml_free.argtypes = [vp]
+        L.ggml_new_tensor_2d.restype = vp
+        L.ggml_new_tensor_2d.argtypes = [vp, C.c_int, i64, i64]
+        L.ggml_set_name.restype = vp
+        L.ggml_set_name.argtypes = [vp, C.c_char_p]
+        L.ggml_get_data.restype = vp
+        L.ggml_get_data.argtypes = [vp]
+        L.ggml_nbytes.restype = sz
+        L.ggml_nbytes.argtypes = [vp]
+        self._gguf_ready = True
+        return L
+
+    def gguf_read(self, path: str) -> dict:
+        """Parse with the reference's gguf_init_from_file: tensors [(name, type, abs offset, size)], perms, reorder flag
+        (the scan of src/llama-model.cpp:7133-7166)."""
+        L = self._gguf_sigs()
+        g = L.gguf_init_from_file(path.encode(), self._GgufInit(True, None))
+        assert g, "reference gguf_init_from_file failed"
+        try:
+            base = L.gguf_get_data_offset(g)
+            tensors = [(L.gguf_get_tensor_name(g, i).decode(), L.gguf_get_tensor_type(g, i), base + L.gguf_get_tensor_offset(g, i),
+                        L.gguf_get_tensor_size(g, i)) for i in range(L.gguf_get_n_tensors(g))]
+            perms, reorder = {}, None
+            k = L.gguf_find_key(g, b"tcq4.reorder.enabled")
+            if k >= 0:
+                reorder = bool(L.gguf_get_val_bool(g, k))
+            for i in range(L.gguf_get_n_kv(g)):
+                key = L.gguf_get_key(g, i).decode()
+                if key.startswith("tcq4.") and len(key) > 10 and key.endswith(".perm") and L.gguf_get_kv_type(g, i) == 9 \
+                        and L.gguf_get_arr_type(g, i) == 5:
+                    n = L.gguf_get_arr_n(g, i)
+                    ptr = C.cast(L.gguf_get_arr_data(g, i), C.POINTER(C.c_int32))
+                    perms[key[5:-5]] = np.ctypeslib.as_array(ptr, (n,)).copy()
+            return dict(tensors=tensors, perms=perms, reorder=reorder)
+        finally:
+            L.gguf_free(g)
+
+    def gguf_write(self, path: str, tensors, perms=None, reorder=None) -> None:
+        """Write with the reference's gguf writer: tensors [(name, ggml type, ne0, ne1, numpy bytes)], the TCQ4 keys as
+        src/llama-quant.cpp:840-854 sets them."""
+        L = self._gguf_sigs()
+        total = sum(int(np.asarray(t[4]).nbytes) for t in tensors) + 4096 * (len(tensors) + 4)
+        ctx = L.ggml_init(self._GgmlInit(total, None, False))
+        g = L.gguf_init_empty()
+        try:
+            if reorder is not None:
+                L.gguf_set_val_bool(g, b"tcq4.reorder.enabled", bool(reorder))
+            keep = []
+            for name, p in (perms or {}).items():
+                a = np.ascontiguousarray(p, dtype=np.int32)
+                keep.append(a)
+                L.gguf_set_arr_data(g, f"tcq4.{name}.perm".encode(), 5, a.ctypes.data, a.size)
+            for name, typ, ne0, ne1, data in tensors:
+                t = L.ggml_new_tensor_2d(ctx, typ, ne0, ne1)
+                L.ggml_set_name(t, name.encode())
+                raw = np.ascontiguousarray(data).view(np.uint8).reshape(-1)
+                assert L.ggml_nbytes(t) == raw.size, (name, L.ggml_nbytes(t), raw.size)
+                C.memmove(L.ggml_get_data(t), raw.ctypes.data, raw.size)
+                L.gguf_add_tensor(g, t)
+            assert L.gguf_write_to_file(g, path.encode(), False)
+        finally:
+            L.gguf_free(g)
+            L.ggml_free(ctx)
+
     def type_traits(self):
         L = self.lib
         return dict(name=L.ggml_type_name(GGML_TYPE_TCQ4_K32).decode(),
