@@ -247,7 +247,7 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
     // measured SLOWER (Qwen3-4B prefill chain 7.93 vs 7.04 ms; +7 us per MUL_MAT at K=2560, +15 us at K=9728) -- with 16
     // warps per SM the butterfly is a latency chain of ~1.8 us per round, the stand-alone kernel hides it with 64.
     static const bool want_fuse = getenv("TCQ4_G2_FUSE") != nullptr;
-    const bool fuse = (k == TCQ4_KERNEL_GEMM2) && want_fuse && L.ticket_bytes >= 8;
+    const bool fuse = (k == TCQ4_KERNEL_GEMM2) && want_fuse && plain && L.ticket_bytes >= 8;
     cudaError_t e = cudaSuccess;
     if (!fuse) {
         e = tcq4::launch_act_quant_stage(x, perm, M, K, st, d->num_sms, stream);

@@ -299,7 +299,9 @@ struct G2YMaps {       // one store map per destination matrix (this GPU's C, or
 // OUTM: 0 = one destination (ggml's dst; the code path of the single-GPU product), 1 = several peer-mapped
 // destinations (one tiled store per GPU), 2 = one NVSwitch multicast destination (multimem.st).  A template parameter:
 // carrying the choice at run time cost the plain path 8-10 % (measured).
-template <int NTL, bool DEBUG, bool PROF = false, int OUTM = 0>
+// FUSE: the opt-in fused activation stage; a template parameter because its run-time checks alone cost the default
+// path 1.7 % (measured: 7.04 vs 6.92 ms per Qwen3-4B prefill step).
+template <int NTL, bool DEBUG, bool PROF = false, int OUTM = 0, bool FUSE = false>
 __global__ void __launch_bounds__(G2_THREADS, 1)
 tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_constant__ CUtensorMap tm_meta,
                   const __grid_constant__ G2YMaps tm_y, const uint8_t *__restrict__ w, ActStage st, const G2Fuse fz, int M, int N,
@@ -400,7 +402,7 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
                     g2_tma_2d(stg + G2_A_BYTES + G2_RAW_BYTES, &tm_meta, kt * (TILE_BYTES / 8) + TILE_NIB / 8, nt_pair,
                               &full[s]);
                     // fused mode: the weights are already on their way; the codes exist once every warp has reported
-                    if (gk == 0 && fz.x != nullptr) g2_fused_wait(fz, fused_target, sm_go);
+                    if (FUSE && gk == 0) g2_fused_wait(fz, fused_target, sm_go);
                     bulk_g2s(stg, a_src, G2_A_BYTES, &full[s]);
                     a_src += ACT_UNIT_BYTES;
                     G2_STAMP(0, gk, 1);
@@ -463,7 +465,7 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         asm volatile("setmaxnreg.dec.sync.aligned.u32 56;" ::: "memory");
         // ===================== weight unpack (this CTA's NTL n-tiles) =====================
         const int uw = warp - G2_UNPACK_WARP0;
-        if (fz.x != nullptr)
+        if (FUSE)
             g2_fused_act(fz, st, M, K, (int)blockIdx.x * (G2_UNPACK_WARPS + G2_EPI_WARPS) + uw, fused_nw, lane, sm_cnt);
         const int ut = threadIdx.x - G2_UNPACK_WARP0 * 32;          // 0..255
         // chunk of this thread inside a half k-tile: (gl, j, c) with 8*NTL chunks per group
@@ -545,7 +547,7 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         int gk = 0;
         int mb = 2 * (cluster_id % MB2) + (int)rank;
         float a7 = 0.0f;
-        if (fz.x != nullptr) {
+        if (FUSE) {
             g2_fused_act(fz, st, M, K, (int)blockIdx.x * (G2_UNPACK_WARPS + G2_EPI_WARPS) + G2_UNPACK_WARPS + ew, fused_nw, lane,
                          sm_cnt);
             if (lane == 0) {                                    // the scales below come from other CTAs' warps
@@ -708,7 +710,7 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
 
     tc_fence_before();
     g2_cluster_sync();
-    if (fz.x != nullptr && threadIdx.x == 0) {               // last CTA out re-arms the counters for the next launch
+    if (FUSE && threadIdx.x == 0) {                          // last CTA out re-arms the counters for the next launch
         if (atomicAdd(fz.cnt + 1, 1) == (int)gridDim.x - 1) {
             fz.cnt[0] = 0;
             fz.cnt[1] = 0;
@@ -813,6 +815,18 @@ static cudaError_t launch_gemm2_t(cudaLaunchConfig_t *cfg, const void *w_tiles, 
         cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              Gemm2Smem::total);
         return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, true>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st, fz, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
+    }
+    if (fz.x != nullptr) {      // TCQ4_G2_FUSE=1 (single destination only; checked by the caller)
+        if (dbg_isum) {
+            cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, true, false, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 Gemm2Smem::total);
+            return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, true, false, 0, true>, tm_tiles, tm_meta, tm_y,
+                                      (const uint8_t *)w_tiles, st, fz, (int)M, (int)N, (int)K, MB2, num_tiles, dbg_isum);
+        }
+        cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, false, false, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             Gemm2Smem::total);
+        return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, false, 0, true>, tm_tiles, tm_meta, tm_y,
+                                  (const uint8_t *)w_tiles, st, fz, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
     }
     if (dbg_isum)
         return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, true>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st, fz,
