@@ -45,6 +45,14 @@ __device__ __forceinline__ void fwht256_warp(float (&v)[8], int lane) {
     for (int r = 0; r < 8; r++) v[r] = v[r] * 0.0625f;
 }
 
+// roundf (half away from zero) from one FRND: rintf differs from roundf only on exact .5 ties (it goes to even), and
+// x - rintf(x) is exact for the |x| < 2^22 that occur here, so the tie is detected exactly and repaired.
+__device__ __forceinline__ float round_half_away(float x) {
+    const float r = rintf(x);
+    const float d = x - r;
+    return (fabsf(d) == 0.5f) ? x + copysignf(0.5f, x) : r;      // tie: the neighbour away from zero
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // K4: one CTA of 8 warps builds one tile (warp c = channel c) in shared memory and writes it out as 74 x 16 bytes.
 // ---------------------------------------------------------------------------------------------------------------
@@ -58,9 +66,12 @@ tcq4_quantize_tiles_kernel(const float *__restrict__ w, const int32_t *__restric
     const int g = lane >> 2, s = lane & 3;
     const int KT = K / TILE_K;
 
+    // tile counter kept as (n-tile, k-tile) and advanced without a division per tile
+    long long nt = blockIdx.x / KT;
+    int kt = (int)(blockIdx.x - nt * KT);
+    const long long nt_step = gridDim.x / KT;
+    const int kt_step = (int)(gridDim.x - nt_step * KT);
     for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        const long long nt = t / KT;
-        const int kt = (int)(t - nt * KT);
         const long long row = nt * TILE_CH + c;
         float v[8];
         if (row < nrow) {                                          // rows past the end are zero (ggml-quants.c:1565-1568)
@@ -100,12 +111,12 @@ tcq4_quantize_tiles_kernel(const float *__restrict__ w, const int32_t *__restric
         S = fmaxf(S, __shfl_xor_sync(0xffffffffu, S, 8));
         S = fmaxf(S, __shfl_xor_sync(0xffffffffu, S, 16));
         const float sc_f = __fdiv_rn(scale, S) * 127.0f;
-        const int sc = (int)fmaxf(-127.0f, fminf(127.0f, roundf(sc_f)));
+        const int sc = (int)fmaxf(-127.0f, fminf(127.0f, round_half_away(sc_f)));
         const float inv = __fdiv_rn(1.0f, scale);
         uint32_t reg = 0;
 #pragma unroll
         for (int r = 0; r < 8; r++) {
-            const int q = (int)fmaxf(-8.0f, fminf(7.0f, roundf(v[r] * inv)));
+            const int q = (int)fmaxf(-8.0f, fminf(7.0f, round_half_away(v[r] * inv)));
             reg |= ((uint32_t)q & 0xFu) << (4 * r);
         }
         // fragment order (ggml-quants.c:1381-1400): word c*4 + s of group g holds elements s*8 .. s*8+7 of channel c
@@ -123,6 +134,9 @@ tcq4_quantize_tiles_kernel(const float *__restrict__ w, const int32_t *__restric
             __stcs(reinterpret_cast<uint4 *>(out + (size_t)t * TILE_BYTES) + threadIdx.x,
                    reinterpret_cast<const uint4 *>(&tile)[threadIdx.x]);
         __syncthreads();
+        nt += nt_step;
+        kt += kt_step;
+        if (kt >= KT) { kt -= KT; nt++; }
     }
 }
 

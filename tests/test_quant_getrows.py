@@ -225,3 +225,23 @@ def test_ggml_get_rows_mirror_batched(t4, orc):
         for i11 in range(ne11):
             want = orc.get_rows(slices[i12 * ne11 + i11], idx[i12, i11], K)
             assert np.array_equal(got[i12, i11].view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_quantiser_exact_half_ties_everywhere(t4, orc):
+    """every code boundary k + 0.5 (k = -8 .. 6) in both directions: the kernel's one-FRND roundf must round half away
+    from zero exactly like roundf (ggml-quants.c:1620), including after the clamp to [-8, 7]"""
+    K = 256
+    W = np.zeros((8, K), dtype=np.float32)
+    ties = np.arange(-8, 7, dtype=np.float32) + 0.5                       # 15 ties
+    for c in range(8):
+        for g in range(8):
+            blk = np.zeros(32, dtype=np.float32)
+            blk[0] = 7.0 * (c + 1)                                        # absmax -> scale = c + 1 exactly
+            blk[1:16] = ties * (c + 1)
+            blk[16:31] = -ties * (c + 1)
+            W[c, g * 32:(g + 1) * 32] = blk
+    # the quantiser sees FWHT(W): feed the inverse transform so that the transformed block is exactly `W`
+    Wt = np.stack([np.concatenate([orc.fwht(W[c, b * 256:(b + 1) * 256].copy()) for b in range(K // 256)]) for c in range(8)])
+    got = t4.quantize_tiles(_dev(Wt)).cpu().numpy()
+    assert np.array_equal(got, orc.quantize_tiles(Wt))
