@@ -313,11 +313,11 @@ __device__ __forceinline__ ActQuant rrs_quantize_block(float (&v)[8], int lane) 
     // stages h = 8 .. 128: across lanes, partner = lane ^ (h/8); upper lane computes lower - upper
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-        const bool upper = (lane & d) != 0;
+        const float sgn = (lane & d) ? -1.0f : 1.0f;           // upper lane: lower - upper = o + (-v)
 #pragma unroll
         for (int r = 0; r < 8; r++) {
             const float o = __shfl_xor_sync(0xffffffffu, v[r], d);
-            v[r] = upper ? (o - v[r]) : (v[r] + o);
+            v[r] = __fmaf_rn(v[r], sgn, o);                    // exact: v * (+-1) + o rounds once, like the add
         }
     }
     float mx = 0.0f;
