@@ -396,7 +396,7 @@ def e2e_leg(t4, torch, chain, steps, M):
 
 
 # per-launch DRAM traffic of the headline shapes from the committed ncu captures (profiles/)
-PREFILL_TRAFFIC_BYTES = 15789568
+PREFILL_TRAFFIC_BYTES = 15783680
 DECODE_TRAFFIC_BYTES = 14439680
 
 
@@ -540,7 +540,7 @@ def run_own_arm(args):
             "roofline": {"bound": "tensor", "kernel": "tcq4_gemm2_kernel (tcgen05.mma.cta_group::2 kind::i8)", "achieved": gm_tops,
                          "peak": i8_peak, "unit": "TOP/s", "frac": gm_tops / i8_peak, "traffic": PREFILL_TRAFFIC_BYTES,
                          "traffic_note": "dram__bytes_read+write of the M=512,N=9728,K=2560 launch from one ncu --set full capture "
-                                         "(profiles/prof_gemm2_r01_summary.csv): the weights; x codes and y stay in the 126 MB L2; "
+                                         "(profiles/prof_gemm2_r01d_summary.csv): the weights; x codes and y stay in the 126 MB L2; "
                                          "algorithmic bytes of that launch incl. x and y are 39.6 MB",
                          "peak_source": f"2 x bf16_tflops of MEASURED_PEAKS.json ({peaks['source']}, burst)",
                          "peak_umma_i8_measured": umma_i8, "frac_of_umma_i8": (gm_tops / umma_i8) if umma_i8 else None,
