@@ -71,12 +71,13 @@ __host__ __device__ inline int64_t round_up(int64_t x, int64_t a) { return (x + 
 //      four byte permutes).  Even nibbles land in one register and odd ones in the next: K byte order inside an
 //      8-slice is {0,2,4,6,1,3,5,7}, which the activation kernel mirrors in its s8 codes.
 //      out_hi / out_lo point at this channel's 16-byte row in K-chunk 0; K-chunk 1 is lbo bytes further.
-__device__ __forceinline__ void unpack_chunk_split(const uint4 wq, int sc, uint8_t *out_hi, uint8_t *out_lo, int lbo) {
+// The arithmetic and the four stores are separate steps so that a caller can do the arithmetic BEFORE it waits for the
+// destination stage to become free (tcq4_gemm2.cu).
+__device__ __forceinline__ void unpack_chunk_compute(const uint4 wq, int sc, uint32_t (&hi)[8], uint32_t (&lo)[8]) {
     const uint32_t sh = (uint32_t)(sc >> 4), sl = (uint32_t)(sc & 15);
     const uint32_t ch = 0x80808080u - sh * 0x08080808u;        // 128 - 8*sh in every byte
     const uint32_t cl = 0x80808080u - sl * 0x08080808u;
     const uint32_t wv[4] = {wq.x, wq.y, wq.z, wq.w};
-    uint32_t hi[8], lo[8];
 #pragma unroll
     for (int s = 0; s < 4; s++) {
         const uint32_t e = (wv[s] ^ 0x08080808u) & 0x0F0F0F0Fu;            // u of elements 0, 2, 4, 6
@@ -86,10 +87,18 @@ __device__ __forceinline__ void unpack_chunk_split(const uint4 wq, int sc, uint8
         lo[s * 2 + 0] = (e * sl + cl) ^ 0x80808080u;
         lo[s * 2 + 1] = (o * sl + cl) ^ 0x80808080u;
     }
+}
+__device__ __forceinline__ void unpack_chunk_store(const uint32_t (&hi)[8], const uint32_t (&lo)[8], uint8_t *out_hi,
+                                                   uint8_t *out_lo, int lbo) {
     *reinterpret_cast<uint4 *>(out_hi) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
     *reinterpret_cast<uint4 *>(out_hi + lbo) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
     *reinterpret_cast<uint4 *>(out_lo) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
     *reinterpret_cast<uint4 *>(out_lo + lbo) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+}
+__device__ __forceinline__ void unpack_chunk_split(const uint4 wq, int sc, uint8_t *out_hi, uint8_t *out_lo, int lbo) {
+    uint32_t hi[8], lo[8];
+    unpack_chunk_compute(wq, sc, hi, lo);
+    unpack_chunk_store(hi, lo, out_hi, out_lo, lbo);
 }
 #endif
 
