@@ -95,6 +95,22 @@ TCQ4_B200_API int tcq4_b200_mul_mat(const void *w_tiles, const float *x, float *
                                     cudaStream_t stream);
 TCQ4_B200_API int tcq4_b200_reserve(int64_t max_M, int64_t max_N, int64_t max_K);
 
+/* MUL_MAT_ID, the mixture-of-experts form of the same operator: replaces ggml_cuda_mul_mat_id
+ * (ggml-cuda.cu:2287-2436) for a TCQ4 src0, which the reference admits in supports_op (:4457-4459) and serves through
+ * its generic path (ids to the host, rows sorted by expert, one ggml_cuda_mul_mat per expert).
+ *   w_experts : n_expert matrices of [N/8][K/256] tiles, expert e at w_experts + e * expert_stride_bytes (ggml nb02)
+ *   x   : F32 [n_tokens][x_slots][K] contiguous, x_slots = 1 (one row per token, broadcast to its experts: gate / up)
+ *         or n_used (one row per token and slot: down)                       -- ggml src1 [K, ne11, n_tokens]
+ *   ids : device int32, ids[t * ids_stride + s] = expert of slot s of token t  -- ggml ids [n_used, n_tokens]
+ *   y   : F32 [n_tokens][n_used][N] contiguous:  y[t][s][:] = W[ids[t][s]] * x[t][s % x_slots][:]
+ * n_tokens == 1 runs without any host round trip (the kernel reads the id on the device; capturable in a CUDA graph;
+ * an id outside [0, n_expert) sets *err_flag -- device int, may be NULL -- and computes with expert 0).
+ * n_tokens > 1 reads the ids on the host like the reference (synchronises the stream; a bad id returns TCQ4_ERR_ARG). */
+TCQ4_B200_API int tcq4_b200_mul_mat_id(const void *w_experts, int64_t n_expert, size_t expert_stride_bytes,
+                                       const float *x, int64_t x_slots, const int32_t *ids, int64_t ids_stride,
+                                       int64_t n_used, int64_t n_tokens, float *y, int64_t N, int64_t K,
+                                       const int32_t *d_perm, int *err_flag, cudaStream_t stream);
+
 /* End-to-end entry with HOST activations/outputs (weights stay resident on the device, as they do
  * in a ggml CUDA buffer): H2D copy of x, MUL_MAT, D2H copy of y, all on `stream`, then a stream
  * synchronise.  Mirrors ggml_backend_tensor_set + graph_compute + ggml_backend_tensor_get. */
@@ -216,6 +232,12 @@ TCQ4_B200_API int tcq4_b200_ggml_supports_op(const tcq4_tensor_view *src0, const
 TCQ4_B200_API int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1,
                                          tcq4_tensor_view *dst, void *workspace, size_t workspace_bytes,
                                          cudaStream_t stream);
+
+/* ggml_cuda_mul_mat_id (ggml-cuda.cu:2287-2436) for a TCQ4 src0: src0 [K, N, n_expert], src1 F32 [K, ne11, n_tokens]
+ * with ne11 in {1, n_used}, ids I32 [n_used, n_tokens], dst F32 [N, n_used, n_tokens]; perm looked up by src0->name. */
+TCQ4_B200_API int tcq4_b200_ggml_mul_mat_id(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1,
+                                            const tcq4_tensor_view *ids, tcq4_tensor_view *dst, int *err_flag,
+                                            cudaStream_t stream);
 
 /* ggml_cuda_op_get_rows for a TCQ4 src0 (ggml/src/ggml-cuda/getrows.cu:397-430, 348-380): src1 is GGML_TYPE_I32 (26)
  * [ne10, ne11, ne12] with contiguous dim 0, dst F32 [K, ne10, ne11, ne12]; admitted by supports_op at ggml-cuda.cu:4478-4480. */

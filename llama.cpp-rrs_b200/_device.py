@@ -15,7 +15,7 @@ import torch
 from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
                ACT_BLOCK_BYTES, TensorView, _check, quantize_size, shard_range, tile_bytes, workspace_size)
 
-__all__ = ["Workspace", "mul_mat", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
+__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
            "ggml_supports_op", "ShardedWeight", "random_tiles", "quantize_tiles", "get_rows", "ggml_get_rows"]
 
@@ -251,6 +251,57 @@ def ggml_get_rows(w_tiles: torch.Tensor, idx: torch.Tensor, nrows: int, K: int, 
     dst = _view(out, GGML_TYPE_F32, [K, ne10, ne11, ne12], [4, 4 * K, 4 * K * ne10, 4 * K * ne10 * ne11], b"dst")
     ef = err_flag.data_ptr() if err_flag is not None else 0
     _check(LIB.tcq4_b200_ggml_get_rows(C.byref(src0), C.byref(src1), C.byref(dst), ef, _stream_ptr(stream)))
+    return out
+
+
+def mul_mat_id(w_experts: torch.Tensor, x: torch.Tensor, ids: torch.Tensor, N: int, perm: torch.Tensor | None = None,
+               out: torch.Tensor | None = None, err_flag: torch.Tensor | None = None, stream=None) -> torch.Tensor:
+    """MUL_MAT_ID (ggml_cuda_mul_mat_id, ggml-cuda.cu:2287-2436): w_experts uint8 [n_expert][tile bytes of N x K],
+    x F32 [n_tokens][1 or n_used][K], ids int32 [n_tokens][n_used] -> y F32 [n_tokens][n_used][N] with
+    y[t][s] = W[ids[t][s]] x[t][s % x_slots]."""
+    _req_cuda(w_experts, torch.uint8, "w_experts")
+    _req_cuda(x, torch.float32, "x")
+    if not ids.is_cuda or ids.dtype != torch.int32 or ids.dim() != 2:
+        raise ValueError("ids must be a 2-D CUDA tensor of dtype torch.int32 (rows may be strided)")
+    n_tokens, x_slots, K = x.shape
+    n_used = ids.shape[1]
+    n_expert = w_experts.shape[0]
+    if ids.shape[0] != n_tokens or (n_used > 1 and ids.stride(1) != 1):
+        raise ValueError("ids must be [n_tokens][n_used] with contiguous slots")
+    if w_experts.dim() != 2 or w_experts.shape[1] != tile_bytes(N, K) or w_experts.stride(1) != 1:
+        raise ValueError(f"w_experts must be [n_expert][{tile_bytes(N, K)}] bytes")
+    if out is None:
+        out = torch.empty((n_tokens, n_used, N), dtype=torch.float32, device=x.device)
+    _req_cuda(out, torch.float32, "out")
+    pp = 0
+    if perm is not None:
+        _req_cuda(perm, torch.int32, "perm")
+        pp = perm.data_ptr()
+    ef = err_flag.data_ptr() if err_flag is not None else 0
+    ids_stride = ids.stride(0) if n_tokens > 1 else n_used          # a size-1 dimension may carry any stride
+    _check(LIB.tcq4_b200_mul_mat_id(w_experts.data_ptr(), n_expert, w_experts.stride(0), x.data_ptr(), x_slots,
+                                    ids.data_ptr(), ids_stride, n_used, n_tokens, out.data_ptr(), N, K, pp, ef,
+                                    _stream_ptr(stream)))
+    return out
+
+
+def ggml_mul_mat_id(w_experts: torch.Tensor, x: torch.Tensor, ids: torch.Tensor, N: int, name: str = "",
+                    err_flag: torch.Tensor | None = None, stream=None) -> torch.Tensor:
+    """The same through the ggml operator mirror: src0 [K, N, n_expert], src1 [K, ne11, n_tokens], ids [n_used, n_tokens],
+    dst [N, n_used, n_tokens]; the perm is looked up by src0->name."""
+    n_tokens, ne11, K = x.shape
+    n_used = ids.shape[1]
+    n_expert = w_experts.shape[0]
+    row = (K // TILE_K) * 148
+    ist = ids.stride(0) if n_tokens > 1 else n_used
+    out = torch.empty((n_tokens, n_used, N), dtype=torch.float32, device=x.device)
+    src0 = _view(w_experts, GGML_TYPE_TCQ4_K32, [K, N, n_expert, 1], [148, row, w_experts.stride(0), w_experts.stride(0) * n_expert],
+                 name.encode())
+    src1 = _view(x, GGML_TYPE_F32, [K, ne11, n_tokens, 1], [4, 4 * K, 4 * K * ne11, 4 * K * ne11 * n_tokens], b"x")
+    idv = _view(ids, 26, [n_used, n_tokens, 1, 1], [4, 4 * ist, 4 * ist * n_tokens, 4 * ist * n_tokens], b"ids")
+    dst = _view(out, GGML_TYPE_F32, [N, n_used, n_tokens, 1], [4, 4 * N, 4 * N * n_used, 4 * N * n_used * n_tokens], b"dst")
+    ef = err_flag.data_ptr() if err_flag is not None else 0
+    _check(LIB.tcq4_b200_ggml_mul_mat_id(C.byref(src0), C.byref(src1), C.byref(idv), C.byref(dst), ef, _stream_ptr(stream)))
     return out
 
 

@@ -14,6 +14,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <vector>
 
 #include "tcq4_kernels.h"
 
@@ -386,6 +387,129 @@ int tcq4_b200_mul_mat(const void *w_tiles, const float *x, float *y, int64_t M, 
     if (status != TCQ4_OK) return status;
     return run_mul_mat(w_tiles, x, single_out(y, N), M, N, K, d_perm, d->arena, d->arena_bytes, TCQ4_KERNEL_AUTO, nullptr,
                        stream);
+}
+
+// MUL_MAT_ID (ggml_mul_mat_id: dst[tok][slot][:] = W[ids[tok][slot]] * x[tok][slot % x_slots][:]), the operator the
+// reference admits for TCQ4 in supports_op (ggml-cuda.cu:4457-4459) and serves through its generic sorted path
+// (ggml_cuda_mul_mat_id, :2287-2436: ids to the host, rows sorted by expert, get_rows, one ggml_cuda_mul_mat per expert,
+// get_rows back).
+//  * n_tokens == 1 (decode): NO host round trip and ONE launch -- a GEMV over the virtual [n_used * N][K] matrix whose
+//    channel blocks take their tiles from the expert the ids name, read by the kernel on the device; x and y are used
+//    in place.  Capturable in a graph.  (Fallback when x_slots activation rows do not fit the GEMV's shared memory: one
+//    GEMV per slot; slot 0 in plain stream order -- the ids come from the router kernel before it -- slots 1.. with
+//    programmatic dependent launch: they cannot start before slot 0 has, i.e. not before the router has completed.)
+//  * n_tokens  > 1: the reference's scheme -- ids are read on the host (stream synchronise; not capturable), rows are
+//    counting-sorted by expert, gathered by one copy kernel, multiplied per expert through the normal dispatch (GEMV
+//    for <= 16 rows, tcgen05 GEMMs above), and scattered back by the same copy kernel.
+int tcq4_b200_mul_mat_id(const void *w_experts, int64_t n_expert, size_t expert_stride_bytes, const float *x,
+                         int64_t x_slots, const int32_t *ids, int64_t ids_stride, int64_t n_used, int64_t n_tokens, float *y,
+                         int64_t N, int64_t K, const int32_t *d_perm, int *err_flag, cudaStream_t stream) {
+    if (n_expert < 1 || n_used < 1 || n_tokens < 1 || (n_tokens > 1 && ids_stride < n_used) ||
+        (x_slots != 1 && x_slots != n_used)) {
+        set_err("mul_mat_id: need n_expert, n_used, n_tokens >= 1, ids_stride >= n_used and x_slots in {1, n_used}");
+        return TCQ4_ERR_ARG;
+    }
+    if (!shape_ok(1, N, K)) {
+        set_err("unsupported shape N=%lld K=%lld (need K%%256==0, N%%8==0)", (long long)N, (long long)K);
+        return TCQ4_ERR_SHAPE;
+    }
+    if (!w_experts || !x || !ids || !y || ((uintptr_t)w_experts & 15) || (expert_stride_bytes & 15) ||
+        expert_stride_bytes < (size_t)(N / 8) * (size_t)(K / 256) * 1184 || ((uintptr_t)ids & 3)) {
+        set_err("mul_mat_id: null / misaligned pointer or expert stride smaller than one matrix");
+        return TCQ4_ERR_ARG;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    const int64_t R = n_tokens * n_used;
+    tcq4::GemvPlan gv;
+    static const bool no_group = getenv("TCQ4_MOE_GROUP") == nullptr;        // grouped launch: opt-in until verified on the GPU
+    if (n_tokens == 1 && !no_group && tcq4::gemv_plan(x_slots, n_used * N, K, d->num_sms, d->smem_optin, &gv)) {
+        // ONE launch for all slots: a GEMV over the virtual [n_used * N][K] matrix (launch_gemv_grouped)
+        const tcq4::GvExpert ex{ids, (long long)expert_stride_bytes, (int)n_expert, err_flag, 0, (int)x_slots, (int)(N / 8)};
+        cudaError_t e = tcq4::launch_gemv_grouped(w_experts, x, d_perm, y, n_used, N, K, gv, ex, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "grouped gemv launch (mul_mat_id)");
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        return TCQ4_OK;
+    }
+    if (n_tokens == 1 && tcq4::gemv_plan(1, N, K, d->num_sms, d->smem_optin, &gv)) {
+        const WsLayout L = ws_layout(1, N, K);
+        status = arena_ensure(d, L.total, stream);
+        if (status != TCQ4_OK) return status;
+        uint8_t *wsb = reinterpret_cast<uint8_t *>(d->arena);
+        for (int64_t s = 0; s < n_used; s++) {
+            const tcq4::GvExpert ex{ids + s, (long long)expert_stride_bytes, (int)n_expert, err_flag, s > 0 ? 1 : 0, 0, 0};
+            cudaError_t e = tcq4::launch_gemv(w_experts, x + (s % x_slots) * K, d_perm, single_out(y + s * N, N), 1, N, K, gv,
+                                              nullptr, reinterpret_cast<int *>(wsb + L.ticket_off), nullptr, stream, &ex);
+            if (e != cudaSuccess) return cuda_fail(e, "gemv launch (mul_mat_id)");
+            g_launches.fetch_add(1, std::memory_order_relaxed);
+        }
+        return TCQ4_OK;
+    }
+
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (stream != nullptr && cudaStreamIsCapturing(stream, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone) {
+        set_err("mul_mat_id with more than one token reads the ids on the host (as ggml_cuda_mul_mat_id does): not capturable");
+        return TCQ4_ERR_ARG;
+    }
+    // ---- ids to the host, counting sort by expert (ggml-cuda.cu:2349-2368) -----------------------------------------
+    if (n_tokens == 1) ids_stride = n_used;
+    std::vector<int32_t> ids_host((size_t)((n_tokens - 1) * ids_stride + n_used));
+    cudaError_t e = cudaMemcpyAsync(ids_host.data(), ids, ids_host.size() * 4, cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) return cuda_fail(e, "mul_mat_id: ids to host");
+    std::vector<int64_t> count((size_t)n_expert + 1, 0);
+    for (int64_t t = 0; t < n_tokens; t++)
+        for (int64_t s = 0; s < n_used; s++) {
+            const int32_t ex = ids_host[(size_t)(t * ids_stride + s)];
+            if (ex < 0 || ex >= n_expert) {
+                set_err("mul_mat_id: expert id %d of token %lld slot %lld outside [0, %lld)", ex, (long long)t, (long long)s,
+                        (long long)n_expert);
+                return TCQ4_ERR_ARG;
+            }
+            count[(size_t)ex + 1]++;
+        }
+    for (int64_t i = 0; i < n_expert; i++) count[(size_t)i + 1] += count[(size_t)i];     // count[e] = first sorted row of e
+    std::vector<int32_t> idx((size_t)2 * R);            // [0, R): source row of x per sorted row; [R, 2R): row of dst
+    {
+        std::vector<int64_t> fill(count.begin(), count.end() - 1);
+        for (int64_t t = 0; t < n_tokens; t++)
+            for (int64_t s = 0; s < n_used; s++) {
+                const int32_t ex = ids_host[(size_t)(t * ids_stride + s)];
+                const int64_t r = fill[(size_t)ex]++;
+                idx[(size_t)r] = (int32_t)(t * x_slots + s % x_slots);
+                idx[(size_t)(R + r)] = (int32_t)(t * n_used + s);
+            }
+    }
+    // ---- scratch: [MUL_MAT workspace][x sorted R x K][y sorted R x N][2R indices] ---------------------------------
+    size_t ws_need = ws_layout(R, N, K).total;
+    for (int64_t m : {(int64_t)8, (int64_t)16}) ws_need = std::max(ws_need, ws_layout(std::min(R, m), N, K).total);
+    const size_t xs_off = (size_t)tcq4::round_up((int64_t)ws_need, 256);
+    const size_t ys_off = xs_off + (size_t)tcq4::round_up(R * K * 4, 256);
+    const size_t ix_off = ys_off + (size_t)tcq4::round_up(R * N * 4, 256);
+    const size_t total = ix_off + (size_t)tcq4::round_up(2 * R * 4, 256);
+    status = arena_ensure(d, total, stream);
+    if (status != TCQ4_OK) return status;
+    uint8_t *base = reinterpret_cast<uint8_t *>(d->arena);
+    float *xs = reinterpret_cast<float *>(base + xs_off), *ys = reinterpret_cast<float *>(base + ys_off);
+    int32_t *ix = reinterpret_cast<int32_t *>(base + ix_off);
+    e = cudaMemcpyAsync(ix, idx.data(), idx.size() * 4, cudaMemcpyHostToDevice, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);          // idx is a local: the copy must have left it
+    if (e != cudaSuccess) return cuda_fail(e, "mul_mat_id: indices to device");
+    e = tcq4::launch_copy_rows(x, ix, xs, nullptr, R, K, d->num_sms, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "mul_mat_id: gather");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    for (int64_t ex = 0; ex < n_expert; ex++) {
+        const int64_t r0 = count[(size_t)ex], m = count[(size_t)ex + 1] - r0;
+        if (m == 0) continue;
+        status = run_mul_mat(reinterpret_cast<const uint8_t *>(w_experts) + (size_t)ex * expert_stride_bytes, xs + r0 * K,
+                             single_out(ys + r0 * N, N), m, N, K, d_perm, base, ws_need, TCQ4_KERNEL_AUTO, nullptr, stream);
+        if (status != TCQ4_OK) return status;
+    }
+    e = tcq4::launch_copy_rows(ys, nullptr, y, ix + R, R, N, d->num_sms, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "mul_mat_id: scatter");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return TCQ4_OK;
 }
 
 // N-sharded MUL_MAT with the all-gather fused away: the N columns this GPU owns are written, by the kernel's own

@@ -177,11 +177,11 @@ tcq4_gemv_prepass_kernel(const float *__restrict__ x, const int32_t *__restrict_
 // MT > 0 selects the dp4a inner loop for exactly MT <= 3 tokens (at 4 the IMMA loop is faster: 14.9 vs 17.7 us at
 // N=14336, K=4096) (see "dp4a path" below); MT = 0 the IMMA loop for
 // up to 8 * MB tokens.
-template <int MB, int MT, bool DEBUG>
+template <int MB, int MT, bool DEBUG, bool GROUP = false>
 __global__ void __launch_bounds__(512, (MT == 1 && !DEBUG) ? 2 : 1)
 tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, const int32_t *__restrict__ perm,
                  const YOut out, int M, int N, int K, int depth, const uint8_t *__restrict__ pre_blob,
-                 int32_t *__restrict__ dbg_isum) {
+                 int32_t *__restrict__ dbg_isum, const GvExpert ex) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int KT = K / TILE_K;
     const int NT = N / TILE_CH;
@@ -190,12 +190,16 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
 
     const int NW = (int)(blockDim.x >> 5);          // warps of this CTA
     const int workers = NW * GV_CLUSTER, entries = workers * 2;
-    const GvSmem L(M, KT, NW, depth);
+    // GROUP (MUL_MAT_ID, one token): M = 1 token is computed per channel, but Ma activation rows (one per slot) may sit
+    // in shared memory; N is the virtual channel count n_used * N_expert
+    static_assert(!GROUP || (MB == 1 && MT == 1), "grouped launches use the one-token dp4a loop");
+    const int Ma = GROUP ? ex.xslots : M;
+    const GvSmem L(Ma, KT, NW, depth);
     uint8_t *ring = smem + L.off_ring;
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + L.off_full);
     uint2 *afrag = reinterpret_cast<uint2 *>(smem + L.off_afrag);      // [KT][8][M][4]
     float *rms = reinterpret_cast<float *>(smem + L.off_rm);           // [KT][M]   a7 / 127
-    float *a7s = rms + M * KT;                                         // [KT][M]   max_abs / 7
+    float *a7s = rms + Ma * KT;                                        // [KT][M]   max_abs / 7
     int *sumq = reinterpret_cast<int *>(smem + L.off_sumq);            // [M][KT][8]
     float *part = reinterpret_cast<float *>(smem + L.off_part);        // [entry][M][8]   (CTA 0's copy is the live one)
     int *prow = reinterpret_cast<int *>(smem + L.off_prow);            // [entry] n-tile or -1
@@ -225,6 +229,33 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     uint8_t *myring = ring + warp * depth * TILE_BYTES;
     uint64_t *myfull = full + warp * depth;
     const uint8_t *wsrc = w + ((size_t)R0 * KT + lt0) * TILE_BYTES;
+    // weight tile i of this warp.  Plain: tiles are in memory order.  GROUP: the slot's expert comes from the ids
+    auto tile_src = [&](int i) -> const uint8_t * {
+        if constexpr (!GROUP) {
+            return wsrc + (size_t)i * TILE_BYTES;
+        } else {
+            const int g = lt0 + i, rr = g / KT;
+            const int row = R0 + rr, k = g - rr * KT;
+            const int s = row / ex.nt_expert;
+            int e = __ldg(ex.sel + s);
+            if ((unsigned)e >= (unsigned)ex.n) {
+                if (ex.err != nullptr) *ex.err = 1;
+                e = 0;
+            }
+            return w + (size_t)e * (size_t)ex.stride + ((size_t)(row - s * ex.nt_expert) * KT + k) * TILE_BYTES;
+        }
+    };
+    if (!GROUP && ex.sel != nullptr) {
+        // MUL_MAT_ID: this launch's expert matrix.  The id comes from an earlier kernel of the stream (the router) and is
+        // read here, ahead of griddepcontrol.wait: the first slot's launch is made without programmatic serialisation (it
+        // starts after the router has completed), the later ones start no earlier than the first one has.
+        int e = __ldcg(ex.sel);
+        if ((unsigned)e >= (unsigned)ex.n) {
+            if (ex.err != nullptr && threadIdx.x == 0 && blockIdx.x == 0) *ex.err = 1;
+            e = 0;
+        }
+        wsrc += (size_t)e * (size_t)ex.stride;
+    }
     uint64_t pol = 0;
     if (lane == 0) {
         for (int i = 0; i < depth; i++) mbar_init(&myfull[i], 1);
@@ -233,7 +264,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
         const int pre = cnt < depth ? cnt : depth;
         for (int i = 0; i < pre; i++) {
             mbar_arrive_expect_tx(&myfull[i], TILE_BYTES);
-            bulk_g2s_stream(myring + i * TILE_BYTES, wsrc + (size_t)i * TILE_BYTES, TILE_BYTES, &myfull[i], pol);
+            bulk_g2s_stream(myring + i * TILE_BYTES, tile_src(i), TILE_BYTES, &myfull[i], pol);
         }
     }
     __syncwarp();
@@ -259,17 +290,17 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
         for (int i = threadIdx.x; i < n16; i += blockDim.x) dst[i] = __ldcg(src + i);
     } else {
         float vn[8];
-        if (warp < M * KT) rrs_load_block_cg(x + (size_t)(warp / KT) * K, perm, warp % KT, lane, vn);
-        for (int b = warp; b < M * KT; b += NW) {
+        if (warp < Ma * KT) rrs_load_block_cg(x + (size_t)(warp / KT) * K, perm, warp % KT, lane, vn);
+        for (int b = warp; b < Ma * KT; b += NW) {
             const int m = b / KT, kt = b - m * KT;
             float v[8];
 #pragma unroll
             for (int i = 0; i < 8; i++) v[i] = vn[i];
-            if (b + NW < M * KT) rrs_load_block_cg(x + (size_t)((b + NW) / KT) * K, perm, (b + NW) % KT, lane, vn);
+            if (b + NW < Ma * KT) rrs_load_block_cg(x + (size_t)((b + NW) / KT) * K, perm, (b + NW) % KT, lane, vn);
             if (b == warp) GV_STAMP_DEP(8, v[0] + v[7]);
             const ActQuant a = rrs_quantize_block(v, lane);            // lane = (group r, k-quarter q), elements lane*8..+7
             if (b == warp) GV_STAMP_DEP(9, a.max_abs + (float)(a.q[7] + a.gsum));
-            gv_store_act_block(a, smem + L.off_afrag, L.off_rm - L.off_afrag, L.off_sumq - L.off_afrag, M, KT, m, kt, lane,
+            gv_store_act_block(a, smem + L.off_afrag, L.off_rm - L.off_afrag, L.off_sumq - L.off_afrag, Ma, KT, m, kt, lane,
                                MT > 0);
             if (b == warp) GV_STAMP(6);
         }
@@ -314,6 +345,8 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     for (int m = 0; m < MT; m++) accd[m] = 0.0f;
     int slot = 0;
     uint32_t phase = 0;
+    const int MS = GROUP ? Ma : MT;                            // activation rows in the shared-memory layout
+    int m0 = (GROUP && Ma > 1) ? nt / ex.nt_expert : 0;       // GROUP: this channel block's own activation row
     for (int i = 0; i < cnt; i++) {
         GV_ITER(i, 0);
         mbar_wait(&myfull[slot], phase);
@@ -334,7 +367,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(TILE_BYTES) : "memory");
                 asm volatile(
                     "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
-                        "r"(dst), "l"(wsrc + (size_t)(i + depth) * TILE_BYTES), "r"(TILE_BYTES), "r"(bar), "l"(pol)
+                        "r"(dst), "l"(tile_src(i + depth)), "r"(TILE_BYTES), "r"(bar), "l"(pol)
                     : "memory");
             }
         }
@@ -349,8 +382,8 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
         const float S = __half2float(__ushort_as_half(sh));
 #pragma unroll
         for (int m = 0; m < MT; m++) {
-            const uint4 *a0p = afq + ((kt * 8 + gq) * MT + m) * 2;
-            const uint4 *a1p = afq + ((kt * 8 + gq + 4) * MT + m) * 2;
+            const uint4 *a0p = afq + ((kt * 8 + gq) * MS + m0 + m) * 2;
+            const uint4 *a1p = afq + ((kt * 8 + gq + 4) * MS + m0 + m) * 2;
             const uint4 e0 = a0p[0], o0 = a0p[1], e1 = a1p[0], o1 = a1p[1];
             int d0 = __dp4a((int)ae[0], (int)e0.x, 0);
             d0 = __dp4a((int)ao[0], (int)o0.x, d0);
@@ -372,8 +405,8 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
             is += __shfl_xor_sync(0xffffffffu, is, 8);
             is += __shfl_xor_sync(0xffffffffu, is, 16);
             const int isv = is >> 4;                                 // weights were carried as 16*q: exact
-            accd[m] = __fmaf_rn((float)isv * rms[kt * MT + m], S, accd[m]);
-            if (anyz) accd[m] += gv_zero_point(zh, zcv, sumq + (m * KT + kt) * 8, a7s[kt * MT + m]);
+            accd[m] = __fmaf_rn((float)isv * rms[kt * MS + m0 + m], S, accd[m]);
+            if (anyz) accd[m] += gv_zero_point(zh, zcv, sumq + ((m0 + m) * KT + kt) * 8, a7s[kt * MS + m0 + m]);
             if (DEBUG && dbg_isum && lane < 8) dbg_isum[((size_t)m * N + nt * 8 + cc) * KT + kt] = isv;
         }
         GV_ITER(i, 2);
@@ -406,6 +439,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
         if (row_end) {
             kt = 0;
             nt++;
+            if (GROUP && Ma > 1) m0 = nt / ex.nt_expert;
             from_row_start = true;
         } else {
             kt++;
@@ -690,7 +724,7 @@ bool gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, 
 template <int MB, int MT, bool DEBUG>
 static cudaError_t launch_gemv_t(const void *w, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
                                  int64_t K, const GemvPlan &plan, const uint8_t *pre_blob, int32_t *dbg,
-                                 cudaStream_t stream) {
+                                 cudaStream_t stream, const GvExpert *expert) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)plan.grid);
     cfg.blockDim = dim3((unsigned)plan.warps * 32);
@@ -708,9 +742,11 @@ static cudaError_t launch_gemv_t(const void *w, const float *x, const int32_t *p
     // together (M = 1: 64 registers, ring of <= 5 tiles): the next MUL_MAT's barrier setup and weight prefetch run under
     // this one's loop.  N=9728, K=2560, M=1, 24 launches in a graph: 8.5 us per launch without, 7.0 us with.
     static const bool pdl = getenv("TCQ4_NO_PDL") == nullptr;
-    cfg.numAttrs = pdl ? 2 : 1;
+    // an expert id is read at kernel entry, before griddepcontrol.wait: the caller says when that is safe
+    cfg.numAttrs = (pdl && (expert == nullptr || expert->pdl)) ? 2 : 1;
+    const GvExpert ex = expert ? *expert : GvExpert{nullptr, 0, 0, nullptr, 0, 0, 0};
     return cudaLaunchKernelEx(&cfg, tcq4_gemv_kernel<MB, MT, DEBUG>, (const uint8_t *)w, x, perm, y, (int)M, (int)N, (int)K,
-                              plan.depth, pre_blob, dbg);
+                              plan.depth, pre_blob, dbg, ex);
 }
 
 template <int MB, int MT>
@@ -738,12 +774,46 @@ cudaError_t gemv_init_attributes(size_t smem_optin) {
     if (e == cudaSuccess) e = gemv_attr_one<1, 1>(smem_optin);
     if (e == cudaSuccess) e = gemv_attr_one<1, 2>(smem_optin);
     if (e == cudaSuccess) e = gemv_attr_one<1, 3>(smem_optin);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(tcq4_gemv_kernel<1, 1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem_optin);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(tcq4_gemv_kernel<1, 1, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                 (int)cudaSharedmemCarveoutMaxShared);
     return e;
+}
+
+// MUL_MAT_ID for one token as ONE launch: a GEMV over the virtual matrix of n_used * N channels whose channel blocks
+// take their weight tiles from the expert the ids name (GvExpert, tcq4_kernels.h).  Launched in plain stream order: the
+// ids are read at kernel entry.
+cudaError_t launch_gemv_grouped(const void *w_experts, const float *x, const int32_t *perm, float *y, int64_t n_used,
+                                int64_t N, int64_t K, const GemvPlan &plan, const GvExpert &expert, cudaStream_t stream) {
+    if (expert.sel == nullptr || expert.xslots < 1 || expert.nt_expert != (int)(N / TILE_CH)) return cudaErrorInvalidValue;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)plan.grid);
+    cfg.blockDim = dim3((unsigned)plan.warps * 32);
+    cfg.dynamicSmemBytes = plan.smem_bytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = GV_CLUSTER;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    YOut yo;
+    for (int i = 0; i < MAX_PEERS; i++) yo.p[i] = y;
+    yo.n = 1;
+    yo.ldc = n_used * N;
+    yo.mc = nullptr;
+    return cudaLaunchKernelEx(&cfg, tcq4_gemv_kernel<1, 1, false, true>, (const uint8_t *)w_experts, x, perm, yo, 1,
+                              (int)(n_used * N), (int)K, plan.depth, (const uint8_t *)nullptr, (int32_t *)nullptr, expert);
 }
 
 template <int MB, int MT>
 static cudaError_t launch_gemv_d(bool debug, const void *w, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
-                                 int64_t K, const GemvPlan &plan, uint8_t *blob, int32_t *dbg, cudaStream_t stream) {
+                                 int64_t K, const GemvPlan &plan, uint8_t *blob, int32_t *dbg, cudaStream_t stream,
+                                 const GvExpert *expert) {
     const uint8_t *pre = nullptr;
     if (plan.prepass && blob != nullptr) {
         // activation stage once for the whole GPU (see tcq4_gemv_prepass_kernel), in the GEMV's own layout
@@ -764,13 +834,13 @@ static cudaError_t launch_gemv_d(bool debug, const void *w, const float *x, cons
         if (e != cudaSuccess) return e;
         pre = blob;
     }
-    if (debug) return launch_gemv_t<MB, MT, true>(w, x, perm, y, M, N, K, plan, pre, dbg, stream);
-    return launch_gemv_t<MB, MT, false>(w, x, perm, y, M, N, K, plan, pre, nullptr, stream);
+    if (debug) return launch_gemv_t<MB, MT, true>(w, x, perm, y, M, N, K, plan, pre, dbg, stream, expert);
+    return launch_gemv_t<MB, MT, false>(w, x, perm, y, M, N, K, plan, pre, nullptr, stream, expert);
 }
 
 cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
                         int64_t K, const GemvPlan &plan, float *ws_partial, int *ws_ticket, int32_t *dbg_isum,
-                        cudaStream_t stream) {
+                        cudaStream_t stream, const GvExpert *expert) {
     uint8_t *blob = reinterpret_cast<uint8_t *>(ws_partial);      // pre-pass output (plan.blob_bytes), may be null
     (void)ws_ticket;
     if (M < 1 || M > GEMV_MAX_M) return cudaErrorInvalidValue;
@@ -779,14 +849,14 @@ cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm
     const bool dbg = dbg_isum != nullptr || prof;
     if (!nodp) {
         switch (M) {
-            case 1: return launch_gemv_d<1, 1>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream);
-            case 2: return launch_gemv_d<1, 2>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream);
-            case 3: return launch_gemv_d<1, 3>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream);
+            case 1: return launch_gemv_d<1, 1>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream, expert);
+            case 2: return launch_gemv_d<1, 2>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream, expert);
+            case 3: return launch_gemv_d<1, 3>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream, expert);
             default: break;
         }
     }
-    if (gemv_mb(M) == 1) return launch_gemv_d<1, 0>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream);
-    return launch_gemv_d<2, 0>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream);
+    if (gemv_mb(M) == 1) return launch_gemv_d<1, 0>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream, expert);
+    return launch_gemv_d<2, 0>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream, expert);
 }
 
 cudaError_t gemv_read_prof(unsigned long long *host_out, size_t bytes) {

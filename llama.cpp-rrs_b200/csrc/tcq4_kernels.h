@@ -30,9 +30,31 @@ struct GemvPlan {
 };
 bool        gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, GemvPlan *plan);
 cudaError_t gemv_init_attributes(size_t smem_optin);
+// MUL_MAT_ID decode: the weight matrix of a launch is chosen ON THE DEVICE, w_tiles + sel[0] * stride, so that the
+// router's output never travels to the host (sel == nullptr: plain MUL_MAT).  An id outside [0, n) sets *err and
+// computes with expert 0 (the reference asserts: ggml-cuda.cu:2357).
+struct GvExpert {
+    const int32_t *sel;
+    long long stride;      // bytes between expert matrices (ggml nb02)
+    int n;
+    int *err;
+    int pdl;               // host side: this launch may use programmatic serialisation (see tcq4_b200_mul_mat_id)
+    // grouped launch (launch_gemv_grouped): ONE launch for all slots of a token.  The kernel sees a virtual matrix of
+    // n_used * N channels; channel block nt belongs to slot nt / nt_expert, whose expert is sel[slot] and whose
+    // activation row is slot % xslots.
+    int xslots;            // activation rows held in shared memory (1 or n_used); 0 = not grouped
+    int nt_expert;         // N / 8 of one expert
+};
+// plan: gemv_plan(x_slots, n_used * N, K); y: [n_used][N] contiguous
+cudaError_t launch_gemv_grouped(const void *w_experts, const float *x, const int32_t *perm, float *y, int64_t n_used,
+                                int64_t N, int64_t K, const GemvPlan &plan, const GvExpert &expert, cudaStream_t stream);
 cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
                         int64_t K, const GemvPlan &plan, float *ws_blob, int *ws_ticket, int32_t *dbg_isum,
-                        cudaStream_t stream);
+                        cudaStream_t stream, const GvExpert *expert = nullptr);
+
+// ---- MUL_MAT_ID row gather / scatter (tcq4_moe.cu) ------------------------------------------------
+cudaError_t launch_copy_rows(const float *src, const int32_t *src_idx, float *dst, const int32_t *dst_idx, int64_t rows,
+                             int64_t cols, int num_sms, cudaStream_t stream);
 
 // ---- K4 / K5: device weight quantiser and GET_ROWS (tcq4_quant.cu) ------------------------------
 cudaError_t launch_quantize_tiles(const float *w, const int32_t *perm, void *tiles, int64_t nrow, int64_t K, int num_sms,

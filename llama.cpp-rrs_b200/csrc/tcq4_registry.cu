@@ -131,6 +131,29 @@ int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq4_tensor_view 
     return tcq4_b200_mul_mat(src0->data, (const float *)src1->data, (float *)dst->data, M, N, K, d_perm, stream);
 }
 
+// ggml_cuda_mul_mat_id (ggml-cuda.cu:2287-2436) for a TCQ4 src0.  Shape rules as there (:2293-2295, 2326-2327) plus the
+// contiguity this library needs; the reference's asserts become status codes.
+int tcq4_b200_ggml_mul_mat_id(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1, const tcq4_tensor_view *ids,
+                              tcq4_tensor_view *dst, int *err_flag, cudaStream_t stream) {
+    if (!src0 || !src1 || !ids || !dst) return TCQ4_ERR_ARG;
+    if (src0->type != TCQ4_B200_GGML_TYPE || src1->type != 0 || dst->type != 0 || ids->type != 26 /* GGML_TYPE_I32 */)
+        return TCQ4_ERR_ARG;
+    const int64_t K = src0->ne[0], N = src0->ne[1], n_expert = src0->ne[2];
+    const int64_t ne11 = src1->ne[1], n_tokens = src1->ne[2];
+    const int64_t n_used = ids->ne[0];
+    if (src1->ne[0] != K || ids->ne[1] != n_tokens || src0->ne[3] != 1 || src1->ne[3] != 1) return TCQ4_ERR_SHAPE;
+    if (dst->ne[0] != N || dst->ne[1] != n_used || dst->ne[2] != n_tokens) return TCQ4_ERR_SHAPE;
+    if (ne11 != 1 && ne11 != n_used) return TCQ4_ERR_SHAPE;
+    if (src0->nb[1] != (size_t)(K / 256) * 148) return TCQ4_ERR_SHAPE;
+    if (src1->nb[0] != 4 || src1->nb[1] != (size_t)K * 4 || src1->nb[2] != (size_t)ne11 * K * 4) return TCQ4_ERR_SHAPE;
+    if (dst->nb[0] != 4 || dst->nb[1] != (size_t)N * 4 || dst->nb[2] != (size_t)n_used * N * 4) return TCQ4_ERR_SHAPE;
+    if (ids->nb[0] != 4 || (ids->nb[1] & 3)) return TCQ4_ERR_SHAPE;
+    const int32_t *d_perm = src0->name ? tcq4_b200_get_perm(src0->name) : nullptr;
+    return tcq4_b200_mul_mat_id(src0->data, n_expert, src0->nb[2], (const float *)src1->data, ne11,
+                                (const int32_t *)ids->data, (int64_t)(ids->nb[1] / 4), n_used, n_tokens, (float *)dst->data, N,
+                                K, d_perm, err_flag, stream);
+}
+
 // ggml_cuda_op_get_rows for a TCQ4 src0 (ggml/src/ggml-cuda/getrows.cu:397-430 -> get_rows_cuda :348-380):
 //   src0 [K, nrows, ne02, ne03] tiles, src1 I32 [ne10, ne11, ne12], dst F32 [K, ne10, ne11, ne12];
 //   slice (i11, i12) of the indices selects rows of slice (i11, i12) of src0 (k_get_rows_tcq4_tile :126).

@@ -1,0 +1,148 @@
+"""MUL_MAT_ID for TCQ4 expert tensors (reference: ggml_cuda_mul_mat_id, ggml-cuda.cu:2287-2436, which sorts rows by
+expert on the host and calls the TCQ4 MUL_MAT once per expert).  The oracle is the MUL_MAT oracle applied per (token, slot) with
+the expert the ids name; on top of that every row must be BIT-IDENTICAL to the plain MUL_MAT of the same expert and batch."""
+import numpy as np
+import pytest
+
+from conftest import make_acts, make_weights, nmse
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def t4():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    import __graft_entry__ as graft
+    return graft.load_package()
+
+
+def _dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _experts(orc, rng, n_expert, N, K, perm=None):
+    Ws = [make_weights(rng, N, K) for _ in range(n_expert)]
+    tiles = [orc.quantize_tiles(orc.apply_perm_weights(W, perm) if perm is not None else W) for W in Ws]
+    return tiles, _dev(np.stack(tiles))                    # device: [n_expert][tile bytes]
+
+
+def _oracle(orc, tiles, x, ids, N, perm=None):
+    n_tokens, x_slots, K = x.shape
+    n_used = ids.shape[1]
+    ref = np.zeros((n_tokens, n_used, N), np.float32)
+    for t in range(n_tokens):
+        for s in range(n_used):
+            ref[t, s] = orc.mul_mat(tiles[int(ids[t, s])], x[t, s % x_slots][None, :], N, perm)["C"][0]
+    return ref
+
+
+@pytest.mark.parametrize("x_slots_full", [False, True])
+def test_decode_one_token_device_routed(t4, orc, x_slots_full):
+    """n_tokens == 1: one GEMV per slot, the expert id is read by the kernel (no host round trip)"""
+    rng = np.random.default_rng(7 + x_slots_full)
+    n_expert, n_used, N, K = 8, 4, 512, 1024
+    perm = np.concatenate([b * 256 + rng.permutation(256) for b in range(K // 256)]).astype(np.int32)
+    tiles, td = _experts(orc, rng, n_expert, N, K, perm)
+    x = make_acts(rng, n_used if x_slots_full else 1, K)[None]          # [1][x_slots][K]
+    ids = rng.permutation(n_expert)[:n_used].astype(np.int32)[None]     # [1][n_used]
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    y = t4.mul_mat_id(td, _dev(x), _dev(ids), N, perm=_dev(perm), err_flag=err)
+    assert err.item() == 0
+    assert nmse(y.cpu().numpy(), _oracle(orc, tiles, x, ids, N, perm)) <= 1e-9
+    for s in range(n_used):
+        plain = t4.mul_mat(td[int(ids[0, s])], _dev(x[0, s % x.shape[1]][None]), N, perm=_dev(perm))
+        assert torch.equal(y[0, s], plain[0]), s
+
+
+def test_decode_is_graph_capturable_and_follows_device_ids(t4, orc):
+    rng = np.random.default_rng(11)
+    n_expert, n_used, N, K = 6, 2, 256, 512
+    tiles, td = _experts(orc, rng, n_expert, N, K)
+    x = make_acts(rng, 1, K)[None]
+    xd = _dev(x)
+    ids_d = torch.zeros((1, n_used), dtype=torch.int32, device="cuda")
+    out = torch.empty((1, n_used, N), dtype=torch.float32, device="cuda")
+    t4.reserve(1, N, K)
+    t4.mul_mat_id(td, xd, ids_d, N, out=out)                            # warm-up outside capture
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        with torch.cuda.graph(g, stream=s):
+            t4.mul_mat_id(td, xd, ids_d, N, out=out)
+    for pick in ([5, 1], [0, 3], [2, 2]):
+        ids = np.array([pick], np.int32)
+        ids_d.copy_(_dev(ids))                                          # the router's output changes ON THE DEVICE only
+        g.replay()
+        torch.cuda.synchronize()
+        assert nmse(out.cpu().numpy(), _oracle(orc, tiles, x, ids, N)) <= 1e-9, pick
+
+
+def test_decode_bad_expert_id_sets_flag(t4, orc):
+    rng = np.random.default_rng(12)
+    tiles, td = _experts(orc, rng, 2, 64, 256)
+    x = _dev(make_acts(rng, 1, 256)[None])
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    t4.mul_mat_id(td, x, _dev(np.array([[1, 7]], np.int32)), 64, err_flag=err)
+    torch.cuda.synchronize()
+    assert err.item() == 1
+
+
+@pytest.mark.parametrize("x_slots_full", [False, True])
+def test_prefill_sorted_by_expert(t4, orc, x_slots_full):
+    """n_tokens > 1: rows counting-sorted by expert; expert 0 gets > 16 rows (tcgen05 GEMM), others <= 16 (GEMV), one none"""
+    rng = np.random.default_rng(21 + x_slots_full)
+    n_expert, n_used, n_tokens, N, K = 5, 2, 24, 256, 512
+    tiles, td = _experts(orc, rng, n_expert, N, K)
+    ids = np.zeros((n_tokens, n_used), np.int32)
+    for t in range(n_tokens):
+        ids[t, 0] = 0 if t < 20 else 1                                  # 20 rows for expert 0
+        ids[t, 1] = 1 + (t % 3)                                         # experts 1..3; expert 4 never used
+    x = np.stack([make_acts(rng, n_used if x_slots_full else 1, K) for _ in range(n_tokens)])
+    y = t4.mul_mat_id(td, _dev(x), _dev(ids), N)
+    assert nmse(y.cpu().numpy(), _oracle(orc, tiles, x, ids, N)) <= 1e-9
+    # bit-identical to the plain MUL_MAT of each expert over its rows in (token, slot) order
+    for e in range(n_expert):
+        rows = [(t, s) for t in range(n_tokens) for s in range(n_used) if ids[t, s] == e]
+        if not rows:
+            continue
+        xe = np.stack([x[t, s % x.shape[1]] for t, s in rows])
+        plain = t4.mul_mat(td[e], _dev(xe), N)
+        got = torch.stack([y[t, s] for t, s in rows])
+        assert torch.equal(got, plain), e
+
+
+def test_prefill_strided_ids_and_ggml_mirror_with_registered_perm(t4, orc):
+    """ids as a view of a wider [n_tokens][n_expert] top-k tensor (ggml nb[1] > n_used * 4); perm looked up by tensor name"""
+    rng = np.random.default_rng(31)
+    n_expert, n_used, n_tokens, N, K = 4, 2, 9, 128, 512
+    name = "blk.3.ffn_up_exps.weight"
+    perm = np.concatenate([b * 256 + rng.permutation(256) for b in range(K // 256)]).astype(np.int32)
+    tiles, td = _experts(orc, rng, n_expert, N, K, perm)
+    wide = np.stack([rng.permutation(n_expert) for _ in range(n_tokens)]).astype(np.int32)
+    wide_d = _dev(wide)
+    ids_view = wide_d[:, :n_used]                                       # stride(0) = n_expert
+    x = np.stack([make_acts(rng, 1, K) for _ in range(n_tokens)])
+    ref = _oracle(orc, tiles, x, wide[:, :n_used], N, perm)
+    y = t4.mul_mat_id(td, _dev(x), ids_view, N, perm=_dev(perm))
+    assert nmse(y.cpu().numpy(), ref) <= 1e-9
+    t4.clear_perms()
+    t4.set_reorder_enabled(True)
+    t4.register_perm(name, perm)
+    try:
+        y2 = t4.ggml_mul_mat_id(td, _dev(x), ids_view, N, name=name)
+        assert torch.equal(y2, y)
+    finally:
+        t4.clear_perms()
+
+
+def test_prefill_bad_expert_id_is_an_error(t4, orc):
+    rng = np.random.default_rng(41)
+    tiles, td = _experts(orc, rng, 2, 64, 256)
+    x = _dev(np.stack([make_acts(rng, 1, 256) for _ in range(3)]))
+    with pytest.raises(Exception, match="expert id"):
+        t4.mul_mat_id(td, x, _dev(np.array([[0], [2], [1]], np.int32)), 64)
+    with pytest.raises(Exception):
+        t4.mul_mat_id(td, x, _dev(np.array([[0], [-1], [1]], np.int32)), 64)
