@@ -423,7 +423,7 @@ int tcq4_b200_mul_mat_id(const void *w_experts, int64_t n_expert, size_t expert_
     if (!d) return status;
     const int64_t R = n_tokens * n_used;
     tcq4::GemvPlan gv;
-    static const bool no_group = getenv("TCQ4_MOE_GROUP") == nullptr;        // grouped launch: opt-in until verified on the GPU
+    static const bool no_group = getenv("TCQ4_MOE_NOGROUP") != nullptr;      // diagnostics / tests: one launch per slot
     if (n_tokens == 1 && !no_group && tcq4::gemv_plan(x_slots, n_used * N, K, d->num_sms, d->smem_optin, &gv)) {
         // ONE launch for all slots: a GEMV over the virtual [n_used * N][K] matrix (launch_gemv_grouped)
         const tcq4::GvExpert ex{ids, (long long)expert_stride_bytes, (int)n_expert, err_flag, 0, (int)x_slots, (int)(N / 8)};

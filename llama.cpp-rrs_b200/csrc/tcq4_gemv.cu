@@ -261,10 +261,12 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
         for (int i = 0; i < depth; i++) mbar_init(&myfull[i], 1);
         fence_mbar_init();
         pol = l2_policy_evict_first();
-        const int pre = cnt < depth ? cnt : depth;
-        for (int i = 0; i < pre; i++) {
-            mbar_arrive_expect_tx(&myfull[i], TILE_BYTES);
-            bulk_g2s_stream(myring + i * TILE_BYTES, tile_src(i), TILE_BYTES, &myfull[i], pol);
+        if (!GROUP) {
+            const int pre = cnt < depth ? cnt : depth;
+            for (int i = 0; i < pre; i++) {
+                mbar_arrive_expect_tx(&myfull[i], TILE_BYTES);
+                bulk_g2s_stream(myring + i * TILE_BYTES, tile_src(i), TILE_BYTES, &myfull[i], pol);
+            }
         }
     }
     __syncwarp();
@@ -276,6 +278,13 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                                  // the activation stage or after the loop -- measured 3-20 % slower)
     pdl_wait();                  // x belongs to the previous kernel until here
     GV_STAMP(2);
+    if (GROUP && lane == 0) {    // the ids may come from the kernel just before this one: first copies only now
+        const int pre = cnt < depth ? cnt : depth;
+        for (int i = 0; i < pre; i++) {
+            mbar_arrive_expect_tx(&myfull[i], TILE_BYTES);
+            bulk_g2s_stream(myring + i * TILE_BYTES, tile_src(i), TILE_BYTES, &myfull[i], pol);
+        }
+    }
 
     // ---- activation stage for all M rows -----------------------------------------------------------------
     // (latency-bound here -- at most a few 256-blocks per warp -- so the all-shuffle butterfly, whose dependent
@@ -784,8 +793,8 @@ cudaError_t gemv_init_attributes(size_t smem_optin) {
 }
 
 // MUL_MAT_ID for one token as ONE launch: a GEMV over the virtual matrix of n_used * N channels whose channel blocks
-// take their weight tiles from the expert the ids name (GvExpert, tcq4_kernels.h).  Launched in plain stream order: the
-// ids are read at kernel entry.
+// take their weight tiles from the expert the ids name (GvExpert, tcq4_kernels.h).  The ids are read behind
+// griddepcontrol.wait (they may be the previous kernel's output), so only the set-up overlaps the previous launch.
 cudaError_t launch_gemv_grouped(const void *w_experts, const float *x, const int32_t *perm, float *y, int64_t n_used,
                                 int64_t N, int64_t K, const GemvPlan &plan, const GvExpert &expert, cudaStream_t stream) {
     if (expert.sel == nullptr || expert.xslots < 1 || expert.nt_expert != (int)(N / TILE_CH)) return cudaErrorInvalidValue;
@@ -794,13 +803,16 @@ cudaError_t launch_gemv_grouped(const void *w_experts, const float *x, const int
     cfg.blockDim = dim3((unsigned)plan.warps * 32);
     cfg.dynamicSmemBytes = plan.smem_bytes;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = GV_CLUSTER;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;      // safe: the ids are read behind griddepcontrol.wait
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    static const bool pdl = getenv("TCQ4_NO_PDL") == nullptr;
+    cfg.numAttrs = pdl ? 2 : 1;
     YOut yo;
     for (int i = 0; i < MAX_PEERS; i++) yo.p[i] = y;
     yo.n = 1;

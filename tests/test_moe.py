@@ -146,3 +146,18 @@ def test_prefill_bad_expert_id_is_an_error(t4, orc):
         t4.mul_mat_id(td, x, _dev(np.array([[0], [2], [1]], np.int32)), 64)
     with pytest.raises(Exception):
         t4.mul_mat_id(td, x, _dev(np.array([[0], [-1], [1]], np.int32)), 64)
+
+
+def test_decode_per_slot_fallback_in_a_child_process():
+    """TCQ4_MOE_NOGROUP=1 (read once at load, hence the child): one GEMV per slot instead of the grouped launch -- the path
+    taken when the slots' activation rows do not fit the GEMV's shared memory.  Same decode tests, same bar."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("TCQ4_MOE_NOGROUP"):
+        pytest.skip("already the child")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, TCQ4_MOE_NOGROUP="1")
+    out = subprocess.run([sys.executable, "-m", "pytest", "tests/test_moe.py", "-m", "gpu", "-q", "-x", "-k", "decode and not child"],
+                         cwd=root, env=env, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and " passed" in out.stdout, out.stdout[-3000:] + out.stderr[-2000:]
