@@ -95,6 +95,13 @@ TCQ4_B200_API int tcq4_b200_mul_mat(const void *w_tiles, const float *x, float *
                                     cudaStream_t stream);
 TCQ4_B200_API int tcq4_b200_reserve(int64_t max_M, int64_t max_N, int64_t max_K);
 
+/* Fan-out: n <= 8 weight matrices applied to the SAME activations x [M][K] (Q/K/V, gate/up: consecutive
+ * MUL_MAT nodes of the ggml graph that share src1; the fusion hook is ggml-cuda.cu:3481-3688).  y[i] = F32 [M][N[i]].
+ * The activation stage runs once; results are bit-identical to n separate tcq4_b200_mul_mat calls with the same perm. */
+TCQ4_B200_API int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N, float *const *y,
+                                           const float *x, int64_t M, int64_t K, const int32_t *d_perm,
+                                           cudaStream_t stream);
+
 /* MUL_MAT_ID, the mixture-of-experts form of the same operator: replaces ggml_cuda_mul_mat_id
  * (ggml-cuda.cu:2287-2436) for a TCQ4 src0, which the reference admits in supports_op (:4457-4459) and serves through
  * its generic path (ids to the host, rows sorted by expert, one ggml_cuda_mul_mat per expert).

@@ -15,7 +15,7 @@ import torch
 from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
                ACT_BLOCK_BYTES, TensorView, _check, quantize_size, shard_range, tile_bytes, workspace_size)
 
-__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
+__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
            "ggml_supports_op", "ShardedWeight", "random_tiles", "quantize_tiles", "get_rows", "ggml_get_rows"]
 
@@ -252,6 +252,32 @@ def ggml_get_rows(w_tiles: torch.Tensor, idx: torch.Tensor, nrows: int, K: int, 
     ef = err_flag.data_ptr() if err_flag is not None else 0
     _check(LIB.tcq4_b200_ggml_get_rows(C.byref(src0), C.byref(src1), C.byref(dst), ef, _stream_ptr(stream)))
     return out
+
+
+class Fanout:
+    """Several weight matrices over the same activations (Q/K/V, gate/up): tcq4_b200_mul_mat_fanout.  The pointer
+    tables are built once; call with x (and optionally the outputs of the first call) as often as needed."""
+
+    def __init__(self, w_tiles: list, Ns: list, K: int):
+        for w, N in zip(w_tiles, Ns):
+            _req_cuda(w, torch.uint8, "w_tiles")
+            if w.numel() != tile_bytes(N, K):
+                raise ValueError(f"w_tiles has {w.numel()} bytes, expected {tile_bytes(N, K)} for N={N} K={K}")
+        self.n, self.K, self.Ns, self._keep = len(Ns), K, list(Ns), list(w_tiles)
+        self._w = (C.c_void_p * self.n)(*[w.data_ptr() for w in w_tiles])
+        self._N = (C.c_int64 * self.n)(*Ns)
+
+    def __call__(self, x: torch.Tensor, outs: list | None = None, perm: torch.Tensor | None = None, stream=None) -> list:
+        _req_cuda(x, torch.float32, "x")
+        M, K = x.shape
+        if K != self.K:
+            raise ValueError("x has the wrong K")
+        if outs is None:
+            outs = [torch.empty((M, N), dtype=torch.float32, device=x.device) for N in self.Ns]
+        y = (C.c_void_p * self.n)(*[o.data_ptr() for o in outs])
+        pp = perm.data_ptr() if perm is not None else 0
+        _check(LIB.tcq4_b200_mul_mat_fanout(self.n, self._w, self._N, y, x.data_ptr(), M, K, pp, _stream_ptr(stream)))
+        return outs
 
 
 def mul_mat_id(w_experts: torch.Tensor, x: torch.Tensor, ids: torch.Tensor, N: int, perm: torch.Tensor | None = None,

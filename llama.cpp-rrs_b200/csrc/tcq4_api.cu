@@ -165,8 +165,11 @@ tcq4::YOut single_out(float *y, int64_t N) {
     return o;
 }
 
+// N_layout / reuse_act (fan-out, tcq4_b200_mul_mat_fanout): several weight matrices applied to the SAME activations share
+// one workspace layout (that of the widest matrix) and the GEMMs after the first skip the activation kernel.
 int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t N, int64_t K, const int32_t *perm,
-                void *ws, size_t ws_bytes, int kernel, int32_t *dbg_isum, cudaStream_t stream) {
+                void *ws, size_t ws_bytes, int kernel, int32_t *dbg_isum, cudaStream_t stream, int64_t N_layout = 0,
+                bool reuse_act = false, bool *act_done = nullptr) {
     float *y = yo.p[0];
     const bool plain = (yo.n == 1 && yo.ldc == N && !yo.mc);     // ggml's dst; otherwise strided / several destinations
     if (!shape_ok(M, N, K)) {
@@ -191,7 +194,7 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
     int status;
     DevInfo *d = current_device(&status);
     if (!d) return status;
-    const WsLayout L = ws_layout(M, N, K);
+    const WsLayout L = ws_layout(M, N_layout > N ? N_layout : N, K);
     if (!ws || ((uintptr_t)ws & 255) || ws_bytes < L.total) {
         set_err("workspace too small or misaligned: need %zu bytes (256-aligned), got %zu", L.total, ws_bytes);
         return TCQ4_ERR_WORKSPACE;
@@ -250,10 +253,11 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
     static const bool want_fuse = getenv("TCQ4_G2_FUSE") != nullptr;
     const bool fuse = (k == TCQ4_KERNEL_GEMM2) && want_fuse && plain && L.ticket_bytes >= 8;
     cudaError_t e = cudaSuccess;
-    if (!fuse) {
+    if (!fuse && !reuse_act) {
         e = tcq4::launch_act_quant_stage(x, perm, M, K, st, d->num_sms, stream);
         if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
     }
+    if (act_done) *act_done = !fuse;         // the codes of x now sit in the workspace
     if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
     if (k == TCQ4_KERNEL_GEMM2) {
         tcq4::Gemm2Plan g2;
@@ -271,7 +275,7 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
         cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
         g_prof.kind[g_prof.n++] = k;
     }
-    g_launches.fetch_add(2, std::memory_order_relaxed);
+    g_launches.fetch_add((!fuse && !reuse_act) ? 2 : 1, std::memory_order_relaxed);
     return TCQ4_OK;
 }
 
@@ -387,6 +391,41 @@ int tcq4_b200_mul_mat(const void *w_tiles, const float *x, float *y, int64_t M, 
     if (status != TCQ4_OK) return status;
     return run_mul_mat(w_tiles, x, single_out(y, N), M, N, K, d_perm, d->arena, d->arena_bytes, TCQ4_KERNEL_AUTO, nullptr,
                        stream);
+}
+
+// Fan-out (graph-level fusion): n weight matrices applied to the SAME activations -- Q/K/V and gate/up of a
+// transformer layer are consecutive MUL_MAT nodes with one src1 (the hook is where ggml-cuda tries its other fusions,
+// ggml-cuda.cu:3481-3688).  The activation stage (perm + FWHT + int4 quantisation, K1) runs ONCE; every GEMM after the
+// first reads the codes already in the workspace.  Results are bit-identical to n separate tcq4_b200_mul_mat calls.
+// All matrices must share the channel permutation (they do when it derives from the imatrix of their common input).
+int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *Ns, float *const *ys, const float *x, int64_t M,
+                             int64_t K, const int32_t *d_perm, cudaStream_t stream) {
+    if (n < 1 || n > 8 || !w_tiles || !Ns || !ys) {
+        set_err("mul_mat_fanout: 1..8 weight matrices");
+        return TCQ4_ERR_ARG;
+    }
+    int64_t Nmax = 0;
+    for (int i = 0; i < n; i++) {
+        if (!shape_ok(M, Ns[i], K)) {
+            set_err("unsupported shape M=%lld N=%lld K=%lld", (long long)M, (long long)Ns[i], (long long)K);
+            return TCQ4_ERR_SHAPE;
+        }
+        Nmax = std::max(Nmax, Ns[i]);
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    status = arena_ensure(d, ws_layout(M, Nmax, K).total, stream);
+    if (status != TCQ4_OK) return status;
+    bool have_codes = false;
+    for (int i = 0; i < n; i++) {
+        bool done = false;
+        status = run_mul_mat(w_tiles[i], x, single_out(ys[i], Ns[i]), M, Ns[i], K, d_perm, d->arena, d->arena_bytes,
+                             TCQ4_KERNEL_AUTO, nullptr, stream, Nmax, have_codes, &done);
+        if (status != TCQ4_OK) return status;
+        have_codes = have_codes || done;
+    }
+    return TCQ4_OK;
 }
 
 // MUL_MAT_ID (ggml_mul_mat_id: dst[tok][slot][:] = W[ids[tok][slot]] * x[tok][slot % x_slots][:]), the operator the

@@ -39,8 +39,20 @@ def layer_chain(M, layers=int(os.environ.get('LAYERS', '36'))):
     x = {k: torch.randn((M, k), device="cuda") for k in (2560, 4096, 9728)}
     y = {n: torch.empty((M, n), device="cuda") for n in (4096, 1024, 2560, 9728)}
     ws = t4.Workspace.for_shape(M, 9728, 9728)
+    fan = os.environ.get("FANOUT")                 # q/k/v and gate/up share their activations: one activation stage each
+    if fan:
+        yk, yv, yu = torch.empty_like(y[1024]), torch.empty_like(y[1024]), torch.empty_like(y[9728])
+        qkv = [t4.Fanout([W[l][0], W[l][1], W[l][2]], [4096, 1024, 1024], 2560) for l in range(layers)]
+        gu = [t4.Fanout([W[l][4], W[l][5]], [9728, 9728], 2560) for l in range(layers)]
+        t4.reserve(M, 9728, 9728)
     def chain():
         for l in range(layers):
+            if fan:
+                qkv[l](x[2560], outs=[y[4096], yk, yv])
+                t4.mul_mat(W[l][3], x[4096], 2560, out=y[2560])
+                gu[l](x[2560], outs=[y[9728], yu])
+                t4.mul_mat(W[l][6], x[9728], 2560, out=y[2560])
+                continue
             for j, (n, k) in enumerate(shapes):
                 t4.mul_mat(W[l][j], x[k], n, out=y[n], workspace=ws)
     for _ in range(2): chain()
