@@ -339,6 +339,92 @@ class Chain:
             self.step_eager()
 
 
+class FanoutChain:
+    """The same 252 matmuls with the graph-level fusion of SURVEY 8 f4: q/k/v and gate/up share their activations, so each
+    group is ONE tcq4_b200_mul_mat_fanout call (one activation stage at prefill, one GEMV launch at decode).  Single GPU."""
+
+    def __init__(self, t4, torch, M, base):
+        self.t4, self.torch, self.M = t4, torch, M
+        self.x = base.x
+        L = len(QWEN3_4B_LAYER)
+        self.layers = []
+        for l in range(QWEN3_4B_LAYERS):
+            w = base.weights[l * L:(l + 1) * L]
+            byname = {name: w[j] for j, (name, _, _) in enumerate(QWEN3_4B_LAYER)}
+            self.layers.append((w, byname))
+        names = [n for n, _, _ in QWEN3_4B_LAYER]
+        self.groups = []                                # per layer: list of ("fan", Fanout, K, outs) | ("one", weight, out)
+        y = {n: torch.empty((M, N), device="cuda") for n, N, _ in QWEN3_4B_LAYER}
+        self.y = y
+        fan_sets = [s for s in (("attn_q", "attn_k", "attn_v"), ("ffn_gate", "ffn_up")) if all(n in names for n in s)]
+        for w, byname in self.layers:
+            ops, done = [], set()
+            for n, N, K in QWEN3_4B_LAYER:
+                if n in done:
+                    continue
+                fs = next((s for s in fan_sets if n in s), None)
+                if fs:
+                    ws = [byname[m] for m in fs]
+                    ops.append(("fan", t4.Fanout([v.tiles for v in ws], [v.N for v in ws], K), K, [y[m] for m in fs]))
+                    done.update(fs)
+                else:
+                    ops.append(("one", byname[n], K, y[n]))
+            self.groups.append(ops)
+        t4.reserve(M, max(N for _, N, _ in QWEN3_4B_LAYER), max(K for _, _, K in QWEN3_4B_LAYER))
+        for fs in fan_sets:                             # the segmented decode launch plans over the summed channels
+            t4.reserve(M, sum(N for n, N, _ in QWEN3_4B_LAYER if n in fs), max(K for n, _, K in QWEN3_4B_LAYER if n in fs))
+        self.graph = None
+
+    def step_eager(self):
+        for ops in self.groups:
+            for kind, a, K, out in ops:
+                if kind == "fan":
+                    a(self.x[K], outs=out)
+                else:
+                    self.t4.mul_mat(a.tiles, self.x[K], a.N, out=out)
+
+    def capture(self):
+        torch = self.torch
+        c0 = self.t4.launch_count()
+        self.step_eager()
+        self.launches_per_step = self.t4.launch_count() - c0
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            with torch.cuda.graph(g, stream=s):
+                self.step_eager()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        self.graph = g
+
+    def step(self):
+        self.graph.replay()
+
+
+def fanout_leg(t4, torch, pre, dec, steps, warmup):
+    """graph-level fusion on top of the headline path (reported beside it, never instead of it); outputs checked
+    against the per-node path on the last layer (prefill: bit-identical; decode: the fp32 sum over 256-blocks is cut between
+    warps at other places in the segmented launch, same int32 accumulators)"""
+    out = {"what": "q/k/v and gate/up of each layer through tcq4_b200_mul_mat_fanout (shared activation stage at prefill, one "
+                   "segmented GEMV launch at decode); the headline numbers above stay on one call per MUL_MAT node"}
+    for key, base, M, n in (("prefill", pre, pre.M, steps), ("decode", dec, 1, max(steps, 20))):
+        fc = FanoutChain(t4, torch, M, base)
+        fc.capture()
+        ms = timed_steps(torch, None, fc, n, max(warmup, 3), 1)
+        w, _ = fc.layers[-1]
+        same, worst = True, 0.0
+        for j, (name, N, K) in enumerate(QWEN3_4B_LAYER):
+            ref = t4.mul_mat(w[j].tiles, fc.x[K], N)
+            same = same and bool(torch.equal(ref, fc.y[name]))
+            worst = max(worst, float(((ref - fc.y[name]).double() ** 2).sum() / (ref.double() ** 2).sum()))
+        out[key] = {"ms_per_step": ms, "value": M / (ms * 1e-3), "unit": UNIT, "launches_per_step": int(fc.launches_per_step),
+                    "bit_identical_to_per_node": same, "nmse_vs_per_node": worst}
+        del fc
+    return out
+
+
 def timed_steps(torch, dist, chain, steps, warmup, world):
     """W untimed steps, then exactly K steps between barrier + synchronize, CUDA events, max over ranks."""
     for _ in range(warmup):
@@ -568,6 +654,11 @@ def run_own_arm(args):
                 "value": M / (ms_step_ng * 1e-3), "unit": UNIT, "ms_per_step": ms_step_ng,
                 "tops": total_ops / (ms_step_ng * 1e-3) / 1e12,
                 "decode": {"value": 1.0 / (ms_dec_ng * 1e-3), "unit": UNIT, "ms_per_step": ms_dec_ng}}
+        if world == 1:
+            try:
+                line["graph_fusion"] = fanout_leg(t4, torch, pre, dec, args.steps, args.warmup)
+            except Exception as e:  # noqa: BLE001
+                line["graph_fusion"] = {"error": f"{type(e).__name__}: {e}"}
         if world == 1 and not args.no_cpu_baseline:
             try:
                 line["cpu_baseline"] = cpu_baseline_leg()

@@ -97,7 +97,9 @@ TCQ4_B200_API int tcq4_b200_reserve(int64_t max_M, int64_t max_N, int64_t max_K)
 
 /* Fan-out: n <= 8 weight matrices applied to the SAME activations x [M][K] (Q/K/V, gate/up: consecutive
  * MUL_MAT nodes of the ggml graph that share src1; the fusion hook is ggml-cuda.cu:3481-3688).  y[i] = F32 [M][N[i]].
- * The activation stage runs once; results are bit-identical to n separate tcq4_b200_mul_mat calls with the same perm. */
+ * M > 16: the activation stage runs once and the GEMMs follow; bit-identical to n separate tcq4_b200_mul_mat calls with
+ * the same perm.  M <= 16 and n <= 4: ONE GEMV launch over all matrices (same int32 accumulators; the fp32 sum over a
+ * channel's 256-blocks may be split differently, i.e. last-bit differences against separate calls). */
 TCQ4_B200_API int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N, float *const *y,
                                            const float *x, int64_t M, int64_t K, const int32_t *d_perm,
                                            cudaStream_t stream);

@@ -396,7 +396,9 @@ int tcq4_b200_mul_mat(const void *w_tiles, const float *x, float *y, int64_t M, 
 // Fan-out (graph-level fusion): n weight matrices applied to the SAME activations -- Q/K/V and gate/up of a
 // transformer layer are consecutive MUL_MAT nodes with one src1 (the hook is where ggml-cuda tries its other fusions,
 // ggml-cuda.cu:3481-3688).  The activation stage (perm + FWHT + int4 quantisation, K1) runs ONCE; every GEMM after the
-// first reads the codes already in the workspace.  Results are bit-identical to n separate tcq4_b200_mul_mat calls.
+// first reads the codes already in the workspace: bit-identical to n separate tcq4_b200_mul_mat calls.  With a decode
+// batch (M <= 16) all matrices run as ONE GEMV launch: same int32 accumulators per 256-block; the fp32 sum over a
+// channel's blocks may be cut between warps at other places than in a separate launch (last-bit differences).
 // All matrices must share the channel permutation (they do when it derives from the imatrix of their common input).
 int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *Ns, float *const *ys, const float *x, int64_t M,
                              int64_t K, const int32_t *d_perm, cudaStream_t stream) {
@@ -415,6 +417,42 @@ int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N
     int status;
     DevInfo *d = current_device(&status);
     if (!d) return status;
+    // decode batch (M <= 16): ONE GEMV launch over the sum(N_i) channels of all matrices (SEG mode of tcq4_gemv_kernel:
+    // a channel block takes its tiles from, and stores to, the matrix it belongs to) -- a decode MUL_MAT costs a fixed
+    // ~4.5 us per launch, so Q/K/V in one launch is worth more than the shared activation stage
+    int64_t Nsum = 0;
+    for (int i = 0; i < n; i++) Nsum += Ns[i];
+    tcq4::GemvPlan gv;
+    static const bool no_seg = getenv("TCQ4_FANOUT_NOSEG") != nullptr;       // diagnostics / tests: one launch per matrix
+    if (n >= 2 && n <= tcq4::GV_MAX_SEG && !no_seg && shape_ok(M, Nsum, K) &&
+        tcq4::gemv_plan(M, Nsum, K, d->num_sms, d->smem_optin, &gv)) {
+        tcq4::GvExpert ex{};
+        ex.pdl = 1;
+        ex.nseg = n;
+        for (int i = 0; i < n; i++) {
+            if (!w_tiles[i] || !ys[i] || ((uintptr_t)w_tiles[i] & 15) || ((uintptr_t)ys[i] & 15)) {
+                set_err("mul_mat_fanout: null or misaligned pointer of matrix %d", i);
+                return TCQ4_ERR_ARG;
+            }
+            ex.seg_w[i] = reinterpret_cast<const uint8_t *>(w_tiles[i]);
+            ex.seg_y[i] = ys[i];
+            ex.seg_nt0[i + 1] = ex.seg_nt0[i] + (int)(Ns[i] / 8);
+        }
+        if (!x || ((uintptr_t)x & 15) || (d_perm && ((uintptr_t)d_perm & 15))) {
+            set_err("mul_mat_fanout: null or misaligned x / perm");
+            return TCQ4_ERR_ARG;
+        }
+        const WsLayout L = ws_layout(M, Nsum, K);
+        status = arena_ensure(d, L.total, stream);
+        if (status != TCQ4_OK) return status;
+        uint8_t *wsb = reinterpret_cast<uint8_t *>(d->arena);
+        float *blob = gv.blob_bytes <= L.partial_bytes ? reinterpret_cast<float *>(wsb + L.partial_off) : nullptr;
+        cudaError_t e = tcq4::launch_gemv(nullptr, x, d_perm, single_out(ys[0], Nsum), M, Nsum, K, gv, blob,
+                                          reinterpret_cast<int *>(wsb + L.ticket_off), nullptr, stream, &ex);
+        if (e != cudaSuccess) return cuda_fail(e, "fan-out gemv launch");
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        return TCQ4_OK;
+    }
     status = arena_ensure(d, ws_layout(M, Nmax, K).total, stream);
     if (status != TCQ4_OK) return status;
     bool have_codes = false;

@@ -177,7 +177,7 @@ tcq4_gemv_prepass_kernel(const float *__restrict__ x, const int32_t *__restrict_
 // MT > 0 selects the dp4a inner loop for exactly MT <= 3 tokens (at 4 the IMMA loop is faster: 14.9 vs 17.7 us at
 // N=14336, K=4096) (see "dp4a path" below); MT = 0 the IMMA loop for
 // up to 8 * MB tokens.
-template <int MB, int MT, bool DEBUG, bool GROUP = false>
+template <int MB, int MT, bool DEBUG, int MODE = 0>
 __global__ void __launch_bounds__(512, (MT == 1 && !DEBUG) ? 2 : 1)
 tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, const int32_t *__restrict__ perm,
                  const YOut out, int M, int N, int K, int depth, const uint8_t *__restrict__ pre_blob,
@@ -192,6 +192,8 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     const int workers = NW * GV_CLUSTER, entries = workers * 2;
     // GROUP (MUL_MAT_ID, one token): M = 1 token is computed per channel, but Ma activation rows (one per slot) may sit
     // in shared memory; N is the virtual channel count n_used * N_expert
+    // MODE: 0 plain, 1 GROUP (MUL_MAT_ID, below), 2 SEG (fan-out: channel blocks of several weight matrices, same x)
+    constexpr bool GROUP = (MODE == 1), SEG = (MODE == 2);
     static_assert(!GROUP || (MB == 1 && MT == 1), "grouped launches use the one-token dp4a loop");
     const int Ma = GROUP ? ex.xslots : M;
     const GvSmem L(Ma, KT, NW, depth);
@@ -231,7 +233,13 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     const uint8_t *wsrc = w + ((size_t)R0 * KT + lt0) * TILE_BYTES;
     // weight tile i of this warp.  Plain: tiles are in memory order.  GROUP: the slot's expert comes from the ids
     auto tile_src = [&](int i) -> const uint8_t * {
-        if constexpr (!GROUP) {
+        if constexpr (SEG) {
+            const int g = lt0 + i, rr = g / KT;
+            const int row = R0 + rr, k = g - rr * KT;
+            int si = 0;
+            while (si + 1 < ex.nseg && row >= ex.seg_nt0[si + 1]) si++;
+            return ex.seg_w[si] + ((size_t)(row - ex.seg_nt0[si]) * KT + k) * TILE_BYTES;
+        } else if constexpr (!GROUP) {
             return wsrc + (size_t)i * TILE_BYTES;
         } else {
             const int g = lt0 + i, rr = g / KT;
@@ -245,7 +253,20 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
             return w + (size_t)e * (size_t)ex.stride + ((size_t)(row - s * ex.nt_expert) * KT + k) * TILE_BYTES;
         }
     };
-    if (!GROUP && ex.sel != nullptr) {
+    // y[m][row * 8 + ch] = v.  SEG: the row's own matrix and its own [M][N_i] output
+    auto store_out = [&](int m, int row, int ch, float v) {
+        if constexpr (SEG) {
+            int si = 0;
+            while (si + 1 < ex.nseg && row >= ex.seg_nt0[si + 1]) si++;
+            const int ni = (ex.seg_nt0[si + 1] - ex.seg_nt0[si]) * 8;
+            ex.seg_y[si][(size_t)m * ni + (row - ex.seg_nt0[si]) * 8 + ch] = v;
+        } else {
+            if (out.mc) multimem_st_f32(out.mc + (size_t)m * out.ldc + row * 8 + ch, v);
+            else
+                for (int pi = 0; pi < out.n; pi++) out.p[pi][(size_t)m * out.ldc + row * 8 + ch] = v;
+        }
+    };
+    if (MODE == 0 && ex.sel != nullptr) {
         // MUL_MAT_ID: this launch's expert matrix.  The id comes from an earlier kernel of the stream (the router) and is
         // read here, ahead of griddepcontrol.wait: the first slot's launch is made without programmatic serialisation (it
         // starts after the router has completed), the later ones start no earlier than the first one has.
@@ -427,9 +448,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                 if (lane < 8) {
 #pragma unroll
                     for (int m = 0; m < MT; m++) {
-                        if (out.mc) multimem_st_f32(out.mc + (size_t)m * out.ldc + nt * 8 + cc, accd[m]);
-                        else
-                            for (int pi = 0; pi < out.n; pi++) out.p[pi][(size_t)m * out.ldc + nt * 8 + cc] = accd[m];
+                        store_out(m, nt, cc, accd[m]);
                     }
                 }
             } else {                                    // a cut row: park the partial in CTA 0's shared memory
@@ -487,7 +506,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(TILE_BYTES) : "memory");
                 asm volatile(
                     "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
-                        "r"(dst), "l"(wsrc + (size_t)(i + depth) * TILE_BYTES), "r"(TILE_BYTES), "r"(bar), "l"(pol)
+                        "r"(dst), "l"(tile_src(i + depth)), "r"(TILE_BYTES), "r"(bar), "l"(pol)
                     : "memory");
             }
         }
@@ -549,12 +568,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                 for (int mb = 0; mb < MB; mb++)
 #pragma unroll
                     for (int j = 0; j < 2; j++)
-                        if (8 * mb + tk0 + j < M) {
-                            if (out.mc) multimem_st_f32(out.mc + (size_t)(8 * mb + tk0 + j) * out.ldc + nt * 8 + c, acc[mb][j]);
-                            else
-                                for (int pi = 0; pi < out.n; pi++)
-                                    out.p[pi][(size_t)(8 * mb + tk0 + j) * out.ldc + nt * 8 + c] = acc[mb][j];
-                        }
+                        if (8 * mb + tk0 + j < M) store_out(8 * mb + tk0 + j, nt, c, acc[mb][j]);
             } else {                                    // a cut row: park the partial in CTA 0's shared memory
                 const int e = wid * 2 + nseg;
 #pragma unroll
@@ -617,9 +631,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                     if (pr != row) break;
                     sum += part[(size_t)(j * M + m) * 8 + c8];
                 }
-                if (out.mc) multimem_st_f32(out.mc + (size_t)m * out.ldc + row * 8 + c8, sum);
-                else
-                    for (int pi = 0; pi < out.n; pi++) out.p[pi][(size_t)m * out.ldc + row * 8 + c8] = sum;
+                store_out(m, row, c8, sum);
             }
         }
     } else if (crank == 0) {
@@ -662,11 +674,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                     float v = s2[m];
                     v += __shfl_xor_sync(0xffffffffu, v, 8);
                     v += __shfl_xor_sync(0xffffffffu, v, 16);
-                    if (jj == 0) {
-                        if (out.mc) multimem_st_f32(out.mc + (size_t)m * out.ldc + row * 8 + c8, v);
-                        else
-                            for (int pi = 0; pi < out.n; pi++) out.p[pi][(size_t)m * out.ldc + row * 8 + c8] = v;
-                    }
+                    if (jj == 0) store_out(m, row, c8, v);
                 }
                 continue;
             }
@@ -679,9 +687,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
                     if (pr != row) break;
                     sum += part[(size_t)(j * M + m) * 8 + (lane & 7)];
                 }
-                if (out.mc) multimem_st_f32(out.mc + (size_t)m * out.ldc + row * 8 + (lane & 7), sum);
-                else
-                    for (int pi = 0; pi < out.n; pi++) out.p[pi][(size_t)m * out.ldc + row * 8 + (lane & 7)] = sum;
+                store_out(m, row, lane & 7, sum);
             }
         }
     }
@@ -753,7 +759,12 @@ static cudaError_t launch_gemv_t(const void *w, const float *x, const int32_t *p
     static const bool pdl = getenv("TCQ4_NO_PDL") == nullptr;
     // an expert id is read at kernel entry, before griddepcontrol.wait: the caller says when that is safe
     cfg.numAttrs = (pdl && (expert == nullptr || expert->pdl)) ? 2 : 1;
-    const GvExpert ex = expert ? *expert : GvExpert{nullptr, 0, 0, nullptr, 0, 0, 0};
+    const GvExpert ex = expert ? *expert : GvExpert{};
+    if constexpr (!DEBUG) {
+        if (ex.nseg > 0)
+            return cudaLaunchKernelEx(&cfg, tcq4_gemv_kernel<MB, MT, false, 2>, (const uint8_t *)w, x, perm, y, (int)M, (int)N,
+                                      (int)K, plan.depth, pre_blob, dbg, ex);
+    }
     return cudaLaunchKernelEx(&cfg, tcq4_gemv_kernel<MB, MT, DEBUG>, (const uint8_t *)w, x, perm, y, (int)M, (int)N, (int)K,
                               plan.depth, pre_blob, dbg, ex);
 }
@@ -770,7 +781,12 @@ static cudaError_t gemv_attr_one(size_t smem_optin) {
     e = cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
                              (int)cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, false>, cudaFuncAttributePreferredSharedMemoryCarveout,
+    e = cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, false>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                             (int)cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_optin);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, false, 2>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                 (int)cudaSharedmemCarveoutMaxShared);
 }
 
@@ -784,10 +800,10 @@ cudaError_t gemv_init_attributes(size_t smem_optin) {
     if (e == cudaSuccess) e = gemv_attr_one<1, 2>(smem_optin);
     if (e == cudaSuccess) e = gemv_attr_one<1, 3>(smem_optin);
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(tcq4_gemv_kernel<1, 1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        e = cudaFuncSetAttribute(tcq4_gemv_kernel<1, 1, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem_optin);
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(tcq4_gemv_kernel<1, 1, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
+        e = cudaFuncSetAttribute(tcq4_gemv_kernel<1, 1, false, 1>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                  (int)cudaSharedmemCarveoutMaxShared);
     return e;
 }
@@ -818,7 +834,7 @@ cudaError_t launch_gemv_grouped(const void *w_experts, const float *x, const int
     yo.n = 1;
     yo.ldc = n_used * N;
     yo.mc = nullptr;
-    return cudaLaunchKernelEx(&cfg, tcq4_gemv_kernel<1, 1, false, true>, (const uint8_t *)w_experts, x, perm, yo, 1,
+    return cudaLaunchKernelEx(&cfg, tcq4_gemv_kernel<1, 1, false, 1>, (const uint8_t *)w_experts, x, perm, yo, 1,
                               (int)(n_used * N), (int)K, plan.depth, (const uint8_t *)nullptr, (int32_t *)nullptr, expert);
 }
 

@@ -44,7 +44,14 @@ struct GvExpert {
     // activation row is slot % xslots.
     int xslots;            // activation rows held in shared memory (1 or n_used); 0 = not grouped
     int nt_expert;         // N / 8 of one expert
+    // fan-out launch (launch_gemv with nseg > 0): ONE launch for up to GV_MAX_SEG weight matrices over the same activations.
+    // The kernel sees sum(N_i) channels; channel block nt in [seg_nt0[i], seg_nt0[i+1]) belongs to matrix i.
+    int nseg;
+    int seg_nt0[5];
+    const uint8_t *seg_w[4];
+    float *seg_y[4];       // [M][N_i] each
 };
+constexpr int GV_MAX_SEG = 4;
 // plan: gemv_plan(x_slots, n_used * N, K); y: [n_used][N] contiguous
 cudaError_t launch_gemv_grouped(const void *w_experts, const float *x, const int32_t *perm, float *y, int64_t n_used,
                                 int64_t N, int64_t K, const GemvPlan &plan, const GvExpert &expert, cudaStream_t stream);

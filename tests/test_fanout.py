@@ -1,5 +1,6 @@
-"""Fan-out: several weight matrices over the same activations with ONE activation stage.  The bar: every output is
-BIT-IDENTICAL to the separate MUL_MAT (which is itself pinned to the oracle in test_gpu_parity.py) at decode and prefill batch."""
+"""Fan-out: several weight matrices over the same activations with ONE activation stage.  The bar: at prefill batch
+every output is BIT-IDENTICAL to the separate MUL_MAT (itself pinned to the oracle in test_gpu_parity.py); at decode batch the
+int32 accumulators are the same and the fp32 sum over 256-blocks may be cut elsewhere (NMSE <= 1e-12), and the oracle bar holds."""
 import numpy as np
 import pytest
 
@@ -32,10 +33,18 @@ def test_fanout_equals_separate_mul_mats(t4, orc, M, use_perm):
     for rep in range(2):                                # second pass: the workspace holds stale codes of the first
         outs = fan(xd, perm=pd)
         for td, N, y in zip(tds, Ns, outs):
-            assert torch.equal(y, t4.mul_mat(td, xd, N, perm=pd)), (N, rep)
+            sep = t4.mul_mat(td, xd, N, perm=pd)
+            if M > 16:
+                assert torch.equal(y, sep), (N, rep)            # same GEMM launches, minus the repeated activation kernel
+            else:
+                # one segmented GEMV: same int32 accumulators per 256-block, but a channel's blocks may be cut between
+                # warps at other places than in the separate launch, so the fp32 sum over blocks can differ in the last bits
+                assert nmse(y.cpu().numpy(), sep.cpu().numpy()) <= 1e-12, (N, rep)
         xd = xd * 0.5 + 0.25
-    ref = orc.mul_mat(tiles[2], (x * 0.5 + 0.25).astype(np.float32), Ns[2], perm)
-    assert nmse(outs[2].cpu().numpy(), ref["C"]) <= 1e-9
+    x2 = (x * 0.5 + 0.25).astype(np.float32)
+    for i in range(len(Ns)):
+        ref = orc.mul_mat(tiles[i], x2, Ns[i], perm)
+        assert nmse(outs[i].cpu().numpy(), ref["C"]) <= 1e-9, i
 
 
 def test_fanout_in_a_graph_and_other_order(t4, orc):
@@ -59,3 +68,18 @@ def test_fanout_in_a_graph_and_other_order(t4, orc):
     torch.cuda.synchronize()
     for o, w in zip(outs, want):
         assert torch.equal(o, w)
+
+
+def test_fanout_decode_one_launch_per_matrix_in_a_child_process():
+    """TCQ4_FANOUT_NOSEG=1 (read once at load, hence the child): decode batches through one GEMV per matrix instead of the
+    single segmented launch -- the path taken with more than four matrices or when sum(N) does not plan as a GEMV."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("TCQ4_FANOUT_NOSEG"):
+        pytest.skip("already the child")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, TCQ4_FANOUT_NOSEG="1")
+    out = subprocess.run([sys.executable, "-m", "pytest", "tests/test_fanout.py", "-m", "gpu", "-q", "-x", "-k",
+                          "equals_separate and not (17 or 130 or 300)"], cwd=root, env=env, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and " passed" in out.stdout, out.stdout[-3000:] + out.stderr[-2000:]
