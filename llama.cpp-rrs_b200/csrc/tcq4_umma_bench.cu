@@ -4,6 +4,9 @@
 // quoted against, and the experiment that decides the operand layout.  Operand contents are
 // irrelevant (zeroed smem); only issue/fetch/execute timing is measured.
 #include "../../include/tcq4_b200.h"
+#include <cstdio>
+#include <cstdlib>
+
 #include "tcq4_common.cuh"
 
 namespace tcq4 {
@@ -131,11 +134,16 @@ extern "C" TCQ4_B200_API int tcq4_b200_measure_umma(int kind, int N, int swizzle
 
 // ---- cta_group::2 variant: a CTA pair issues M = 256 MMAs (each CTA holds 128 rows of A and N/2 rows of B) ----
 namespace tcq4 {
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1)
-umma2_bench_kernel(int N, int iters, int kslices, long long *cycles_out) {
+// bg_warps > 0 (diagnostic, TCQ4_UMMA2_BG="warps,mode"): warps 4.. of BOTH CTAs stream through a separate 32 KB of shared
+// memory while the MMAs run -- mode 1 = STS.128, 2 = LDS.128 -- to see what concurrent shared-memory traffic (the unpack
+// stores, TMA fills and scale reads of the real kernel) costs the tensor pipe's operand fetch.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(512, 1)
+umma2_bench_kernel(int N, int iters, int kslices, long long *cycles_out, int bg_warps, int bg_mode) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t bar;
     __shared__ uint32_t tmem_slot;
+    __shared__ volatile int bg_stop;
+    if (threadIdx.x == 0) bg_stop = 0;
     const int warp = threadIdx.x >> 5;
     uint32_t crank;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
@@ -153,7 +161,27 @@ umma2_bench_kernel(int N, int iters, int kslices, long long *cycles_out) {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
     tc_fence_after();
     const uint32_t tmem = tmem_slot;
-    if (crank == 0 && threadIdx.x == 0) {
+    if (warp >= 4) {
+        if (warp - 4 < bg_warps) {
+            uint4 *area = reinterpret_cast<uint4 *>(smem + 64 * 1024 + 1024) + (threadIdx.x & 31);
+            uint4 v = make_uint4(threadIdx.x, 1, 2, 3);
+            int k = (warp - 4) * 64;
+            while (!bg_stop) {
+#pragma unroll
+                for (int u = 0; u < 8; u++) {
+                    uint4 *pp = area + ((k + u * 4) & 63) * 32;           // 64 x 512 B = 32 KB, conflict-free per instruction
+                    if (bg_mode == 1) *pp = v;
+                    else {
+                        uint4 t;
+                        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(t.x), "=r"(t.y), "=r"(t.z), "=r"(t.w) : "r"(smem_u32(pp)));
+                        v.x ^= t.x;
+                    }
+                }
+                k++;
+            }
+            if (v.x == 0xdeadbeefu) cycles_out[0] = 0;                     // keep the loads alive
+        }
+    } else if (crank == 0 && threadIdx.x == 0) {
         const uint32_t idesc = umma_idesc_i8(256, N, 1, 1);
         const uint32_t a_base = smem_u32(smem), b_base = a_base + 32 * 1024;
         const int nh = N / 2;     // B rows held by each CTA
@@ -173,6 +201,10 @@ umma2_bench_kernel(int N, int iters, int kslices, long long *cycles_out) {
         mbar_wait(&bar, 0);
         const long long t1 = clock64();
         cycles_out[blockIdx.x / 2] = t1 - t0;
+        bg_stop = 1;
+        // the peer CTA's background warps stop too
+        asm volatile("{\n\t.reg .b32 ra;\n\tmapa.shared::cluster.u32 ra, %0, 1;\n\tst.shared::cluster.u32 [ra], %1;\n\t}" ::
+                         "r"(smem_u32(const_cast<int *>(&bg_stop))), "r"(1) : "memory");
     }
     tc_fence_before();
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -187,7 +219,10 @@ extern "C" TCQ4_B200_API int tcq4_b200_measure_umma2(int N, int iters, double *t
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     sms &= ~1;
     const int kslices = 4;
-    const size_t smem = 64 * 1024 + 1024;
+    int bg_warps = 0, bg_mode = 0;
+    if (const char *bg = getenv("TCQ4_UMMA2_BG")) sscanf(bg, "%d,%d", &bg_warps, &bg_mode);
+    if (bg_warps < 0 || bg_warps > 12) bg_warps = 0;
+    const size_t smem = 64 * 1024 + 1024 + 32 * 1024 + 512;
     long long *d_cycles = nullptr;
     if (cudaMalloc(&d_cycles, sizeof(long long) * sms) != cudaSuccess) return TCQ4_ERR_CUDA;
     cudaEvent_t e0, e1;
@@ -197,7 +232,7 @@ extern "C" TCQ4_B200_API int tcq4_b200_measure_umma2(int N, int iters, double *t
     cudaError_t err = cudaFuncSetAttribute(umma2_bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     for (int rep = 0; rep < 2 && err == cudaSuccess; rep++) {
         cudaEventRecord(e0);
-        umma2_bench_kernel<<<sms, 128, smem>>>(N, iters, kslices, d_cycles);
+        umma2_bench_kernel<<<sms, bg_warps > 0 ? 128 + 32 * bg_warps : 128, smem>>>(N, iters, kslices, d_cycles, bg_warps, bg_mode);
         cudaEventRecord(e1);
         err = cudaEventSynchronize(e1);
         if (err != cudaSuccess) break;
