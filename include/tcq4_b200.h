@@ -242,6 +242,11 @@ TCQ4_B200_API int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq
                                          tcq4_tensor_view *dst, void *workspace, size_t workspace_bytes,
                                          cudaStream_t stream);
 
+/* The fan-out through the operator mirror: n consecutive MUL_MAT nodes (src0[i], src1) -> dst[i] with ONE src1.  Perms are
+ * looked up by src0[i]->name; when they are not all equal the nodes are run one by one. */
+TCQ4_B200_API int tcq4_b200_ggml_mul_mat_fanout(int n, const tcq4_tensor_view *const *src0, const tcq4_tensor_view *src1,
+                                                tcq4_tensor_view *const *dst, cudaStream_t stream);
+
 /* ggml_cuda_mul_mat_id (ggml-cuda.cu:2287-2436) for a TCQ4 src0: src0 [K, N, n_expert], src1 F32 [K, ne11, n_tokens]
  * with ne11 in {1, n_used}, ids I32 [n_used, n_tokens], dst F32 [N, n_used, n_tokens]; perm looked up by src0->name. */
 TCQ4_B200_API int tcq4_b200_ggml_mul_mat_id(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1,

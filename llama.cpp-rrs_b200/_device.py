@@ -15,7 +15,7 @@ import torch
 from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
                ACT_BLOCK_BYTES, TensorView, _check, quantize_size, shard_range, tile_bytes, workspace_size)
 
-__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
+__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "ggml_mul_mat_fanout", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
            "ggml_supports_op", "ShardedWeight", "random_tiles", "quantize_tiles", "get_rows", "ggml_get_rows"]
 
@@ -278,6 +278,18 @@ class Fanout:
         pp = perm.data_ptr() if perm is not None else 0
         _check(LIB.tcq4_b200_mul_mat_fanout(self.n, self._w, self._N, y, x.data_ptr(), M, K, pp, _stream_ptr(stream)))
         return outs
+
+
+def ggml_mul_mat_fanout(w_tiles: list, x: torch.Tensor, Ns: list, names: list, stream=None) -> list:
+    """tcq4_b200_ggml_mul_mat_fanout: consecutive MUL_MAT nodes with one src1; perms looked up by each src0->name."""
+    M, K = x.shape
+    n = len(Ns)
+    outs = [torch.empty((M, N), dtype=torch.float32, device=x.device) for N in Ns]
+    views = [_views(w, x, o, N, nm.encode()) for w, o, N, nm in zip(w_tiles, outs, Ns, names)]
+    s0 = (C.POINTER(TensorView) * n)(*[C.pointer(v[0]) for v in views])
+    ds = (C.POINTER(TensorView) * n)(*[C.pointer(v[2]) for v in views])
+    _check(LIB.tcq4_b200_ggml_mul_mat_fanout(n, s0, C.byref(views[0][1]), ds, _stream_ptr(stream)))
+    return outs
 
 
 def mul_mat_id(w_experts: torch.Tensor, x: torch.Tensor, ids: torch.Tensor, N: int, perm: torch.Tensor | None = None,

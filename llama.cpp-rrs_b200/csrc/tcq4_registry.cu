@@ -17,6 +17,7 @@
 #include <atomic>
 #include <cstring>
 #include <map>
+#include <vector>
 #include <mutex>
 #include <shared_mutex>
 #include <string>
@@ -27,6 +28,7 @@ namespace {
 struct PermEntry {
     int32_t *d_perm = nullptr;
     int      K = 0;
+    std::vector<int32_t> h;      // host copy: the fan-out mirror compares permutations of different tensors
 };
 struct KeyLess {
     using is_transparent = void;
@@ -80,6 +82,7 @@ void ggml_backend_cuda_tcq4_register_perm(const char *tensor_name, const int32_t
     if (e.d_perm) cudaFree(e.d_perm);                      // rrs.cu:88-90: replace an existing entry
     e.d_perm = d_perm;
     e.K = K;
+    e.h.assign(h_perm, h_perm + K);
 }
 
 void ggml_backend_cuda_tcq4_clear_perms(void) {
@@ -129,6 +132,52 @@ int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq4_tensor_view 
         return tcq4_b200_mul_mat_ws(src0->data, (const float *)src1->data, (float *)dst->data, M, N, K, d_perm,
                                     workspace, workspace_bytes, TCQ4_KERNEL_AUTO, stream);
     return tcq4_b200_mul_mat(src0->data, (const float *)src1->data, (float *)dst->data, M, N, K, d_perm, stream);
+}
+
+// Fan-out over consecutive MUL_MAT nodes that share src1 (tcq4_b200_mul_mat_fanout).  Each node is checked like
+// tcq4_b200_ggml_mul_mat; the permutations registered for the n weight tensors must be equal (same registry entry or same
+// contents) -- otherwise the nodes are run one by one, which is always correct.
+int tcq4_b200_ggml_mul_mat_fanout(int n, const tcq4_tensor_view *const *src0, const tcq4_tensor_view *src1,
+                                  tcq4_tensor_view *const *dst, cudaStream_t stream) {
+    if (n < 1 || n > 8 || !src0 || !src1 || !dst) return TCQ4_ERR_ARG;
+    const int64_t K = src1->ne[0], M = src1->ne[1];
+    const void *w[8];
+    int64_t Ns[8];
+    float *y[8];
+    for (int i = 0; i < n; i++) {
+        if (!src0[i] || !dst[i]) return TCQ4_ERR_ARG;
+        if (src0[i]->type != TCQ4_B200_GGML_TYPE || src1->type != 0 || dst[i]->type != 0) return TCQ4_ERR_ARG;
+        const int64_t N = src0[i]->ne[1];
+        if (src0[i]->ne[0] != K || dst[i]->ne[0] != N || dst[i]->ne[1] != M) return TCQ4_ERR_SHAPE;
+        if (src0[i]->ne[2] != 1 || src0[i]->ne[3] != 1) return TCQ4_ERR_SHAPE;
+        if (!is_contiguous_2d(src1, (size_t)K * 4) || !is_contiguous_2d(dst[i], (size_t)N * 4)) return TCQ4_ERR_SHAPE;
+        if (src0[i]->nb[1] != (size_t)(K / 256) * 148) return TCQ4_ERR_SHAPE;
+        w[i] = src0[i]->data;
+        Ns[i] = N;
+        y[i] = (float *)dst[i]->data;
+    }
+    const int32_t *d_perm = src0[0]->name ? tcq4_b200_get_perm(src0[0]->name) : nullptr;
+    bool same = true;
+    if (g_reorder_enabled.load()) {
+        const int dev = current_dev();
+        std::shared_lock<std::shared_mutex> lk(g_perm_mu);
+        const PermEntry *first = nullptr;
+        for (int i = 0; i < n && same; i++) {
+            const PermEntry *e = nullptr;
+            if (dev >= 0 && src0[i]->name && src0[i]->name[0]) {
+                auto it = g_perms.find(std::make_pair(dev, src0[i]->name));
+                if (it != g_perms.end()) e = &it->second;
+            }
+            if (i == 0) first = e;
+            else same = (e == first) || (e && first && e->h == first->h);
+        }
+    }
+    if (same) return tcq4_b200_mul_mat_fanout(n, w, Ns, y, (const float *)src1->data, M, K, d_perm, stream);
+    for (int i = 0; i < n; i++) {
+        const int st = tcq4_b200_ggml_mul_mat(src0[i], src1, dst[i], nullptr, 0, stream);
+        if (st != TCQ4_OK) return st;
+    }
+    return TCQ4_OK;
 }
 
 // ggml_cuda_mul_mat_id (ggml-cuda.cu:2287-2436) for a TCQ4 src0.  Shape rules as there (:2293-2295, 2326-2327) plus the

@@ -83,3 +83,33 @@ def test_fanout_decode_one_launch_per_matrix_in_a_child_process():
     out = subprocess.run([sys.executable, "-m", "pytest", "tests/test_fanout.py", "-m", "gpu", "-q", "-x", "-k",
                           "equals_separate and not (17 or 130 or 300)"], cwd=root, env=env, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and " passed" in out.stdout, out.stdout[-3000:] + out.stderr[-2000:]
+
+
+@pytest.mark.parametrize("M", [2, 96])
+def test_ggml_mirror_same_perm_fans_out_and_different_perms_fall_back(t4, orc, M):
+    """perms looked up by tensor name (rrs.cu:266-270): equal perms -> one fan-out call, different perms -> node by node"""
+    rng = np.random.default_rng(900 + M)
+    K, Ns, names = 512, [256, 64], ["blk.0.attn_q.weight", "blk.0.attn_k.weight"]
+    p0, p1 = block_perm(rng, K), block_perm(rng, K)
+    xd = torch.from_numpy(make_acts(rng, M, K)).cuda()
+    t4.set_reorder_enabled(True)
+    try:
+        for perms in ([p0, p0.copy()], [p0, p1]):
+            t4.clear_perms()
+            tds = []
+            for N, nm, p in zip(Ns, names, perms):
+                t4.register_perm(nm, p)
+                tds.append(torch.from_numpy(orc.quantize_tiles(orc.apply_perm_weights(make_weights(rng, N, K), p))).cuda())
+            c0 = t4.launch_count()
+            outs = t4.ggml_mul_mat_fanout(tds, xd, Ns, names)
+            launches = t4.launch_count() - c0
+            same = perms[1] is not p1
+            if M <= 16:
+                assert launches == (1 if same else 2)           # one segmented GEMV vs one GEMV per node
+            else:
+                assert launches == (3 if same else 4)           # one activation kernel + two GEMMs vs two of each
+            for td, N, nm, y in zip(tds, Ns, names, outs):
+                sep = t4.ggml_mul_mat(td, xd, N, name=nm)
+                assert nmse(y.cpu().numpy(), sep.cpu().numpy()) <= 1e-12, (nm, same)
+    finally:
+        t4.clear_perms()
