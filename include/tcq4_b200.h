@@ -95,6 +95,13 @@ TCQ4_B200_API int tcq4_b200_mul_mat(const void *w_tiles, const float *x, float *
                                     cudaStream_t stream);
 TCQ4_B200_API int tcq4_b200_reserve(int64_t max_M, int64_t max_N, int64_t max_K);
 
+/* Epilogue fusion: y = W x + bias[n] + residual[m][n] -- the ggml_add nodes behind a MUL_MAT (residual
+ * stream after attn_output / ffn_down, ggml_add of a bias tensor) folded into its epilogue.  residual: F32 [M][N] or
+ * NULL, may alias y; bias: F32 [N] or NULL.  Equal to MUL_MAT followed by the adds up to fp32 summation order. */
+TCQ4_B200_API int tcq4_b200_mul_mat_add(const void *w_tiles, const float *x, float *y, int64_t M, int64_t N, int64_t K,
+                                        const int32_t *d_perm, const float *residual, const float *bias,
+                                        cudaStream_t stream);
+
 /* Fan-out: n <= 8 weight matrices applied to the SAME activations x [M][K] (Q/K/V, gate/up: consecutive
  * MUL_MAT nodes of the ggml graph that share src1; the fusion hook is ggml-cuda.cu:3481-3688).  y[i] = F32 [M][N[i]].
  * M > 16: the activation stage runs once and the GEMMs follow; bit-identical to n separate tcq4_b200_mul_mat calls with

@@ -15,7 +15,7 @@ import torch
 from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
                ACT_BLOCK_BYTES, TensorView, _check, quantize_size, shard_range, tile_bytes, workspace_size)
 
-__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "ggml_mul_mat_fanout", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
+__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "ggml_mul_mat_fanout", "mul_mat_add", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
            "ggml_supports_op", "ShardedWeight", "random_tiles", "quantize_tiles", "get_rows", "ggml_get_rows"]
 
@@ -251,6 +251,27 @@ def ggml_get_rows(w_tiles: torch.Tensor, idx: torch.Tensor, nrows: int, K: int, 
     dst = _view(out, GGML_TYPE_F32, [K, ne10, ne11, ne12], [4, 4 * K, 4 * K * ne10, 4 * K * ne10 * ne11], b"dst")
     ef = err_flag.data_ptr() if err_flag is not None else 0
     _check(LIB.tcq4_b200_ggml_get_rows(C.byref(src0), C.byref(src1), C.byref(dst), ef, _stream_ptr(stream)))
+    return out
+
+
+def mul_mat_add(w_tiles: torch.Tensor, x: torch.Tensor, N: int, residual: torch.Tensor | None = None,
+                bias: torch.Tensor | None = None, perm: torch.Tensor | None = None, out: torch.Tensor | None = None,
+                stream=None) -> torch.Tensor:
+    """y = W x + bias + residual in the MUL_MAT's epilogue (tcq4_b200_mul_mat_add); out may be the residual tensor itself."""
+    _req_cuda(w_tiles, torch.uint8, "w_tiles")
+    _req_cuda(x, torch.float32, "x")
+    M, K = x.shape
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.float32, device=x.device)
+    for t, what, shape in ((residual, "residual", (M, N)), (bias, "bias", (N,))):
+        if t is not None:
+            _req_cuda(t, torch.float32, what)
+            if tuple(t.shape) != shape:
+                raise ValueError(f"{what} must have shape {shape}")
+    _check(LIB.tcq4_b200_mul_mat_add(w_tiles.data_ptr(), x.data_ptr(), out.data_ptr(), M, N, K,
+                                     perm.data_ptr() if perm is not None else 0,
+                                     residual.data_ptr() if residual is not None else 0,
+                                     bias.data_ptr() if bias is not None else 0, _stream_ptr(stream)))
     return out
 
 

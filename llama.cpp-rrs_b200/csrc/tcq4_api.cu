@@ -169,7 +169,7 @@ tcq4::YOut single_out(float *y, int64_t N) {
 // one workspace layout (that of the widest matrix) and the GEMMs after the first skip the activation kernel.
 int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t N, int64_t K, const int32_t *perm,
                 void *ws, size_t ws_bytes, int kernel, int32_t *dbg_isum, cudaStream_t stream, int64_t N_layout = 0,
-                bool reuse_act = false, bool *act_done = nullptr) {
+                bool reuse_act = false, bool *act_done = nullptr, const float *res = nullptr, const float *bias = nullptr) {
     float *y = yo.p[0];
     const bool plain = (yo.n == 1 && yo.ldc == N && !yo.mc);     // ggml's dst; otherwise strided / several destinations
     if (!shape_ok(M, N, K)) {
@@ -205,6 +205,7 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
     int k = kernel;
     if (k == TCQ4_KERNEL_AUTO) k = select_kernel(d, M, N, K, &gv);
     if (k == TCQ4_KERNEL_GEMM && !plain) k = TCQ4_KERNEL_GEMM2;      // only the pair GEMM and the GEMV write strided / to peers
+    if (k == TCQ4_KERNEL_GEMM && (res || bias)) k = TCQ4_KERNEL_GEMM2;            // ... and fuse bias / residual
     if (k == TCQ4_KERNEL_GEMV) {
         if (!tcq4::gemv_plan(M, N, K, d->num_sms, d->smem_optin, &gv)) {
             set_err("GEMV kernel does not take M=%lld K=%lld (M<=%d and M*K codes must fit shared memory)",
@@ -222,8 +223,12 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
         }
         // the region once used for split-K partials now receives the pre-pass output when it is large enough
         float *blob = gv.blob_bytes <= L.partial_bytes ? reinterpret_cast<float *>(wsb + L.partial_off) : nullptr;
-        cudaError_t e = tcq4::launch_gemv(w, x, perm, yo, M, N, K, gv, blob,
-                                          reinterpret_cast<int *>(wsb + L.ticket_off), dbg_isum, stream);
+        tcq4::GvExpert ex{};
+        ex.pdl = 1;
+        ex.res = res;
+        ex.bias = bias;
+        cudaError_t e = tcq4::launch_gemv(w, x, perm, yo, M, N, K, gv, blob, reinterpret_cast<int *>(wsb + L.ticket_off),
+                                          dbg_isum, stream, (res || bias) ? &ex : nullptr);
         if (e != cudaSuccess) return cuda_fail(e, "gemv launch");
         if (prof) {
             cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
@@ -266,7 +271,7 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
             return TCQ4_ERR_SHAPE;
         }
         e = tcq4::launch_gemm2(w, st, yo, M, N, K, g2, dbg_isum, stream, fuse ? x : nullptr, perm,
-                               reinterpret_cast<int *>(wsb + L.ticket_off));
+                               reinterpret_cast<int *>(wsb + L.ticket_off), res, bias);
     } else {
         e = tcq4::launch_gemm(w, st, y, M, N, K, gm, dbg_isum, stream);
     }
@@ -391,6 +396,29 @@ int tcq4_b200_mul_mat(const void *w_tiles, const float *x, float *y, int64_t M, 
     if (status != TCQ4_OK) return status;
     return run_mul_mat(w_tiles, x, single_out(y, N), M, N, K, d_perm, d->arena, d->arena_bytes, TCQ4_KERNEL_AUTO, nullptr,
                        stream);
+}
+
+// Epilogue fusion: y = W x + bias[n] + residual[m][n] in the MUL_MAT's own epilogue -- the ggml_add nodes
+// that follow the attention-output and ffn-down projections (residual stream) and the bias add of models that have one.
+// residual may alias y (in-place add).  The pair GEMM starts its fp32 accumulators from bias + residual, the GEMV adds
+// them at its store; both differ from "MUL_MAT, then add" only in fp32 summation order.
+int tcq4_b200_mul_mat_add(const void *w_tiles, const float *x, float *y, int64_t M, int64_t N, int64_t K,
+                          const int32_t *d_perm, const float *residual, const float *bias, cudaStream_t stream) {
+    if (!shape_ok(M, N, K)) {
+        set_err("unsupported shape M=%lld N=%lld K=%lld", (long long)M, (long long)N, (long long)K);
+        return TCQ4_ERR_SHAPE;
+    }
+    if (((uintptr_t)residual & 15) || ((uintptr_t)bias & 15)) {
+        set_err("mul_mat_add: residual / bias must be 16-byte aligned");
+        return TCQ4_ERR_ARG;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    status = arena_ensure(d, ws_layout(M, N, K).total, stream);
+    if (status != TCQ4_OK) return status;
+    return run_mul_mat(w_tiles, x, single_out(y, N), M, N, K, d_perm, d->arena, d->arena_bytes, TCQ4_KERNEL_AUTO, nullptr, stream,
+                       0, false, nullptr, residual, bias);
 }
 
 // Fan-out (graph-level fusion): n weight matrices applied to the SAME activations -- Q/K/V and gate/up of a

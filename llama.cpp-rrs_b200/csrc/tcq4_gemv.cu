@@ -192,7 +192,8 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
     const int workers = NW * GV_CLUSTER, entries = workers * 2;
     // GROUP (MUL_MAT_ID, one token): M = 1 token is computed per channel, but Ma activation rows (one per slot) may sit
     // in shared memory; N is the virtual channel count n_used * N_expert
-    // MODE: 0 plain, 1 GROUP (MUL_MAT_ID, below), 2 SEG (fan-out: channel blocks of several weight matrices, same x)
+    // MODE: 0 plain, 1 GROUP (MUL_MAT_ID, below), 2 SEG (fan-out: channel blocks of several weight matrices, same x),
+    // 3 plain + bias / residual added at the store
     constexpr bool GROUP = (MODE == 1), SEG = (MODE == 2);
     static_assert(!GROUP || (MB == 1 && MT == 1), "grouped launches use the one-token dp4a loop");
     const int Ma = GROUP ? ex.xslots : M;
@@ -261,12 +262,16 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
             const int ni = (ex.seg_nt0[si + 1] - ex.seg_nt0[si]) * 8;
             ex.seg_y[si][(size_t)m * ni + (row - ex.seg_nt0[si]) * 8 + ch] = v;
         } else {
+            if constexpr (MODE == 3) {                                  // tcq4_b200_mul_mat_add
+                if (ex.bias) v += __ldg(ex.bias + row * 8 + ch);
+                if (ex.res) v += ex.res[(size_t)m * N + row * 8 + ch];
+            }
             if (out.mc) multimem_st_f32(out.mc + (size_t)m * out.ldc + row * 8 + ch, v);
             else
                 for (int pi = 0; pi < out.n; pi++) out.p[pi][(size_t)m * out.ldc + row * 8 + ch] = v;
         }
     };
-    if (MODE == 0 && ex.sel != nullptr) {
+    if ((MODE == 0 || MODE == 3) && ex.sel != nullptr) {
         // MUL_MAT_ID: this launch's expert matrix.  The id comes from an earlier kernel of the stream (the router) and is
         // read here, ahead of griddepcontrol.wait: the first slot's launch is made without programmatic serialisation (it
         // starts after the router has completed), the later ones start no earlier than the first one has.
@@ -761,6 +766,9 @@ static cudaError_t launch_gemv_t(const void *w, const float *x, const int32_t *p
     cfg.numAttrs = (pdl && (expert == nullptr || expert->pdl)) ? 2 : 1;
     const GvExpert ex = expert ? *expert : GvExpert{};
     if constexpr (!DEBUG) {
+        if (ex.res != nullptr || ex.bias != nullptr)
+            return cudaLaunchKernelEx(&cfg, tcq4_gemv_kernel<MB, MT, false, 3>, (const uint8_t *)w, x, perm, y, (int)M, (int)N,
+                                      (int)K, plan.depth, pre_blob, dbg, ex);
         if (ex.nseg > 0)
             return cudaLaunchKernelEx(&cfg, tcq4_gemv_kernel<MB, MT, false, 2>, (const uint8_t *)w, x, perm, y, (int)M, (int)N,
                                       (int)K, plan.depth, pre_blob, dbg, ex);
@@ -786,7 +794,12 @@ static cudaError_t gemv_attr_one(size_t smem_optin) {
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_optin);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, false, 2>, cudaFuncAttributePreferredSharedMemoryCarveout,
+    e = cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, false, 2>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                             (int)cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_optin);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(tcq4_gemv_kernel<MB, MT, false, 3>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                 (int)cudaSharedmemCarveoutMaxShared);
 }
 

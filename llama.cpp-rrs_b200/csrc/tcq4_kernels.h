@@ -50,6 +50,9 @@ struct GvExpert {
     int seg_nt0[5];
     const uint8_t *seg_w[4];
     float *seg_y[4];       // [M][N_i] each
+    // epilogue fusion (tcq4_b200_mul_mat_add, MODE 3 of the kernel): y = W x + bias[n] + res[m][n]; res may alias y
+    const float *res;      // [M][N] contiguous or null
+    const float *bias;     // [N] or null
 };
 constexpr int GV_MAX_SEG = 4;
 // plan: gemv_plan(x_slots, n_used * N, K); y: [n_used][N] contiguous
@@ -96,6 +99,7 @@ cudaError_t gemm2_init_attributes(size_t smem_optin);
 // fuse_x != null: the kernel's own warps run the activation stage (x, perm) into `st` first; fuse_cnt = two zeroed ints
 cudaError_t launch_gemm2(const void *w_tiles, ActStage st, YOut y, int64_t M, int64_t N, int64_t K,
                          const Gemm2Plan &plan, int32_t *dbg_isum, cudaStream_t stream, const float *fuse_x = nullptr,
-                         const int32_t *fuse_perm = nullptr, int *fuse_cnt = nullptr);
+                         const int32_t *fuse_perm = nullptr, int *fuse_cnt = nullptr, const float *res = nullptr,
+                         const float *bias = nullptr);
 
 }  // namespace tcq4
