@@ -265,6 +265,12 @@ TCQ4_B200_API int tcq4_b200_ggml_mul_mat_id(const tcq4_tensor_view *src0, const 
 TCQ4_B200_API int tcq4_b200_ggml_get_rows(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1,
                                           tcq4_tensor_view *dst, int *err_flag, cudaStream_t stream);
 
+/* Quantiser side: the type llama_tensor_get_type picks for a tensor under LLAMA_FTYPE_MOSTLY_TCQ4_K32
+ * (src/llama-quant.cpp:204-526): TCQ4_K32 (42) for 2-D weights with K % 256 == 0 and N % 8 == 0, Q4_K (12) for the token
+ * embeddings and as the shape fallback, Q6_K / Q8_0 for the output matrix, F32 (0) for everything that is not a 2-D
+ * "weight".  Returns a ggml_type id, or -1 where the reference throws. */
+TCQ4_B200_API int tcq4_b200_quant_type_for(const char *name, int n_dims, int64_t K, int64_t N, int has_output);
+
 /* ---- GGUF files with TCQ4 tensors and permutations (host side) ------------------------------------------
  * The loader's scan for "tcq4.reorder.enabled" / "tcq4.<tensor>.perm" and the registration flow
  * (src/llama-model.cpp:7129-7205), the verbatim upload of tensor bytes (ggml-cuda.cu:627-633), and the writer side of

@@ -119,3 +119,24 @@ def test_load_register_and_run_from_the_golden_file(t4, orc):
         exact = x @ W.T
         assert float(((got - exact) ** 2).sum() / (exact ** 2).sum()) < 5e-2
     t4.clear_perms()
+
+
+def test_quant_type_selection_rules():
+    """llama_tensor_get_type under LLAMA_FTYPE_MOSTLY_TCQ4_K32 (src/llama-quant.cpp:204-526, 885-898): which tensors become
+    TCQ4_K32 and what the others fall back to"""
+    import __graft_entry__ as graft
+    t4 = graft.load_package()
+    F32, F16, Q5_0, Q8_0, Q4_K, Q6_K, TCQ4 = 0, 1, 6, 8, 12, 14, 42
+    f = lambda name, nd, K, N, has_output=1: t4.LIB.tcq4_b200_quant_type_for(name.encode(), nd, K, N, has_output)
+    assert f("blk.0.attn_q.weight", 2, 2560, 4096) == TCQ4
+    assert f("blk.3.ffn_down_exps.weight", 3, 768, 2048) == TCQ4          # expert tensors are 3-D
+    assert f("blk.0.attn_k.weight", 2, 2560, 1020) == Q4_K                # rows not a multiple of 8 (:481-483, :515)
+    assert f("blk.0.ffn_up.weight", 2, 2432, 4096) == F16                 # K % 256 != 0: Q4_K needs it too -> F16 (:518-520)
+    assert f("token_embd.weight", 2, 2560, 151936) == Q4_K                # :280-285
+    assert f("token_embd.weight", 2, 4096, 128256, has_output=0) == Q6_K  # tied embeddings follow the output rule (:232)
+    assert f("output.weight", 2, 4096, 128256) == Q6_K                    # 4096 % 2048 == 0 (:243-253)
+    assert f("output.weight", 2, 2560, 151936) == Q8_0                    # 2560 % 2048 != 0 -> Q8_0
+    assert f("blk.0.attn_norm.weight", 1, 2560, 1) == F32
+    assert f("blk.0.attn_q_norm.weight", 2, 128, 32) == F32               # :891
+    assert f("blk.0.ffn_gate_inp.weight", 2, 2048, 128) == F32            # MoE router (:898)
+    assert f("blk.0.attn_q.bias", 1, 4096, 1) == F32
