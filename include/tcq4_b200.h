@@ -119,9 +119,10 @@ TCQ4_B200_API int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, co
  *         or n_used (one row per token and slot: down)                       -- ggml src1 [K, ne11, n_tokens]
  *   ids : device int32, ids[t * ids_stride + s] = expert of slot s of token t  -- ggml ids [n_used, n_tokens]
  *   y   : F32 [n_tokens][n_used][N] contiguous:  y[t][s][:] = W[ids[t][s]] * x[t][s % x_slots][:]
- * n_tokens == 1 runs without any host round trip (the kernel reads the id on the device; capturable in a CUDA graph;
- * an id outside [0, n_expert) sets *err_flag -- device int, may be NULL -- and computes with expert 0).
- * n_tokens > 1 reads the ids on the host like the reference (synchronises the stream; a bad id returns TCQ4_ERR_ARG). */
+ * n_tokens <= 8 runs without any host round trip (the kernel reads the ids on the device, one launch per token;
+ * capturable in a CUDA graph; an id outside [0, n_expert) sets *err_flag -- device int, may be NULL -- and computes
+ * with expert 0).  More tokens: the ids are read on the host like the reference (synchronises the stream; a bad id
+ * returns TCQ4_ERR_ARG). */
 TCQ4_B200_API int tcq4_b200_mul_mat_id(const void *w_experts, int64_t n_expert, size_t expert_stride_bytes,
                                        const float *x, int64_t x_slots, const int32_t *ids, int64_t ids_stride,
                                        int64_t n_used, int64_t n_tokens, float *y, int64_t N, int64_t K,

@@ -503,7 +503,8 @@ int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N
 //    in place.  Capturable in a graph.  (Fallback when x_slots activation rows do not fit the GEMV's shared memory: one
 //    GEMV per slot; slot 0 in plain stream order -- the ids come from the router kernel before it -- slots 1.. with
 //    programmatic dependent launch: they cannot start before slot 0 has, i.e. not before the router has completed.)
-//  * n_tokens  > 1: the reference's scheme -- ids are read on the host (stream synchronise; not capturable), rows are
+//    Up to 8 tokens (a decode batch) take the same route, one grouped launch per token.
+//  * more tokens: the reference's scheme -- ids are read on the host (stream synchronise; not capturable), rows are
 //    counting-sorted by expert, gathered by one copy kernel, multiplied per expert through the normal dispatch (GEMV
 //    for <= 16 rows, tcgen05 GEMMs above), and scattered back by the same copy kernel.
 int tcq4_b200_mul_mat_id(const void *w_experts, int64_t n_expert, size_t expert_stride_bytes, const float *x,
@@ -529,12 +530,18 @@ int tcq4_b200_mul_mat_id(const void *w_experts, int64_t n_expert, size_t expert_
     const int64_t R = n_tokens * n_used;
     tcq4::GemvPlan gv;
     static const bool no_group = getenv("TCQ4_MOE_NOGROUP") != nullptr;      // diagnostics / tests: one launch per slot
-    if (n_tokens == 1 && !no_group && tcq4::gemv_plan(x_slots, n_used * N, K, d->num_sms, d->smem_optin, &gv)) {
-        // ONE launch for all slots: a GEMV over the virtual [n_used * N][K] matrix (launch_gemv_grouped)
-        const tcq4::GvExpert ex{ids, (long long)expert_stride_bytes, (int)n_expert, err_flag, 0, (int)x_slots, (int)(N / 8)};
-        cudaError_t e = tcq4::launch_gemv_grouped(w_experts, x, d_perm, y, n_used, N, K, gv, ex, stream);
-        if (e != cudaSuccess) return cuda_fail(e, "grouped gemv launch (mul_mat_id)");
-        g_launches.fetch_add(1, std::memory_order_relaxed);
+    constexpr int64_t MOE_GROUPED_MAX_TOKENS = 8;      // a decode batch: one grouped launch per token beats the host round trip
+    if (n_tokens <= MOE_GROUPED_MAX_TOKENS && !no_group &&
+        tcq4::gemv_plan(x_slots, n_used * N, K, d->num_sms, d->smem_optin, &gv)) {
+        // ONE launch for all slots of a token: a GEMV over the virtual [n_used * N][K] matrix (launch_gemv_grouped)
+        for (int64_t t = 0; t < n_tokens; t++) {
+            const tcq4::GvExpert ex{ids + t * ids_stride, (long long)expert_stride_bytes, (int)n_expert, err_flag, 0,
+                                    (int)x_slots,         (int)(N / 8)};
+            cudaError_t e = tcq4::launch_gemv_grouped(w_experts, x + t * x_slots * K, d_perm, y + t * n_used * N, n_used, N, K,
+                                                      gv, ex, stream);
+            if (e != cudaSuccess) return cuda_fail(e, "grouped gemv launch (mul_mat_id)");
+            g_launches.fetch_add(1, std::memory_order_relaxed);
+        }
         return TCQ4_OK;
     }
     if (n_tokens == 1 && tcq4::gemv_plan(1, N, K, d->num_sms, d->smem_optin, &gv)) {

@@ -82,6 +82,22 @@ def test_decode_is_graph_capturable_and_follows_device_ids(t4, orc):
         assert nmse(out.cpu().numpy(), _oracle(orc, tiles, x, ids, N)) <= 1e-9, pick
 
 
+@pytest.mark.parametrize("x_slots_full", [False, True])
+def test_decode_batch_of_tokens_device_routed(t4, orc, x_slots_full):
+    """2..8 tokens: one grouped launch per token, still no host round trip (ids with a row stride)"""
+    rng = np.random.default_rng(17 + x_slots_full)
+    n_expert, n_used, n_tokens, N, K = 6, 3, 5, 128, 768
+    tiles, td = _experts(orc, rng, n_expert, N, K)
+    wide = np.stack([rng.permutation(n_expert) for _ in range(n_tokens)]).astype(np.int32)
+    ids_view = _dev(wide)[:, :n_used]                                   # stride(0) = n_expert
+    x = np.stack([make_acts(rng, n_used if x_slots_full else 1, K) for _ in range(n_tokens)])
+    c0 = t4.launch_count()
+    y = t4.mul_mat_id(td, _dev(x), ids_view, N)
+    if not __import__("os").environ.get("TCQ4_MOE_NOGROUP"):
+        assert t4.launch_count() - c0 == n_tokens
+    assert nmse(y.cpu().numpy(), _oracle(orc, tiles, x, wide[:, :n_used], N)) <= 1e-9
+
+
 def test_decode_bad_expert_id_sets_flag(t4, orc):
     rng = np.random.default_rng(12)
     tiles, td = _experts(orc, rng, 2, 64, 256)
@@ -143,11 +159,12 @@ def test_prefill_strided_ids_and_ggml_mirror_with_registered_perm(t4, orc):
 def test_prefill_bad_expert_id_is_an_error(t4, orc):
     rng = np.random.default_rng(41)
     tiles, td = _experts(orc, rng, 2, 64, 256)
-    x = _dev(np.stack([make_acts(rng, 1, 256) for _ in range(3)]))
+    x = _dev(np.stack([make_acts(rng, 1, 256) for _ in range(9)]))      # more than 8 tokens: the host-sorted path
+    good = [[0], [1], [1], [0], [0], [1], [0], [1]]
     with pytest.raises(Exception, match="expert id"):
-        t4.mul_mat_id(td, x, _dev(np.array([[0], [2], [1]], np.int32)), 64)
+        t4.mul_mat_id(td, x, _dev(np.array(good + [[2]], np.int32)), 64)
     with pytest.raises(Exception):
-        t4.mul_mat_id(td, x, _dev(np.array([[0], [-1], [1]], np.int32)), 64)
+        t4.mul_mat_id(td, x, _dev(np.array([[-1]] + good, np.int32)), 64)
 
 
 def test_decode_per_slot_fallback_in_a_child_process():
