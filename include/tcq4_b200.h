@@ -268,8 +268,9 @@ TCQ4_B200_API int tcq4_b200_ggml_get_rows(const tcq4_tensor_view *src0, const tc
 
 /* Quantiser side: the type llama_tensor_get_type picks for a tensor under LLAMA_FTYPE_MOSTLY_TCQ4_K32
  * (src/llama-quant.cpp:204-526): TCQ4_K32 (42) for 2-D weights with K % 256 == 0 and N % 8 == 0, Q4_K (12) for the token
- * embeddings and as the shape fallback, Q6_K / Q8_0 for the output matrix, F32 (0) for everything that is not a 2-D
- * "weight".  Returns a ggml_type id, or -1 where the reference throws. */
+ * embeddings and as the shape fallback, Q6_K (K % 256 == 0, the block size of the ftype's default type, ggml.c:750-753) or
+ * Q8_0 for the output matrix.  Returns a ggml_type id, -2 for tensors the reference does not quantise (1-D tensors, norms,
+ * the MoE router: they keep their source type), or -1 where the reference throws. */
 TCQ4_B200_API int tcq4_b200_quant_type_for(const char *name, int n_dims, int64_t K, int64_t N, int has_output);
 
 /* ---- GGUF files with TCQ4 tensors and permutations (host side) ------------------------------------------
@@ -302,13 +303,6 @@ TCQ4_B200_API int     tcq4_b200_gguf_write(const char *path, int n_tensors, cons
                                            const char *const *perm_tensors, const int32_t *const *perms,
                                            const int64_t *perm_K, int reorder_enabled);
 
-/* Tensor-pipe peak of this device for one tcgen05.mma flavour: a bare single-thread issue loop on
- * every SM (kind: 0 = i8, 1 = bf16 (kind::f16), 2 = e4m3 (kind::f8f6f4); M = 128; N in {64..256};
- * swizzle: 0 = none (the GEMM's operand layout), 1 = 128B).  MEASURED_PEAKS.json has no INT8 figure,
- * so this is the measured denominator for the GEMM's tensor roofline.  Synchronous. */
-TCQ4_B200_API int tcq4_b200_measure_umma(int kind, int N, int swizzle, int iters, double *tops_out,
-                                         double *cycles_per_mma_out);
-
 /* Per-launch timing tap for the roofline leg of bench.py (no reference counterpart; the fork's
  * ggml_cuda_rrs_benchmark, rrs.cu:350-419, times with CUDA events the same way): between begin and
  * end every tcq4_b200_mul_mat* call records CUDA events on its stream around the activation kernel and
@@ -317,24 +311,6 @@ TCQ4_B200_API int tcq4_b200_measure_umma(int kind, int N, int swizzle, int iters
  * Not thread-safe, not usable under stream capture. */
 TCQ4_B200_API int tcq4_b200_profile_begin(int max_launches);
 TCQ4_B200_API int tcq4_b200_profile_end(int kernel, double *main_ms_sum, double *pre_ms_sum, int *launches);
-
-/* Same for a CTA pair: tcgen05.mma.cta_group::2.kind::i8, M = 256, N in {64..256}, no-swizzle K-major. */
-TCQ4_B200_API int tcq4_b200_measure_umma2(int N, int iters, double *tops_out, double *cycles_per_mma_out);
-
-/* Diagnostic: SM-wide cost (cycles per warp-instruction, 16 resident warps) of the warp-level instructions the
- * decode kernel is built from.  kind: 0 = mma.sync.m16n8k32.s8 (legacy IMMA), 1 = dp4a, 2 = shfl, 3 = redux.add,
- * 4 = cvt.rn.f32.s32 (I2FP), 5 = mad.lo.s32 (IMAD) */
-TCQ4_B200_API int tcq4_b200_measure_pipe(int kind, int iters, double *cycles_per_warp_instr_per_sm);
-/* TMEM read bandwidth: `warps` warps per SM loop tcgen05.ld.32x32b.x{cols} (cols = 8, 16 or 32) over their lane
- * quarter; returns bytes per clock per SM.  Bounds the prefill epilogue ("TMEM read rate"). */
-TCQ4_B200_API int tcq4_b200_measure_tmem_ld(int cols, int warps, int iters, double* bytes_per_clk_per_sm);
-
-/* Diagnostic: per-CTA phase timestamps (ns) of the last GEMV launched through tcq4_b200_mul_mat_debug:
- * out[cta][8] = {start, prefetch issued, dependency resolved, activation stage done, stream done, end}. */
-TCQ4_B200_API int tcq4_b200_debug_gemv_phases(unsigned long long *out, size_t bytes);
-/* Diagnostics: SM-clock stamps [cta 2][role 6][k-tile 16][event 8] of one cluster of the pair GEMM, recorded when
- * the environment has TCQ4_G2_PROF set (a separate instantiation; the product kernel carries no stamps). */
-TCQ4_B200_API int tcq4_b200_debug_gemm2_timeline(long long *out, size_t bytes);
 
 /* Launch statistics since load (kernels launched by this library), for bench.py's gpu_launches. */
 TCQ4_B200_API uint64_t tcq4_b200_launch_count(void);

@@ -19,6 +19,12 @@ import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libtcq4_b200.so")
+# diagnostics (include/tcq4_b200_diag.h): a superset build of the product with the instrumented kernel instantiations
+# and the microbenchmarks.  Never loaded by the product path; TCQ4_B200_USE_DIAG=1 makes the box-side diagnostic
+# scripts (tests/gpu_*.py) run the whole module on it.
+DIAG_LIB_PATH = os.path.join(HERE, "libtcq4_b200_diag.so")
+if os.environ.get("TCQ4_B200_USE_DIAG") == "1":
+    LIB_PATH = DIAG_LIB_PATH
 
 TILE_BYTES = 1184
 TILE_K = 256
@@ -39,10 +45,8 @@ EXPORTS = [
     "ggml_backend_cuda_tcq4_register_perm", "ggml_backend_cuda_tcq4_clear_perms",
     "ggml_backend_cuda_tcq4_set_reorder_enabled", "tcq4_b200_get_perm", "tcq4_b200_has_perm",
     "tcq4_b200_get_reorder_enabled", "tcq4_b200_shard_range", "tcq4_b200_ggml_supports_op",
-    "tcq4_b200_ggml_mul_mat", "tcq4_b200_launch_count", "tcq4_b200_measure_umma",
-    "tcq4_b200_profile_begin", "tcq4_b200_profile_end", "tcq4_b200_debug_gemv_phases", "tcq4_b200_debug_gemm2_timeline",
-    "tcq4_b200_measure_pipe",
-    "tcq4_b200_measure_tmem_ld", "tcq4_b200_measure_umma2",
+    "tcq4_b200_ggml_mul_mat", "tcq4_b200_launch_count",
+    "tcq4_b200_profile_begin", "tcq4_b200_profile_end",
     "tcq4_b200_quantize_size", "tcq4_b200_quantize_tiles", "tcq4_b200_perm_from_imatrix", "tcq4_b200_get_rows", "tcq4_b200_ggml_get_rows",
     "tcq4_b200_mul_mat_id", "tcq4_b200_ggml_mul_mat_id", "tcq4_b200_mul_mat_fanout", "tcq4_b200_ggml_mul_mat_fanout", "tcq4_b200_mul_mat_add", "tcq4_b200_quant_type_for",
     "tcq4_b200_gguf_open", "tcq4_b200_gguf_close", "tcq4_b200_gguf_reorder_enabled", "tcq4_b200_gguf_n_tensors",
@@ -101,12 +105,6 @@ def _load() -> C.CDLL:
     lib.tcq4_b200_ggml_supports_op.argtypes = [C.POINTER(TensorView)] * 3 + [ci]
     lib.tcq4_b200_ggml_mul_mat.argtypes = [C.POINTER(TensorView)] * 3 + [vp, sz, vp]
     lib.tcq4_b200_launch_count.restype = C.c_uint64
-    lib.tcq4_b200_measure_umma.argtypes = [ci, ci, ci, ci, C.POINTER(C.c_double), C.POINTER(C.c_double)]
-    lib.tcq4_b200_debug_gemv_phases.argtypes = [vp, sz]
-    lib.tcq4_b200_debug_gemm2_timeline.argtypes = [vp, sz]
-    lib.tcq4_b200_measure_umma2.argtypes = [ci, ci, C.POINTER(C.c_double), C.POINTER(C.c_double)]
-    lib.tcq4_b200_measure_pipe.argtypes = [ci, ci, C.POINTER(C.c_double)]
-    lib.tcq4_b200_measure_tmem_ld.argtypes = [ci, ci, ci, C.POINTER(C.c_double)]
     lib.tcq4_b200_profile_begin.argtypes = [ci]
     lib.tcq4_b200_gguf_open.argtypes = [C.c_char_p, C.POINTER(vp)]
     lib.tcq4_b200_gguf_close.argtypes = [vp]
@@ -142,6 +140,29 @@ def _load() -> C.CDLL:
 
 LIB = _load()
 
+# every symbol include/tcq4_b200_diag.h declares
+DIAG_EXPORTS = ["tcq4_b200_measure_umma", "tcq4_b200_measure_umma2", "tcq4_b200_measure_pipe", "tcq4_b200_measure_tmem_ld",
+                "tcq4_b200_measure_fabric", "tcq4_b200_measure_f16_exact", "tcq4_b200_debug_gemv_phases", "tcq4_b200_debug_gemm2_timeline"]
+_DIAG = None
+
+
+def diag_lib() -> C.CDLL:
+    """libtcq4_b200_diag.so (diagnostics only: microbenchmarks and timeline readers)."""
+    global _DIAG
+    if _DIAG is None:
+        lib = LIB if LIB_PATH == DIAG_LIB_PATH else C.CDLL(DIAG_LIB_PATH)
+        ci, vp, sz, dp = C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_double)
+        lib.tcq4_b200_measure_umma.argtypes = [ci, ci, ci, ci, dp, dp]
+        lib.tcq4_b200_measure_umma2.argtypes = [ci, ci, dp, dp]
+        lib.tcq4_b200_measure_pipe.argtypes = [ci, ci, dp]
+        lib.tcq4_b200_measure_tmem_ld.argtypes = [ci, ci, ci, dp]
+        lib.tcq4_b200_measure_fabric.argtypes = [ci, ci, ci, ci, sz, ci, dp, C.POINTER(ci)]
+        lib.tcq4_b200_measure_f16_exact.argtypes = [ci, C.c_uint, C.POINTER(ci), C.POINTER(ci)]
+        lib.tcq4_b200_debug_gemv_phases.argtypes = [vp, sz]
+        lib.tcq4_b200_debug_gemm2_timeline.argtypes = [vp, sz]
+        _DIAG = lib
+    return _DIAG
+
 
 def _check(status: int):
     if status != 0:
@@ -159,7 +180,7 @@ def launch_count() -> int:
 def measure_umma(kind: int, N: int = 256, swizzle: int = 0, iters: int = 2000):
     """(TOPS, cycles per MMA) of a bare tcgen05.mma loop: kind 0 = i8, 1 = bf16, 2 = fp8."""
     tops, cyc = C.c_double(), C.c_double()
-    _check(LIB.tcq4_b200_measure_umma(kind, N, swizzle, iters, C.byref(tops), C.byref(cyc)))
+    _check(diag_lib().tcq4_b200_measure_umma(kind, N, swizzle, iters, C.byref(tops), C.byref(cyc)))
     return tops.value, cyc.value
 
 

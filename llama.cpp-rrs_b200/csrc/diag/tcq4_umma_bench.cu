@@ -3,11 +3,11 @@
 // has no INT8 entry, so this is the denominator the GEMM's tensor roofline is
 // quoted against, and the experiment that decides the operand layout.  Operand contents are
 // irrelevant (zeroed smem); only issue/fetch/execute timing is measured.
-#include "../../include/tcq4_b200.h"
+#include "../../../include/tcq4_b200_diag.h"
 #include <cstdio>
 #include <cstdlib>
 
-#include "tcq4_common.cuh"
+#include "../tcq4_common.cuh"
 
 namespace tcq4 {
 
@@ -398,5 +398,112 @@ extern "C" TCQ4_B200_API int tcq4_b200_measure_tmem_ld(int cols, int warps, int 
     cudaFree(d_sink);
     if (err != cudaSuccess) return TCQ4_ERR_CUDA;
     if (bytes_per_clk_per_sm) *bytes_per_clk_per_sm = (double)iters * 4 * warps * 32.0 * cols * 4.0 / (double)h;
+    return TCQ4_OK;
+}
+
+// ---- exactness probe: kind::f16 on small integers ---------------------------------------------------------------------
+// A (128 x 256) holds activation codes in [-7, 7] and B (256 x 256) holds sc*q in [-1016, 1016], both exactly
+// representable in fp16; every partial sum of a 256-deep dot is an integer below 2^21, so an fp32 accumulator that keeps
+// 24 significant bits holds the int32 result EXACTLY.  This kernel checks that the tensor core's accumulation does
+// (one CTA, 16 MMAs of 128 x 256 x 16, D read back with tcgen05.ld and compared with an integer dot product).
+// pattern 0: random, 1: every product at its maximum (+7 * +1016), 2: alternating signs of maximal products, 3: random
+// with A in [-7,7] and B restricted to +-1016 / +-1015 (odd/even mix: low bits alive at the largest magnitudes)
+namespace tcq4 {
+__device__ __forceinline__ uint32_t f16x_hash(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+    return x;
+}
+__global__ void __launch_bounds__(128, 1) f16_exact_kernel(int pattern, uint32_t seed, int *mismatches, int *max_abs_out) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    __half *sA = reinterpret_cast<__half *>(smem);                 // [32 chunks][128 rows][8]
+    __half *sB = reinterpret_cast<__half *>(smem + 64 * 1024);     // [32 chunks][256 rows][8]
+    const int warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < 128 * 256; i += blockDim.x) {
+        const int r = i >> 8, k = i & 255;
+        int a;
+        if (pattern == 1) a = 7;
+        else if (pattern == 2) a = (k & 1) ? -7 : 7;
+        else a = (int)(f16x_hash(seed ^ (uint32_t)i) % 15u) - 7;
+        sA[(k >> 3) * (128 * 8) + r * 8 + (k & 7)] = __int2half_rn(a);
+    }
+    for (int i = threadIdx.x; i < 256 * 256; i += blockDim.x) {
+        const int n = i >> 8, k = i & 255;
+        int b;
+        const uint32_t h = f16x_hash(seed * 31u + 0x9E3779B9u + (uint32_t)i);
+        if (pattern == 1) b = 1016;
+        else if (pattern == 2) b = (k & 2) ? -1016 : 1016;
+        else if (pattern == 3) b = ((h & 1) ? 1016 : 1015) * ((h & 2) ? 1 : -1);
+        else b = (int)(h % 2033u) - 1016;
+        sB[(k >> 3) * (256 * 8) + n * 8 + (k & 7)] = __int2half_rn(b);
+    }
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        fence_mbar_init();
+    }
+    if (warp == 0) {
+        tmem_alloc(&tmem_slot, 256);
+        tmem_relinquish();
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_slot;
+    if (threadIdx.x == 0) {
+        const uint32_t idesc = (1u << 4) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);   // F32 acc, F16 x F16
+        const uint32_t a_base = smem_u32(sA), b_base = smem_u32(sB);
+        for (int ks = 0; ks < 16; ks++) {
+            const uint64_t ad = umma_desc_kmajor_noswz(a_base + ks * 2 * 2048, 2048, 128);
+            const uint64_t bd = umma_desc_kmajor_noswz(b_base + ks * 2 * 4096, 4096, 128);
+            ub_mma<UB_BF16>(tmem, ad, bd, idesc, ks > 0 ? 1u : 0u);       // kind::f16 (operand format comes from idesc)
+        }
+        umma_commit(&bar);
+    }
+    mbar_wait(&bar, 0);
+    tc_fence_after();
+    const int r = threadIdx.x;      // TMEM lane = row
+    int bad = 0, mx = 0;
+    for (int c0 = 0; c0 < 256; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
+        tmem_ld_wait();
+        for (int j = 0; j < 32; j++) {
+            const int n = c0 + j;
+            int ref = 0;
+            for (int k = 0; k < 256; k++)
+                ref += __half2int_rn(sA[(k >> 3) * (128 * 8) + r * 8 + (k & 7)]) *
+                       __half2int_rn(sB[(k >> 3) * (256 * 8) + n * 8 + (k & 7)]);
+            const float got = __uint_as_float(v[j]);
+            if (got != (float)ref || (int)got != ref) bad++;
+            mx = max(mx, abs(ref));
+        }
+    }
+    if (bad) atomicAdd(mismatches, bad);
+    atomicMax(max_abs_out, mx);
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 256);
+}
+}  // namespace tcq4
+
+extern "C" TCQ4_B200_API int tcq4_b200_measure_f16_exact(int pattern, unsigned seed, int *mismatches, int *max_abs) {
+    using namespace tcq4;
+    int *d = nullptr;
+    if (cudaMalloc(&d, 8) != cudaSuccess) return TCQ4_ERR_CUDA;
+    cudaMemset(d, 0, 8);
+    const size_t smem = 192 * 1024 + 1024;
+    cudaError_t e = cudaFuncSetAttribute(f16_exact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) {
+        f16_exact_kernel<<<1, 128, smem>>>(pattern, seed, d, d + 1);
+        e = cudaDeviceSynchronize();
+    }
+    int h[2] = {-1, -1};
+    if (e == cudaSuccess) cudaMemcpy(h, d, 8, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (e != cudaSuccess) return TCQ4_ERR_CUDA;
+    if (mismatches) *mismatches = h[0];
+    if (max_abs) *max_abs = h[1];
     return TCQ4_OK;
 }

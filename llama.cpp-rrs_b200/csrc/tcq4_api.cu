@@ -6,6 +6,9 @@
 // Nothing here allocates or synchronises on the launch path except the explicit convenience
 // entries (tcq4_b200_mul_mat's arena growth outside capture, tcq4_b200_mul_mat_host).
 #include "../../include/tcq4_b200.h"
+#ifdef TCQ4_DIAG
+#include "../../include/tcq4_b200_diag.h"
+#endif
 
 #include <algorithm>
 #include <atomic>
@@ -889,6 +892,7 @@ int tcq4_b200_perm_from_imatrix(const float *imatrix_host, int64_t K, int32_t *p
     return TCQ4_OK;
 }
 
+#ifdef TCQ4_DIAG
 int tcq4_b200_debug_gemm2_timeline(long long *out, size_t bytes) {
     cudaError_t e = cudaDeviceSynchronize();
     if (e == cudaSuccess) e = tcq4::gemm2_read_prof(out, bytes);
@@ -900,6 +904,7 @@ int tcq4_b200_debug_gemv_phases(unsigned long long *out, size_t bytes) {
     if (e == cudaSuccess) e = tcq4::gemv_read_prof(out, bytes);
     return e == cudaSuccess ? TCQ4_OK : cuda_fail(e, "gemv phase read");
 }
+#endif
 
 int tcq4_b200_profile_begin(int max_launches) {
     if (max_launches < 1 || max_launches > (1 << 20)) {

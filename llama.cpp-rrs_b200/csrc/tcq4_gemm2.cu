@@ -855,12 +855,14 @@ static cudaError_t launch_gemm2_t(cudaLaunchConfig_t *cfg, const void *w_tiles, 
         return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, false, 2>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st, fz, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
     if (y.n > 1)
         return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, false, 1>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st, fz, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
-    static const bool prof = getenv("TCQ4_G2_PROF") != nullptr;     // diagnostics: timeline stamps of one cluster
+#ifdef TCQ4_DIAG
+    static const bool prof = getenv("TCQ4_G2_PROF") != nullptr;     // diagnostics build: timeline stamps of one cluster
     if (prof && !dbg_isum) {
         cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              Gemm2Smem::total);
         return cudaLaunchKernelEx(cfg, tcq4_gemm2_kernel<NTL, false, true>, tm_tiles, tm_meta, tm_y, (const uint8_t *)w_tiles, st, fz, (int)M, (int)N, (int)K, MB2, num_tiles, (int32_t *)nullptr);
     }
+#endif
     if (fz.res != nullptr || fz.bias != nullptr) {      // tcq4_b200_mul_mat_add (single destination)
         cudaFuncSetAttribute(tcq4_gemm2_kernel<NTL, false, false, 0, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              Gemm2Smem::total);

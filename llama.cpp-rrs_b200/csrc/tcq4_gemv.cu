@@ -875,6 +875,12 @@ static cudaError_t launch_gemv_d(bool debug, const void *w, const float *x, cons
         if (e != cudaSuccess) return e;
         pre = blob;
     }
+    // the instrumented instantiation exists for the plain kernel only: a fan-out (nseg) or bias / residual launch always
+    // takes its own non-debug instantiation, whatever the diagnostics switches say
+    if (expert && (expert->nseg > 0 || expert->res != nullptr || expert->bias != nullptr)) {
+        if (dbg != nullptr) return cudaErrorNotSupported;
+        debug = false;
+    }
     if (debug) return launch_gemv_t<MB, MT, true>(w, x, perm, y, M, N, K, plan, pre, dbg, stream, expert);
     return launch_gemv_t<MB, MT, false>(w, x, perm, y, M, N, K, plan, pre, nullptr, stream, expert);
 }
@@ -885,7 +891,11 @@ cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm
     uint8_t *blob = reinterpret_cast<uint8_t *>(ws_partial);      // pre-pass output (plan.blob_bytes), may be null
     (void)ws_ticket;
     if (M < 1 || M > GEMV_MAX_M) return cudaErrorInvalidValue;
-    static const bool prof = getenv("TCQ4_GV_PROF") != nullptr;      // phase stamps without the isum dump
+#ifdef TCQ4_DIAG
+    static const bool prof = getenv("TCQ4_GV_PROF") != nullptr;      // phase stamps without the isum dump (diagnostics build)
+#else
+    const bool prof = false;
+#endif
     static const bool nodp = getenv("TCQ4_GV_NODP") != nullptr;      // diagnostics: IMMA loop for every M
     const bool dbg = dbg_isum != nullptr || prof;
     if (!nodp) {

@@ -334,16 +334,17 @@ int tcq4_b200_gguf_write(const char *path, int n_tensors, const char *const *nam
 // llama_tensor_get_type for ftype LLAMA_FTYPE_MOSTLY_TCQ4_K32 (src/llama-quant.cpp:204-526; default type :590) restated for the
 // tensor classes it distinguishes.  Returns the ggml_type id the reference would store the tensor as.
 extern "C" TCQ4_B200_API int tcq4_b200_quant_type_for(const char *name, int n_dims, int64_t K, int64_t N, int has_output) {
-    enum { T_F32 = 0, T_F16 = 1, T_Q5_0 = 6, T_Q8_0 = 8, T_Q4_K = 12, T_Q6_K = 14, T_TCQ4 = 42 };
+    enum { T_F16 = 1, T_Q5_0 = 6, T_Q8_0 = 8, T_Q4_K = 12, T_Q6_K = 14, T_TCQ4 = 42 };
     const std::string nm = name ? name : "";
     const bool is_weight = nm.size() >= 6 && nm.compare(nm.size() - 6, 6, "weight") == 0;
-    if (n_dims < 2 || !is_weight) return T_F32;                  // only 2-D+ "weight" tensors are quantised (:885-888)
+    constexpr int UNCHANGED = -2;                                // the tensor keeps the type it has in the source model
+    if (n_dims < 2 || !is_weight) return UNCHANGED;              // only 2-D+ "weight" tensors are quantised (:885-888)
     if (nm.find("_norm.weight") != std::string::npos || nm.find("ffn_gate_inp.weight") != std::string::npos)
-        return T_F32;                                            // norms and the MoE router stay F32 (:891, :898)
+        return UNCHANGED;                                        // norms and the MoE router are not quantised (:891, :898)
     int t = T_TCQ4;
-    int64_t blck = 2048;                                         // ggml_blck_size(TCQ4_K32) = 8 channels x 256
+    const int64_t blck = 256;                                    // ggml_blck_size(TCQ4_K32) = TCQ4_TILE_K (ggml.c:750-753)
     if (nm == "output.weight" || (!has_output && nm == "token_embd.weight")) {
-        // :232-253: the output matrix gets more bits; K is tested against the DEFAULT type's block size (2048)
+        // :232-253: the output matrix gets more bits; K is tested against the DEFAULT type's block size (256)
         t = (K % blck != 0) ? T_Q8_0 : T_Q6_K;
     } else if (nm == "token_embd.weight" || nm == "per_layer_token_embd.weight") {
         t = T_Q4_K;                                              // :280-285: the FWHT domain does not suit GET_ROWS consumers

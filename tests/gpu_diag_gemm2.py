@@ -20,7 +20,7 @@ for _ in range(3):
     t4.mul_mat(tiles, x, N, out=out, workspace=ws, kernel=t4.KERNEL_GEMM2)
 torch.cuda.synchronize()
 raw = np.zeros(2 * 6 * 32 * 8 + 4096 * 6, dtype=np.int64)
-rc = t4.LIB.tcq4_b200_debug_gemm2_timeline(raw.ctypes.data, raw.nbytes)
+rc = t4.diag_lib().tcq4_b200_debug_gemm2_timeline(raw.ctypes.data, raw.nbytes)
 buf = raw[:2 * 6 * 32 * 8].reshape(2, 6, 32, 8)
 cta = raw[2 * 6 * 32 * 8:].reshape(4096, 6)
 cta = cta[cta[:, 1] > 0]

@@ -29,7 +29,7 @@ def phases(M, N, K):
         t4.mul_mat_debug(tiles, x, N, kernel=t4.KERNEL_GEMV, workspace=ws)
     torch.cuda.synchronize()
     raw = np.zeros(160 * 16 + 16 * 8 * 3, dtype=np.uint64)
-    t4.LIB.tcq4_b200_debug_gemv_phases(raw.ctypes.data, raw.nbytes)
+    t4.diag_lib().tcq4_b200_debug_gemv_phases(raw.ctypes.data, raw.nbytes)
     buf = raw[:160 * 16].reshape(160, 16)
     it = raw[160 * 16:].reshape(16, 8, 3).astype(np.int64)
     b = buf[:148, :6].astype(np.int64)

@@ -22,7 +22,7 @@ def phases(M, N, K):
         t4.mul_mat(tiles, x, N, out=out, workspace=ws, kernel=t4.KERNEL_GEMV)
     torch.cuda.synchronize()
     raw = np.zeros(160 * 16 + 16 * 8 * 3, dtype=np.uint64)
-    t4.LIB.tcq4_b200_debug_gemv_phases(raw.ctypes.data, raw.nbytes)
+    t4.diag_lib().tcq4_b200_debug_gemv_phases(raw.ctypes.data, raw.nbytes)
     b8 = raw[:160 * 16].reshape(160, 16)[:148].astype(np.int64)
     b = b8[:, :6]
     it = raw[160 * 16:].reshape(16, 8, 3).astype(np.int64)

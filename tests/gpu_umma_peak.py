@@ -12,5 +12,5 @@ for kind in (0, 1, 2):
 import ctypes as C
 for N in (64, 128, 256):
     tops, cyc = C.c_double(), C.c_double()
-    rc = t4.LIB.tcq4_b200_measure_umma2(N, 4000, C.byref(tops), C.byref(cyc))
+    rc = t4.diag_lib().tcq4_b200_measure_umma2(N, 4000, C.byref(tops), C.byref(cyc))
     print(f"kind=i8 cta_group::2 M=256 N={N:3d}: rc={rc} {tops.value:8.1f} TOPS  {cyc.value:7.1f} cyc/MMA", flush=True)

@@ -23,6 +23,18 @@ def test_exports_match_header(t4):
         assert hasattr(lib, s), s
 
 
+def test_diag_library_is_separate(t4):
+    """measure_* / debug_* live in libtcq4_b200_diag.so (include/tcq4_b200_diag.h), not in the product library"""
+    src = open(os.path.join(ROOT, "include", "tcq4_b200_diag.h")).read()
+    syms = sorted(set(re.findall(r"^TCQ4_B200_API[^;(]*?\b(\w+)\s*\(", src, flags=re.M)))
+    assert sorted(t4.DIAG_EXPORTS) == syms
+    prod = C.CDLL(os.path.join(os.path.dirname(t4.DIAG_LIB_PATH), "libtcq4_b200.so"))
+    diag = C.CDLL(t4.DIAG_LIB_PATH)
+    for s in syms:
+        assert hasattr(diag, s), s
+        assert not hasattr(prod, s), f"{s} must not be exported by the product library"
+
+
 def test_supports_and_select(t4):
     assert t4.supports(1, 9728, 2560) and t4.supports(512, 9728, 2560)
     assert not t4.supports(1, 9728, 2500)           # K % 256 (rrs.cu:258)

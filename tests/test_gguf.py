@@ -134,9 +134,12 @@ def test_quant_type_selection_rules():
     assert f("blk.0.ffn_up.weight", 2, 2432, 4096) == F16                 # K % 256 != 0: Q4_K needs it too -> F16 (:518-520)
     assert f("token_embd.weight", 2, 2560, 151936) == Q4_K                # :280-285
     assert f("token_embd.weight", 2, 4096, 128256, has_output=0) == Q6_K  # tied embeddings follow the output rule (:232)
-    assert f("output.weight", 2, 4096, 128256) == Q6_K                    # 4096 % 2048 == 0 (:243-253)
-    assert f("output.weight", 2, 2560, 151936) == Q8_0                    # 2560 % 2048 != 0 -> Q8_0
-    assert f("blk.0.attn_norm.weight", 1, 2560, 1) == F32
-    assert f("blk.0.attn_q_norm.weight", 2, 128, 32) == F32               # :891
-    assert f("blk.0.ffn_gate_inp.weight", 2, 2048, 128) == F32            # MoE router (:898)
-    assert f("blk.0.attn_q.bias", 1, 4096, 1) == F32
+    assert f("output.weight", 2, 4096, 128256) == Q6_K                    # 4096 % 256 == 0 (:237-253; blck_size 256, ggml.c:750-753)
+    assert f("output.weight", 2, 2560, 151936) == Q6_K                    # Qwen3-4B: 2560 % 256 == 0 -> Q6_K
+    assert f("token_embd.weight", 2, 2560, 151936, has_output=0) == Q6_K  # ... and its tied embedding
+    assert f("output.weight", 2, 2432, 32000) == Q8_0                     # K % 256 != 0 -> Q8_0 (:243-244)
+    UNCHANGED = -2                                                        # not quantised: keeps its source type (:885-898)
+    assert f("blk.0.attn_norm.weight", 1, 2560, 1) == UNCHANGED
+    assert f("blk.0.attn_q_norm.weight", 2, 128, 32) == UNCHANGED         # :891
+    assert f("blk.0.ffn_gate_inp.weight", 2, 2048, 128) == UNCHANGED      # MoE router (:898)
+    assert f("blk.0.attn_q.bias", 1, 4096, 1) == UNCHANGED
