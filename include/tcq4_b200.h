@@ -95,6 +95,20 @@ TCQ4_B200_API int tcq4_b200_mul_mat(const void *w_tiles, const float *x, float *
                                     cudaStream_t stream);
 TCQ4_B200_API int tcq4_b200_reserve(int64_t max_M, int64_t max_N, int64_t max_K);
 
+/* Allocation-free variant of tcq4_b200_mul_mat.  NO counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (stream capture, tight serving loops, harnesses that forbid it).
+ * The scratch (activation codes, scales, group sums) lives in a file-scope `static __device__` array of
+ * TCQ4_B200_STATIC_SCRATCH_BYTES inside the library -- every GPU that loads the library holds it until exit -- whose
+ * device address is taken once per device with cudaGetSymbolAddress.  The call performs no cudaMalloc / cudaFree and
+ * calls no allocating routine; shapes whose tcq4_b200_workspace_size exceeds the array are refused with
+ * TCQ4_ERR_WORKSPACE and a message.  All calls on a device share the array (it keeps the previous call's contents; the
+ * few bytes that must be zero are cleared on `stream` by each call): calls that overlap on the GPU -- other streams,
+ * concurrently replayed graphs -- RACE; serialise them on one stream.  Same kernels, same results as tcq4_b200_mul_mat. */
+#define TCQ4_B200_STATIC_SCRATCH_BYTES (8u << 20)
+TCQ4_B200_API int tcq4_b200_mul_mat_static(const void *w_tiles, const float *x, float *y,
+                                           int64_t M, int64_t N, int64_t K, const int32_t *d_perm,
+                                           cudaStream_t stream);
+
 /* Epilogue fusion: y = W x + bias[n] + residual[m][n] -- the ggml_add nodes behind a MUL_MAT (residual
  * stream after attn_output / ffn_down, ggml_add of a bias tensor) folded into its epilogue.  residual: F32 [M][N] or
  * NULL, may alias y; bias: F32 [N] or NULL.  Equal to MUL_MAT followed by the adds up to fp32 summation order. */

@@ -41,7 +41,7 @@ STATUS = {0: "OK", 1: "ERR_SHAPE", 2: "ERR_ARG", 3: "ERR_WORKSPACE", 4: "ERR_CUD
 EXPORTS = [
     "tcq4_b200_version", "tcq4_b200_last_error", "tcq4_b200_supports", "tcq4_b200_select_kernel",
     "tcq4_b200_workspace_size", "tcq4_b200_mul_mat_ws", "tcq4_b200_workspace_init", "tcq4_b200_mul_mat",
-    "tcq4_b200_reserve", "tcq4_b200_mul_mat_peers", "tcq4_b200_mul_mat_multicast", "tcq4_b200_push_columns", "tcq4_b200_mul_mat_host", "tcq4_b200_mul_mat_host_async", "tcq4_b200_host_sync", "tcq4_b200_fwht_quantize_tc", "tcq4_b200_mul_mat_debug",
+    "tcq4_b200_reserve", "tcq4_b200_mul_mat_static", "tcq4_b200_mul_mat_peers", "tcq4_b200_mul_mat_multicast", "tcq4_b200_push_columns", "tcq4_b200_mul_mat_host", "tcq4_b200_mul_mat_host_async", "tcq4_b200_host_sync", "tcq4_b200_fwht_quantize_tc", "tcq4_b200_mul_mat_debug",
     "ggml_backend_cuda_tcq4_register_perm", "ggml_backend_cuda_tcq4_clear_perms",
     "ggml_backend_cuda_tcq4_set_reorder_enabled", "tcq4_b200_get_perm", "tcq4_b200_has_perm",
     "tcq4_b200_get_reorder_enabled", "tcq4_b200_shard_range", "tcq4_b200_ggml_supports_op",
@@ -84,6 +84,7 @@ def _load() -> C.CDLL:
     lib.tcq4_b200_workspace_init.argtypes = [vp, sz, vp]
     lib.tcq4_b200_mul_mat.argtypes = [vp, vp, vp, i64, i64, i64, vp, vp]
     lib.tcq4_b200_reserve.argtypes = [i64, i64, i64]
+    lib.tcq4_b200_mul_mat_static.argtypes = [vp, vp, vp, i64, i64, i64, vp, vp]
     lib.tcq4_b200_mul_mat_multicast.argtypes = [vp, vp, vp, i64, i64, i64, i64, i64, vp, vp]
     lib.tcq4_b200_push_columns.argtypes = [vp, vp, i64, i64, i64, i64, vp]
     lib.tcq4_b200_mul_mat_peers.argtypes = [vp, vp, vp, ci, i64, i64, i64, i64, i64, vp, vp]

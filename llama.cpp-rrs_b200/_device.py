@@ -15,7 +15,7 @@ import torch
 from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
                ACT_BLOCK_BYTES, TensorView, _check, quantize_size, shard_range, tile_bytes, workspace_size)
 
-__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "ggml_mul_mat_fanout", "mul_mat_add", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
+__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "ggml_mul_mat_fanout", "mul_mat_add", "mul_mat_static", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
            "ggml_supports_op", "ShardedWeight", "random_tiles", "quantize_tiles", "get_rows", "ggml_get_rows"]
 
@@ -69,6 +69,27 @@ def mul_mat(w_tiles: torch.Tensor, x: torch.Tensor, N: int, perm: torch.Tensor |
     else:
         _check(LIB.tcq4_b200_mul_mat_ws(w_tiles.data_ptr(), x.data_ptr(), out.data_ptr(), M, N, K, pp,
                                         workspace.ptr, workspace.nbytes, kernel, _stream_ptr(stream)))
+    return out
+
+
+def mul_mat_static(w_tiles: torch.Tensor, x: torch.Tensor, N: int, perm: torch.Tensor | None = None,
+                   out: torch.Tensor | None = None, stream=None) -> torch.Tensor:
+    """tcq4_b200_mul_mat_static: the same MUL_MAT with its scratch in the library's file-scope device array -- no
+    cudaMalloc on the call path (the output must be passed in by callers that may not allocate either).  Calls that
+    overlap on the GPU race on the shared array."""
+    _req_cuda(w_tiles, torch.uint8, "w_tiles")
+    _req_cuda(x, torch.float32, "x")
+    M, K = x.shape
+    if w_tiles.numel() != tile_bytes(N, K):
+        raise ValueError(f"w_tiles has {w_tiles.numel()} bytes, expected {tile_bytes(N, K)} for N={N} K={K}")
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.float32, device=x.device)
+    _req_cuda(out, torch.float32, "out")
+    pp = 0
+    if perm is not None:
+        _req_cuda(perm, torch.int32, "perm")
+        pp = perm.data_ptr()
+    _check(LIB.tcq4_b200_mul_mat_static(w_tiles.data_ptr(), x.data_ptr(), out.data_ptr(), M, N, K, pp, _stream_ptr(stream)))
     return out
 
 

@@ -401,6 +401,56 @@ int tcq4_b200_mul_mat(const void *w_tiles, const float *x, float *y, int64_t M, 
                        stream);
 }
 
+// ---- allocation-free entry -----------------------------------------------------------------------------------------
+// tcq4_b200_mul_mat_static: the same MUL_MAT with its scratch (activation codes, scales, group sums, GEMV pre-pass
+// blob) in a file-scope device array instead of a caller workspace or the cudaMalloc'ed arena, for callers that may
+// not allocate: code under stream capture, tight serving loops, harnesses that forbid cudaMalloc.  No counterpart in
+// the reference.  Every GPU that loads the library holds the array until
+// exit; every call on a device shares it (it keeps the previous call's contents), so two calls that overlap on the
+// GPU -- different streams, or graphs replayed concurrently -- race on it.
+constexpr size_t TCQ4_STATIC_SCRATCH_BYTES = (size_t)TCQ4_B200_STATIC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_static_scratch[TCQ4_STATIC_SCRATCH_BYTES];
+static void *g_static_scratch_ptr[MAX_DEV] = {};      // device ADDRESS of the array, per device (the name above is only
+static std::mutex g_static_mu;                         // a host-side stand-in and must never be handed to a kernel)
+
+int tcq4_b200_mul_mat_static(const void *w_tiles, const float *x, float *y, int64_t M, int64_t N, int64_t K,
+                             const int32_t *d_perm, cudaStream_t stream) {
+    if (!shape_ok(M, N, K)) {
+        set_err("unsupported shape M=%lld N=%lld K=%lld", (long long)M, (long long)N, (long long)K);
+        return TCQ4_ERR_SHAPE;
+    }
+    const WsLayout L = ws_layout(M, N, K);
+    if (L.total > TCQ4_STATIC_SCRATCH_BYTES) {
+        set_err("mul_mat_static: M=%lld N=%lld K=%lld needs %zu bytes of scratch, the static array holds %zu "
+                "(use tcq4_b200_mul_mat_ws with a caller workspace for larger shapes)",
+                (long long)M, (long long)N, (long long)K, L.total, TCQ4_STATIC_SCRATCH_BYTES);
+        return TCQ4_ERR_WORKSPACE;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+    void *scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_static_mu);
+        if (!g_static_scratch_ptr[dev]) {      // once per device, with that device current
+            void *p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_static_scratch);
+            if (e != cudaSuccess || !p) return cuda_fail(e, "cudaGetSymbolAddress(static scratch)");
+            g_static_scratch_ptr[dev] = p;
+        }
+        scratch = g_static_scratch_ptr[dev];
+    }
+    // the only region that must start at zero (counters of the opt-in fused activation stage); everything else is
+    // written before it is read within the call
+    e = cudaMemsetAsync(scratch, 0, L.ticket_bytes < 256 ? L.ticket_bytes : 256, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "static scratch memset");
+    return run_mul_mat(w_tiles, x, single_out(y, N), M, N, K, d_perm, scratch, TCQ4_STATIC_SCRATCH_BYTES, TCQ4_KERNEL_AUTO,
+                       nullptr, stream);
+}
+
 // Epilogue fusion: y = W x + bias[n] + residual[m][n] in the MUL_MAT's own epilogue -- the ggml_add nodes
 // that follow the attention-output and ffn-down projections (residual stream) and the bias add of models that have one.
 // residual may alias y (in-place add).  The pair GEMM starts its fp32 accumulators from bias + residual, the GEMV adds
