@@ -54,7 +54,9 @@ enum {
     TCQ4_KERNEL_AUTO  = 0,
     TCQ4_KERNEL_GEMV  = 1,     /* fused FWHT+quant+streaming dot, small M, HBM-bound          */
     TCQ4_KERNEL_GEMM  = 2,     /* activation kernel + tcgen05.mma kind::i8 GEMM, one CTA per 128 tokens   */
-    TCQ4_KERNEL_GEMM2 = 3      /* same on CTA pairs (cta_group::2, 256 tokens per pair): M > 128          */
+    TCQ4_KERNEL_GEMM2 = 3,     /* same on CTA pairs (cta_group::2, 256 tokens per pair); several destinations       */
+    TCQ4_KERNEL_GEMM3 = 4      /* CTA pairs, tcgen05.mma kind::f16 on exact fp16 integers, nibble operands widened
+                                  in the SM, fan-out segments, K split: the prefill kernel (round 2)                */
 };
 
 TCQ4_B200_API const char *tcq4_b200_version(void);

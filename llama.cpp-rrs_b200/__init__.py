@@ -33,7 +33,7 @@ ACT_BLOCK_BYTES = 160
 GGML_TYPE_F32 = 0
 GGML_TYPE_TCQ4_K32 = 42
 
-KERNEL_AUTO, KERNEL_GEMV, KERNEL_GEMM, KERNEL_GEMM2 = 0, 1, 2, 3
+KERNEL_AUTO, KERNEL_GEMV, KERNEL_GEMM, KERNEL_GEMM2, KERNEL_GEMM3 = 0, 1, 2, 3, 4
 
 STATUS = {0: "OK", 1: "ERR_SHAPE", 2: "ERR_ARG", 3: "ERR_WORKSPACE", 4: "ERR_CUDA", 5: "ERR_NO_DEVICE"}
 

@@ -18,12 +18,12 @@ namespace tcq4 {
 
 constexpr int ACT_WARPS_PER_CTA = 8;
 
-enum { MODE_REF = 0, MODE_STAGE = 1 };
+enum { MODE_REF = 0, MODE_STAGE = 1, MODE_NIB = 2 };
 
 template <int MODE>
 __global__ void __launch_bounds__(ACT_WARPS_PER_CTA * 32)
 tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ perm, int M, int K,
-                      ActBlockTC *__restrict__ out_ref, ActStage st) {
+                      ActBlockTC *__restrict__ out_ref, ActStage st, float4 *__restrict__ zero_y, long long zero_n4) {
     const int lane = threadIdx.x & 31;
     const int KT = K / TILE_K;
     const long long nblocks = (long long)M * KT;
@@ -36,6 +36,12 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
     pdl_launch_dependents();     // the GEMM behind this kernel may set itself up (it waits before reading the codes)
     pdl_wait();                  // x and the staging arena belong to the previous kernel until here
 
+    if (MODE == MODE_NIB && zero_y != nullptr) {      // K-split GEMM behind this launch: its output starts at zero
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < zero_n4; i += (long long)gridDim.x * blockDim.x)
+            zero_y[i] = z;
+    }
+
     for (long long b = warp0; b < nblocks; b += nwarps) {
         const int m = (int)(b / KT);
         const int kt = (int)(b - (long long)m * KT);
@@ -43,7 +49,11 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
         // ld.global.cg: every element is read once, and under programmatic stream serialization a stale L1 line of x
         // could survive from an overlapping predecessor
         rrs_load_block_cg(x + (size_t)m * K, perm, kt, lane, v);
-        const ActQuantT a = rrs_quantize_block_t<true>(v, lane, scratch);
+        ActQuantT a = rrs_quantize_block_t<true>(v, lane, scratch);
+        if (MODE == MODE_NIB) {      // the byte that travels is the high byte of fp16(q) (exact: |q| <= 7 needs 2 mantissa bits)
+#pragma unroll
+            for (int g = 0; g < 8; g++) a.q[g] = (int)(__half_as_ushort(__int2half_rn(a.q[g])) >> 8);
+        }
         const uint2 e = rrs_codes_layout_a(a, lane, scratch);        // byte r = code of element lane*8 + r
         int gs = 0;                                                  // lane g < 8 keeps the sum of group g
 #pragma unroll
@@ -60,6 +70,15 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
             if (lane == 0) blk->smooth_scale = a.max_abs;
             if (lane < 8) blk->sum_q[lane] = (int16_t)gs;
             if (lane < 3) reinterpret_cast<uint32_t *>(blk->pad)[lane] = 0u;
+        } else if (MODE == MODE_NIB) {
+            // fp16 high bytes (tcq4_common.cuh, ACT_B8_UNIT_BYTES): lane l owns operand cell l of the block
+            // (chunk of 16 K = l >> 1, half l & 1), bytes in the order (0,4,1,5,2,6,3,7)
+            const int mb = m >> 7, r = m & 127;
+            int8_t *unit = st.codes + ((size_t)mb * KT + kt) * ACT_B8_UNIT_BYTES;
+            *reinterpret_cast<uint2 *>(unit + (lane >> 1) * 2048 + r * 16 + (lane & 1) * 8) =
+                make_uint2(__byte_perm(e.x, e.y, 0x5140), __byte_perm(e.x, e.y, 0x7362));
+            if (lane == 0) st.a7[b] = __fdiv_rn(a.max_abs, 7.0f);
+            if (lane < 8) st.sumq[b * 8 + lane] = (int16_t)gs;
         } else {
             // s8 codes, sigma order {0,2,4,6,1,3,5,7}; lane pair (2j, 2j+1) forms 16-B K-chunk j
             const uint32_t w0 = __byte_perm(e.x, e.y, 0x6420);       // e0 e2 e4 e6
@@ -82,7 +101,7 @@ static int act_grid(int64_t nblocks, int num_sms) {
 
 template <typename Kern>
 static cudaError_t launch_act(Kern kern, int grid, cudaStream_t stream, const float *x, const int32_t *perm, int M, int K,
-                              ActBlockTC *out_ref, ActStage st) {
+                              ActBlockTC *out_ref, ActStage st, int which = 0, float *zero_y = nullptr, int64_t zero_floats = 0) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(ACT_WARPS_PER_CTA * 32);
@@ -94,16 +113,18 @@ static cudaError_t launch_act(Kern kern, int grid, cudaStream_t stream, const fl
     // Dependent launch is OFF by default (measured round 1: no gain for prefill, -8 % for the decode chain once the
     // kernels' own prologues had been shortened); TCQ4_PDL=1 turns it on for experiments -- then x must be read
     // with ld.global.cg (rrs_load_block_cg).
-    static const bool pdl = getenv("TCQ4_PDL") != nullptr;
-    cfg.numAttrs = pdl ? 1 : 0;
+    // The nibble-staging launch (which == 2) feeds tcq4_gemm3.cu, whose prologue and first weight copies run under this
+    // kernel's tail: dependent launch is on for that pair unless TCQ4_NO_PDL is set.
+    static const bool pdl = getenv("TCQ4_PDL") != nullptr, no_pdl = getenv("TCQ4_NO_PDL") != nullptr;
+    cfg.numAttrs = (pdl || (which == 2 && !no_pdl)) ? 1 : 0;
     // same L1/shared split as the GEMM that follows (no SM reconfiguration between the two launches)
-    static bool carve_ref = false, carve_stage = false;
-    bool &done = (out_ref != nullptr) ? carve_ref : carve_stage;
+    static bool carve_ref = false, carve_stage = false, carve_nib = false;
+    bool &done = (out_ref != nullptr) ? carve_ref : (which == 2 ? carve_nib : carve_stage);
     if (!done) {
         cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
         done = true;
     }
-    return cudaLaunchKernelEx(&cfg, kern, x, perm, M, K, out_ref, st);
+    return cudaLaunchKernelEx(&cfg, kern, x, perm, M, K, out_ref, st, reinterpret_cast<float4 *>(zero_y), (long long)(zero_floats / 4));
 }
 
 cudaError_t launch_act_quant_ref(const float *x, const int32_t *perm, int64_t M, int64_t K, void *out_blocks,
@@ -121,6 +142,29 @@ cudaError_t launch_act_quant_stage(const float *x, const int32_t *perm, int64_t 
     if (nblocks == 0) return cudaSuccess;
     return launch_act(tcq4_act_quant_kernel<MODE_STAGE>, act_grid(nblocks, num_sms), stream, x, perm, (int)M, (int)K,
                       (ActBlockTC *)nullptr, st);
+}
+
+cudaError_t launch_act_quant_nib(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st, int num_sms,
+                                 cudaStream_t stream, float *zero_y, int64_t zero_floats) {
+    const int64_t nblocks = M * (K / TILE_K);
+    if (nblocks == 0) return cudaSuccess;
+    return launch_act(tcq4_act_quant_kernel<MODE_NIB>, act_grid(nblocks, num_sms), stream, x, perm, (int)M, (int)K,
+                      (ActBlockTC *)nullptr, st, 2, zero_y, zero_floats);
+}
+
+__global__ void tcq4_zero_kernel(float4 *__restrict__ y, long long n4) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) y[i] = z;
+}
+cudaError_t launch_zero_floats(float *y, int64_t n_floats, int num_sms, cudaStream_t stream) {
+    const long long n4 = n_floats / 4;
+    if (n4 == 0) return cudaSuccess;
+    long long grid = (n4 + 255) / 256;
+    if (grid > (long long)num_sms * 8) grid = (long long)num_sms * 8;
+    tcq4_zero_kernel<<<(unsigned)grid, 256, 0, stream>>>(reinterpret_cast<float4 *>(y), n4);
+    return cudaGetLastError();
 }
 
 }  // namespace tcq4

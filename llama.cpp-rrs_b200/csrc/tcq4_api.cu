@@ -94,6 +94,7 @@ DevInfo *current_device(int *status) {
                 cudaError_t e1 = tcq4::gemv_init_attributes(d.smem_optin);
                 cudaError_t e2 = tcq4::gemm_init_attributes(d.smem_optin);
                 if (e2 == cudaSuccess) e2 = tcq4::gemm2_init_attributes(d.smem_optin);
+                if (e2 == cudaSuccess) e2 = tcq4::gemm3_init_attributes(d.smem_optin);
                 d.ok = (e1 == cudaSuccess && e2 == cudaSuccess);
                 if (!d.ok) set_err("kernel attribute setup failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
             } else {
@@ -156,7 +157,8 @@ int select_kernel(const DevInfo *d, int64_t M, int64_t N, int64_t K, tcq4::GemvP
     // elsewhere the persistent pair GEMM is up to 2x faster even with its second row block empty (measured:
     // profiles/, "M <= 128")
     if (M <= 128 && N >= 8192 && K <= 4096) return TCQ4_KERNEL_GEMM;
-    return TCQ4_KERNEL_GEMM2;
+    static const bool no_g3 = getenv("TCQ4_NO_GEMM3") != nullptr;       // experiments: the round-1 kind::i8 pair GEMM
+    return no_g3 ? TCQ4_KERNEL_GEMM2 : TCQ4_KERNEL_GEMM3;
 }
 
 tcq4::YOut single_out(float *y, int64_t N) {
@@ -207,8 +209,10 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
     tcq4::GemvPlan gv;
     int k = kernel;
     if (k == TCQ4_KERNEL_AUTO) k = select_kernel(d, M, N, K, &gv);
-    if (k == TCQ4_KERNEL_GEMM && !plain) k = TCQ4_KERNEL_GEMM2;      // only the pair GEMM and the GEMV write strided / to peers
-    if (k == TCQ4_KERNEL_GEMM && (res || bias)) k = TCQ4_KERNEL_GEMM2;            // ... and fuse bias / residual
+    const bool one_dest = (yo.n == 1 && !yo.mc);
+    if (k == TCQ4_KERNEL_GEMM && !plain) k = one_dest ? TCQ4_KERNEL_GEMM3 : TCQ4_KERNEL_GEMM2;      // only the pair GEMMs and the GEMV write strided
+    if (k == TCQ4_KERNEL_GEMM && (res || bias)) k = TCQ4_KERNEL_GEMM3;           // ... and fuse bias / residual
+    if (k == TCQ4_KERNEL_GEMM3 && !one_dest) k = TCQ4_KERNEL_GEMM2;               // several destinations / multicast: kind::i8 pair GEMM
     if (k == TCQ4_KERNEL_GEMV) {
         if (!tcq4::gemv_plan(M, N, K, d->num_sms, d->smem_optin, &gv)) {
             set_err("GEMV kernel does not take M=%lld K=%lld (M<=%d and M*K codes must fit shared memory)",
@@ -238,6 +242,41 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
             g_prof.kind[g_prof.n++] = TCQ4_KERNEL_GEMV;
         }
         g_launches.fetch_add(1, std::memory_order_relaxed);
+        return TCQ4_OK;
+    }
+    if (k == TCQ4_KERNEL_GEMM3) {
+        // kind::f16 pair GEMM: nibble staging (K1 MODE_NIB), optional K split with the output cleared by K1
+        tcq4::Gemm3Plan g3;
+        const int64_t Ns[1] = {N};
+        const bool allow_split = (yo.ldc == N) && !(res != nullptr && res == y);
+        if (!tcq4::gemm3_plan(M, Ns, 1, K, d->num_sms, d->smem_optin, allow_split, &g3)) {
+            set_err("pair GEMM (kind::f16) cannot be planned for this shape/device");
+            return TCQ4_ERR_SHAPE;
+        }
+        tcq4::ActStage st;
+        st.codes = reinterpret_cast<int8_t *>(wsb + L.codes_off);
+        st.a7 = reinterpret_cast<float *>(wsb + L.a7_off);
+        st.sumq = reinterpret_cast<int16_t *>(wsb + L.sumq_off);
+        const bool prof = g_prof.on && g_prof.n < g_prof.cap;
+        if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
+        cudaError_t e = cudaSuccess;
+        if (!reuse_act) {
+            e = tcq4::launch_act_quant_nib(x, perm, M, K, st, d->num_sms, stream, g3.ksplit > 1 ? y : nullptr, M * N);
+            if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
+        } else if (g3.ksplit > 1) {
+            e = tcq4::launch_zero_floats(y, M * N, d->num_sms, stream);
+            if (e != cudaSuccess) return cuda_fail(e, "output clear launch");
+        }
+        if (act_done) *act_done = true;
+        if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
+        const tcq4::Gemm3Seg sg{w, y, N, yo.ldc};
+        e = tcq4::launch_gemm3(&sg, 1, st, M, K, g3, dbg_isum, stream, res, bias);
+        if (e != cudaSuccess) return cuda_fail(e, "gemm3 launch");
+        if (prof) {
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
+            g_prof.kind[g_prof.n++] = k;
+        }
+        g_launches.fetch_add((!reuse_act || g3.ksplit > 1) ? 2 : 1, std::memory_order_relaxed);
         return TCQ4_OK;
     }
     if (k != TCQ4_KERNEL_GEMM && k != TCQ4_KERNEL_GEMM2) {
@@ -536,6 +575,45 @@ int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N
     }
     status = arena_ensure(d, ws_layout(M, Nmax, K).total, stream);
     if (status != TCQ4_OK) return status;
+    if (select_kernel(d, M, Nmax, K, nullptr) == TCQ4_KERNEL_GEMM3) {
+        // ONE activation launch and ONE GEMM launch per group of up to four matrices: their column blocks form one tile list
+        for (int i = 0; i < n; i++)
+            if (!w_tiles[i] || !ys[i] || ((uintptr_t)w_tiles[i] & 15) || ((uintptr_t)ys[i] & 15)) {
+                set_err("mul_mat_fanout: null or misaligned pointer of matrix %d", i);
+                return TCQ4_ERR_ARG;
+            }
+        if (!x || ((uintptr_t)x & 15) || (d_perm && ((uintptr_t)d_perm & 15))) {
+            set_err("mul_mat_fanout: null or misaligned x / perm");
+            return TCQ4_ERR_ARG;
+        }
+        const WsLayout L = ws_layout(M, Nmax, K);
+        uint8_t *wsb = reinterpret_cast<uint8_t *>(d->arena);
+        tcq4::ActStage st;
+        st.codes = reinterpret_cast<int8_t *>(wsb + L.codes_off);
+        st.a7 = reinterpret_cast<float *>(wsb + L.a7_off);
+        st.sumq = reinterpret_cast<int16_t *>(wsb + L.sumq_off);
+        cudaError_t e = tcq4::launch_act_quant_nib(x, d_perm, M, K, st, d->num_sms, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        for (int i0 = 0; i0 < n; i0 += 4) {
+            const int ns = std::min(4, n - i0);
+            tcq4::Gemm3Seg sg[4];
+            int64_t Nl[4];
+            for (int i = 0; i < ns; i++) {
+                sg[i] = tcq4::Gemm3Seg{w_tiles[i0 + i], ys[i0 + i], Ns[i0 + i], Ns[i0 + i]};
+                Nl[i] = Ns[i0 + i];
+            }
+            tcq4::Gemm3Plan g3;
+            if (!tcq4::gemm3_plan(M, Nl, ns, K, d->num_sms, d->smem_optin, false, &g3)) {
+                set_err("pair GEMM (kind::f16) cannot be planned for this fan-out");
+                return TCQ4_ERR_SHAPE;
+            }
+            e = tcq4::launch_gemm3(sg, ns, st, M, K, g3, nullptr, stream);
+            if (e != cudaSuccess) return cuda_fail(e, "gemm3 fan-out launch");
+            g_launches.fetch_add(1, std::memory_order_relaxed);
+        }
+        return TCQ4_OK;
+    }
     bool have_codes = false;
     for (int i = 0; i < n; i++) {
         bool done = false;

@@ -50,8 +50,16 @@ constexpr int ACT_UNIT_BYTES = 128 * 256;
 constexpr int ACT_LBO        = 2048;
 constexpr int ACT_SBO        = 128;
 
+// ---- GEMM activation staging, fp16-high-byte form (tcq4_gemm3.cu) ---------------------------------
+// Every integer in [-7, 7] is an fp16 number whose low byte is zero (two mantissa bits suffice: 5 = 1.25*4, 7 = 1.75*4),
+// so ONE byte per code -- the high byte of its fp16 representation -- travels, and the SM widens it with a byte permute
+// (no arithmetic).  For every (m-block of 128 rows, k-tile) one 32 KB unit [16 chunks of 16 K][128 rows][16 B]; the 16
+// bytes are two operand cells of 8 elements each, inside a cell in the order (0,4,1,5,2,6,3,7) -- the order the weight
+// unpack of tcq4_gemm3.cu produces for free.
+constexpr int ACT_B8_UNIT_BYTES = 128 * 256;
+
 struct ActStage {           // pointers into the caller's workspace
-    int8_t  *codes;         // [MB][KT][32 KB]
+    int8_t  *codes;         // [MB][KT][32 KB] s8 units, or the fp16-high-byte units of tcq4_gemm3.cu (same size, same region)
     float   *a7;            // [M][KT]      max_abs / 7
     int16_t *sumq;          // [M][KT][8]   per-group code sums (zero-point term)
 };

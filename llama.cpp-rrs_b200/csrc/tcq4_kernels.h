@@ -14,6 +14,11 @@ cudaError_t launch_act_quant_ref(const float *x, const int32_t *perm, int64_t M,
                                  int num_sms, cudaStream_t stream);
 cudaError_t launch_act_quant_stage(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st,
                                    int num_sms, cudaStream_t stream);
+// nibble staging for tcq4_gemm3.cu; zero_y / zero_floats (a multiple of 4, 16-byte aligned): an output matrix the GEMM
+// behind this launch accumulates into (K split), cleared by the same launch
+cudaError_t launch_act_quant_nib(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st, int num_sms,
+                                 cudaStream_t stream, float *zero_y = nullptr, int64_t zero_floats = 0);
+cudaError_t launch_zero_floats(float *y, int64_t n_floats, int num_sms, cudaStream_t stream);
 
 // ---- K3: fused decode GEMV (tcq4_gemv.cu) -----------------------------------------------------
 constexpr int GEMV_MAX_M = 16;
@@ -101,5 +106,24 @@ cudaError_t launch_gemm2(const void *w_tiles, ActStage st, YOut y, int64_t M, in
                          const Gemm2Plan &plan, int32_t *dbg_isum, cudaStream_t stream, const float *fuse_x = nullptr,
                          const int32_t *fuse_perm = nullptr, int *fuse_cnt = nullptr, const float *res = nullptr,
                          const float *bias = nullptr);
+
+// ---- K2 (round 2): kind::f16 pair GEMM with in-SM nibble conversion, fan-out segments, K split (tcq4_gemm3.cu) ----
+struct Gemm3Seg {
+    const void *w;       // [N/8][K/256] tiles
+    float      *y;       // [M][ldc]
+    int64_t     N, ldc;
+};
+struct Gemm3Plan {
+    dim3    grid;
+    size_t  smem_bytes;
+    int     ntl;         // n-tiles per CTA (12: 192 channels per pair-tile)
+    int     ksplit;      // 1, or 2: the two K halves of a tile meet in y through a TMA reduce-add (y must start at zero)
+    int     num_tiles;
+};
+bool        gemm3_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, size_t smem_optin, bool allow_split,
+                       Gemm3Plan *plan);
+cudaError_t gemm3_init_attributes(size_t smem_optin);
+cudaError_t launch_gemm3(const Gemm3Seg *segs, int nseg, ActStage st, int64_t M, int64_t K, const Gemm3Plan &plan,
+                         int32_t *dbg_isum, cudaStream_t stream, const float *res = nullptr, const float *bias = nullptr);
 
 }  // namespace tcq4

@@ -241,6 +241,76 @@ def test_gemm2_pairs_vs_oracle(t4, orc, M, N, K):
     assert torch.equal(y1, y2)
 
 
+GEMM3_SHAPES = GEMM2_SHAPES + [(300, 256, 2048), (512, 2560, 4096), (17, 200, 2304), (1000, 392, 512), (256, 6144, 256)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM3_SHAPES)
+def test_gemm3_f16_pairs_vs_oracle(t4, orc, M, N, K):
+    """The round-2 prefill kernel (cta_group::2 kind::f16 on exact fp16 integers, nibble operands widened in the SM): the
+    fp32 TMEM accumulators hold the oracle's int32 sums EXACTLY, fp32 outputs as tight as the kind::i8 kernels'.  Shapes
+    with few tiles and K >= 2048 also run the K split (two halves meeting in y through a TMA reduce-add)."""
+    rng = np.random.default_rng(900 + M + N + K)
+    W = make_weights(rng, N, K)
+    x = make_acts(rng, M, K)
+    tiles = orc.quantize_tiles(W)
+    big = M * N * K > 2e9
+    Mo = 24 if big else M
+    rows = np.sort(rng.choice(M, Mo, replace=False)) if big else np.arange(M)
+    ref = orc.mul_mat(tiles, x[rows], N, want_isum=True)
+    y, isum = t4.mul_mat_debug(_dev(tiles), _dev(x), N, kernel=t4.KERNEL_GEMM3)
+    torch.cuda.synchronize()
+    assert np.array_equal(isum.cpu().numpy()[rows], ref["isum"])
+    e = nmse(y.cpu().numpy()[rows], ref["C"])
+    assert e <= FP32_NMSE_TIGHT <= FP32_NMSE_SPEC, e
+    ws = t4.Workspace.for_shape(M, N, K)
+    y3 = t4.mul_mat(_dev(tiles), _dev(x), N, workspace=ws, kernel=t4.KERNEL_GEMM3).clone()
+    y3b = t4.mul_mat(_dev(tiles), _dev(x), N, workspace=ws, kernel=t4.KERNEL_GEMM3).clone()
+    assert torch.equal(y3, y3b)                      # deterministic, K split included (two addends commute)
+    assert torch.equal(y3, y)                        # debug and plain instantiations agree
+    y1 = t4.mul_mat(_dev(tiles), _dev(x), N, workspace=ws, kernel=t4.KERNEL_GEMM)
+    if K < 2048:                                     # no K split: the same fp32 operation order as the kind::i8 kernels
+        assert torch.equal(y1, y3)
+    else:
+        assert nmse(y3.cpu().numpy(), y1.cpu().numpy()) <= 1e-12
+
+
+def test_gemm3_zero_points_perm_negative_scales(t4, orc):
+    rng = np.random.default_rng(16)
+    M, N, K = 200, 136, 512
+    perm = block_perm(rng, K)
+    t = orc.quantize_tiles(orc.apply_perm_weights(make_weights(rng, N, K), perm)).reshape(-1, 1184).copy()
+    t[:, 1040:1056] = np.frombuffer(rng.uniform(-0.01, 0.01, (t.shape[0], 8)).astype(np.float16).tobytes(),
+                                    dtype=np.uint8).reshape(t.shape[0], 16)
+    t[:, 1120:1184] = rng.integers(-127, 128, (t.shape[0], 64)).astype(np.int8).view(np.uint8)
+    sc = t[:, 1056:1120].view(np.int8)
+    sc[:, ::5] = -sc[:, ::5]
+    sc[:, 7] = -127
+    sc[:, 9] = 127
+    t = t.reshape(-1)
+    x = make_acts(rng, M, K)
+    ref = orc.mul_mat(t, x, N, perm, want_isum=True)
+    y, isum = t4.mul_mat_debug(_dev(t), _dev(x), N, _dev(perm), kernel=t4.KERNEL_GEMM3)
+    assert np.array_equal(isum.cpu().numpy(), ref["isum"])
+    assert nmse(y.cpu().numpy(), ref["C"]) <= 1e-8
+
+
+def test_gemm3_extreme_codes_are_exact(t4, orc):
+    """every weight nibble -8 or 7 with |sc| = 127 and saturated activation codes: the largest sums the format allows
+    (|isum| up to 256 * 7 * 1016) must still be exact in the fp32 accumulator"""
+    rng = np.random.default_rng(3)
+    M, N, K = 130, 64, 512
+    t = orc.quantize_tiles(make_weights(rng, N, K)).reshape(-1, 1184).copy()
+    t[:, :1024] = rng.choice(np.array([0x88, 0x77, 0x87, 0x78], dtype=np.uint8), (t.shape[0], 1024))
+    t[:, 1056:1120] = rng.choice(np.array([127, -127], dtype=np.int8), (t.shape[0], 64)).view(np.uint8)
+    t = t.reshape(-1)
+    x = np.where(rng.random((M, K)) < 0.5, -1.0, 1.0).astype(np.float32)      # FWHT of +-1 rows: many saturated codes
+    x[::2] = 1.0                                                              # constant rows: one huge coefficient per block
+    ref = orc.mul_mat(t, x, N, want_isum=True)
+    y, isum = t4.mul_mat_debug(_dev(t), _dev(x), N, kernel=t4.KERNEL_GEMM3)
+    assert np.array_equal(isum.cpu().numpy(), ref["isum"])
+    assert nmse(y.cpu().numpy(), ref["C"]) <= FP32_NMSE_TIGHT
+
+
 def test_gemm2_zero_points_and_perm(t4, orc):
     rng = np.random.default_rng(15)
     M, N, K = 200, 136, 512
