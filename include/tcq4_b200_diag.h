@@ -38,6 +38,9 @@ TCQ4_B200_API int tcq4_b200_debug_gemv_phases(unsigned long long *out, size_t by
 /* Diagnostics: SM-clock stamps [cta 2][role 6][k-tile 16][event 8] of one cluster of the pair GEMM, recorded when
  * the environment has TCQ4_G2_PROF set (a separate instantiation; the product kernel carries no stamps). */
 TCQ4_B200_API int tcq4_b200_debug_gemm2_timeline(long long *out, size_t bytes);
+/* Same for the kind::f16 pair GEMM (TCQ4_G3_PROF): [role 4: MMA issuer, activation warp 0, weight warp 0, epilogue warp 0]
+ * [k-tile 64][event 8] of the leader CTA of one cluster. */
+TCQ4_B200_API int tcq4_b200_debug_gemm3_timeline(long long *out, size_t bytes);
 
 /* L2 -> SM fabric rate: every CTA (one per SM, clusters of `cluster` CTAs) streams `unit_bytes` units with cp.async.bulk
  * out of an L2-resident region of `region_bytes` into a 4-stage shared-memory ring, `iters` units per CTA.

@@ -143,7 +143,7 @@ LIB = _load()
 
 # every symbol include/tcq4_b200_diag.h declares
 DIAG_EXPORTS = ["tcq4_b200_measure_umma", "tcq4_b200_measure_umma2", "tcq4_b200_measure_pipe", "tcq4_b200_measure_tmem_ld",
-                "tcq4_b200_measure_fabric", "tcq4_b200_measure_f16_exact", "tcq4_b200_debug_gemv_phases", "tcq4_b200_debug_gemm2_timeline"]
+                "tcq4_b200_measure_fabric", "tcq4_b200_measure_f16_exact", "tcq4_b200_debug_gemv_phases", "tcq4_b200_debug_gemm2_timeline", "tcq4_b200_debug_gemm3_timeline"]
 _DIAG = None
 
 
@@ -161,6 +161,7 @@ def diag_lib() -> C.CDLL:
         lib.tcq4_b200_measure_f16_exact.argtypes = [ci, C.c_uint, C.POINTER(ci), C.POINTER(ci)]
         lib.tcq4_b200_debug_gemv_phases.argtypes = [vp, sz]
         lib.tcq4_b200_debug_gemm2_timeline.argtypes = [vp, sz]
+        lib.tcq4_b200_debug_gemm3_timeline.argtypes = [vp, sz]
         _DIAG = lib
     return _DIAG
 

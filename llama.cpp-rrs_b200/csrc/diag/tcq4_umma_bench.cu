@@ -137,6 +137,7 @@ namespace tcq4 {
 // bg_warps > 0 (diagnostic, TCQ4_UMMA2_BG="warps,mode"): warps 4.. of BOTH CTAs stream through a separate 32 KB of shared
 // memory while the MMAs run -- mode 1 = STS.128, 2 = LDS.128 -- to see what concurrent shared-memory traffic (the unpack
 // stores, TMA fills and scale reads of the real kernel) costs the tensor pipe's operand fetch.
+template <int kind>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(512, 1)
 umma2_bench_kernel(int N, int iters, int kslices, long long *cycles_out, int bg_warps, int bg_mode) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -182,7 +183,9 @@ umma2_bench_kernel(int N, int iters, int kslices, long long *cycles_out, int bg_
             if (v.x == 0xdeadbeefu) cycles_out[0] = 0;                     // keep the loads alive
         }
     } else if (crank == 0 && threadIdx.x == 0) {
-        const uint32_t idesc = umma_idesc_i8(256, N, 1, 1);
+        // kind 0: i8 (K = 32); 1: f16 x f16 -> f32 (K = 16), both operands in shared memory; 2: the same with A in TMEM
+        const uint32_t idesc = kind == 0 ? umma_idesc_i8(256, N, 1, 1)
+                                         : ((1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(256 >> 4) << 24));
         const uint32_t a_base = smem_u32(smem), b_base = a_base + 32 * 1024;
         const int nh = N / 2;     // B rows held by each CTA
         const long long t0 = clock64();
@@ -191,9 +194,18 @@ umma2_bench_kernel(int N, int iters, int kslices, long long *cycles_out, int bg_
                 const uint64_t ad = umma_desc_kmajor_noswz(a_base + ks * 4096, 2048, 128);
                 const uint64_t bd = umma_desc_kmajor_noswz(b_base + ks * (nh * 32), nh * 16, 128);
                 const uint32_t d = tmem + (it & 1) * 256;
-                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                             "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(ad), "l"(bd),
-                             "r"(idesc), "r"(1u) : "memory");
+                if (kind == 0)
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                 "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(ad), "l"(bd),
+                                 "r"(idesc), "r"(1u) : "memory");
+                else if (kind == 1)
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                 "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(ad), "l"(bd),
+                                 "r"(idesc), "r"(1u) : "memory");
+                else      // A from TMEM columns 448.. (8 columns per K = 16); D uses columns 0..N-1 / 192..192+N-1
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                 "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem + (it & 1) * 192),
+                                 "r"(tmem + 448 + ks * 8), "l"(bd), "r"(idesc), "r"(1u) : "memory");
             }
         }
         asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::
@@ -222,6 +234,9 @@ extern "C" TCQ4_B200_API int tcq4_b200_measure_umma2(int N, int iters, double *t
     int bg_warps = 0, bg_mode = 0;
     if (const char *bg = getenv("TCQ4_UMMA2_BG")) sscanf(bg, "%d,%d", &bg_warps, &bg_mode);
     if (bg_warps < 0 || bg_warps > 12) bg_warps = 0;
+    int kind = 0;      // TCQ4_UMMA2_KIND: 0 = i8, 1 = f16 (SS), 2 = f16 with A in TMEM (N <= 192)
+    if (const char *k = getenv("TCQ4_UMMA2_KIND")) kind = atoi(k);
+    if (kind < 0 || kind > 2 || (kind == 2 && N > 192)) kind = 0;
     const size_t smem = 64 * 1024 + 1024 + 32 * 1024 + 512;
     long long *d_cycles = nullptr;
     if (cudaMalloc(&d_cycles, sizeof(long long) * sms) != cudaSuccess) return TCQ4_ERR_CUDA;
@@ -229,10 +244,11 @@ extern "C" TCQ4_B200_API int tcq4_b200_measure_umma2(int N, int iters, double *t
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
     float ms = 0.f;
-    cudaError_t err = cudaFuncSetAttribute(umma2_bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    auto kern = kind == 0 ? umma2_bench_kernel<0> : kind == 1 ? umma2_bench_kernel<1> : umma2_bench_kernel<2>;
+    cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     for (int rep = 0; rep < 2 && err == cudaSuccess; rep++) {
         cudaEventRecord(e0);
-        umma2_bench_kernel<<<sms, bg_warps > 0 ? 128 + 32 * bg_warps : 128, smem>>>(N, iters, kslices, d_cycles, bg_warps, bg_mode);
+        kern<<<sms, bg_warps > 0 ? 128 + 32 * bg_warps : 128, smem>>>(N, iters, kslices, d_cycles, bg_warps, bg_mode);
         cudaEventRecord(e1);
         err = cudaEventSynchronize(e1);
         if (err != cudaSuccess) break;
@@ -244,7 +260,7 @@ extern "C" TCQ4_B200_API int tcq4_b200_measure_umma2(int N, int iters, double *t
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     if (err != cudaSuccess) return TCQ4_ERR_CUDA;
-    const double ops = 2.0 * 256.0 * N * 32.0 * (double)iters * kslices * (sms / 2);
+    const double ops = 2.0 * 256.0 * N * (kind == 0 ? 32.0 : 16.0) * (double)iters * kslices * (sms / 2);
     if (tops_out) *tops_out = ops / (ms * 1e-3) / 1e12;
     if (cycles_per_mma_out) *cycles_per_mma_out = (double)h_cycles / ((double)iters * kslices);
     return TCQ4_OK;

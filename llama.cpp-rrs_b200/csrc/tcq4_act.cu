@@ -77,7 +77,11 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
             int8_t *unit = st.codes + ((size_t)mb * KT + kt) * ACT_B8_UNIT_BYTES;
             *reinterpret_cast<uint2 *>(unit + (lane >> 1) * 2048 + r * 16 + (lane & 1) * 8) =
                 make_uint2(__byte_perm(e.x, e.y, 0x5140), __byte_perm(e.x, e.y, 0x7362));
-            if (lane == 0) st.a7[b] = __fdiv_rn(a.max_abs, 7.0f);
+            if (lane == 0) {
+                const float a7 = __fdiv_rn(a.max_abs, 7.0f);
+                st.a7[b] = a7;
+                st.a7t[((size_t)mb * KT + kt) * 128 + r] = a7;
+            }
             if (lane < 8) st.sumq[b * 8 + lane] = (int16_t)gs;
         } else {
             // s8 codes, sigma order {0,2,4,6,1,3,5,7}; lane pair (2j, 2j+1) forms 16-B K-chunk j
@@ -131,7 +135,7 @@ cudaError_t launch_act_quant_ref(const float *x, const int32_t *perm, int64_t M,
                                  int num_sms, cudaStream_t stream) {
     const int64_t nblocks = M * (K / TILE_K);
     if (nblocks == 0) return cudaSuccess;
-    ActStage none{nullptr, nullptr, nullptr};
+    ActStage none{nullptr, nullptr, nullptr, nullptr};
     return launch_act(tcq4_act_quant_kernel<MODE_REF>, act_grid(nblocks, num_sms), stream, x, perm, (int)M, (int)K,
                       reinterpret_cast<ActBlockTC *>(out_blocks), none);
 }

@@ -123,7 +123,7 @@ bool shape_ok(int64_t M, int64_t N, int64_t K) {
 struct WsLayout {
     size_t ticket_off = 0, ticket_bytes = 0;
     size_t partial_off = 0, partial_bytes = 0;
-    size_t codes_off = 0, a7_off = 0, sumq_off = 0;
+    size_t codes_off = 0, a7_off = 0, sumq_off = 0, a7t_off = 0;
     size_t total = 0;
 };
 
@@ -144,7 +144,8 @@ WsLayout ws_layout(int64_t M, int64_t N, int64_t K) {
     const size_t codes = (size_t)tcq4::round_up(MB * KT * (int64_t)tcq4::ACT_UNIT_BYTES, 256);
     L.a7_off = L.codes_off + codes;
     L.sumq_off = L.a7_off + (size_t)tcq4::round_up(M * KT * 4, 256);
-    L.total = L.sumq_off + (size_t)tcq4::round_up(M * KT * 16, 256);
+    L.a7t_off = L.sumq_off + (size_t)tcq4::round_up(M * KT * 16, 256);
+    L.total = L.a7t_off + (size_t)tcq4::round_up(MB * 128 * KT * 4, 256);       // scales per (128-row block, k-tile), tcq4_gemm3.cu
     return L;
 }
 
@@ -257,6 +258,7 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
         st.codes = reinterpret_cast<int8_t *>(wsb + L.codes_off);
         st.a7 = reinterpret_cast<float *>(wsb + L.a7_off);
         st.sumq = reinterpret_cast<int16_t *>(wsb + L.sumq_off);
+        st.a7t = reinterpret_cast<float *>(wsb + L.a7t_off);
         const bool prof = g_prof.on && g_prof.n < g_prof.cap;
         if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
         cudaError_t e = cudaSuccess;
@@ -292,6 +294,7 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
     st.codes = reinterpret_cast<int8_t *>(wsb + L.codes_off);
     st.a7 = reinterpret_cast<float *>(wsb + L.a7_off);
     st.sumq = reinterpret_cast<int16_t *>(wsb + L.sumq_off);
+    st.a7t = nullptr;
     const bool prof = g_prof.on && g_prof.n < g_prof.cap;
     if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
     // TCQ4_G2_FUSE=1: the pair GEMM runs the activation stage itself on its idle warps (no separate launch).  Opt-in:
@@ -592,6 +595,7 @@ int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N
         st.codes = reinterpret_cast<int8_t *>(wsb + L.codes_off);
         st.a7 = reinterpret_cast<float *>(wsb + L.a7_off);
         st.sumq = reinterpret_cast<int16_t *>(wsb + L.sumq_off);
+        st.a7t = reinterpret_cast<float *>(wsb + L.a7t_off);
         cudaError_t e = tcq4::launch_act_quant_nib(x, d_perm, M, K, st, d->num_sms, stream);
         if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
         g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -1024,6 +1028,12 @@ int tcq4_b200_perm_from_imatrix(const float *imatrix_host, int64_t K, int32_t *p
 int tcq4_b200_debug_gemm2_timeline(long long *out, size_t bytes) {
     cudaError_t e = cudaDeviceSynchronize();
     if (e == cudaSuccess) e = tcq4::gemm2_read_prof(out, bytes);
+    return e == cudaSuccess ? TCQ4_OK : TCQ4_ERR_CUDA;
+}
+
+int tcq4_b200_debug_gemm3_timeline(long long *out, size_t bytes) {
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = tcq4::gemm3_read_prof(out, bytes);
     return e == cudaSuccess ? TCQ4_OK : TCQ4_ERR_CUDA;
 }
 

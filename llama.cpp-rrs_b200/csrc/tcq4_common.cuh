@@ -62,7 +62,8 @@ struct ActStage {           // pointers into the caller's workspace
     int8_t  *codes;         // [MB][KT][32 KB] s8 units, or the fp16-high-byte units of tcq4_gemm3.cu (same size, same region)
     float   *a7;            // [M][KT]      max_abs / 7
     int16_t *sumq;          // [M][KT][8]   per-group code sums (zero-point term)
-};
+    float   *a7t;           // [MB][KT][128] the same scales, contiguous per (128-row block, k-tile): one 512-byte bulk copy
+};                          //               (tcq4_gemm3.cu only; null otherwise)
 
 __host__ __device__ inline int64_t round_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 

@@ -51,35 +51,43 @@ namespace tcq4 {
 
 constexpr int G3_BM = 128;                               // tokens per CTA (256 per pair)
 constexpr int G3_MAXNTL = 12;                            // n-tiles (8 channels) unpacked per CTA
-constexpr int G3_UNPACK_WARP0 = 4, G3_UNPACK_WARPS = 8;
+constexpr int G3_AW_WARP0 = 4, G3_AW_WARPS = 4;          // activation warps: thread = token row, fp16 codes -> TMEM
+constexpr int G3_UNPACK_WARP0 = G3_AW_WARP0 + G3_AW_WARPS, G3_UNPACK_WARPS = 12;     // weight warps: one (group, channel) unit per thread and half k-tile
 constexpr int G3_EPI_WARP0 = G3_UNPACK_WARP0 + G3_UNPACK_WARPS, G3_EPI_WARPS = 8;
-constexpr int G3_THREADS = (G3_EPI_WARP0 + G3_EPI_WARPS) * 32;          // 640
+constexpr int G3_THREADS = (G3_EPI_WARP0 + G3_EPI_WARPS) * 32;          // 896
 
 constexpr int G3_RAW_A = ACT_B8_UNIT_BYTES / 2;          // 16384: half a k-tile (128 K) of activation bytes
 constexpr int G3_RAW_W = G3_MAXNTL * 512;                // 6144: the same 4 groups of this CTA's NTL tiles
 constexpr int G3_RAW_META = 2 * G3_MAXNTL * 160;         // 3840: S, Z, sc, zc of the pair's 2*NTL tiles
-constexpr int G3_RAW_BYTES = G3_RAW_A + G3_RAW_W + G3_RAW_META;         // 26368
-constexpr int G3_RAW_STAGES = 3;
-constexpr int G3_F_A = 8 * G3_BM * 16;                   // 16384: quarter k-tile (64 K) of fp16 activations
-constexpr int G3_F_B = 8 * 8 * G3_MAXNTL * 16;           // 12288: the same of this CTA's 8*NTL channels
-constexpr int G3_F_BYTES = G3_F_A + G3_F_B;              // 28672
+constexpr int G3_RAW_A7 = G3_BM * 4;                     // 512: a7 of this CTA's 128 rows for the k-tile
+constexpr int G3_RAW_BYTES = G3_RAW_A + G3_RAW_W + G3_RAW_META + G3_RAW_A7;      // 26880
+constexpr int G3_RAW_STAGES = 5;
+constexpr int G3_F_B = 8 * 8 * G3_MAXNTL * 16;           // 12288: quarter k-tile (64 K) of this CTA's 8*NTL channels in fp16
+constexpr int G3_F_BYTES = G3_F_B;
 constexpr int G3_F_STAGES = 4;                           // = quarters per k-tile: stage index = quarter
 constexpr int G3_SN_RING = 8;
 constexpr int G3_SN_STRIDE = 16 * G3_MAXNTL;             // floats per ring slot
 constexpr int G3_OUT_BOXES = 2;
+// TMEM columns: two fp32 accumulator stages of 16*NTL columns, then two half-k-tile buffers of fp16 activations
+// (128 K = 64 columns of packed pairs each)
+constexpr int G3_TM_D_STRIDE = 16 * G3_MAXNTL;           // 192
+constexpr int G3_TM_A0 = 2 * G3_TM_D_STRIDE;             // 384
+constexpr int G3_TM_A_COLS = 64;
+static_assert(G3_TM_A0 + 2 * G3_TM_A_COLS <= 512, "TMEM budget");
 
 struct Gemm3Smem {
     static constexpr int off_f = 0;
-    static constexpr int off_raw = off_f + G3_F_STAGES * G3_F_BYTES;                    // 114688
-    static constexpr int off_sn = off_raw + G3_RAW_STAGES * G3_RAW_BYTES;               // 187392
-    static constexpr int off_out = off_sn + G3_SN_RING * G3_SN_STRIDE * 4;              // 193536
-    static constexpr int off_zflag = off_out + G3_EPI_WARPS * G3_OUT_BOXES * 1024;      // 209920
+    static constexpr int off_raw = off_f + G3_F_STAGES * G3_F_BYTES;
+    static constexpr int off_sn = off_raw + G3_RAW_STAGES * G3_RAW_BYTES;
+    static constexpr int off_rm = off_sn + G3_SN_RING * G3_SN_STRIDE * 4;              // [ring][128 rows] a7 / 127
+    static constexpr int off_out = off_rm + G3_SN_RING * G3_BM * 4;
+    static constexpr int off_zflag = off_out + G3_EPI_WARPS * G3_OUT_BOXES * 1024;
     static constexpr int off_bar = off_zflag + G3_SN_RING * 8 * 4;
-    static constexpr int n_bar = 2 * G3_RAW_STAGES + 2 * G3_F_STAGES + 2 + 2 + G3_SN_RING;
+    static constexpr int n_bar = 2 * G3_RAW_STAGES + 2 * G3_F_STAGES + 2 + 2 + 2 + 2 + G3_SN_RING;
     static constexpr int off_tmem = off_bar + n_bar * 8;
     static constexpr int total = off_tmem + 16;
 };
-static_assert(G3_RAW_BYTES % 128 == 0 && G3_F_BYTES % 128 == 0 && Gemm3Smem::off_raw % 128 == 0 &&
+static_assert(G3_RAW_BYTES % 128 == 0 && G3_F_BYTES % 128 == 0 && Gemm3Smem::off_raw % 128 == 0 && Gemm3Smem::off_sn % 16 == 0 &&
                   Gemm3Smem::off_out % 128 == 0 && (G3_RAW_A + G3_RAW_W) % 128 == 0,
               "operands, copy destinations and store boxes must be 128-byte aligned");
 static_assert(Gemm3Smem::off_bar % 8 == 0, "barriers must be 8-byte aligned");
@@ -125,6 +133,27 @@ __device__ __forceinline__ void umma_f16_2cta_parts(uint32_t d_tmem, uint32_t a_
         "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// same with the A operand in TENSOR MEMORY (written there by tcgen05.st): 128 lanes = this CTA's token rows, 8 columns of
+// packed fp16 pairs per K = 16
+__device__ __forceinline__ void umma_f16_2cta_ts(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t b_hi,
+                                                 uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], db, %4, p;\n\t}" ::"r"(d_tmem),
+        "r"(a_tmem), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void g3_tmem_st_32x16(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::
+            "r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+        "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+__device__ __forceinline__ void g3_tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void g3_commit_2cta(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::
                      "r"(smem_u32(bar)), "h"((uint16_t)3)
@@ -266,11 +295,23 @@ __device__ __forceinline__ G3Tile g3_decode(const G3Params &P, int t, int MB2, i
     return r;
 }
 
-template <int NTL, bool DEBUG, bool ADD>
+// Timeline stamps (diagnostics build, TCQ4_G3_PROF=1): SM clocks of one cluster's leader CTA, [role 4][k-tile 64][event 8]
+constexpr int G3_PROF_KT = 64;
+#ifdef TCQ4_DIAG
+__device__ long long g_g3_prof[4 * G3_PROF_KT * 8];
+#define G3_STAMP(role, kt, ev)                                                                          \
+    do {                                                                                                \
+        if (PROF && prof_on && (kt) < G3_PROF_KT) g_g3_prof[((role) * G3_PROF_KT + (kt)) * 8 + (ev)] = clock64(); \
+    } while (0)
+#else
+#define G3_STAMP(role, kt, ev) do { } while (0)
+#endif
+
+template <int NTL, bool DEBUG, bool ADD, bool PROF = false>
 __global__ void __launch_bounds__(G3_THREADS, 1)
 tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K, int MB2, int num_tiles,
                   int32_t *__restrict__ dbg_isum) {
-    static_assert(NTL % 2 == 0 && NTL >= 2 && NTL <= G3_MAXNTL, "NTL: even, at most 12");
+    static_assert(NTL % 4 == 0 && NTL >= 4 && NTL <= G3_MAXNTL, "NTL: a multiple of 4, at most 12");
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int NCOL = 16 * NTL;                     // channels per pair-tile = MMA N = TMEM columns per stage
     constexpr int LBO_B = 8 * NTL * 16;                // K-chunk stride of the B operand
@@ -279,31 +320,39 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
     const int KT = K / TILE_K;
     const uint32_t rank = g3_ctarank();
     const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+    const bool prof_on = PROF && cluster_id == num_clusters / 2 && rank == 0 && lane == 0;
+    (void)prof_on;
 
     uint8_t *sF = smem + Gemm3Smem::off_f;
     uint8_t *sRaw = smem + Gemm3Smem::off_raw;
     float *sSn = reinterpret_cast<float *>(smem + Gemm3Smem::off_sn);
+    float *sRm = reinterpret_cast<float *>(smem + Gemm3Smem::off_rm);
     int *sZflag = reinterpret_cast<int *>(smem + Gemm3Smem::off_zflag);
     uint8_t *sOut = smem + Gemm3Smem::off_out;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + Gemm3Smem::off_bar);
     uint64_t *rawfull = bars, *rawempty = rawfull + G3_RAW_STAGES, *bfull = rawempty + G3_RAW_STAGES,
-             *bfree = bfull + G3_F_STAGES, *accfull = bfree + G3_F_STAGES, *accempty = accfull + 2, *snfull = accempty + 2;
+             *bfree = bfull + G3_F_STAGES, *accfull = bfree + G3_F_STAGES, *accempty = accfull + 2, *afull = accempty + 2,
+             *afree = afull + 2, *snfull = afree + 2;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + Gemm3Smem::off_tmem);
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < G3_RAW_STAGES; i++) {
             mbar_init(&rawfull[i], 1);
-            mbar_init(&rawempty[i], G3_UNPACK_WARPS);
+            mbar_init(&rawempty[i], G3_UNPACK_WARPS + G3_AW_WARPS);
         }
         for (int i = 0; i < G3_F_STAGES; i++) {
-            mbar_init(&bfull[i], 2 * G3_UNPACK_WARPS);           // unpack warps of both CTAs (used in the leader)
+            mbar_init(&bfull[i], G3_UNPACK_WARPS);               // the half of the weight warps that owns this quarter, both CTAs (used in the leader)
             mbar_init(&bfree[i], 1);                             // leader's commit (multicast)
         }
         for (int i = 0; i < 2; i++) {
             mbar_init(&accfull[i], 1);                           // leader's commit (multicast)
             mbar_init(&accempty[i], 2 * G3_EPI_WARPS);           // epilogue warps of both CTAs (used in the leader)
         }
-        for (int i = 0; i < G3_SN_RING; i++) mbar_init(&snfull[i], SN_WARPS);
+        for (int i = 0; i < 2; i++) {
+            mbar_init(&afull[i], 2 * (G3_AW_WARPS + G3_UNPACK_WARPS));      // all 16 unpack warps of both CTAs (used in the leader)
+            mbar_init(&afree[i], 1);                             // leader's commit (multicast)
+        }
+        for (int i = 0; i < G3_SN_RING; i++) mbar_init(&snfull[i], SN_WARPS + G3_AW_WARPS);      // S by weight warps, a7/127 by activation warps
         fence_mbar_init();
     }
     if (warp == 0 && lane == 0) {
@@ -328,12 +377,12 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
     // Weight tiles are constants of the model: their copies, the barrier set-up and the TMEM allocation above run
     // while the activation kernel in front of this launch is still finishing.
 
-    if (warp < G3_UNPACK_WARP0) {
+    if (warp < G3_AW_WARP0) {
       asm volatile("setmaxnreg.dec.sync.aligned.u32 40;" ::: "memory");
       if (warp == 0) {
         // ===================== producer: three copies per half k-tile =====================
         if (lane == 0) {
-            constexpr uint32_t total_tx = (uint32_t)(G3_RAW_A + NTL * 512 + 2 * NTL * 160);
+            constexpr uint32_t total_tx = (uint32_t)(G3_RAW_A + NTL * 512 + 2 * NTL * 160 + G3_RAW_A7);
             const uint64_t pol_w = l2_policy_evict_first();
             // pass 0: the weight copies of the first G3_RAW_STAGES stages (nothing to wait for); then griddepcontrol.wait;
             // pass 1: everything else in ring order
@@ -345,6 +394,7 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
                     const G3Tile tl = g3_decode(P, t, MB2, KT, rank);
                     const int nt_pair = tl.cbl * (2 * NTL), nt0 = nt_pair + (int)rank * NTL;
                     const uint8_t *a_src = reinterpret_cast<const uint8_t *>(st.codes) + (size_t)tl.mb * KT * ACT_B8_UNIT_BYTES;
+                    const float *a7_src = st.a7t + (size_t)tl.mb * KT * G3_BM;
                     const CUtensorMap *mt = &P.seg[tl.sg].tm_tiles, *mm = &P.seg[tl.sg].tm_meta;
                     for (int kt = tl.kt0; kt < tl.kt1 && !done; kt++) {
 #pragma unroll 1
@@ -361,8 +411,10 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
                                 g3_tma_2d_hint(stg + G3_RAW_A, mt, kt * (TILE_BYTES / 8) + h * 64, nt0, &rawfull[s], pol_w);
                                 g3_tma_2d(stg + G3_RAW_A + G3_RAW_W, mm, kt * (TILE_BYTES / 8) + TILE_NIB / 8, nt_pair, &rawfull[s]);
                             }
-                            if (pass == 1)
+                            if (pass == 1) {
                                 bulk_g2s(stg, a_src + (size_t)kt * ACT_B8_UNIT_BYTES + h * G3_RAW_A, G3_RAW_A, &rawfull[s]);
+                                bulk_g2s(stg + G3_RAW_A + G3_RAW_W + G3_RAW_META, a7_src + (size_t)kt * G3_BM, G3_RAW_A7, &rawfull[s]);
+                            }
                             if (++s == G3_RAW_STAGES) { s = 0; u++; }
                         }
                     }
@@ -374,10 +426,8 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
         // ===================== MMA issuer (leader CTA only) =====================
         if (rank == 0) {
             constexpr uint32_t idesc = (1u << 4) | ((uint32_t)(NCOL >> 3) << 17) | ((uint32_t)((2 * G3_BM) >> 4) << 24);
-            constexpr uint32_t a_hi = (uint32_t)(128 >> 4) | (1u << 14);              // SBO = 128 B, descriptor version 1
-            constexpr uint32_t b_hi = (uint32_t)(128 >> 4) | (1u << 14);
-            const uint32_t a_lo0 = (smem_u32(sF) >> 4) | ((uint32_t)((G3_BM * 16) >> 4) << 16);        // LBO = 2048 B
-            const uint32_t b_lo0 = ((smem_u32(sF) + G3_F_A) >> 4) | ((uint32_t)(LBO_B >> 4) << 16);
+            constexpr uint32_t b_hi = (uint32_t)(128 >> 4) | (1u << 14);              // SBO = 128 B, descriptor version 1
+            const uint32_t b_lo0 = (smem_u32(sF) >> 4) | ((uint32_t)(LBO_B >> 4) << 16);
             int total_k = 0;
             for (int t = cluster_id; t < num_tiles; t += num_clusters) {
                 const G3Tile tl = g3_decode(P, t, MB2, KT, rank);
@@ -385,20 +435,26 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
             }
             for (int gk = 0; gk < total_k; gk++) {
                 const int as = gk & 1, u2 = gk >> 1;
+                G3_STAMP(0, gk, 0);
                 if (u2 > 0) g3_wait(&accempty[as], (uint32_t)((u2 - 1) & 1));
-                const uint32_t d = tmem + as * 256;
+                G3_STAMP(0, gk, 1);
+                const uint32_t d = tmem + as * G3_TM_D_STRIDE;
 #pragma unroll
                 for (int q = 0; q < 4; q++) {
+                    if ((q & 1) == 0) g3_wait(&afull[q >> 1], (uint32_t)(gk & 1));      // both CTAs' activations of this half are in TMEM
+                    if ((q & 1) == 0) G3_STAMP(0, gk, 2 + q);
                     g3_wait(&bfull[q], (uint32_t)(gk & 1));
+                    G3_STAMP(0, gk, 3 + (q & 2) + (q & 1) * 0);
+                    if (q == 3) G3_STAMP(0, gk, 6);
                     tc_fence_after();
                     if (elect_one()) {
-                        const uint32_t a_lo = a_lo0 + (uint32_t)q * (G3_F_BYTES >> 4);
                         const uint32_t b_lo = b_lo0 + (uint32_t)q * (G3_F_BYTES >> 4);
+                        const uint32_t a_t = tmem + G3_TM_A0 + (q >> 1) * G3_TM_A_COLS + (q & 1) * 32;
 #pragma unroll
-                        for (int ks = 0; ks < 4; ks++)      // K = 16 per instruction = two 8-element K-chunks
-                            umma_f16_2cta_parts(d, a_lo + (uint32_t)ks * ((2 * G3_BM * 16) >> 4), a_hi,
-                                                b_lo + (uint32_t)ks * ((2 * LBO_B) >> 4), b_hi, idesc, (q | ks) ? 1u : 0u);
+                        for (int ks = 0; ks < 4; ks++)      // K = 16 per instruction: 8 TMEM columns of A, two 8-element K-chunks of B
+                            umma_f16_2cta_ts(d, a_t + ks * 8, b_lo + (uint32_t)ks * ((2 * LBO_B) >> 4), b_hi, idesc, (q | ks) ? 1u : 0u);
                         g3_commit_2cta(&bfree[q]);
+                        if (q & 1) g3_commit_2cta(&afree[q >> 1]);
                         if (q == 3) g3_commit_2cta(&accfull[as]);
                     }
                     __syncwarp();
@@ -407,109 +463,121 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
         }
       }
     } else if (warp < G3_EPI_WARP0) {
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 72;" ::: "memory");
-        // ===================== unpack: narrow operands -> fp16 =====================
-        const int uw = warp - G3_UNPACK_WARP0;
-        const int ut = threadIdx.x - G3_UNPACK_WARP0 * 32;          // 0..255
-        const int a_gg = ut >> 7, a_row = ut & 127;                  // activation items of this thread: (pair of 16-K chunks, token row)
-        const uint32_t bfull_leader = g3_mapa(smem_u32(bfull), 0);
-        // S / zero-point publisher role of the first NCOL threads: channel (half, j, c) of the pair's 16*NTL channels
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;" ::: "memory");
+        // ===================== unpack warps (16): activations -> TMEM, weights -> shared memory =====================
+        // Activations.  Every warp owns one (TMEM lane quarter, 16-column chunk) job per half k-tile: thread = token row,
+        // 32 bytes of fp16 high bytes -> 16 TMEM columns of packed fp16 pairs (tcgen05.st).  Going through registers instead
+        // of shared memory keeps 128 KB per k-tile (the fp16 stores and the tensor core's operand reads) off the
+        // shared-memory pipe.  Four warps per lane quarter share the work: one warp per quarter was the critical path.
+        // Weights.  Warps 4..15 of the 16 additionally convert one (group, channel) unit of 4 words per thread and half
+        // k-tile into the fp16 B operand; warps 0..3 forward the row factors a7/127 to the epilogue warps instead.
+        static_assert(8 * 16 * NTL == 2 * 2 * G3_UNPACK_WARPS * 32, "one weight unit per weight-warp thread and half k-tile");
+        const int w16 = warp - G3_AW_WARP0;                 // 0..15
+        const int a_c2 = w16 >> 2;                          // 16-column chunk of the half k-tile (32 bytes of every row)
+        const int row = (warp & 3) * 32 + lane;             // TMEM lane = token row of this CTA
+        const bool is_b = w16 >= G3_AW_WARPS;
+        const int uw = w16 - G3_AW_WARPS;                   // weight-warp index 0..11 (negative: activation-only warp)
+        const int ut = threadIdx.x - G3_UNPACK_WARP0 * 32;  // 0..383 for weight warps
+        const uint32_t afull_leader = g3_mapa(smem_u32(afull), 0);
+        const uint32_t ta = tmem + ((uint32_t)((warp & 3) * 32) << 16) + G3_TM_A0 + a_c2 * 16;
+        const int a_off = (2 * a_c2) * 2048 + row * 16;
+        // this thread's weight unit inside every half k-tile: quarter b_ql (warp-uniform: 6 warps per quarter), group b_gg of
+        // the quarter, channel b_ch; 4 words = 4 operand cells
+        const int b_ql = is_b ? ut / NCOL : 0, b_r = is_b ? ut - b_ql * NCOL : 0, b_gg = b_r / (8 * NTL), b_ch = b_r - b_gg * (8 * NTL);
+        const int src_off = G3_RAW_A + (b_ch >> 3) * 512 + (2 * b_ql + b_gg) * 128 + (b_ch & 7) * 16;
+        const int sc_off = G3_RAW_A + G3_RAW_W + ((int)rank * NTL + (b_ch >> 3)) * 160 + 32 + (b_ch & 7) * 8 + 2 * b_ql + b_gg;
+        const int dst_off = b_ql * G3_F_BYTES + (b_gg * 4) * LBO_B + b_ch * 16;
+        const uint32_t bfull_leader = g3_mapa(smem_u32(bfull), 0) + (uint32_t)b_ql * 8;
+        // S / zero-point publisher role of the first NCOL weight-warp threads: channel (half, j, c) of the pair's 16*NTL channels
         const int p_half = ut / (8 * NTL), p_j = (ut % (8 * NTL)) >> 3, p_c = ut & 7;
         const int p_off = G3_RAW_A + G3_RAW_W + (p_half * NTL + p_j) * 160;
-        const int own_meta = G3_RAW_A + G3_RAW_W + (int)rank * NTL * 160;
         int s = 0, u = 0, gk = 0;
         for (int t = cluster_id; t < num_tiles; t += num_clusters) {
             const G3Tile tl = g3_decode(P, t, MB2, KT, rank);
             for (int kt = tl.kt0; kt < tl.kt1; kt++, gk++) {
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
+                    if (w16 == 0) G3_STAMP(1, gk, 4 * h);
+                    if (uw == 0) G3_STAMP(2, gk, 4 * h);
                     g3_wait(&rawfull[s], (uint32_t)(u & 1));
+                    if (w16 == 0) G3_STAMP(1, gk, 4 * h + 1);
+                    if (uw == 0) G3_STAMP(2, gk, 4 * h + 1);
                     const uint8_t *stg = sRaw + s * G3_RAW_BYTES;
-                    if (h == 0 && uw < SN_WARPS) {      // per-channel super-scales of this k-tile for the epilogue warps
-                        float sv = 0.0f;
-                        int zf = 0;
-                        if (ut < NCOL) {
+                    const uint4 w0 = *reinterpret_cast<const uint4 *>(stg + a_off), w1 = *reinterpret_cast<const uint4 *>(stg + a_off + 2048);
+                    uint4 wb = make_uint4(0, 0, 0, 0);
+                    int sc = 0;
+                    if (is_b) {
+                        wb = *reinterpret_cast<const uint4 *>(stg + src_off);
+                        sc = *reinterpret_cast<const int8_t *>(stg + sc_off + 4 * h);
+                    }
+                    // ---- activations first: 32 bytes -> 16 TMEM columns, handed over at once (afull does not wait for the weights)
+                    if (gk > 0) {
+                        g3_wait(&afree[h], (uint32_t)((gk - 1) & 1));
+                        tc_fence_after();
+                    }
+                    if (w16 == 0) G3_STAMP(1, gk, 4 * h + 2);
+                    {
+                        uint4 c0, c1, c2v, c3;
+                        g3_cvt_act16(w0, c0, c1);
+                        g3_cvt_act16(w1, c2v, c3);
+                        const uint32_t r[16] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w,
+                                                c2v.x, c2v.y, c2v.z, c2v.w, c3.x, c3.y, c3.z, c3.w};
+                        g3_tmem_st_32x16(ta + h * G3_TM_A_COLS, r);
+                    }
+                    g3_tmem_st_wait();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) g3_arrive_cluster(afull_leader + (uint32_t)h * 8);
+                    if (!is_b) {
+                        if (h == 0) {      // the row factor a7 / 127 of this k-tile, for the epilogue warps
+                            const float a7v = *reinterpret_cast<const float *>(stg + G3_RAW_A + G3_RAW_W + G3_RAW_META + row * 4);
+                            sRm[(gk & (G3_SN_RING - 1)) * G3_BM + row] = a7v * (1.0f / 127.0f);
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(&snfull[gk & (G3_SN_RING - 1)]);
+                        }
+                    } else {
+                        if (h == 0 && uw < SN_WARPS) {      // per-channel super-scales of this k-tile
                             const uint8_t *md = stg + p_off;
-                            sv = __half2float(*reinterpret_cast<const __half *>(md + 2 * p_c));
+                            const float sv = __half2float(*reinterpret_cast<const __half *>(md + 2 * p_c));
                             const float zv = __half2float(*reinterpret_cast<const __half *>(md + 16 + 2 * p_c));
                             const uint2 zc = *reinterpret_cast<const uint2 *>(md + 96 + p_c * 8);
-                            zf = (zv != 0.0f) && ((zc.x | zc.y) != 0u);
+                            const int zf = (zv != 0.0f) && ((zc.x | zc.y) != 0u);
                             sSn[(gk & (G3_SN_RING - 1)) * G3_SN_STRIDE + ut] = sv;
+                            const int anyz = __any_sync(0xffffffffu, zf);
+                            __syncwarp();
+                            if (lane == 0) {
+                                sZflag[(gk & (G3_SN_RING - 1)) * 8 + uw] = anyz;
+                                mbar_arrive(&snfull[gk & (G3_SN_RING - 1)]);
+                            }
                         }
-                        const int anyz = __any_sync(0xffffffffu, zf);
-                        __syncwarp();
-                        if (lane == 0) {
-                            sZflag[(gk & (G3_SN_RING - 1)) * 8 + uw] = anyz;
-                            mbar_arrive(&snfull[gk & (G3_SN_RING - 1)]);
-                        }
+                        // ---- weights: 4 words -> 4 operand cells of the quarter this warp belongs to
+                        const __half sch = __int2half_rn(sc);
+                        const __half2 sc2h = __halves2half2(sch, sch);
+                        const __half2 c72h = __hmul2(sc2h, __float2half2_rn(-72.0f));      // exact: 72*sc = 8 * (9*sc), 9*sc < 2048
+                        const uint32_t sc2 = *reinterpret_cast<const uint32_t *>(&sc2h), c72 = *reinterpret_cast<const uint32_t *>(&c72h);
+                        if (gk > 0) g3_wait(&bfree[2 * h + b_ql], (uint32_t)((gk - 1) & 1));
+                        if (uw == 0) G3_STAMP(2, gk, 4 * h + 2);
+                        uint8_t *dst = sF + (2 * h) * G3_F_BYTES + dst_off;
+                        *reinterpret_cast<uint4 *>(dst) = g3_cvt_w(wb.x, sc2, c72);
+                        *reinterpret_cast<uint4 *>(dst + 1 * LBO_B) = g3_cvt_w(wb.y, sc2, c72);
+                        *reinterpret_cast<uint4 *>(dst + 2 * LBO_B) = g3_cvt_w(wb.z, sc2, c72);
+                        *reinterpret_cast<uint4 *>(dst + 3 * LBO_B) = g3_cvt_w(wb.w, sc2, c72);
+                        fence_proxy_async_smem();
                     }
-                    // ---- all raw words of this half k-tile are fetched up front (4 + up to 2 LDS.128) ...
-                    // activations: per quarter two 16-K chunks (= 4 operand cells) of one token row
-                    uint4 wa[2][2];
-#pragma unroll
-                    for (int ql = 0; ql < 2; ql++)
-#pragma unroll
-                        for (int j = 0; j < 2; j++)
-                            wa[ql][j] = *reinterpret_cast<const uint4 *>(stg + (4 * ql + 2 * a_gg + j) * 2048 + a_row * 16);
-                    // weights: (group, channel) units of 4 words, dealt round-robin over the k-tile's 4 quarters so that every
-                    // thread converts 4 * NCOL / 256 = 3 units per k-tile (NTL = 12)
-                    uint4 wb[2];
-                    int sc[2], w_dst[2];
-                    bool has_w[2];
-#pragma unroll
-                    for (int ql = 0; ql < 2; ql++) {
-                        const int q = 2 * h + ql;
-                        const int v = (ut - q * NCOL) & 255;
-                        has_w[ql] = v < NCOL;
-                        const int w_gg = v / (8 * NTL), w_ch = v - w_gg * (8 * NTL);
-                        w_dst[ql] = (w_gg * 4) * LBO_B + w_ch * 16;
-                        wb[ql] = make_uint4(0, 0, 0, 0);
-                        sc[ql] = 0;
-                        if (has_w[ql]) {
-                            wb[ql] = *reinterpret_cast<const uint4 *>(stg + G3_RAW_A + (w_ch >> 3) * 512 + (2 * ql + w_gg) * 128 + (w_ch & 7) * 16);
-                            sc[ql] = *reinterpret_cast<const int8_t *>(stg + own_meta + (w_ch >> 3) * 160 + 32 + (w_ch & 7) * 8 + (4 * h + 2 * ql + w_gg));
-                        }
-                    }
-                    // ---- ... then both quarters are converted and stored, one proxy fence and one hand-over for the half
-#pragma unroll
-                    for (int ql = 0; ql < 2; ql++) {
-                        const int q = 2 * h + ql;                     // quarter of the k-tile = fp16 stage
-                        uint8_t *fA = sF + q * G3_F_BYTES, *fB = fA + G3_F_A;
-                        if (gk > 0) g3_wait(&bfree[q], (uint32_t)((gk - 1) & 1));
-#pragma unroll
-                        for (int j = 0; j < 2; j++) {
-                            uint4 c0, c1;
-                            g3_cvt_act16(wa[ql][j], c0, c1);
-                            uint8_t *dst = fA + ((2 * a_gg + j) * 2) * (G3_BM * 16) + a_row * 16;
-                            *reinterpret_cast<uint4 *>(dst) = c0;
-                            *reinterpret_cast<uint4 *>(dst + G3_BM * 16) = c1;
-                        }
-                        if (has_w[ql]) {
-                            const __half sch = __int2half_rn(sc[ql]);
-                            const __half2 sc2h = __halves2half2(sch, sch);
-                            const __half2 c72h = __hmul2(sc2h, __float2half2_rn(-72.0f));      // exact: 72*sc = 8 * (9*sc), 9*sc < 2048
-                            const uint32_t sc2 = *reinterpret_cast<const uint32_t *>(&sc2h), c72 = *reinterpret_cast<const uint32_t *>(&c72h);
-                            uint8_t *dst = fB + w_dst[ql];
-                            *reinterpret_cast<uint4 *>(dst) = g3_cvt_w(wb[ql].x, sc2, c72);
-                            *reinterpret_cast<uint4 *>(dst + 1 * LBO_B) = g3_cvt_w(wb[ql].y, sc2, c72);
-                            *reinterpret_cast<uint4 *>(dst + 2 * LBO_B) = g3_cvt_w(wb[ql].z, sc2, c72);
-                            *reinterpret_cast<uint4 *>(dst + 3 * LBO_B) = g3_cvt_w(wb[ql].w, sc2, c72);
-                        }
-                    }
-                    fence_proxy_async_smem();
                     __syncwarp();
                     if (lane == 0) {
-                        g3_arrive_cluster(bfull_leader + (uint32_t)(2 * h) * 8);
-                        g3_arrive_cluster(bfull_leader + (uint32_t)(2 * h + 1) * 8);
+                        if (is_b) g3_arrive_cluster(bfull_leader + (uint32_t)(2 * h) * 8);
                         mbar_arrive(&rawempty[s]);       // after the __syncwarp: every lane has read its raw bytes
                     }
+                    if (w16 == 0) G3_STAMP(1, gk, 4 * h + 3);
+                    if (uw == 0) G3_STAMP(2, gk, 4 * h + 3);
                     if (++s == G3_RAW_STAGES) { s = 0; u++; }
                 }
             }
         }
     } else {
         // ===================== epilogue =====================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 144;" ::: "memory");
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 152;" ::: "memory");
         pdl_wait();                                          // a7 / res come from, and y may be read by, earlier kernels
         const int ew = warp - G3_EPI_WARP0;                 // 0..7
         const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
@@ -526,8 +594,6 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
             const bool mvalid = m < M;
             const int N = P.N[tl.sg];
             const int n_base = (tl.cbl * (2 * NTL) + colhalf * NTL) * TILE_CH;
-            const float *a7p = st.a7 + (size_t)(mvalid ? m : 0) * KT;
-            float a7 = mvalid ? __ldcg(a7p + tl.kt0) : 0.0f;      // its latency hides under the wait for the first accumulator
 #pragma unroll
             for (int i = 0; i < 4 * NTL; i++) acc2[i] = 0ull;
             if (ADD && tl.ks == 0 && (P.bias != nullptr || (P.res != nullptr && !P.res_in_y))) {
@@ -555,52 +621,57 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
             }
             for (int kt = tl.kt0; kt < tl.kt1; kt++, gk++) {
                 const int as = gk & 1, u2 = gk >> 1;
-                const float rm = a7 * (1.0f / 127.0f);          // row factor a7/127; column factor S[n]
-                const float a7_cur = a7;
-                if (kt + 1 < tl.kt1 && mvalid) a7 = __ldcg(a7p + kt + 1);     // next block's scale: hides under this block
-                const uint64_t rm2 = g3_pack(rm, rm);
                 const int ring = gk & (G3_SN_RING - 1);
+                if (ew == 0) G3_STAMP(3, gk, 0);
                 g3_wait(&snfull[ring], (uint32_t)((gk / G3_SN_RING) & 1));
                 g3_wait(&accfull[as], (uint32_t)(u2 & 1));
+                if (ew == 0) G3_STAMP(3, gk, 1);
                 tc_fence_after();
+                const float rm = sRm[ring * G3_BM + row];       // row factor a7/127 (activation warps); column factor S[n]
+                const uint64_t rm2 = g3_pack(rm, rm);
                 const float *sn = sSn + ring * G3_SN_STRIDE + colhalf * (8 * NTL);
                 int anyz = 0;
 #pragma unroll
                 for (int i = 0; i < SN_WARPS; i++) anyz |= sZflag[ring * 8 + i];
-                const uint32_t t0 = t_base + as * 256;
-                // one n-tile (8 columns) per step, two TMEM loads in flight: the register budget (96 accumulators + 16 + 8)
-                // is what lets the unpack warps keep 80 registers each
-                uint32_t r[2][8];
-                tmem_ld_32x8(t0, r[0]);
+                const uint32_t t0 = t_base + as * G3_TM_D_STRIDE;
+                // 32 columns per TMEM load.  tcgen05.wait::ld waits for ALL loads of the thread, so loads cannot be pipelined
+                // behind each other: the read phase costs (load latency + math) per chunk, and it must stay below the k-tile's
+                // MMA time or the two accumulator stages stall the tensor pipe (8-column chunks: 12 x ~250 cycles of latency
+                // per k-tile WAS the kernel's period).  Three chunks of 32 columns, one staging buffer.
+                uint32_t r[32];
 #pragma unroll
-                for (int c = 0; c < NTL; c++) {
-                    // S[] of this k-tile is read BEFORE the accumulator stage is handed back (ring slot reuse: the unpack
-                    // warps may be up to G3_SN_RING - 1 k-tiles ahead only while an accumulator stage is still held)
-                    const ulonglong2 s01 = *reinterpret_cast<const ulonglong2 *>(sn + c * 8);
-                    const ulonglong2 s23 = *reinterpret_cast<const ulonglong2 *>(sn + c * 8 + 4);
-                    tmem_ld_wait();                  // chunk c has landed
-                    if (c + 1 < NTL) {
-                        tmem_ld_32x8(t0 + (c + 1) * 8, r[(c + 1) & 1]);
-                    } else {                         // all TMEM reads of this stage are done: hand it back
+                for (int c = 0; c < NTL / 4; c++) {
+                    tmem_ld_32x32(t0 + c * 32, r);
+                    // (S[] and the row factor of this k-tile may still be read after the hand-back below: the weight warps
+                    // run at most 4 k-tiles ahead of the last accumulator stage released, the rings hold 8)
+                    tmem_ld_wait();
+                    if (c + 1 == NTL / 4) {          // all TMEM reads of this stage are done: hand it back
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0) g3_arrive_cluster(accempty_leader + (uint32_t)as * 8);
+                        if (ew == 0) G3_STAMP(3, gk, 2);
                     }
-                    const uint64_t sv2[4] = {s01.x, s01.y, s23.x, s23.y};
 #pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const float f0 = __uint_as_float(r[c & 1][2 * i]), f1 = __uint_as_float(r[c & 1][2 * i + 1]);   // = sum_g sc*dot, exact integers
-                        const uint64_t f2 = g3_mul2(g3_pack(f0, f1), rm2);
-                        acc2[c * 4 + i] = g3_fma2(f2, sv2[i], acc2[c * 4 + i]);
-                        if (DEBUG) {
-                            const int n = n_base + c * 8 + 2 * i;
-                            if (dbg_isum && mvalid && n < N) {
-                                dbg_isum[((size_t)m * N + n) * KT + kt] = (int)f0;
-                                dbg_isum[((size_t)m * N + n + 1) * KT + kt] = (int)f1;
+                    for (int j = 0; j < 4; j++) {    // 8 columns per step
+                        const ulonglong2 sa = *reinterpret_cast<const ulonglong2 *>(sn + c * 32 + j * 8);
+                        const ulonglong2 sb = *reinterpret_cast<const ulonglong2 *>(sn + c * 32 + j * 8 + 4);
+                        const uint64_t sv2[4] = {sa.x, sa.y, sb.x, sb.y};
+#pragma unroll
+                        for (int i = 0; i < 4; i++) {
+                            const float f0 = __uint_as_float(r[j * 8 + 2 * i]), f1 = __uint_as_float(r[j * 8 + 2 * i + 1]);   // = sum_g sc*dot, exact integers
+                            const uint64_t f2 = g3_mul2(g3_pack(f0, f1), rm2);
+                            acc2[c * 16 + j * 4 + i] = g3_fma2(f2, sv2[i], acc2[c * 16 + j * 4 + i]);
+                            if (DEBUG) {
+                                const int n = n_base + c * 32 + j * 8 + 2 * i;
+                                if (dbg_isum && mvalid && n < N) {
+                                    dbg_isum[((size_t)m * N + n) * KT + kt] = (int)f0;
+                                    dbg_isum[((size_t)m * N + n + 1) * KT + kt] = (int)f1;
+                                }
                             }
                         }
                     }
                 }
+                if (ew == 0) G3_STAMP(3, gk, 3);
                 if (anyz && mvalid) {
 #pragma unroll
                     for (int i = 0; i < 4 * NTL; i++) {      // unrolled although cold: a dynamic index would put acc2[] in local memory
@@ -608,6 +679,7 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
                         if (n < N) {
                             float a, b;
                             g3_unpack(acc2[i], a, b);
+                            const float a7_cur = st.a7[(size_t)m * KT + kt];
                             a += g3_zero_point_term(P.w[tl.sg], st.sumq, m, n, kt, KT, a7_cur);
                             b += g3_zero_point_term(P.w[tl.sg], st.sumq, m, n + 1, kt, KT, a7_cur);
                             acc2[i] = g3_pack(a, b);
@@ -752,6 +824,13 @@ static bool g3_y_map(CUtensorMap *map, float *y, int64_t M, int64_t N, int64_t l
 template <int NTL>
 static cudaError_t launch_gemm3_t(cudaLaunchConfig_t *cfg, G3Params &P, ActStage st, int64_t M, int64_t K, int MB2,
                                   int num_tiles, int32_t *dbg_isum) {
+#ifdef TCQ4_DIAG
+    static const bool prof = getenv("TCQ4_G3_PROF") != nullptr;
+    if (prof && !dbg_isum && !P.res && !P.bias) {
+        cudaFuncSetAttribute(tcq4_gemm3_kernel<NTL, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm3Smem::total);
+        return cudaLaunchKernelEx(cfg, tcq4_gemm3_kernel<NTL, false, false, true>, P, st, (int)M, (int)K, MB2, num_tiles, (int32_t *)nullptr);
+    }
+#endif
     if (dbg_isum)
         return cudaLaunchKernelEx(cfg, tcq4_gemm3_kernel<NTL, true, false>, P, st, (int)M, (int)K, MB2, num_tiles, dbg_isum);
     if (P.res != nullptr || P.bias != nullptr)
@@ -805,6 +884,15 @@ cudaError_t launch_gemm3(const Gemm3Seg *segs, int nseg, ActStage st, int64_t M,
         case 12: return launch_gemm3_t<12>(&cfg, P, st, M, K, MB2, plan.num_tiles, dbg_isum);
         default: return cudaErrorInvalidValue;
     }
+}
+
+cudaError_t gemm3_read_prof(long long *host_out, size_t bytes) {
+#ifdef TCQ4_DIAG
+    return cudaMemcpyFromSymbol(host_out, g_g3_prof, bytes < sizeof(g_g3_prof) ? bytes : sizeof(g_g3_prof));
+#else
+    (void)host_out; (void)bytes;
+    return cudaErrorNotSupported;
+#endif
 }
 
 cudaError_t gemm3_init_attributes(size_t smem_optin) {

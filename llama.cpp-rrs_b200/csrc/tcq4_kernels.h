@@ -123,6 +123,7 @@ struct Gemm3Plan {
 bool        gemm3_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, size_t smem_optin, bool allow_split,
                        Gemm3Plan *plan);
 cudaError_t gemm3_init_attributes(size_t smem_optin);
+cudaError_t gemm3_read_prof(long long *host_out, size_t bytes);           // PROF-instantiation timeline stamps (diagnostics build)
 cudaError_t launch_gemm3(const Gemm3Seg *segs, int nseg, ActStage st, int64_t M, int64_t K, const Gemm3Plan &plan,
                          int32_t *dbg_isum, cudaStream_t stream, const float *res = nullptr, const float *bias = nullptr);
 
