@@ -49,11 +49,7 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
         // ld.global.cg: every element is read once, and under programmatic stream serialization a stale L1 line of x
         // could survive from an overlapping predecessor
         rrs_load_block_cg(x + (size_t)m * K, perm, kt, lane, v);
-        ActQuantT a = rrs_quantize_block_t<true>(v, lane, scratch);
-        if (MODE == MODE_NIB) {      // the byte that travels is the high byte of fp16(q) (exact: |q| <= 7 needs 2 mantissa bits)
-#pragma unroll
-            for (int g = 0; g < 8; g++) a.q[g] = (int)(__half_as_ushort(__int2half_rn(a.q[g])) >> 8);
-        }
+        const ActQuantT a = rrs_quantize_block_t<true>(v, lane, scratch);
         const uint2 e = rrs_codes_layout_a(a, lane, scratch);        // byte r = code of element lane*8 + r
         int gs = 0;                                                  // lane g < 8 keeps the sum of group g
 #pragma unroll
@@ -71,12 +67,13 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
             if (lane < 8) blk->sum_q[lane] = (int16_t)gs;
             if (lane < 3) reinterpret_cast<uint32_t *>(blk->pad)[lane] = 0u;
         } else if (MODE == MODE_NIB) {
-            // fp16 high bytes (tcq4_common.cuh, ACT_B8_UNIT_BYTES): lane l owns operand cell l of the block
-            // (chunk of 16 K = l >> 1, half l & 1), bytes in the order (0,4,1,5,2,6,3,7)
+            // u = q + 8 as nibbles, element i of the lane's 8-slice at bits [4i, 4i+4): word (lane & 3) of group lane >> 2
+            const uint32_t t0 = (e.x ^ 0x08080808u) & 0x0F0F0F0Fu, t1 = (e.y ^ 0x08080808u) & 0x0F0F0F0Fu;
+            const uint32_t p0 = t0 | (t0 >> 4), p1 = t1 | (t1 >> 4);        // bytes 0 and 2 hold two nibbles each
+            const uint32_t w = __byte_perm(p0, p1, 0x6420);
             const int mb = m >> 7, r = m & 127;
-            int8_t *unit = st.codes + ((size_t)mb * KT + kt) * ACT_B8_UNIT_BYTES;
-            *reinterpret_cast<uint2 *>(unit + (lane >> 1) * 2048 + r * 16 + (lane & 1) * 8) =
-                make_uint2(__byte_perm(e.x, e.y, 0x5140), __byte_perm(e.x, e.y, 0x7362));
+            int8_t *unit = st.codes + ((size_t)mb * KT + kt) * ACT_NIB_UNIT_BYTES;
+            *reinterpret_cast<uint32_t *>(unit + (lane >> 2) * 2048 + r * 16 + (lane & 3) * 4) = w;
             if (lane == 0) {
                 const float a7 = __fdiv_rn(a.max_abs, 7.0f);
                 st.a7[b] = a7;

@@ -50,16 +50,16 @@ constexpr int ACT_UNIT_BYTES = 128 * 256;
 constexpr int ACT_LBO        = 2048;
 constexpr int ACT_SBO        = 128;
 
-// ---- GEMM activation staging, fp16-high-byte form (tcq4_gemm3.cu) ---------------------------------
-// Every integer in [-7, 7] is an fp16 number whose low byte is zero (two mantissa bits suffice: 5 = 1.25*4, 7 = 1.75*4),
-// so ONE byte per code -- the high byte of its fp16 representation -- travels, and the SM widens it with a byte permute
-// (no arithmetic).  For every (m-block of 128 rows, k-tile) one 32 KB unit [16 chunks of 16 K][128 rows][16 B]; the 16
-// bytes are two operand cells of 8 elements each, inside a cell in the order (0,4,1,5,2,6,3,7) -- the order the weight
-// unpack of tcq4_gemm3.cu produces for free.
-constexpr int ACT_B8_UNIT_BYTES = 128 * 256;
+// ---- GEMM activation staging, nibble form (tcq4_gemm3.cu) -------------------------------------
+// For every (m-block of 128 rows, k-tile) one 16 KB unit [8 groups][128 rows][16 B]: the 16 bytes are the four
+// 32-bit words of the row's 32-group, word s = elements s*8 .. s*8+7, element i at bits [4i, 4i+4) as u = q + 8 in
+// [1, 15] -- the weight tiles' own nibble order, so the same widening trick serves both operands.  Half the bytes of an
+// s8 unit: the L2 -> SM fabric and the depth of the copy ring (bytes in flight = bandwidth x latency) are what bound the
+// GEMM's operand supply, not the extra ALU work of widening nibbles.
+constexpr int ACT_NIB_UNIT_BYTES = 128 * 128;
 
 struct ActStage {           // pointers into the caller's workspace
-    int8_t  *codes;         // [MB][KT][32 KB] s8 units, or the fp16-high-byte units of tcq4_gemm3.cu (same size, same region)
+    int8_t  *codes;         // [MB][KT][32 KB] s8 units, or [MB][KT][16 KB] nibble units (tcq4_gemm3.cu; same region)
     float   *a7;            // [M][KT]      max_abs / 7
     int16_t *sumq;          // [M][KT][8]   per-group code sums (zero-point term)
     float   *a7t;           // [MB][KT][128] the same scales, contiguous per (128-row block, k-tile): one 512-byte bulk copy

@@ -51,29 +51,32 @@ namespace tcq4 {
 
 constexpr int G3_BM = 128;                               // tokens per CTA (256 per pair)
 constexpr int G3_MAXNTL = 12;                            // n-tiles (8 channels) unpacked per CTA
-constexpr int G3_AW_WARP0 = 4, G3_AW_WARPS = 4;          // activation warps: thread = token row, fp16 codes -> TMEM
-constexpr int G3_UNPACK_WARP0 = G3_AW_WARP0 + G3_AW_WARPS, G3_UNPACK_WARPS = 12;     // weight warps: one (group, channel) unit per thread and half k-tile
+constexpr int G3_AW_WARP0 = 4, G3_AW_WARPS = 8;          // activation warps: two per TMEM lane quarter (thread = token row)
+constexpr int G3_UNPACK_WARP0 = G3_AW_WARP0 + G3_AW_WARPS, G3_UNPACK_WARPS = 12;     // weight warps: two (group, channel) units per thread and k-tile
 constexpr int G3_EPI_WARP0 = G3_UNPACK_WARP0 + G3_UNPACK_WARPS, G3_EPI_WARPS = 8;
-constexpr int G3_THREADS = (G3_EPI_WARP0 + G3_EPI_WARPS) * 32;          // 896
+constexpr int G3_THREADS = (G3_EPI_WARP0 + G3_EPI_WARPS) * 32;          // 1024
 
-constexpr int G3_RAW_A = ACT_B8_UNIT_BYTES / 2;          // 16384: half a k-tile (128 K) of activation bytes
-constexpr int G3_RAW_W = G3_MAXNTL * 512;                // 6144: the same 4 groups of this CTA's NTL tiles
+// one raw stage = one k-tile of this CTA's inputs
+constexpr int G3_RAW_A = ACT_NIB_UNIT_BYTES;             // 16384: activation nibbles [8 groups][128 rows][16 B]
+constexpr int G3_RAW_W = G3_MAXNTL * 1024;               // 12288: the nibbles of this CTA's NTL tiles
 constexpr int G3_RAW_META = 2 * G3_MAXNTL * 160;         // 3840: S, Z, sc, zc of the pair's 2*NTL tiles
 constexpr int G3_RAW_A7 = G3_BM * 4;                     // 512: a7 of this CTA's 128 rows for the k-tile
-constexpr int G3_RAW_BYTES = G3_RAW_A + G3_RAW_W + G3_RAW_META + G3_RAW_A7;      // 26880
-constexpr int G3_RAW_STAGES = 5;
-constexpr int G3_F_B = 8 * 8 * G3_MAXNTL * 16;           // 12288: quarter k-tile (64 K) of this CTA's 8*NTL channels in fp16
-constexpr int G3_F_BYTES = G3_F_B;
-constexpr int G3_F_STAGES = 4;                           // = quarters per k-tile: stage index = quarter
+constexpr int G3_RAW_BYTES = G3_RAW_A + G3_RAW_W + G3_RAW_META + G3_RAW_A7;      // 33024
+// bytes in flight = bandwidth x latency: ~1.3 us of L2 latency under load at 33 KB per k-tile (0.8 us) needs two stages in
+// flight besides the one being read (two stages of a fatter unit WAS the kernel's period: what-if runs, tests/gpu_g3_exp.py)
+constexpr int G3_RAW_STAGES = 3;
+constexpr int G3_F_Q = 8 * 8 * G3_MAXNTL * 16;           // 12288: quarter k-tile (64 K) of this CTA's 8*NTL channels in fp16
+constexpr int G3_F_BYTES = 4 * G3_F_Q;                   // 49152: one k-tile of the fp16 B operand
+constexpr int G3_F_STAGES = 2;                           // the weight warps run up to two k-tiles ahead of the tensor pipe
 constexpr int G3_SN_RING = 8;
 constexpr int G3_SN_STRIDE = 16 * G3_MAXNTL;             // floats per ring slot
 constexpr int G3_OUT_BOXES = 2;
-// TMEM columns: two fp32 accumulator stages of 16*NTL columns, then two half-k-tile buffers of fp16 activations
-// (128 K = 64 columns of packed pairs each)
+// TMEM columns: two fp32 accumulator stages of 16*NTL columns, then four quarter-k-tile buffers of fp16 activations
+// (64 K = 32 columns of packed pairs each)
 constexpr int G3_TM_D_STRIDE = 16 * G3_MAXNTL;           // 192
 constexpr int G3_TM_A0 = 2 * G3_TM_D_STRIDE;             // 384
-constexpr int G3_TM_A_COLS = 64;
-static_assert(G3_TM_A0 + 2 * G3_TM_A_COLS <= 512, "TMEM budget");
+constexpr int G3_TM_A_COLS = 32;
+static_assert(G3_TM_A0 + 4 * G3_TM_A_COLS <= 512, "TMEM budget");
 
 struct Gemm3Smem {
     static constexpr int off_f = 0;
@@ -83,11 +86,11 @@ struct Gemm3Smem {
     static constexpr int off_out = off_rm + G3_SN_RING * G3_BM * 4;
     static constexpr int off_zflag = off_out + G3_EPI_WARPS * G3_OUT_BOXES * 1024;
     static constexpr int off_bar = off_zflag + G3_SN_RING * 8 * 4;
-    static constexpr int n_bar = 2 * G3_RAW_STAGES + 2 * G3_F_STAGES + 2 + 2 + 2 + 2 + G3_SN_RING;
+    static constexpr int n_bar = 2 * G3_RAW_STAGES + 2 * G3_F_STAGES + 2 + 2 + 4 + 4 + G3_SN_RING;
     static constexpr int off_tmem = off_bar + n_bar * 8;
     static constexpr int total = off_tmem + 16;
 };
-static_assert(G3_RAW_BYTES % 128 == 0 && G3_F_BYTES % 128 == 0 && Gemm3Smem::off_raw % 128 == 0 && Gemm3Smem::off_sn % 16 == 0 &&
+static_assert(G3_RAW_BYTES % 128 == 0 && G3_F_BYTES % 128 == 0 && G3_F_Q % 128 == 0 && Gemm3Smem::off_raw % 128 == 0 && Gemm3Smem::off_sn % 16 == 0 &&
                   Gemm3Smem::off_out % 128 == 0 && (G3_RAW_A + G3_RAW_W) % 128 == 0,
               "operands, copy destinations and store boxes must be 128-byte aligned");
 static_assert(Gemm3Smem::off_bar % 8 == 0, "barriers must be 8-byte aligned");
@@ -116,6 +119,16 @@ __device__ __forceinline__ void g3_wait(uint64_t *bar, uint32_t parity) {
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
         "@!p bra G3_WAIT_%=;\n\t}" ::"r"(smem_u32(bar)),
         "r"(parity), "r"(20000u)
+        : "memory");
+}
+// Busy poll (no suspend): for the few threads whose wake-up latency is on the critical path of the tensor pipe
+__device__ __forceinline__ void g3_spin(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "G3_SPIN_%=:\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@!p bra G3_SPIN_%=;\n\t}" ::"r"(smem_u32(bar)),
+        "r"(parity)
         : "memory");
 }
 __device__ __forceinline__ void g3_cluster_sync() {
@@ -190,6 +203,16 @@ __device__ __forceinline__ uint32_t g3_hfma2(uint32_t a, uint32_t b, uint32_t c)
 // representable result.  Order of the 8 values inside the 16-byte operand cell: elements (0,4,1,5,2,6,3,7); the
 // activation kernel writes its bytes in the same order, which is all the MMA needs.
 constexpr uint32_t G3_MAGIC = 0x54005400u;      // (64.0, 64.0)
+// activation nibbles (u = q + 8 stored by K1, element i at bits [4i, 4i+4)) -> 8 fp16 values q in the cell order
+__device__ __forceinline__ uint4 g3_cvt_act(uint32_t w) {
+    constexpr uint32_t K16 = 0x4C004C00u, KM1032 = 0xE408E408u, K1 = 0x3C003C00u, KM72 = 0xD480D480u;
+    const uint32_t hi = w >> 8;
+    const uint32_t t0 = (w & 0x000F000Fu) | G3_MAGIC;       // 64 + u/16 : elements 0, 4
+    const uint32_t t1 = (w & 0x00F000F0u) | G3_MAGIC;       // 64 + u    : elements 1, 5
+    const uint32_t t2 = (hi & 0x000F000Fu) | G3_MAGIC;      //             elements 2, 6
+    const uint32_t t3 = (hi & 0x00F000F0u) | G3_MAGIC;      //             elements 3, 7
+    return make_uint4(g3_hfma2(t0, K16, KM1032), g3_hfma2(t1, K1, KM72), g3_hfma2(t2, K16, KM1032), g3_hfma2(t3, K1, KM72));
+}
 // 16 activation bytes (two operand cells) -> 16 fp16: byte b becomes the half (b << 8)
 __device__ __forceinline__ void g3_cvt_act16(const uint4 w, uint4 &c0, uint4 &c1) {
     c0 = make_uint4(__byte_perm(w.x, 0u, 0x1404), __byte_perm(w.x, 0u, 0x3424), __byte_perm(w.y, 0u, 0x1404), __byte_perm(w.y, 0u, 0x3424));
@@ -259,7 +282,7 @@ __device__ __forceinline__ void g3_store_wait_read() {
 // ---- kernel parameters -------------------------------------------------------------------------------------------
 constexpr int G3_MAX_SEG = 4;
 struct G3Seg {
-    CUtensorMap tm_tiles;      // [NT rows][KT*148 8-byte words], box {64 words = 4 groups of nibbles, NTL rows}
+    CUtensorMap tm_tiles;      // [NT rows][KT*148 8-byte words], box {128 words = the 1024 bytes of nibbles, NTL rows}
     CUtensorMap tm_meta;       // same tensor, box {20 words = S, Z, sc, zc, 2*NTL rows}
     CUtensorMap tm_y;          // fp32 [M][ldc], box {8 channels, 32 rows}
 };
@@ -273,6 +296,7 @@ struct G3Params {
     const float *res;          // ADD: [M][N] contiguous or null (single segment only); may alias y
     const float *bias;         // ADD: [N] or null
     int res_in_y;              // ADD with ksplit > 1 and res == y: y already holds the residual, nothing to pre-add
+    int exp;                   // diagnostics (PROF instantiation only): bit 0 skip epilogue math, 1 skip activation conversion, 2 skip weight conversion
 };
 
 struct G3Tile {
@@ -332,27 +356,27 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + Gemm3Smem::off_bar);
     uint64_t *rawfull = bars, *rawempty = rawfull + G3_RAW_STAGES, *bfull = rawempty + G3_RAW_STAGES,
              *bfree = bfull + G3_F_STAGES, *accfull = bfree + G3_F_STAGES, *accempty = accfull + 2, *afull = accempty + 2,
-             *afree = afull + 2, *snfull = afree + 2;
+             *afree = afull + 4, *snfull = afree + 4;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + Gemm3Smem::off_tmem);
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < G3_RAW_STAGES; i++) {
             mbar_init(&rawfull[i], 1);
-            mbar_init(&rawempty[i], G3_UNPACK_WARPS + G3_AW_WARPS);
+            mbar_init(&rawempty[i], G3_UNPACK_WARPS + G3_AW_WARPS);      // every unpack warp releases the k-tile's raw stage once
         }
         for (int i = 0; i < G3_F_STAGES; i++) {
-            mbar_init(&bfull[i], G3_UNPACK_WARPS);               // the half of the weight warps that owns this quarter, both CTAs (used in the leader)
+            mbar_init(&bfull[i], 2 * G3_UNPACK_WARPS);           // weight warps of both CTAs (used in the leader)
             mbar_init(&bfree[i], 1);                             // leader's commit (multicast)
         }
         for (int i = 0; i < 2; i++) {
             mbar_init(&accfull[i], 1);                           // leader's commit (multicast)
             mbar_init(&accempty[i], 2 * G3_EPI_WARPS);           // epilogue warps of both CTAs (used in the leader)
         }
-        for (int i = 0; i < 2; i++) {
-            mbar_init(&afull[i], 2 * (G3_AW_WARPS + G3_UNPACK_WARPS));      // all 16 unpack warps of both CTAs (used in the leader)
+        for (int i = 0; i < 4; i++) {
+            mbar_init(&afull[i], G3_AW_WARPS);                   // the four activation warps that own this quarter, both CTAs (leader)
             mbar_init(&afree[i], 1);                             // leader's commit (multicast)
         }
-        for (int i = 0; i < G3_SN_RING; i++) mbar_init(&snfull[i], SN_WARPS + G3_AW_WARPS);      // S by weight warps, a7/127 by activation warps
+        for (int i = 0; i < G3_SN_RING; i++) mbar_init(&snfull[i], SN_WARPS + 4);      // S by weight warps, a7/127 by four activation warps
         fence_mbar_init();
     }
     if (warp == 0 && lane == 0) {
@@ -378,13 +402,13 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
     // while the activation kernel in front of this launch is still finishing.
 
     if (warp < G3_AW_WARP0) {
-      asm volatile("setmaxnreg.dec.sync.aligned.u32 40;" ::: "memory");
+      asm volatile("setmaxnreg.dec.sync.aligned.u32 48;" ::: "memory");
       if (warp == 0) {
-        // ===================== producer: three copies per half k-tile =====================
+        // ===================== producer: four copies per k-tile =====================
         if (lane == 0) {
-            constexpr uint32_t total_tx = (uint32_t)(G3_RAW_A + NTL * 512 + 2 * NTL * 160 + G3_RAW_A7);
+            constexpr uint32_t total_tx = (uint32_t)(G3_RAW_A + NTL * 1024 + 2 * NTL * 160 + G3_RAW_A7);
             const uint64_t pol_w = l2_policy_evict_first();
-            // pass 0: the weight copies of the first G3_RAW_STAGES stages (nothing to wait for); then griddepcontrol.wait;
+            // pass 0: the weight copies of the first G3_RAW_STAGES k-tiles (nothing to wait for); then griddepcontrol.wait;
             // pass 1: everything else in ring order
 #pragma unroll 1
             for (int pass = 0; pass < 2; pass++) {
@@ -393,30 +417,27 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
                 for (int t = cluster_id; t < num_tiles && !done; t += num_clusters) {
                     const G3Tile tl = g3_decode(P, t, MB2, KT, rank);
                     const int nt_pair = tl.cbl * (2 * NTL), nt0 = nt_pair + (int)rank * NTL;
-                    const uint8_t *a_src = reinterpret_cast<const uint8_t *>(st.codes) + (size_t)tl.mb * KT * ACT_B8_UNIT_BYTES;
+                    const uint8_t *a_src = reinterpret_cast<const uint8_t *>(st.codes) + (size_t)tl.mb * KT * ACT_NIB_UNIT_BYTES;
                     const float *a7_src = st.a7t + (size_t)tl.mb * KT * G3_BM;
                     const CUtensorMap *mt = &P.seg[tl.sg].tm_tiles, *mm = &P.seg[tl.sg].tm_meta;
-                    for (int kt = tl.kt0; kt < tl.kt1 && !done; kt++) {
 #pragma unroll 1
-                        for (int h = 0; h < 2; h++, i++) {
-                            if (pass == 0 && i >= G3_RAW_STAGES) {
-                                done = true;
-                                break;
-                            }
-                            uint8_t *stg = sRaw + s * G3_RAW_BYTES;
-                            const bool weights_now = (pass == 0) || (i >= G3_RAW_STAGES);
-                            if (weights_now) {
-                                if (u > 0) g3_wait(&rawempty[s], (uint32_t)((u - 1) & 1));
-                                mbar_arrive_expect_tx(&rawfull[s], total_tx);
-                                g3_tma_2d_hint(stg + G3_RAW_A, mt, kt * (TILE_BYTES / 8) + h * 64, nt0, &rawfull[s], pol_w);
-                                g3_tma_2d(stg + G3_RAW_A + G3_RAW_W, mm, kt * (TILE_BYTES / 8) + TILE_NIB / 8, nt_pair, &rawfull[s]);
-                            }
-                            if (pass == 1) {
-                                bulk_g2s(stg, a_src + (size_t)kt * ACT_B8_UNIT_BYTES + h * G3_RAW_A, G3_RAW_A, &rawfull[s]);
-                                bulk_g2s(stg + G3_RAW_A + G3_RAW_W + G3_RAW_META, a7_src + (size_t)kt * G3_BM, G3_RAW_A7, &rawfull[s]);
-                            }
-                            if (++s == G3_RAW_STAGES) { s = 0; u++; }
+                    for (int kt = tl.kt0; kt < tl.kt1; kt++, i++) {
+                        if (pass == 0 && i >= G3_RAW_STAGES) {
+                            done = true;
+                            break;
                         }
+                        uint8_t *stg = sRaw + s * G3_RAW_BYTES;
+                        if (pass == 0 || i >= G3_RAW_STAGES) {
+                            if (u > 0) g3_wait(&rawempty[s], (uint32_t)((u - 1) & 1));
+                            mbar_arrive_expect_tx(&rawfull[s], total_tx);
+                            g3_tma_2d_hint(stg + G3_RAW_A, mt, kt * (TILE_BYTES / 8), nt0, &rawfull[s], pol_w);
+                            g3_tma_2d(stg + G3_RAW_A + G3_RAW_W, mm, kt * (TILE_BYTES / 8) + TILE_NIB / 8, nt_pair, &rawfull[s]);
+                        }
+                        if (pass == 1) {
+                            bulk_g2s(stg, a_src + (size_t)kt * ACT_NIB_UNIT_BYTES, G3_RAW_A, &rawfull[s]);
+                            bulk_g2s(stg + G3_RAW_A + G3_RAW_W + G3_RAW_META, a7_src + (size_t)kt * G3_BM, G3_RAW_A7, &rawfull[s]);
+                        }
+                        if (++s == G3_RAW_STAGES) { s = 0; u++; }
                     }
                 }
                 if (pass == 0) pdl_wait();       // the activation codes belong to the kernel in front until here
@@ -438,141 +459,157 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
                 G3_STAMP(0, gk, 0);
                 if (u2 > 0) g3_wait(&accempty[as], (uint32_t)((u2 - 1) & 1));
                 G3_STAMP(0, gk, 1);
+                g3_wait(&bfull[as], (uint32_t)(u2 & 1));       // the whole k-tile of fp16 weights (ring of two k-tiles)
+                G3_STAMP(0, gk, 2);
                 const uint32_t d = tmem + as * G3_TM_D_STRIDE;
-#pragma unroll
+#pragma unroll 1      // rolled on purpose: the unrolled form kept four sets of descriptors alive and spilled them into the issue path
                 for (int q = 0; q < 4; q++) {
-                    if ((q & 1) == 0) g3_wait(&afull[q >> 1], (uint32_t)(gk & 1));      // both CTAs' activations of this half are in TMEM
-                    if ((q & 1) == 0) G3_STAMP(0, gk, 2 + q);
-                    g3_wait(&bfull[q], (uint32_t)(gk & 1));
-                    G3_STAMP(0, gk, 3 + (q & 2) + (q & 1) * 0);
-                    if (q == 3) G3_STAMP(0, gk, 6);
+                    g3_wait(&afull[q], (uint32_t)(gk & 1));      // both CTAs' activations of this quarter are in TMEM
+                    G3_STAMP(0, gk, 3 + q);
                     tc_fence_after();
                     if (elect_one()) {
-                        const uint32_t b_lo = b_lo0 + (uint32_t)q * (G3_F_BYTES >> 4);
-                        const uint32_t a_t = tmem + G3_TM_A0 + (q >> 1) * G3_TM_A_COLS + (q & 1) * 32;
+                        const uint32_t b_lo = b_lo0 + (uint32_t)(as * 4 + q) * (G3_F_Q >> 4);
+                        const uint32_t a_t = tmem + G3_TM_A0 + q * G3_TM_A_COLS;
 #pragma unroll
                         for (int ks = 0; ks < 4; ks++)      // K = 16 per instruction: 8 TMEM columns of A, two 8-element K-chunks of B
                             umma_f16_2cta_ts(d, a_t + ks * 8, b_lo + (uint32_t)ks * ((2 * LBO_B) >> 4), b_hi, idesc, (q | ks) ? 1u : 0u);
-                        g3_commit_2cta(&bfree[q]);
-                        if (q & 1) g3_commit_2cta(&afree[q >> 1]);
-                        if (q == 3) g3_commit_2cta(&accfull[as]);
+                        g3_commit_2cta(&afree[q]);
+                        if (q == 3) {
+                            g3_commit_2cta(&bfree[as]);
+                            g3_commit_2cta(&accfull[as]);
+                        }
                     }
                     __syncwarp();
                 }
             }
         }
       }
-    } else if (warp < G3_EPI_WARP0) {
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;" ::: "memory");
-        // ===================== unpack warps (16): activations -> TMEM, weights -> shared memory =====================
-        // Activations.  Every warp owns one (TMEM lane quarter, 16-column chunk) job per half k-tile: thread = token row,
-        // 32 bytes of fp16 high bytes -> 16 TMEM columns of packed fp16 pairs (tcgen05.st).  Going through registers instead
-        // of shared memory keeps 128 KB per k-tile (the fp16 stores and the tensor core's operand reads) off the
-        // shared-memory pipe.  Four warps per lane quarter share the work: one warp per quarter was the critical path.
-        // Weights.  Warps 4..15 of the 16 additionally convert one (group, channel) unit of 4 words per thread and half
-        // k-tile into the fp16 B operand; warps 0..3 forward the row factors a7/127 to the epilogue warps instead.
-        static_assert(8 * 16 * NTL == 2 * 2 * G3_UNPACK_WARPS * 32, "one weight unit per weight-warp thread and half k-tile");
-        const int w16 = warp - G3_AW_WARP0;                 // 0..15
-        const int a_c2 = w16 >> 2;                          // 16-column chunk of the half k-tile (32 bytes of every row)
-        const int row = (warp & 3) * 32 + lane;             // TMEM lane = token row of this CTA
-        const bool is_b = w16 >= G3_AW_WARPS;
-        const int uw = w16 - G3_AW_WARPS;                   // weight-warp index 0..11 (negative: activation-only warp)
-        const int ut = threadIdx.x - G3_UNPACK_WARP0 * 32;  // 0..383 for weight warps
+    } else if (warp < G3_UNPACK_WARP0) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 32;" ::: "memory");
+        // ===================== activation warps: nibbles -> fp16 -> TMEM (the MMA's A operand) =====================
+        // thread = token row = TMEM lane.  Going through registers and tcgen05.st instead of shared memory keeps 128 KB per
+        // k-tile (the fp16 stores and the tensor core's operand reads) off the shared-memory pipe.  Two warps per lane
+        // quarter: warp j of the pair owns quarters j and j + 2 of every k-tile (32 bytes of nibbles of the row -> 32 columns each);
+        // the MMA frees a quarter buffer as soon as it has consumed it, so a warp has 3/4 of a k-tile to refill it.
+        const int aw = warp - G3_AW_WARP0;                  // 0..7
+        const int aj = aw >> 2;                             // which quarters: aj, aj + 2
+        const int row = (warp & 3) * 32 + lane;
         const uint32_t afull_leader = g3_mapa(smem_u32(afull), 0);
-        const uint32_t ta = tmem + ((uint32_t)((warp & 3) * 32) << 16) + G3_TM_A0 + a_c2 * 16;
-        const int a_off = (2 * a_c2) * 2048 + row * 16;
-        // this thread's weight unit inside every half k-tile: quarter b_ql (warp-uniform: 6 warps per quarter), group b_gg of
-        // the quarter, channel b_ch; 4 words = 4 operand cells
-        const int b_ql = is_b ? ut / NCOL : 0, b_r = is_b ? ut - b_ql * NCOL : 0, b_gg = b_r / (8 * NTL), b_ch = b_r - b_gg * (8 * NTL);
-        const int src_off = G3_RAW_A + (b_ch >> 3) * 512 + (2 * b_ql + b_gg) * 128 + (b_ch & 7) * 16;
-        const int sc_off = G3_RAW_A + G3_RAW_W + ((int)rank * NTL + (b_ch >> 3)) * 160 + 32 + (b_ch & 7) * 8 + 2 * b_ql + b_gg;
-        const int dst_off = b_ql * G3_F_BYTES + (b_gg * 4) * LBO_B + b_ch * 16;
-        const uint32_t bfull_leader = g3_mapa(smem_u32(bfull), 0) + (uint32_t)b_ql * 8;
-        // S / zero-point publisher role of the first NCOL weight-warp threads: channel (half, j, c) of the pair's 16*NTL channels
+        const uint32_t ta = tmem + ((uint32_t)((warp & 3) * 32) << 16) + G3_TM_A0;
+        int s = 0, u = 0, gk = 0;
+        for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+            const G3Tile tl = g3_decode(P, t, MB2, KT, rank);
+            for (int kt = tl.kt0; kt < tl.kt1; kt++, gk++) {
+                if (aw == 0) G3_STAMP(1, gk, 0);
+                g3_wait(&rawfull[s], (uint32_t)(u & 1));
+                if (aw == 0) G3_STAMP(1, gk, 1);
+                const uint8_t *stg = sRaw + s * G3_RAW_BYTES;
+                if (aj == 0) {      // the row factor a7 / 127 of this k-tile, for the epilogue warps
+                    const float a7v = *reinterpret_cast<const float *>(stg + G3_RAW_A + G3_RAW_W + G3_RAW_META + row * 4);
+                    sRm[(gk & (G3_SN_RING - 1)) * G3_BM + row] = a7v * (1.0f / 127.0f);
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&snfull[gk & (G3_SN_RING - 1)]);
+                }
+#pragma unroll
+                for (int i = 0; i < 2; i++) {
+                    const int q = aj + 2 * i;
+                    const uint8_t *src = stg + (2 * q) * 2048 + row * 16;      // the quarter's two 32-groups of this row
+                    const uint4 w0 = *reinterpret_cast<const uint4 *>(src), w1 = *reinterpret_cast<const uint4 *>(src + 2048);
+                    if (gk > 0) {
+                        g3_wait(&afree[q], (uint32_t)((gk - 1) & 1));
+                        tc_fence_after();
+                    }
+                    if (aw == 0) G3_STAMP(1, gk, 2 + 3 * i);
+                    if (!(PROF && (P.exp & 2)))
+#pragma unroll
+                    for (int c2 = 0; c2 < 2; c2++) {      // one 32-group = 4 words -> 4 operand cells = 16 TMEM columns per step
+                        const uint4 w = c2 ? w1 : w0;
+                        const uint4 c0 = g3_cvt_act(w.x), c1 = g3_cvt_act(w.y), c2v = g3_cvt_act(w.z), c3 = g3_cvt_act(w.w);
+                        const uint32_t r[16] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w,
+                                                c2v.x, c2v.y, c2v.z, c2v.w, c3.x, c3.y, c3.z, c3.w};
+                        g3_tmem_st_32x16(ta + q * G3_TM_A_COLS + c2 * 16, r);
+                    }
+                    g3_tmem_st_wait();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) {
+                        g3_arrive_cluster(afull_leader + (uint32_t)q * 8);
+                        if (i == 1) mbar_arrive(&rawempty[s]);       // every lane has read its raw bytes
+                    }
+                    if (aw == 0) G3_STAMP(1, gk, 3 + 3 * i);
+                }
+                if (++s == G3_RAW_STAGES) { s = 0; u++; }
+            }
+        }
+    } else if (warp < G3_EPI_WARP0) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 32;" ::: "memory");
+        // ===================== weight warps: nibbles -> fp16 B operand in shared memory =====================
+        // One hand-over per k-tile: a thread converts two (group, channel) units of 4 words each -- the same (group of the
+        // quarter, channel) in quarters b_q and b_q + 2 -- into the ring slot of this k-tile (the ring holds two k-tiles, so
+        // these warps have a full k-tile of tensor-pipe time for it).
+        static_assert(8 * 8 * NTL == 2 * G3_UNPACK_WARPS * 32, "two weight units per weight-warp thread and k-tile");
+        const int uw = warp - G3_UNPACK_WARP0;              // 0..11
+        const int ut = threadIdx.x - G3_UNPACK_WARP0 * 32;  // 0..383
+        const int b_q = ut / NCOL, b_r = ut - b_q * NCOL, b_gg = b_r / (8 * NTL), b_ch = b_r - b_gg * (8 * NTL);
+        const int src_off = G3_RAW_A + (b_ch >> 3) * 1024 + (2 * b_q + b_gg) * 128 + (b_ch & 7) * 16;
+        const int sc_off = G3_RAW_A + G3_RAW_W + ((int)rank * NTL + (b_ch >> 3)) * 160 + 32 + (b_ch & 7) * 8 + 2 * b_q + b_gg;
+        const int dst_off = b_q * G3_F_Q + (b_gg * 4) * LBO_B + b_ch * 16;
+        const uint32_t bfull_leader = g3_mapa(smem_u32(bfull), 0);
+        // S / zero-point publisher role of the first NCOL threads: channel (half, j, c) of the pair's 16*NTL channels
         const int p_half = ut / (8 * NTL), p_j = (ut % (8 * NTL)) >> 3, p_c = ut & 7;
         const int p_off = G3_RAW_A + G3_RAW_W + (p_half * NTL + p_j) * 160;
         int s = 0, u = 0, gk = 0;
         for (int t = cluster_id; t < num_tiles; t += num_clusters) {
             const G3Tile tl = g3_decode(P, t, MB2, KT, rank);
             for (int kt = tl.kt0; kt < tl.kt1; kt++, gk++) {
-#pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    if (w16 == 0) G3_STAMP(1, gk, 4 * h);
-                    if (uw == 0) G3_STAMP(2, gk, 4 * h);
-                    g3_wait(&rawfull[s], (uint32_t)(u & 1));
-                    if (w16 == 0) G3_STAMP(1, gk, 4 * h + 1);
-                    if (uw == 0) G3_STAMP(2, gk, 4 * h + 1);
-                    const uint8_t *stg = sRaw + s * G3_RAW_BYTES;
-                    const uint4 w0 = *reinterpret_cast<const uint4 *>(stg + a_off), w1 = *reinterpret_cast<const uint4 *>(stg + a_off + 2048);
-                    uint4 wb = make_uint4(0, 0, 0, 0);
-                    int sc = 0;
-                    if (is_b) {
-                        wb = *reinterpret_cast<const uint4 *>(stg + src_off);
-                        sc = *reinterpret_cast<const int8_t *>(stg + sc_off + 4 * h);
-                    }
-                    // ---- activations first: 32 bytes -> 16 TMEM columns, handed over at once (afull does not wait for the weights)
-                    if (gk > 0) {
-                        g3_wait(&afree[h], (uint32_t)((gk - 1) & 1));
-                        tc_fence_after();
-                    }
-                    if (w16 == 0) G3_STAMP(1, gk, 4 * h + 2);
-                    {
-                        uint4 c0, c1, c2v, c3;
-                        g3_cvt_act16(w0, c0, c1);
-                        g3_cvt_act16(w1, c2v, c3);
-                        const uint32_t r[16] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w,
-                                                c2v.x, c2v.y, c2v.z, c2v.w, c3.x, c3.y, c3.z, c3.w};
-                        g3_tmem_st_32x16(ta + h * G3_TM_A_COLS, r);
-                    }
-                    g3_tmem_st_wait();
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) g3_arrive_cluster(afull_leader + (uint32_t)h * 8);
-                    if (!is_b) {
-                        if (h == 0) {      // the row factor a7 / 127 of this k-tile, for the epilogue warps
-                            const float a7v = *reinterpret_cast<const float *>(stg + G3_RAW_A + G3_RAW_W + G3_RAW_META + row * 4);
-                            sRm[(gk & (G3_SN_RING - 1)) * G3_BM + row] = a7v * (1.0f / 127.0f);
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(&snfull[gk & (G3_SN_RING - 1)]);
-                        }
-                    } else {
-                        if (h == 0 && uw < SN_WARPS) {      // per-channel super-scales of this k-tile
-                            const uint8_t *md = stg + p_off;
-                            const float sv = __half2float(*reinterpret_cast<const __half *>(md + 2 * p_c));
-                            const float zv = __half2float(*reinterpret_cast<const __half *>(md + 16 + 2 * p_c));
-                            const uint2 zc = *reinterpret_cast<const uint2 *>(md + 96 + p_c * 8);
-                            const int zf = (zv != 0.0f) && ((zc.x | zc.y) != 0u);
-                            sSn[(gk & (G3_SN_RING - 1)) * G3_SN_STRIDE + ut] = sv;
-                            const int anyz = __any_sync(0xffffffffu, zf);
-                            __syncwarp();
-                            if (lane == 0) {
-                                sZflag[(gk & (G3_SN_RING - 1)) * 8 + uw] = anyz;
-                                mbar_arrive(&snfull[gk & (G3_SN_RING - 1)]);
-                            }
-                        }
-                        // ---- weights: 4 words -> 4 operand cells of the quarter this warp belongs to
-                        const __half sch = __int2half_rn(sc);
-                        const __half2 sc2h = __halves2half2(sch, sch);
-                        const __half2 c72h = __hmul2(sc2h, __float2half2_rn(-72.0f));      // exact: 72*sc = 8 * (9*sc), 9*sc < 2048
-                        const uint32_t sc2 = *reinterpret_cast<const uint32_t *>(&sc2h), c72 = *reinterpret_cast<const uint32_t *>(&c72h);
-                        if (gk > 0) g3_wait(&bfree[2 * h + b_ql], (uint32_t)((gk - 1) & 1));
-                        if (uw == 0) G3_STAMP(2, gk, 4 * h + 2);
-                        uint8_t *dst = sF + (2 * h) * G3_F_BYTES + dst_off;
-                        *reinterpret_cast<uint4 *>(dst) = g3_cvt_w(wb.x, sc2, c72);
-                        *reinterpret_cast<uint4 *>(dst + 1 * LBO_B) = g3_cvt_w(wb.y, sc2, c72);
-                        *reinterpret_cast<uint4 *>(dst + 2 * LBO_B) = g3_cvt_w(wb.z, sc2, c72);
-                        *reinterpret_cast<uint4 *>(dst + 3 * LBO_B) = g3_cvt_w(wb.w, sc2, c72);
-                        fence_proxy_async_smem();
-                    }
+                if (uw == 0) G3_STAMP(2, gk, 0);
+                g3_wait(&rawfull[s], (uint32_t)(u & 1));
+                if (uw == 0) G3_STAMP(2, gk, 1);
+                const uint8_t *stg = sRaw + s * G3_RAW_BYTES;
+                const uint4 wb0 = *reinterpret_cast<const uint4 *>(stg + src_off);
+                const uint4 wb1 = *reinterpret_cast<const uint4 *>(stg + src_off + 512);       // the same unit two quarters (4 groups) later
+                const int sc0 = *reinterpret_cast<const int8_t *>(stg + sc_off);
+                const int sc1 = *reinterpret_cast<const int8_t *>(stg + sc_off + 4);
+                if (uw < SN_WARPS) {      // per-channel super-scales of this k-tile for the epilogue warps
+                    const uint8_t *md = stg + p_off;
+                    const float sv = __half2float(*reinterpret_cast<const __half *>(md + 2 * p_c));
+                    const float zv = __half2float(*reinterpret_cast<const __half *>(md + 16 + 2 * p_c));
+                    const uint2 zc = *reinterpret_cast<const uint2 *>(md + 96 + p_c * 8);
+                    const int zf = (zv != 0.0f) && ((zc.x | zc.y) != 0u);
+                    sSn[(gk & (G3_SN_RING - 1)) * G3_SN_STRIDE + ut] = sv;
+                    const int anyz = __any_sync(0xffffffffu, zf);
                     __syncwarp();
                     if (lane == 0) {
-                        if (is_b) g3_arrive_cluster(bfull_leader + (uint32_t)(2 * h) * 8);
-                        mbar_arrive(&rawempty[s]);       // after the __syncwarp: every lane has read its raw bytes
+                        sZflag[(gk & (G3_SN_RING - 1)) * 8 + uw] = anyz;
+                        mbar_arrive(&snfull[gk & (G3_SN_RING - 1)]);
                     }
-                    if (w16 == 0) G3_STAMP(1, gk, 4 * h + 3);
-                    if (uw == 0) G3_STAMP(2, gk, 4 * h + 3);
-                    if (++s == G3_RAW_STAGES) { s = 0; u++; }
                 }
+                const int fs = gk & 1;
+                if (gk > 1) g3_wait(&bfree[fs], (uint32_t)(((gk >> 1) - 1) & 1));
+                if (uw == 0) G3_STAMP(2, gk, 2);
+                uint8_t *dst = sF + fs * G3_F_BYTES + dst_off;
+                if (!(PROF && (P.exp & 4)))
+#pragma unroll
+                for (int i = 0; i < 2; i++) {
+                    const uint4 wb = i ? wb1 : wb0;
+                    const __half sch = __int2half_rn(i ? sc1 : sc0);
+                    const __half2 sc2h = __halves2half2(sch, sch);
+                    const __half2 c72h = __hmul2(sc2h, __float2half2_rn(-72.0f));      // exact: 72*sc = 8 * (9*sc), 9*sc < 2048
+                    const uint32_t sc2 = *reinterpret_cast<const uint32_t *>(&sc2h), c72 = *reinterpret_cast<const uint32_t *>(&c72h);
+                    uint8_t *d2 = dst + i * (2 * G3_F_Q);
+                    *reinterpret_cast<uint4 *>(d2) = g3_cvt_w(wb.x, sc2, c72);
+                    *reinterpret_cast<uint4 *>(d2 + 1 * LBO_B) = g3_cvt_w(wb.y, sc2, c72);
+                    *reinterpret_cast<uint4 *>(d2 + 2 * LBO_B) = g3_cvt_w(wb.z, sc2, c72);
+                    *reinterpret_cast<uint4 *>(d2 + 3 * LBO_B) = g3_cvt_w(wb.w, sc2, c72);
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    g3_arrive_cluster(bfull_leader + (uint32_t)fs * 8);
+                    mbar_arrive(&rawempty[s]);       // after the __syncwarp: every lane has read its raw bytes
+                }
+                if (uw == 0) G3_STAMP(2, gk, 3);
+                if (++s == G3_RAW_STAGES) { s = 0; u++; }
             }
         }
     } else {
@@ -651,6 +688,7 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
                         if (lane == 0) g3_arrive_cluster(accempty_leader + (uint32_t)as * 8);
                         if (ew == 0) G3_STAMP(3, gk, 2);
                     }
+                    if (PROF && (P.exp & 1)) continue;
 #pragma unroll
                     for (int j = 0; j < 4; j++) {    // 8 columns per step
                         const ulonglong2 sa = *reinterpret_cast<const ulonglong2 *>(sn + c * 32 + j * 8);
@@ -849,7 +887,7 @@ cudaError_t launch_gemm3(const Gemm3Seg *segs, int nseg, ActStage st, int64_t M,
     int cb = 0;
     for (int i = 0; i < nseg; i++) {
         const int64_t NT = segs[i].N / TILE_CH;
-        if (!g3_weight_map(&P.seg[i].tm_tiles, segs[i].w, NT, KT, 64, (uint32_t)plan.ntl) ||
+        if (!g3_weight_map(&P.seg[i].tm_tiles, segs[i].w, NT, KT, 128, (uint32_t)plan.ntl) ||
             !g3_weight_map(&P.seg[i].tm_meta, segs[i].w, NT, KT, 160 / 8, (uint32_t)(2 * plan.ntl)) ||
             !g3_y_map(&P.seg[i].tm_y, segs[i].y, M, segs[i].N, segs[i].ldc))
             return cudaErrorInvalidValue;      // unaligned tensor base or no driver entry point
@@ -864,6 +902,7 @@ cudaError_t launch_gemm3(const Gemm3Seg *segs, int nseg, ActStage st, int64_t M,
     P.res = res;
     P.bias = bias;
     P.res_in_y = (res != nullptr && res == segs[0].y && plan.ksplit > 1) ? 1 : 0;
+    P.exp = getenv("TCQ4_G3_EXP") ? atoi(getenv("TCQ4_G3_EXP")) : 0;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = plan.grid;
     cfg.blockDim = dim3(G3_THREADS);

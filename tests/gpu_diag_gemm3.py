@@ -25,9 +25,9 @@ torch.cuda.synchronize()
 raw = np.zeros(4 * 64 * 8, dtype=np.int64)
 rc = d.tcq4_b200_debug_gemm3_timeline(C.c_void_p(raw.ctypes.data), C.c_size_t(raw.nbytes))
 buf = raw.reshape(4, 64, 8)
-names = {0: ("mma", ["top", "accempty_ok", "afull0_ok", "bfull01_ok", "afull1_ok", "bfull23_ok", "q3_issue"]),
-         1: ("act w0", ["h0 top", "raw_ok", "afree_ok", "done", "h1 top", "raw_ok", "afree_ok", "done"]),
-         2: ("wgt w0", ["h0 top", "raw_ok", "bfree_ok", "done", "h1 top", "raw_ok", "bfree_ok", "done"]),
+names = {0: ("mma", ["top", "accempty_ok", "bfull_ok", "afull0_ok", "afull1_ok", "afull2_ok", "afull3_ok"]),
+         1: ("act w0", ["top", "raw_ok", "afree(q0)_ok", "q0 done", "-", "afree(q2)_ok", "q2 done"]),
+         2: ("wgt w0", ["top", "raw_ok", "bfree_ok", "done"]),
          3: ("epi w0", ["top", "accfull_ok", "handback", "end"])}
 t0 = buf[0, 0, 0]
 KT = min(4 * (K // 256), 64)
