@@ -169,23 +169,31 @@ def run_reference_arm(args):
         return
     layer = CpuLayer(PREFILL_M)
     for _ in range(max(1, min(args.warmup, 2))):
-        layer.run()
+        layer.run()                                        # warm-up: thread pool, page faults (one layer each)
     ts = []
-    for _ in range(args.steps):
-        t, _ = layer.run()
-        ts.append(t)
-    t_step = sum(ts) / len(ts) * QWEN3_4B_LAYERS           # a step = all 36 layers; each timed step is a 1-layer sample
+    for _ in range(args.steps):                            # a step = all 36 layers (the same layer's tiles 36 times: the
+        t0 = time.perf_counter()                           # arithmetic of a step, a bounded sample of its weights)
+        for _l in range(QWEN3_4B_LAYERS):
+            layer.run()
+        ts.append(time.perf_counter() - t0)
+    t_step = sum(ts) / len(ts)
     val = PREFILL_M / t_step
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": t_step * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "Qwen3-4B TCQ4_K32 252 linear matmuls, 512-token prefill (BASELINE.json configs[1])",
-                       "M": PREFILL_M, "layers": QWEN3_4B_LAYERS, "matmuls_per_layer": len(QWEN3_4B_LAYER)},
+            "config": base_config(),
+            "detail": {"arm": "reference CPU path (oracle/_ref: dequantize_row_tcq4_tile + ggml_fwht_impl + ggml CPU F32 MUL_MAT)"},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": layer.rb.threads, "kind": layer.rb.kind,
-                             "sample": f"each step = 1 of {QWEN3_4B_LAYERS} layers (7 matmuls, M={PREFILL_M}) scaled x{QWEN3_4B_LAYERS}"},
+                             "sample": f"each step = {QWEN3_4B_LAYERS} x (7 matmuls, M={PREFILL_M}) over one layer's synthetic tiles"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit(line)
+
+
+def base_config():
+    """`config` of BOTH arms (key-identical; arm-specific detail goes under `detail`)."""
+    return {"workload": "Qwen3-4B TCQ4_K32 252 linear matmuls, 512-token prefill (BASELINE.json configs[1])",
+            "M": PREFILL_M, "layers": QWEN3_4B_LAYERS, "matmuls_per_layer": len(QWEN3_4B_LAYER)}
 
 
 # --------------------------------------------------------------------------------------------------
@@ -194,7 +202,7 @@ def run_reference_arm(args):
 class Chain:
     """The 252 matmuls of Qwen3-4B, N-sharded over `world` ranks (shard = contiguous tile byte range)."""
 
-    def __init__(self, t4, torch, M, world, rank, weights=None, gather=True, mode="fused"):
+    def __init__(self, t4, torch, M, world, rank, weights=None, gather=True, mode="fused", per_node=False):
         self.t4, self.torch, self.M, self.world, self.rank = t4, torch, M, world, rank
         self.gather = gather                           # False: the sharded MUL_MATs alone (SURVEY 8e reports both)
         self.ops = []                                  # (sharded weight, K, N)
@@ -255,6 +263,18 @@ class Chain:
                 self.gather_kind = "NCCL all-gather of every output on a second stream (overlaps the next matmul)"
         self.graph = None
         self.launches_per_step = None
+        # single GPU: the step is ONE call of the graph-level entry (tcq4_b200_ggml_graph_compute) over the 252 MUL_MAT nodes in
+        # execution order, every node with its own dst as in a ggml graph; the library fans out the runs that share src1
+        self.ggml = None
+        if world == 1 and not per_node:
+            self.y_node = {name: torch.empty((M, N), device="cuda") for name, N, _ in QWEN3_4B_LAYER}
+            nodes = []
+            for i, w in enumerate(weights):
+                name = QWEN3_4B_LAYER[i % len(QWEN3_4B_LAYER)][0]
+                nodes.append((w.tiles, self.x[w.K], self.y_node[name], w.N, f"blk.{i // len(QWEN3_4B_LAYER)}.{name}.weight"))
+            self.ggml = t4.GgmlGraph(nodes)
+            t4.reserve(M, max(N for _, N, _ in QWEN3_4B_LAYER), max(K for _, _, K in QWEN3_4B_LAYER))
+            t4.reserve(M, sum(N for n, N, _ in QWEN3_4B_LAYER if n in ("ffn_gate", "ffn_up")), 2560)
 
     def weight_bytes(self):
         return sum(w.tiles.numel() for w in self.weights)
@@ -296,6 +316,9 @@ class Chain:
                     main.wait_stream(self.copy_streams[r])
             self.sym[self.weights[-1].N][1].barrier()
             return last
+        if self.ggml is not None:
+            self.ggml.compute()
+            return self.y_node[QWEN3_4B_LAYER[-1][0]]
         if self.comm is None:
             for w in self.weights:
                 last = w.local(self.x[w.K], out=self.y_local[w.N], workspace=self.ws)
@@ -403,25 +426,28 @@ class FanoutChain:
         self.graph.replay()
 
 
-def fanout_leg(t4, torch, pre, dec, steps, warmup):
-    """graph-level fusion on top of the headline path (reported beside it, never instead of it); outputs checked
-    against the per-node path on the last layer (prefill: bit-identical; decode: the fp32 sum over 256-blocks is cut between
-    warps at other places in the segmented launch, same int32 accumulators)"""
-    out = {"what": "q/k/v and gate/up of each layer through tcq4_b200_mul_mat_fanout (shared activation stage at prefill, one "
-                   "segmented GEMV launch at decode); the headline numbers above stay on one call per MUL_MAT node"}
+def per_node_leg(t4, torch, pre, dec, steps, warmup):
+    """The same chains with one tcq4_b200_mul_mat call per MUL_MAT node (no graph-level fusion), reported beside the headline;
+    the outputs of the last layer are compared (prefill: bit-identical unless a K split applies to the node; decode: the fp32
+    sum over 256-blocks is cut between warps at other places in the segmented launch, same int32 accumulators)."""
+    out = {"what": "one tcq4_b200_mul_mat call per MUL_MAT node (the round-1 headline path); the headline above goes through "
+                   "tcq4_b200_ggml_graph_compute, which fans out consecutive nodes sharing src1"}
+    L = len(QWEN3_4B_LAYER)
     for key, base, M, n in (("prefill", pre, pre.M, steps), ("decode", dec, 1, max(steps, 20))):
-        fc = FanoutChain(t4, torch, M, base)
-        fc.capture()
-        ms = timed_steps(torch, None, fc, n, max(warmup, 3), 1)
-        w, _ = fc.layers[-1]
+        pn = Chain(t4, torch, M, 1, 0, weights=base.weights, per_node=True)
+        pn.capture()
+        ms = timed_steps(torch, None, pn, n, max(warmup, 3), 1)
+        base.step()
+        torch.cuda.synchronize()
         same, worst = True, 0.0
         for j, (name, N, K) in enumerate(QWEN3_4B_LAYER):
-            ref = t4.mul_mat(w[j].tiles, fc.x[K], N)
-            same = same and bool(torch.equal(ref, fc.y[name]))
-            worst = max(worst, float(((ref - fc.y[name]).double() ** 2).sum() / (ref.double() ** 2).sum()))
-        out[key] = {"ms_per_step": ms, "value": M / (ms * 1e-3), "unit": UNIT, "launches_per_step": int(fc.launches_per_step),
-                    "bit_identical_to_per_node": same, "nmse_vs_per_node": worst}
-        del fc
+            ref = t4.mul_mat(base.weights[-L + j].tiles, base.x[K], N)
+            got = base.y_node[name]
+            same = same and bool(torch.equal(ref, got))
+            worst = max(worst, float(((ref - got).double() ** 2).sum() / (ref.double() ** 2).sum()))
+        out[key] = {"ms_per_step": ms, "value": M / (ms * 1e-3), "unit": UNIT, "launches_per_step": int(pn.launches_per_step),
+                    "graph_outputs_bit_identical_to_per_node": same, "nmse_graph_vs_per_node": worst}
+        del pn
     return out
 
 
@@ -453,8 +479,11 @@ def kernel_leg(t4, torch, chain, steps, kernel, M):
     n_launch = len(chain.weights) * steps
     t4.profile_begin(n_launch)
     for _ in range(steps):
-        for w in chain.weights:
-            w.local(chain.x[w.K], out=chain.y_local[w.N], workspace=chain.ws)
+        if chain.ggml is not None:
+            chain.ggml.compute()
+        else:
+            for w in chain.weights:
+                w.local(chain.x[w.K], out=chain.y_local[w.N], workspace=chain.ws)
     main_ms, pre_ms, n = t4.profile_end(kernel)
     return main_ms, pre_ms, n
 
@@ -481,9 +510,15 @@ def e2e_leg(t4, torch, chain, steps, M):
     return (time.perf_counter() - t0) / steps, h2d, d2h
 
 
-# per-launch DRAM traffic of the headline shapes from the committed ncu captures (profiles/)
-PREFILL_TRAFFIC_BYTES = 15783680
-DECODE_TRAFFIC_BYTES = 14439680
+def load_traffic():
+    """per-launch DRAM traffic (dram__bytes_read + write) of the dominant kernels from the committed ncu capture of this
+    round, written by tests/ncu_summary.py --traffic; null when the file is absent (never a hard-coded constant)"""
+    p = os.path.join(ROOT, "profiles", "traffic_r02.json")
+    try:
+        with open(p) as f:
+            return json.load(f)
+    except Exception:  # noqa: BLE001
+        return {}
 
 
 def run_own_arm(args):
@@ -592,13 +627,21 @@ def run_own_arm(args):
         umma_i8, _ = t4.measure_umma(0, 256, 0, 4000)    # bare tcgen05.mma kind::i8 128x256x32 issue loop, all SMs
     except Exception:  # noqa: BLE001
         umma_i8 = None
-    gm_tops = ops_local * (gm_n / max(1, len(pre.weights))) / (gm_ms * 1e-3) / 1e12 if gm_n else 0.0
-    gv_gbs_eager = bytes_local_dec * (gv_n / max(1, len(dec.weights))) / (gv_ms * 1e-3) / 1e9 if gv_n else 0.0
+    gv_gbs_eager = bytes_local_dec * (min(dec_steps, 10)) / (gv_ms * 1e-3) / 1e9 if gv_n else 0.0
+    # Dominant prefill kernel: its share of the step comes from the eager pass (per-launch events around the activation kernel
+    # and the GEMM launches of every call: share = GEMM time / (GEMM + activation time), host launch gaps hit both alike); the
+    # duration it is charged with is that share of the TIMED region (CUDA-graph replays): kernel share x step.
+    ms_pre_local = ms_step_ng if (world > 1 and ms_step_ng) else ms_step
+    gemm_share = gm_ms / max(1e-9, gm_ms + act_ms)
+    gemm_launches_per_step = gm_n / max(1, args.steps)
+    gm_tops = ops_local / (ms_pre_local * 1e-3 * gemm_share) / 1e12
+    gemm_avg_us = ms_pre_local * 1e3 * gemm_share / max(1.0, gemm_launches_per_step)
     # the decode kernel's launch duration inside the TIMED region (CUDA-graph replays, events around the steps): the step
-    # is nothing but these launches, so step time / launches is the per-launch duration including every gap between them;
-    # the eager per-launch events above also count ~5 us of host launch latency per kernel and are kept for reference
+    # is nothing but these launches, so step time / launches is the per-launch duration including every gap between them
     ms_dec_local = ms_dec_ng if (world > 1 and ms_dec_ng) else ms_dec
     gv_gbs = bytes_local_dec / (ms_dec_local * 1e-3) / 1e9
+    dec_launches = int(dec.launches_per_step or len(dec.weights))
+    traffic = load_traffic()
 
     # ---- end to end through the host-buffer C-ABI call ---------------------------------------------------
     e2e_s, h2d, d2h = e2e_leg(t4, torch, pre, max(1, min(args.steps, 2)), M)
@@ -613,34 +656,42 @@ def run_own_arm(args):
         line = {
             "metric": METRIC, "value": M / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "s8", "data": "synthetic",
-            "config": {"workload": "Qwen3-4B TCQ4_K32 252 linear matmuls, 512-token prefill (BASELINE.json configs[1])",
-                       "M": M, "layers": QWEN3_4B_LAYERS, "matmuls_per_layer": len(QWEN3_4B_LAYER),
-                       "weight_bytes_per_gpu": pre.weight_bytes(), "parallelism": (f"N-shard x{world}; gather: {pre.gather_kind}" if world > 1 else "single GPU"),
+            "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+            "config": base_config(),
+            "detail": {"weight_bytes_per_gpu": pre.weight_bytes(),
+                       "parallelism": (f"N-shard x{world}; gather: {pre.gather_kind}" if world > 1 else "single GPU"),
+                       "data_plane": ("symmetric memory (peer-mapped stores / NVSwitch multicast / copy engines); NCCL only for the "
+                                      "bootstrap and the reference all-gather check" if world > 1 else "none (one GPU)"),
+                       "api": ("one tcq4_b200_ggml_graph_compute call per step over the 252 MUL_MAT nodes (consecutive nodes sharing "
+                               "src1 fan out: 4 activation + 4 GEMM launches per layer)" if world == 1 else
+                               "one tcq4_b200_mul_mat_peers / _multicast call per MUL_MAT node"),
                        "l2": "252 distinct weight buffers (2.1 GB total) >> 126 MB L2; activations stay L2-resident",
                        "cuda_graph": pre.graph is not None},
             "tops": total_ops / (ms_step * 1e-3) / 1e12,
             "decode": {"value": 1.0 / (ms_dec * 1e-3), "unit": UNIT, "ms_per_step": ms_dec, "steps": dec_steps,
                        "gbs": total_dec_bytes / (ms_dec * 1e-3) / 1e9, "frac_hbm": total_dec_bytes / (ms_dec * 1e-3) / 1e9
                        / (peaks["hbm_gbs"] * world), "cuda_graph": dec.graph is not None},
-            "roofline": {"bound": "tensor", "kernel": "tcq4_gemm2_kernel (tcgen05.mma.cta_group::2 kind::i8)", "achieved": gm_tops,
-                         "peak": i8_peak, "unit": "TOP/s", "frac": gm_tops / i8_peak, "traffic": PREFILL_TRAFFIC_BYTES,
-                         "traffic_note": "dram__bytes_read+write of the M=512,N=9728,K=2560 launch from one ncu --set full capture "
-                                         "(profiles/prof_gemm2_r01d_summary.csv): the weights; x codes and y stay in the 126 MB L2; "
-                                         "algorithmic bytes of that launch incl. x and y are 39.6 MB",
-                         "peak_source": f"2 x bf16_tflops of MEASURED_PEAKS.json ({peaks['source']}, burst)",
+            "roofline": {"bound": "tensor", "kernel": ("tcq4_gemm3_kernel (tcgen05.mma.cta_group::2 kind::f16 on exact fp16 integers)" if world == 1
+                                                        else "tcq4_gemm2_kernel (tcgen05.mma.cta_group::2 kind::i8; several destinations)"),
+                         "achieved": gm_tops, "peak": i8_peak, "unit": "TOP/s", "frac": gm_tops / i8_peak,
+                         "traffic": traffic.get("prefill_gemm_bytes_per_launch"),
+                         "traffic_note": traffic.get("prefill_note", "no ncu capture of this round in profiles/traffic_r02.json"),
+                         "peak_source": f"2 x bf16_tflops of MEASURED_PEAKS.json ({peaks['source']}, burst): dense int8 rate of the pipe",
                          "peak_umma_i8_measured": umma_i8, "frac_of_umma_i8": (gm_tops / umma_i8) if umma_i8 else None,
-                         "ops": "useful 2*M*N*K per launch; the tensor pipe executes 2x that (exact hi/lo split)",
-                         "launches": gm_n, "avg_launch_us": gm_ms * 1e3 / max(1, gm_n),
-                         "act_kernel_avg_us": act_ms * 1e3 / max(1, gm_n),
-                         "timed": "per-launch CUDA events, eager pass of the same steps after the timed region"},
+                         "ops": "useful 2*M*N*K; the tensor pipe runs them as fp16 MACs with fp32 accumulators holding the exact integer "
+                                "(kind::f16 = half the int8 rate: the exact per-group scale caps USEFUL ops at 50 % of the int8 peak)",
+                         "launches_per_step": gemm_launches_per_step, "avg_launch_us": gemm_avg_us,
+                         "kernel_share_of_step": gemm_share,
+                         "act_kernel_share_of_step": 1.0 - gemm_share,
+                         "timed": "kernel share (eager per-launch events) x step time of the timed region (graph replays)"},
             "roofline_decode": {"bound": "hbm", "kernel": "tcq4_gemv_kernel", "achieved": gv_gbs, "peak": peaks["hbm_gbs"],
-                                "unit": "GB/s", "frac": gv_gbs / peaks["hbm_gbs"], "traffic": DECODE_TRAFFIC_BYTES,
-                                "traffic_note": "dram__bytes_read+write of the M=1,N=9728,K=2560 launch (profiles/prof_gemv_r01c_summary.csv); "
-                                                "algorithmic 14.45 MB", "launches": len(dec.weights) * dec_steps,
-                                "avg_launch_us": ms_dec_local * 1e3 / max(1, len(dec.weights)),
-                                "timed": "decode steps of the timed region (graph replays): step time / 252 launches, gaps included",
-                                "eager_event_avg_launch_us": gv_ms * 1e3 / max(1, gv_n), "eager_event_gbs": gv_gbs_eager,
+                                "unit": "GB/s", "frac": gv_gbs / peaks["hbm_gbs"],
+                                "traffic": traffic.get("decode_gemv_bytes_per_launch"),
+                                "traffic_note": traffic.get("decode_note", "no ncu capture of this round in profiles/traffic_r02.json"),
+                                "launches": dec_launches * dec_steps,
+                                "avg_launch_us": ms_dec_local * 1e3 / max(1, dec_launches),
+                                "timed": "decode steps of the timed region (graph replays): step time / launches, gaps included",
+                                "eager_event_gbs": gv_gbs_eager,
                                 "peak_source": f"hbm_gbs ({peaks['source']})"},
             "e2e": {"value": M / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_s * 1e3, "api": "tcq4_b200_mul_mat_host_async per matmul (pinned host x and y, copies inside the timed region) + tcq4_b200_host_sync per step"},
@@ -648,7 +699,7 @@ def run_own_arm(args):
             "clocks": clocks,
         }
         if world > 1:
-            line["config"]["exchange_variants"] = variants      # value / decode use the faster one
+            line["detail"]["exchange_variants"] = variants      # value / decode use the faster one
             line["sharded_mul_mat_only"] = {
                 "note": "same chains without the fp32 all-gather of the N-sharded outputs (max over ranks)",
                 "value": M / (ms_step_ng * 1e-3), "unit": UNIT, "ms_per_step": ms_step_ng,
@@ -656,9 +707,9 @@ def run_own_arm(args):
                 "decode": {"value": 1.0 / (ms_dec_ng * 1e-3), "unit": UNIT, "ms_per_step": ms_dec_ng}}
         if world == 1:
             try:
-                line["graph_fusion"] = fanout_leg(t4, torch, pre, dec, args.steps, args.warmup)
+                line["per_node"] = per_node_leg(t4, torch, pre, dec, args.steps, args.warmup)
             except Exception as e:  # noqa: BLE001
-                line["graph_fusion"] = {"error": f"{type(e).__name__}: {e}"}
+                line["per_node"] = {"error": f"{type(e).__name__}: {e}"}
         if world == 1 and not args.no_cpu_baseline:
             try:
                 line["cpu_baseline"] = cpu_baseline_leg()

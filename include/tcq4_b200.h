@@ -271,6 +271,14 @@ TCQ4_B200_API int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq
 TCQ4_B200_API int tcq4_b200_ggml_mul_mat_fanout(int n, const tcq4_tensor_view *const *src0, const tcq4_tensor_view *src1,
                                                 tcq4_tensor_view *const *dst, cudaStream_t stream);
 
+/* The graph-level entry (the node loop of ggml_cuda_graph_evaluate_and_capture, ggml-cuda.cu:3481-3688): the TCQ4 MUL_MAT
+ * nodes of a graph in execution order.  Runs of consecutive nodes with one src1 (Q/K/V, gate/up) become one activation
+ * stage + one segmented launch (tcq4_b200_ggml_mul_mat_fanout); the rest go node by node.  TCQ4_NO_GRAPH_FUSION=1 in the
+ * environment turns the fusion off. */
+TCQ4_B200_API int tcq4_b200_ggml_graph_compute(int n_nodes, const tcq4_tensor_view *const *src0,
+                                               const tcq4_tensor_view *const *src1, tcq4_tensor_view *const *dst,
+                                               cudaStream_t stream);
+
 /* ggml_cuda_mul_mat_id (ggml-cuda.cu:2287-2436) for a TCQ4 src0: src0 [K, N, n_expert], src1 F32 [K, ne11, n_tokens]
  * with ne11 in {1, n_used}, ids I32 [n_used, n_tokens], dst F32 [N, n_used, n_tokens]; perm looked up by src0->name. */
 TCQ4_B200_API int tcq4_b200_ggml_mul_mat_id(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1,

@@ -15,7 +15,7 @@ import torch
 from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
                ACT_BLOCK_BYTES, TensorView, _check, quantize_size, shard_range, tile_bytes, workspace_size)
 
-__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "ggml_mul_mat_fanout", "mul_mat_add", "mul_mat_static", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
+__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "ggml_mul_mat_fanout", "GgmlGraph", "mul_mat_add", "mul_mat_static", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
            "ggml_supports_op", "ShardedWeight", "random_tiles", "quantize_tiles", "get_rows", "ggml_get_rows"]
 
@@ -332,6 +332,24 @@ def ggml_mul_mat_fanout(w_tiles: list, x: torch.Tensor, Ns: list, names: list, s
     ds = (C.POINTER(TensorView) * n)(*[C.pointer(v[2]) for v in views])
     _check(LIB.tcq4_b200_ggml_mul_mat_fanout(n, s0, C.byref(views[0][1]), ds, _stream_ptr(stream)))
     return outs
+
+
+class GgmlGraph:
+    """tcq4_b200_ggml_graph_compute: the TCQ4 MUL_MAT nodes of a ggml graph in execution order, as the backend's graph
+    loop sees them (ggml-cuda.cu:3481-3688).  nodes: list of (w_tiles, x, out, N, name); consecutive nodes that share x
+    are fanned out by the library.  The tensor views are built once; compute() is one C call."""
+
+    def __init__(self, nodes):
+        self.keep = nodes
+        self.n = len(nodes)
+        self.views = [_views(w, x, o, N, (nm or "").encode()) for (w, x, o, N, nm) in nodes]
+        P = C.POINTER(TensorView)
+        self.s0 = (P * self.n)(*[C.pointer(v[0]) for v in self.views])
+        self.s1 = (P * self.n)(*[C.pointer(v[1]) for v in self.views])
+        self.ds = (P * self.n)(*[C.pointer(v[2]) for v in self.views])
+
+    def compute(self, stream=None):
+        _check(LIB.tcq4_b200_ggml_graph_compute(self.n, self.s0, self.s1, self.ds, _stream_ptr(stream)))
 
 
 def mul_mat_id(w_experts: torch.Tensor, x: torch.Tensor, ids: torch.Tensor, N: int, perm: torch.Tensor | None = None,

@@ -158,8 +158,11 @@ int select_kernel(const DevInfo *d, int64_t M, int64_t N, int64_t K, tcq4::GemvP
     // elsewhere the persistent pair GEMM is up to 2x faster even with its second row block empty (measured:
     // profiles/, "M <= 128")
     if (M <= 128 && N >= 8192 && K <= 4096) return TCQ4_KERNEL_GEMM;
-    static const bool no_g3 = getenv("TCQ4_NO_GEMM3") != nullptr;       // experiments: the round-1 kind::i8 pair GEMM
-    return no_g3 ? TCQ4_KERNEL_GEMM2 : TCQ4_KERNEL_GEMM3;
+    // One matrix per call: the kind::i8 pair GEMM (measured per shape, tests/gpu_g3_shapes.py: 5-40 % ahead of the kind::f16
+    // kernel on most single matrices).  Fan-out groups take the kind::f16 kernel (tcq4_b200_mul_mat_fanout: its segmented
+    // tile list makes Q/K/V or gate/up ONE launch), as does an explicit TCQ4_KERNEL_GEMM3 / TCQ4_AUTO_GEMM3=1.
+    static const bool auto_g3 = getenv("TCQ4_AUTO_GEMM3") != nullptr;
+    return auto_g3 ? TCQ4_KERNEL_GEMM3 : TCQ4_KERNEL_GEMM2;
 }
 
 tcq4::YOut single_out(float *y, int64_t N) {
@@ -211,8 +214,8 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
     int k = kernel;
     if (k == TCQ4_KERNEL_AUTO) k = select_kernel(d, M, N, K, &gv);
     const bool one_dest = (yo.n == 1 && !yo.mc);
-    if (k == TCQ4_KERNEL_GEMM && !plain) k = one_dest ? TCQ4_KERNEL_GEMM3 : TCQ4_KERNEL_GEMM2;      // only the pair GEMMs and the GEMV write strided
-    if (k == TCQ4_KERNEL_GEMM && (res || bias)) k = TCQ4_KERNEL_GEMM3;           // ... and fuse bias / residual
+    if (k == TCQ4_KERNEL_GEMM && !plain) k = TCQ4_KERNEL_GEMM2;      // only the pair GEMMs and the GEMV write strided / to peers
+    if (k == TCQ4_KERNEL_GEMM && (res || bias)) k = TCQ4_KERNEL_GEMM2;            // ... and fuse bias / residual
     if (k == TCQ4_KERNEL_GEMM3 && !one_dest) k = TCQ4_KERNEL_GEMM2;               // several destinations / multicast: kind::i8 pair GEMM
     if (k == TCQ4_KERNEL_GEMV) {
         if (!tcq4::gemv_plan(M, N, K, d->num_sms, d->smem_optin, &gv)) {
@@ -570,15 +573,26 @@ int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N
         if (status != TCQ4_OK) return status;
         uint8_t *wsb = reinterpret_cast<uint8_t *>(d->arena);
         float *blob = gv.blob_bytes <= L.partial_bytes ? reinterpret_cast<float *>(wsb + L.partial_off) : nullptr;
+        const bool prof = g_prof.on && g_prof.n < g_prof.cap;
+        if (prof) {
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
+        }
         cudaError_t e = tcq4::launch_gemv(nullptr, x, d_perm, single_out(ys[0], Nsum), M, Nsum, K, gv, blob,
                                           reinterpret_cast<int *>(wsb + L.ticket_off), nullptr, stream, &ex);
         if (e != cudaSuccess) return cuda_fail(e, "fan-out gemv launch");
+        if (prof) {
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
+            g_prof.kind[g_prof.n++] = TCQ4_KERNEL_GEMV;
+        }
         g_launches.fetch_add(1, std::memory_order_relaxed);
         return TCQ4_OK;
     }
     status = arena_ensure(d, ws_layout(M, Nmax, K).total, stream);
     if (status != TCQ4_OK) return status;
-    if (select_kernel(d, M, Nmax, K, nullptr) == TCQ4_KERNEL_GEMM3) {
+    static const bool no_g3 = getenv("TCQ4_NO_GEMM3") != nullptr;       // experiments: fan-out through the round-1 kernels
+    const int ksel = select_kernel(d, M, Nmax, K, nullptr);
+    if (!no_g3 && n >= 2 && (ksel == TCQ4_KERNEL_GEMM2 || ksel == TCQ4_KERNEL_GEMM3 || ksel == TCQ4_KERNEL_GEMM)) {
         // ONE activation launch and ONE GEMM launch per group of up to four matrices: their column blocks form one tile list
         for (int i = 0; i < n; i++)
             if (!w_tiles[i] || !ys[i] || ((uintptr_t)w_tiles[i] & 15) || ((uintptr_t)ys[i] & 15)) {
@@ -596,8 +610,11 @@ int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N
         st.a7 = reinterpret_cast<float *>(wsb + L.a7_off);
         st.sumq = reinterpret_cast<int16_t *>(wsb + L.sumq_off);
         st.a7t = reinterpret_cast<float *>(wsb + L.a7t_off);
+        const bool prof = g_prof.on && g_prof.n < g_prof.cap;
+        if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
         cudaError_t e = tcq4::launch_act_quant_nib(x, d_perm, M, K, st, d->num_sms, stream);
         if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
+        if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
         g_launches.fetch_add(1, std::memory_order_relaxed);
         for (int i0 = 0; i0 < n; i0 += 4) {
             const int ns = std::min(4, n - i0);
@@ -615,6 +632,10 @@ int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N
             e = tcq4::launch_gemm3(sg, ns, st, M, K, g3, nullptr, stream);
             if (e != cudaSuccess) return cuda_fail(e, "gemm3 fan-out launch");
             g_launches.fetch_add(1, std::memory_order_relaxed);
+        }
+        if (prof) {
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
+            g_prof.kind[g_prof.n++] = TCQ4_KERNEL_GEMM3;
         }
         return TCQ4_OK;
     }

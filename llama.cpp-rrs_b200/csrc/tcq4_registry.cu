@@ -15,6 +15,7 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <vector>
@@ -104,6 +105,16 @@ const int32_t *tcq4_b200_get_perm(const char *tensor_name) {
     return it == g_perms.end() ? nullptr : it->second.d_perm;
 }
 
+// length of the permutation registered for this tensor on the current device (0: none)
+static int64_t perm_len(const char *tensor_name) {
+    if (!tensor_name || !tensor_name[0]) return 0;
+    const int dev = current_dev();
+    if (dev < 0) return 0;
+    std::shared_lock<std::shared_mutex> lk(g_perm_mu);
+    auto it = g_perms.find(std::make_pair(dev, tensor_name));
+    return it == g_perms.end() ? 0 : (int64_t)it->second.K;
+}
+
 int tcq4_b200_has_perm(const char *tensor_name) { return tcq4_b200_get_perm(tensor_name) != nullptr ? 1 : 0; }
 
 int tcq4_b200_ggml_supports_op(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1, const tcq4_tensor_view *dst,
@@ -128,6 +139,7 @@ int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq4_tensor_view 
     if (!is_contiguous_2d(src1, (size_t)K * 4) || !is_contiguous_2d(dst, (size_t)N * 4)) return TCQ4_ERR_SHAPE;
     if (src0->nb[1] != (size_t)(K / 256) * 148) return TCQ4_ERR_SHAPE;          // ggml_row_size, ggml.c:750-757
     const int32_t *d_perm = src0->name ? tcq4_b200_get_perm(src0->name) : nullptr;   // rrs.cu:266-270
+    if (d_perm && perm_len(src0->name) != K) return TCQ4_ERR_SHAPE;          // a registered permutation of another length would gather out of bounds
     if (workspace)
         return tcq4_b200_mul_mat_ws(src0->data, (const float *)src1->data, (float *)dst->data, M, N, K, d_perm,
                                     workspace, workspace_bytes, TCQ4_KERNEL_AUTO, stream);
@@ -157,6 +169,7 @@ int tcq4_b200_ggml_mul_mat_fanout(int n, const tcq4_tensor_view *const *src0, co
         y[i] = (float *)dst[i]->data;
     }
     const int32_t *d_perm = src0[0]->name ? tcq4_b200_get_perm(src0[0]->name) : nullptr;
+    if (d_perm && perm_len(src0[0]->name) != K) return TCQ4_ERR_SHAPE;
     bool same = true;
     if (g_reorder_enabled.load()) {
         const int dev = current_dev();
@@ -180,6 +193,39 @@ int tcq4_b200_ggml_mul_mat_fanout(int n, const tcq4_tensor_view *const *src0, co
     return TCQ4_OK;
 }
 
+// The graph-level entry: the TCQ4 MUL_MAT nodes of a ggml graph in execution order (the loop of
+// ggml_cuda_graph_evaluate_and_capture, ggml-cuda.cu:3481-3688, where the backend tries its fusions before it falls back
+// to one kernel per node).  Consecutive nodes with ONE src1 (same data pointer, shape and strides: Q/K/V, gate/up) are
+// fanned out -- one activation stage and one segmented GEMM / GEMV launch per run of up to 4 -- everything else goes
+// node by node.  Always equal to calling tcq4_b200_ggml_mul_mat per node (bit-identical at prefill; at decode batch the
+// fp32 sum over 256-blocks may be cut between warps at other places, see tcq4_b200_mul_mat_fanout).
+int tcq4_b200_ggml_graph_compute(int n_nodes, const tcq4_tensor_view *const *src0, const tcq4_tensor_view *const *src1,
+                                 tcq4_tensor_view *const *dst, cudaStream_t stream) {
+    if (n_nodes < 0 || (n_nodes > 0 && (!src0 || !src1 || !dst))) return TCQ4_ERR_ARG;
+    static const bool no_fuse = getenv("TCQ4_NO_GRAPH_FUSION") != nullptr;
+    auto same_src1 = [](const tcq4_tensor_view *a, const tcq4_tensor_view *b) {
+        if (!a || !b || a->data != b->data || a->type != b->type) return false;
+        for (int d = 0; d < 4; d++)
+            if (a->ne[d] != b->ne[d] || a->nb[d] != b->nb[d]) return false;
+        return true;
+    };
+    int i = 0;
+    while (i < n_nodes) {
+        int j = i + 1;
+        if (!no_fuse)
+            while (j < n_nodes && j - i < 4 && same_src1(src1[i], src1[j]) && src0[j] && src0[i] && src0[j]->ne[0] == src0[i]->ne[0]) j++;
+        // an output that aliases the shared input (or another output of the run) breaks the "one src1" premise
+        for (int a = i; a < j && j - i > 1; a++)
+            for (int b = i; b < j; b++)
+                if (dst[a] && src1[i] && (dst[a]->data == src1[i]->data || (a != b && dst[b] && dst[a]->data == dst[b]->data))) j = i + 1;
+        const int st = (j - i > 1) ? tcq4_b200_ggml_mul_mat_fanout(j - i, src0 + i, src1[i], dst + i, stream)
+                                   : tcq4_b200_ggml_mul_mat(src0[i], src1[i], dst[i], nullptr, 0, stream);
+        if (st != TCQ4_OK) return st;
+        i = j;
+    }
+    return TCQ4_OK;
+}
+
 // ggml_cuda_mul_mat_id (ggml-cuda.cu:2287-2436) for a TCQ4 src0.  Shape rules as there (:2293-2295, 2326-2327) plus the
 // contiguity this library needs; the reference's asserts become status codes.
 int tcq4_b200_ggml_mul_mat_id(const tcq4_tensor_view *src0, const tcq4_tensor_view *src1, const tcq4_tensor_view *ids,
@@ -198,6 +244,7 @@ int tcq4_b200_ggml_mul_mat_id(const tcq4_tensor_view *src0, const tcq4_tensor_vi
     if (dst->nb[0] != 4 || dst->nb[1] != (size_t)N * 4 || dst->nb[2] != (size_t)n_used * N * 4) return TCQ4_ERR_SHAPE;
     if (ids->nb[0] != 4 || (ids->nb[1] & 3)) return TCQ4_ERR_SHAPE;
     const int32_t *d_perm = src0->name ? tcq4_b200_get_perm(src0->name) : nullptr;
+    if (d_perm && perm_len(src0->name) != K) return TCQ4_ERR_SHAPE;
     return tcq4_b200_mul_mat_id(src0->data, n_expert, src0->nb[2], (const float *)src1->data, ne11,
                                 (const int32_t *)ids->data, (int64_t)(ids->nb[1] / 4), n_used, n_tokens, (float *)dst->data, N,
                                 K, d_perm, err_flag, stream);

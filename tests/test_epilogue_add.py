@@ -52,3 +52,17 @@ def test_residual_in_place(t4, orc, M):
     td, xd, h = torch.from_numpy(tiles).cuda(), torch.from_numpy(x).cuda(), torch.from_numpy(res).cuda()
     t4.mul_mat_add(td, xd, N, residual=h, out=h)
     assert nmse(h.cpu().numpy(), orc.mul_mat(tiles, x, N)["C"] + res) <= 1e-9
+
+
+@pytest.mark.gpu
+def test_epilogue_add_through_the_f16_pair_gemm_in_a_child_process():
+    """TCQ4_AUTO_GEMM3=1 (read once at load, hence the child) routes single matrices to the kind::f16 pair GEMM as well: its
+    bias / residual instantiation (incl. the K split meeting a pre-added residual) must pass the same checks."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, TCQ4_AUTO_GEMM3="1")
+    out = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", os.path.join(root, "tests", "test_epilogue_add.py"),
+                          "-k", "not child_process"], cwd=root, env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-2000:]
