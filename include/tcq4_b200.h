@@ -91,7 +91,12 @@ TCQ4_B200_API int tcq4_b200_mul_mat_ws(const void *w_tiles, const float *x, floa
 TCQ4_B200_API int tcq4_b200_workspace_init(void *workspace, size_t workspace_bytes, cudaStream_t stream);
 
 /* Same, with scratch taken from a per-device arena owned by the library.  The arena grows with
- * cudaMalloc only outside stream capture; call tcq4_b200_reserve at load time to pre-size it. */
+ * cudaMalloc only outside stream capture; call tcq4_b200_reserve at load time to pre-size it.  A block the arena has
+ * outgrown is retired, not freed (graphs captured earlier may still point into it).  ONE arena per device: every entry
+ * without a workspace argument (tcq4_b200_mul_mat, _add, _fanout, _mul_mat_id, _peers, _multicast, the ggml mirror) is
+ * asynchronous on `stream` but must not run CONCURRENTLY with another such call on a different stream of the same
+ * device -- callers with several streams pass their own workspaces (tcq4_b200_mul_mat_ws); the host-buffer pipeline
+ * (tcq4_b200_mul_mat_host_async) owns a workspace of its own. */
 TCQ4_B200_API int tcq4_b200_mul_mat(const void *w_tiles, const float *x, float *y,
                                     int64_t M, int64_t N, int64_t K, const int32_t *d_perm,
                                     cudaStream_t stream);

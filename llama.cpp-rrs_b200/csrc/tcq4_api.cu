@@ -58,7 +58,8 @@ struct DevInfo {
     size_t smem_optin = 0;
     // arena
     void  *arena = nullptr;
-    size_t arena_bytes = 0;
+    size_t arena_bytes = 0, arena_high = 0;
+    std::vector<void *> retired;      // earlier arena blocks (kept: captured graphs may still point into them)
     // host staging for tcq4_b200_mul_mat_host
     float *hx = nullptr, *hy = nullptr;
     size_t hx_bytes = 0, hy_bytes = 0;
@@ -389,7 +390,7 @@ int tcq4_b200_mul_mat_debug(const void *w_tiles, const float *x, float *y, int64
 }
 
 // grow the per-device arena (never while the stream is capturing)
-static int arena_ensure(DevInfo *d, size_t need, cudaStream_t stream) {
+static int arena_ensure(DevInfo *d, size_t need, cudaStream_t stream) {      // `need` may be raised below (geometric growth)
     if (d->arena_bytes >= need) return TCQ4_OK;
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     if (stream != nullptr && cudaStreamIsCapturing(stream, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone) {
@@ -401,9 +402,14 @@ static int arena_ensure(DevInfo *d, size_t need, cudaStream_t stream) {
     if (d->arena_bytes >= need) return TCQ4_OK;
     cudaError_t e = cudaDeviceSynchronize();          // old arena may still be in use
     if (e != cudaSuccess) return cuda_fail(e, "arena sync");
-    if (d->arena) cudaFree(d->arena);
+    // The old block is RETIRED, never freed: a CUDA graph captured earlier holds its address (activation codes, scales,
+    // pre-pass blob) and may be replayed after this growth.  Blocks grow geometrically, so the retired ones sum to less than
+    // the live one.
+    if (d->arena) d->retired.push_back(d->arena);
     d->arena = nullptr;
     d->arena_bytes = 0;
+    if (need < 2 * d->arena_high) need = 2 * d->arena_high;
+    d->arena_high = need;
     const size_t bytes = (size_t)tcq4::round_up((int64_t)need, 1 << 20);
     e = cudaMalloc(&d->arena, bytes);
     if (e != cudaSuccess) return cuda_fail(e, "arena cudaMalloc");
@@ -888,6 +894,8 @@ struct HostPipe {
     cudaEvent_t in_done[2] = {nullptr, nullptr}, cmp_done[2] = {nullptr, nullptr}, out_done[2] = {nullptr, nullptr};
     float *hx[2] = {nullptr, nullptr}, *hy[2] = {nullptr, nullptr};
     size_t hx_bytes[2] = {0, 0}, hy_bytes[2] = {0, 0};
+    float *ws = nullptr;              // the pipeline's OWN workspace: its compute stream must not share the device arena
+    size_t ws_bytes = 0;              // with whatever stream the caller runs tcq4_b200_mul_mat on
     uint64_t n = 0;
 };
 HostPipe g_pipe[MAX_DEV];
@@ -946,7 +954,15 @@ int tcq4_b200_mul_mat_host_async(const void *w_tiles_dev, const float *x_host, f
         return cuda_fail(e, "H2D copy");
     cudaEventRecord(p.in_done[slot], p.s_in);
     cudaStreamWaitEvent(p.s_cmp, p.in_done[slot], 0);
-    status = tcq4_b200_mul_mat(w_tiles_dev, p.hx[slot], p.hy[slot], M, N, K, d_perm, p.s_cmp);
+    {
+        size_t need = ws_layout(M, N, K).total;
+        for (int64_t m : {(int64_t)8, (int64_t)16}) need = std::max(need, ws_layout(std::min(M, m), N, K).total);
+        if (p.ws_bytes < need) {
+            if ((e = pipe_grow(p, &p.ws, &p.ws_bytes, need)) != cudaSuccess) return cuda_fail(e, "pipeline workspace cudaMalloc");
+            if ((e = cudaMemset(p.ws, 0, p.ws_bytes)) != cudaSuccess) return cuda_fail(e, "pipeline workspace memset");
+        }
+    }
+    status = tcq4_b200_mul_mat_ws(w_tiles_dev, p.hx[slot], p.hy[slot], M, N, K, d_perm, p.ws, p.ws_bytes, TCQ4_KERNEL_AUTO, p.s_cmp);
     if (status != TCQ4_OK) return status;
     cudaEventRecord(p.cmp_done[slot], p.s_cmp);
     cudaStreamWaitEvent(p.s_out, p.cmp_done[slot], 0);

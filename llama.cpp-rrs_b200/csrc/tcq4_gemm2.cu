@@ -381,7 +381,8 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
     volatile int *sm_go = reinterpret_cast<volatile int *>(tmem_slot) + 2;
 
     if (warp < G2_UNPACK_WARP0) {
-      asm volatile("setmaxnreg.dec.sync.aligned.u32 56;" ::: "memory");
+      if constexpr (NTL >= 7) asm volatile("setmaxnreg.dec.sync.aligned.u32 48;" ::: "memory");
+      else asm volatile("setmaxnreg.dec.sync.aligned.u32 56;" ::: "memory");
       if (warp == 0) {
         // ===================== producer: three copies per k-tile =====================
         //   the CTA's activation unit (32 KB, contiguous), its NTL raw tiles and the 160 metadata bytes of all 2*NTL
@@ -465,7 +466,8 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         }
       }
     } else if (warp < G2_EPI_WARP0) {
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;" ::: "memory");
+        if constexpr (NTL >= 7) asm volatile("setmaxnreg.dec.sync.aligned.u32 48;" ::: "memory");
+        else asm volatile("setmaxnreg.dec.sync.aligned.u32 56;" ::: "memory");
         // ===================== weight unpack (this CTA's NTL n-tiles) =====================
         const int uw = warp - G2_UNPACK_WARP0;
         if (FUSE)
@@ -556,7 +558,9 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
         }
     } else {
         // ===================== epilogue =====================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 152;" ::: "memory");
+        // 8*NTL accumulators + two 32-register TMEM steps in flight
+        if constexpr (NTL >= 7) asm volatile("setmaxnreg.inc.sync.aligned.u32 168;" ::: "memory");
+        else asm volatile("setmaxnreg.inc.sync.aligned.u32 152;" ::: "memory");
         const int ew = warp - G2_EPI_WARP0;                 // 0..7
         const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
         const int colhalf = ew >> 2;                        // 0: channels unpacked by CTA 0, 1: by CTA 1
@@ -634,37 +638,61 @@ tcq4_gemm2_kernel(const __grid_constant__ CUtensorMap tm_tiles, const __grid_con
                 const float *sn = sSn + ring * 128 + colhalf * 64;
                 const int anyz = sZflag[ring * 4 + colhalf * 2] | sZflag[ring * 4 + colhalf * 2 + 1];
                 const uint32_t t_hi = t_base + as * 256;
-                // two chunks of TMEM loads in flight: chunk ch+1 is requested before the math of chunk ch
-                uint32_t rh[2][8], rl[2][8];
-                tmem_ld_32x8(t_hi, rh[0]);
-                tmem_ld_32x8(t_hi + 8 * NTL, rl[0]);
+                // TMEM loads: 16 columns of hi and 16 of lo per step, the next step requested before the math of this one
+                // (tcgen05.wait::ld waits for ALL loads of the thread, so a step costs max(load latency, math): with 8-column
+                // steps the read phase of a k-tile was NTL x ~250 cycles of load latency -- longer than the k-tile's MMA time,
+                // and the two accumulator stages stalled the tensor pipe).  An odd NTL ends with one 8-column step.
+                constexpr int NP = NTL / 2;                     // 16-column steps
+                uint32_t rh[2][16], rl[2][16];
+                if (NP > 0) {
+                    tmem_ld_32x16(t_hi, rh[0]);
+                    tmem_ld_32x16(t_hi + 8 * NTL, rl[0]);
+                } else {
+                    tmem_ld_32x8(t_hi, *reinterpret_cast<uint32_t(*)[8]>(&rh[0][0]));
+                    tmem_ld_32x8(t_hi + 8 * NTL, *reinterpret_cast<uint32_t(*)[8]>(&rl[0][0]));
+                }
 #pragma unroll
-                for (int ch = 0; ch < NTL; ch++) {
+                for (int cp = 0; cp < NP + (NTL & 1); cp++) {
+                    const bool tail = cp == NP;                  // the 8-column step of an odd NTL
+                    const int nch = tail ? 1 : 2;                // n-tiles in this step
                     // S[] of this k-tile is read BEFORE the stage is handed back (ring slot reuse, see tcq4_gemm.cu)
-                    const ulonglong2 s01 = *reinterpret_cast<const ulonglong2 *>(sn + ch * 8);
-                    const ulonglong2 s23 = *reinterpret_cast<const ulonglong2 *>(sn + ch * 8 + 4);
-                    tmem_ld_wait();                  // chunk ch has landed
-                    if (ch + 1 < NTL) {
-                        tmem_ld_32x8(t_hi + (ch + 1) * 8, rh[(ch + 1) & 1]);
-                        tmem_ld_32x8(t_hi + 8 * NTL + (ch + 1) * 8, rl[(ch + 1) & 1]);
+                    ulonglong2 s01[2], s23[2];
+#pragma unroll
+                    for (int j = 0; j < 2; j++)
+                        if (j < nch) {
+                            s01[j] = *reinterpret_cast<const ulonglong2 *>(sn + (2 * cp + j) * 8);
+                            s23[j] = *reinterpret_cast<const ulonglong2 *>(sn + (2 * cp + j) * 8 + 4);
+                        }
+                    tmem_ld_wait();                  // step cp has landed
+                    if (cp + 1 < NP) {
+                        tmem_ld_32x16(t_hi + (cp + 1) * 16, rh[(cp + 1) & 1]);
+                        tmem_ld_32x16(t_hi + 8 * NTL + (cp + 1) * 16, rl[(cp + 1) & 1]);
+                    } else if (cp + 1 == NP && (NTL & 1)) {
+                        tmem_ld_32x8(t_hi + (cp + 1) * 16, *reinterpret_cast<uint32_t(*)[8]>(&rh[(cp + 1) & 1][0]));
+                        tmem_ld_32x8(t_hi + 8 * NTL + (cp + 1) * 16, *reinterpret_cast<uint32_t(*)[8]>(&rl[(cp + 1) & 1][0]));
                     } else {                         // all TMEM reads of this stage are done: hand it back
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0) g2_arrive_cluster(accempty_leader + (uint32_t)as * 8);
                         if (erole >= 0) G2_STAMP(erole, gk, 2);
                     }
-                    const uint64_t sv2[4] = {s01.x, s01.y, s23.x, s23.y};
 #pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const int is0 = g2_mad16(rh[ch & 1][2 * i], rl[ch & 1][2 * i]);             // = sum_g sc*dot, exact
-                        const int is1 = g2_mad16(rh[ch & 1][2 * i + 1], rl[ch & 1][2 * i + 1]);
-                        const uint64_t f2 = g2_mul2(g2_pack((float)is0, (float)is1), rm2);
-                        acc2[ch * 4 + i] = g2_fma2(f2, sv2[i], acc2[ch * 4 + i]);
-                        if (DEBUG) {
-                            const int n = n_base + ch * 8 + 2 * i;
-                            if (dbg_isum && mvalid && n < N) {
-                                dbg_isum[((size_t)m * N + n) * KT + kt] = is0;
-                                dbg_isum[((size_t)m * N + n + 1) * KT + kt] = is1;
+                    for (int j = 0; j < 2; j++) {
+                        if (j >= nch) continue;
+                        const int ch = 2 * cp + j;
+                        const uint64_t sv2[4] = {s01[j].x, s01[j].y, s23[j].x, s23[j].y};
+#pragma unroll
+                        for (int i = 0; i < 4; i++) {
+                            const int is0 = g2_mad16(rh[cp & 1][j * 8 + 2 * i], rl[cp & 1][j * 8 + 2 * i]);             // = sum_g sc*dot, exact
+                            const int is1 = g2_mad16(rh[cp & 1][j * 8 + 2 * i + 1], rl[cp & 1][j * 8 + 2 * i + 1]);
+                            const uint64_t f2 = g2_mul2(g2_pack((float)is0, (float)is1), rm2);
+                            acc2[ch * 4 + i] = g2_fma2(f2, sv2[i], acc2[ch * 4 + i]);
+                            if (DEBUG) {
+                                const int n = n_base + ch * 8 + 2 * i;
+                                if (dbg_isum && mvalid && n < N) {
+                                    dbg_isum[((size_t)m * N + n) * KT + kt] = is0;
+                                    dbg_isum[((size_t)m * N + n + 1) * KT + kt] = is1;
+                                }
                             }
                         }
                     }

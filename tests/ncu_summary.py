@@ -14,7 +14,7 @@ KEEP = [
     "sm__pipe_tc_cycles_active.avg.pct_of_peak_sustained_elapsed", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
     "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
     "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
-    "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic", "launch__cluster_size", "launch__occupancy_limit_registers",
+    "sm__inst_executed_pipe_tensor_op_hmma.sum", "sm__pipe_tensor_op_hmma_cycles_active.avg.pct_of_peak_sustained_elapsed", "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic", "launch__cluster_size", "launch__occupancy_limit_registers",
     "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
     "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
     "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
@@ -65,8 +65,46 @@ def launches(log, out, header):
     print("wrote", out, i, "launches")
 
 
+def traffic(prefill_rep, decode_rep, out):
+    """profiles/traffic_r02.json for bench.py: DRAM bytes (read + write) per launch of the dominant kernels, averaged over
+    the launches of the capture (one layer's GEMM launches / decode GEMV launches of the bench's own graphs)."""
+    import json
+
+    def avg(rep, pat):
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+        rows = list(csv.reader(io.StringIO(raw)))
+        names, units, ls = rows[0], rows[1], rows[2:]
+        col = {n: i for i, n in enumerate(names)}
+        tot, per = [], []
+        for l in ls:
+            if pat not in l[col["Kernel Name"]]:
+                continue
+            b = 0.0
+            for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                v = float(l[col[m]].replace(",", ""))
+                b += v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[units[col[m]]]
+            tot.append(b)
+            per.append((l[col["Kernel Name"]].split("(")[0][-40:], l[col["Grid Size"]], int(b)))
+        return (sum(tot) / len(tot) if tot else None), per
+
+    pg, pl = avg(prefill_rep, "gemm")
+    dg, dl = avg(decode_rep, "gemv")
+    d = {"prefill_gemm_bytes_per_launch": pg, "decode_gemv_bytes_per_launch": dg,
+         "prefill_note": f"dram__bytes_read.sum + dram__bytes_write.sum, mean over {len(pl)} GEMM launches (the first two layers of the "
+                         f"bench's timed step: fan-out q/k/v, attn_output, fan-out gate/up, ffn_down) of one ncu --set full capture "
+                         f"(profiles/prof_prefill_r02_summary.csv); weights come from DRAM once, codes and most of y stay in the 126 MB L2",
+         "decode_note": f"same, mean over {len(dl)} decode launches (segmented q/k/v GEMV, attn_output, segmented gate/up, ffn_down; "
+                        f"profiles/prof_decode_r02_summary.csv)",
+         "prefill_launches": pl, "decode_launches": dl}
+    with open(out, "w") as f:
+        json.dump(d, f, indent=1)
+    print("wrote", out, pg, dg)
+
+
 if __name__ == "__main__":
-    if sys.argv[1] == "--launches":
+    if sys.argv[1] == "--traffic":
+        traffic(sys.argv[2], sys.argv[3], sys.argv[4])
+    elif sys.argv[1] == "--launches":
         launches(sys.argv[2], sys.argv[3], sys.argv[4] if len(sys.argv) > 4 else "# launch list")
     else:
         report(sys.argv[1], sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "# ncu summary")
