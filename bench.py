@@ -202,9 +202,10 @@ def base_config():
 class Chain:
     """The 252 matmuls of Qwen3-4B, N-sharded over `world` ranks (shard = contiguous tile byte range)."""
 
-    def __init__(self, t4, torch, M, world, rank, weights=None, gather=True, mode="fused", per_node=False):
+    def __init__(self, t4, torch, M, world, rank, weights=None, gather=True, mode="fused", per_node=False, barrier="layer"):
         self.t4, self.torch, self.M, self.world, self.rank = t4, torch, M, world, rank
         self.gather = gather                           # False: the sharded MUL_MATs alone (SURVEY 8e reports both)
+        self.barrier = barrier                         # cross-GPU barrier per "layer" (a consumer of layer l's outputs may start) or per "step"
         self.ops = []                                  # (sharded weight, K, N)
         if weights is None:
             weights = []
@@ -235,25 +236,48 @@ class Chain:
                 # fused path: every rank's epilogue stores its column block straight into every rank's C
                 import torch.distributed as dist
                 import torch.distributed._symmetric_memory as symm_mem
-                self.sym = {}
-                for N in Ns:
+                self.sym = {}                          # one symmetric C per matmul of a layer (every node has its own dst)
+                for j, (_, N, _) in enumerate(QWEN3_4B_LAYER):
                     buf = symm_mem.empty((M, N), dtype=torch.float32, device="cuda")
                     hdl = symm_mem.rendezvous(buf, dist.group.WORLD)
-                    self.sym[N] = (buf, hdl, [int(p) for p in hdl.buffer_ptrs])
-                self.mc = {N: int(getattr(self.sym[N][1], "multicast_ptr", 0) or 0) for N in Ns}
+                    self.sym[j] = (buf, hdl, [int(p) for p in hdl.buffer_ptrs])
+                self.mc = {j: int(getattr(self.sym[j][1], "multicast_ptr", 0) or 0) for j in self.sym}
+                self.pbar = t4.PeerBarrier()           # tcq4_b200_peer_barrier: one 32-thread kernel per barrier
                 if mode == "multicast" and not all(self.mc.values()):
                     raise RuntimeError("no multicast (NVLS) address for the symmetric buffers")
                 self.mode = mode
                 if mode == "multicast":
                     self.gather_kind = ("epilogue stores through the NVSwitch multicast address of the symmetric C (multimem.st, "
-                                        "tcq4_b200_mul_mat_multicast) + one cross-GPU barrier per step")
+                                        f"tcq4_b200_mul_mat_multicast) + one cross-GPU barrier per {barrier}")
                 elif mode == "fused":
                     self.gather_kind = ("fused peer stores (tcq4_b200_mul_mat_peers over symmetric memory) + one cross-GPU "
-                                        "barrier per step")
+                                        f"barrier per {barrier}")
                 else:
                     self.copy_streams = [torch.cuda.Stream() for _ in range(world)]
+                    # the MUL_MATs of this variant are ordinary single-destination calls, so they go through the graph-level
+                    # entry like the single-GPU step: one GgmlGraph per run of nodes sharing src1 (q/k/v, o, gate/up, down),
+                    # each node's dst = this rank's column window of the symmetric C
+                    Lr = len(QWEN3_4B_LAYER)
+                    fan = {"attn_q": 0, "attn_k": 0, "attn_v": 0, "ffn_gate": 1, "ffn_up": 1}
+                    self.groups = []
+                    i = 0
+                    while i < len(weights):
+                        j = i + 1
+                        gi = fan.get(QWEN3_4B_LAYER[i % Lr][0])
+                        while gi is not None and j < len(weights) and j // Lr == i // Lr and fan.get(QWEN3_4B_LAYER[j % Lr][0]) == gi:
+                            j += 1
+                        nodes = []
+                        for t in range(i, j):
+                            w = weights[t]
+                            if w.n_local:
+                                out = self.sym[t % Lr][0][:, w.n0:w.n1]
+                                nodes.append((w.tiles, self.x[w.K], out, w.n_local, f"blk.{t // Lr}.{QWEN3_4B_LAYER[t % Lr][0]}.weight"))
+                        self.groups.append((t4.GgmlGraph(nodes) if nodes else None, list(range(i, j))))
+                        i = j
+                    t4.reserve(M, max(max(w.n_local for w in weights), 8), max(K for _, _, K in QWEN3_4B_LAYER))
+                    t4.reserve(M, max(8, sum(w.n_local for w in weights[4:6])), 2560)
                     self.gather_kind = ("MUL_MAT into the local symmetric C + copy-engine pushes of the column block to every "
-                                        "peer on side streams (tcq4_b200_push_columns) + one cross-GPU barrier per step")
+                                        f"peer on side streams (tcq4_b200_push_columns) + one cross-GPU barrier per {barrier}")
             except Exception as e:  # noqa: BLE001
                 print(f"[bench] symmetric memory unavailable ({type(e).__name__}: {e}); NCCL all-gather on a second stream",
                       file=sys.stderr)
@@ -266,15 +290,17 @@ class Chain:
         # single GPU: the step is ONE call of the graph-level entry (tcq4_b200_ggml_graph_compute) over the 252 MUL_MAT nodes in
         # execution order, every node with its own dst as in a ggml graph; the library fans out the runs that share src1
         self.ggml = None
-        if world == 1 and not per_node:
-            self.y_node = {name: torch.empty((M, N), device="cuda") for name, N, _ in QWEN3_4B_LAYER}
+        if (world == 1 or not gather) and not per_node:      # (N > 1 without the exchange: the same graph over the shards)
+            Lr = len(QWEN3_4B_LAYER)
+            self.y_node = {QWEN3_4B_LAYER[j][0]: torch.empty((M, max(8, weights[j].n_local)), device="cuda") for j in range(Lr)}
             nodes = []
             for i, w in enumerate(weights):
-                name = QWEN3_4B_LAYER[i % len(QWEN3_4B_LAYER)][0]
-                nodes.append((w.tiles, self.x[w.K], self.y_node[name], w.N, f"blk.{i // len(QWEN3_4B_LAYER)}.{name}.weight"))
+                name = QWEN3_4B_LAYER[i % Lr][0]
+                if w.n_local:
+                    nodes.append((w.tiles, self.x[w.K], self.y_node[name], w.n_local, f"blk.{i // Lr}.{name}.weight"))
             self.ggml = t4.GgmlGraph(nodes)
-            t4.reserve(M, max(N for _, N, _ in QWEN3_4B_LAYER), max(K for _, _, K in QWEN3_4B_LAYER))
-            t4.reserve(M, sum(N for n, N, _ in QWEN3_4B_LAYER if n in ("ffn_gate", "ffn_up")), 2560)
+            t4.reserve(M, max(8, max(w.n_local for w in weights)), max(K for _, _, K in QWEN3_4B_LAYER))
+            t4.reserve(M, max(8, sum(w.n_local for w in weights[4:6])), 2560)
 
     def weight_bytes(self):
         return sum(w.tiles.numel() for w in self.weights)
@@ -282,39 +308,44 @@ class Chain:
     def step_eager(self):
         torch = self.torch
         last = None
-        if self.sym is not None and self.mode == "multicast":
-            for w in self.weights:
+        L = len(QWEN3_4B_LAYER)
+        any_hdl = self.sym[0][1] if self.sym is not None else None
+        if self.sym is not None and self.mode in ("multicast", "fused"):
+            for i, w in enumerate(self.weights):
+                buf, hdl, ptrs = self.sym[i % L]
                 if w.n_local:
-                    self.t4.mul_mat_multicast(w.tiles, self.x[w.K], self.mc[w.N], w.N, w.n0, w.n_local)
-                last = self.sym[w.N][0]
-            self.sym[self.weights[-1].N][1].barrier()
-            return last
-        if self.sym is not None and self.mode == "fused":
-            for w in self.weights:
-                buf, hdl, ptrs = self.sym[w.N]
-                if w.n_local:
-                    self.t4.mul_mat_peers(w.tiles, self.x[w.K], ptrs, w.N, w.n0, w.n_local)
+                    if self.mode == "multicast":
+                        self.t4.mul_mat_multicast(w.tiles, self.x[w.K], self.mc[i % L], w.N, w.n0, w.n_local)
+                    else:
+                        self.t4.mul_mat_peers(w.tiles, self.x[w.K], ptrs, w.N, w.n0, w.n_local)
                 last = buf
-            self.sym[self.weights[-1].N][1].barrier()     # every rank's stores of this step have landed everywhere
+                if self.barrier == "layer" and (i + 1) % L == 0:
+                    self.pbar()                      # every rank's stores of this layer have landed everywhere
+            if self.barrier != "layer":
+                self.pbar()
             return last
         if self.sym is not None:
             main = torch.cuda.current_stream()
-            for w in self.weights:
-                buf, hdl, ptrs = self.sym[w.N]
-                if w.n_local:
-                    self.t4.mul_mat_peers(w.tiles, self.x[w.K], [ptrs[self.rank]], w.N, w.n0, w.n_local)
-                    ev = torch.cuda.Event()
-                    ev.record(main)
+            for g, idxs in self.groups:
+                if g is not None:
+                    g.compute()
+                ev = torch.cuda.Event()
+                ev.record(main)
+                for r in range(self.world):
+                    if r != self.rank:
+                        cs = self.copy_streams[r]
+                        cs.wait_event(ev)
+                        for t in idxs:
+                            w = self.weights[t]
+                            if w.n_local:
+                                ptrs = self.sym[t % L][2]
+                                self.t4.push_columns(ptrs[r], ptrs[self.rank], self.M, w.N, w.n0, w.n_local, stream=cs)
+                last = self.sym[idxs[-1] % L][0]
+                if (self.barrier == "layer" and (idxs[-1] + 1) % L == 0) or idxs[-1] + 1 == len(self.weights):
                     for r in range(self.world):
                         if r != self.rank:
-                            cs = self.copy_streams[r]
-                            cs.wait_event(ev)
-                            self.t4.push_columns(ptrs[r], ptrs[self.rank], self.M, w.N, w.n0, w.n_local, stream=cs)
-                last = buf
-            for r in range(self.world):
-                if r != self.rank:
-                    main.wait_stream(self.copy_streams[r])
-            self.sym[self.weights[-1].N][1].barrier()
+                            main.wait_stream(self.copy_streams[r])
+                    self.pbar()
             return last
         if self.ggml is not None:
             self.ggml.compute()
@@ -362,70 +393,6 @@ class Chain:
             self.step_eager()
 
 
-class FanoutChain:
-    """The same 252 matmuls with the graph-level fusion of SURVEY 8 f4: q/k/v and gate/up share their activations, so each
-    group is ONE tcq4_b200_mul_mat_fanout call (one activation stage at prefill, one GEMV launch at decode).  Single GPU."""
-
-    def __init__(self, t4, torch, M, base):
-        self.t4, self.torch, self.M = t4, torch, M
-        self.x = base.x
-        L = len(QWEN3_4B_LAYER)
-        self.layers = []
-        for l in range(QWEN3_4B_LAYERS):
-            w = base.weights[l * L:(l + 1) * L]
-            byname = {name: w[j] for j, (name, _, _) in enumerate(QWEN3_4B_LAYER)}
-            self.layers.append((w, byname))
-        names = [n for n, _, _ in QWEN3_4B_LAYER]
-        self.groups = []                                # per layer: list of ("fan", Fanout, K, outs) | ("one", weight, out)
-        y = {n: torch.empty((M, N), device="cuda") for n, N, _ in QWEN3_4B_LAYER}
-        self.y = y
-        fan_sets = [s for s in (("attn_q", "attn_k", "attn_v"), ("ffn_gate", "ffn_up")) if all(n in names for n in s)]
-        for w, byname in self.layers:
-            ops, done = [], set()
-            for n, N, K in QWEN3_4B_LAYER:
-                if n in done:
-                    continue
-                fs = next((s for s in fan_sets if n in s), None)
-                if fs:
-                    ws = [byname[m] for m in fs]
-                    ops.append(("fan", t4.Fanout([v.tiles for v in ws], [v.N for v in ws], K), K, [y[m] for m in fs]))
-                    done.update(fs)
-                else:
-                    ops.append(("one", byname[n], K, y[n]))
-            self.groups.append(ops)
-        t4.reserve(M, max(N for _, N, _ in QWEN3_4B_LAYER), max(K for _, _, K in QWEN3_4B_LAYER))
-        for fs in fan_sets:                             # the segmented decode launch plans over the summed channels
-            t4.reserve(M, sum(N for n, N, _ in QWEN3_4B_LAYER if n in fs), max(K for n, _, K in QWEN3_4B_LAYER if n in fs))
-        self.graph = None
-
-    def step_eager(self):
-        for ops in self.groups:
-            for kind, a, K, out in ops:
-                if kind == "fan":
-                    a(self.x[K], outs=out)
-                else:
-                    self.t4.mul_mat(a.tiles, self.x[K], a.N, out=out)
-
-    def capture(self):
-        torch = self.torch
-        c0 = self.t4.launch_count()
-        self.step_eager()
-        self.launches_per_step = self.t4.launch_count() - c0
-        torch.cuda.synchronize()
-        g = torch.cuda.CUDAGraph()
-        s = torch.cuda.Stream()
-        s.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(s):
-            with torch.cuda.graph(g, stream=s):
-                self.step_eager()
-        torch.cuda.current_stream().wait_stream(s)
-        torch.cuda.synchronize()
-        self.graph = g
-
-    def step(self):
-        self.graph.replay()
-
-
 def per_node_leg(t4, torch, pre, dec, steps, warmup):
     """The same chains with one tcq4_b200_mul_mat call per MUL_MAT node (no graph-level fusion), reported beside the headline;
     the outputs of the last layer are compared (prefill: bit-identical unless a K split applies to the node; decode: the fp32
@@ -448,6 +415,112 @@ def per_node_leg(t4, torch, pre, dec, steps, warmup):
         out[key] = {"ms_per_step": ms, "value": M / (ms * 1e-3), "unit": UNIT, "launches_per_step": int(pn.launches_per_step),
                     "graph_outputs_bit_identical_to_per_node": same, "nmse_graph_vs_per_node": worst}
         del pn
+    return out
+
+
+# BASELINE.json configs[3] and configs[4]: one transformer layer's seven TCQ4 matmuls (name, N, K), N-sharded over the ranks
+BIG_CONFIGS = {
+    "qwen3_32b_prefill4096": {"Ms": [4096], "worlds": (1, 2, 4, 8),
+                              "layer": [("attn_q", 8192, 5120), ("attn_k", 1024, 5120), ("attn_v", 1024, 5120), ("attn_output", 5120, 8192),
+                                        ("ffn_gate", 25600, 5120), ("ffn_up", 25600, 5120), ("ffn_down", 5120, 25600)]},
+    "llama3_70b_column_parallel": {"Ms": [1, 8, 64, 512, 4096, 8192], "worlds": (1, 8),
+                                   "layer": [("attn_q", 8192, 8192), ("attn_k", 1024, 8192), ("attn_v", 1024, 8192), ("attn_output", 8192, 8192),
+                                             ("ffn_gate", 28672, 8192), ("ffn_up", 28672, 8192), ("ffn_down", 8192, 28672)]},
+}
+
+
+def configs_leg(t4, torch, dist, world, rank, mode):
+    """Per config and batch size: one layer's seven N-sharded MUL_MATs, (a) into this rank's own C only, (b) with the exchange
+    of the fp32 column blocks (`mode`) and one cross-GPU barrier per layer.  ms per layer (max over ranks), useful TOP/s per GPU,
+    outbound exchange bytes per GPU and layer, and the NVLink time those bytes would need at 900 GB/s per direction."""
+    out = {}
+    symm_mem = None
+    if world > 1:
+        import torch.distributed._symmetric_memory as symm_mem
+        pbar = t4.PeerBarrier()
+        copy_streams = [torch.cuda.Stream() for _ in range(world)]
+    for cname, cfg in BIG_CONFIGS.items():
+        if world not in cfg["worlds"]:
+            continue
+        res = []
+        for M in cfg["Ms"]:
+            ws_, xs, cs, fans = [], {}, [], None
+            for j, (_, N, K) in enumerate(cfg["layer"]):
+                n0, n1, _, _ = t4.shard_range(N, K, world, rank, 64)
+                ws_.append(t4.ShardedWeight(N, K, world, rank, tiles_local=t4.random_tiles(n1 - n0, K, seed=977 + j * 8 + rank), align=64))
+                if K not in xs:
+                    xs[K] = torch.randn((M, K), device="cuda")
+                if world > 1:
+                    buf = symm_mem.empty((M, N), dtype=torch.float32, device="cuda")
+                    hdl = symm_mem.rendezvous(buf, dist.group.WORLD)
+                    cs.append((buf, hdl, [int(p) for p in hdl.buffer_ptrs], int(getattr(hdl, "multicast_ptr", 0) or 0)))
+                else:
+                    cs.append((torch.empty((M, N), device="cuda"), None, None, 0))
+            t4.reserve(M, max(w.n_local for w in ws_) or 8, max(K for _, _, K in cfg["layer"]))
+
+            def layer(exchange):
+                main = torch.cuda.current_stream()
+                for j, w in enumerate(ws_):
+                    buf, hdl, ptrs, mc = cs[j]
+                    if not w.n_local:
+                        continue
+                    if world == 1:
+                        t4.mul_mat(w.tiles, xs[w.K], w.N, out=buf)
+                    elif not exchange or mode == "dma":
+                        t4.mul_mat_peers(w.tiles, xs[w.K], [ptrs[rank]], w.N, w.n0, w.n_local)
+                        if exchange:                       # copy engines push the finished column block while the next matmul runs
+                            ev = torch.cuda.Event()
+                            ev.record(main)
+                            for r in range(world):
+                                if r != rank:
+                                    copy_streams[r].wait_event(ev)
+                                    t4.push_columns(ptrs[r], ptrs[rank], M, w.N, w.n0, w.n_local, stream=copy_streams[r])
+                    elif mode == "multicast" and mc:
+                        t4.mul_mat_multicast(w.tiles, xs[w.K], mc, w.N, w.n0, w.n_local)
+                    else:
+                        t4.mul_mat_peers(w.tiles, xs[w.K], ptrs, w.N, w.n0, w.n_local)
+                if world > 1 and exchange:
+                    if mode == "dma":
+                        for r in range(world):
+                            if r != rank:
+                                main.wait_stream(copy_streams[r])
+                    pbar()
+
+            def time_it(exchange, reps=5):
+                for _ in range(2):
+                    layer(exchange)
+                torch.cuda.synchronize()
+                if world > 1:
+                    dist.barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(reps):
+                    layer(exchange)
+                e1.record()
+                torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1) / reps
+                if world > 1:
+                    t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                    ms = float(t.item())
+                return ms
+
+            ms_local = time_it(False)
+            ms_x = time_it(True) if world > 1 else None
+            ops_gpu = sum(2 * M * w.n_local * w.K for w in ws_)
+            out_bytes = sum(4 * M * w.n_local for w in ws_) * (1 if (mode == "multicast") else (world - 1)) if world > 1 else 0      # per GPU, outbound
+            r = {"M": M, "ms_per_layer_shard_local": ms_local, "useful_tops_per_gpu_shard_local": ops_gpu / (ms_local * 1e-3) / 1e12,
+                 "weight_gbs_per_gpu_shard_local": sum(w.tiles.numel() for w in ws_) / (ms_local * 1e-3) / 1e9}
+            if world > 1:
+                r.update({"ms_per_layer_with_exchange": ms_x, "useful_tops_per_gpu_with_exchange": ops_gpu / (ms_x * 1e-3) / 1e12,
+                          "exchange_outbound_bytes_per_gpu": out_bytes,
+                          "nvlink_bound_ms_at_900GBs": out_bytes / 900e9 * 1e3,
+                          "exchange_gbs_per_gpu_if_serial": out_bytes / (ms_x * 1e-3) / 1e9})
+            res.append(r)
+            del ws_, xs, cs
+            torch.cuda.empty_cache()
+        out[cname] = {"shapes": [f"{n}: N={N} K={K}" for n, N, K in cfg["layer"]], "exchange": mode if world > 1 else "none",
+                      "timing": "eager calls, CUDA events over 5 layer passes, max over ranks", "per_batch": res}
     return out
 
 
@@ -557,56 +630,71 @@ def run_own_arm(args):
     ms_dec = timed_steps(torch, dist, dec, dec_steps, max(args.warmup, 3), world)
     torch.cuda.profiler.stop()
     clocks = sampler.stop() if rank == 0 else None
-    fused_ok = None
     variants = None
+    exchange_rule = None
     if world > 1 and pre.sym is not None:
+        L = len(QWEN3_4B_LAYER)
+
         def check(chain):
-            # one-off check (not timed): the exchange gives the same full C as the NCCL all-gather
-            chain.sym[chain.weights[-1].N][0].zero_()
+            # one-off check (not timed): after a step, the symmetric C of EVERY matmul of the last layer equals the NCCL
+            # all-gather of the shard outputs, bitwise, on every rank
+            for j in chain.sym:
+                chain.sym[j][0].fill_(float("nan"))
             torch.cuda.synchronize()
             dist.barrier()
             chain.step_eager()
             torch.cuda.synchronize()
             dist.barrier()
-            wl = chain.weights[-1]
-            want = wl.forward(chain.x[wl.K], workspace=chain.ws)
-            torch.cuda.synchronize()
-            ok = bool(torch.equal(chain.sym[wl.N][0], want))
+            ok = True
+            for j in range(L):
+                wl = chain.weights[-L + j]
+                want = wl.forward(chain.x[wl.K], workspace=chain.ws)
+                torch.cuda.synchronize()
+                ok = ok and bool(torch.equal(chain.sym[j][0], want))
+            t = torch.tensor([1 if ok else 0], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
             dist.barrier()
-            return ok
-        fused_ok = check(pre)
-        # second variant of the exchange: copy engines instead of the epilogue's own peer stores
-        pre_dma = Chain(t4, torch, M, world, rank, weights=pre.weights, mode="dma")
-        pre_dma.capture()
-        ms_step_dma = timed_steps(torch, dist, pre_dma, args.steps, args.warmup, world)
-        dec_dma = Chain(t4, torch, 1, world, rank, weights=pre.weights, mode="dma")
-        dec_dma.capture()
-        ms_dec_dma = timed_steps(torch, dist, dec_dma, dec_steps, max(args.warmup, 3), world)
-        dma_ok = check(pre_dma)
-        variants = {"fused_peer_stores": {"ms_per_step": ms_step, "decode_ms_per_step": ms_dec, "matches_nccl": fused_ok},
-                    "copy_engine_pushes": {"ms_per_step": ms_step_dma, "decode_ms_per_step": ms_dec_dma, "matches_nccl": dma_ok}}
-        best = (ms_step, pre.gather_kind)
-        if ms_step_dma < best[0]:
-            best = (ms_step_dma, pre_dma.gather_kind)
-        ms_dec = min(ms_dec, ms_dec_dma)
+            return bool(t.item())
+
+        variants = {}
+        timed = {}
+        for key, mode in (("fused_peer_stores", "fused"), ("switch_multicast_stores", "multicast"), ("copy_engine_pushes", "dma")):
+            try:
+                if mode == "fused":
+                    p_, d_ = pre, dec
+                else:
+                    p_ = Chain(t4, torch, M, world, rank, weights=pre.weights, mode=mode)
+                    if p_.sym is None or p_.mode != mode:
+                        raise RuntimeError(f"{mode} unavailable")
+                    p_.capture()
+                    d_ = Chain(t4, torch, 1, world, rank, weights=pre.weights, mode=mode)
+                    d_.capture()
+                ms_p = ms_step if mode == "fused" else timed_steps(torch, dist, p_, args.steps, args.warmup, world)
+                ms_d = ms_dec if mode == "fused" else timed_steps(torch, dist, d_, dec_steps, max(args.warmup, 3), world)
+                variants[key] = {"ms_per_step": ms_p, "decode_ms_per_step": ms_d, "matches_nccl_all_7_outputs": check(p_),
+                                 "sync": "one cross-GPU barrier per layer (36 per step)"}
+                timed[key] = (ms_p, ms_d, p_.gather_kind)
+            except Exception as e:  # noqa: BLE001
+                variants[key] = {"unavailable": f"{type(e).__name__}: {e}"}
+        # ONE variant per run, chosen by rule (not the fastest of three per leg): the switch's multicast when the fabric offers
+        # it (outbound traffic 1x instead of (G-1)x), else the fused peer stores
+        # (round 2: the copy-engine variant is the rule's first choice -- its MUL_MATs are ordinary single-destination calls and so
+        # take the graph-level fan-out like the single-GPU step, and its transfers use no SM; the store variants follow)
+        # G = 2: one push per output; G > 2: the copy engines would move every block G-1 times (and at G = 8 issue 1 764 copies per
+        # step), the switch replicates ONE multicast store stream
+        order = ("copy_engine_pushes", "switch_multicast_stores", "fused_peer_stores") if world == 2 else \
+                ("switch_multicast_stores", "copy_engine_pushes", "fused_peer_stores")
+        exchange_rule = next(k for k in order if k in timed)
+        ms_step, ms_dec, pre.gather_kind = timed[exchange_rule]
+        # the same variant with ONE barrier per step (round 1's placement), for comparison
         try:
-            pre_mc = Chain(t4, torch, M, world, rank, weights=pre.weights, mode="multicast")
-            if pre_mc.sym is None or pre_mc.mode != "multicast":
-                raise RuntimeError("multicast unavailable")
-            pre_mc.capture()
-            ms_step_mc = timed_steps(torch, dist, pre_mc, args.steps, args.warmup, world)
-            dec_mc = Chain(t4, torch, 1, world, rank, weights=pre.weights, mode="multicast")
-            dec_mc.capture()
-            ms_dec_mc = timed_steps(torch, dist, dec_mc, dec_steps, max(args.warmup, 3), world)
-            mc_ok = check(pre_mc)
-            variants["switch_multicast_stores"] = {"ms_per_step": ms_step_mc, "decode_ms_per_step": ms_dec_mc, "matches_nccl": mc_ok}
-            if mc_ok and ms_step_mc < best[0]:
-                best = (ms_step_mc, pre_mc.gather_kind)
-            if mc_ok:
-                ms_dec = min(ms_dec, ms_dec_mc)
+            p1 = Chain(t4, torch, M, world, rank, weights=pre.weights, mode={"switch_multicast_stores": "multicast", "copy_engine_pushes": "dma",
+                                                                            "fused_peer_stores": "fused"}[exchange_rule], barrier="step")
+            p1.capture()
+            variants[exchange_rule]["ms_per_step_one_barrier_per_step"] = timed_steps(torch, dist, p1, args.steps, args.warmup, world)
+            del p1
         except Exception as e:  # noqa: BLE001
-            variants["switch_multicast_stores"] = {"unavailable": f"{type(e).__name__}: {e}"}
-        ms_step, pre.gather_kind = best
+            variants[exchange_rule]["one_barrier_per_step_error"] = f"{type(e).__name__}: {e}"
     # ---- N > 1: the same chains without the fp32 all-gather (the sharded MUL_MATs alone; SURVEY 8e asks for both) ----
     ms_step_ng = ms_dec_ng = None
     if world > 1:
@@ -618,8 +706,8 @@ def run_own_arm(args):
         ms_dec_ng = timed_steps(torch, dist, dec_ng, dec_steps, max(args.warmup, 3), world)
 
     # ---- per-kernel roofline legs (N-shard-local kernels; events on the launching stream) ----------------
-    gm_ms, act_ms, gm_n = kernel_leg(t4, torch, pre, args.steps, t4.KERNEL_AUTO, M)
-    gv_ms, _, gv_n = kernel_leg(t4, torch, dec, min(dec_steps, 10), t4.KERNEL_GEMV, 1)
+    gm_ms, act_ms, gm_n = kernel_leg(t4, torch, pre_ng if world > 1 else pre, args.steps, t4.KERNEL_AUTO, M)
+    gv_ms, _, gv_n = kernel_leg(t4, torch, dec_ng if world > 1 else dec, min(dec_steps, 10), t4.KERNEL_GEMV, 1)
     ops_local = sum(2 * M * w.n_local * w.K for w in pre.weights)                 # per step, this rank
     bytes_local_dec = sum(alg_bytes(1, w.n_local, w.K) for w in dec.weights)
     i8_peak = 2.0 * peaks["bf16_tflops"]          # dense int8 = 2 x dense bf16 on the same tensor pipe
@@ -640,8 +728,20 @@ def run_own_arm(args):
     # is nothing but these launches, so step time / launches is the per-launch duration including every gap between them
     ms_dec_local = ms_dec_ng if (world > 1 and ms_dec_ng) else ms_dec
     gv_gbs = bytes_local_dec / (ms_dec_local * 1e-3) / 1e9
-    dec_launches = int(dec.launches_per_step or len(dec.weights))
+    dec_launches = int((dec_ng if world > 1 else dec).launches_per_step or len(dec.weights))
     traffic = load_traffic()
+
+    # ---- BASELINE configs[3] / configs[4] on this many GPUs ------------------------------------------------
+    big_configs = None
+    if not args.no_configs:
+        try:
+            big_configs = configs_leg(t4, torch, dist, world, rank,
+                                      {"switch_multicast_stores": "multicast", "copy_engine_pushes": "dma"}.get(exchange_rule, "peers"))
+        except Exception as e:  # noqa: BLE001
+            big_configs = {"error": f"{type(e).__name__}: {e}"}
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
 
     # ---- end to end through the host-buffer C-ABI call ---------------------------------------------------
     e2e_s, h2d, d2h = e2e_leg(t4, torch, pre, max(1, min(args.steps, 2)), M)
@@ -671,8 +771,8 @@ def run_own_arm(args):
             "decode": {"value": 1.0 / (ms_dec * 1e-3), "unit": UNIT, "ms_per_step": ms_dec, "steps": dec_steps,
                        "gbs": total_dec_bytes / (ms_dec * 1e-3) / 1e9, "frac_hbm": total_dec_bytes / (ms_dec * 1e-3) / 1e9
                        / (peaks["hbm_gbs"] * world), "cuda_graph": dec.graph is not None},
-            "roofline": {"bound": "tensor", "kernel": ("tcq4_gemm3_kernel (tcgen05.mma.cta_group::2 kind::f16 on exact fp16 integers)" if world == 1
-                                                        else "tcq4_gemm2_kernel (tcgen05.mma.cta_group::2 kind::i8; several destinations)"),
+            "roofline": {"bound": "tensor", "kernel": "tcq4_gemm3_kernel (tcgen05.mma.cta_group::2 kind::f16 on exact fp16 integers; fan-out groups) "
+                                                       "and tcq4_gemm2_kernel (kind::i8; single matrices)",
                          "achieved": gm_tops, "peak": i8_peak, "unit": "TOP/s", "frac": gm_tops / i8_peak,
                          "traffic": traffic.get("prefill_gemm_bytes_per_launch"),
                          "traffic_note": traffic.get("prefill_note", "no ncu capture of this round in profiles/traffic_r02.json"),
@@ -699,7 +799,8 @@ def run_own_arm(args):
             "clocks": clocks,
         }
         if world > 1:
-            line["detail"]["exchange_variants"] = variants      # value / decode use the faster one
+            line["detail"]["exchange_variants"] = variants
+            line["detail"]["exchange_rule"] = f"value and decode use {exchange_rule} (rule: copy engines at 2 GPUs, switch multicast above, peer stores as the fallback; never best-of-three)"
             line["sharded_mul_mat_only"] = {
                 "note": "same chains without the fp32 all-gather of the N-sharded outputs (max over ranks)",
                 "value": M / (ms_step_ng * 1e-3), "unit": UNIT, "ms_per_step": ms_step_ng,
@@ -710,6 +811,7 @@ def run_own_arm(args):
                 line["per_node"] = per_node_leg(t4, torch, pre, dec, args.steps, args.warmup)
             except Exception as e:  # noqa: BLE001
                 line["per_node"] = {"error": f"{type(e).__name__}: {e}"}
+        line["configs"] = big_configs
         if world == 1 and not args.no_cpu_baseline:
             try:
                 line["cpu_baseline"] = cpu_baseline_leg()
@@ -749,6 +851,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the BASELINE configs[3]/[4] layer timings")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

@@ -131,6 +131,11 @@ TCQ4_B200_API int tcq4_b200_mul_mat_add(const void *w_tiles, const float *x, flo
 TCQ4_B200_API int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N, float *const *y,
                                            const float *x, int64_t M, int64_t K, const int32_t *d_perm,
                                            cudaStream_t stream);
+/* Same with a leading dimension per output (ldc[i] >= N[i], multiple of 4; NULL: contiguous): y[i] may be a column window of a
+ * wider row-major matrix (a ggml view; this GPU's column block of an N-sharded C). */
+TCQ4_B200_API int tcq4_b200_mul_mat_fanout_ld(int n, const void *const *w_tiles, const int64_t *N, float *const *y,
+                                              const int64_t *ldc, const float *x, int64_t M, int64_t K,
+                                              const int32_t *d_perm, cudaStream_t stream);
 
 /* MUL_MAT_ID, the mixture-of-experts form of the same operator: replaces ggml_cuda_mul_mat_id
  * (ggml-cuda.cu:2287-2436) for a TCQ4 src0, which the reference admits in supports_op (:4457-4459) and serves through
@@ -172,6 +177,11 @@ TCQ4_B200_API int tcq4_b200_mul_mat_multicast(const void *w_tiles, const float *
  * (one cudaMemcpy2DAsync; no SM work, overlaps the next matmul when issued on a side stream). */
 TCQ4_B200_API int tcq4_b200_push_columns(float *dst_base, const float *src_base, int64_t M, int64_t ldc, int64_t col0,
                                          int64_t ncols, cudaStream_t stream);
+/* Cross-GPU barrier for the exchange (no counterpart in the fork): flags_peers[r] = rank r's peer-mapped int32[9] (8 peer
+ * slots + this rank's epoch), zeroed once; every rank calls it after the stores / pushes its consumers depend on.  One
+ * 32-thread kernel on `stream` (release / acquire at system scope), capturable. */
+#define TCQ4_B200_MAX_PEERS 8
+TCQ4_B200_API int tcq4_b200_peer_barrier(int *const *flags_peers, int n_peers, int rank, cudaStream_t stream);
 
 TCQ4_B200_API int tcq4_b200_mul_mat_host(const void *w_tiles_dev, const float *x_host, float *y_host,
                                          int64_t M, int64_t N, int64_t K, const int32_t *d_perm,

@@ -41,14 +41,14 @@ STATUS = {0: "OK", 1: "ERR_SHAPE", 2: "ERR_ARG", 3: "ERR_WORKSPACE", 4: "ERR_CUD
 EXPORTS = [
     "tcq4_b200_version", "tcq4_b200_last_error", "tcq4_b200_supports", "tcq4_b200_select_kernel",
     "tcq4_b200_workspace_size", "tcq4_b200_mul_mat_ws", "tcq4_b200_workspace_init", "tcq4_b200_mul_mat",
-    "tcq4_b200_reserve", "tcq4_b200_mul_mat_static", "tcq4_b200_mul_mat_peers", "tcq4_b200_mul_mat_multicast", "tcq4_b200_push_columns", "tcq4_b200_mul_mat_host", "tcq4_b200_mul_mat_host_async", "tcq4_b200_host_sync", "tcq4_b200_fwht_quantize_tc", "tcq4_b200_mul_mat_debug",
+    "tcq4_b200_reserve", "tcq4_b200_mul_mat_static", "tcq4_b200_mul_mat_peers", "tcq4_b200_mul_mat_multicast", "tcq4_b200_push_columns", "tcq4_b200_peer_barrier", "tcq4_b200_mul_mat_host", "tcq4_b200_mul_mat_host_async", "tcq4_b200_host_sync", "tcq4_b200_fwht_quantize_tc", "tcq4_b200_mul_mat_debug",
     "ggml_backend_cuda_tcq4_register_perm", "ggml_backend_cuda_tcq4_clear_perms",
     "ggml_backend_cuda_tcq4_set_reorder_enabled", "tcq4_b200_get_perm", "tcq4_b200_has_perm",
     "tcq4_b200_get_reorder_enabled", "tcq4_b200_shard_range", "tcq4_b200_ggml_supports_op",
     "tcq4_b200_ggml_mul_mat", "tcq4_b200_launch_count",
     "tcq4_b200_profile_begin", "tcq4_b200_profile_end",
     "tcq4_b200_quantize_size", "tcq4_b200_quantize_tiles", "tcq4_b200_perm_from_imatrix", "tcq4_b200_get_rows", "tcq4_b200_ggml_get_rows",
-    "tcq4_b200_mul_mat_id", "tcq4_b200_ggml_mul_mat_id", "tcq4_b200_mul_mat_fanout", "tcq4_b200_ggml_mul_mat_fanout", "tcq4_b200_ggml_graph_compute", "tcq4_b200_mul_mat_add", "tcq4_b200_quant_type_for",
+    "tcq4_b200_mul_mat_id", "tcq4_b200_ggml_mul_mat_id", "tcq4_b200_mul_mat_fanout", "tcq4_b200_mul_mat_fanout_ld", "tcq4_b200_ggml_mul_mat_fanout", "tcq4_b200_ggml_graph_compute", "tcq4_b200_mul_mat_add", "tcq4_b200_quant_type_for",
     "tcq4_b200_gguf_open", "tcq4_b200_gguf_close", "tcq4_b200_gguf_reorder_enabled", "tcq4_b200_gguf_n_tensors",
     "tcq4_b200_gguf_n_perms", "tcq4_b200_gguf_tensor_info", "tcq4_b200_gguf_perm", "tcq4_b200_gguf_register_perms",
     "tcq4_b200_gguf_read_tensor", "tcq4_b200_gguf_load_tensor", "tcq4_b200_gguf_write",
@@ -87,6 +87,7 @@ def _load() -> C.CDLL:
     lib.tcq4_b200_mul_mat_static.argtypes = [vp, vp, vp, i64, i64, i64, vp, vp]
     lib.tcq4_b200_mul_mat_multicast.argtypes = [vp, vp, vp, i64, i64, i64, i64, i64, vp, vp]
     lib.tcq4_b200_push_columns.argtypes = [vp, vp, i64, i64, i64, i64, vp]
+    lib.tcq4_b200_peer_barrier.argtypes = [vp, ci, ci, vp]
     lib.tcq4_b200_mul_mat_peers.argtypes = [vp, vp, vp, ci, i64, i64, i64, i64, i64, vp, vp]
     lib.tcq4_b200_mul_mat_host.argtypes = [vp, vp, vp, i64, i64, i64, vp, vp]
     lib.tcq4_b200_mul_mat_host_async.argtypes = [vp, vp, vp, i64, i64, i64, vp]
@@ -132,6 +133,7 @@ def _load() -> C.CDLL:
     lib.tcq4_b200_mul_mat_id.argtypes = [vp, i64, C.c_size_t, vp, i64, vp, i64, i64, i64, vp, i64, i64, vp, vp, vp]
     lib.tcq4_b200_ggml_mul_mat_id.argtypes = [C.POINTER(TensorView)] * 4 + [vp, vp]
     lib.tcq4_b200_mul_mat_fanout.argtypes = [ci, vp, vp, vp, vp, i64, i64, vp, vp]
+    lib.tcq4_b200_mul_mat_fanout_ld.argtypes = [ci, vp, vp, vp, vp, vp, i64, i64, vp, vp]
     lib.tcq4_b200_mul_mat_add.argtypes = [vp, vp, vp, i64, i64, i64, vp, vp, vp, vp]
     lib.tcq4_b200_quant_type_for.argtypes = [C.c_char_p, ci, i64, i64, ci]
     lib.tcq4_b200_ggml_mul_mat_fanout.argtypes = [ci, vp, C.POINTER(TensorView), vp, vp]

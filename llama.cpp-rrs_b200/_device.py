@@ -15,7 +15,7 @@ import torch
 from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
                ACT_BLOCK_BYTES, TensorView, _check, quantize_size, shard_range, tile_bytes, workspace_size)
 
-__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "ggml_mul_mat_fanout", "GgmlGraph", "mul_mat_add", "mul_mat_static", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
+__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "ggml_mul_mat_fanout", "GgmlGraph", "mul_mat_add", "mul_mat_static", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "PeerBarrier", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
            "ggml_supports_op", "ShardedWeight", "random_tiles", "quantize_tiles", "get_rows", "ggml_get_rows"]
 
@@ -140,6 +140,25 @@ def push_columns(dst_ptr: int, src_ptr: int, M: int, ldc: int, col0: int, ncols:
     _check(LIB.tcq4_b200_push_columns(int(dst_ptr), int(src_ptr), M, ldc, col0, ncols, _stream_ptr(stream)))
 
 
+class PeerBarrier:
+    """tcq4_b200_peer_barrier over a symmetric int32 flag buffer (torch symmetric memory supplies the peer mapping)."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        group = group or dist.group.WORLD
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.buf = symm_mem.empty((16,), dtype=torch.int32, device="cuda")
+        self.buf.zero_()
+        self.hdl = symm_mem.rendezvous(self.buf, group)
+        torch.cuda.synchronize()
+        self.hdl.barrier()                      # everybody's flags are zero before the first use
+        self.ptrs = (C.c_void_p * self.world)(*[int(p) for p in self.hdl.buffer_ptrs])
+
+    def __call__(self, stream=None):
+        _check(LIB.tcq4_b200_peer_barrier(self.ptrs, self.world, self.rank, _stream_ptr(stream)))
+
+
 def mul_mat_host(w_tiles: torch.Tensor, x_host: torch.Tensor, y_host: torch.Tensor, N: int,
                  perm: torch.Tensor | None = None, stream=None) -> torch.Tensor:
     """End-to-end call with HOST (pinned) x and y; weights resident on the device.  Synchronous."""
@@ -246,7 +265,8 @@ def _views(w_tiles, x, y, N, name):
     row = (K // TILE_K) * 148
     src0 = _view(w_tiles, GGML_TYPE_TCQ4_K32, [K, N, 1, 1], [148, row, row * N, row * N], name)
     src1 = _view(x, GGML_TYPE_F32, [K, M, 1, 1], [4, 4 * K, 4 * K * M, 4 * K * M], b"src1")
-    dst = _view(y, GGML_TYPE_F32, [N, M, 1, 1], [4, 4 * N, 4 * N * M, 4 * N * M], b"dst")
+    ldc = y.stride(0) if (y is not None and y.dim() == 2 and M > 1) else N      # a column window of a wider matrix is a strided view
+    dst = _view(y, GGML_TYPE_F32, [N, M, 1, 1], [4, 4 * ldc, 4 * ldc * M, 4 * ldc * M], b"dst")
     return src0, src1, dst
 
 

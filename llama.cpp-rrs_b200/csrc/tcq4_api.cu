@@ -534,9 +534,24 @@ int tcq4_b200_mul_mat_add(const void *w_tiles, const float *x, float *y, int64_t
 // All matrices must share the channel permutation (they do when it derives from the imatrix of their common input).
 int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *Ns, float *const *ys, const float *x, int64_t M,
                              int64_t K, const int32_t *d_perm, cudaStream_t stream) {
+    return tcq4_b200_mul_mat_fanout_ld(n, w_tiles, Ns, ys, nullptr, x, M, K, d_perm, stream);
+}
+
+// Same with a leading dimension per output (ldcs[i] >= Ns[i], a multiple of 4; null: contiguous): ys[i] may be a column window
+// of a wider row-major matrix -- a ggml view, or this GPU's column block of an N-sharded C.
+int tcq4_b200_mul_mat_fanout_ld(int n, const void *const *w_tiles, const int64_t *Ns, float *const *ys, const int64_t *ldcs,
+                                const float *x, int64_t M, int64_t K, const int32_t *d_perm, cudaStream_t stream) {
     if (n < 1 || n > 8 || !w_tiles || !Ns || !ys) {
         set_err("mul_mat_fanout: 1..8 weight matrices");
         return TCQ4_ERR_ARG;
+    }
+    int64_t ld[8];
+    for (int i = 0; i < n; i++) {
+        ld[i] = ldcs ? ldcs[i] : Ns[i];
+        if (ld[i] < Ns[i] || (ld[i] & 3)) {
+            set_err("mul_mat_fanout: ldc of matrix %d must be >= N and a multiple of 4", i);
+            return TCQ4_ERR_ARG;
+        }
     }
     int64_t Nmax = 0;
     for (int i = 0; i < n; i++) {
@@ -568,6 +583,7 @@ int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N
             }
             ex.seg_w[i] = reinterpret_cast<const uint8_t *>(w_tiles[i]);
             ex.seg_y[i] = ys[i];
+            ex.seg_ldc[i] = ld[i];
             ex.seg_nt0[i + 1] = ex.seg_nt0[i] + (int)(Ns[i] / 8);
         }
         if (!x || ((uintptr_t)x & 15) || (d_perm && ((uintptr_t)d_perm & 15))) {
@@ -627,7 +643,7 @@ int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N
             tcq4::Gemm3Seg sg[4];
             int64_t Nl[4];
             for (int i = 0; i < ns; i++) {
-                sg[i] = tcq4::Gemm3Seg{w_tiles[i0 + i], ys[i0 + i], Ns[i0 + i], Ns[i0 + i]};
+                sg[i] = tcq4::Gemm3Seg{w_tiles[i0 + i], ys[i0 + i], Ns[i0 + i], ld[i0 + i]};
                 Nl[i] = Ns[i0 + i];
             }
             tcq4::Gemm3Plan g3;
@@ -648,7 +664,9 @@ int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N
     bool have_codes = false;
     for (int i = 0; i < n; i++) {
         bool done = false;
-        status = run_mul_mat(w_tiles[i], x, single_out(ys[i], Ns[i]), M, Ns[i], K, d_perm, d->arena, d->arena_bytes,
+        tcq4::YOut yo = single_out(ys[i], Ns[i]);
+        yo.ldc = ld[i];
+        status = run_mul_mat(w_tiles[i], x, yo, M, Ns[i], K, d_perm, d->arena, d->arena_bytes,
                              TCQ4_KERNEL_AUTO, nullptr, stream, Nmax, have_codes, &done);
         if (status != TCQ4_OK) return status;
         have_codes = have_codes || done;
@@ -827,6 +845,18 @@ int tcq4_b200_mul_mat_multicast(const void *w_tiles, const float *x, float *y_mu
     o.ldc = ldc;
     o.mc = y_multicast + col0;
     return run_mul_mat(w_tiles, x, o, M, N, K, d_perm, d->arena, d->arena_bytes, TCQ4_KERNEL_AUTO, nullptr, stream);
+}
+
+// Cross-GPU barrier of the exchange: every rank calls it with the same peer-mapped flag arrays (int32[TCQ4_B200_MAX_PEERS + 1]
+// per rank, zeroed once) after the stores / pushes of the outputs its consumers need; returns (on the stream) when every rank
+// has.  One 32-thread kernel, capturable; see tcq4_peer.cu.
+int tcq4_b200_peer_barrier(int *const *flags_peers, int n_peers, int rank, cudaStream_t stream) {
+    int status;
+    if (!current_device(&status)) return status;
+    cudaError_t e = tcq4::launch_peer_barrier(flags_peers, n_peers, rank, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "peer barrier launch");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return TCQ4_OK;
 }
 
 // Copy-engine half of the same exchange: push `ncols` columns starting at col0 of a local row-major [M][ldc] fp32

@@ -86,7 +86,7 @@ struct Gemm3Smem {
     static constexpr int off_out = off_rm + G3_SN_RING * G3_BM * 4;
     static constexpr int off_zflag = off_out + G3_EPI_WARPS * G3_OUT_BOXES * 1024;
     static constexpr int off_bar = off_zflag + G3_SN_RING * 8 * 4;
-    static constexpr int n_bar = 2 * G3_RAW_STAGES + 2 * G3_F_STAGES + 2 + 2 + 4 + 4 + G3_SN_RING;
+    static constexpr int n_bar = 2 * G3_RAW_STAGES + 2 * G3_F_STAGES + 2 + 2 + 8 + 8 + G3_SN_RING;
     static constexpr int off_tmem = off_bar + n_bar * 8;
     static constexpr int total = off_tmem + 16;
 };
@@ -356,7 +356,7 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + Gemm3Smem::off_bar);
     uint64_t *rawfull = bars, *rawempty = rawfull + G3_RAW_STAGES, *bfull = rawempty + G3_RAW_STAGES,
              *bfree = bfull + G3_F_STAGES, *accfull = bfree + G3_F_STAGES, *accempty = accfull + 2, *afull = accempty + 2,
-             *afree = afull + 4, *snfull = afree + 4;
+             *afree = afull + 8, *snfull = afree + 8;      // afull / afree: [issuing warp = k-tile & 1][quarter]
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + Gemm3Smem::off_tmem);
 
     if (threadIdx.x == 0) {
@@ -372,7 +372,7 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
             mbar_init(&accfull[i], 1);                           // leader's commit (multicast)
             mbar_init(&accempty[i], 2 * G3_EPI_WARPS);           // epilogue warps of both CTAs (used in the leader)
         }
-        for (int i = 0; i < 4; i++) {
+        for (int i = 0; i < 8; i++) {
             mbar_init(&afull[i], G3_AW_WARPS);                   // the four activation warps that own this quarter, both CTAs (leader)
             mbar_init(&afree[i], 1);                             // leader's commit (multicast)
         }
@@ -443,37 +443,45 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
                 if (pass == 0) pdl_wait();       // the activation codes belong to the kernel in front until here
             }
         }
-      } else if (warp == 1) {
-        // ===================== MMA issuer (leader CTA only) =====================
+      } else if (warp <= 2) {
+        // ===================== MMA issuers (leader CTA only): warp 1 takes the even k-tiles, warp 2 the odd ones =====================
+        // One issuing thread spends ~600 cycles per k-tile outside the MMA instructions themselves (three commits, loop,
+        // the accumulator / weight / first-quarter waits: ~50 dependent instructions at ~10 cycles each in a loaded SM) --
+        // longer than the 391 cycles of tensor-pipe work it has queued, so the pipe drained at every k-tile boundary
+        // (timeline of the what-if run with all CUDA-core work off: tests/gpu_g3_exp.py).  Two issuers alternate: each owns
+        // one accumulator stage, one slot of the weight ring and its own set of activation barriers, and has two k-tiles
+        // of pipe time per k-tile of its own.  MMAs of different k-tiles write different accumulators, so their
+        // interleaving in the pipe's queue is free; tcgen05.commit tracks the issuing thread's own MMAs.
         if (rank == 0) {
             constexpr uint32_t idesc = (1u << 4) | ((uint32_t)(NCOL >> 3) << 17) | ((uint32_t)((2 * G3_BM) >> 4) << 24);
             constexpr uint32_t b_hi = (uint32_t)(128 >> 4) | (1u << 14);              // SBO = 128 B, descriptor version 1
-            const uint32_t b_lo0 = (smem_u32(sF) >> 4) | ((uint32_t)(LBO_B >> 4) << 16);
+            const int as = warp - 1;                                                  // this issuer's accumulator stage / ring slot
+            const uint32_t b_lo0 = ((smem_u32(sF) + as * G3_F_BYTES) >> 4) | ((uint32_t)(LBO_B >> 4) << 16);
+            const uint32_t d = tmem + as * G3_TM_D_STRIDE;
+            uint64_t *my_afull = afull + as * 4, *my_afree = afree + as * 4;
             int total_k = 0;
             for (int t = cluster_id; t < num_tiles; t += num_clusters) {
                 const G3Tile tl = g3_decode(P, t, MB2, KT, rank);
                 total_k += tl.kt1 - tl.kt0;
             }
-            for (int gk = 0; gk < total_k; gk++) {
-                const int as = gk & 1, u2 = gk >> 1;
-                G3_STAMP(0, gk, 0);
+            for (int gk = as, u2 = 0; gk < total_k; gk += 2, u2++) {
+                if (as == 0) G3_STAMP(0, gk, 0);
                 if (u2 > 0) g3_wait(&accempty[as], (uint32_t)((u2 - 1) & 1));
-                G3_STAMP(0, gk, 1);
+                if (as == 0) G3_STAMP(0, gk, 1);
                 g3_wait(&bfull[as], (uint32_t)(u2 & 1));       // the whole k-tile of fp16 weights (ring of two k-tiles)
-                G3_STAMP(0, gk, 2);
-                const uint32_t d = tmem + as * G3_TM_D_STRIDE;
+                if (as == 0) G3_STAMP(0, gk, 2);
 #pragma unroll 1      // rolled on purpose: the unrolled form kept four sets of descriptors alive and spilled them into the issue path
                 for (int q = 0; q < 4; q++) {
-                    g3_wait(&afull[q], (uint32_t)(gk & 1));      // both CTAs' activations of this quarter are in TMEM
-                    G3_STAMP(0, gk, 3 + q);
+                    g3_wait(&my_afull[q], (uint32_t)(u2 & 1));      // both CTAs' activations of this quarter are in TMEM
+                    if (as == 0) G3_STAMP(0, gk, 3 + q);
                     tc_fence_after();
                     if (elect_one()) {
-                        const uint32_t b_lo = b_lo0 + (uint32_t)(as * 4 + q) * (G3_F_Q >> 4);
+                        const uint32_t b_lo = b_lo0 + (uint32_t)q * (G3_F_Q >> 4);
                         const uint32_t a_t = tmem + G3_TM_A0 + q * G3_TM_A_COLS;
 #pragma unroll
                         for (int ks = 0; ks < 4; ks++)      // K = 16 per instruction: 8 TMEM columns of A, two 8-element K-chunks of B
                             umma_f16_2cta_ts(d, a_t + ks * 8, b_lo + (uint32_t)ks * ((2 * LBO_B) >> 4), b_hi, idesc, (q | ks) ? 1u : 0u);
-                        g3_commit_2cta(&afree[q]);
+                        g3_commit_2cta(&my_afree[q]);
                         if (q == 3) {
                             g3_commit_2cta(&bfree[as]);
                             g3_commit_2cta(&accfull[as]);
@@ -516,7 +524,7 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
                     const uint8_t *src = stg + (2 * q) * 2048 + row * 16;      // the quarter's two 32-groups of this row
                     const uint4 w0 = *reinterpret_cast<const uint4 *>(src), w1 = *reinterpret_cast<const uint4 *>(src + 2048);
                     if (gk > 0) {
-                        g3_wait(&afree[q], (uint32_t)((gk - 1) & 1));
+                        g3_wait(&afree[((gk - 1) & 1) * 4 + q], (uint32_t)(((gk - 1) >> 1) & 1));      // MMA(q) of the previous k-tile: the other issuer's
                         tc_fence_after();
                     }
                     if (aw == 0) G3_STAMP(1, gk, 2 + 3 * i);
@@ -533,7 +541,7 @@ tcq4_gemm3_kernel(const __grid_constant__ G3Params P, ActStage st, int M, int K,
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) {
-                        g3_arrive_cluster(afull_leader + (uint32_t)q * 8);
+                        g3_arrive_cluster(afull_leader + (uint32_t)((gk & 1) * 4 + q) * 8);
                         if (i == 1) mbar_arrive(&rawempty[s]);       // every lane has read its raw bytes
                     }
                     if (aw == 0) G3_STAMP(1, gk, 3 + 3 * i);

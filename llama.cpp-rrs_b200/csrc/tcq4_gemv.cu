@@ -259,8 +259,7 @@ tcq4_gemv_kernel(const uint8_t *__restrict__ w, const float *__restrict__ x, con
         if constexpr (SEG) {
             int si = 0;
             while (si + 1 < ex.nseg && row >= ex.seg_nt0[si + 1]) si++;
-            const int ni = (ex.seg_nt0[si + 1] - ex.seg_nt0[si]) * 8;
-            ex.seg_y[si][(size_t)m * ni + (row - ex.seg_nt0[si]) * 8 + ch] = v;
+            ex.seg_y[si][(size_t)m * (size_t)ex.seg_ldc[si] + (row - ex.seg_nt0[si]) * 8 + ch] = v;
         } else {
             if constexpr (MODE == 3) {                                  // tcq4_b200_mul_mat_add
                 if (ex.bias) v += __ldg(ex.bias + row * 8 + ch);

@@ -54,7 +54,8 @@ struct GvExpert {
     int nseg;
     int seg_nt0[5];
     const uint8_t *seg_w[4];
-    float *seg_y[4];       // [M][N_i] each
+    float *seg_y[4];       // [M][seg_ldc[i]] each (N_i columns used)
+    long long seg_ldc[4];
     // epilogue fusion (tcq4_b200_mul_mat_add, MODE 3 of the kernel): y = W x + bias[n] + res[m][n]; res may alias y
     const float *res;      // [M][N] contiguous or null
     const float *bias;     // [N] or null
@@ -66,6 +67,9 @@ cudaError_t launch_gemv_grouped(const void *w_experts, const float *x, const int
 cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
                         int64_t K, const GemvPlan &plan, float *ws_blob, int *ws_ticket, int32_t *dbg_isum,
                         cudaStream_t stream, const GvExpert *expert = nullptr);
+
+// ---- cross-GPU barrier of the N-shard exchange (tcq4_peer.cu): flags[r] = rank r's peer-mapped int32[MAX_PEERS + 1], zeroed once
+cudaError_t launch_peer_barrier(int *const *flags, int n, int rank, cudaStream_t stream);
 
 // ---- MUL_MAT_ID row gather / scatter (tcq4_moe.cu) ------------------------------------------------
 cudaError_t launch_copy_rows(const float *src, const int32_t *src_idx, float *dst, const int32_t *dst_idx, int64_t rows,

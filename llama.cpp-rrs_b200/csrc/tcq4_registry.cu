@@ -136,10 +136,16 @@ int tcq4_b200_ggml_mul_mat(const tcq4_tensor_view *src0, const tcq4_tensor_view 
     if (dst->ne[0] != N || dst->ne[1] != M) return TCQ4_ERR_SHAPE;
     // the reference silently ignores ne[2], ne[3] and strides (rrs.cu:247-254); assert instead
     if (src0->ne[2] != 1 || src0->ne[3] != 1) return TCQ4_ERR_SHAPE;
-    if (!is_contiguous_2d(src1, (size_t)K * 4) || !is_contiguous_2d(dst, (size_t)N * 4)) return TCQ4_ERR_SHAPE;
+    // dst may be a row-strided view (ggml_view_2d of a wider matrix: nb[1] >= N*4, a multiple of 16 bytes)
+    if (!is_contiguous_2d(src1, (size_t)K * 4) || dst->nb[0] != 4 || dst->nb[1] < (size_t)N * 4 || (dst->nb[1] & 15)) return TCQ4_ERR_SHAPE;
     if (src0->nb[1] != (size_t)(K / 256) * 148) return TCQ4_ERR_SHAPE;          // ggml_row_size, ggml.c:750-757
     const int32_t *d_perm = src0->name ? tcq4_b200_get_perm(src0->name) : nullptr;   // rrs.cu:266-270
     if (d_perm && perm_len(src0->name) != K) return TCQ4_ERR_SHAPE;          // a registered permutation of another length would gather out of bounds
+    if (dst->nb[1] != (size_t)N * 4) {
+        if (workspace) return TCQ4_ERR_SHAPE;                                 // the strided store goes through the arena entry
+        float *yp[1] = {(float *)dst->data};
+        return tcq4_b200_mul_mat_peers(src0->data, (const float *)src1->data, yp, 1, (int64_t)(dst->nb[1] / 4), 0, M, N, K, d_perm, stream);
+    }
     if (workspace)
         return tcq4_b200_mul_mat_ws(src0->data, (const float *)src1->data, (float *)dst->data, M, N, K, d_perm,
                                     workspace, workspace_bytes, TCQ4_KERNEL_AUTO, stream);
@@ -154,7 +160,7 @@ int tcq4_b200_ggml_mul_mat_fanout(int n, const tcq4_tensor_view *const *src0, co
     if (n < 1 || n > 8 || !src0 || !src1 || !dst) return TCQ4_ERR_ARG;
     const int64_t K = src1->ne[0], M = src1->ne[1];
     const void *w[8];
-    int64_t Ns[8];
+    int64_t Ns[8], ld[8];
     float *y[8];
     for (int i = 0; i < n; i++) {
         if (!src0[i] || !dst[i]) return TCQ4_ERR_ARG;
@@ -162,10 +168,11 @@ int tcq4_b200_ggml_mul_mat_fanout(int n, const tcq4_tensor_view *const *src0, co
         const int64_t N = src0[i]->ne[1];
         if (src0[i]->ne[0] != K || dst[i]->ne[0] != N || dst[i]->ne[1] != M) return TCQ4_ERR_SHAPE;
         if (src0[i]->ne[2] != 1 || src0[i]->ne[3] != 1) return TCQ4_ERR_SHAPE;
-        if (!is_contiguous_2d(src1, (size_t)K * 4) || !is_contiguous_2d(dst[i], (size_t)N * 4)) return TCQ4_ERR_SHAPE;
+        if (!is_contiguous_2d(src1, (size_t)K * 4) || dst[i]->nb[0] != 4 || dst[i]->nb[1] < (size_t)N * 4 || (dst[i]->nb[1] & 15)) return TCQ4_ERR_SHAPE;
         if (src0[i]->nb[1] != (size_t)(K / 256) * 148) return TCQ4_ERR_SHAPE;
         w[i] = src0[i]->data;
         Ns[i] = N;
+        ld[i] = (int64_t)(dst[i]->nb[1] / 4);
         y[i] = (float *)dst[i]->data;
     }
     const int32_t *d_perm = src0[0]->name ? tcq4_b200_get_perm(src0[0]->name) : nullptr;
@@ -185,7 +192,7 @@ int tcq4_b200_ggml_mul_mat_fanout(int n, const tcq4_tensor_view *const *src0, co
             else same = (e == first) || (e && first && e->h == first->h);
         }
     }
-    if (same) return tcq4_b200_mul_mat_fanout(n, w, Ns, y, (const float *)src1->data, M, K, d_perm, stream);
+    if (same) return tcq4_b200_mul_mat_fanout_ld(n, w, Ns, y, ld, (const float *)src1->data, M, K, d_perm, stream);
     for (int i = 0; i < n; i++) {
         const int st = tcq4_b200_ggml_mul_mat(src0[i], src1, dst[i], nullptr, 0, stream);
         if (st != TCQ4_OK) return st;
