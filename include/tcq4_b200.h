@@ -55,8 +55,10 @@ enum {
     TCQ4_KERNEL_GEMV  = 1,     /* fused FWHT+quant+streaming dot, small M, HBM-bound          */
     TCQ4_KERNEL_GEMM  = 2,     /* activation kernel + tcgen05.mma kind::i8 GEMM, one CTA per 128 tokens   */
     TCQ4_KERNEL_GEMM2 = 3,     /* same on CTA pairs (cta_group::2, 256 tokens per pair); several destinations       */
-    TCQ4_KERNEL_GEMM3 = 4      /* CTA pairs, tcgen05.mma kind::f16 on exact fp16 integers, nibble operands widened
+    TCQ4_KERNEL_GEMM3 = 4,     /* CTA pairs, tcgen05.mma kind::f16 on exact fp16 integers, nibble operands widened
                                   in the SM, fan-out segments, K split: the prefill kernel (round 2)                */
+    TCQ4_KERNEL_GEMM4 = 5      /* batched decode, 17 <= M <= 64: weights widened into TMEM (the MMA's A operand, 128
+                                  channels per CTA), tokens as the MMA's N; K split on narrow matrices              */
 };
 
 TCQ4_B200_API const char *tcq4_b200_version(void);

@@ -42,6 +42,11 @@ TCQ4_B200_API int tcq4_b200_debug_gemm2_timeline(long long *out, size_t bytes);
  * [k-tile 64][event 8] of the leader CTA of one cluster. */
 TCQ4_B200_API int tcq4_b200_debug_gemm3_timeline(long long *out, size_t bytes);
 
+/* Same for the batched-decode GEMM (TCQ4_G4_PROF): [role 4: MMA issuer, widening warp 0, widening warp 15, epilogue warp 0]
+ * [k-tile 64][event 8] of the middle CTA.  TCQ4_G4_EXP switches parts of the CUDA-core work off (bit 0 weight widening,
+ * bit 1 token widening, bit 2 epilogue arithmetic; results are then wrong on purpose). */
+TCQ4_B200_API int tcq4_b200_debug_gemm4_timeline(long long *out, size_t bytes);
+
 /* L2 -> SM fabric rate: every CTA (one per SM, clusters of `cluster` CTAs) streams `unit_bytes` units with cp.async.bulk
  * out of an L2-resident region of `region_bytes` into a 4-stage shared-memory ring, `iters` units per CTA.
  *   pattern 0: clusters read different units at any time;  pattern 1: all clusters read the same unit sequence

@@ -33,7 +33,7 @@ ACT_BLOCK_BYTES = 160
 GGML_TYPE_F32 = 0
 GGML_TYPE_TCQ4_K32 = 42
 
-KERNEL_AUTO, KERNEL_GEMV, KERNEL_GEMM, KERNEL_GEMM2, KERNEL_GEMM3 = 0, 1, 2, 3, 4
+KERNEL_AUTO, KERNEL_GEMV, KERNEL_GEMM, KERNEL_GEMM2, KERNEL_GEMM3, KERNEL_GEMM4 = 0, 1, 2, 3, 4, 5
 
 STATUS = {0: "OK", 1: "ERR_SHAPE", 2: "ERR_ARG", 3: "ERR_WORKSPACE", 4: "ERR_CUDA", 5: "ERR_NO_DEVICE"}
 
@@ -146,7 +146,7 @@ LIB = _load()
 
 # every symbol include/tcq4_b200_diag.h declares
 DIAG_EXPORTS = ["tcq4_b200_measure_umma", "tcq4_b200_measure_umma2", "tcq4_b200_measure_pipe", "tcq4_b200_measure_tmem_ld",
-                "tcq4_b200_measure_fabric", "tcq4_b200_measure_f16_exact", "tcq4_b200_debug_gemv_phases", "tcq4_b200_debug_gemm2_timeline", "tcq4_b200_debug_gemm3_timeline"]
+                "tcq4_b200_measure_fabric", "tcq4_b200_measure_f16_exact", "tcq4_b200_debug_gemv_phases", "tcq4_b200_debug_gemm2_timeline", "tcq4_b200_debug_gemm3_timeline", "tcq4_b200_debug_gemm4_timeline"]
 _DIAG = None
 
 
@@ -165,6 +165,7 @@ def diag_lib() -> C.CDLL:
         lib.tcq4_b200_debug_gemv_phases.argtypes = [vp, sz]
         lib.tcq4_b200_debug_gemm2_timeline.argtypes = [vp, sz]
         lib.tcq4_b200_debug_gemm3_timeline.argtypes = [vp, sz]
+        lib.tcq4_b200_debug_gemm4_timeline.argtypes = [vp, sz]
         _DIAG = lib
     return _DIAG
 

@@ -96,6 +96,7 @@ DevInfo *current_device(int *status) {
                 cudaError_t e2 = tcq4::gemm_init_attributes(d.smem_optin);
                 if (e2 == cudaSuccess) e2 = tcq4::gemm2_init_attributes(d.smem_optin);
                 if (e2 == cudaSuccess) e2 = tcq4::gemm3_init_attributes(d.smem_optin);
+                if (e2 == cudaSuccess) e2 = tcq4::gemm4_init_attributes(d.smem_optin);
                 d.ok = (e1 == cudaSuccess && e2 == cudaSuccess);
                 if (!d.ok) set_err("kernel attribute setup failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
             } else {
@@ -155,7 +156,10 @@ int select_kernel(const DevInfo *d, int64_t M, int64_t N, int64_t K, tcq4::GemvP
     const size_t optin = d ? d->smem_optin : (size_t)232448;
     tcq4::GemvPlan tmp;
     if (tcq4::gemv_plan(M, N, K, sms, optin, gv ? gv : &tmp)) return TCQ4_KERNEL_GEMV;
-    // 17 <= M <= 128: the single-CTA GEMM (128-row tiles, every SM busy) only wins on wide, shallow matrices;
+    // 17 <= M <= 64 (batched decode): weights through TMEM, tokens as the MMA's N (tcq4_gemm4.cu)
+    static const bool no_g4 = getenv("TCQ4_NO_GEMM4") != nullptr;
+    if (M <= 64 && !no_g4) return TCQ4_KERNEL_GEMM4;
+    // 65 <= M <= 128: the single-CTA GEMM (128-row tiles, every SM busy) only wins on wide, shallow matrices;
     // elsewhere the persistent pair GEMM is up to 2x faster even with its second row block empty (measured:
     // profiles/, "M <= 128")
     if (M <= 128 && N >= 8192 && K <= 4096) return TCQ4_KERNEL_GEMM;
@@ -218,6 +222,7 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
     if (k == TCQ4_KERNEL_GEMM && !plain) k = TCQ4_KERNEL_GEMM2;      // only the pair GEMMs and the GEMV write strided / to peers
     if (k == TCQ4_KERNEL_GEMM && (res || bias)) k = TCQ4_KERNEL_GEMM2;            // ... and fuse bias / residual
     if (k == TCQ4_KERNEL_GEMM3 && !one_dest) k = TCQ4_KERNEL_GEMM2;               // several destinations / multicast: kind::i8 pair GEMM
+    if (k == TCQ4_KERNEL_GEMM4 && (!one_dest || res || bias || M > 64)) k = TCQ4_KERNEL_GEMM2;
     if (k == TCQ4_KERNEL_GEMV) {
         if (!tcq4::gemv_plan(M, N, K, d->num_sms, d->smem_optin, &gv)) {
             set_err("GEMV kernel does not take M=%lld K=%lld (M<=%d and M*K codes must fit shared memory)",
@@ -247,6 +252,40 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
             g_prof.kind[g_prof.n++] = TCQ4_KERNEL_GEMV;
         }
         g_launches.fetch_add(1, std::memory_order_relaxed);
+        return TCQ4_OK;
+    }
+    if (k == TCQ4_KERNEL_GEMM4) {
+        // batched decode: nibble staging (K1 MODE_NIB), weights widened into TMEM, optional K split onto a cleared output
+        tcq4::Gemm4Plan g4;
+        if (!tcq4::gemm4_plan(M, N, K, d->num_sms, d->smem_optin, yo.ldc == N, &g4)) {
+            set_err("batched-decode GEMM cannot be planned for this shape/device");
+            return TCQ4_ERR_SHAPE;
+        }
+        tcq4::ActStage st;
+        st.codes = reinterpret_cast<int8_t *>(wsb + L.codes_off);
+        st.a7 = reinterpret_cast<float *>(wsb + L.a7_off);
+        st.sumq = reinterpret_cast<int16_t *>(wsb + L.sumq_off);
+        st.a7t = reinterpret_cast<float *>(wsb + L.a7t_off);
+        const bool prof = g_prof.on && g_prof.n < g_prof.cap;
+        if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
+        cudaError_t e = cudaSuccess;
+        const bool split = !g4.whole_blocks;
+        if (!reuse_act) {
+            e = tcq4::launch_act_quant_nib(x, perm, M, K, st, d->num_sms, stream, split ? y : nullptr, M * N);
+            if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
+        } else if (split) {
+            e = tcq4::launch_zero_floats(y, M * N, d->num_sms, stream);
+            if (e != cudaSuccess) return cuda_fail(e, "output clear launch");
+        }
+        if (act_done) *act_done = true;
+        if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
+        e = tcq4::launch_gemm4(w, st, y, yo.ldc, M, N, K, g4, dbg_isum, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "gemm4 launch");
+        if (prof) {
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
+            g_prof.kind[g_prof.n++] = k;
+        }
+        g_launches.fetch_add((!reuse_act || split) ? 2 : 1, std::memory_order_relaxed);
         return TCQ4_OK;
     }
     if (k == TCQ4_KERNEL_GEMM3) {
@@ -1101,6 +1140,12 @@ int tcq4_b200_debug_gemm2_timeline(long long *out, size_t bytes) {
 int tcq4_b200_debug_gemm3_timeline(long long *out, size_t bytes) {
     cudaError_t e = cudaDeviceSynchronize();
     if (e == cudaSuccess) e = tcq4::gemm3_read_prof(out, bytes);
+    return e == cudaSuccess ? TCQ4_OK : TCQ4_ERR_CUDA;
+}
+
+int tcq4_b200_debug_gemm4_timeline(long long *out, size_t bytes) {
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = tcq4::gemm4_read_prof(out, bytes);
     return e == cudaSuccess ? TCQ4_OK : TCQ4_ERR_CUDA;
 }
 

@@ -44,12 +44,14 @@ def test_supports_and_select(t4):
     assert t4.select_kernel(1, 9728, 2560) == t4.KERNEL_GEMV
     assert t4.select_kernel(4, 2560, 9728) == t4.KERNEL_GEMV
     assert t4.select_kernel(16, 9728, 2560) == t4.KERNEL_GEMV
-    assert t4.select_kernel(17, 9728, 2560) == t4.KERNEL_GEMM
+    assert t4.select_kernel(17, 9728, 2560) == t4.KERNEL_GEMM4     # batched decode: weights through TMEM
+    assert t4.select_kernel(65, 9728, 2560) == t4.KERNEL_GEMM
     assert t4.select_kernel(128, 9728, 2560) == t4.KERNEL_GEMM
     assert t4.select_kernel(512, 9728, 2560) == t4.KERNEL_GEMM2
-    assert t4.select_kernel(64, 2560, 9728) == t4.KERNEL_GEMM2      # deep or narrow matrices: the pair GEMM
-    assert t4.select_kernel(64, 1024, 2560) == t4.KERNEL_GEMM2
-    assert t4.select_kernel(4, 1024, 65536) == t4.KERNEL_GEMM2     # codes do not fit shared memory: a tcgen05 GEMM
+    assert t4.select_kernel(64, 2560, 9728) == t4.KERNEL_GEMM4
+    assert t4.select_kernel(100, 2560, 9728) == t4.KERNEL_GEMM2     # deep or narrow matrices: the pair GEMM
+    assert t4.select_kernel(100, 1024, 2560) == t4.KERNEL_GEMM2
+    assert t4.select_kernel(4, 1024, 65536) == t4.KERNEL_GEMM4     # codes do not fit shared memory: a tcgen05 GEMM
 
 
 def test_ggml_supports_op(t4):
