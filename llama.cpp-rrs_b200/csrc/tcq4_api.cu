@@ -141,6 +141,10 @@ WsLayout ws_layout(int64_t M, int64_t N, int64_t K) {
     const int64_t maxslots = KT;
     const int64_t slot_rows = (M <= 8) ? 8 : 16;
     L.partial_bytes = (size_t)tcq4::round_up(NT * maxslots * slot_rows * 8 * 4, 256);   // kept for every M: size is monotone in M
+    if (M > 8 && ((N + 127) / 128) * 3 <= tcq4::GEMM4_MAX_CTAS) {      // batched-decode GEMM, K parts: one [32|64 tokens][128 channels] slot per CTA
+        const int64_t g4 = (int64_t)tcq4::GEMM4_MAX_CTAS * (M <= 32 ? 32 : 64) * 128 * 4;
+        L.partial_bytes = std::max(L.partial_bytes, (size_t)tcq4::round_up(g4, 256));
+    }
     L.codes_off = L.partial_off + L.partial_bytes;
     const int64_t MB = ((M + 255) / 256) * 2;       // whole CTA pairs: the pair kernel bulk-copies both units
     const size_t codes = (size_t)tcq4::round_up(MB * KT * (int64_t)tcq4::ACT_UNIT_BYTES, 256);
@@ -155,9 +159,17 @@ int select_kernel(const DevInfo *d, int64_t M, int64_t N, int64_t K, tcq4::GemvP
     const int sms = d ? d->num_sms : 148;
     const size_t optin = d ? d->smem_optin : (size_t)232448;
     tcq4::GemvPlan tmp;
-    if (tcq4::gemv_plan(M, N, K, sms, optin, gv ? gv : &tmp)) return TCQ4_KERNEL_GEMV;
-    // 17 <= M <= 64 (batched decode): weights through TMEM, tokens as the MMA's N (tcq4_gemm4.cu)
     static const bool no_g4 = getenv("TCQ4_NO_GEMM4") != nullptr;
+    if (tcq4::gemv_plan(M, N, K, sms, optin, gv ? gv : &tmp)) {
+        // 9 <= M <= 16: the batched-decode GEMM is 15-20 % ahead of the GEMV when its CTAs get at most 16 k-tiles each
+        // (measured, tests/gpu_g4_vs_gemv.py); deeper ranges and M <= 8 stay with the GEMV
+        tcq4::Gemm4Plan g4;
+        if (M >= 9 && !no_g4 && tcq4::gemm4_plan(M, N, K, sms, optin, true, &g4) &&
+            ((N + 127) / 128) * (K / 256) <= 16 * (int64_t)g4.grid)
+            return TCQ4_KERNEL_GEMM4;
+        return TCQ4_KERNEL_GEMV;
+    }
+    // 17 <= M <= 64 (batched decode): weights through TMEM, tokens as the MMA's N (tcq4_gemm4.cu)
     if (M <= 64 && !no_g4) return TCQ4_KERNEL_GEMM4;
     // 65 <= M <= 128: the single-CTA GEMM (128-row tiles, every SM busy) only wins on wide, shallow matrices;
     // elsewhere the persistent pair GEMM is up to 2x faster even with its second row block empty (measured:
@@ -261,6 +273,10 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
             set_err("batched-decode GEMM cannot be planned for this shape/device");
             return TCQ4_ERR_SHAPE;
         }
+        if (g4.partial_bytes > L.partial_bytes || g4.counter_bytes > L.ticket_bytes || g4.grid > tcq4::GEMM4_MAX_CTAS) {
+            set_err("internal: batched-decode GEMM workspace bound too small");
+            return TCQ4_ERR_WORKSPACE;
+        }
         tcq4::ActStage st;
         st.codes = reinterpret_cast<int8_t *>(wsb + L.codes_off);
         st.a7 = reinterpret_cast<float *>(wsb + L.a7_off);
@@ -269,23 +285,27 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
         const bool prof = g_prof.on && g_prof.n < g_prof.cap;
         if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
         cudaError_t e = cudaSuccess;
-        const bool split = !g4.whole_blocks;
+        // what must start at zero: the output (two-part blocks meet through red.add) or the arrival counters (K parts; their
+        // last arriver clears them again, so fan-out calls that reuse the activations find them zero)
+        float *zero_p = g4.mode == 1 ? y : g4.mode == 2 ? reinterpret_cast<float *>(wsb + L.ticket_off) : nullptr;
+        const int64_t zero_n = g4.mode == 1 ? M * N : (int64_t)tcq4::round_up((int64_t)g4.counter_bytes, 16) / 4;
         if (!reuse_act) {
-            e = tcq4::launch_act_quant_nib(x, perm, M, K, st, d->num_sms, stream, split ? y : nullptr, M * N);
+            e = tcq4::launch_act_quant_nib(x, perm, M, K, st, d->num_sms, stream, zero_p, zero_n);
             if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
-        } else if (split) {
+        } else if (g4.mode == 1) {
             e = tcq4::launch_zero_floats(y, M * N, d->num_sms, stream);
             if (e != cudaSuccess) return cuda_fail(e, "output clear launch");
         }
         if (act_done) *act_done = true;
         if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
-        e = tcq4::launch_gemm4(w, st, y, yo.ldc, M, N, K, g4, dbg_isum, stream);
+        e = tcq4::launch_gemm4(w, st, y, yo.ldc, M, N, K, g4, reinterpret_cast<float *>(wsb + L.partial_off),
+                               reinterpret_cast<int *>(wsb + L.ticket_off), dbg_isum, stream);
         if (e != cudaSuccess) return cuda_fail(e, "gemm4 launch");
         if (prof) {
             cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
             g_prof.kind[g_prof.n++] = k;
         }
-        g_launches.fetch_add((!reuse_act || split) ? 2 : 1, std::memory_order_relaxed);
+        g_launches.fetch_add((!reuse_act || g4.mode == 1) ? 2 : 1, std::memory_order_relaxed);
         return TCQ4_OK;
     }
     if (k == TCQ4_KERNEL_GEMM3) {
@@ -535,7 +555,7 @@ int tcq4_b200_mul_mat_static(const void *w_tiles, const float *x, float *y, int6
     }
     // the only region that must start at zero (counters of the opt-in fused activation stage); everything else is
     // written before it is read within the call
-    e = cudaMemsetAsync(scratch, 0, L.ticket_bytes < 256 ? L.ticket_bytes : 256, stream);
+    e = cudaMemsetAsync(scratch, 0, L.ticket_bytes < 1024 ? L.ticket_bytes : 1024, stream);
     if (e != cudaSuccess) return cuda_fail(e, "static scratch memset");
     return run_mul_mat(w_tiles, x, single_out(y, N), M, N, K, d_perm, scratch, TCQ4_STATIC_SCRATCH_BYTES, TCQ4_KERNEL_AUTO,
                        nullptr, stream);

@@ -30,6 +30,7 @@
 #include <cuda.h>
 #include <cuda_fp16.h>
 
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 
@@ -164,6 +165,7 @@ __device__ __noinline__ float g4_zero_point_term(const uint8_t *__restrict__ w, 
 // Timeline stamps and what-if switches (diagnostics build only, TCQ4_G4_PROF / TCQ4_G4_EXP): SM clocks of the middle CTA,
 // [role 4: MMA issuer, widening warp 0, widening warp 15, epilogue warp 0][k-tile 64][event 8]
 constexpr int G4_PROF_KT = 64;
+enum { G4_WHOLE = 0, G4_TWO = 1, G4_PARTS = 2 };      // how the ranges of the blocks * KT line meet in y (Gemm4Plan::mode)
 #ifdef TCQ4_DIAG
 __device__ long long g_g4_prof[4 * G4_PROF_KT * 8];
 #define G4_STAMP(role, kt, ev)                                                                                            \
@@ -180,7 +182,8 @@ __device__ long long g_g4_prof[4 * G4_PROF_KT * 8];
 template <int NCH, bool DEBUG>
 __global__ void __launch_bounds__(G4_THREADS, 1)
 tcq4_gemm4_kernel(const __grid_constant__ CUtensorMap tm_w, const uint8_t *__restrict__ w, ActStage st, float *__restrict__ y,
-                  long long ldc, int M, int N, int K, int num_blocks, int whole_blocks, int32_t *__restrict__ dbg_isum, int exp) {
+                  long long ldc, int M, int N, int K, int num_blocks, int mode, int parts, float *__restrict__ partials,
+                  int *__restrict__ counters, int32_t *__restrict__ dbg_isum, int exp) {
     extern __shared__ __align__(128) uint8_t smem[];
 #ifdef TCQ4_DIAG
     const bool prof_on = (exp & 0x100) && blockIdx.x == gridDim.x / 2 && (threadIdx.x & 31) == 0;
@@ -228,7 +231,8 @@ tcq4_gemm4_kernel(const __grid_constant__ CUtensorMap tm_w, const uint8_t *__res
     const uint32_t tmem = *tmem_slot;
     pdl_launch_dependents();
     // this CTA's range of the blocks * KT line, walked segment by segment (block nb, k-tiles [kt0, kt1)) by every role
-    // (whole_blocks: ranges of whole blocks only -- strided outputs cannot be zeroed by K1)
+    // (mode G4_WHOLE: ranges of whole blocks only -- strided outputs cannot be zeroed by K1)
+    const bool whole_blocks = (mode == G4_WHOLE);
     const long long total_units = (long long)num_blocks * KT;
     const long long lin0 = whole_blocks ? ((long long)num_blocks * blockIdx.x / gridDim.x) * KT : total_units * blockIdx.x / gridDim.x;
     const long long lin1 = whole_blocks ? ((long long)num_blocks * (blockIdx.x + 1) / gridDim.x) * KT : total_units * (blockIdx.x + 1) / gridDim.x;
@@ -249,6 +253,9 @@ tcq4_gemm4_kernel(const __grid_constant__ CUtensorMap tm_w, const uint8_t *__res
                 for (int kt = kt0; kt < kt1; kt++) {
                     if (u > 0) g4_wait(&wempty[s], (uint32_t)((u - 1) & 1));
                     mbar_arrive_expect_tx(&wfull[s], (uint32_t)G4_RAW_W);
+                    if (G4_EXP(16))      // what-if: the same bytes as one contiguous unit (is the tile layout what bounds the stream?)
+                        bulk_g2s(sRaw + s * G4_W_BYTES, w + ((size_t)nb * KT + kt) * G4_RAW_W, G4_RAW_W, &wfull[s]);
+                    else
                     g4_tma_2d(sRaw + s * G4_W_BYTES, &tm_w, kt * (TILE_BYTES / 8), nb * 16, &wfull[s], pol_w);
                     if (++s == G4_W_STAGES) { s = 0; u++; }
                 }
@@ -370,6 +377,7 @@ tcq4_gemm4_kernel(const __grid_constant__ CUtensorMap tm_w, const uint8_t *__res
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&snfull[ring]);
                 }
+                G4_CSTAMP(7);
                 if (gk > 1) {
                     g4_wait(&opfree[team], (uint32_t)(((gk >> 1) - 1) & 1));
                     tc_fence_after();
@@ -485,8 +493,57 @@ tcq4_gemm4_kernel(const __grid_constant__ CUtensorMap tm_w, const uint8_t *__res
                     }
                 }
             }
-            // ---- end of the segment.  A warp stores 32 consecutive channels of one token: coalesced.  A part of a block (stream-K)
-            //      is added to the zeroed output: a block has at most two parts, so the sum does not depend on their order.
+            // ---- end of the segment.  A warp stores 32 consecutive channels of one token: coalesced.
+            if (mode == G4_PARTS) {
+                // The block is cut into `parts` K ranges, one CTA each (narrow, deep matrices: every SM gets a share of K).  Each
+                // part leaves its sums in a workspace slot and counts itself in; whoever arrives LAST adds the slots in part order
+                // (its own too, re-read: one code path) and stores -- deterministic, no waiting, no zeroed output.  Counters
+                // are per (block, lane quarter): a warp needs only the same warp's columns of the other parts.
+                float *slot = partials + (size_t)blockIdx.x * (MT * G4_CH) + chl;
+#pragma unroll
+                for (int i = 0; i < MT / 2; i++) {
+                    float a, bb;
+                    g4_unpack(acc2[i], a, bb);
+                    if (2 * i < M) __stcg(slot + (2 * i) * G4_CH, a);
+                    if (2 * i + 1 < M) __stcg(slot + (2 * i + 1) * G4_CH, bb);
+                }
+                __threadfence();
+                __syncwarp();
+                int old = 0;
+                if (lane == 0) old = atomicAdd(counters + nb * 4 + q4, 1);
+                old = __shfl_sync(0xffffffffu, old, 0);
+                if (old != parts - 1) continue;
+                __threadfence();
+                if (lane == 0) counters[nb * 4 + q4] = 0;      // ready for the next launch
+                const float *base = partials + (size_t)nb * parts * (MT * G4_CH) + chl;
+                for (int t0 = 0; t0 < M; t0 += 8) {            // 8 tokens x parts loads in flight per round trip
+                    float sum[8];
+#pragma unroll
+                    for (int i = 0; i < 8; i++) sum[i] = 0.0f;
+#pragma unroll 1
+                    for (int p0 = 0; p0 < parts; p0 += 4) {
+                        float pv[4][8];
+#pragma unroll
+                        for (int pp = 0; pp < 4; pp++)
+#pragma unroll
+                            for (int i = 0; i < 8; i++)
+                                pv[pp][i] = (p0 + pp < parts && t0 + i < M) ? __ldcg(base + (size_t)(p0 + pp) * (MT * G4_CH) + (t0 + i) * G4_CH) : 0.0f;
+#pragma unroll
+                        for (int pp = 0; pp < 4; pp++)
+#pragma unroll
+                            for (int i = 0; i < 8; i++)
+                                if (p0 + pp < parts) sum[i] += pv[pp][i];
+                    }
+                    if (n < N) {
+#pragma unroll
+                        for (int i = 0; i < 8; i++)
+                            if (t0 + i < M) y[(size_t)(t0 + i) * ldc + n] = sum[i];
+                    }
+                }
+                continue;
+            }
+            // A part of a block (stream-K, K halves) is added to the zeroed output: a block has at most two parts, so the sum does
+            // not depend on their order.
             if (n < N) {
                 const bool part = (kt0 > 0) || (kt1 < KT);
 #pragma unroll
@@ -511,25 +568,43 @@ tcq4_gemm4_kernel(const __grid_constant__ CUtensorMap tm_w, const uint8_t *__res
 }
 
 // ---- host side ---------------------------------------------------------------------------------------------------
-bool gemm4_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, bool allow_split, Gemm4Plan *plan) {
+bool gemm4_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, bool contiguous_y, Gemm4Plan *plan) {
     if (M < 1 || M > G4_MAXMT || (size_t)Gemm4Smem::total > smem_optin || num_sms < 1) return false;
     const int64_t blocks = (N + G4_CH - 1) / G4_CH, KT = K / TILE_K;
     static const bool no_split = getenv("TCQ4_G4_NOSPLIT") != nullptr;
+    static const bool no_parts = getenv("TCQ4_G4_NOPARTS") != nullptr;
     int64_t grid = blocks < num_sms ? blocks : num_sms;
-    bool whole = true;
-    if (allow_split && !no_split) {
+    int mode = G4_WHOLE, parts = 1;
+    if (!no_split) {
         if (blocks > num_sms && blocks % num_sms != 0) {
-            whole = false;                                     // stream-K: ranges >= one block, a block is cut at most once
+            if (contiguous_y) mode = G4_TWO;                   // stream-K: ranges >= one block, a block is cut at most once
         } else if (2 * blocks <= num_sms && KT >= 8) {
-            grid = 2 * blocks;                                 // the blocks' K halves
-            whole = false;
+            // K parts.  Cost model in k-tile times (~1 us): a part's k-tiles + the last arriver's reduction (one atomic round
+            // trip, then ceil(M/8) * ceil(P/4) load round trips); two parts meet through red.add instead and cost nothing extra
+            const int64_t pmax = std::min<int64_t>({(int64_t)num_sms / blocks, (int64_t)GEMM4_MAX_PARTS, KT / 4});
+            double best = contiguous_y ? (double)((KT + 1) / 2) : (double)KT;
+            int bp = contiguous_y ? 2 : 1;
+            for (int64_t p = 3; p <= pmax && !no_parts; p++) {
+                const double fix = 2.0 + 0.6 * (double)((M + 7) / 8) * (double)((p + 3) / 4);
+                const double c = (double)((KT + p - 1) / p) + fix;
+                if (c < best - 1.0) {
+                    best = c;
+                    bp = (int)p;
+                }
+            }
+            parts = bp;
+            grid = blocks * parts;
+            mode = parts == 1 ? G4_WHOLE : parts == 2 ? G4_TWO : G4_PARTS;
         }
     }
     plan->grid = (int)grid;
     plan->num_blocks = (int)blocks;
-    plan->whole_blocks = whole ? 1 : 0;
+    plan->mode = mode;
+    plan->parts = parts;
     plan->mt = M <= 32 ? 32 : 64;
     plan->smem_bytes = Gemm4Smem::total;
+    plan->partial_bytes = mode == G4_PARTS ? (size_t)grid * plan->mt * G4_CH * 4 : 0;
+    plan->counter_bytes = mode == G4_PARTS ? (size_t)blocks * 16 : 0;
     return true;
 }
 
@@ -549,7 +624,7 @@ static G4EncodeTiled g4_encoder() {
 }
 
 cudaError_t launch_gemm4(const void *w_tiles, ActStage st, float *y, int64_t ldc, int64_t M, int64_t N, int64_t K,
-                         const Gemm4Plan &plan, int32_t *dbg_isum, cudaStream_t stream) {
+                         const Gemm4Plan &plan, float *partials, int *counters, int32_t *dbg_isum, cudaStream_t stream) {
     G4EncodeTiled enc = g4_encoder();
     if (!enc) return cudaErrorInvalidValue;
     CUtensorMap tm;
@@ -579,12 +654,12 @@ cudaError_t launch_gemm4(const void *w_tiles, ActStage st, float *y, int64_t ldc
 #endif
     if (plan.mt == 32) {
         if (dbg_isum)
-            return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<1, true>, tm, w8, st, y, (long long)ldc, (int)M, (int)N, (int)K, plan.num_blocks, plan.whole_blocks, dbg_isum, exp);
-        return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<1, false>, tm, w8, st, y, (long long)ldc, (int)M, (int)N, (int)K, plan.num_blocks, plan.whole_blocks, (int32_t *)nullptr, exp);
+            return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<1, true>, tm, w8, st, y, (long long)ldc, (int)M, (int)N, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, dbg_isum, exp);
+        return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<1, false>, tm, w8, st, y, (long long)ldc, (int)M, (int)N, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, (int32_t *)nullptr, exp);
     }
     if (dbg_isum)
-        return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, true>, tm, w8, st, y, (long long)ldc, (int)M, (int)N, (int)K, plan.num_blocks, plan.whole_blocks, dbg_isum, exp);
-    return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, false>, tm, w8, st, y, (long long)ldc, (int)M, (int)N, (int)K, plan.num_blocks, plan.whole_blocks, (int32_t *)nullptr, exp);
+        return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, true>, tm, w8, st, y, (long long)ldc, (int)M, (int)N, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, dbg_isum, exp);
+    return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, false>, tm, w8, st, y, (long long)ldc, (int)M, (int)N, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, (int32_t *)nullptr, exp);
 }
 
 cudaError_t gemm4_read_prof(long long *host_out, size_t bytes) {

@@ -132,19 +132,25 @@ cudaError_t launch_gemm3(const Gemm3Seg *segs, int nseg, ActStage st, int64_t M,
                          int32_t *dbg_isum, cudaStream_t stream, const float *res = nullptr, const float *bias = nullptr);
 
 // ---- K2c: batched-decode GEMM, 17 <= M <= 64 (tcq4_gemm4.cu) -----------------------------------------------------
+constexpr int GEMM4_MAX_PARTS = 8;
+constexpr int GEMM4_MAX_CTAS = 160;        // bound of blocks * parts (workspace sizing is device independent)
 struct Gemm4Plan {
     int    grid;            // CTAs = contiguous ranges of the blocks * KT line
     size_t smem_bytes;
     int    mt;              // tokens per MMA (32 or 64)
     int    num_blocks;      // 128-channel blocks
-    int    whole_blocks;    // 1: every range is whole blocks (plain stores); 0: blocks are cut (at most once each) and their parts
-                            //    meet in y through red.global.add.f32 -- y must start at zero
+    int    mode;            // 0: every range is whole blocks (plain stores); 1: a block has at most two parts, they meet in y through
+                            //    red.global.add.f32 -- y must start at zero; 2: `parts` K ranges per block, partial sums in workspace
+                            //    slots, the last part to arrive adds them in order -- the counters must start at zero
+    int    parts;
+    size_t partial_bytes;   // mode 2: one [mt][128] fp32 slot per CTA
+    size_t counter_bytes;   // mode 2: 4 ints per block
 };
-bool        gemm4_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, bool allow_split, Gemm4Plan *plan);
+bool        gemm4_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, bool contiguous_y, Gemm4Plan *plan);
 cudaError_t gemm4_init_attributes(size_t smem_optin);
 cudaError_t gemm4_read_prof(long long *host_out, size_t bytes);           // timeline stamps (diagnostics build)
 // st: MODE_NIB activation stage of the M <= 64 tokens (nibble units + a7t); y row stride ldc floats
 cudaError_t launch_gemm4(const void *w_tiles, ActStage st, float *y, int64_t ldc, int64_t M, int64_t N, int64_t K,
-                         const Gemm4Plan &plan, int32_t *dbg_isum, cudaStream_t stream);
+                         const Gemm4Plan &plan, float *partials, int *counters, int32_t *dbg_isum, cudaStream_t stream);
 
 }  // namespace tcq4

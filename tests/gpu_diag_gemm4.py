@@ -33,8 +33,8 @@ if os.environ.get("TCQ4_G4_PROF"):
     rc = d.tcq4_b200_debug_gemm4_timeline(C.c_void_p(raw.ctypes.data), C.c_size_t(raw.nbytes))
     buf = raw.reshape(4, 64, 8)
     names = {0: ("mma", ["top", "accempty_ok", "opfull_ok", "issued"]),
-             1: ("cw 0", ["top", "wfull_ok", "afull_ok", "opfree_ok", "w cvt+st", "act sts", "wait::st", "-"]),
-             2: ("cw15", ["top", "wfull_ok", "afull_ok", "opfree_ok", "w cvt+st", "act sts", "wait::st", "-"]),
+             1: ("cw 0", ["top", "wfull_ok", "afull_ok", "opfree_ok", "w cvt+st", "act sts", "wait::st", "published"]),
+             2: ("cw15", ["top", "wfull_ok", "afull_ok", "opfree_ok", "w cvt+st", "act sts", "wait::st", "published"]),
              3: ("epi0", ["top", "snfull_ok", "accfull_ok", "ld done", "math end"])}
     t0 = buf[0, 0, 0]
     KT = min(K // 256, 40)

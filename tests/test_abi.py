@@ -43,7 +43,8 @@ def test_supports_and_select(t4):
     assert not t4.supports(0, 8, 256)
     assert t4.select_kernel(1, 9728, 2560) == t4.KERNEL_GEMV
     assert t4.select_kernel(4, 2560, 9728) == t4.KERNEL_GEMV
-    assert t4.select_kernel(16, 9728, 2560) == t4.KERNEL_GEMV
+    assert t4.select_kernel(8, 9728, 2560) == t4.KERNEL_GEMV
+    assert t4.select_kernel(16, 9728, 2560) == t4.KERNEL_GEMM4     # 9 <= M <= 16 and <= 16 k-tiles per CTA: weights through TMEM
     assert t4.select_kernel(17, 9728, 2560) == t4.KERNEL_GEMM4     # batched decode: weights through TMEM
     assert t4.select_kernel(65, 9728, 2560) == t4.KERNEL_GEMM
     assert t4.select_kernel(128, 9728, 2560) == t4.KERNEL_GEMM
