@@ -23,7 +23,7 @@ enum { MODE_REF = 0, MODE_STAGE = 1, MODE_NIB = 2 };
 template <int MODE>
 __global__ void __launch_bounds__(ACT_WARPS_PER_CTA * 32)
 tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ perm, int M, int K,
-                      ActBlockTC *__restrict__ out_ref, ActStage st, float4 *__restrict__ zero_y, long long zero_n4) {
+                      ActBlockTC *__restrict__ out_ref, ActStage st, const __grid_constant__ ZeroList zl) {
     const int lane = threadIdx.x & 31;
     const int KT = K / TILE_K;
     const long long nblocks = (long long)M * KT;
@@ -36,10 +36,15 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
     pdl_launch_dependents();     // the GEMM behind this kernel may set itself up (it waits before reading the codes)
     pdl_wait();                  // x and the staging arena belong to the previous kernel until here
 
-    if (MODE == MODE_NIB && zero_y != nullptr) {      // K-split GEMM behind this launch: its output starts at zero
+    if (MODE == MODE_NIB && zl.n > 0) {      // the GEMM behind this launch accumulates into its outputs (K split) / counts arrivals
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < zero_n4; i += (long long)gridDim.x * blockDim.x)
-            zero_y[i] = z;
+        for (int r = 0; r < zl.n; r++) {
+            const long long c4 = zl.cols[r] >> 2, n4 = zl.rows[r] * c4;
+            for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+                const long long row = i / c4;
+                reinterpret_cast<float4 *>(zl.p[r] + row * zl.ld[r])[i - row * c4] = z;
+            }
+        }
     }
 
     for (long long b = warp0; b < nblocks; b += nwarps) {
@@ -102,7 +107,7 @@ static int act_grid(int64_t nblocks, int num_sms) {
 
 template <typename Kern>
 static cudaError_t launch_act(Kern kern, int grid, cudaStream_t stream, const float *x, const int32_t *perm, int M, int K,
-                              ActBlockTC *out_ref, ActStage st, int which = 0, float *zero_y = nullptr, int64_t zero_floats = 0) {
+                              ActBlockTC *out_ref, ActStage st, int which = 0, const ZeroList *zlp = nullptr) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(ACT_WARPS_PER_CTA * 32);
@@ -125,7 +130,9 @@ static cudaError_t launch_act(Kern kern, int grid, cudaStream_t stream, const fl
         cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
         done = true;
     }
-    return cudaLaunchKernelEx(&cfg, kern, x, perm, M, K, out_ref, st, reinterpret_cast<float4 *>(zero_y), (long long)(zero_floats / 4));
+    ZeroList zl{};
+    if (zlp) zl = *zlp;
+    return cudaLaunchKernelEx(&cfg, kern, x, perm, M, K, out_ref, st, zl);
 }
 
 cudaError_t launch_act_quant_ref(const float *x, const int32_t *perm, int64_t M, int64_t K, void *out_blocks,
@@ -145,12 +152,24 @@ cudaError_t launch_act_quant_stage(const float *x, const int32_t *perm, int64_t 
                       (ActBlockTC *)nullptr, st);
 }
 
-cudaError_t launch_act_quant_nib(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st, int num_sms,
-                                 cudaStream_t stream, float *zero_y, int64_t zero_floats) {
+cudaError_t launch_act_quant_nib_zl(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st, int num_sms,
+                                    cudaStream_t stream, const ZeroList *zl) {
     const int64_t nblocks = M * (K / TILE_K);
     if (nblocks == 0) return cudaSuccess;
     return launch_act(tcq4_act_quant_kernel<MODE_NIB>, act_grid(nblocks, num_sms), stream, x, perm, (int)M, (int)K,
-                      (ActBlockTC *)nullptr, st, 2, zero_y, zero_floats);
+                      (ActBlockTC *)nullptr, st, 2, zl);
+}
+cudaError_t launch_act_quant_nib(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st, int num_sms,
+                                 cudaStream_t stream, float *zero_y, int64_t zero_floats) {
+    ZeroList zl{};
+    if (zero_y != nullptr && zero_floats >= 4) {
+        zl.n = 1;
+        zl.p[0] = zero_y;
+        zl.rows[0] = 1;
+        zl.cols[0] = zero_floats & ~(int64_t)3;
+        zl.ld[0] = zl.cols[0];
+    }
+    return launch_act_quant_nib_zl(x, perm, M, K, st, num_sms, stream, &zl);
 }
 
 __global__ void tcq4_zero_kernel(float4 *__restrict__ y, long long n4) {
@@ -158,6 +177,23 @@ __global__ void tcq4_zero_kernel(float4 *__restrict__ y, long long n4) {
     pdl_wait();
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) y[i] = z;
+}
+__global__ void tcq4_zero_list_kernel(const __grid_constant__ ZeroList zl) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < zl.n; r++) {
+        const long long c4 = zl.cols[r] >> 2, n4 = zl.rows[r] * c4;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+            const long long row = i / c4;
+            reinterpret_cast<float4 *>(zl.p[r] + row * zl.ld[r])[i - row * c4] = z;
+        }
+    }
+}
+cudaError_t launch_zero_list(const ZeroList &zl, int num_sms, cudaStream_t stream) {
+    if (zl.n == 0) return cudaSuccess;
+    tcq4_zero_list_kernel<<<(unsigned)num_sms, 256, 0, stream>>>(zl);
+    return cudaGetLastError();
 }
 cudaError_t launch_zero_floats(float *y, int64_t n_floats, int num_sms, cudaStream_t stream) {
     const long long n4 = n_floats / 4;

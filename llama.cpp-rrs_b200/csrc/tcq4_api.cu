@@ -161,12 +161,10 @@ int select_kernel(const DevInfo *d, int64_t M, int64_t N, int64_t K, tcq4::GemvP
     tcq4::GemvPlan tmp;
     static const bool no_g4 = getenv("TCQ4_NO_GEMM4") != nullptr;
     if (tcq4::gemv_plan(M, N, K, sms, optin, gv ? gv : &tmp)) {
-        // 9 <= M <= 16: the batched-decode GEMM is 15-20 % ahead of the GEMV when its CTAs get at most 16 k-tiles each
-        // (measured, tests/gpu_g4_vs_gemv.py); deeper ranges and M <= 8 stay with the GEMV
+        // 9 <= M <= 16: the batched-decode GEMM is 10-25 % ahead of the GEMV on every shape of BASELINE's configs (measured,
+        // tests/gpu_g4_vs_gemv.py, profiles/batched_decode_r02.txt); M <= 8 stays with the GEMV (1.2-1.9x ahead there)
         tcq4::Gemm4Plan g4;
-        if (M >= 9 && !no_g4 && tcq4::gemm4_plan(M, N, K, sms, optin, true, &g4) &&
-            ((N + 127) / 128) * (K / 256) <= 16 * (int64_t)g4.grid)
-            return TCQ4_KERNEL_GEMM4;
+        if (M >= 9 && !no_g4 && tcq4::gemm4_plan(M, &N, 1, K, sms, optin, &g4)) return TCQ4_KERNEL_GEMM4;
         return TCQ4_KERNEL_GEMV;
     }
     // 17 <= M <= 64 (batched decode): weights through TMEM, tokens as the MMA's N (tcq4_gemm4.cu)
@@ -189,6 +187,60 @@ tcq4::YOut single_out(float *y, int64_t N) {
     o.ldc = N;
     o.mc = nullptr;
     return o;
+}
+
+// K1 (unless the activations of x already sit in the workspace) + ONE batched-decode GEMM launch over up to four matrices
+// that share x.  What must start at zero -- the outputs when blocks are cut in two (red.add), the arrival counters when
+// they are cut in K parts -- is cleared by K1 itself (strided outputs row by row), or by a small kernel when K1 does not run.
+int run_gemm4_group(DevInfo *d, const tcq4::Gemm4Seg *segs, int nseg, const float *x, const int32_t *perm, int64_t M, int64_t K,
+                    uint8_t *wsb, const WsLayout &L, bool reuse_act, int32_t *dbg_isum, cudaStream_t stream, int *launches) {
+    int64_t Ns[tcq4::GEMM4_MAX_SEG];
+    for (int i = 0; i < nseg; i++) Ns[i] = segs[i].N;
+    tcq4::Gemm4Plan g4;
+    if (!tcq4::gemm4_plan(M, Ns, nseg, K, d->num_sms, d->smem_optin, &g4)) {
+        set_err("batched-decode GEMM cannot be planned for this shape/device");
+        return TCQ4_ERR_SHAPE;
+    }
+    if (g4.partial_bytes > L.partial_bytes || g4.counter_bytes > L.ticket_bytes || g4.grid > tcq4::GEMM4_MAX_CTAS) {
+        set_err("internal: batched-decode GEMM workspace bound too small");
+        return TCQ4_ERR_WORKSPACE;
+    }
+    tcq4::ActStage st;
+    st.codes = reinterpret_cast<int8_t *>(wsb + L.codes_off);
+    st.a7 = reinterpret_cast<float *>(wsb + L.a7_off);
+    st.sumq = reinterpret_cast<int16_t *>(wsb + L.sumq_off);
+    st.a7t = reinterpret_cast<float *>(wsb + L.a7t_off);
+    tcq4::ZeroList zl{};
+    if (g4.mode == 1) {
+        zl.n = nseg;
+        for (int i = 0; i < nseg; i++) {
+            zl.p[i] = segs[i].y;
+            zl.rows[i] = M;
+            zl.cols[i] = segs[i].N;       // N % 8 == 0
+            zl.ld[i] = segs[i].ldc;
+        }
+    } else if (g4.mode == 2) {
+        zl.n = 1;
+        zl.p[0] = reinterpret_cast<float *>(wsb + L.ticket_off);
+        zl.rows[0] = 1;
+        zl.cols[0] = tcq4::round_up((int64_t)g4.counter_bytes, 16) / 4;
+        zl.ld[0] = zl.cols[0];
+    }
+    cudaError_t e = cudaSuccess;
+    if (!reuse_act) {
+        e = tcq4::launch_act_quant_nib_zl(x, perm, M, K, st, d->num_sms, stream, &zl);
+        if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
+        (*launches)++;
+    } else if (g4.mode == 1) {       // (counters: their last reader left them at zero)
+        e = tcq4::launch_zero_list(zl, d->num_sms, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "output clear launch");
+        (*launches)++;
+    }
+    e = tcq4::launch_gemm4(segs, nseg, st, M, K, g4, reinterpret_cast<float *>(wsb + L.partial_off),
+                           reinterpret_cast<int *>(wsb + L.ticket_off), dbg_isum, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "gemm4 launch");
+    (*launches)++;
+    return TCQ4_OK;
 }
 
 // N_layout / reuse_act (fan-out, tcq4_b200_mul_mat_fanout): several weight matrices applied to the SAME activations share
@@ -267,45 +319,22 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
         return TCQ4_OK;
     }
     if (k == TCQ4_KERNEL_GEMM4) {
-        // batched decode: nibble staging (K1 MODE_NIB), weights widened into TMEM, optional K split onto a cleared output
-        tcq4::Gemm4Plan g4;
-        if (!tcq4::gemm4_plan(M, N, K, d->num_sms, d->smem_optin, yo.ldc == N, &g4)) {
-            set_err("batched-decode GEMM cannot be planned for this shape/device");
-            return TCQ4_ERR_SHAPE;
-        }
-        if (g4.partial_bytes > L.partial_bytes || g4.counter_bytes > L.ticket_bytes || g4.grid > tcq4::GEMM4_MAX_CTAS) {
-            set_err("internal: batched-decode GEMM workspace bound too small");
-            return TCQ4_ERR_WORKSPACE;
-        }
-        tcq4::ActStage st;
-        st.codes = reinterpret_cast<int8_t *>(wsb + L.codes_off);
-        st.a7 = reinterpret_cast<float *>(wsb + L.a7_off);
-        st.sumq = reinterpret_cast<int16_t *>(wsb + L.sumq_off);
-        st.a7t = reinterpret_cast<float *>(wsb + L.a7t_off);
+        // batched decode: nibble staging (K1 MODE_NIB), weights widened into TMEM, stream-K / K parts
         const bool prof = g_prof.on && g_prof.n < g_prof.cap;
-        if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
-        cudaError_t e = cudaSuccess;
-        // what must start at zero: the output (two-part blocks meet through red.add) or the arrival counters (K parts; their
-        // last arriver clears them again, so fan-out calls that reuse the activations find them zero)
-        float *zero_p = g4.mode == 1 ? y : g4.mode == 2 ? reinterpret_cast<float *>(wsb + L.ticket_off) : nullptr;
-        const int64_t zero_n = g4.mode == 1 ? M * N : (int64_t)tcq4::round_up((int64_t)g4.counter_bytes, 16) / 4;
-        if (!reuse_act) {
-            e = tcq4::launch_act_quant_nib(x, perm, M, K, st, d->num_sms, stream, zero_p, zero_n);
-            if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
-        } else if (g4.mode == 1) {
-            e = tcq4::launch_zero_floats(y, M * N, d->num_sms, stream);
-            if (e != cudaSuccess) return cuda_fail(e, "output clear launch");
+        if (prof) {
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
         }
+        const tcq4::Gemm4Seg sg{w, y, N, yo.ldc};
+        int launches = 0;
+        const int rc = run_gemm4_group(d, &sg, 1, x, perm, M, K, wsb, L, reuse_act, dbg_isum, stream, &launches);
+        if (rc != TCQ4_OK) return rc;
         if (act_done) *act_done = true;
-        if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
-        e = tcq4::launch_gemm4(w, st, y, yo.ldc, M, N, K, g4, reinterpret_cast<float *>(wsb + L.partial_off),
-                               reinterpret_cast<int *>(wsb + L.ticket_off), dbg_isum, stream);
-        if (e != cudaSuccess) return cuda_fail(e, "gemm4 launch");
         if (prof) {
             cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
             g_prof.kind[g_prof.n++] = k;
         }
-        g_launches.fetch_add((!reuse_act || g4.mode == 1) ? 2 : 1, std::memory_order_relaxed);
+        g_launches.fetch_add(launches, std::memory_order_relaxed);
         return TCQ4_OK;
     }
     if (k == TCQ4_KERNEL_GEMM3) {
@@ -673,6 +702,40 @@ int tcq4_b200_mul_mat_fanout_ld(int n, const void *const *w_tiles, const int64_t
     if (status != TCQ4_OK) return status;
     static const bool no_g3 = getenv("TCQ4_NO_GEMM3") != nullptr;       // experiments: fan-out through the round-1 kernels
     const int ksel = select_kernel(d, M, Nmax, K, nullptr);
+    if (ksel == TCQ4_KERNEL_GEMM4 && n >= 2) {
+        // batched decode: ONE activation launch and ONE GEMM launch per group of up to four matrices (their 128-channel
+        // blocks form one stream-K line)
+        for (int i = 0; i < n; i++)
+            if (!w_tiles[i] || !ys[i] || ((uintptr_t)w_tiles[i] & 15) || ((uintptr_t)ys[i] & 15)) {
+                set_err("mul_mat_fanout: null or misaligned pointer of matrix %d", i);
+                return TCQ4_ERR_ARG;
+            }
+        if (!x || ((uintptr_t)x & 15) || (d_perm && ((uintptr_t)d_perm & 15))) {
+            set_err("mul_mat_fanout: null or misaligned x / perm");
+            return TCQ4_ERR_ARG;
+        }
+        const WsLayout L = ws_layout(M, Nmax, K);
+        uint8_t *wsb = reinterpret_cast<uint8_t *>(d->arena);
+        const bool prof = g_prof.on && g_prof.n < g_prof.cap;
+        if (prof) {
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
+        }
+        int launches = 0;
+        for (int i0 = 0; i0 < n; i0 += tcq4::GEMM4_MAX_SEG) {
+            const int ns = std::min(tcq4::GEMM4_MAX_SEG, n - i0);
+            tcq4::Gemm4Seg sg[tcq4::GEMM4_MAX_SEG];
+            for (int i = 0; i < ns; i++) sg[i] = tcq4::Gemm4Seg{w_tiles[i0 + i], ys[i0 + i], Ns[i0 + i], ld[i0 + i]};
+            const int rc = run_gemm4_group(d, sg, ns, x, d_perm, M, K, wsb, L, i0 > 0, nullptr, stream, &launches);
+            if (rc != TCQ4_OK) return rc;
+        }
+        if (prof) {
+            cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
+            g_prof.kind[g_prof.n++] = TCQ4_KERNEL_GEMM4;
+        }
+        g_launches.fetch_add(launches, std::memory_order_relaxed);
+        return TCQ4_OK;
+    }
     if (!no_g3 && n >= 2 && (ksel == TCQ4_KERNEL_GEMM2 || ksel == TCQ4_KERNEL_GEMM3 || ksel == TCQ4_KERNEL_GEMM)) {
         // ONE activation launch and ONE GEMM launch per group of up to four matrices: their column blocks form one tile list
         for (int i = 0; i < n; i++)

@@ -178,11 +178,21 @@ __device__ long long g_g4_prof[4 * G4_PROF_KT * 8];
 #define G4_EXP(bit) false
 #endif
 
+// up to four matrices over the same tokens (a fan-out group: Q/K/V, gate/up): their 128-channel blocks form one line
+struct G4Params {
+    CUtensorMap tm[GEMM4_MAX_SEG];
+    const uint8_t *w[GEMM4_MAX_SEG];
+    float *y[GEMM4_MAX_SEG];
+    long long ldc[GEMM4_MAX_SEG];
+    int N[GEMM4_MAX_SEG];
+    int blk0[GEMM4_MAX_SEG + 1];      // first block of each segment (unused: INT_MAX)
+    int nseg;
+};
+
 // NCH = Mt / 32 (1 or 2)
 template <int NCH, bool DEBUG>
 __global__ void __launch_bounds__(G4_THREADS, 1)
-tcq4_gemm4_kernel(const __grid_constant__ CUtensorMap tm_w, const uint8_t *__restrict__ w, ActStage st, float *__restrict__ y,
-                  long long ldc, int M, int N, int K, int num_blocks, int mode, int parts, float *__restrict__ partials,
+tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K, int num_blocks, int mode, int parts, float *__restrict__ partials,
                   int *__restrict__ counters, int32_t *__restrict__ dbg_isum, int exp) {
     extern __shared__ __align__(128) uint8_t smem[];
 #ifdef TCQ4_DIAG
@@ -220,7 +230,7 @@ tcq4_gemm4_kernel(const __grid_constant__ CUtensorMap tm_w, const uint8_t *__res
         for (int i = 0; i < G4_RING; i++) mbar_init(&snfull[i], 4 + (MT + 31) / 32);      // S: 4 warps, a7/127: NCH warps
         fence_mbar_init();
     }
-    if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_w) : "memory");
+    if (warp == 0 && lane < P.nseg) asm volatile("prefetch.tensormap [%0];" ::"l"(&P.tm[lane]) : "memory");
     if (warp == 1) {
         tmem_alloc(tmem_slot, 512);
         tmem_relinquish();
@@ -253,10 +263,11 @@ tcq4_gemm4_kernel(const __grid_constant__ CUtensorMap tm_w, const uint8_t *__res
                 for (int kt = kt0; kt < kt1; kt++) {
                     if (u > 0) g4_wait(&wempty[s], (uint32_t)((u - 1) & 1));
                     mbar_arrive_expect_tx(&wfull[s], (uint32_t)G4_RAW_W);
+                    const int sg = (nb >= P.blk0[1]) + (nb >= P.blk0[2]) + (nb >= P.blk0[3]);
                     if (G4_EXP(16))      // what-if: the same bytes as one contiguous unit (is the tile layout what bounds the stream?)
-                        bulk_g2s(sRaw + s * G4_W_BYTES, w + ((size_t)nb * KT + kt) * G4_RAW_W, G4_RAW_W, &wfull[s]);
+                        bulk_g2s(sRaw + s * G4_W_BYTES, P.w[0] + ((size_t)nb * KT + kt) * G4_RAW_W, G4_RAW_W, &wfull[s]);
                     else
-                    g4_tma_2d(sRaw + s * G4_W_BYTES, &tm_w, kt * (TILE_BYTES / 8), nb * 16, &wfull[s], pol_w);
+                    g4_tma_2d(sRaw + s * G4_W_BYTES, &P.tm[sg], kt * (TILE_BYTES / 8), (nb - P.blk0[sg]) * 16, &wfull[s], pol_w);
                     if (++s == G4_W_STAGES) { s = 0; u++; }
                 }
             }
@@ -435,7 +446,12 @@ tcq4_gemm4_kernel(const __grid_constant__ CUtensorMap tm_w, const uint8_t *__res
         uint64_t acc2[MT / 2];
         int gk = 0;
         G4_FOR_SEGMENTS {
-            const int n = nb * G4_CH + chl;
+            const int sg = (nb >= P.blk0[1]) + (nb >= P.blk0[2]) + (nb >= P.blk0[3]);
+            const int n = (nb - P.blk0[sg]) * G4_CH + chl;      // channel within its matrix
+            const int N = P.N[sg];
+            float *__restrict__ y = P.y[sg];
+            const long long ldc = P.ldc[sg];
+            const uint8_t *__restrict__ w = P.w[sg];
 #pragma unroll
             for (int i = 0; i < MT / 2; i++) acc2[i] = 0ull;
             for (int kt = kt0; kt < kt1; kt++, gk++) {
@@ -568,9 +584,12 @@ tcq4_gemm4_kernel(const __grid_constant__ CUtensorMap tm_w, const uint8_t *__res
 }
 
 // ---- host side ---------------------------------------------------------------------------------------------------
-bool gemm4_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, bool contiguous_y, Gemm4Plan *plan) {
-    if (M < 1 || M > G4_MAXMT || (size_t)Gemm4Smem::total > smem_optin || num_sms < 1) return false;
-    const int64_t blocks = (N + G4_CH - 1) / G4_CH, KT = K / TILE_K;
+bool gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, size_t smem_optin, Gemm4Plan *plan) {
+    if (M < 1 || M > G4_MAXMT || (size_t)Gemm4Smem::total > smem_optin || num_sms < 1 || nseg < 1 || nseg > GEMM4_MAX_SEG) return false;
+    int64_t blocks = 0;
+    for (int i = 0; i < nseg; i++) blocks += (Ns[i] + G4_CH - 1) / G4_CH;
+    const int64_t KT = K / TILE_K;
+    const bool contiguous_y = true;      // strided outputs are cleared row by row (ZeroList)
     static const bool no_split = getenv("TCQ4_G4_NOSPLIT") != nullptr;
     static const bool no_parts = getenv("TCQ4_G4_NOPARTS") != nullptr;
     int64_t grid = blocks < num_sms ? blocks : num_sms;
@@ -623,19 +642,34 @@ static G4EncodeTiled g4_encoder() {
     return fn;
 }
 
-cudaError_t launch_gemm4(const void *w_tiles, ActStage st, float *y, int64_t ldc, int64_t M, int64_t N, int64_t K,
-                         const Gemm4Plan &plan, float *partials, int *counters, int32_t *dbg_isum, cudaStream_t stream) {
+cudaError_t launch_gemm4(const Gemm4Seg *segs, int nseg, ActStage st, int64_t M, int64_t K, const Gemm4Plan &plan,
+                         float *partials, int *counters, int32_t *dbg_isum, cudaStream_t stream) {
     G4EncodeTiled enc = g4_encoder();
-    if (!enc) return cudaErrorInvalidValue;
-    CUtensorMap tm;
-    const int64_t NT = N / TILE_CH, KT = K / TILE_K;
-    const cuuint64_t gdim[2] = {(cuuint64_t)KT * (TILE_BYTES / 8), (cuuint64_t)NT};
-    const cuuint64_t gstride[1] = {(cuuint64_t)KT * TILE_BYTES};
-    const cuuint32_t box[2] = {TILE_BYTES / 8, 16};
-    const cuuint32_t estr[2] = {1, 1};
-    if (enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, const_cast<void *>(w_tiles), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
-        return cudaErrorInvalidValue;
+    if (!enc || nseg < 1 || nseg > GEMM4_MAX_SEG) return cudaErrorInvalidValue;
+    G4Params P;
+    memset(&P, 0, sizeof(P));
+    const int64_t KT = K / TILE_K;
+    int blk = 0;
+    for (int i = 0; i <= GEMM4_MAX_SEG; i++) P.blk0[i] = 0x7fffffff;
+    for (int i = 0; i < nseg; i++) {
+        const int64_t NT = segs[i].N / TILE_CH;
+        const cuuint64_t gdim[2] = {(cuuint64_t)KT * (TILE_BYTES / 8), (cuuint64_t)NT};
+        const cuuint64_t gstride[1] = {(cuuint64_t)KT * TILE_BYTES};
+        const cuuint32_t box[2] = {TILE_BYTES / 8, 16};
+        const cuuint32_t estr[2] = {1, 1};
+        if (enc(&P.tm[i], CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, const_cast<void *>(segs[i].w), gdim, gstride, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+            return cudaErrorInvalidValue;
+        P.w[i] = reinterpret_cast<const uint8_t *>(segs[i].w);
+        P.y[i] = segs[i].y;
+        P.ldc[i] = (long long)segs[i].ldc;
+        P.N[i] = (int)segs[i].N;
+        P.blk0[i] = blk;
+        blk += (int)((segs[i].N + G4_CH - 1) / G4_CH);
+    }
+    P.nseg = nseg;
+    if (blk != plan.num_blocks) return cudaErrorInvalidValue;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)plan.grid);
     cfg.blockDim = dim3(G4_THREADS);
@@ -647,19 +681,19 @@ cudaError_t launch_gemm4(const void *w_tiles, ActStage st, float *y, int64_t ldc
     cfg.attrs = attr;
     static const bool no_pdl = getenv("TCQ4_NO_PDL") != nullptr;
     cfg.numAttrs = no_pdl ? 0 : 1;
-    const uint8_t *w8 = reinterpret_cast<const uint8_t *>(w_tiles);
     int exp = 0;
 #ifdef TCQ4_DIAG
     exp = (getenv("TCQ4_G4_EXP") ? atoi(getenv("TCQ4_G4_EXP")) : 0) | (getenv("TCQ4_G4_PROF") ? 0x100 : 0);
 #endif
+    if (dbg_isum && nseg != 1) return cudaErrorInvalidValue;
     if (plan.mt == 32) {
         if (dbg_isum)
-            return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<1, true>, tm, w8, st, y, (long long)ldc, (int)M, (int)N, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, dbg_isum, exp);
-        return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<1, false>, tm, w8, st, y, (long long)ldc, (int)M, (int)N, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, (int32_t *)nullptr, exp);
+            return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<1, true>, P, st, (int)M, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, dbg_isum, exp);
+        return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<1, false>, P, st, (int)M, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, (int32_t *)nullptr, exp);
     }
     if (dbg_isum)
-        return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, true>, tm, w8, st, y, (long long)ldc, (int)M, (int)N, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, dbg_isum, exp);
-    return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, false>, tm, w8, st, y, (long long)ldc, (int)M, (int)N, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, (int32_t *)nullptr, exp);
+        return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, true>, P, st, (int)M, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, dbg_isum, exp);
+    return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, false>, P, st, (int)M, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, (int32_t *)nullptr, exp);
 }
 
 cudaError_t gemm4_read_prof(long long *host_out, size_t bytes) {

@@ -19,6 +19,16 @@ cudaError_t launch_act_quant_stage(const float *x, const int32_t *perm, int64_t 
 cudaError_t launch_act_quant_nib(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st, int num_sms,
                                  cudaStream_t stream, float *zero_y = nullptr, int64_t zero_floats = 0);
 cudaError_t launch_zero_floats(float *y, int64_t n_floats, int num_sms, cudaStream_t stream);
+// the same for up to four strided regions (rows x cols floats, row stride ld; cols and ld multiples of 4, p 16-byte aligned):
+// the outputs of a fan-out group whose blocks are cut (tcq4_gemm4.cu), or its arrival counters
+struct ZeroList {
+    float    *p[4];
+    long long rows[4], cols[4], ld[4];
+    int       n;
+};
+cudaError_t launch_act_quant_nib_zl(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st, int num_sms,
+                                    cudaStream_t stream, const ZeroList *zl);
+cudaError_t launch_zero_list(const ZeroList &zl, int num_sms, cudaStream_t stream);
 
 // ---- K3: fused decode GEMV (tcq4_gemv.cu) -----------------------------------------------------
 constexpr int GEMV_MAX_M = 16;
@@ -134,11 +144,17 @@ cudaError_t launch_gemm3(const Gemm3Seg *segs, int nseg, ActStage st, int64_t M,
 // ---- K2c: batched-decode GEMM, 17 <= M <= 64 (tcq4_gemm4.cu) -----------------------------------------------------
 constexpr int GEMM4_MAX_PARTS = 8;
 constexpr int GEMM4_MAX_CTAS = 160;        // bound of blocks * parts (workspace sizing is device independent)
+constexpr int GEMM4_MAX_SEG = 4;           // matrices of a fan-out group served by one launch
+struct Gemm4Seg {
+    const void *w;       // tiles of this matrix
+    float      *y;       // its output, row stride ldc floats
+    int64_t     N, ldc;
+};
 struct Gemm4Plan {
     int    grid;            // CTAs = contiguous ranges of the blocks * KT line
     size_t smem_bytes;
     int    mt;              // tokens per MMA (32 or 64)
-    int    num_blocks;      // 128-channel blocks
+    int    num_blocks;      // 128-channel blocks of all segments
     int    mode;            // 0: every range is whole blocks (plain stores); 1: a block has at most two parts, they meet in y through
                             //    red.global.add.f32 -- y must start at zero; 2: `parts` K ranges per block, partial sums in workspace
                             //    slots, the last part to arrive adds them in order -- the counters must start at zero
@@ -146,11 +162,11 @@ struct Gemm4Plan {
     size_t partial_bytes;   // mode 2: one [mt][128] fp32 slot per CTA
     size_t counter_bytes;   // mode 2: 4 ints per block
 };
-bool        gemm4_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, bool contiguous_y, Gemm4Plan *plan);
+bool        gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, size_t smem_optin, Gemm4Plan *plan);
 cudaError_t gemm4_init_attributes(size_t smem_optin);
 cudaError_t gemm4_read_prof(long long *host_out, size_t bytes);           // timeline stamps (diagnostics build)
 // st: MODE_NIB activation stage of the M <= 64 tokens (nibble units + a7t); y row stride ldc floats
-cudaError_t launch_gemm4(const void *w_tiles, ActStage st, float *y, int64_t ldc, int64_t M, int64_t N, int64_t K,
-                         const Gemm4Plan &plan, float *partials, int *counters, int32_t *dbg_isum, cudaStream_t stream);
+cudaError_t launch_gemm4(const Gemm4Seg *segs, int nseg, ActStage st, int64_t M, int64_t K, const Gemm4Plan &plan,
+                         float *partials, int *counters, int32_t *dbg_isum, cudaStream_t stream);
 
 }  // namespace tcq4

@@ -4,7 +4,7 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 import gpu_g3_bench as b
 t4 = b.t4
-SHAPES = [(14336, 4096), (4096, 14336), (6144, 4096), (4096, 4096), (9728, 2560), (2560, 9728)]
+SHAPES = [(14336, 4096), (4096, 14336), (6144, 4096), (4096, 4096), (9728, 2560), (2560, 9728), (28672, 8192), (8192, 28672)]
 for M in (int(a) for a in (sys.argv[1:] or ["2", "4", "6", "8", "12", "16"])):
     b.M = M
     for N, K in SHAPES:

@@ -81,23 +81,32 @@ def test_gemm4_extreme_codes_are_exact(t4, orc):
     assert nmse(y.cpu().numpy(), ref["C"]) <= FP32_NMSE_TIGHT
 
 
-def test_gemm4_strided_output_and_fanout(t4, orc):
-    """Q/K/V of a 48-token decode batch into one fused buffer (row stride 6144 floats): one activation launch, the matrices
-    reuse its nibbles"""
-    rng = np.random.default_rng(6)
-    M, K = 48, 1024
-    Ns = [1024, 256, 256]
+@pytest.mark.parametrize("M,K,Ns", [(48, 1024, [1024, 256, 256]), (48, 2048, [1024, 256, 256]), (33, 512, [19200, 1032]),
+                                    (20, 6144, [128, 136])])
+def test_gemm4_strided_output_and_fanout(t4, orc, M, K, Ns):
+    """A fan-out group of a decode batch (Q/K/V, gate/up) into one fused buffer (strided outputs): one activation launch and
+    ONE GEMM launch whose blocks run over all matrices -- whole blocks, K halves (outputs cleared row by row by K1),
+    stream-K over 158 blocks, K parts"""
+    rng = np.random.default_rng(6 + K)
     x = make_acts(rng, M, K)
     tl = [orc.quantize_tiles(make_weights(rng, n, K)) for n in Ns]
-    buf = torch.full((M, sum(Ns)), float("nan"), device="cuda")
+    buf = torch.full((M, sum(Ns) + 8), float("nan"), device="cuda")
     outs, o = [], 0
     for n in Ns:
         outs.append(buf[:, o:o + n])
         o += n
     xd = _dev(x)
     g = t4.GgmlGraph([(_dev(t), xd, out, n, "") for t, n, out in zip(tl, Ns, outs)])
+    n0 = t4.launch_count()
     g.compute()
     torch.cuda.synchronize()
-    for t, n, out in zip(tl, Ns, outs):
-        ref = orc.mul_mat(t, x, n)["C"]
-        assert nmse(out.cpu().numpy(), ref) <= FP32_NMSE_TIGHT
+    assert t4.launch_count() - n0 == 2
+    first = [o_.clone() for o_ in outs]
+    g.compute()                                           # a second call on the same workspace: counters / cleared outputs
+    torch.cuda.synchronize()
+    assert torch.isnan(buf[:, sum(Ns):]).all()            # nothing written outside the outputs
+    for t, n, out, f in zip(tl, Ns, outs, first):
+        assert torch.equal(out, f)
+        rows = slice(0, 8) if n * K * M > 3e8 else slice(0, M)
+        ref = orc.mul_mat(t, x[rows], n)["C"]
+        assert nmse(out[rows].cpu().numpy(), ref) <= FP32_NMSE_TIGHT
