@@ -659,7 +659,9 @@ int tcq4_b200_mul_mat_fanout_ld(int n, const void *const *w_tiles, const int64_t
     for (int i = 0; i < n; i++) Nsum += Ns[i];
     tcq4::GemvPlan gv;
     static const bool no_seg = getenv("TCQ4_FANOUT_NOSEG") != nullptr;       // diagnostics / tests: one launch per matrix
-    if (n >= 2 && n <= tcq4::GV_MAX_SEG && !no_seg && shape_ok(M, Nsum, K) &&
+    // (9 <= M <= 16: the batched-decode GEMM takes the group, as it takes single matrices -- select_kernel)
+    const bool gemv_group = select_kernel(d, M, Nmax, K, nullptr) == TCQ4_KERNEL_GEMV;
+    if (n >= 2 && n <= tcq4::GV_MAX_SEG && !no_seg && gemv_group && shape_ok(M, Nsum, K) &&
         tcq4::gemv_plan(M, Nsum, K, d->num_sms, d->smem_optin, &gv)) {
         tcq4::GvExpert ex{};
         ex.pdl = 1;
