@@ -524,6 +524,68 @@ def configs_leg(t4, torch, dist, world, rank, mode):
     return out
 
 
+# BASELINE.json configs[2]: Llama-3-8B with imatrix channel reordering, decode batch 1-64.  One layer's seven TCQ4 matmuls
+LLAMA3_8B_LAYER = [("attn_q", 4096, 4096, "attn_norm"), ("attn_k", 1024, 4096, "attn_norm"), ("attn_v", 1024, 4096, "attn_norm"),
+                   ("attn_output", 4096, 4096, "kqv_out"), ("ffn_gate", 14336, 4096, "ffn_norm"), ("ffn_up", 14336, 4096, "ffn_norm"),
+                   ("ffn_down", 4096, 14336, "ffn_act")]
+
+
+def batch_decode_leg(t4, torch, peak_gbs, Ms=(1, 2, 4, 8, 16, 32, 64)):
+    """Llama-3-8B layer shapes with a synthetic-imatrix channel permutation per activation tensor (tensors fed by the same
+    activations share it, as derive_tcq4_perms_from_imatrix gives them), batch sizes 1..64: the ggml-graph entry over three
+    layers of distinct weights (378 MB, L2-cold), replayed as one CUDA graph; us per layer, launches per layer, weight GB/s."""
+    import numpy as np
+    rng = np.random.default_rng(2024)
+    n_layers = 3
+    t4.set_reorder_enabled(True)
+    perms = {}
+    for _, _, K, src in LLAMA3_8B_LAYER:
+        if src not in perms:
+            perms[src] = t4.perm_from_imatrix(rng.gamma(2.0, 1.0, K).astype(np.float32))
+    weights = []
+    for l in range(n_layers):
+        for j, (nm, N, K, src) in enumerate(LLAMA3_8B_LAYER):
+            name = f"blk.{l}.{nm}.weight"
+            t4.register_perm(name, perms[src])
+            weights.append((name, N, K, src, t4.random_tiles(N, K, seed=5000 + l * 8 + j)))
+    wbytes = sum(w[4].numel() for w in weights) / n_layers
+    res = []
+    for M in Ms:
+        xs = {src: torch.randn((M, K), device="cuda") for _, _, K, src in LLAMA3_8B_LAYER}
+        nodes = [(w, xs[src], torch.empty((M, N), device="cuda"), N, name) for (name, N, K, src, w) in weights]
+        t4.reserve(M, 14336, 14336)
+        g = t4.GgmlGraph(nodes)
+        n0 = t4.launch_count()
+        g.compute()
+        launches = (t4.launch_count() - n0) / n_layers
+        torch.cuda.synchronize()
+        cg = torch.cuda.CUDAGraph()
+        st = torch.cuda.Stream()
+        st.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(st):
+            with torch.cuda.graph(cg, stream=st):
+                g.compute(stream=st)
+        torch.cuda.current_stream().wait_stream(st)
+        for _ in range(3):
+            cg.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 10
+        e0.record()
+        for _ in range(reps):
+            cg.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / reps / n_layers
+        res.append({"M": M, "us_per_layer": us, "launches_per_layer": launches, "weight_gbs": wbytes / (us * 1e-6) / 1e9,
+                    "frac_hbm": wbytes / (us * 1e-6) / 1e9 / peak_gbs, "tok_per_s_per_layer": M / (us * 1e-6)})
+        del nodes, g, cg
+    t4.clear_perms()
+    return {"shapes": [f"{n}: N={N} K={K}" for n, N, K, _ in LLAMA3_8B_LAYER], "perm": "synthetic imatrix, per activation tensor",
+            "timing": "tcq4_b200_ggml_graph_compute over 3 layers of distinct weights in one CUDA graph, 10 replays",
+            "weight_bytes_per_layer": wbytes, "per_batch": res}
+
+
 def timed_steps(torch, dist, chain, steps, warmup, world):
     """W untimed steps, then exactly K steps between barrier + synchronize, CUDA events, max over ranks."""
     for _ in range(warmup):
@@ -742,6 +804,11 @@ def run_own_arm(args):
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
+        if world == 1:      # configs[2]: Llama-3-8B decode batch 1-64 (one GPU)
+            try:
+                big_configs["llama3_8b_decode_batch"] = batch_decode_leg(t4, torch, peaks["hbm_gbs"])
+            except Exception as e:  # noqa: BLE001
+                big_configs["llama3_8b_decode_batch"] = {"error": f"{type(e).__name__}: {e}"}
 
     # ---- end to end through the host-buffer C-ABI call ---------------------------------------------------
     e2e_s, h2d, d2h = e2e_leg(t4, torch, pre, max(1, min(args.steps, 2)), M)

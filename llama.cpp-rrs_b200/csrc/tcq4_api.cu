@@ -315,7 +315,7 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
             cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
             g_prof.kind[g_prof.n++] = TCQ4_KERNEL_GEMV;
         }
-        g_launches.fetch_add(1, std::memory_order_relaxed);
+        g_launches.fetch_add((blob && tcq4::gemv_uses_prepass(gv, perm)) ? 2 : 1, std::memory_order_relaxed);
         return TCQ4_OK;
     }
     if (k == TCQ4_KERNEL_GEMM4) {
@@ -697,7 +697,7 @@ int tcq4_b200_mul_mat_fanout_ld(int n, const void *const *w_tiles, const int64_t
             cudaEventRecord(g_prof.ev[3 * g_prof.n + 2], stream);
             g_prof.kind[g_prof.n++] = TCQ4_KERNEL_GEMV;
         }
-        g_launches.fetch_add(1, std::memory_order_relaxed);
+        g_launches.fetch_add((blob && tcq4::gemv_uses_prepass(gv, d_perm)) ? 2 : 1, std::memory_order_relaxed);
         return TCQ4_OK;
     }
     status = arena_ensure(d, ws_layout(M, Nmax, K).total, stream);

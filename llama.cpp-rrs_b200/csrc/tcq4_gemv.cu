@@ -156,6 +156,7 @@ __device__ __forceinline__ void gv_store_act_block(const ActQuant &a, uint8_t *b
 // (M = 8, K = 14336: 448 blocks on 16 warps = 28 rounds, 20 us); here the blocks are spread over the whole GPU once and
 // the GEMV copies the finished codes and scales (M*K + 40*M*K/256 bytes, L2-resident) into its shared memory.
 constexpr int GV_PREPASS_BLOCKS = 32;
+constexpr int GV_PREPASS_PERM_BLOCKS = 16;
 constexpr int GVP_WARPS = 4;
 
 __global__ void __launch_bounds__(GVP_WARPS * 32)
@@ -728,6 +729,9 @@ bool gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, 
     // M = 1 keeps the stage inside the kernel: consecutive M = 1 launches share an SM (dependent launch), and a kernel
     // between them costs more than the 2-4 rounds it saves (K = 14336: 14.1 us inside, 15.6 us with the pre-pass)
     plan->prepass = !nopre && M >= 2 && M * KT > GV_PREPASS_BLOCKS;
+    // with a channel permutation every block is a gather (two dependent loads per element): there the pre-pass pays from 17
+    // blocks, M = 1 included (Llama-3-8B layer with imatrix perms, graph: M = 1 61.2 -> 56.8 us, M = 2 66.1 -> 55.4 us)
+    plan->prepass_perm = !nopre && M * KT > GV_PREPASS_PERM_BLOCKS;
     plan->blob_bytes = (size_t)(L.off_part - L.off_afrag);
     int64_t clusters = num_sms / GV_CLUSTER;
     if (NT < clusters) clusters = NT;                              // a cluster owns whole rows
@@ -850,12 +854,14 @@ cudaError_t launch_gemv_grouped(const void *w_experts, const float *x, const int
                               (int)(n_used * N), (int)K, plan.depth, (const uint8_t *)nullptr, (int32_t *)nullptr, expert);
 }
 
+bool gemv_uses_prepass(const GemvPlan &plan, const int32_t *perm) { return plan.prepass || (perm != nullptr && plan.prepass_perm); }
+
 template <int MB, int MT>
 static cudaError_t launch_gemv_d(bool debug, const void *w, const float *x, const int32_t *perm, YOut y, int64_t M, int64_t N,
                                  int64_t K, const GemvPlan &plan, uint8_t *blob, int32_t *dbg, cudaStream_t stream,
                                  const GvExpert *expert) {
     const uint8_t *pre = nullptr;
-    if (plan.prepass && blob != nullptr) {
+    if (gemv_uses_prepass(plan, perm) && blob != nullptr) {
         // activation stage once for the whole GPU (see tcq4_gemv_prepass_kernel), in the GEMV's own layout
         const GvSmem L((int)M, (int)(K / TILE_K), plan.warps, plan.depth);
         cudaLaunchConfig_t cfg = {};
@@ -901,7 +907,11 @@ cudaError_t launch_gemv(const void *w_tiles, const float *x, const int32_t *perm
         switch (M) {
             case 1: return launch_gemv_d<1, 1>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream, expert);
             case 2: return launch_gemv_d<1, 2>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream, expert);
-            case 3: return launch_gemv_d<1, 3>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream, expert);
+            case 3: {      // round 2: with the pre-pass in front the IMMA loop is 3-11 % ahead at M = 3 on every shape measured
+                static const bool dp3 = getenv("TCQ4_GV_DP3") != nullptr;      // (tests/gpu_g4_vs_gemv.py 3); the dp4a form stays selectable
+                if (dp3) return launch_gemv_d<1, 3>(dbg, w_tiles, x, perm, y, M, N, K, plan, blob, dbg_isum, stream, expert);
+                break;
+            }
             default: break;
         }
     }

@@ -32,11 +32,14 @@ cudaError_t launch_zero_list(const ZeroList &zl, int num_sms, cudaStream_t strea
 
 // ---- K3: fused decode GEMV (tcq4_gemv.cu) -----------------------------------------------------
 constexpr int GEMV_MAX_M = 16;
+struct GemvPlan;
+bool gemv_uses_prepass(const GemvPlan &plan, const int32_t *perm);
 struct GemvPlan {
     int     grid;            // CTAs (persistent, one per SM)
     int     warps;           // warps per CTA (16 or 32)
     int     depth;           // tiles in flight per warp (ring slots)
     bool    prepass;         // activation stage in its own launch (M * K/256 large), result in the workspace blob
+    bool    prepass_perm;    // the same when the call has a channel permutation (gathers: pays from fewer blocks, M = 1 included)
     size_t  blob_bytes;      // workspace bytes of that result
     size_t  smem_bytes;
     int     maxslots;        // split-K partial slots per n-tile row
