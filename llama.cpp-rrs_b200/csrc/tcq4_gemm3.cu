@@ -859,8 +859,11 @@ static bool g3_get_map(CUtensorMap *out, const G3MapKey &key) {
     return true;
 }
 // the TCQ4 tensor as [NT rows][KT*148 eight-byte words]
-static bool g3_weight_map(CUtensorMap *map, const void *w, int64_t NT, int64_t KT, uint32_t box_words, uint32_t box_rows) {
+bool weight_tensor_map(CUtensorMap_st *map, const void *w, int64_t NT, int64_t KT, uint32_t box_words, uint32_t box_rows) {
     return g3_get_map(map, G3MapKey{w, KT * (TILE_BYTES / 8), NT, KT * TILE_BYTES, box_words, box_rows, 0});
+}
+static bool g3_weight_map(CUtensorMap *map, const void *w, int64_t NT, int64_t KT, uint32_t box_words, uint32_t box_rows) {
+    return weight_tensor_map(map, w, NT, KT, box_words, box_rows);
 }
 // the fp32 output [M][ldc] with boxes of 32 rows x 8 channels
 static bool g3_y_map(CUtensorMap *map, float *y, int64_t M, int64_t N, int64_t ldc) {

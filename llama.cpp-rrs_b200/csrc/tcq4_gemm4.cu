@@ -627,40 +627,16 @@ bool gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, 
     return true;
 }
 
-typedef CUresult (*G4EncodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static G4EncodeTiled g4_encoder() {
-    static G4EncodeTiled fn = [] {
-        void *p = nullptr;
-        cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
-            q != cudaDriverEntryPointSuccess)
-            p = nullptr;
-        return (G4EncodeTiled)p;
-    }();
-    return fn;
-}
-
 cudaError_t launch_gemm4(const Gemm4Seg *segs, int nseg, ActStage st, int64_t M, int64_t K, const Gemm4Plan &plan,
                          float *partials, int *counters, int32_t *dbg_isum, cudaStream_t stream) {
-    G4EncodeTiled enc = g4_encoder();
-    if (!enc || nseg < 1 || nseg > GEMM4_MAX_SEG) return cudaErrorInvalidValue;
+    if (nseg < 1 || nseg > GEMM4_MAX_SEG) return cudaErrorInvalidValue;
     G4Params P;
     memset(&P, 0, sizeof(P));
     const int64_t KT = K / TILE_K;
     int blk = 0;
     for (int i = 0; i <= GEMM4_MAX_SEG; i++) P.blk0[i] = 0x7fffffff;
     for (int i = 0; i < nseg; i++) {
-        const int64_t NT = segs[i].N / TILE_CH;
-        const cuuint64_t gdim[2] = {(cuuint64_t)KT * (TILE_BYTES / 8), (cuuint64_t)NT};
-        const cuuint64_t gstride[1] = {(cuuint64_t)KT * TILE_BYTES};
-        const cuuint32_t box[2] = {TILE_BYTES / 8, 16};
-        const cuuint32_t estr[2] = {1, 1};
-        if (enc(&P.tm[i], CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, const_cast<void *>(segs[i].w), gdim, gstride, box, estr,
-                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
-            return cudaErrorInvalidValue;
+        if (!weight_tensor_map(&P.tm[i], segs[i].w, segs[i].N / TILE_CH, KT, TILE_BYTES / 8, 16)) return cudaErrorInvalidValue;
         P.w[i] = reinterpret_cast<const uint8_t *>(segs[i].w);
         P.y[i] = segs[i].y;
         P.ldc[i] = (long long)segs[i].ldc;

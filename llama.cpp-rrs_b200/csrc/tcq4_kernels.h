@@ -7,6 +7,8 @@
 
 #include "tcq4_common.cuh"
 
+struct CUtensorMap_st;      // <cuda.h>
+
 namespace tcq4 {
 
 // ---- K1: activation stage (tcq4_act.cu) -------------------------------------------------------
@@ -144,7 +146,10 @@ cudaError_t gemm3_read_prof(long long *host_out, size_t bytes);           // PRO
 cudaError_t launch_gemm3(const Gemm3Seg *segs, int nseg, ActStage st, int64_t M, int64_t K, const Gemm3Plan &plan,
                          int32_t *dbg_isum, cudaStream_t stream, const float *res = nullptr, const float *bias = nullptr);
 
-// ---- K2c: batched-decode GEMM, 17 <= M <= 64 (tcq4_gemm4.cu) -----------------------------------------------------
+// cached cuTensorMapEncodeTiled of a TCQ4 tensor seen as [NT rows][KT * 148 eight-byte words] (tcq4_gemm3.cu); box in words x rows
+bool weight_tensor_map(::CUtensorMap_st *map, const void *w, int64_t NT, int64_t KT, uint32_t box_words, uint32_t box_rows);
+
+// ---- K2c: batched-decode GEMM, 9 <= M <= 64 (tcq4_gemm4.cu) -----------------------------------------------------
 constexpr int GEMM4_MAX_PARTS = 8;
 constexpr int GEMM4_MAX_CTAS = 160;        // bound of blocks * parts (workspace sizing is device independent)
 constexpr int GEMM4_MAX_SEG = 4;           // matrices of a fan-out group served by one launch

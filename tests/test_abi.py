@@ -114,3 +114,18 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 txt = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "pyoracle" not in txt and "liboracle" not in txt and "tcq4_oracle" not in txt, f
+
+
+def test_integration_shim_compiles_against_the_forks_headers():
+    """INTEGRATION.md sections 2-4 (the shim that replaces ggml_cuda_rrs_mul_mat, the supports_op case, the registry names)
+    as a translation unit against the fork's own ggml.h and ggml-cuda/common.cuh; also pins GGML_TYPE_TCQ4_K32 == 42.  Only
+    where /root/reference exists (this container); the shim text in INTEGRATION.md must be the TU's text."""
+    import subprocess
+    if not os.path.isdir("/root/reference/ggml/src/ggml-cuda"):
+        pytest.skip("no reference tree on this machine")
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "shimcheck"], stdout=subprocess.DEVNULL)
+    assert os.path.exists(os.path.join(ROOT, "oracle", "_ref", "obj", "shim_check.o"))
+    tu = open(os.path.join(ROOT, "oracle", "shim_check.cu")).read()
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    body = tu[tu.index("static tcq4_tensor_view tcq4_view"):tu.index("// the MUL_MAT case of")].strip()
+    assert body in doc, "INTEGRATION.md section 2 and oracle/shim_check.cu have drifted apart"
