@@ -196,6 +196,12 @@ TCQ4_B200_API int tcq4_b200_mul_mat_host(const void *w_tiles_dev, const float *x
  * Pinned host memory is needed for the copies to be asynchronous.  Not capturable (it owns its streams). */
 TCQ4_B200_API int tcq4_b200_mul_mat_host_async(const void *w_tiles_dev, const float *x_host, float *y_host, int64_t M,
                                                int64_t N, int64_t K, const int32_t *d_perm);
+/* The same for a fan-out group (n <= 8 consecutive MUL_MAT nodes that share src1: Q/K/V, gate/up): x crosses PCIe once for the
+ * group, y_host[i] = F32 [M][N[i]] comes back one copy per matrix.  Uses the device arena for scratch (tcq4_b200_reserve
+ * is called for the group's shape); same two-deep pipeline and the same tcq4_b200_host_sync. */
+TCQ4_B200_API int tcq4_b200_mul_mat_fanout_host_async(int n, const void *const *w_tiles_dev, const int64_t *N,
+                                                      float *const *y_host, const float *x_host, int64_t M, int64_t K,
+                                                      const int32_t *d_perm);
 TCQ4_B200_API int tcq4_b200_host_sync(void);
 
 /* Stand-alone activation stage.  Replaces tcq4_rrs_fwht_quantize_tc / tcq4_rrs_perm_fwht_quantize_tc

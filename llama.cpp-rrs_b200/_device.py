@@ -15,7 +15,7 @@ import torch
 from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
                ACT_BLOCK_BYTES, TensorView, _check, quantize_size, shard_range, tile_bytes, workspace_size)
 
-__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "ggml_mul_mat_fanout", "GgmlGraph", "mul_mat_add", "mul_mat_static", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "PeerBarrier", "mul_mat_host", "mul_mat_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
+__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "ggml_mul_mat_fanout", "GgmlGraph", "mul_mat_add", "mul_mat_static", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "PeerBarrier", "mul_mat_host", "mul_mat_host_async", "mul_mat_fanout_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
            "ggml_supports_op", "ShardedWeight", "random_tiles", "quantize_tiles", "get_rows", "ggml_get_rows"]
 
@@ -181,6 +181,22 @@ def mul_mat_host_async(w_tiles: torch.Tensor, x_host: torch.Tensor, y_host: torc
     M, K = x_host.shape
     pp = perm.data_ptr() if perm is not None else 0
     _check(LIB.tcq4_b200_mul_mat_host_async(w_tiles.data_ptr(), x_host.data_ptr(), y_host.data_ptr(), M, N, K, pp))
+
+
+def mul_mat_fanout_host_async(w_tiles: list, x_host: torch.Tensor, y_hosts: list, Ns: list,
+                              perm: torch.Tensor | None = None) -> None:
+    """Queue a fan-out group (matrices that share x: Q/K/V, gate/up) on the host pipeline: x crosses PCIe once."""
+    for w in w_tiles:
+        _req_cuda(w, torch.uint8, "w_tiles")
+    if x_host.is_cuda or x_host.dtype != torch.float32 or any(y.is_cuda or y.dtype != torch.float32 for y in y_hosts):
+        raise ValueError("x_host / y_hosts must be float32 CPU tensors (pinned for asynchronous copies)")
+    M, K = x_host.shape
+    n = len(w_tiles)
+    wp = (C.c_void_p * n)(*[w.data_ptr() for w in w_tiles])
+    yp = (C.c_void_p * n)(*[y.data_ptr() for y in y_hosts])
+    Np = (C.c_int64 * n)(*Ns)
+    pp = perm.data_ptr() if perm is not None else 0
+    _check(LIB.tcq4_b200_mul_mat_fanout_host_async(n, wp, Np, yp, x_host.data_ptr(), M, K, pp))
 
 
 def host_sync() -> None:

@@ -193,7 +193,8 @@ tcq4::YOut single_out(float *y, int64_t N) {
 // that share x.  What must start at zero -- the outputs when blocks are cut in two (red.add), the arrival counters when
 // they are cut in K parts -- is cleared by K1 itself (strided outputs row by row), or by a small kernel when K1 does not run.
 int run_gemm4_group(DevInfo *d, const tcq4::Gemm4Seg *segs, int nseg, const float *x, const int32_t *perm, int64_t M, int64_t K,
-                    uint8_t *wsb, const WsLayout &L, bool reuse_act, int32_t *dbg_isum, cudaStream_t stream, int *launches) {
+                    uint8_t *wsb, const WsLayout &L, bool reuse_act, int32_t *dbg_isum, cudaStream_t stream, int *launches,
+                    cudaEvent_t after_act = nullptr) {
     int64_t Ns[tcq4::GEMM4_MAX_SEG];
     for (int i = 0; i < nseg; i++) Ns[i] = segs[i].N;
     tcq4::Gemm4Plan g4;
@@ -236,6 +237,7 @@ int run_gemm4_group(DevInfo *d, const tcq4::Gemm4Seg *segs, int nseg, const floa
         if (e != cudaSuccess) return cuda_fail(e, "output clear launch");
         (*launches)++;
     }
+    if (after_act) cudaEventRecord(after_act, stream);      // profile tap: activation stage | GEMM
     e = tcq4::launch_gemm4(segs, nseg, st, M, K, g4, reinterpret_cast<float *>(wsb + L.partial_off),
                            reinterpret_cast<int *>(wsb + L.ticket_off), dbg_isum, stream);
     if (e != cudaSuccess) return cuda_fail(e, "gemm4 launch");
@@ -321,13 +323,11 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
     if (k == TCQ4_KERNEL_GEMM4) {
         // batched decode: nibble staging (K1 MODE_NIB), weights widened into TMEM, stream-K / K parts
         const bool prof = g_prof.on && g_prof.n < g_prof.cap;
-        if (prof) {
-            cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
-            cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
-        }
+        if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
         const tcq4::Gemm4Seg sg{w, y, N, yo.ldc};
         int launches = 0;
-        const int rc = run_gemm4_group(d, &sg, 1, x, perm, M, K, wsb, L, reuse_act, dbg_isum, stream, &launches);
+        const int rc = run_gemm4_group(d, &sg, 1, x, perm, M, K, wsb, L, reuse_act, dbg_isum, stream, &launches,
+                                       prof ? g_prof.ev[3 * g_prof.n + 1] : nullptr);
         if (rc != TCQ4_OK) return rc;
         if (act_done) *act_done = true;
         if (prof) {
@@ -719,16 +719,14 @@ int tcq4_b200_mul_mat_fanout_ld(int n, const void *const *w_tiles, const int64_t
         const WsLayout L = ws_layout(M, Nmax, K);
         uint8_t *wsb = reinterpret_cast<uint8_t *>(d->arena);
         const bool prof = g_prof.on && g_prof.n < g_prof.cap;
-        if (prof) {
-            cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
-            cudaEventRecord(g_prof.ev[3 * g_prof.n + 1], stream);
-        }
+        if (prof) cudaEventRecord(g_prof.ev[3 * g_prof.n + 0], stream);
         int launches = 0;
         for (int i0 = 0; i0 < n; i0 += tcq4::GEMM4_MAX_SEG) {
             const int ns = std::min(tcq4::GEMM4_MAX_SEG, n - i0);
             tcq4::Gemm4Seg sg[tcq4::GEMM4_MAX_SEG];
             for (int i = 0; i < ns; i++) sg[i] = tcq4::Gemm4Seg{w_tiles[i0 + i], ys[i0 + i], Ns[i0 + i], ld[i0 + i]};
-            const int rc = run_gemm4_group(d, sg, ns, x, d_perm, M, K, wsb, L, i0 > 0, nullptr, stream, &launches);
+            const int rc = run_gemm4_group(d, sg, ns, x, d_perm, M, K, wsb, L, i0 > 0, nullptr, stream, &launches,
+                                           (prof && i0 == 0) ? g_prof.ev[3 * g_prof.n + 1] : nullptr);
             if (rc != TCQ4_OK) return rc;
         }
         if (prof) {
@@ -1122,6 +1120,65 @@ int tcq4_b200_mul_mat_host_async(const void *w_tiles_dev, const float *x_host, f
     cudaStreamWaitEvent(p.s_out, p.cmp_done[slot], 0);
     if ((e = cudaMemcpyAsync(y_host, p.hy[slot], yb, cudaMemcpyDeviceToHost, p.s_out)) != cudaSuccess)
         return cuda_fail(e, "D2H copy");
+    cudaEventRecord(p.out_done[slot], p.s_out);
+    p.n++;
+    return TCQ4_OK;
+}
+
+// The same pipeline for a fan-out group (consecutive MUL_MAT nodes that share src1: Q/K/V, gate/up): x crosses PCIe ONCE for
+// the group, the outputs come back one copy per matrix.
+int tcq4_b200_mul_mat_fanout_host_async(int n, const void *const *w_tiles_dev, const int64_t *Ns, float *const *y_host,
+                                        const float *x_host, int64_t M, int64_t K, const int32_t *d_perm) {
+    if (n < 1 || n > 8 || !w_tiles_dev || !Ns || !y_host || !x_host) {
+        set_err("mul_mat_fanout_host_async: 1..8 matrices, non-null tables and host pointers");
+        return TCQ4_ERR_ARG;
+    }
+    int64_t Nsum = 0, Nmax = 0;
+    for (int i = 0; i < n; i++) {
+        if (!shape_ok(M, Ns[i], K) || !y_host[i]) {
+            set_err("mul_mat_fanout_host_async: bad shape or null host pointer of matrix %d", i);
+            return TCQ4_ERR_SHAPE;
+        }
+        Nsum += Ns[i];
+        Nmax = std::max(Nmax, Ns[i]);
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    HostPipe &p = g_pipe[dev];
+    cudaError_t e = pipe_init(p);
+    if (e != cudaSuccess) return cuda_fail(e, "host pipeline setup");
+    const size_t xb = (size_t)M * K * 4, yb = (size_t)M * Nsum * 4;
+    const int slot = (int)(p.n & 1);
+    if ((e = pipe_grow(p, &p.hx[slot], &p.hx_bytes[slot], xb)) != cudaSuccess) return cuda_fail(e, "x staging cudaMalloc");
+    if ((e = pipe_grow(p, &p.hy[slot], &p.hy_bytes[slot], yb)) != cudaSuccess) return cuda_fail(e, "y staging cudaMalloc");
+    status = tcq4_b200_reserve(M, Nmax, K);      // the fan-out's scratch is the device arena (grown here, outside the streams' work)
+    if (status != TCQ4_OK) return status;
+    if (p.n >= 2) {
+        cudaStreamWaitEvent(p.s_in, p.cmp_done[slot], 0);      // the kernels of call n-2 have read this x slot
+        cudaStreamWaitEvent(p.s_cmp, p.out_done[slot], 0);     // the D2H copies of call n-2 have drained this y slot
+    }
+    if ((e = cudaMemcpyAsync(p.hx[slot], x_host, xb, cudaMemcpyHostToDevice, p.s_in)) != cudaSuccess)
+        return cuda_fail(e, "H2D copy");
+    cudaEventRecord(p.in_done[slot], p.s_in);
+    cudaStreamWaitEvent(p.s_cmp, p.in_done[slot], 0);
+    float *ys[8];
+    {
+        float *yd = reinterpret_cast<float *>(p.hy[slot]);
+        for (int i = 0; i < n; i++) {
+            ys[i] = yd;
+            yd += (size_t)M * Ns[i];
+        }
+    }
+    status = tcq4_b200_mul_mat_fanout(n, w_tiles_dev, Ns, ys, reinterpret_cast<const float *>(p.hx[slot]), M, K, d_perm, p.s_cmp);
+    if (status != TCQ4_OK) return status;
+    cudaEventRecord(p.cmp_done[slot], p.s_cmp);
+    cudaStreamWaitEvent(p.s_out, p.cmp_done[slot], 0);
+    for (int i = 0; i < n; i++)
+        if ((e = cudaMemcpyAsync(y_host[i], ys[i], (size_t)M * Ns[i] * 4, cudaMemcpyDeviceToHost, p.s_out)) != cudaSuccess)
+            return cuda_fail(e, "D2H copy");
     cudaEventRecord(p.out_done[slot], p.s_out);
     p.n++;
     return TCQ4_OK;

@@ -21,7 +21,7 @@
 //     the SMs the same line is cut at the blocks' halves (two addends again).  (An ordered fix-up through workspace slots and
 //     flags -- any number of parts per block -- was built and measured: every hand-over is two dependent L2 round trips under
 //     load, 5-20 us per launch)
-// Warps: 0 weight producer (TMA, HBM), 1 MMA issuer, 2 token producer (bulk copies, L2), 3 idle, 4-19 widening (lane quarter =
+// Warps: 0 weight producer (TMA, HBM), 1 MMA issuer, 2 token producer (bulk copies, L2), 3 publisher (scales for the epilogue), 4-19 widening (lane quarter =
 // warp % 4, k-quarter = (warp - 4) / 4), 20-23 epilogue.  Rings: 6 weight stages (114 KB in flight: a weight stream is bound by
 // latency x bandwidth per SM), 3 token stages, 2 operand stages (A in TMEM, B in shared memory), 2 accumulator stages.
 //
@@ -215,11 +215,11 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
     if (threadIdx.x == 0) {
         for (int i = 0; i < G4_W_STAGES; i++) {
             mbar_init(&wfull[i], 1);
-            mbar_init(&wempty[i], G4_CW_WARPS / 2);      // one team
+            mbar_init(&wempty[i], G4_CW_WARPS / 2 + 1);      // one team + the publisher
         }
         for (int i = 0; i < G4_A_STAGES; i++) {
             mbar_init(&afull[i], 1);
-            mbar_init(&aempty[i], G4_CW_WARPS / 2);
+            mbar_init(&aempty[i], G4_CW_WARPS / 2 + 1);
         }
         for (int i = 0; i < 2; i++) {
             mbar_init(&opfull[i], G4_CW_WARPS / 2);
@@ -227,7 +227,7 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
             mbar_init(&accfull[i], 1);
             mbar_init(&accempty[i], G4_EPI_WARPS);
         }
-        for (int i = 0; i < G4_RING; i++) mbar_init(&snfull[i], 4 + (MT + 31) / 32);      // S: 4 warps, a7/127: NCH warps
+        for (int i = 0; i < G4_RING; i++) mbar_init(&snfull[i], 1);      // the publisher warp
         fence_mbar_init();
     }
     if (warp == 0 && lane < P.nseg) asm volatile("prefetch.tensormap [%0];" ::"l"(&P.tm[lane]) : "memory");
@@ -370,24 +370,6 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
                     const int un = tt + 256 * j, a_g = un / MT, a_row = un - a_g * MT;
                     wa[j] = *reinterpret_cast<const uint4 *>(sta + a_g * (MT * 16) + a_row * 16);
                 }
-                const int ring = gk & (G4_RING - 1);
-                if (hf == 0) {      // per-channel super-scale and zero-point flag of this k-tile, for the epilogue
-                    const uint8_t *md = stg + (ch >> 3) * TILE_BYTES;
-                    sS[ring * G4_CH + ch] = __half2float(*reinterpret_cast<const __half *>(md + TILE_OFF_S + 2 * (ch & 7)));
-                    const float zv = __half2float(*reinterpret_cast<const __half *>(md + TILE_OFF_Z + 2 * (ch & 7)));
-                    const uint2 zc = *reinterpret_cast<const uint2 *>(md + TILE_OFF_ZC + (ch & 7) * 8);
-                    const int anyz = __any_sync(0xffffffffu, (zv != 0.0f) && ((zc.x | zc.y) != 0u));
-                    __syncwarp();
-                    if (lane == 0) {
-                        sZf[ring * 4 + (cw & 3)] = anyz;
-                        mbar_arrive(&snfull[ring]);
-                    }
-                } else if ((cw & 3) < NCH) {      // the row factors a7 / 127 of the tokens
-                    const int t = (cw & 3) * 32 + lane;
-                    sRm[ring * G4_MAXMT + t] = *reinterpret_cast<const float *>(sta + 8 * MT * 16 + t * 4) * (1.0f / 127.0f);
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&snfull[ring]);
-                }
                 G4_CSTAMP(7);
                 if (gk > 1) {
                     g4_wait(&opfree[team], (uint32_t)(((gk >> 1) - 1) & 1));
@@ -435,7 +417,49 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
             }
         }
     } else if (warp < G4_CW_WARP0) {
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 64;" ::: "memory");      // warp 3: idle
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 64;" ::: "memory");
+        // ===================== publisher (warp 3): what the epilogue needs of a k-tile, out of the rings =====================
+        // per-channel super-scales S, the zero-point flag, the tokens' row factors a7 / 127 -- 8 rings slots ahead of the epilogue,
+        // so that the raw stages can be recycled as soon as the widening team is done with them
+        int gk = 0;
+        G4_FOR_SEGMENTS {
+            (void)nb;
+            for (int kt = kt0; kt < kt1; kt++, gk++) {
+                const int s = gk % G4_W_STAGES, as = gk % G4_A_STAGES, ring = gk & (G4_RING - 1);
+                g4_wait(&wfull[s], (uint32_t)((gk / G4_W_STAGES) & 1));
+                g4_wait(&afull[as], (uint32_t)((gk / G4_A_STAGES) & 1));
+                const uint8_t *stg = sRaw + s * G4_W_BYTES;
+                const uint8_t *sta = sAct + as * G4_A_BYTES;
+                int zf = 0;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int ch = j * 32 + lane;
+                    const uint8_t *md = stg + (ch >> 3) * TILE_BYTES;
+                    sS[ring * G4_CH + ch] = __half2float(*reinterpret_cast<const __half *>(md + TILE_OFF_S + 2 * (ch & 7)));
+                    const float zv = __half2float(*reinterpret_cast<const __half *>(md + TILE_OFF_Z + 2 * (ch & 7)));
+                    const uint2 zc = *reinterpret_cast<const uint2 *>(md + TILE_OFF_ZC + (ch & 7) * 8);
+                    zf |= (zv != 0.0f) && ((zc.x | zc.y) != 0u);
+                }
+#pragma unroll
+                for (int j = 0; j < NCH; j++) {
+                    const int t = j * 32 + lane;
+                    sRm[ring * G4_MAXMT + t] = *reinterpret_cast<const float *>(sta + 8 * MT * 16 + t * 4) * (1.0f / 127.0f);
+                }
+                const int anyz = __any_sync(0xffffffffu, zf);
+                // (the ring slot is free: the epilogue finished k-tile gk - 8 before the MMA of gk - 6 could start, and that
+                //  MMA's commit is what let the team widen k-tile gk - 4 ... the raw stage of gk itself was filled after that)
+                __syncwarp();
+                if (lane == 0) {
+                    sZf[ring * 4] = anyz;
+                    sZf[ring * 4 + 1] = 0;
+                    sZf[ring * 4 + 2] = 0;
+                    sZf[ring * 4 + 3] = 0;
+                    mbar_arrive(&snfull[ring]);
+                    mbar_arrive(&wempty[s]);
+                    mbar_arrive(&aempty[as]);
+                }
+            }
+        }
     } else {
         asm volatile("setmaxnreg.inc.sync.aligned.u32 152;" ::: "memory");
         // ===================== epilogue: thread = channel =====================

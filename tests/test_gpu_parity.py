@@ -474,6 +474,28 @@ def test_pipelined_host_entry_matches_device_entry(t4, orc):
             assert torch.equal(yh, t4.mul_mat(tiles, xh.cuda(), N).cpu())
 
 
+@pytest.mark.parametrize("M", [1, 12, 40, 300])
+def test_pipelined_host_fanout_matches_device_fanout(t4, orc, M):
+    """tcq4_b200_mul_mat_fanout_host_async: a group of matrices that share x, x copied once, interleaved with single-matrix
+    host calls on the same two-deep pipeline; results equal the device fan-out's bits and the oracle."""
+    rng = np.random.default_rng(152 + M)
+    K, Ns = 512, [512, 128, 128]
+    tl = [_dev(orc.quantize_tiles(make_weights(rng, n, K))) for n in Ns]
+    xh = torch.from_numpy(make_acts(rng, M, K)).pin_memory()
+    yhs = [torch.full((M, n), float("nan"), dtype=torch.float32).pin_memory() for n in Ns]
+    single = torch.full((M, Ns[0]), float("nan"), dtype=torch.float32).pin_memory()
+    for rep in range(3):
+        t4.mul_mat_fanout_host_async(tl, xh, yhs, Ns)
+        t4.mul_mat_host_async(tl[0], xh, single, Ns[0])
+    t4.host_sync()
+    want = t4.Fanout(tl, Ns, K)(xh.cuda())
+    torch.cuda.synchronize()
+    for y, w, t, n in zip(yhs, want, tl, Ns):
+        assert torch.equal(y, w.cpu())
+        assert nmse(y.numpy(), orc.mul_mat(t.cpu().numpy(), xh.numpy(), n)["C"]) <= FP32_NMSE_TIGHT
+    assert nmse(single.numpy(), yhs[0].numpy()) <= 1e-12
+
+
 @pytest.mark.parametrize("M", [1, 3, 16, 64, 300])
 def test_peer_destinations_strided_window(t4, orc, M):
     """tcq4_b200_mul_mat_peers: the shard's columns land at column col0 of EVERY destination matrix (here two
