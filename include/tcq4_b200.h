@@ -147,10 +147,13 @@ TCQ4_B200_API int tcq4_b200_mul_mat_fanout_ld(int n, const void *const *w_tiles,
  *         or n_used (one row per token and slot: down)                       -- ggml src1 [K, ne11, n_tokens]
  *   ids : device int32, ids[t * ids_stride + s] = expert of slot s of token t  -- ggml ids [n_used, n_tokens]
  *   y   : F32 [n_tokens][n_used][N] contiguous:  y[t][s][:] = W[ids[t][s]] * x[t][s % x_slots][:]
- * n_tokens <= 8 runs without any host round trip (the kernel reads the ids on the device, one launch per token;
- * capturable in a CUDA graph; an id outside [0, n_expert) sets *err_flag -- device int, may be NULL -- and computes
- * with expert 0).  More tokens: the ids are read on the host like the reference (synchronises the stream; a bad id
- * returns TCQ4_ERR_ARG). */
+ * No host round trip for any n_tokens, capturable in a CUDA graph (warm the scratch arena up once outside the capture).
+ * n_tokens <= 8: the GEMV reads the ids on the device, one launch per token; an id outside [0, n_expert) sets *err_flag --
+ * device int, may be NULL -- and computes with expert 0.  More tokens: three launches -- a routing kernel bins the rows by
+ * expert into chunks of <= 64 rows, the activation stage reads x through the row map, ONE grouped launch of the batched-decode
+ * GEMM serves every (chunk, channel block) pair and scatters the rows into y; a bad id sets *err_flag and the row is skipped.
+ * TCQ4_MOE_HOSTSORT=1 in the environment selects the reference's scheme instead (ids to the host: synchronises the stream,
+ * not capturable, a bad id returns TCQ4_ERR_ARG). */
 TCQ4_B200_API int tcq4_b200_mul_mat_id(const void *w_experts, int64_t n_expert, size_t expert_stride_bytes,
                                        const float *x, int64_t x_slots, const int32_t *ids, int64_t ids_stride,
                                        int64_t n_used, int64_t n_tokens, float *y, int64_t N, int64_t K,

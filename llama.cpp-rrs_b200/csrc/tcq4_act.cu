@@ -23,7 +23,8 @@ enum { MODE_REF = 0, MODE_STAGE = 1, MODE_NIB = 2 };
 template <int MODE>
 __global__ void __launch_bounds__(ACT_WARPS_PER_CTA * 32)
 tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ perm, int M, int K,
-                      ActBlockTC *__restrict__ out_ref, ActStage st, const __grid_constant__ ZeroList zl) {
+                      ActBlockTC *__restrict__ out_ref, ActStage st, const __grid_constant__ ZeroList zl,
+                      const int32_t *__restrict__ row_map, const int *__restrict__ n_chunks) {
     const int lane = threadIdx.x & 31;
     const int KT = K / TILE_K;
     const long long nblocks = (long long)M * KT;
@@ -47,13 +48,25 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
         }
     }
 
-    for (long long b = warp0; b < nblocks; b += nwarps) {
+    // MUL_MAT_ID (device-routed, tcq4_moe.cu): m is a VIRTUAL row -- 64-row chunks of one expert each -- whose source row of x is
+    // row_map[m] (-1: empty slot of a chunk); only the first *n_chunks chunks exist
+    long long nblocks_rt = nblocks;
+    if (MODE == MODE_NIB && row_map != nullptr) {
+        const long long lim = (long long)__ldcg(n_chunks) * 64 * KT;
+        if (lim < nblocks_rt) nblocks_rt = lim;
+    }
+    for (long long b = warp0; b < nblocks_rt; b += nwarps) {
         const int m = (int)(b / KT);
         const int kt = (int)(b - (long long)m * KT);
+        long long m_src = m;
+        if (MODE == MODE_NIB && row_map != nullptr) {
+            m_src = __ldcg(row_map + m);
+            if (m_src < 0) continue;
+        }
         float v[8];
         // ld.global.cg: every element is read once, and under programmatic stream serialization a stale L1 line of x
         // could survive from an overlapping predecessor
-        rrs_load_block_cg(x + (size_t)m * K, perm, kt, lane, v);
+        rrs_load_block_cg(x + (size_t)m_src * K, perm, kt, lane, v);
         const ActQuantT a = rrs_quantize_block_t<true>(v, lane, scratch);
         const uint2 e = rrs_codes_layout_a(a, lane, scratch);        // byte r = code of element lane*8 + r
         int gs = 0;                                                  // lane g < 8 keeps the sum of group g
@@ -107,7 +120,8 @@ static int act_grid(int64_t nblocks, int num_sms) {
 
 template <typename Kern>
 static cudaError_t launch_act(Kern kern, int grid, cudaStream_t stream, const float *x, const int32_t *perm, int M, int K,
-                              ActBlockTC *out_ref, ActStage st, int which = 0, const ZeroList *zlp = nullptr) {
+                              ActBlockTC *out_ref, ActStage st, int which = 0, const ZeroList *zlp = nullptr,
+                              const int32_t *row_map = nullptr, const int *n_chunks = nullptr) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(ACT_WARPS_PER_CTA * 32);
@@ -132,7 +146,7 @@ static cudaError_t launch_act(Kern kern, int grid, cudaStream_t stream, const fl
     }
     ZeroList zl{};
     if (zlp) zl = *zlp;
-    return cudaLaunchKernelEx(&cfg, kern, x, perm, M, K, out_ref, st, zl);
+    return cudaLaunchKernelEx(&cfg, kern, x, perm, M, K, out_ref, st, zl, row_map, n_chunks);
 }
 
 cudaError_t launch_act_quant_ref(const float *x, const int32_t *perm, int64_t M, int64_t K, void *out_blocks,
@@ -158,6 +172,14 @@ cudaError_t launch_act_quant_nib_zl(const float *x, const int32_t *perm, int64_t
     if (nblocks == 0) return cudaSuccess;
     return launch_act(tcq4_act_quant_kernel<MODE_NIB>, act_grid(nblocks, num_sms), stream, x, perm, (int)M, (int)K,
                       (ActBlockTC *)nullptr, st, 2, zl);
+}
+// MUL_MAT_ID: max_rows virtual rows (64 per chunk), of which the first *n_chunks * 64 exist; row r reads x[row_map[r]]
+cudaError_t launch_act_quant_nib_rows(const float *x, const int32_t *perm, int64_t max_rows, int64_t K, ActStage st, int num_sms,
+                                      cudaStream_t stream, const int32_t *row_map, const int *n_chunks) {
+    const int64_t nblocks = max_rows * (K / TILE_K);
+    if (nblocks == 0) return cudaSuccess;
+    return launch_act(tcq4_act_quant_kernel<MODE_NIB>, act_grid(nblocks, num_sms), stream, x, perm, (int)max_rows, (int)K,
+                      (ActBlockTC *)nullptr, st, 2, nullptr, row_map, n_chunks);
 }
 cudaError_t launch_act_quant_nib(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st, int num_sms,
                                  cudaStream_t stream, float *zero_y, int64_t zero_floats) {

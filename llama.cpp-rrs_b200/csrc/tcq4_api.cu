@@ -861,9 +861,49 @@ int tcq4_b200_mul_mat_id(const void *w_experts, int64_t n_expert, size_t expert_
         return TCQ4_OK;
     }
 
+    // ---- more tokens: routing on the DEVICE, three launches, no host round trip, capturable (round 2) ----------------------
+    //  (1) one CTA bins the rows by expert into chunks of <= 64 rows at 64-aligned virtual rows (tcq4_moe_route_kernel);
+    //  (2) K1 quantises the virtual rows straight from x through the row map (no gathered copy of x);
+    //  (3) the batched-decode GEMM runs over (chunk, 128-channel block) pairs -- a chunk's tokens are its N, the expert's tiles
+    //      come through a 3-D tensor map -- and scatters every token's row to its place in y.
+    static const bool host_sort = getenv("TCQ4_MOE_HOSTSORT") != nullptr;      // the reference's scheme (below), for comparison
+    if (!host_sort && (size_t)(2 * n_expert + 1) * sizeof(int) <= 48 * 1024 && d->smem_optin >= 227 * 1024 - 4096) {
+        const int64_t max_chunks = n_expert + (R + 63) / 64;
+        const int64_t vmax = max_chunks * 64;
+        const WsLayout L = ws_layout(vmax, N, K);
+        const size_t map_off = (size_t)tcq4::round_up((int64_t)L.total, 256);
+        const size_t src_off = map_off + 256;                                               // [n_chunks]
+        const size_t dst_off = src_off + (size_t)tcq4::round_up(vmax * 4, 256);
+        const size_t ce_off = dst_off + (size_t)tcq4::round_up(vmax * 4, 256);
+        const size_t pos_off = ce_off + (size_t)tcq4::round_up(max_chunks * 4, 256);
+        const size_t total = pos_off + (size_t)tcq4::round_up(R * 4, 256);
+        status = arena_ensure(d, total, stream);
+        if (status != TCQ4_OK) return status;
+        uint8_t *base = reinterpret_cast<uint8_t *>(d->arena);
+        int *n_chunks = reinterpret_cast<int *>(base + map_off);
+        int32_t *src_map = reinterpret_cast<int32_t *>(base + src_off), *dst_map = reinterpret_cast<int32_t *>(base + dst_off);
+        int *chunk_expert = reinterpret_cast<int *>(base + ce_off);
+        int32_t *pos_tmp = reinterpret_cast<int32_t *>(base + pos_off);
+        cudaError_t e = tcq4::launch_moe_route(ids, n_tokens == 1 ? n_used : ids_stride, n_used, n_tokens, n_expert, x_slots,
+                                               (int)max_chunks, n_chunks, chunk_expert, src_map, dst_map, pos_tmp, err_flag, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "mul_mat_id: routing launch");
+        tcq4::ActStage st;
+        st.codes = reinterpret_cast<int8_t *>(base + L.codes_off);
+        st.a7 = reinterpret_cast<float *>(base + L.a7_off);
+        st.sumq = reinterpret_cast<int16_t *>(base + L.sumq_off);
+        st.a7t = reinterpret_cast<float *>(base + L.a7t_off);
+        e = tcq4::launch_act_quant_nib_rows(x, d_perm, vmax, K, st, d->num_sms, stream, src_map, n_chunks);
+        if (e != cudaSuccess) return cuda_fail(e, "mul_mat_id: activation kernel launch");
+        e = tcq4::launch_gemm4_id(w_experts, n_expert, expert_stride_bytes, st, y, N, K, n_chunks, chunk_expert, dst_map,
+                                  (int)max_chunks, d->num_sms, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "mul_mat_id: grouped GEMM launch");
+        g_launches.fetch_add(3, std::memory_order_relaxed);
+        return TCQ4_OK;
+    }
+
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     if (stream != nullptr && cudaStreamIsCapturing(stream, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone) {
-        set_err("mul_mat_id with more than one token reads the ids on the host (as ggml_cuda_mul_mat_id does): not capturable");
+        set_err("mul_mat_id (host-sorted path) reads the ids on the host (as ggml_cuda_mul_mat_id does): not capturable");
         return TCQ4_ERR_ARG;
     }
     // ---- ids to the host, counting sort by expert (ggml-cuda.cu:2349-2368) -----------------------------------------

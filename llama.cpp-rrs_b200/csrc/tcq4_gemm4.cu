@@ -92,6 +92,13 @@ __device__ __forceinline__ void g4_tma_2d(void *dst_smem, const CUtensorMap *map
         "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
         : "memory");
 }
+__device__ __forceinline__ void g4_tma_3d(void *dst_smem, const CUtensorMap *map, int c0, int c1, int c2, uint64_t *bar, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4, %5}], "
+        "[%2], %6;" ::"r"(smem_u32(dst_smem)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "l"(policy)
+        : "memory");
+}
 // D[tmem] (+)= A[tmem] * B[smem], fp16 x fp16 -> fp32, one CTA
 __device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t b_hi, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -187,6 +194,14 @@ struct G4Params {
     int N[GEMM4_MAX_SEG];
     int blk0[GEMM4_MAX_SEG + 1];      // first block of each segment (unused: INT_MAX)
     int nseg;
+    // MUL_MAT_ID, device-routed (tcq4_moe.cu): the line is (chunk, block) pairs -- a chunk = up to 64 rows of one expert at the
+    // 64-aligned virtual rows of K1's units; tm[0] is then a 3-D map [expert][tile row][words], w[0] / N[0] / y[0] describe one
+    // expert's matrix and the [row][N] output
+    const int *id_nchunks;            // null: not this mode
+    const int *id_chunk_expert;
+    const int32_t *id_dst_map;        // virtual row -> row of y (-1: empty)
+    long long id_stride;              // bytes between experts
+    int id_blocks;                    // 128-channel blocks of one expert
 };
 
 // NCH = Mt / 32 (1 or 2)
@@ -243,6 +258,11 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
     // this CTA's range of the blocks * KT line, walked segment by segment (block nb, k-tiles [kt0, kt1)) by every role
     // (mode G4_WHOLE: ranges of whole blocks only -- strided outputs cannot be zeroed by K1)
     const bool whole_blocks = (mode == G4_WHOLE);
+    const bool id_mode = P.id_nchunks != nullptr;
+    if (id_mode) {      // the chunk table comes from the routing kernel two launches ahead: nothing may start before it is there
+        pdl_wait();
+        num_blocks = __ldcg(P.id_nchunks) * P.id_blocks;
+    }
     const long long total_units = (long long)num_blocks * KT;
     const long long lin0 = whole_blocks ? ((long long)num_blocks * blockIdx.x / gridDim.x) * KT : total_units * blockIdx.x / gridDim.x;
     const long long lin1 = whole_blocks ? ((long long)num_blocks * (blockIdx.x + 1) / gridDim.x) * KT : total_units * (blockIdx.x + 1) / gridDim.x;
@@ -259,15 +279,23 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
             const uint64_t pol_w = l2_policy_evict_first();
             int s = 0, u = 0;
             G4_FOR_SEGMENTS {
+                const int sg = (nb >= P.blk0[1]) + (nb >= P.blk0[2]) + (nb >= P.blk0[3]);
+                int row16 = (nb - P.blk0[sg]) * 16, expert = 0;
+                if (id_mode) {
+                    const int c = nb / P.id_blocks;
+                    row16 = (nb - c * P.id_blocks) * 16;
+                    expert = __ldcg(P.id_chunk_expert + c);
+                }
 #pragma unroll 1
                 for (int kt = kt0; kt < kt1; kt++) {
                     if (u > 0) g4_wait(&wempty[s], (uint32_t)((u - 1) & 1));
                     mbar_arrive_expect_tx(&wfull[s], (uint32_t)G4_RAW_W);
-                    const int sg = (nb >= P.blk0[1]) + (nb >= P.blk0[2]) + (nb >= P.blk0[3]);
                     if (G4_EXP(16))      // what-if: the same bytes as one contiguous unit (is the tile layout what bounds the stream?)
                         bulk_g2s(sRaw + s * G4_W_BYTES, P.w[0] + ((size_t)nb * KT + kt) * G4_RAW_W, G4_RAW_W, &wfull[s]);
+                    else if (id_mode)
+                        g4_tma_3d(sRaw + s * G4_W_BYTES, &P.tm[0], kt * (TILE_BYTES / 8), row16, expert, &wfull[s], pol_w);
                     else
-                    g4_tma_2d(sRaw + s * G4_W_BYTES, &P.tm[sg], kt * (TILE_BYTES / 8), (nb - P.blk0[sg]) * 16, &wfull[s], pol_w);
+                    g4_tma_2d(sRaw + s * G4_W_BYTES, &P.tm[sg], kt * (TILE_BYTES / 8), row16, &wfull[s], pol_w);
                     if (++s == G4_W_STAGES) { s = 0; u++; }
                 }
             }
@@ -285,10 +313,14 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
                     if (u > 0) g4_wait(&aempty[s], (uint32_t)((u - 1) & 1));
                     uint8_t *stg = sAct + s * G4_A_BYTES;
                     mbar_arrive_expect_tx(&afull[s], total_tx);
-                    const uint8_t *a_src = reinterpret_cast<const uint8_t *>(st.codes) + (size_t)kt * ACT_NIB_UNIT_BYTES;
+                    // (MUL_MAT_ID: chunk c of the block is half `c & 1` of K1's 128-row unit c / 2)
+                    const int chunk = id_mode ? nb / P.id_blocks : 0;
+                    const size_t unit = (size_t)(chunk >> 1) * KT + kt;
+                    const int row0 = (chunk & 1) * 64;
+                    const uint8_t *a_src = reinterpret_cast<const uint8_t *>(st.codes) + unit * ACT_NIB_UNIT_BYTES + row0 * 16;
 #pragma unroll
                     for (int g = 0; g < 8; g++) bulk_g2s(stg + g * (MT * 16), a_src + g * 2048, MT * 16, &afull[s]);
-                    bulk_g2s(stg + 8 * MT * 16, st.a7t + (size_t)kt * 128, MT * 4, &afull[s]);
+                    bulk_g2s(stg + 8 * MT * 16, st.a7t + unit * 128 + row0, MT * 4, &afull[s]);
                     if (++s == G4_A_STAGES) { s = 0; u++; }
                 }
             }
@@ -471,11 +503,18 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
         int gk = 0;
         G4_FOR_SEGMENTS {
             const int sg = (nb >= P.blk0[1]) + (nb >= P.blk0[2]) + (nb >= P.blk0[3]);
-            const int n = (nb - P.blk0[sg]) * G4_CH + chl;      // channel within its matrix
+            int n = (nb - P.blk0[sg]) * G4_CH + chl;      // channel within its matrix
             const int N = P.N[sg];
             float *__restrict__ y = P.y[sg];
             const long long ldc = P.ldc[sg];
             const uint8_t *__restrict__ w = P.w[sg];
+            int vrow0 = 0;                                  // first (virtual) token row of this segment
+            if (id_mode) {
+                const int c = nb / P.id_blocks;
+                n = (nb - c * P.id_blocks) * G4_CH + chl;
+                w += (size_t)__ldcg(P.id_chunk_expert + c) * P.id_stride;
+                vrow0 = c * 64;
+            }
 #pragma unroll
             for (int i = 0; i < MT / 2; i++) acc2[i] = 0ull;
             for (int kt = kt0; kt < kt1; kt++, gk++) {
@@ -527,8 +566,8 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
                     for (int i = 0; i < MT / 2; i++) {
                         float a, bb;
                         g4_unpack(acc2[i], a, bb);
-                        if (2 * i < M) a += g4_zero_point_term(w, st.sumq, 2 * i, n, kt, KT, st.a7[(size_t)(2 * i) * KT + kt]);
-                        if (2 * i + 1 < M) bb += g4_zero_point_term(w, st.sumq, 2 * i + 1, n, kt, KT, st.a7[(size_t)(2 * i + 1) * KT + kt]);
+                        if (2 * i < M) a += g4_zero_point_term(w, st.sumq, vrow0 + 2 * i, n, kt, KT, st.a7[(size_t)(vrow0 + 2 * i) * KT + kt]);
+                        if (2 * i + 1 < M) bb += g4_zero_point_term(w, st.sumq, vrow0 + 2 * i + 1, n, kt, KT, st.a7[(size_t)(vrow0 + 2 * i + 1) * KT + kt]);
                         acc2[i] = g4_pack(a, bb);
                     }
                 }
@@ -582,6 +621,24 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
                 }
                 continue;
             }
+            if (id_mode) {      // MUL_MAT_ID: token t of the chunk goes to row dst_map[vrow0 + t] of y (-1: an empty slot)
+                if (n < N) {
+#pragma unroll
+                    for (int h = 0; h < MT / 16; h++) {
+                        int drow[16];
+#pragma unroll
+                        for (int i = 0; i < 16; i++) drow[i] = __ldcg(P.id_dst_map + vrow0 + h * 16 + i);
+#pragma unroll
+                        for (int i = 0; i < 8; i++) {
+                            float a, bb;
+                            g4_unpack(acc2[h * 8 + i], a, bb);
+                            if (drow[2 * i] >= 0) y[(size_t)drow[2 * i] * ldc + n] = a;
+                            if (drow[2 * i + 1] >= 0) y[(size_t)drow[2 * i + 1] * ldc + n] = bb;
+                        }
+                    }
+                }
+                continue;
+            }
             // A part of a block (stream-K, K halves) is added to the zeroed output: a block has at most two parts, so the sum does
             // not depend on their order.
             if (n < N) {
@@ -608,6 +665,9 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
 }
 
 // ---- host side ---------------------------------------------------------------------------------------------------
+typedef CUresult (*G4EncodeTiled3)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 bool gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, size_t smem_optin, Gemm4Plan *plan) {
     if (M < 1 || M > G4_MAXMT || (size_t)Gemm4Smem::total > smem_optin || num_sms < 1 || nseg < 1 || nseg > GEMM4_MAX_SEG) return false;
     int64_t blocks = 0;
@@ -694,6 +754,58 @@ cudaError_t launch_gemm4(const Gemm4Seg *segs, int nseg, ActStage st, int64_t M,
     if (dbg_isum)
         return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, true>, P, st, (int)M, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, dbg_isum, exp);
     return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, false>, P, st, (int)M, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, (int32_t *)nullptr, exp);
+}
+
+// MUL_MAT_ID with device-side routing: one launch over (chunk, block) pairs; the chunk count lives on the device, so the grid is
+// sized for the bound and CTAs whose range is empty fall through
+cudaError_t launch_gemm4_id(const void *w_experts, int64_t n_expert, size_t expert_stride_bytes, ActStage st, float *y, int64_t N,
+                            int64_t K, const int *n_chunks, const int *chunk_expert, const int32_t *dst_map, int max_chunks,
+                            int num_sms, cudaStream_t stream) {
+    static G4EncodeTiled3 enc = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (G4EncodeTiled3)p;
+    }();
+    if (!enc) return cudaErrorInvalidValue;
+    G4Params P;
+    memset(&P, 0, sizeof(P));
+    const int64_t KT = K / TILE_K, NT = N / TILE_CH;
+    const cuuint64_t gdim[3] = {(cuuint64_t)KT * (TILE_BYTES / 8), (cuuint64_t)NT, (cuuint64_t)n_expert};
+    const cuuint64_t gstride[2] = {(cuuint64_t)KT * TILE_BYTES, (cuuint64_t)expert_stride_bytes};
+    const cuuint32_t box[3] = {TILE_BYTES / 8, 16, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    if (enc(&P.tm[0], CU_TENSOR_MAP_DATA_TYPE_UINT64, 3, const_cast<void *>(w_experts), gdim, gstride, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return cudaErrorInvalidValue;
+    for (int i = 0; i <= GEMM4_MAX_SEG; i++) P.blk0[i] = 0x7fffffff;
+    P.blk0[0] = 0;
+    P.w[0] = reinterpret_cast<const uint8_t *>(w_experts);
+    P.y[0] = y;
+    P.ldc[0] = (long long)N;
+    P.N[0] = (int)N;
+    P.nseg = 1;
+    P.id_nchunks = n_chunks;
+    P.id_chunk_expert = chunk_expert;
+    P.id_dst_map = dst_map;
+    P.id_stride = (long long)expert_stride_bytes;
+    P.id_blocks = (int)((N + G4_CH - 1) / G4_CH);
+    const long long items = (long long)max_chunks * P.id_blocks;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(items < num_sms ? items : num_sms));
+    cfg.blockDim = dim3(G4_THREADS);
+    cfg.dynamicSmemBytes = Gemm4Smem::total;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    static const bool no_pdl = getenv("TCQ4_NO_PDL") != nullptr;
+    cfg.numAttrs = no_pdl ? 0 : 1;
+    return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, false>, P, st, 64, (int)K, 0, (int)G4_WHOLE, 1, (float *)nullptr, (int *)nullptr,
+                              (int32_t *)nullptr, 0);
 }
 
 cudaError_t gemm4_read_prof(long long *host_out, size_t bytes) {

@@ -31,6 +31,9 @@ struct ZeroList {
 cudaError_t launch_act_quant_nib_zl(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st, int num_sms,
                                     cudaStream_t stream, const ZeroList *zl);
 cudaError_t launch_zero_list(const ZeroList &zl, int num_sms, cudaStream_t stream);
+// MUL_MAT_ID (device-routed): max_rows virtual rows, the first *n_chunks * 64 exist, virtual row r reads x[row_map[r]] (-1: skip)
+cudaError_t launch_act_quant_nib_rows(const float *x, const int32_t *perm, int64_t max_rows, int64_t K, ActStage st, int num_sms,
+                                      cudaStream_t stream, const int32_t *row_map, const int *n_chunks);
 
 // ---- K3: fused decode GEMV (tcq4_gemv.cu) -----------------------------------------------------
 constexpr int GEMV_MAX_M = 16;
@@ -89,6 +92,10 @@ cudaError_t launch_peer_barrier(int *const *flags, int n, int rank, cudaStream_t
 // ---- MUL_MAT_ID row gather / scatter (tcq4_moe.cu) ------------------------------------------------
 cudaError_t launch_copy_rows(const float *src, const int32_t *src_idx, float *dst, const int32_t *dst_idx, int64_t rows,
                              int64_t cols, int num_sms, cudaStream_t stream);
+// device-side routing (one CTA): rows binned by expert into chunks of <= 64 rows at 64-aligned virtual rows; see tcq4_moe.cu
+cudaError_t launch_moe_route(const int32_t *ids, int64_t ids_stride, int64_t n_used, int64_t n_tokens, int64_t n_expert,
+                             int64_t x_slots, int max_chunks, int *n_chunks, int *chunk_expert, int32_t *src_map,
+                             int32_t *dst_map, int32_t *pos_tmp, int *err_flag, cudaStream_t stream);
 
 // ---- K4 / K5: device weight quantiser and GET_ROWS (tcq4_quant.cu) ------------------------------
 cudaError_t launch_quantize_tiles(const float *w, const int32_t *perm, void *tiles, int64_t nrow, int64_t K, int num_sms,
@@ -171,6 +178,9 @@ struct Gemm4Plan {
     size_t counter_bytes;   // mode 2: 4 ints per block
 };
 bool        gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, size_t smem_optin, Gemm4Plan *plan);
+cudaError_t launch_gemm4_id(const void *w_experts, int64_t n_expert, size_t expert_stride_bytes, ActStage st, float *y, int64_t N,
+                            int64_t K, const int *n_chunks, const int *chunk_expert, const int32_t *dst_map, int max_chunks,
+                            int num_sms, cudaStream_t stream);
 cudaError_t gemm4_init_attributes(size_t smem_optin);
 cudaError_t gemm4_read_prof(long long *host_out, size_t bytes);           // timeline stamps (diagnostics build)
 // st: MODE_NIB activation stage of the M <= 64 tokens (nibble units + a7t); y row stride ldc floats
