@@ -110,3 +110,51 @@ def test_gemm4_strided_output_and_fanout(t4, orc, M, K, Ns):
         rows = slice(0, 8) if n * K * M > 3e8 else slice(0, M)
         ref = orc.mul_mat(t, x[rows], n)["C"]
         assert nmse(out[rows].cpu().numpy(), ref) <= FP32_NMSE_TIGHT
+
+
+def test_gemm4_fuzz_against_pair_gemm(t4):
+    """60 seeded random shapes (M 9..64, N any multiple of 8 up to 40 000, K any multiple of 256 up to 8 192): the batched-decode
+    GEMM against the kind::i8 pair GEMM on the same inputs -- the int32 sums of both are pinned to the oracle elsewhere, here the
+    planner's corners are what is exercised (ragged N, blocks just above / below the SM count, K halves, K parts, one k-tile)."""
+    rng = np.random.default_rng(77)
+    shapes = [(int(rng.integers(9, 65)), int(rng.integers(1, 64)) * 8, int(rng.integers(1, 9)) * 256) for _ in range(30)]
+    shapes += [(int(rng.integers(9, 65)), int(rng.integers(140, 160)) * 128 + int(rng.integers(0, 16)) * 8, 512) for _ in range(6)]
+    shapes += [(int(rng.integers(9, 65)), int(rng.integers(1, 12)) * 128 - int(rng.integers(0, 15)) * 8, int(rng.integers(8, 33)) * 256)
+               for _ in range(14)]
+    shapes += [(int(rng.integers(9, 65)), int(rng.integers(300, 5000)) * 8, int(rng.integers(1, 5)) * 256) for _ in range(10)]
+    for M, N, K in shapes:
+        N = max(N, 8)
+        tiles = t4.random_tiles(N, K, seed=M + N + K)
+        x = torch.randn((M, K), device="cuda") * float(rng.uniform(0.1, 4.0))
+        ws = t4.Workspace.for_shape(M, N, K)
+        y4 = t4.mul_mat(tiles, x, N, workspace=ws, kernel=t4.KERNEL_GEMM4).clone()
+        y4b = t4.mul_mat(tiles, x, N, workspace=ws, kernel=t4.KERNEL_GEMM4).clone()
+        y2 = t4.mul_mat(tiles, x, N, workspace=ws, kernel=t4.KERNEL_GEMM2)
+        assert torch.equal(y4, y4b), (M, N, K)
+        e = nmse(y4.cpu().numpy(), y2.cpu().numpy())
+        assert e <= 1e-12, (M, N, K, e)
+
+
+def test_gemm4_fuzz_fanout_groups(t4):
+    """random fan-out groups of 2..4 matrices into one strided buffer through the graph entry, against per-matrix calls"""
+    rng = np.random.default_rng(78)
+    for _ in range(12):
+        M = int(rng.integers(9, 65))
+        K = int(rng.integers(1, 13)) * 256
+        Ns = [int(rng.integers(1, 300)) * 8 for _ in range(int(rng.integers(2, 5)))]
+        if rng.random() < 0.3:
+            Ns[0] = int(rng.integers(145, 152)) * 128
+        tl = [t4.random_tiles(n, K, seed=n + K) for n in Ns]
+        x = torch.randn((M, K), device="cuda")
+        buf = torch.full((M, sum(Ns) + 8), float("nan"), device="cuda")
+        outs, o = [], 0
+        for n in Ns:
+            outs.append(buf[:, o:o + n])
+            o += n
+        t4.GgmlGraph([(t, x, out, n, "") for t, n, out in zip(tl, Ns, outs)]).compute()
+        torch.cuda.synchronize()
+        assert torch.isnan(buf[:, sum(Ns):]).all()
+        for t, n, out in zip(tl, Ns, outs):
+            want = t4.mul_mat(t, x, n, kernel=t4.KERNEL_GEMM2)
+            e = nmse(out.cpu().numpy(), want.cpu().numpy())
+            assert e <= 1e-12, (M, K, Ns, n, e)

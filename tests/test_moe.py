@@ -264,3 +264,27 @@ def test_decode_per_slot_fallback_in_a_child_process():
     out = subprocess.run([sys.executable, "-m", "pytest", "tests/test_moe.py", "-m", "gpu", "-q", "-x", "-k", "decode and not child"],
                          cwd=root, env=env, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and " passed" in out.stdout, out.stdout[-3000:] + out.stderr[-2000:]
+
+
+def test_prefill_fuzz_device_routed_against_per_expert_calls(t4):
+    """random (experts, slots, tokens, shapes, one row per token or per slot): the device-routed op against one plain MUL_MAT per
+    expert over that expert's rows"""
+    rng = np.random.default_rng(61)
+    for _ in range(10):
+        n_expert = int(rng.integers(1, 40))
+        n_used = int(rng.integers(1, min(n_expert, 6) + 1))
+        n_tokens = int(rng.integers(9, 180))
+        N, K = int(rng.integers(1, 40)) * 8, int(rng.integers(1, 5)) * 256
+        x_slots = n_used if rng.random() < 0.5 else 1
+        td = torch.stack([t4.random_tiles(N, K, seed=1000 + e) for e in range(n_expert)])
+        ids = np.stack([rng.choice(n_expert, n_used, replace=False) for _ in range(n_tokens)]).astype(np.int32)
+        x = torch.randn((n_tokens, x_slots, K), device="cuda")
+        y = t4.mul_mat_id(td, x, _dev(ids), N)
+        for e in range(n_expert):
+            rows = [(t, s) for t in range(n_tokens) for s in range(n_used) if ids[t, s] == e]
+            if not rows:
+                continue
+            xe = torch.stack([x[t, s % x_slots] for t, s in rows])
+            plain = t4.mul_mat(td[e], xe, N, kernel=t4.KERNEL_GEMM2)
+            got = torch.stack([y[t, s] for t, s in rows])
+            assert nmse(got.cpu().numpy(), plain.cpu().numpy()) <= 1e-12, (n_expert, n_used, n_tokens, N, K, e)
