@@ -569,20 +569,24 @@ def batch_decode_leg(t4, torch, peak_gbs, Ms=(1, 2, 4, 8, 16, 32, 64)):
         for _ in range(3):
             cg.replay()
         torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        reps = 10
-        e0.record()
-        for _ in range(reps):
-            cg.replay()
-        e1.record()
-        torch.cuda.synchronize()
-        us = e0.elapsed_time(e1) * 1e3 / reps / n_layers
-        res.append({"M": M, "us_per_layer": us, "launches_per_layer": launches, "weight_gbs": wbytes / (us * 1e-6) / 1e9,
+        reps, trials = 20, []
+        for _ in range(5):      # 5 bursts of 20 replays, median burst: a burst is 3-7 ms, short enough for one host hiccup to show
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                cg.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            trials.append(e0.elapsed_time(e1) * 1e3 / reps / n_layers)
+        trials.sort()
+        us = trials[len(trials) // 2]
+        res.append({"M": M, "us_per_layer": us, "us_per_layer_min": trials[0], "us_per_layer_max": trials[-1],
+                    "launches_per_layer": launches, "weight_gbs": wbytes / (us * 1e-6) / 1e9,
                     "frac_hbm": wbytes / (us * 1e-6) / 1e9 / peak_gbs, "tok_per_s_per_layer": M / (us * 1e-6)})
         del nodes, g, cg
     t4.clear_perms()
     return {"shapes": [f"{n}: N={N} K={K}" for n, N, K, _ in LLAMA3_8B_LAYER], "perm": "synthetic imatrix, per activation tensor",
-            "timing": "tcq4_b200_ggml_graph_compute over 3 layers of distinct weights in one CUDA graph, 10 replays",
+            "timing": "tcq4_b200_ggml_graph_compute over 3 layers of distinct weights in one CUDA graph; median of 5 bursts of 20 replays",
             "weight_bytes_per_layer": wbytes, "per_batch": res}
 
 
