@@ -1,32 +1,40 @@
-// tcq4_gemm4.cu -- K2c: batched-decode GEMM for 17 <= M <= 64 tokens (BASELINE configs[2], "decode batch 1-64").
+// tcq4_gemm4.cu -- K2c: batched-decode GEMM for 9 <= M <= 64 tokens (BASELINE configs[2], "decode batch 1-64"), fan-out groups of
+// up to four matrices in one launch, and the grouped launch of MUL_MAT_ID with many tokens.
 //
 // At these batch sizes the MUL_MAT is bound by the weight stream (0.578 B per weight from HBM) and by the CUDA-core work of
 // widening every nibble once, not by tensor throughput -- but the 256-token tiles of the prefill GEMMs make the tensor pipe
 // (and their epilogues) pay for 256 rows of which at most 64 exist: 32-47 us per Llama-3-8B matrix against a 5 us memory
 // floor.  This kernel turns the operands around:
-//   * WEIGHTS are the A operand: 128 channels per CTA = the 128 TMEM lanes.  A thread owns one channel and a quarter of the
-//     k-tile: two 16-byte loads of nibbles, the magic-number widening of tcq4_gemm3.cu (LOP3 + HFMA2: p = sc*q exactly in
-//     fp16), two tcgen05.st -- the widened weights never touch shared memory.
-//   * TOKENS are the N dimension of tcgen05.mma.cta_group::1.kind::f16 with A in TMEM: an instruction costs 128*N/256 cycles,
-//     32 at N = 64, so a k-tile is 512 tensor cycles instead of 1 565.  The B operand (Mt x 256 fp16, Mt = 32 or 64) is
+//   * WEIGHTS are the A operand: 128 channels per CTA = the 128 TMEM lanes.  A thread owns one channel and half of the
+//     k-tile: four 16-byte loads of nibbles, the magic-number widening of tcq4_gemm3.cu (LOP3 + HFMA2: p = sc*q exactly in
+//     fp16), four tcgen05.st -- the widened weights never touch shared memory.
+//   * TOKENS are the N dimension of tcgen05.mma.cta_group::1.kind::f16 with A in TMEM (ideal cost 128*N/256 cycles per
+//     instruction; measured ~40-60 at N <= 64: the 128 rows of A set a floor).  The B operand (Mt x 256 fp16, Mt = 32 or 64) is
 //     widened from K1's nibble units by the same warps into shared memory (8 KB of nibbles per k-tile at Mt = 64).
 //   * D: 128 lanes (channels) x Mt columns (tokens) of fp32 holding the exact integer sums; the epilogue thread owns a channel:
 //     acc[t] += float(isum) * (a7[t]/127) * S, S a per-thread scalar, a7/127 broadcast from shared memory -- the reference's
 //     operation order, bit-identical to the other kernels' fp32 results.  Stores are coalesced (a warp = 32 channels of one token).
-//   * Stream-K where it stays deterministic for free: the (128-channel block, k-tile) pairs form one line of blocks * KT
-//     units, cut into one contiguous range per CTA.  With at least as many blocks as SMs a range is at least one block long, so
-//     a block is cut by at most ONE range boundary: its two parts meet in y through red.global.add.f32 on an output K1 has
-//     zeroed -- two addends commute, the result does not depend on arrival order -- and every SM works to the end (224 blocks
-//     on 148 SMs: 48.4 k-tiles each instead of 64 for the SMs that would take two whole blocks).  With fewer blocks than half
-//     the SMs the same line is cut at the blocks' halves (two addends again).  (An ordered fix-up through workspace slots and
-//     flags -- any number of parts per block -- was built and measured: every hand-over is two dependent L2 round trips under
-//     load, 5-20 us per launch)
-// Warps: 0 weight producer (TMA, HBM), 1 MMA issuer, 2 token producer (bulk copies, L2), 3 publisher (scales for the epilogue), 4-19 widening (lane quarter =
-// warp % 4, k-quarter = (warp - 4) / 4), 20-23 epilogue.  Rings: 6 weight stages (114 KB in flight: a weight stream is bound by
-// latency x bandwidth per SM), 3 token stages, 2 operand stages (A in TMEM, B in shared memory), 2 accumulator stages.
+//   * Work = one line of (128-channel block, k-tile) units over all matrices of the group, cut into one contiguous range per CTA:
+//       - more blocks than SMs: stream-K.  A range is at least one block long, so a block is cut by at most ONE boundary; its
+//         two parts meet in y through red.global.add.f32 on an output K1 has zeroed (two addends commute: the result does not
+//         depend on arrival order) and every SM works to the end (224 blocks on 148 SMs: 48.4 k-tiles each instead of 64);
+//       - at most half as many blocks as SMs: the blocks' K halves (two addends again), or P >= 3 K parts per block that leave
+//         their sums in workspace slots and count themselves in -- the LAST part to arrive adds the slots in part order and
+//         stores (deterministic, no waiting, no zeroed output; the planner weighs a part's k-tiles against that reduction);
+//       - otherwise whole blocks.
+//     (An ordered fix-up where a block's owner WAITS for the other parts was built first and measured 5-20 us per launch:
+//     every hand-over is two dependent L2 round trips under load, and a waiting CTA delays the SM's next launch.)
+//   * MUL_MAT_ID: the line is (chunk, block) pairs, a chunk = up to 64 rows of one expert at 64-aligned virtual rows of K1's
+//     units (tcq4_moe.cu); the expert's tiles come through a 3-D tensor map, the epilogue scatters rows through a map.
+// Warps: 0 weight producer (TMA, HBM), 1 MMA issuer, 2 token producer (bulk copies, L2), 3 publisher (per-channel scales and
+// row factors for the epilogue), 4-19 widening -- two teams of 8 on alternating k-tiles (lane quarter = warp % 4, K half =
+// (warp / 4) % 2) so that the hand-over latencies of one team hide under the other's work -- 20-23 epilogue.  Rings: 6 weight
+// stages (114 KB in flight: a weight stream is bound by latency x bandwidth per SM), 4 token stages, 2 operand stages (A in
+// TMEM, B in shared memory), 2 accumulator stages.
 //
 // Replaces, for these M, the live kernel tcq4_rrs_fused_gemm_smallM (/root/reference/ggml/src/ggml-cuda/tcq4_k32.cu:733-889),
-// which serves every M with one scalar loop (dispatch rrs.cu:317-323).
+// which serves every M with one scalar loop (dispatch rrs.cu:317-323), and the per-expert loop of ggml_cuda_mul_mat_id
+// (ggml-cuda.cu:2287-2436) for a TCQ4 src0.
 #include <cuda.h>
 #include <cuda_fp16.h>
 
