@@ -232,7 +232,7 @@ int run_gemm4_group(DevInfo *d, const tcq4::Gemm4Seg *segs, int nseg, const floa
         e = tcq4::launch_act_quant_nib_zl(x, perm, M, K, st, d->num_sms, stream, &zl);
         if (e != cudaSuccess) return cuda_fail(e, "activation kernel launch");
         (*launches)++;
-    } else if (g4.mode == 1) {       // (counters: their last reader left them at zero)
+    } else if (zl.n) {               // (the counters too: another shape's layout may have put other data where they live)
         e = tcq4::launch_zero_list(zl, d->num_sms, stream);
         if (e != cudaSuccess) return cuda_fail(e, "output clear launch");
         (*launches)++;
