@@ -57,7 +57,7 @@ enum {
     TCQ4_KERNEL_GEMM2 = 3,     /* same on CTA pairs (cta_group::2, 256 tokens per pair); several destinations       */
     TCQ4_KERNEL_GEMM3 = 4,     /* CTA pairs, tcgen05.mma kind::f16 on exact fp16 integers, nibble operands widened
                                   in the SM, fan-out segments, K split: the prefill kernel (round 2)                */
-    TCQ4_KERNEL_GEMM4 = 5      /* batched decode, 17 <= M <= 64: weights widened into TMEM (the MMA's A operand, 128
+    TCQ4_KERNEL_GEMM4 = 5      /* batched decode, 9 <= M <= 64: weights widened into TMEM (the MMA's A operand, 128
                                   channels per CTA), tokens as the MMA's N; K split on narrow matrices              */
 };
 
@@ -127,9 +127,10 @@ TCQ4_B200_API int tcq4_b200_mul_mat_add(const void *w_tiles, const float *x, flo
 
 /* Fan-out: n <= 8 weight matrices applied to the SAME activations x [M][K] (Q/K/V, gate/up: consecutive
  * MUL_MAT nodes of the ggml graph that share src1; the fusion hook is ggml-cuda.cu:3481-3688).  y[i] = F32 [M][N[i]].
- * M > 16: the activation stage runs once and the GEMMs follow; bit-identical to n separate tcq4_b200_mul_mat calls with
- * the same perm.  M <= 16 and n <= 4: ONE GEMV launch over all matrices (same int32 accumulators; the fp32 sum over a
- * channel's 256-blocks may be split differently, i.e. last-bit differences against separate calls). */
+ * The activation stage runs once; M > 64: one segmented launch of the kind::f16 pair GEMM per group of up to four matrices;
+ * 9 <= M <= 64: one launch of the batched-decode GEMM per group of up to four; M <= 8 and n <= 4: ONE GEMV launch over all
+ * matrices.  Same int32 accumulators as n separate tcq4_b200_mul_mat calls with the same perm; the fp32 sum over a channel's
+ * 256-blocks may be split differently (last-bit differences against separate calls). */
 TCQ4_B200_API int tcq4_b200_mul_mat_fanout(int n, const void *const *w_tiles, const int64_t *N, float *const *y,
                                            const float *x, int64_t M, int64_t K, const int32_t *d_perm,
                                            cudaStream_t stream);
