@@ -681,20 +681,19 @@ bool gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, 
     int64_t blocks = 0;
     for (int i = 0; i < nseg; i++) blocks += (Ns[i] + G4_CH - 1) / G4_CH;
     const int64_t KT = K / TILE_K;
-    const bool contiguous_y = true;      // strided outputs are cleared row by row (ZeroList)
     static const bool no_split = getenv("TCQ4_G4_NOSPLIT") != nullptr;
     static const bool no_parts = getenv("TCQ4_G4_NOPARTS") != nullptr;
     int64_t grid = blocks < num_sms ? blocks : num_sms;
     int mode = G4_WHOLE, parts = 1;
     if (!no_split) {
         if (blocks > num_sms && blocks % num_sms != 0) {
-            if (contiguous_y) mode = G4_TWO;                   // stream-K: ranges >= one block, a block is cut at most once
+            mode = G4_TWO;      // stream-K: ranges >= one block, a block is cut at most once (strided outputs are cleared row by row)
         } else if (2 * blocks <= num_sms && KT >= 8) {
             // K parts.  Cost model in k-tile times (~1 us): a part's k-tiles + the last arriver's reduction (one atomic round
             // trip, then ceil(M/8) * ceil(P/4) load round trips); two parts meet through red.add instead and cost nothing extra
             const int64_t pmax = std::min<int64_t>({(int64_t)num_sms / blocks, (int64_t)GEMM4_MAX_PARTS, KT / 4});
-            double best = contiguous_y ? (double)((KT + 1) / 2) : (double)KT;
-            int bp = contiguous_y ? 2 : 1;
+            double best = (double)((KT + 1) / 2);
+            int bp = 2;
             for (int64_t p = 3; p <= pmax && !no_parts; p++) {
                 const double fix = 2.0 + 0.6 * (double)((M + 7) / 8) * (double)((p + 3) / 4);
                 const double c = (double)((KT + p - 1) / p) + fix;
