@@ -140,6 +140,22 @@ TCQ4_B200_API int tcq4_b200_mul_mat_fanout_ld(int n, const void *const *w_tiles,
                                               const int64_t *ldc, const float *x, int64_t M, int64_t K,
                                               const int32_t *d_perm, cudaStream_t stream);
 
+/* Input-side fusion: the element-wise op that produced the activations in the graph, applied while the activation
+ * stage loads them -- one fp32 round trip of [M][K] less.
+ *   TCQ4_INPUT_RMS_NORM_MUL: x' = (row_scale[m] * x[m][k]) * col_weight[k]   -- RMSNorm * weight in front of Q/K/V and gate/up
+ *       (rms_norm_f32<.., do_multiply>, ggml-cuda/norm.cu:75-150); row_scale = rsqrt(mean(x^2) + eps) from tcq4_b200_rms_row_scale
+ *   TCQ4_INPUT_SWIGLU:       x' = (x / (1 + expf(-x))) * x2                  -- SwiGLU in front of down (unary.cu:255-267)
+ * Bit-identical to tcq4_b200_apply_input followed by tcq4_b200_mul_mat_fanout_ld (the same expression, evaluated in the load);
+ * M <= 8 (decode GEMV) takes that unfused route inside the call.  ldc may be NULL (contiguous outputs). */
+enum { TCQ4_INPUT_NONE = 0, TCQ4_INPUT_RMS_NORM_MUL = 1, TCQ4_INPUT_SWIGLU = 2 };
+TCQ4_B200_API int tcq4_b200_rms_row_scale(const float *x, float *row_scale, int64_t M, int64_t K, float eps, cudaStream_t stream);
+TCQ4_B200_API int tcq4_b200_apply_input(int mode, const float *x, const float *x2, const float *row_scale,
+                                        const float *col_weight, float *out, int64_t M, int64_t K, cudaStream_t stream);
+TCQ4_B200_API int tcq4_b200_mul_mat_fanout_input(int n, const void *const *w_tiles, const int64_t *N, float *const *y,
+                                                 const int64_t *ldc, const float *x, int mode, const float *x2,
+                                                 const float *row_scale, const float *col_weight, int64_t M, int64_t K,
+                                                 const int32_t *d_perm, cudaStream_t stream);
+
 /* MUL_MAT_ID, the mixture-of-experts form of the same operator: replaces ggml_cuda_mul_mat_id
  * (ggml-cuda.cu:2287-2436) for a TCQ4 src0, which the reference admits in supports_op (:4457-4459) and serves through
  * its generic path (ids to the host, rows sorted by expert, one ggml_cuda_mul_mat per expert).

@@ -48,7 +48,7 @@ EXPORTS = [
     "tcq4_b200_ggml_mul_mat", "tcq4_b200_launch_count",
     "tcq4_b200_profile_begin", "tcq4_b200_profile_end",
     "tcq4_b200_quantize_size", "tcq4_b200_quantize_tiles", "tcq4_b200_perm_from_imatrix", "tcq4_b200_get_rows", "tcq4_b200_ggml_get_rows",
-    "tcq4_b200_mul_mat_id", "tcq4_b200_ggml_mul_mat_id", "tcq4_b200_mul_mat_fanout", "tcq4_b200_mul_mat_fanout_ld", "tcq4_b200_mul_mat_fanout_host_async", "tcq4_b200_ggml_mul_mat_fanout", "tcq4_b200_ggml_graph_compute", "tcq4_b200_mul_mat_add", "tcq4_b200_quant_type_for",
+    "tcq4_b200_mul_mat_id", "tcq4_b200_ggml_mul_mat_id", "tcq4_b200_mul_mat_fanout", "tcq4_b200_mul_mat_fanout_ld", "tcq4_b200_mul_mat_fanout_host_async", "tcq4_b200_rms_row_scale", "tcq4_b200_apply_input", "tcq4_b200_mul_mat_fanout_input", "tcq4_b200_ggml_mul_mat_fanout", "tcq4_b200_ggml_graph_compute", "tcq4_b200_mul_mat_add", "tcq4_b200_quant_type_for",
     "tcq4_b200_gguf_open", "tcq4_b200_gguf_close", "tcq4_b200_gguf_reorder_enabled", "tcq4_b200_gguf_n_tensors",
     "tcq4_b200_gguf_n_perms", "tcq4_b200_gguf_tensor_info", "tcq4_b200_gguf_perm", "tcq4_b200_gguf_register_perms",
     "tcq4_b200_gguf_read_tensor", "tcq4_b200_gguf_load_tensor", "tcq4_b200_gguf_write",
@@ -135,6 +135,9 @@ def _load() -> C.CDLL:
     lib.tcq4_b200_mul_mat_fanout.argtypes = [ci, vp, vp, vp, vp, i64, i64, vp, vp]
     lib.tcq4_b200_mul_mat_fanout_ld.argtypes = [ci, vp, vp, vp, vp, vp, i64, i64, vp, vp]
     lib.tcq4_b200_mul_mat_fanout_host_async.argtypes = [ci, vp, vp, vp, vp, i64, i64, vp]
+    lib.tcq4_b200_rms_row_scale.argtypes = [vp, vp, i64, i64, C.c_float, vp]
+    lib.tcq4_b200_apply_input.argtypes = [ci, vp, vp, vp, vp, vp, i64, i64, vp]
+    lib.tcq4_b200_mul_mat_fanout_input.argtypes = [ci, vp, vp, vp, vp, vp, ci, vp, vp, vp, i64, i64, vp, vp]
     lib.tcq4_b200_mul_mat_add.argtypes = [vp, vp, vp, i64, i64, i64, vp, vp, vp, vp]
     lib.tcq4_b200_quant_type_for.argtypes = [C.c_char_p, ci, i64, i64, ci]
     lib.tcq4_b200_ggml_mul_mat_fanout.argtypes = [ci, vp, C.POINTER(TensorView), vp, vp]

@@ -15,7 +15,7 @@ import torch
 from . import (GGML_TYPE_F32, GGML_TYPE_TCQ4_K32, KERNEL_AUTO, LIB, TILE_BYTES, TILE_CHANNELS, TILE_K,
                ACT_BLOCK_BYTES, TensorView, _check, quantize_size, shard_range, tile_bytes, workspace_size)
 
-__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "ggml_mul_mat_fanout", "GgmlGraph", "mul_mat_add", "mul_mat_static", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "PeerBarrier", "mul_mat_host", "mul_mat_host_async", "mul_mat_fanout_host_async", "host_sync", "fwht_quantize_tc", "register_perm",
+__all__ = ["Workspace", "mul_mat", "mul_mat_id", "ggml_mul_mat_id", "Fanout", "ggml_mul_mat_fanout", "GgmlGraph", "mul_mat_add", "mul_mat_static", "mul_mat_debug", "mul_mat_peers", "mul_mat_multicast", "push_columns", "PeerBarrier", "mul_mat_host", "mul_mat_host_async", "mul_mat_fanout_host_async", "rms_row_scale", "apply_input", "mul_mat_fanout_input", "INPUT_RMS_NORM_MUL", "INPUT_SWIGLU", "host_sync", "fwht_quantize_tc", "register_perm",
            "clear_perms", "set_reorder_enabled", "get_perm_ptr", "has_perm", "reserve", "ggml_mul_mat",
            "ggml_supports_op", "ShardedWeight", "random_tiles", "quantize_tiles", "get_rows", "ggml_get_rows"]
 
@@ -356,6 +356,46 @@ class Fanout:
         pp = perm.data_ptr() if perm is not None else 0
         _check(LIB.tcq4_b200_mul_mat_fanout(self.n, self._w, self._N, y, x.data_ptr(), M, K, pp, _stream_ptr(stream)))
         return outs
+
+
+INPUT_RMS_NORM_MUL, INPUT_SWIGLU = 1, 2
+
+
+def rms_row_scale(x: torch.Tensor, eps: float, stream=None) -> torch.Tensor:
+    """rsqrt(mean(x^2) + eps) per row, in the reduction order of ggml-cuda's rms_norm_f32."""
+    _req_cuda(x, torch.float32, "x")
+    M, K = x.shape
+    out = torch.empty((M,), dtype=torch.float32, device=x.device)
+    _check(LIB.tcq4_b200_rms_row_scale(x.data_ptr(), out.data_ptr(), M, K, float(eps), _stream_ptr(stream)))
+    return out
+
+
+def apply_input(mode: int, x: torch.Tensor, x2=None, row_scale=None, col_weight=None, stream=None) -> torch.Tensor:
+    """The input transform on its own (what the fused activation-stage load computes): [M][K] -> [M][K]."""
+    _req_cuda(x, torch.float32, "x")
+    M, K = x.shape
+    out = torch.empty_like(x)
+    p = lambda t: t.data_ptr() if t is not None else 0
+    _check(LIB.tcq4_b200_apply_input(mode, x.data_ptr(), p(x2), p(row_scale), p(col_weight), out.data_ptr(), M, K, _stream_ptr(stream)))
+    return out
+
+
+def mul_mat_fanout_input(w_tiles: list, x: torch.Tensor, Ns: list, mode: int, x2=None, row_scale=None, col_weight=None,
+                         perm=None, outs=None, stream=None) -> list:
+    """tcq4_b200_mul_mat_fanout_input: the fan-out (or one matrix) with the op that produced x fused into the activation stage."""
+    _req_cuda(x, torch.float32, "x")
+    M, K = x.shape
+    n = len(Ns)
+    if outs is None:
+        outs = [torch.empty((M, N), dtype=torch.float32, device=x.device) for N in Ns]
+    wp = (C.c_void_p * n)(*[w.data_ptr() for w in w_tiles])
+    yp = (C.c_void_p * n)(*[o.data_ptr() for o in outs])
+    Np = (C.c_int64 * n)(*Ns)
+    ld = (C.c_int64 * n)(*[o.stride(0) for o in outs])
+    p = lambda t: t.data_ptr() if t is not None else 0
+    _check(LIB.tcq4_b200_mul_mat_fanout_input(n, wp, Np, yp, ld, x.data_ptr(), mode, p(x2), p(row_scale), p(col_weight), M, K,
+                                              p(perm), _stream_ptr(stream)))
+    return outs
 
 
 def ggml_mul_mat_fanout(w_tiles: list, x: torch.Tensor, Ns: list, names: list, stream=None) -> list:

@@ -20,11 +20,19 @@ constexpr int ACT_WARPS_PER_CTA = 8;
 
 enum { MODE_REF = 0, MODE_STAGE = 1, MODE_NIB = 2 };
 
-template <int MODE>
+// one element of the fused input transform (see ActInput): x is what K1 would have read from the op's output
+template <int IN>
+__device__ __forceinline__ float act_input_value(const ActInput &in, float xv, const float *__restrict__ x2_row, float rs, int idx) {
+    if (IN == ACT_IN_NORM) return (rs * xv) * __ldg(in.col_weight + idx);          // scale * x * mul, left to right (norm.cu:143-144)
+    if (IN == ACT_IN_SWIGLU) return (xv / (1.0f + expf(-xv))) * __ldcg(x2_row + idx);      // op_silu(x) * g (unary.cu:266)
+    return xv;
+}
+
+template <int MODE, int IN = ACT_IN_NONE>
 __global__ void __launch_bounds__(ACT_WARPS_PER_CTA * 32)
 tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ perm, int M, int K,
                       ActBlockTC *__restrict__ out_ref, ActStage st, const __grid_constant__ ZeroList zl,
-                      const int32_t *__restrict__ row_map, const int *__restrict__ n_chunks) {
+                      const int32_t *__restrict__ row_map, const int *__restrict__ n_chunks, const ActInput in) {
     const int lane = threadIdx.x & 31;
     const int KT = K / TILE_K;
     const long long nblocks = (long long)M * KT;
@@ -66,7 +74,26 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
         float v[8];
         // ld.global.cg: every element is read once, and under programmatic stream serialization a stale L1 line of x
         // could survive from an overlapping predecessor
-        rrs_load_block_cg(x + (size_t)m_src * K, perm, kt, lane, v);
+        if (IN == ACT_IN_NONE) {
+            rrs_load_block_cg(x + (size_t)m_src * K, perm, kt, lane, v);
+        } else {      // the producing op fused into the load: same values the op's own kernel would have written
+            const float *x_row = x + (size_t)m_src * K;
+            const float *x2_row = IN == ACT_IN_SWIGLU ? in.x2 + (size_t)m_src * K : nullptr;
+            const float rs = IN == ACT_IN_NORM ? __ldcg(in.row_scale + m_src) : 0.0f;
+            const int base = kt * TILE_K + lane * 8;
+            int idx[8];
+            if (perm == nullptr) {
+#pragma unroll
+                for (int r = 0; r < 8; r++) idx[r] = base + r;
+            } else {
+                const int4 p0 = __ldg(reinterpret_cast<const int4 *>(perm + base));
+                const int4 p1 = __ldg(reinterpret_cast<const int4 *>(perm + base) + 1);
+                idx[0] = p0.x; idx[1] = p0.y; idx[2] = p0.z; idx[3] = p0.w;
+                idx[4] = p1.x; idx[5] = p1.y; idx[6] = p1.z; idx[7] = p1.w;
+            }
+#pragma unroll
+            for (int r = 0; r < 8; r++) v[r] = act_input_value<IN>(in, __ldcg(x_row + idx[r]), x2_row, rs, idx[r]);
+        }
         const ActQuantT a = rrs_quantize_block_t<true>(v, lane, scratch);
         const uint2 e = rrs_codes_layout_a(a, lane, scratch);        // byte r = code of element lane*8 + r
         int gs = 0;                                                  // lane g < 8 keeps the sum of group g
@@ -112,6 +139,9 @@ tcq4_act_quant_kernel(const float *__restrict__ x, const int32_t *__restrict__ p
     }
 }
 
+static thread_local const ActInput *tl_pending_in = nullptr;
+void set_pending_act_input(const ActInput *in) { tl_pending_in = in; }
+
 static int act_grid(int64_t nblocks, int num_sms) {
     const int64_t ctas = (nblocks + ACT_WARPS_PER_CTA - 1) / ACT_WARPS_PER_CTA;
     const int64_t cap = (int64_t)num_sms * 8;     // 8 CTAs x 8 warps = full occupancy, then grid-stride
@@ -146,7 +176,32 @@ static cudaError_t launch_act(Kern kern, int grid, cudaStream_t stream, const fl
     }
     ZeroList zl{};
     if (zlp) zl = *zlp;
-    return cudaLaunchKernelEx(&cfg, kern, x, perm, M, K, out_ref, st, zl, row_map, n_chunks);
+    ActInput in{};
+    return cudaLaunchKernelEx(&cfg, kern, x, perm, M, K, out_ref, st, zl, row_map, n_chunks, in);
+}
+
+// the same launch with the pending input transform (stage / nibble outputs only)
+template <int MODE>
+static cudaError_t launch_act_in(int grid, cudaStream_t stream, const float *x, const int32_t *perm, int M, int K, ActStage st,
+                                 int which, const ZeroList *zlp) {
+    const ActInput in = *tl_pending_in;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(ACT_WARPS_PER_CTA * 32);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    static const bool pdl = getenv("TCQ4_PDL") != nullptr, no_pdl = getenv("TCQ4_NO_PDL") != nullptr;
+    cfg.numAttrs = (pdl || (which == 2 && !no_pdl)) ? 1 : 0;
+    ZeroList zl{};
+    if (zlp) zl = *zlp;
+    if (in.mode == ACT_IN_NORM)
+        return cudaLaunchKernelEx(&cfg, tcq4_act_quant_kernel<MODE, ACT_IN_NORM>, x, perm, M, K, (ActBlockTC *)nullptr, st, zl,
+                                  (const int32_t *)nullptr, (const int *)nullptr, in);
+    return cudaLaunchKernelEx(&cfg, tcq4_act_quant_kernel<MODE, ACT_IN_SWIGLU>, x, perm, M, K, (ActBlockTC *)nullptr, st, zl,
+                              (const int32_t *)nullptr, (const int *)nullptr, in);
 }
 
 cudaError_t launch_act_quant_ref(const float *x, const int32_t *perm, int64_t M, int64_t K, void *out_blocks,
@@ -162,6 +217,8 @@ cudaError_t launch_act_quant_stage(const float *x, const int32_t *perm, int64_t 
                                    int num_sms, cudaStream_t stream) {
     const int64_t nblocks = M * (K / TILE_K);
     if (nblocks == 0) return cudaSuccess;
+    if (tl_pending_in && tl_pending_in->mode != ACT_IN_NONE)
+        return launch_act_in<MODE_STAGE>(act_grid(nblocks, num_sms), stream, x, perm, (int)M, (int)K, st, 0, nullptr);
     return launch_act(tcq4_act_quant_kernel<MODE_STAGE>, act_grid(nblocks, num_sms), stream, x, perm, (int)M, (int)K,
                       (ActBlockTC *)nullptr, st);
 }
@@ -170,6 +227,8 @@ cudaError_t launch_act_quant_nib_zl(const float *x, const int32_t *perm, int64_t
                                     cudaStream_t stream, const ZeroList *zl) {
     const int64_t nblocks = M * (K / TILE_K);
     if (nblocks == 0) return cudaSuccess;
+    if (tl_pending_in && tl_pending_in->mode != ACT_IN_NONE)
+        return launch_act_in<MODE_NIB>(act_grid(nblocks, num_sms), stream, x, perm, (int)M, (int)K, st, 2, zl);
     return launch_act(tcq4_act_quant_kernel<MODE_NIB>, act_grid(nblocks, num_sms), stream, x, perm, (int)M, (int)K,
                       (ActBlockTC *)nullptr, st, 2, zl);
 }
@@ -192,6 +251,58 @@ cudaError_t launch_act_quant_nib(const float *x, const int32_t *perm, int64_t M,
         zl.ld[0] = zl.cols[0];
     }
     return launch_act_quant_nib_zl(x, perm, M, K, st, num_sms, stream, &zl);
+}
+
+// ---- the input transforms on their own ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) tcq4_apply_input_kernel(const ActInput in, const float *__restrict__ x, float *__restrict__ out,
+                                                               long long M, int K) {
+    const long long total = M * K;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long m = i / K;
+        const int k = (int)(i - m * K);
+        const float xv = x[i];
+        if (in.mode == ACT_IN_NORM) out[i] = act_input_value<ACT_IN_NORM>(in, xv, nullptr, in.row_scale[m], k);
+        else if (in.mode == ACT_IN_SWIGLU) out[i] = act_input_value<ACT_IN_SWIGLU>(in, xv, in.x2 + m * K, 0.0f, k);
+        else out[i] = xv;
+    }
+}
+cudaError_t launch_apply_input(const ActInput &in, const float *x, float *out, int64_t M, int64_t K, int num_sms, cudaStream_t stream) {
+    const long long total = (long long)M * K;
+    if (total == 0) return cudaSuccess;
+    long long grid = (total + 255) / 256;
+    if (grid > (long long)num_sms * 8) grid = (long long)num_sms * 8;
+    tcq4_apply_input_kernel<<<(unsigned)grid, 256, 0, stream>>>(in, x, out, (long long)M, (int)K);
+    return cudaGetLastError();
+}
+
+// rsqrt(mean(x^2) + eps) of one row per CTA, in the order of rms_norm_f32 (norm.cu:125-137): per-thread partial sums over
+// col = tid, tid + BS, ..., a shuffle-xor tree (16 .. 1) inside each warp, the warps' sums through shared memory and the same
+// tree again
+template <int BS>
+__global__ void __launch_bounds__(BS) tcq4_rms_row_scale_kernel(const float *__restrict__ x, float *__restrict__ row_scale, int K, float eps) {
+    __shared__ float s_sum[32];
+    const float *xr = x + (size_t)blockIdx.x * K;
+    float tmp = 0.0f;
+    for (int col = threadIdx.x; col < K; col += BS) {
+        const float xi = xr[col];
+        tmp += xi * xi;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tmp += __shfl_xor_sync(0xffffffffu, tmp, o);
+    if (BS > 32) {
+        if ((threadIdx.x & 31) == 0) s_sum[threadIdx.x >> 5] = tmp;
+        __syncthreads();
+        tmp = (threadIdx.x & 31) < BS / 32 ? s_sum[threadIdx.x & 31] : 0.0f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) tmp += __shfl_xor_sync(0xffffffffu, tmp, o);
+    }
+    if (threadIdx.x == 0) row_scale[blockIdx.x] = rsqrtf(tmp / K + eps);
+}
+cudaError_t launch_rms_row_scale(const float *x, float *row_scale, int64_t M, int64_t K, float eps, cudaStream_t stream) {
+    if (M == 0) return cudaSuccess;
+    if (K < 1024) tcq4_rms_row_scale_kernel<256><<<(unsigned)M, 256, 0, stream>>>(x, row_scale, (int)K, eps);
+    else tcq4_rms_row_scale_kernel<1024><<<(unsigned)M, 1024, 0, stream>>>(x, row_scale, (int)K, eps);
+    return cudaGetLastError();
 }
 
 __global__ void tcq4_zero_kernel(float4 *__restrict__ y, long long n4) {

@@ -1224,6 +1224,94 @@ int tcq4_b200_mul_mat_fanout_host_async(int n, const void *const *w_tiles_dev, c
     return TCQ4_OK;
 }
 
+// ---- input-side fusion: the op that produced the activations, applied while K1 loads them -----------------------
+// RMSNorm * weight in front of Q/K/V and gate/up (build_norm, llama-graph.cpp; kernel rms_norm_f32<.., do_multiply>, norm.cu:75-150)
+// and SwiGLU in front of down (build_ffn, llama-graph.cpp:731-755; unary_gated_op_kernel<op_silu>, unary.cu:255-267).  One fp32
+// round trip of the [M][K] activations less; results are bit-identical to applying tcq4_b200_apply_input and then the plain
+// entry, because the fused load evaluates the same expression in the same order.  M <= 8 (decode GEMV, whose activation stage
+// lives inside the kernel) takes exactly that unfused route.
+int tcq4_b200_rms_row_scale(const float *x, float *row_scale, int64_t M, int64_t K, float eps, cudaStream_t stream) {
+    if (!x || !row_scale || M < 1 || K < 1) {
+        set_err("rms_row_scale: null pointer or empty shape");
+        return TCQ4_ERR_ARG;
+    }
+    int status;
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    cudaError_t e = tcq4::launch_rms_row_scale(x, row_scale, M, K, eps, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "rms_row_scale launch");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return TCQ4_OK;
+}
+
+static int make_act_input(int mode, const float *x2, const float *row_scale, const float *col_weight, tcq4::ActInput *in) {
+    in->mode = mode;
+    in->x2 = x2;
+    in->row_scale = row_scale;
+    in->col_weight = col_weight;
+    if (mode == TCQ4_INPUT_RMS_NORM_MUL && row_scale && col_weight) return TCQ4_OK;
+    if (mode == TCQ4_INPUT_SWIGLU && x2) return TCQ4_OK;
+    set_err("input transform: mode %d needs %s", mode, mode == TCQ4_INPUT_SWIGLU ? "x2" : "row_scale and col_weight");
+    return TCQ4_ERR_ARG;
+}
+
+int tcq4_b200_apply_input(int mode, const float *x, const float *x2, const float *row_scale, const float *col_weight, float *out,
+                          int64_t M, int64_t K, cudaStream_t stream) {
+    tcq4::ActInput in;
+    int status = make_act_input(mode, x2, row_scale, col_weight, &in);
+    if (status != TCQ4_OK) return status;
+    if (!x || !out || M < 1 || K < 1) {
+        set_err("apply_input: null pointer or empty shape");
+        return TCQ4_ERR_ARG;
+    }
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    cudaError_t e = tcq4::launch_apply_input(in, x, out, M, K, d->num_sms, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "apply_input launch");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return TCQ4_OK;
+}
+
+int tcq4_b200_mul_mat_fanout_input(int n, const void *const *w_tiles, const int64_t *Ns, float *const *ys, const int64_t *ldcs,
+                                   const float *x, int mode, const float *x2, const float *row_scale, const float *col_weight,
+                                   int64_t M, int64_t K, const int32_t *d_perm, cudaStream_t stream) {
+    tcq4::ActInput in;
+    int status = make_act_input(mode, x2, row_scale, col_weight, &in);
+    if (status != TCQ4_OK) return status;
+    if (n < 1 || n > 8 || !Ns) {
+        set_err("mul_mat_fanout_input: 1..8 weight matrices");
+        return TCQ4_ERR_ARG;
+    }
+    int64_t Nmax = 0, Nsum = 0;
+    for (int i = 0; i < n; i++) {
+        if (!shape_ok(M, Ns[i], K)) {
+            set_err("unsupported shape M=%lld N=%lld K=%lld", (long long)M, (long long)Ns[i], (long long)K);
+            return TCQ4_ERR_SHAPE;
+        }
+        Nmax = std::max(Nmax, Ns[i]);
+        Nsum += Ns[i];
+    }
+    DevInfo *d = current_device(&status);
+    if (!d) return status;
+    static const bool g2_fuse = getenv("TCQ4_G2_FUSE") != nullptr;      // (that opt-in runs the activation stage inside the GEMM)
+    if (select_kernel(d, M, Nmax, K, nullptr) == TCQ4_KERNEL_GEMV || g2_fuse) {
+        // decode: transform into scratch behind the MUL_MAT's own workspace, then the plain fan-out
+        size_t tail = std::max(ws_layout(M, Nmax, K).total, shape_ok(M, Nsum, K) ? ws_layout(M, Nsum, K).total : (size_t)0);
+        tail = (size_t)tcq4::round_up((int64_t)tail, 256);
+        status = arena_ensure(d, tail + (size_t)M * K * 4, stream);
+        if (status != TCQ4_OK) return status;
+        float *xt = reinterpret_cast<float *>(reinterpret_cast<uint8_t *>(d->arena) + tail);
+        cudaError_t e = tcq4::launch_apply_input(in, x, xt, M, K, d->num_sms, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "apply_input launch");
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        return tcq4_b200_mul_mat_fanout_ld(n, w_tiles, Ns, ys, ldcs, xt, M, K, d_perm, stream);
+    }
+    tcq4::set_pending_act_input(&in);      // picked up by the one activation-stage launch of the call below
+    status = tcq4_b200_mul_mat_fanout_ld(n, w_tiles, Ns, ys, ldcs, x, M, K, d_perm, stream);
+    tcq4::set_pending_act_input(nullptr);
+    return status;
+}
+
 int tcq4_b200_host_sync(void) {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEV) return TCQ4_ERR_NO_DEVICE;

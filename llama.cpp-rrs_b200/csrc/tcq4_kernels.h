@@ -12,6 +12,25 @@ struct CUtensorMap_st;      // <cuda.h>
 namespace tcq4 {
 
 // ---- K1: activation stage (tcq4_act.cu) -------------------------------------------------------
+// Input-side fusion: the element-wise op that produced the activations in the graph, applied while K1 loads them
+// instead of in a kernel of its own (one fp32 round trip of [M][K] less).  Expressions and operation order are the ggml-cuda
+// kernels': rms_norm_f32<.., do_multiply> (norm.cu:75-150: scale * x * mul) and unary_gated_op_kernel<op_silu> (unary.cu:255-267,
+// unary.cuh:92-94: x / (1 + expf(-x)) * g).
+enum { ACT_IN_NONE = 0, ACT_IN_NORM = 1, ACT_IN_SWIGLU = 2 };
+struct ActInput {
+    int          mode;
+    const float *x2;            // SWIGLU: the second operand ("up"), [M][K] like x ("gate")
+    const float *row_scale;     // NORM: rsqrt(mean(x^2) + eps) per row, [M]
+    const float *col_weight;    // NORM: the norm's weight, [K]
+};
+// the transform on its own (what the fused load computes, element for element): out [M][K]
+cudaError_t launch_apply_input(const ActInput &in, const float *x, float *out, int64_t M, int64_t K, int num_sms, cudaStream_t stream);
+// rsqrt(mean(x^2) + eps) per row with the reduction order of rms_norm_f32 (norm.cu:125-137)
+cudaError_t launch_rms_row_scale(const float *x, float *row_scale, int64_t M, int64_t K, float eps, cudaStream_t stream);
+// the transform the NEXT activation-stage launches of this host thread apply to their input (nullptr: none); set and cleared by
+// the fused entry points of tcq4_api.cu around their calls
+void set_pending_act_input(const ActInput *in);
+
 cudaError_t launch_act_quant_ref(const float *x, const int32_t *perm, int64_t M, int64_t K, void *out_blocks,
                                  int num_sms, cudaStream_t stream);
 cudaError_t launch_act_quant_stage(const float *x, const int32_t *perm, int64_t M, int64_t K, ActStage st,
