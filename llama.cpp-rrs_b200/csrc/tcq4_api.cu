@@ -141,7 +141,7 @@ WsLayout ws_layout(int64_t M, int64_t N, int64_t K) {
     const int64_t maxslots = KT;
     const int64_t slot_rows = (M <= 8) ? 8 : 16;
     L.partial_bytes = (size_t)tcq4::round_up(NT * maxslots * slot_rows * 8 * 4, 256);   // kept for every M: size is monotone in M
-    if (M > 8 && ((N + 127) / 128) * 3 <= tcq4::GEMM4_MAX_CTAS) {      // batched-decode GEMM, K parts: one [32|64 tokens][128 channels] slot per CTA
+    if (M > 8 && ((N + 127) / 128) * 2 <= tcq4::GEMM4_MAX_CTAS) {      // batched-decode GEMM, K parts: one [32|64 tokens][128 channels] slot per CTA
         const int64_t g4 = (int64_t)tcq4::GEMM4_MAX_CTAS * (M <= 32 ? 32 : 64) * 128 * 4;
         L.partial_bytes = std::max(L.partial_bytes, (size_t)tcq4::round_up(g4, 256));
     }
@@ -194,11 +194,11 @@ tcq4::YOut single_out(float *y, int64_t N) {
 // they are cut in K parts -- is cleared by K1 itself (strided outputs row by row), or by a small kernel when K1 does not run.
 int run_gemm4_group(DevInfo *d, const tcq4::Gemm4Seg *segs, int nseg, const float *x, const int32_t *perm, int64_t M, int64_t K,
                     uint8_t *wsb, const WsLayout &L, bool reuse_act, int32_t *dbg_isum, cudaStream_t stream, int *launches,
-                    cudaEvent_t after_act = nullptr) {
+                    cudaEvent_t after_act = nullptr, const float *res = nullptr, const float *bias = nullptr) {
     int64_t Ns[tcq4::GEMM4_MAX_SEG];
     for (int i = 0; i < nseg; i++) Ns[i] = segs[i].N;
     tcq4::Gemm4Plan g4;
-    if (!tcq4::gemm4_plan(M, Ns, nseg, K, d->num_sms, d->smem_optin, &g4)) {
+    if (!tcq4::gemm4_plan(M, Ns, nseg, K, d->num_sms, d->smem_optin, &g4, res != nullptr || bias != nullptr)) {
         set_err("batched-decode GEMM cannot be planned for this shape/device");
         return TCQ4_ERR_SHAPE;
     }
@@ -239,7 +239,7 @@ int run_gemm4_group(DevInfo *d, const tcq4::Gemm4Seg *segs, int nseg, const floa
     }
     if (after_act) cudaEventRecord(after_act, stream);      // profile tap: activation stage | GEMM
     e = tcq4::launch_gemm4(segs, nseg, st, M, K, g4, reinterpret_cast<float *>(wsb + L.partial_off),
-                           reinterpret_cast<int *>(wsb + L.ticket_off), dbg_isum, stream);
+                           reinterpret_cast<int *>(wsb + L.ticket_off), dbg_isum, stream, res, bias);
     if (e != cudaSuccess) return cuda_fail(e, "gemm4 launch");
     (*launches)++;
     return TCQ4_OK;
@@ -288,7 +288,7 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
     if (k == TCQ4_KERNEL_GEMM && !plain) k = TCQ4_KERNEL_GEMM2;      // only the pair GEMMs and the GEMV write strided / to peers
     if (k == TCQ4_KERNEL_GEMM && (res || bias)) k = TCQ4_KERNEL_GEMM2;            // ... and fuse bias / residual
     if (k == TCQ4_KERNEL_GEMM3 && !one_dest) k = TCQ4_KERNEL_GEMM2;               // several destinations / multicast: kind::i8 pair GEMM
-    if (k == TCQ4_KERNEL_GEMM4 && (!one_dest || res || bias || M > 64)) k = TCQ4_KERNEL_GEMM2;
+    if (k == TCQ4_KERNEL_GEMM4 && (!one_dest || M > 64 || ((res || bias) && yo.ldc != N))) k = TCQ4_KERNEL_GEMM2;
     if (k == TCQ4_KERNEL_GEMV) {
         if (!tcq4::gemv_plan(M, N, K, d->num_sms, d->smem_optin, &gv)) {
             set_err("GEMV kernel does not take M=%lld K=%lld (M<=%d and M*K codes must fit shared memory)",
@@ -327,7 +327,7 @@ int run_mul_mat(const void *w, const float *x, tcq4::YOut yo, int64_t M, int64_t
         const tcq4::Gemm4Seg sg{w, y, N, yo.ldc};
         int launches = 0;
         const int rc = run_gemm4_group(d, &sg, 1, x, perm, M, K, wsb, L, reuse_act, dbg_isum, stream, &launches,
-                                       prof ? g_prof.ev[3 * g_prof.n + 1] : nullptr);
+                                       prof ? g_prof.ev[3 * g_prof.n + 1] : nullptr, res, bias);
         if (rc != TCQ4_OK) return rc;
         if (act_done) *act_done = true;
         if (prof) {

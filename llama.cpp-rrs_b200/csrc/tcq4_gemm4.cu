@@ -202,6 +202,11 @@ struct G4Params {
     int N[GEMM4_MAX_SEG];
     int blk0[GEMM4_MAX_SEG + 1];      // first block of each segment (unused: INT_MAX)
     int nseg;
+    // bias / residual fused into the epilogue (tcq4_b200_mul_mat_add; one segment only): the part of a block that holds k-tile 0
+    // starts its accumulators from bias[n] + res[m][n] (same order as the pair GEMMs); res may alias y
+    const float *bias;                // [N] or null
+    const float *res;                 // [M][ldres] or null
+    long long ldres;
     // MUL_MAT_ID, device-routed (tcq4_moe.cu): the line is (chunk, block) pairs -- a chunk = up to 64 rows of one expert at the
     // 64-aligned virtual rows of K1's units; tm[0] is then a 3-D map [expert][tile row][words], w[0] / N[0] / y[0] describe one
     // expert's matrix and the [row][N] output
@@ -525,6 +530,18 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
             }
 #pragma unroll
             for (int i = 0; i < MT / 2; i++) acc2[i] = 0ull;
+            if ((P.bias != nullptr || P.res != nullptr) && kt0 == 0 && n < N) {
+                const float bv = P.bias ? __ldg(P.bias + n) : 0.0f;
+#pragma unroll
+                for (int i = 0; i < MT / 2; i++) {
+                    float a = bv, bb = bv;
+                    if (P.res != nullptr) {      // ld.global.cg: the residual may be the output of the kernel before this one
+                        if (2 * i < M) a += __ldcg(P.res + (size_t)(2 * i) * P.ldres + n);
+                        if (2 * i + 1 < M) bb += __ldcg(P.res + (size_t)(2 * i + 1) * P.ldres + n);
+                    }
+                    acc2[i] = g4_pack(a, bb);
+                }
+            }
             for (int kt = kt0; kt < kt1; kt++, gk++) {
                 const int b = gk & 1, u2 = gk >> 1, ring = gk & (G4_RING - 1);
 #ifdef TCQ4_DIAG
@@ -676,7 +693,7 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
 typedef CUresult (*G4EncodeTiled3)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-bool gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, size_t smem_optin, Gemm4Plan *plan) {
+bool gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, size_t smem_optin, Gemm4Plan *plan, bool no_atomic) {
     if (M < 1 || M > G4_MAXMT || (size_t)Gemm4Smem::total > smem_optin || num_sms < 1 || nseg < 1 || nseg > GEMM4_MAX_SEG) return false;
     int64_t blocks = 0;
     for (int i = 0; i < nseg; i++) blocks += (Ns[i] + G4_CH - 1) / G4_CH;
@@ -687,7 +704,7 @@ bool gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, 
     int mode = G4_WHOLE, parts = 1;
     if (!no_split) {
         if (blocks > num_sms && blocks % num_sms != 0) {
-            mode = G4_TWO;      // stream-K: ranges >= one block, a block is cut at most once (strided outputs are cleared row by row)
+            if (!no_atomic) mode = G4_TWO;      // stream-K: ranges >= one block, a block is cut at most once (strided outputs are cleared row by row)
         } else if (2 * blocks <= num_sms && KT >= 8) {
             // K parts.  Cost model in k-tile times (~1 us): a part's k-tiles + the last arriver's reduction (one atomic round
             // trip, then ceil(M/8) * ceil(P/4) load round trips); two parts meet through red.add instead and cost nothing extra
@@ -704,7 +721,9 @@ bool gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, 
             }
             parts = bp;
             grid = blocks * parts;
-            mode = parts == 1 ? G4_WHOLE : parts == 2 ? G4_TWO : G4_PARTS;
+            // (no_atomic -- a fused residual may sit in y, which can then neither be cleared nor take two adds in either order:
+            //  two parts go through the slots as well)
+            mode = parts == 1 ? G4_WHOLE : (parts == 2 && !no_atomic) ? G4_TWO : G4_PARTS;
         }
     }
     plan->grid = (int)grid;
@@ -719,7 +738,7 @@ bool gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, 
 }
 
 cudaError_t launch_gemm4(const Gemm4Seg *segs, int nseg, ActStage st, int64_t M, int64_t K, const Gemm4Plan &plan,
-                         float *partials, int *counters, int32_t *dbg_isum, cudaStream_t stream) {
+                         float *partials, int *counters, int32_t *dbg_isum, cudaStream_t stream, const float *res, const float *bias) {
     if (nseg < 1 || nseg > GEMM4_MAX_SEG) return cudaErrorInvalidValue;
     G4Params P;
     memset(&P, 0, sizeof(P));
@@ -737,6 +756,10 @@ cudaError_t launch_gemm4(const Gemm4Seg *segs, int nseg, ActStage st, int64_t M,
     }
     P.nseg = nseg;
     if (blk != plan.num_blocks) return cudaErrorInvalidValue;
+    if ((res || bias) && (nseg != 1 || plan.mode == G4_TWO)) return cudaErrorInvalidValue;
+    P.bias = bias;
+    P.res = res;
+    P.ldres = (long long)segs[0].N;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)plan.grid);
     cfg.blockDim = dim3(G4_THREADS);

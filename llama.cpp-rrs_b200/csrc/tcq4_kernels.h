@@ -196,14 +196,18 @@ struct Gemm4Plan {
     size_t partial_bytes;   // mode 2: one [mt][128] fp32 slot per CTA
     size_t counter_bytes;   // mode 2: 4 ints per block
 };
-bool        gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, size_t smem_optin, Gemm4Plan *plan);
+// no_atomic: never let two parts of a block meet in y through red.add (a fused residual may sit there)
+bool        gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, size_t smem_optin, Gemm4Plan *plan,
+                       bool no_atomic = false);
 cudaError_t launch_gemm4_id(const void *w_experts, int64_t n_expert, size_t expert_stride_bytes, ActStage st, float *y, int64_t N,
                             int64_t K, const int *n_chunks, const int *chunk_expert, const int32_t *dst_map, int max_chunks,
                             int num_sms, cudaStream_t stream);
 cudaError_t gemm4_init_attributes(size_t smem_optin);
 cudaError_t gemm4_read_prof(long long *host_out, size_t bytes);           // timeline stamps (diagnostics build)
 // st: MODE_NIB activation stage of the M <= 64 tokens (nibble units + a7t); y row stride ldc floats
+// res ([M][N] contiguous, may alias the output) / bias ([N]): fused into the epilogue, one segment only, plan made with no_atomic
 cudaError_t launch_gemm4(const Gemm4Seg *segs, int nseg, ActStage st, int64_t M, int64_t K, const Gemm4Plan &plan,
-                         float *partials, int *counters, int32_t *dbg_isum, cudaStream_t stream);
+                         float *partials, int *counters, int32_t *dbg_isum, cudaStream_t stream, const float *res = nullptr,
+                         const float *bias = nullptr);
 
 }  // namespace tcq4

@@ -17,8 +17,9 @@ def t4():
     return graft.load_package()
 
 
-@pytest.mark.parametrize("M", [1, 3, 8, 16, 40, 129, 300])      # GEMV dp4a / IMMA loops, then the pair GEMM (M > 16)
-@pytest.mark.parametrize("N,K", [(136, 512), (1024, 1024)])      # a ragged last column tile, and a wide shallow matrix
+@pytest.mark.parametrize("M", [1, 3, 8, 16, 40, 64, 129, 300])  # GEMV dp4a / IMMA loops, the batched-decode GEMM (9..64), the pair GEMM
+@pytest.mark.parametrize("N,K", [(136, 512), (1024, 1024), (256, 4096)])      # a ragged last column tile, a wide shallow matrix,
+                                                                              # a narrow deep one (K parts with the last arriver)
 def test_bias_and_residual_fused(t4, orc, M, N, K):
     rng = np.random.default_rng(M * 7 + N)
     perm = block_perm(rng, K)
@@ -41,17 +42,22 @@ def test_bias_and_residual_fused(t4, orc, M, N, K):
             assert torch.equal(y, plain)
 
 
-@pytest.mark.parametrize("M", [2, 64])
-def test_residual_in_place(t4, orc, M):
-    """the residual stream updated in place: out is the residual tensor (ggml_add inplace)"""
+@pytest.mark.parametrize("M", [2, 24, 64])
+@pytest.mark.parametrize("N,K", [(256, 512), (256, 6144), (19200, 256)])
+def test_residual_in_place(t4, orc, M, N, K):
+    """the residual stream updated in place: out is the residual tensor (ggml_add inplace); also where the batched-decode GEMM
+    would otherwise cut blocks (K parts, stream-K): with a residual in y the parts must not meet there through red.add"""
     rng = np.random.default_rng(5 + M)
-    N, K = 256, 512
     tiles = orc.quantize_tiles(make_weights(rng, N, K))
     x = make_acts(rng, M, K)
     res = rng.standard_normal((M, N)).astype(np.float32)
     td, xd, h = torch.from_numpy(tiles).cuda(), torch.from_numpy(x).cuda(), torch.from_numpy(res).cuda()
     t4.mul_mat_add(td, xd, N, residual=h, out=h)
-    assert nmse(h.cpu().numpy(), orc.mul_mat(tiles, x, N)["C"] + res) <= 1e-9
+    rows = slice(0, 4) if N * K * M > 2e8 else slice(0, M)
+    assert nmse(h[rows].cpu().numpy(), orc.mul_mat(tiles, x[rows], N)["C"] + res[rows]) <= 1e-9
+    h2 = torch.from_numpy(res).cuda()
+    t4.mul_mat_add(td, xd, N, residual=h2, out=h2)
+    assert torch.equal(h, h2)                                    # deterministic
 
 
 @pytest.mark.gpu
