@@ -77,3 +77,42 @@ def test_input_fusion_strided_outputs_and_bad_arguments(t4, orc):
         t4.mul_mat_fanout_input(tl, x, Ns, t4.INPUT_RMS_NORM_MUL, row_scale=rs)  # no weight
     y = t4.mul_mat(tl[0], x, Ns[0])                                             # the pending transform never leaks into a later call
     assert torch.equal(y, t4.mul_mat(tl[0], x, Ns[0]))
+
+
+def test_input_fusion_is_graph_capturable(t4, orc):
+    """row scale + fused fan-out + fused SwiGLU down captured in one CUDA graph and replayed on new activations"""
+    rng = np.random.default_rng(800)
+    M, K, Kd, Ns, Nd = 48, 512, 768, [256, 128], 264
+    tl = [_dev(orc.quantize_tiles(make_weights(rng, n, K))) for n in Ns]
+    wd = _dev(orc.quantize_tiles(make_weights(rng, Nd, Kd)))
+    x = torch.randn((M, K), device="cuda")
+    nw = _dev(rng.uniform(0.5, 1.5, K).astype(np.float32))
+    gate, up = torch.randn((M, Kd), device="cuda"), torch.randn((M, Kd), device="cuda")
+    rs = torch.empty((M,), device="cuda")
+    outs = [torch.empty((M, n), device="cuda") for n in Ns]
+    yd = [torch.empty((M, Nd), device="cuda")]
+
+    def step(stream=None):
+        t4.LIB.tcq4_b200_rms_row_scale(x.data_ptr(), rs.data_ptr(), M, K, 1e-6, stream.cuda_stream if stream else 0)
+        t4.mul_mat_fanout_input(tl, x, Ns, t4.INPUT_RMS_NORM_MUL, row_scale=rs, col_weight=nw, outs=outs, stream=stream)
+        t4.mul_mat_fanout_input([wd], gate, [Nd], t4.INPUT_SWIGLU, x2=up, outs=yd, stream=stream)
+    t4.reserve(M, max(Ns + [Nd]), max(K, Kd))
+    step()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    st = torch.cuda.Stream()
+    st.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(st):
+        with torch.cuda.graph(g, stream=st):
+            step(st)
+    torch.cuda.current_stream().wait_stream(st)
+    for _ in range(2):
+        x.normal_()
+        gate.normal_()
+        up.normal_()
+        g.replay()
+        torch.cuda.synchronize()
+        xn = t4.apply_input(t4.INPUT_RMS_NORM_MUL, x, row_scale=t4.rms_row_scale(x, 1e-6), col_weight=nw)
+        want = t4.Fanout(tl, Ns, K)(xn)
+        assert torch.equal(outs[0], want[0]) and torch.equal(outs[1], want[1])
+        assert torch.equal(yd[0], t4.mul_mat(wd, t4.apply_input(t4.INPUT_SWIGLU, gate, x2=up), Nd))
