@@ -158,3 +158,42 @@ def test_gemm4_fuzz_fanout_groups(t4):
             want = t4.mul_mat(t, x, n, kernel=t4.KERNEL_GEMM2)
             e = nmse(out.cpu().numpy(), want.cpu().numpy())
             assert e <= 1e-12, (M, K, Ns, n, e)
+
+
+@pytest.mark.parametrize("M", [12, 40, 64])
+def test_gemm4_chain_of_groups_in_a_cuda_graph(t4, M):
+    """a decode-batch layer's worth of launches back to back under programmatic dependent launch, captured and replayed: every
+    mode of the planner in one chain on ONE shared arena (whole blocks, K halves with the outputs cleared by K1, K parts with
+    arrival counters, stream-K over > 148 blocks), each output checked against the pair GEMM after every replay"""
+    rng = np.random.default_rng(91)
+    shapes = [([1024, 256, 256], 1024), ([512], 4096), ([9600, 9600], 512), ([256], 6144), ([392], 2048)]
+    nodes, ref = [], []
+    for Ns, K in shapes:
+        x = torch.randn((M, K), device="cuda")
+        for n in Ns:
+            w = t4.random_tiles(n, K, seed=n + K)
+            out = torch.empty((M, n), device="cuda")
+            nodes.append((w, x, out, n, ""))
+    t4.reserve(M, 9600, 6144)
+    g = t4.GgmlGraph(nodes)
+    g.compute()
+    torch.cuda.synchronize()
+    cg = torch.cuda.CUDAGraph()
+    st = torch.cuda.Stream()
+    st.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(st):
+        with torch.cuda.graph(cg, stream=st):
+            g.compute(stream=st)
+    torch.cuda.current_stream().wait_stream(st)
+    for rep in range(3):
+        for (_, x, out, _, _) in nodes:
+            out.fill_(float("nan"))
+        for x in {id(n[1]): n[1] for n in nodes}.values():
+            x.normal_()
+        for _ in range(2):                     # twice on the same inputs: counters and cleared outputs must come back clean
+            cg.replay()
+        torch.cuda.synchronize()
+        for (w, x, out, n, _) in nodes:
+            want = t4.mul_mat(w, x, n, kernel=t4.KERNEL_GEMM2)
+            e = nmse(out.cpu().numpy(), want.cpu().numpy())
+            assert e <= 1e-12, (M, n, x.shape[1], rep, e)
