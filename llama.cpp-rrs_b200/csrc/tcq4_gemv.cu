@@ -155,7 +155,7 @@ __device__ __forceinline__ void gv_store_act_block(const ActQuant &a, uint8_t *b
 // Pre-pass for M * K/256 > GV_PREPASS_BLOCKS: inside the GEMV every CTA repeats the activation stage for all rows
 // (M = 8, K = 14336: 448 blocks on 16 warps = 28 rounds, 20 us); here the blocks are spread over the whole GPU once and
 // the GEMV copies the finished codes and scales (M*K + 40*M*K/256 bytes, L2-resident) into its shared memory.
-constexpr int GV_PREPASS_BLOCKS = 32;
+constexpr int GV_PREPASS_BLOCKS = 16;      // round 2: 32 -> 16 (M = 2, 3 on K = 2560 .. 4096: a decode layer 6 % faster, tests/gpu_decode_layer.py)
 constexpr int GV_PREPASS_PERM_BLOCKS = 16;
 constexpr int GVP_WARPS = 4;
 
@@ -743,7 +743,8 @@ bool gemv_plan(int64_t M, int64_t N, int64_t K, int num_sms, size_t smem_optin, 
     static const bool nopre = getenv("TCQ4_GV_NOPRE") != nullptr;
     // M = 1 keeps the stage inside the kernel: consecutive M = 1 launches share an SM (dependent launch), and a kernel
     // between them costs more than the 2-4 rounds it saves (K = 14336: 14.1 us inside, 15.6 us with the pre-pass)
-    plan->prepass = !nopre && M >= 2 && M * KT > GV_PREPASS_BLOCKS;
+    static const int pre_b = getenv("TCQ4_GV_PRE_BLOCKS") ? atoi(getenv("TCQ4_GV_PRE_BLOCKS")) : GV_PREPASS_BLOCKS;      // experiments
+    plan->prepass = !nopre && M >= 2 && M * KT > pre_b;
     // with a channel permutation every block is a gather (two dependent loads per element): there the pre-pass pays from 17
     // blocks, M = 1 included (Llama-3-8B layer with imatrix perms, graph: M = 1 61.2 -> 56.8 us, M = 2 66.1 -> 55.4 us)
     plan->prepass_perm = !nopre && M * KT > GV_PREPASS_PERM_BLOCKS;
