@@ -217,8 +217,9 @@ struct G4Params {
     int id_blocks;                    // 128-channel blocks of one expert
 };
 
-// NCH = Mt / 32 (1 or 2)
-template <int NCH, bool DEBUG>
+// NCH = Mt / 32 (1 or 2).  ID: the MUL_MAT_ID walk over (chunk, block) pairs -- an instantiation of its own, because its
+// scatter code inside the epilogue cost the plain kernel 7 % when it was a run-time branch (register allocation of the hot loop)
+template <int NCH, bool DEBUG, bool ID = false>
 __global__ void __launch_bounds__(G4_THREADS, 1)
 tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K, int num_blocks, int mode, int parts, float *__restrict__ partials,
                   int *__restrict__ counters, int32_t *__restrict__ dbg_isum, int exp) {
@@ -271,7 +272,7 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
     // this CTA's range of the blocks * KT line, walked segment by segment (block nb, k-tiles [kt0, kt1)) by every role
     // (mode G4_WHOLE: ranges of whole blocks only -- strided outputs cannot be zeroed by K1)
     const bool whole_blocks = (mode == G4_WHOLE);
-    const bool id_mode = P.id_nchunks != nullptr;
+    constexpr bool id_mode = ID;
     if (id_mode) {      // the chunk table comes from the routing kernel two launches ahead: nothing may start before it is there
         pdl_wait();
         num_blocks = __ldcg(P.id_nchunks) * P.id_blocks;
@@ -714,11 +715,13 @@ bool gemm4_plan(int64_t M, const int64_t *Ns, int nseg, int64_t K, int num_sms, 
             for (int64_t p = 3; p <= pmax && !no_parts; p++) {
                 const double fix = 2.0 + 0.6 * (double)((M + 7) / 8) * (double)((p + 3) / 4);
                 const double c = (double)((KT + p - 1) / p) + fix;
-                if (c < best - 1.0) {
+                if (c < best - 0.5) {      // (calibrated on forced part counts, TCQ4_G4_PARTS: N = 4096 / 2560 / 1024, K = 4096 .. 14336, M = 12 .. 64)
                     best = c;
                     bp = (int)p;
                 }
             }
+            static const int force_p = getenv("TCQ4_G4_PARTS") ? atoi(getenv("TCQ4_G4_PARTS")) : 0;      // experiments
+            if (force_p >= 1 && force_p <= pmax) bp = force_p;
             parts = bp;
             grid = blocks * parts;
             // (no_atomic -- a fused residual may sit in y, which can then neither be cleared nor take two adds in either order:
@@ -834,7 +837,7 @@ cudaError_t launch_gemm4_id(const void *w_experts, int64_t n_expert, size_t expe
     cfg.attrs = attr;
     static const bool no_pdl = getenv("TCQ4_NO_PDL") != nullptr;
     cfg.numAttrs = no_pdl ? 0 : 1;
-    return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, false>, P, st, 64, (int)K, 0, (int)G4_WHOLE, 1, (float *)nullptr, (int *)nullptr,
+    return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, false, true>, P, st, 64, (int)K, 0, (int)G4_WHOLE, 1, (float *)nullptr, (int *)nullptr,
                               (int32_t *)nullptr, 0);
 }
 
@@ -853,6 +856,7 @@ cudaError_t gemm4_init_attributes(size_t smem_optin) {
     if ((e = cudaFuncSetAttribute(tcq4_gemm4_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm4Smem::total)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(tcq4_gemm4_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm4Smem::total)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(tcq4_gemm4_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm4Smem::total)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(tcq4_gemm4_kernel<2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm4Smem::total)) != cudaSuccess) return e;
     return cudaFuncSetAttribute(tcq4_gemm4_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm4Smem::total);
 }
 
