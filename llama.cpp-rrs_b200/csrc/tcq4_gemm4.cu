@@ -219,7 +219,8 @@ struct G4Params {
 
 // NCH = Mt / 32 (1 or 2).  ID: the MUL_MAT_ID walk over (chunk, block) pairs -- an instantiation of its own, because its
 // scatter code inside the epilogue cost the plain kernel 7 % when it was a run-time branch (register allocation of the hot loop)
-template <int NCH, bool DEBUG, bool ID = false>
+// EXTRA: the K-parts reduction and the bias / residual start values are compiled in (same reason: code the plain launch never runs)
+template <int NCH, bool DEBUG, bool ID = false, bool EXTRA = false>
 __global__ void __launch_bounds__(G4_THREADS, 1)
 tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K, int num_blocks, int mode, int parts, float *__restrict__ partials,
                   int *__restrict__ counters, int32_t *__restrict__ dbg_isum, int exp) {
@@ -531,7 +532,7 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
             }
 #pragma unroll
             for (int i = 0; i < MT / 2; i++) acc2[i] = 0ull;
-            if ((P.bias != nullptr || P.res != nullptr) && kt0 == 0 && n < N) {
+            if (EXTRA && (P.bias != nullptr || P.res != nullptr) && kt0 == 0 && n < N) {
                 const float bv = P.bias ? __ldg(P.bias + n) : 0.0f;
 #pragma unroll
                 for (int i = 0; i < MT / 2; i++) {
@@ -599,7 +600,7 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
                 }
             }
             // ---- end of the segment.  A warp stores 32 consecutive channels of one token: coalesced.
-            if (mode == G4_PARTS) {
+            if (EXTRA && mode == G4_PARTS) {
                 // The block is cut into `parts` K ranges, one CTA each (narrow, deep matrices: every SM gets a share of K).  Each
                 // part leaves its sums in a workspace slot and counts itself in; whoever arrives LAST adds the slots in part order
                 // (its own too, re-read: one code path) and stores -- deterministic, no waiting, no zeroed output.  Counters
@@ -779,14 +780,17 @@ cudaError_t launch_gemm4(const Gemm4Seg *segs, int nseg, ActStage st, int64_t M,
     exp = (getenv("TCQ4_G4_EXP") ? atoi(getenv("TCQ4_G4_EXP")) : 0) | (getenv("TCQ4_G4_PROF") ? 0x100 : 0);
 #endif
     if (dbg_isum && nseg != 1) return cudaErrorInvalidValue;
+    const bool extra = plan.mode == G4_PARTS || res != nullptr || bias != nullptr;
+#define G4_LAUNCH(NCH_, DBG_, EX_)                                                                                                  \
+    cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<NCH_, DBG_, false, EX_>, P, st, (int)M, (int)K, plan.num_blocks, plan.mode, plan.parts, \
+                       partials, counters, dbg_isum, exp)
     if (plan.mt == 32) {
-        if (dbg_isum)
-            return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<1, true>, P, st, (int)M, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, dbg_isum, exp);
-        return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<1, false>, P, st, (int)M, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, (int32_t *)nullptr, exp);
+        if (dbg_isum) return extra ? G4_LAUNCH(1, true, true) : G4_LAUNCH(1, true, false);
+        return extra ? G4_LAUNCH(1, false, true) : G4_LAUNCH(1, false, false);
     }
-    if (dbg_isum)
-        return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, true>, P, st, (int)M, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, dbg_isum, exp);
-    return cudaLaunchKernelEx(&cfg, tcq4_gemm4_kernel<2, false>, P, st, (int)M, (int)K, plan.num_blocks, plan.mode, plan.parts, partials, counters, (int32_t *)nullptr, exp);
+    if (dbg_isum) return extra ? G4_LAUNCH(2, true, true) : G4_LAUNCH(2, true, false);
+    return extra ? G4_LAUNCH(2, false, true) : G4_LAUNCH(2, false, false);
+#undef G4_LAUNCH
 }
 
 // MUL_MAT_ID with device-side routing: one launch over (chunk, block) pairs; the chunk count lives on the device, so the grid is
@@ -853,11 +857,15 @@ cudaError_t gemm4_read_prof(long long *host_out, size_t bytes) {
 cudaError_t gemm4_init_attributes(size_t smem_optin) {
     if ((size_t)Gemm4Smem::total > smem_optin) return cudaErrorInvalidValue;
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(tcq4_gemm4_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm4Smem::total)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(tcq4_gemm4_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm4Smem::total)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(tcq4_gemm4_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm4Smem::total)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(tcq4_gemm4_kernel<2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm4Smem::total)) != cudaSuccess) return e;
-    return cudaFuncSetAttribute(tcq4_gemm4_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm4Smem::total);
+#define G4_ATTR(...)                                                                                                                \
+    if ((e = cudaFuncSetAttribute(tcq4_gemm4_kernel<__VA_ARGS__>, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm4Smem::total)) != \
+        cudaSuccess)                                                                                                                \
+        return e;
+    G4_ATTR(1, true, false, false) G4_ATTR(1, true, false, true) G4_ATTR(1, false, false, false) G4_ATTR(1, false, false, true)
+    G4_ATTR(2, true, false, false) G4_ATTR(2, true, false, true) G4_ATTR(2, false, false, false) G4_ATTR(2, false, false, true)
+    G4_ATTR(2, false, true, false)
+#undef G4_ATTR
+    return cudaSuccess;
 }
 
 }  // namespace tcq4
