@@ -179,6 +179,9 @@ __device__ __noinline__ float g4_zero_point_term(const uint8_t *__restrict__ w, 
 
 // Timeline stamps and what-if switches (diagnostics build only, TCQ4_G4_PROF / TCQ4_G4_EXP): SM clocks of the middle CTA,
 // [role 4: MMA issuer, widening warp 0, widening warp 15, epilogue warp 0][k-tile 64][event 8]
+#ifndef G4_NOZP
+#define G4_NOZP 0
+#endif
 constexpr int G4_PROF_KT = 64;
 enum { G4_WHOLE = 0, G4_TWO = 1, G4_PARTS = 2 };      // how the ranges of the blocks * KT line meet in y (Gemm4Plan::mode)
 #ifdef TCQ4_DIAG
@@ -192,6 +195,14 @@ __device__ long long g_g4_prof[4 * G4_PROF_KT * 8];
 #define G4_STAMP(role, kt, ev) do { } while (0)
 #define G4_EXP(bit) false
 #endif
+
+// the same summed over the k-tiles [kt0, kt1) of a segment (tiles without zero points contribute exact zeros)
+__device__ __noinline__ float g4_zero_point_range(const uint8_t *__restrict__ w, const int16_t *__restrict__ sumq,
+                                                  const float *__restrict__ a7, int m, int n, int kt0, int kt1, int KT) {
+    float z = 0.0f;
+    for (int kt = kt0; kt < kt1; kt++) z += g4_zero_point_term(w, sumq, m, n, kt, KT, a7[(size_t)m * KT + kt]);
+    return z;
+}
 
 // up to four matrices over the same tokens (a fan-out group: Q/K/V, gate/up): their 128-channel blocks form one line
 struct G4Params {
@@ -532,6 +543,7 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
             }
 #pragma unroll
             for (int i = 0; i < MT / 2; i++) acc2[i] = 0ull;
+            int zseen = 0;
             if (EXTRA && (P.bias != nullptr || P.res != nullptr) && kt0 == 0 && n < N) {
                 const float bv = P.bias ? __ldg(P.bias + n) : 0.0f;
 #pragma unroll
@@ -588,15 +600,19 @@ tcq4_gemm4_kernel(const __grid_constant__ G4Params P, ActStage st, int M, int K,
                     }
                 }
                 G4_ESTAMP(4);
-                if (anyz && n < N) {
+                zseen |= anyz;
+            }
+            // Zero points (cold: the quantiser writes Z = 0): their term of every k-tile of the segment is added here, after the
+            // loop -- as 64 call sites inside the loop the same code cost the plain path 2-4 %.  The sum is the same set of terms in
+            // another order (last-bit differences against the per-k-tile form of the other kernels; the oracle bar holds).
+            if (!G4_NOZP && zseen && n < N) {
 #pragma unroll
-                    for (int i = 0; i < MT / 2; i++) {
-                        float a, bb;
-                        g4_unpack(acc2[i], a, bb);
-                        if (2 * i < M) a += g4_zero_point_term(w, st.sumq, vrow0 + 2 * i, n, kt, KT, st.a7[(size_t)(vrow0 + 2 * i) * KT + kt]);
-                        if (2 * i + 1 < M) bb += g4_zero_point_term(w, st.sumq, vrow0 + 2 * i + 1, n, kt, KT, st.a7[(size_t)(vrow0 + 2 * i + 1) * KT + kt]);
-                        acc2[i] = g4_pack(a, bb);
-                    }
+                for (int i = 0; i < MT / 2; i++) {
+                    float a, bb;
+                    g4_unpack(acc2[i], a, bb);
+                    if (2 * i < M) a += g4_zero_point_range(w, st.sumq, st.a7, vrow0 + 2 * i, n, kt0, kt1, KT);
+                    if (2 * i + 1 < M) bb += g4_zero_point_range(w, st.sumq, st.a7, vrow0 + 2 * i + 1, n, kt0, kt1, KT);
+                    acc2[i] = g4_pack(a, bb);
                 }
             }
             // ---- end of the segment.  A warp stores 32 consecutive channels of one token: coalesced.
